@@ -1,0 +1,367 @@
+// C-ABI implementation (include/ggrm.h): handle life cycle, chunk streaming, kernel launches, read-out.
+// Host-side orchestration only; all arithmetic happens in the kernels of prep_kernels.cuh, syrk_tc.cuh,
+// syrk_f64.cuh and pack_kernels.cuh.  There is deliberately no CPU fallback anywhere in this file.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <numeric>
+
+#include "ggrm_internal.h"
+#include "pack_kernels.cuh"
+
+namespace ggrm {
+
+static thread_local std::string g_create_error;
+
+static inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+// ---------------------------------------------------------------------------------------------------------------
+// TMA descriptor for a K-major 16-bit operand matrix Z[n_pad][k_cap]: box = 64 elements (128 B) x 128 rows,
+// 128-byte swizzle — the smem image tcgen05 descriptors (make_smem_desc_sw128) expect.
+void encode_tensor_map(CUtensorMap* map, void* base, int64_t k_cap, int64_t n_pad, bool fp16) {
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                 const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                 CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = nullptr;
+    if (encode == nullptr) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        GGRM_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+        if (fn == nullptr || qres != cudaDriverEntryPointSuccess) {
+            throw CudaError{GGRM_ERR_CUDA, "CUDA: cuTensorMapEncodeTiled entry point not available"};
+        }
+        encode = reinterpret_cast<EncodeFn>(fn);
+    }
+    const cuuint64_t dims[2] = {static_cast<cuuint64_t>(k_cap), static_cast<cuuint64_t>(n_pad)};
+    const cuuint64_t strides[1] = {static_cast<cuuint64_t>(k_cap) * 2};
+    const cuuint32_t box[2] = {64, 128};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = encode(map, fp16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base,
+                              dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        throw CudaError{GGRM_ERR_CUDA, "CUDA: cuTensorMapEncodeTiled failed with code " + std::to_string(static_cast<int>(r))};
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Tile ownership + persistent work lists.  The lower triangle of 256x256 tiles is cut into 8x8-tile super-tiles
+// (2048x2048 entries); super-tiles are the unit of ownership (2D-tile multi-GPU mode, LPT over their tile counts)
+// and of scheduling order (CTAs that run at the same time work inside one or two super-tiles and share Z panels in L2).
+void build_ownership_and_items(Handle& h) {
+    const int64_t T = h.ntiles_side;
+    constexpr int64_t ST = 8;
+    const int64_t nst = (T + ST - 1) / ST;
+    struct Super { int64_t si, sj, cost; int owner; };
+    std::vector<Super> supers;
+    for (int64_t si = 0; si < nst; ++si) {
+        for (int64_t sj = 0; sj <= si; ++sj) {
+            int64_t cost = 0;
+            for (int64_t I = si * ST; I < std::min(T, (si + 1) * ST); ++I)
+                for (int64_t J = sj * ST; J < std::min(T, (sj + 1) * ST); ++J) cost += (J <= I);
+            supers.push_back({si, sj, cost, 0});
+        }
+    }
+    const int world = std::max(1, h.cfg.tile_world);
+    if (world > 1) {
+        std::vector<size_t> order(supers.size());
+        std::iota(order.begin(), order.end(), size_t{0});
+        std::stable_sort(order.begin(), order.end(), [&](size_t a, size_t b) { return supers[a].cost > supers[b].cost; });
+        std::vector<int64_t> load(world, 0);
+        for (size_t idx : order) {
+            const int r = static_cast<int>(std::min_element(load.begin(), load.end()) - load.begin());
+            supers[idx].owner = r;
+            load[r] += supers[idx].cost;
+        }
+    }
+    h.slot_of_host.assign(static_cast<size_t>(T * (T + 1) / 2), -1);
+    std::vector<TcItem> tc;
+    std::vector<F64Item> f64;
+    int32_t slot = 0;
+    for (const Super& s : supers) {
+        if (s.owner != h.cfg.tile_rank) continue;
+        for (int64_t I = s.si * ST; I < std::min(T, (s.si + 1) * ST); ++I) {
+            for (int64_t J = s.sj * ST; J < std::min(T, (s.sj + 1) * ST); ++J) {
+                if (J > I) continue;
+                h.slot_of_host[static_cast<size_t>(I * (I + 1) / 2 + J)] = slot;
+                const int64_t off = static_cast<int64_t>(slot) * 65536;
+                if (h.fp64) {
+                    for (int bi = 0; bi < 4; ++bi)
+                        for (int bj = 0; bj < 4; ++bj) {
+                            if (I == J && bj > bi) continue;
+                            f64.push_back({static_cast<int32_t>(I * 256 + bi * 64), static_cast<int32_t>(J * 256 + bj * 64),
+                                           off + static_cast<int64_t>(bi) * 64 * 256 + bj * 64});
+                        }
+                } else if (h.tc_mode == 2) {
+                    tc.push_back({static_cast<int32_t>(I * 256), static_cast<int32_t>(J * 256), off});
+                } else {
+                    tc.push_back({static_cast<int32_t>(I * 256), static_cast<int32_t>(J * 256), off});
+                    tc.push_back({static_cast<int32_t>(I * 256 + 128), static_cast<int32_t>(J * 256), off + kHalfTileElems});
+                }
+                ++slot;
+            }
+        }
+    }
+    h.owned_tiles = slot;
+    h.accum_elems = static_cast<int64_t>(slot) * 65536;
+    GGRM_CUDA(cudaMalloc(&h.d_slot_of, std::max<size_t>(1, h.slot_of_host.size()) * sizeof(int32_t)));
+    GGRM_CUDA(cudaMemcpy(h.d_slot_of, h.slot_of_host.data(), h.slot_of_host.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    h.num_items_tc = static_cast<int>(tc.size());
+    h.num_items_f64 = static_cast<int>(f64.size());
+    if (!tc.empty()) {
+        GGRM_CUDA(cudaMalloc(&h.d_items_tc, tc.size() * sizeof(TcItem)));
+        GGRM_CUDA(cudaMemcpy(h.d_items_tc, tc.data(), tc.size() * sizeof(TcItem), cudaMemcpyHostToDevice));
+    }
+    if (!f64.empty()) {
+        GGRM_CUDA(cudaMalloc(&h.d_items_f64, f64.size() * sizeof(F64Item)));
+        GGRM_CUDA(cudaMemcpy(h.d_items_f64, f64.data(), f64.size() * sizeof(F64Item), cudaMemcpyHostToDevice));
+    }
+}
+
+static void check_device(int device, int* sm_count) {
+    int count = 0;
+    const cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count <= 0) {
+        throw CudaError{GGRM_ERR_NO_DEVICE, "no CUDA device visible; the B200 GRM engine has no CPU fallback"};
+    }
+    if (device < 0 || device >= count) {
+        throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "device ordinal " + std::to_string(device) + " out of range"};
+    }
+    cudaDeviceProp prop;
+    GGRM_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        throw CudaError{GGRM_ERR_NO_DEVICE, std::string("device '") + prop.name + "' is sm_" + std::to_string(prop.major) +
+                                                std::to_string(prop.minor) + "; this library is built for sm_100a only"};
+    }
+    if (sm_count != nullptr) *sm_count = prop.multiProcessorCount;
+    GGRM_CUDA(cudaSetDevice(device));
+}
+
+static void free_handle(Handle* h) {
+    if (h == nullptr) return;
+    cudaSetDevice(h->cfg.device);
+    cudaDeviceSynchronize();
+    auto fr = [](void* p) { if (p != nullptr) cudaFree(p); };
+    fr(h->d_slot_of); fr(h->d_items_tc); fr(h->d_items_f64); fr(h->d_out_to_raw);
+    fr(h->d_raw[0]); fr(h->d_raw[1]); fr(h->d_dense); fr(h->d_counts); fr(h->d_freq);
+    for (int k = 0; k < 2; ++k) {
+        fr(h->d_tab16[k]); fr(h->d_tab64[k]); fr(h->d_Z[k]); fr(h->whole[k]);
+        for (void* p : h->pool[k]) fr(p);
+    }
+    fr(h->d_stage); fr(h->d_trace); fr(h->d_fault);
+    for (int i = 0; i < Handle::kRingSlots; ++i) {
+        if (h->ring[i] != nullptr) cudaFreeHost(h->ring[i]);
+        if (h->ring_free[i] != nullptr) cudaEventDestroy(h->ring_free[i]);
+    }
+    for (int i = 0; i < 2; ++i) if (h->raw_free[i] != nullptr) cudaEventDestroy(h->raw_free[i]);
+    if (h->h2d_done != nullptr) cudaEventDestroy(h->h2d_done);
+    for (auto& g : h->groups) if (g.done != nullptr) cudaEventDestroy(g.done);
+    for (auto& t : h->timers) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
+    if (h->s_copy != nullptr) cudaStreamDestroy(h->s_copy);
+    if (h->s_comp != nullptr) cudaStreamDestroy(h->s_comp);
+    if (h->s_fetch != nullptr) cudaStreamDestroy(h->s_fetch);
+    delete h;
+}
+
+static void create_impl(const ggrm_config_t* cfg, Handle* h) {
+    if (cfg->abi_version != GGRM_ABI_VERSION) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "abi_version mismatch"};
+    if (cfg->n_raw <= 0 || cfg->n_out <= 0) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "n_raw and n_out must be positive"};
+    if (cfg->raw_to_out == nullptr && cfg->n_out != cfg->n_raw)
+        throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "identity projection requires n_out == n_raw"};
+    if (cfg->method < 1 || cfg->method > 8) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "Invalid genotype process method."};
+    if (!cfg->want_add && !cfg->want_dom) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "neither additive nor dominance requested"};
+    if (cfg->precision < 0 || cfg->precision > 2) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "invalid precision"};
+    if (cfg->n_groups < 1) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "n_groups must be >= 1"};
+    if (cfg->n_groups > 1 && (cfg->group_begin == nullptr || cfg->group_end == nullptr))
+        throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "group ranges required when n_groups > 1"};
+    if (cfg->m_total <= 0) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "m_total must be positive"};
+    if (cfg->tile_world < 1 || cfg->tile_rank < 0 || cfg->tile_rank >= cfg->tile_world)
+        throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "invalid tile partition"};
+    if (cfg->n_out > (int64_t{1} << 30)) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "n_out too large"};
+
+    h->cfg = *cfg;
+    h->cfg.raw_to_out = nullptr;
+    h->cfg.group_begin = h->cfg.group_end = nullptr;
+    check_device(cfg->device, &h->sm_count);
+    h->n_raw = cfg->n_raw;
+    h->n_out = cfg->n_out;
+    h->n_pad = round_up(cfg->n_out, kTile);
+    h->bpv_raw = (cfg->n_raw + 3) / 4;
+    h->bpv_pad = h->n_pad / 4;
+    h->ntiles_side = h->n_pad / kTile;
+    h->fp64 = cfg->precision == GGRM_PREC_FP64;
+    h->elem_bytes = h->fp64 ? 8 : 4;
+    if (const char* e = std::getenv("GGRM_TC_MODE")) h->tc_mode = std::atoi(e) == 2 ? 2 : 1;
+
+    // groups
+    h->groups.resize(static_cast<size_t>(cfg->n_groups));
+    for (int g = 0; g < cfg->n_groups; ++g) {
+        h->groups[g].begin = cfg->n_groups == 1 && cfg->group_begin == nullptr ? 0 : cfg->group_begin[g];
+        h->groups[g].end = cfg->n_groups == 1 && cfg->group_end == nullptr ? cfg->m_total : cfg->group_end[g];
+        if (h->groups[g].begin < 0 || h->groups[g].end > cfg->m_total || h->groups[g].begin > h->groups[g].end ||
+            (g > 0 && h->groups[g].begin < h->groups[g - 1].end))
+            throw CudaError{GGRM_ERR_COLUMN_RANGE, "invalid group range " + std::to_string(g)};
+        GGRM_CUDA(cudaEventCreateWithFlags(&h->groups[g].done, cudaEventDisableTiming));
+    }
+
+    // projection: invert raw->out, later raw sample wins (variant_decoder.cpp:79-126)
+    if (cfg->raw_to_out != nullptr) {
+        std::vector<int32_t> inv(static_cast<size_t>(cfg->n_out), -1);
+        bool identity = cfg->n_out == cfg->n_raw;
+        for (int64_t i = 0; i < cfg->n_raw; ++i) {
+            const int32_t t = cfg->raw_to_out[i];
+            if (t < -1 || t >= cfg->n_out) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "raw_to_out entry out of range"};
+            if (t >= 0) inv[static_cast<size_t>(t)] = static_cast<int32_t>(i);
+            if (t != i) identity = false;
+        }
+        if (!identity) {
+            GGRM_CUDA(cudaMalloc(&h->d_out_to_raw, inv.size() * sizeof(int32_t)));
+            GGRM_CUDA(cudaMemcpy(h->d_out_to_raw, inv.data(), inv.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+        }
+    }
+
+    GGRM_CUDA(cudaStreamCreateWithFlags(&h->s_copy, cudaStreamNonBlocking));
+    GGRM_CUDA(cudaStreamCreateWithFlags(&h->s_comp, cudaStreamNonBlocking));
+    GGRM_CUDA(cudaStreamCreateWithFlags(&h->s_fetch, cudaStreamNonBlocking));
+    GGRM_CUDA(cudaEventCreateWithFlags(&h->h2d_done, cudaEventDisableTiming));
+    for (int i = 0; i < 2; ++i) GGRM_CUDA(cudaEventCreateWithFlags(&h->raw_free[i], cudaEventDisableTiming));
+
+    build_ownership_and_items(*h);
+
+    // ---- memory plan -------------------------------------------------------------------------------------------
+    size_t free_b = 0, total_b = 0;
+    GGRM_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    const int kinds = (cfg->want_add ? 1 : 0) + (cfg->want_dom ? 1 : 0);
+    const int64_t accum_bytes = std::max<int64_t>(h->accum_elems, 4) * h->elem_bytes;
+    const bool want_whole = cfg->n_groups > 1 && cfg->keep_whole;
+    const int64_t z_elem = h->fp64 ? 8 : 2;
+    const int64_t per_snp = h->n_pad * z_elem * kinds + 2 * h->bpv_raw + h->bpv_pad + 128;
+    int64_t avail = static_cast<int64_t>(free_b) - (int64_t{1} << 30) - (want_whole ? accum_bytes * kinds : 0);
+    const int64_t min_chunk = std::min<int64_t>(round_up(cfg->m_total, 64), 4096) * per_snp;
+    int pool_n = 1;
+    if (cfg->n_groups > 1) {
+        int64_t fit = (avail - min_chunk) / (accum_bytes * kinds);
+        if (cfg->max_resident_groups > 0) fit = std::min<int64_t>(fit, cfg->max_resident_groups);
+        pool_n = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(fit, cfg->n_groups)));
+    }
+    avail -= static_cast<int64_t>(pool_n) * accum_bytes * kinds;
+    int64_t k_cap;
+    if (cfg->chunk_snps > 0) {
+        k_cap = round_up(cfg->chunk_snps, 64);
+    } else {
+        const int64_t budget = std::min<int64_t>(int64_t{24} << 30, avail / 2);
+        k_cap = std::max<int64_t>(1024, std::min<int64_t>(65536, budget / per_snp / 1024 * 1024));
+    }
+    k_cap = std::min<int64_t>(k_cap, round_up(cfg->m_total, 64));
+    if (k_cap * per_snp > avail)
+        throw CudaError{GGRM_ERR_OUT_OF_MEMORY, "not enough device memory for accumulators plus one SNP chunk (need " +
+                                                    std::to_string((k_cap * per_snp) >> 20) + " MiB more)"};
+    h->k_cap = k_cap;
+
+    for (int kind = 0; kind < 2; ++kind) {
+        if (!(kind == 0 ? cfg->want_add : cfg->want_dom)) continue;
+        for (int p = 0; p < pool_n; ++p) {
+            void* buf = nullptr;
+            GGRM_CUDA(cudaMalloc(&buf, static_cast<size_t>(accum_bytes)));
+            h->pool[kind].push_back(buf);
+            h->pool_owner[kind].push_back(-1);
+        }
+        if (want_whole) {
+            GGRM_CUDA(cudaMalloc(&h->whole[kind], static_cast<size_t>(accum_bytes)));
+            GGRM_CUDA(cudaMemsetAsync(h->whole[kind], 0, static_cast<size_t>(accum_bytes), h->s_comp));
+        }
+        GGRM_CUDA(cudaMalloc(&h->d_Z[kind], static_cast<size_t>(h->n_pad * k_cap * z_elem)));
+        if (h->fp64) {
+            GGRM_CUDA(cudaMalloc(&h->d_tab64[kind], static_cast<size_t>(k_cap) * sizeof(SnpTable)));
+        } else {
+            GGRM_CUDA(cudaMalloc(&h->d_tab16[kind], static_cast<size_t>(k_cap) * sizeof(uint2)));
+            encode_tensor_map(&h->tmap[kind], h->d_Z[kind], k_cap, h->n_pad, cfg->precision == GGRM_PREC_FP16);
+        }
+    }
+    for (int i = 0; i < 2; ++i) GGRM_CUDA(cudaMalloc(&h->d_raw[i], static_cast<size_t>(k_cap * h->bpv_raw)));
+    GGRM_CUDA(cudaMalloc(&h->d_dense, static_cast<size_t>(k_cap * h->bpv_pad)));
+    if (cfg->keep_stats) {
+        GGRM_CUDA(cudaMalloc(&h->d_counts, static_cast<size_t>(cfg->m_total) * sizeof(int4)));
+        GGRM_CUDA(cudaMalloc(&h->d_freq, static_cast<size_t>(cfg->m_total) * sizeof(double)));
+        GGRM_CUDA(cudaMemsetAsync(h->d_counts, 0, static_cast<size_t>(cfg->m_total) * sizeof(int4), h->s_comp));
+        GGRM_CUDA(cudaMemsetAsync(h->d_freq, 0, static_cast<size_t>(cfg->m_total) * sizeof(double), h->s_comp));
+    }
+    GGRM_CUDA(cudaMalloc(&h->d_trace, sizeof(double)));
+    GGRM_CUDA(cudaMalloc(&h->d_fault, sizeof(int)));
+    GGRM_CUDA(cudaMemsetAsync(h->d_fault, 0, sizeof(int), h->s_comp));
+
+    if (!h->fp64) {
+        GGRM_CUDA(cudaFuncSetAttribute(syrk_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcConfig<1>::kSmemBytes));
+        GGRM_CUDA(cudaFuncSetAttribute(syrk_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcConfig<2>::kSmemBytes));
+    }
+    GGRM_CUDA(cudaStreamSynchronize(h->s_comp));
+}
+
+}  // namespace ggrm
+
+using namespace ggrm;
+
+#define GGRM_API_BEGIN(h)                          \
+    if ((h) == nullptr) return GGRM_ERR_INVALID_ARGUMENT; \
+    try {                                          \
+        GGRM_CUDA(cudaSetDevice((h)->cfg.device));
+#define GGRM_API_END(h)                            \
+    }                                              \
+    catch (const CudaError& e) {                   \
+        (h)->last_error = e.msg;                   \
+        return e.status;                           \
+    }                                              \
+    catch (const std::bad_alloc&) {                \
+        (h)->last_error = "host allocation failed"; \
+        return GGRM_ERR_OUT_OF_MEMORY;             \
+    }                                              \
+    catch (const std::exception& e) {              \
+        (h)->last_error = e.what();                \
+        return GGRM_ERR_INVALID_OPERATION;         \
+    }                                              \
+    return GGRM_OK;
+
+extern "C" int ggrm_create(const ggrm_config_t* cfg, ggrm_t** out) {
+    if (cfg == nullptr || out == nullptr) {
+        g_create_error = "null argument";
+        return GGRM_ERR_INVALID_ARGUMENT;
+    }
+    *out = nullptr;
+    Handle* h = nullptr;
+    try {
+        h = new Handle();
+        create_impl(cfg, h);
+    } catch (const CudaError& e) {
+        g_create_error = e.msg;
+        free_handle(h);
+        return e.status;
+    } catch (const std::bad_alloc&) {
+        g_create_error = "host allocation failed";
+        free_handle(h);
+        return GGRM_ERR_OUT_OF_MEMORY;
+    }
+    *out = reinterpret_cast<ggrm_t*>(h);
+    return GGRM_OK;
+}
+
+extern "C" void ggrm_destroy(ggrm_t* h) { free_handle(reinterpret_cast<Handle*>(h)); }
+
+extern "C" const char* ggrm_last_error(const ggrm_t* h) {
+    if (h == nullptr) return g_create_error.c_str();
+    return reinterpret_cast<const Handle*>(h)->last_error.c_str();
+}
+
+extern "C" int ggrm_device_count(void) {
+    int c = 0;
+    if (cudaGetDeviceCount(&c) != cudaSuccess) return 0;
+    return c;
+}
+
+extern "C" const char* ggrm_version(void) { return "gelex-grm-b200 0.1 (sm_100a; tcgen05 SYRK)"; }
+
+#include "ggrm_api_stream.inl"
+#include "ggrm_api_fetch.inl"
+#include "ggrm_api_hooks.inl"

@@ -1,0 +1,209 @@
+// Part of ggrm_api.cu: read-out (packed lower rows, trace, normalised / LOCO forms), accumulator access for the
+// multi-GPU reduce, peer reduce.
+
+namespace ggrm {
+
+static inline int64_t tri(int64_t i) { return i * (i + 1) / 2; }
+
+// Resolve (kind, group) to a device accumulator; makes sure the data is final and returns the event to wait on
+// (nullptr when the device is already idle for it).
+static void* resolve_accum(Handle& h, int kind, int group, cudaEvent_t* wait_on) {
+    *wait_on = nullptr;
+    if (kind != GGRM_KIND_ADD && kind != GGRM_KIND_DOM) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "kind must be 0 (add) or 1 (dom)"};
+    if (h.pool[kind].empty()) throw CudaError{GGRM_ERR_INVALID_OPERATION, kind == 0 ? "additive matrix was not requested" : "dominance matrix was not requested"};
+    const int ng = static_cast<int>(h.groups.size());
+    if (group == GGRM_GROUP_WHOLE && ng > 1) {
+        if (h.whole[kind] == nullptr) throw CudaError{GGRM_ERR_INVALID_OPERATION, "whole-genome matrix requires keep_whole when n_groups > 1"};
+        if (!h.finished) throw CudaError{GGRM_ERR_INVALID_OPERATION, "whole-genome matrix is available after ggrm_finish"};
+        return h.whole[kind];
+    }
+    const int g = group == GGRM_GROUP_WHOLE ? 0 : group;
+    if (g < 0 || g >= ng) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "group index out of range"};
+    GroupState& gs = h.groups[g];
+    if (!gs.started) {
+        if (!h.finished && !(h.cur_group > g)) throw CudaError{GGRM_ERR_INVALID_OPERATION, "group is not complete yet: push a later group or call ggrm_finish"};
+        start_group(h, g);  // no SNP of this group was pushed on this handle: an all-zero partial
+        gs.folded = true;
+        complete_group(h, g);
+    }
+    if (!gs.complete) throw CudaError{GGRM_ERR_INVALID_OPERATION, "group is not complete yet: push a later group or call ggrm_finish"};
+    if (gs.buffer[kind] < 0) throw CudaError{GGRM_ERR_INVALID_OPERATION, "group accumulator was released"};
+    *wait_on = gs.done;
+    return h.pool[kind][gs.buffer[kind]];
+}
+
+template <typename TAcc>
+__global__ void __launch_bounds__(256) trace_kernel(const TAcc* __restrict__ A, const int32_t* __restrict__ slot_of, int64_t n,
+                                                    double* __restrict__ trace) {
+    double local = 0.0;
+    for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int64_t I = i >> 8;
+        const int32_t slot = slot_of[I * (I + 1) / 2 + I];
+        if (slot >= 0) local += static_cast<double>(A[static_cast<int64_t>(slot) * 65536 + tile_elem_offset<TAcc>(static_cast<int>(i & 255), static_cast<int>(i & 255))]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+    if ((threadIdx.x & 31) == 0) atomicAdd(trace, local);
+}
+
+template <typename TAcc>
+static double full_trace(Handle& h, const TAcc* A) {
+    GGRM_CUDA(cudaMemsetAsync(h.d_trace, 0, sizeof(double), h.s_fetch));
+    trace_kernel<TAcc><<<std::max(1, std::min<int>(static_cast<int>((h.n_out + 255) / 256), h.sm_count * 4)), 256, 0, h.s_fetch>>>(A, h.d_slot_of, h.n_out, h.d_trace);
+    GGRM_CUDA(cudaGetLastError());
+    ++h.kernel_launches;
+    double t = 0.0;
+    GGRM_CUDA(cudaMemcpyAsync(&t, h.d_trace, sizeof(double), cudaMemcpyDeviceToHost, h.s_fetch));
+    GGRM_CUDA(cudaStreamSynchronize(h.s_fetch));
+    return t;
+}
+
+// mode 0: raw accumulator   mode 1: G/(trace/n)   mode 2: (G_whole - G_group)/(k_whole - k_group)
+template <typename TAcc, typename TOut>
+static void fetch_typed(Handle& h, int kind, int group, int64_t row_begin, int64_t row_count, TOut* out, double* trace_out, int mode) {
+    if (row_begin < 0 || row_count < 0 || row_begin + row_count > h.n_out)
+        throw CudaError{GGRM_ERR_COLUMN_RANGE, "row range outside [0, n_out)"};
+    if (out == nullptr && row_count > 0) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "null output buffer"};
+    if (mode != 0 && h.cfg.tile_world > 1) throw CudaError{GGRM_ERR_INVALID_OPERATION, "normalised / LOCO read-out needs the full trace: not available in 2D-tile mode"};
+    cudaEvent_t ev = nullptr;
+    const TAcc* A = static_cast<const TAcc*>(resolve_accum(h, kind, group, &ev));
+    if (ev != nullptr) GGRM_CUDA(cudaStreamWaitEvent(h.s_fetch, ev, 0));
+    const TAcc* B = nullptr;
+    double scale = 1.0;
+    if (mode == 1) {
+        const double tr = full_trace<TAcc>(h, A);
+        scale = static_cast<double>(h.n_out) / tr;
+    } else if (mode == 2) {
+        cudaEvent_t ev2 = nullptr;
+        const TAcc* W = static_cast<const TAcc*>(resolve_accum(h, kind, GGRM_GROUP_WHOLE, &ev2));
+        if (ev2 != nullptr) GGRM_CUDA(cudaStreamWaitEvent(h.s_fetch, ev2, 0));
+        const double kw = full_trace<TAcc>(h, W) / static_cast<double>(h.n_out);
+        const double kc = full_trace<TAcc>(h, A) / static_cast<double>(h.n_out);
+        B = A;
+        A = W;
+        scale = 1.0 / (kw - kc);
+    }
+    if (h.d_stage == nullptr) {
+        const int64_t want = std::min<int64_t>(int64_t{256} << 20, std::max<int64_t>(tri(h.n_out) * 8, h.n_out * 8 + 1024));
+        h.stage_bytes = std::max<int64_t>(want, h.n_out * 8);
+        GGRM_CUDA(cudaMalloc(&h.d_stage, static_cast<size_t>(h.stage_bytes)));
+    }
+    const int64_t stage_elems = h.stage_bytes / static_cast<int64_t>(sizeof(TOut));
+    phase_begin(h, h.s_fetch, 4);
+    GGRM_CUDA(cudaMemsetAsync(h.d_trace, 0, sizeof(double), h.s_fetch));
+    int64_t r = row_begin;
+    const int64_t r_end = row_begin + row_count;
+    int64_t written = 0;
+    while (r < r_end) {
+        int64_t cnt = 1;
+        // largest cnt with tri(r+cnt) - tri(r) <= stage_elems (at least one row; a row always fits by construction)
+        {
+            int64_t lo = 1, hi = r_end - r;
+            while (lo < hi) {
+                const int64_t mid = (lo + hi + 1) / 2;
+                if (tri(r + mid) - tri(r) <= stage_elems) lo = mid; else hi = mid - 1;
+            }
+            cnt = lo;
+        }
+        const int64_t elems = tri(r + cnt) - tri(r);
+        pack_rows_kernel<TAcc, TOut><<<static_cast<unsigned>(cnt), 256, 0, h.s_fetch>>>(A, B, h.d_slot_of, r, cnt, scale, static_cast<TOut*>(h.d_stage), h.d_trace);
+        GGRM_CUDA(cudaGetLastError());
+        ++h.kernel_launches;
+        GGRM_CUDA(cudaMemcpyAsync(out + written, h.d_stage, static_cast<size_t>(elems) * sizeof(TOut), cudaMemcpyDeviceToHost, h.s_fetch));
+        written += elems;
+        r += cnt;
+    }
+    double tr = 0.0;
+    GGRM_CUDA(cudaMemcpyAsync(&tr, h.d_trace, sizeof(double), cudaMemcpyDeviceToHost, h.s_fetch));
+    phase_end(h, h.s_fetch);
+    GGRM_CUDA(cudaStreamSynchronize(h.s_fetch));
+    if (trace_out != nullptr) *trace_out = tr;
+    if (h.finished) collect_timers(h);
+}
+
+template <typename TOut>
+static void fetch_dispatch(Handle& h, int kind, int group, int64_t row_begin, int64_t row_count, TOut* out, double* trace_out, int mode) {
+    if (h.fp64) fetch_typed<double, TOut>(h, kind, group, row_begin, row_count, out, trace_out, mode);
+    else fetch_typed<float, TOut>(h, kind, group, row_begin, row_count, out, trace_out, mode);
+}
+
+}  // namespace ggrm
+
+extern "C" int ggrm_fetch(ggrm_t* hh, int kind, int group, int64_t row_begin, int64_t row_count, float* out_lower_rows, double* trace_out) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    fetch_dispatch<float>(*h, kind, group, row_begin, row_count, out_lower_rows, trace_out, 0);
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_fetch_f64(ggrm_t* hh, int kind, int group, int64_t row_begin, int64_t row_count, double* out_lower_rows, double* trace_out) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    fetch_dispatch<double>(*h, kind, group, row_begin, row_count, out_lower_rows, trace_out, 0);
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_fetch_normalized(ggrm_t* hh, int kind, int group, int64_t row_begin, int64_t row_count, double* out_lower_rows) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    fetch_dispatch<double>(*h, kind, group, row_begin, row_count, out_lower_rows, nullptr, 1);
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_fetch_loco(ggrm_t* hh, int kind, int group, int64_t row_begin, int64_t row_count, double* out_lower_rows) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    if (h->groups.size() < 2) throw CudaError{GGRM_ERR_INVALID_OPERATION, "LOCO read-out needs n_groups > 1 and keep_whole"};
+    fetch_dispatch<double>(*h, kind, group, row_begin, row_count, out_lower_rows, nullptr, 2);
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_release_group(ggrm_t* hh, int kind, int group) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    if (kind < 0 || kind > 1 || group < 0 || group >= static_cast<int>(h->groups.size())) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "invalid kind/group"};
+    GroupState& gs = h->groups[group];
+    if (!gs.complete) throw CudaError{GGRM_ERR_INVALID_OPERATION, "cannot release a group that is still accumulating"};
+    if (gs.buffer[kind] >= 0) {
+        GGRM_CUDA(cudaStreamSynchronize(h->s_fetch));
+        GGRM_CUDA(cudaEventSynchronize(gs.done));  // the fold into `whole` must have consumed it
+        h->pool_owner[kind][gs.buffer[kind]] = -1;
+        gs.buffer[kind] = -1;
+    }
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_accum_buffer(ggrm_t* hh, int kind, int group, void** d_ptr, int64_t* n_elems, int32_t* elem_bytes) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    cudaEvent_t ev = nullptr;
+    void* p = resolve_accum(*h, kind, group, &ev);
+    if (ev != nullptr) GGRM_CUDA(cudaEventSynchronize(ev));
+    if (d_ptr != nullptr) *d_ptr = p;
+    if (n_elems != nullptr) *n_elems = h->accum_elems;
+    if (elem_bytes != nullptr) *elem_bytes = h->elem_bytes;
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_reduce_peer(ggrm_t* hh, int kind, int group, const void* const* peers, int n_peers, int64_t slice_begin, int64_t slice_end) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    if (n_peers < 0 || n_peers > kMaxPeers) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "n_peers must be 0..7"};
+    if (slice_begin < 0 || slice_end > h->accum_elems || slice_begin > slice_end || (slice_begin & 3) || (slice_end & 3))
+        throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "slice must be 4-element aligned and inside the accumulator"};
+    cudaEvent_t ev = nullptr;
+    void* mine = resolve_accum(*h, kind, group, &ev);
+    if (ev != nullptr) GGRM_CUDA(cudaStreamWaitEvent(h->s_comp, ev, 0));
+    PeerPtrs pp{};
+    for (int i = 0; i < n_peers; ++i) pp.p[i] = peers[i];
+    const int64_t len = slice_end - slice_begin;
+    if (len > 0 && n_peers > 0) {
+        const int blocks = static_cast<int>(std::min<int64_t>((len / 4 + 255) / 256, h->sm_count * 8));
+        if (h->fp64) reduce_peers_kernel<double><<<blocks, 256, 0, h->s_comp>>>(static_cast<double*>(mine), pp, n_peers, slice_begin, slice_end);
+        else reduce_peers_kernel<float><<<blocks, 256, 0, h->s_comp>>>(static_cast<float*>(mine), pp, n_peers, slice_begin, slice_end);
+        GGRM_CUDA(cudaGetLastError());
+        ++h->kernel_launches;
+    }
+    GGRM_CUDA(cudaStreamSynchronize(h->s_comp));
+    GGRM_API_END(h)
+}

@@ -1,0 +1,126 @@
+// Part of ggrm_api.cu: stateless test hooks (bit-exact layers) and the synthetic BED generator entry points.
+
+namespace ggrm {
+
+struct ScratchFree {
+    std::vector<void*> ptrs;
+    ~ScratchFree() { for (void* p : ptrs) if (p != nullptr) cudaFree(p); }
+    template <typename T>
+    T* alloc(size_t n) {
+        void* p = nullptr;
+        GGRM_CUDA(cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)));
+        ptrs.push_back(p);
+        return static_cast<T*>(p);
+    }
+};
+
+static void decode_common(int device, const uint8_t* payload, int64_t snp_count, int64_t bpv, int64_t n_raw, int64_t n_out,
+                          const int32_t* raw_to_out, int method, int kind, int policy, bool standardise, double* out, double* freq) {
+    check_device(device, nullptr);
+    if (payload == nullptr || out == nullptr) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "null argument"};
+    if (n_raw <= 0 || n_out <= 0 || snp_count <= 0 || snp_count > 65535) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "test hook limits: 0 < snp_count <= 65535"};
+    if (bpv != (n_raw + 3) / 4) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "bytes_per_variant != ceil(n_raw/4)"};
+    if (raw_to_out == nullptr && n_out != n_raw) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "identity projection requires n_out == n_raw"};
+    if (standardise && (method < 1 || method > 8)) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "Invalid genotype process method."};
+    const int64_t n_pad = round_up(n_out, kTile), bpv_pad = n_pad / 4;
+    ScratchFree sf;
+    uint8_t* d_raw = sf.alloc<uint8_t>(static_cast<size_t>(snp_count * bpv));
+    uint8_t* d_dense = sf.alloc<uint8_t>(static_cast<size_t>(snp_count * bpv_pad));
+    double* d_out = sf.alloc<double>(static_cast<size_t>(snp_count * n_out));
+    int32_t* d_inv = nullptr;
+    if (raw_to_out != nullptr) {
+        std::vector<int32_t> inv(static_cast<size_t>(n_out), -1);
+        for (int64_t i = 0; i < n_raw; ++i) {
+            const int32_t t = raw_to_out[i];
+            if (t < -1 || t >= n_out) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "raw_to_out entry out of range"};
+            if (t >= 0) inv[static_cast<size_t>(t)] = static_cast<int32_t>(i);
+        }
+        d_inv = sf.alloc<int32_t>(inv.size());
+        GGRM_CUDA(cudaMemcpy(d_inv, inv.data(), inv.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    }
+    GGRM_CUDA(cudaMemcpy(d_raw, payload, static_cast<size_t>(snp_count * bpv), cudaMemcpyHostToDevice));
+    repack_kernel<<<static_cast<unsigned>(snp_count), 256>>>(d_raw, bpv, d_dense, bpv_pad, n_out, d_inv, snp_count);
+    GGRM_CUDA(cudaGetLastError());
+    SnpTable* d_tab = nullptr;
+    double* d_freq = nullptr;
+    if (standardise) {
+        d_tab = sf.alloc<SnpTable>(static_cast<size_t>(snp_count));
+        d_freq = sf.alloc<double>(static_cast<size_t>(snp_count));
+        StatsOut so{};
+        so.freq = d_freq;
+        so.tab64[kind] = d_tab;
+        count_stats_kernel<<<static_cast<unsigned>((snp_count + 7) / 8), 256>>>(d_dense, bpv_pad, n_out, n_pad, snp_count, method, policy, 0, so, 0);
+        GGRM_CUDA(cudaGetLastError());
+    }
+    const dim3 grid(static_cast<unsigned>((n_out + 255) / 256), static_cast<unsigned>(snp_count));
+    decode_colmajor_kernel<<<grid, 256>>>(d_dense, bpv_pad, n_out, snp_count, d_tab, d_out);
+    GGRM_CUDA(cudaGetLastError());
+    GGRM_CUDA(cudaMemcpy(out, d_out, static_cast<size_t>(snp_count * n_out) * sizeof(double), cudaMemcpyDeviceToHost));
+    if (standardise && freq != nullptr) GGRM_CUDA(cudaMemcpy(freq, d_freq, static_cast<size_t>(snp_count) * sizeof(double), cudaMemcpyDeviceToHost));
+}
+
+}  // namespace ggrm
+
+#define GGRM_STATELESS_BEGIN try {
+#define GGRM_STATELESS_END                    \
+    }                                         \
+    catch (const CudaError& e) {              \
+        g_create_error = e.msg;               \
+        return e.status;                      \
+    }                                         \
+    catch (const std::bad_alloc&) {           \
+        g_create_error = "host allocation failed"; \
+        return GGRM_ERR_OUT_OF_MEMORY;        \
+    }                                         \
+    return GGRM_OK;
+
+extern "C" int ggrm_decode_chunk(int device, const uint8_t* bed_payload, int64_t snp_count, int64_t bytes_per_variant, int64_t n_raw,
+                                 int64_t n_out, const int32_t* raw_to_out, double* out_colmajor) {
+    GGRM_STATELESS_BEGIN
+    decode_common(device, bed_payload, snp_count, bytes_per_variant, n_raw, n_out, raw_to_out, 0, 0, 0, false, out_colmajor, nullptr);
+    GGRM_STATELESS_END
+}
+
+extern "C" int ggrm_standardise_chunk(int device, const uint8_t* bed_payload, int64_t snp_count, int64_t bytes_per_variant, int64_t n_raw,
+                                      int64_t n_out, const int32_t* raw_to_out, int method, int kind, int all_missing_policy,
+                                      double* out_colmajor, double* freq) {
+    GGRM_STATELESS_BEGIN
+    if (kind != GGRM_KIND_ADD && kind != GGRM_KIND_DOM) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "kind must be 0 (add) or 1 (dom)"};
+    decode_common(device, bed_payload, snp_count, bytes_per_variant, n_raw, n_out, raw_to_out, method, kind, all_missing_policy, true,
+                  out_colmajor, freq);
+    GGRM_STATELESS_END
+}
+
+static uint32_t miss_threshold(double missing_rate) {
+    if (!(missing_rate > 0.0)) return 0u;
+    if (missing_rate >= 1.0) return 1u << 24;
+    return static_cast<uint32_t>(missing_rate * 16777216.0);
+}
+
+extern "C" int ggrm_synth_bed_host(uint8_t* out, int64_t n, int64_t snp_begin, int64_t snp_count, uint64_t seed, double missing_rate) {
+    if (out == nullptr || n <= 0 || snp_begin < 0 || snp_count < 0) {
+        g_create_error = "invalid argument";
+        return GGRM_ERR_INVALID_ARGUMENT;
+    }
+    const int64_t bpv = (n + 3) / 4;
+    const uint32_t thr = miss_threshold(missing_rate);
+    for (int64_t s = 0; s < snp_count; ++s) {
+        const ggrm_snp_thresholds t = ggrm_synth_thresholds(seed, snp_begin + s);
+        for (int64_t b = 0; b < bpv; ++b) out[s * bpv + b] = ggrm_synth_byte(seed, snp_begin + s, b, n, t, thr);
+    }
+    return GGRM_OK;
+}
+
+extern "C" int ggrm_synth_bed_device(int device, uint8_t* d_out, int64_t n, int64_t snp_begin, int64_t snp_count, uint64_t seed,
+                                     double missing_rate) {
+    GGRM_STATELESS_BEGIN
+    check_device(device, nullptr);
+    if (d_out == nullptr || n <= 0 || snp_begin < 0 || snp_count < 0) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "invalid argument"};
+    if (snp_count > 0) {
+        const int64_t bpv = (n + 3) / 4;
+        synth_bed_kernel<<<static_cast<unsigned>(snp_count), 256>>>(d_out, n, bpv, snp_begin, snp_count, seed, miss_threshold(missing_rate));
+        GGRM_CUDA(cudaGetLastError());
+        GGRM_CUDA(cudaDeviceSynchronize());
+    }
+    GGRM_STATELESS_END
+}

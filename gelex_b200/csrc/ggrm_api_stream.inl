@@ -1,0 +1,309 @@
+// Part of ggrm_api.cu: chunk streaming (push / flush / finish), per-SNP statistics read-back, timers.
+
+namespace ggrm {
+
+static void phase_begin(Handle& h, cudaStream_t s, int phase) {
+    Timer t;
+    GGRM_CUDA(cudaEventCreate(&t.a));
+    GGRM_CUDA(cudaEventCreate(&t.b));
+    t.phase = phase;
+    GGRM_CUDA(cudaEventRecord(t.a, s));
+    h.timers.push_back(t);
+}
+static void phase_end(Handle& h, cudaStream_t s) { GGRM_CUDA(cudaEventRecord(h.timers.back().b, s)); }
+
+static void collect_timers(Handle& h) {
+    for (auto& t : h.timers) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess) h.phase_ms[t.phase] += ms;
+        cudaEventDestroy(t.a);
+        cudaEventDestroy(t.b);
+    }
+    h.timers.clear();
+}
+
+static int group_of(const Handle& h, int64_t snp) {
+    int lo = 0, hi = static_cast<int>(h.groups.size()) - 1;
+    while (lo <= hi) {
+        const int mid = (lo + hi) / 2;
+        if (snp < h.groups[mid].begin) hi = mid - 1;
+        else if (snp >= h.groups[mid].end) lo = mid + 1;
+        else return mid;
+    }
+    return -1;
+}
+
+static void start_group(Handle& h, int g) {
+    GroupState& gs = h.groups[g];
+    if (gs.started) return;
+    for (int kind = 0; kind < 2; ++kind) {
+        if (h.pool[kind].empty()) continue;
+        int slot = -1;
+        for (size_t p = 0; p < h.pool_owner[kind].size(); ++p)
+            if (h.pool_owner[kind][p] < 0) { slot = static_cast<int>(p); break; }
+        if (slot < 0)
+            throw CudaError{GGRM_ERR_OUT_OF_MEMORY,
+                            "accumulator pool exhausted: fetch and ggrm_release_group completed groups, or raise max_resident_groups"};
+        h.pool_owner[kind][slot] = g;
+        gs.buffer[kind] = slot;
+        GGRM_CUDA(cudaMemsetAsync(h.pool[kind][slot], 0, static_cast<size_t>(std::max<int64_t>(h.accum_elems, 4)) * h.elem_bytes, h.s_comp));
+    }
+    gs.started = true;
+}
+
+static void complete_group(Handle& h, int g) {
+    GroupState& gs = h.groups[g];
+    if (gs.complete) return;
+    if (gs.started && !gs.folded) {
+        for (int kind = 0; kind < 2; ++kind) {
+            if (h.whole[kind] == nullptr || gs.buffer[kind] < 0 || h.accum_elems == 0) continue;
+            const int blocks = static_cast<int>(std::min<int64_t>((h.accum_elems / 4 + 255) / 256, h.sm_count * 8));
+            if (h.fp64)
+                axpy_accum_kernel<double><<<blocks, 256, 0, h.s_comp>>>(static_cast<double*>(h.whole[kind]),
+                                                                         static_cast<const double*>(h.pool[kind][gs.buffer[kind]]), h.accum_elems);
+            else
+                axpy_accum_kernel<float><<<blocks, 256, 0, h.s_comp>>>(static_cast<float*>(h.whole[kind]),
+                                                                        static_cast<const float*>(h.pool[kind][gs.buffer[kind]]), h.accum_elems);
+            GGRM_CUDA(cudaGetLastError());
+            ++h.kernel_launches;
+        }
+        gs.folded = true;
+    }
+    GGRM_CUDA(cudaEventRecord(gs.done, h.s_comp));
+    gs.complete = true;
+}
+
+static void launch_syrk(Handle& h, int kind, int g, int64_t c) {
+    const GroupState& gs = h.groups[g];
+    void* accum = h.pool[kind][gs.buffer[kind]];
+    if (h.fp64) {
+        if (h.num_items_f64 == 0) return;
+        const int grid = std::min(h.num_items_f64, h.sm_count * 6);
+        syrk_f64_kernel<<<grid, 128, 0, h.s_comp>>>(static_cast<const double*>(h.d_Z[kind]), h.k_cap, c, static_cast<double*>(accum),
+                                                    h.d_items_f64, h.num_items_f64, 1);
+        GGRM_CUDA(cudaGetLastError());
+    } else {
+        if (h.num_items_tc == 0) return;
+        const int nkb = static_cast<int>(round_up(c, 64) / 64);
+        const uint32_t fmt = h.cfg.precision == GGRM_PREC_FP16 ? 0u : 1u;
+        if (h.tc_mode == 2) {
+            const int clusters = std::min(h.num_items_tc, h.sm_count / 2);
+            cudaLaunchConfig_t lc{};
+            lc.gridDim = dim3(static_cast<unsigned>(2 * clusters));
+            lc.blockDim = dim3(256);
+            lc.dynamicSmemBytes = TcConfig<2>::kSmemBytes;
+            lc.stream = h.s_comp;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = 2;
+            attr[0].val.clusterDim.y = 1;
+            attr[0].val.clusterDim.z = 1;
+            lc.attrs = attr;
+            lc.numAttrs = 1;
+            GGRM_CUDA(cudaLaunchKernelEx(&lc, syrk_tc_kernel<2>, h.tmap[kind], static_cast<float*>(accum),
+                                         static_cast<const TcItem*>(h.d_items_tc), h.num_items_tc, nkb, 0, 1, fmt, h.d_fault));
+        } else {
+            const int grid = std::min(h.num_items_tc, h.sm_count);
+            syrk_tc_kernel<1><<<grid, 256, TcConfig<1>::kSmemBytes, h.s_comp>>>(h.tmap[kind], static_cast<float*>(accum), h.d_items_tc,
+                                                                                h.num_items_tc, nkb, 0, 1, fmt, h.d_fault);
+            GGRM_CUDA(cudaGetLastError());
+        }
+    }
+    ++h.syrk_launches;
+    ++h.kernel_launches;
+}
+
+static void flush_chunk(Handle& h) {
+    if (h.cur_count == 0) return;
+    const int b = h.cur_buf;
+    const int64_t c = h.cur_count;
+    const int g = h.cur_group;
+    GGRM_CUDA(cudaEventRecord(h.h2d_done, h.s_copy));
+    GGRM_CUDA(cudaStreamWaitEvent(h.s_comp, h.h2d_done, 0));
+    start_group(h, g);
+
+    phase_begin(h, h.s_comp, 1);
+    repack_kernel<<<static_cast<unsigned>(c), 256, 0, h.s_comp>>>(h.d_raw[b], h.bpv_raw, h.d_dense, h.bpv_pad, h.n_out, h.d_out_to_raw, c);
+    GGRM_CUDA(cudaGetLastError());
+    GGRM_CUDA(cudaEventRecord(h.raw_free[b], h.s_comp));
+    StatsOut so{};
+    so.counts = h.d_counts;
+    so.freq = h.d_freq;
+    for (int kind = 0; kind < 2; ++kind) {
+        so.tab16[kind] = h.d_tab16[kind];
+        so.tab64[kind] = h.d_tab64[kind];
+    }
+    count_stats_kernel<<<static_cast<unsigned>((c + 7) / 8), 256, 0, h.s_comp>>>(
+        h.d_dense, h.bpv_pad, h.n_out, h.n_pad, c, h.cfg.method, h.cfg.all_missing_policy,
+        h.cfg.precision == GGRM_PREC_FP16 ? 1 : 0, so, h.cur_first_snp);
+    GGRM_CUDA(cudaGetLastError());
+    phase_end(h, h.s_comp);
+    h.kernel_launches += 2;
+
+    const dim3 egrid(static_cast<unsigned>((c + 63) / 64), static_cast<unsigned>(h.bpv_pad / 64));
+    for (int kind = 0; kind < 2; ++kind) {
+        if (h.d_Z[kind] == nullptr) continue;
+        phase_begin(h, h.s_comp, 2);
+        if (h.fp64)
+            expand64_kernel<<<egrid, 256, 0, h.s_comp>>>(h.d_dense, h.bpv_pad, h.d_tab64[kind], c, static_cast<double*>(h.d_Z[kind]), h.k_cap);
+        else
+            expand16_kernel<<<egrid, 256, 0, h.s_comp>>>(h.d_dense, h.bpv_pad, h.d_tab16[kind], c, static_cast<uint16_t*>(h.d_Z[kind]), h.k_cap);
+        GGRM_CUDA(cudaGetLastError());
+        phase_end(h, h.s_comp);
+        ++h.kernel_launches;
+        phase_begin(h, h.s_comp, 3);
+        launch_syrk(h, kind, g, c);
+        phase_end(h, h.s_comp);
+    }
+    h.cur_buf ^= 1;
+    h.cur_count = 0;
+    h.cur_first_snp = -1;
+    GGRM_CUDA(cudaStreamWaitEvent(h.s_copy, h.raw_free[h.cur_buf], 0));
+}
+
+static void copy_rows(Handle& h, const uint8_t* src, bool src_is_device, bool src_is_pinned, int64_t rows, uint8_t* dst) {
+    const int64_t bytes = rows * h.bpv_raw;
+    if (src_is_device) {
+        GGRM_CUDA(cudaMemcpyAsync(dst, src, static_cast<size_t>(bytes), cudaMemcpyDeviceToDevice, h.s_copy));
+        return;
+    }
+    if (src_is_pinned) {
+        GGRM_CUDA(cudaMemcpyAsync(dst, src, static_cast<size_t>(bytes), cudaMemcpyHostToDevice, h.s_copy));
+        return;
+    }
+    if (h.ring[0] == nullptr) {
+        h.ring_bytes = std::max<int64_t>(int64_t{32} << 20, h.bpv_raw);
+        for (int i = 0; i < Handle::kRingSlots; ++i) {
+            GGRM_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&h.ring[i]), static_cast<size_t>(h.ring_bytes), cudaHostAllocDefault));
+            GGRM_CUDA(cudaEventCreateWithFlags(&h.ring_free[i], cudaEventDisableTiming));
+        }
+    }
+    int64_t done = 0;
+    while (done < bytes) {
+        const int slot = h.ring_next;
+        h.ring_next = (h.ring_next + 1) % Handle::kRingSlots;
+        GGRM_CUDA(cudaEventSynchronize(h.ring_free[slot]));  // blocks while the ring is full
+        const int64_t n = std::min<int64_t>(h.ring_bytes, bytes - done);
+        std::memcpy(h.ring[slot], src + done, static_cast<size_t>(n));
+        GGRM_CUDA(cudaMemcpyAsync(dst + done, h.ring[slot], static_cast<size_t>(n), cudaMemcpyHostToDevice, h.s_copy));
+        GGRM_CUDA(cudaEventRecord(h.ring_free[slot], h.s_copy));
+        done += n;
+    }
+}
+
+static void push_impl(Handle& h, const uint8_t* payload, bool is_device, int64_t snp_begin, int64_t snp_count, int64_t bpv) {
+    if (h.finished) throw CudaError{GGRM_ERR_INVALID_OPERATION, "ggrm_push after ggrm_finish"};
+    if (payload == nullptr && snp_count > 0) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "null payload"};
+    if (bpv != h.bpv_raw)
+        throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "bytes_per_variant " + std::to_string(bpv) + " != ceil(n_raw/4) = " + std::to_string(h.bpv_raw)};
+    if (snp_begin < 0 || snp_count < 0 || snp_begin + snp_count > h.cfg.m_total)
+        throw CudaError{GGRM_ERR_COLUMN_RANGE, "invalid chunk range: [" + std::to_string(snp_begin) + ", " + std::to_string(snp_begin + snp_count) +
+                                                   "). Total SNPs: " + std::to_string(h.cfg.m_total)};
+    if (snp_count == 0) return;
+    if (snp_begin <= h.last_snp_pushed) throw CudaError{GGRM_ERR_INVALID_OPERATION, "SNP ranges must be pushed in increasing order without overlap"};
+    bool pinned = false;
+    if (!is_device) {
+        cudaPointerAttributes attr{};
+        if (cudaPointerGetAttributes(&attr, payload) == cudaSuccess) pinned = attr.type == cudaMemoryTypeHost;
+        else cudaGetLastError();
+    }
+    phase_begin(h, h.s_copy, 0);
+    const int64_t end = snp_begin + snp_count;
+    int64_t s = snp_begin;
+    while (s < end) {
+        const int g = group_of(h, s);
+        if (g < 0) {  // SNP outside every group: not part of any requested matrix
+            int64_t next = end;
+            for (const auto& gr : h.groups) if (gr.begin > s) { next = std::min(next, gr.begin); break; }
+            s = next;
+            continue;
+        }
+        const int64_t run_end = std::min(end, h.groups[g].end);
+        while (s < run_end) {
+            if (h.cur_count > 0 && (g != h.cur_group || s != h.cur_first_snp + h.cur_count || h.cur_count == h.k_cap)) flush_chunk(h);
+            if (h.cur_count == 0) {
+                for (int og = 0; og < g; ++og)
+                    if (h.groups[og].started && !h.groups[og].complete) complete_group(h, og);
+                h.cur_group = g;
+                h.cur_first_snp = s;
+            }
+            const int64_t take = std::min(run_end - s, h.k_cap - h.cur_count);
+            copy_rows(h, payload + (s - snp_begin) * h.bpv_raw, is_device, pinned, take, h.d_raw[h.cur_buf] + h.cur_count * h.bpv_raw);
+            h.cur_count += take;
+            s += take;
+        }
+    }
+    phase_end(h, h.s_copy);
+    h.last_snp_pushed = end - 1;
+}
+
+static void finish_impl(Handle& h) {
+    if (!h.finished) {
+        flush_chunk(h);
+        for (size_t g = 0; g < h.groups.size(); ++g)
+            if (h.groups[g].started) complete_group(h, static_cast<int>(g));
+        h.finished = true;
+    }
+    const cudaError_t e1 = cudaStreamSynchronize(h.s_copy);
+    const cudaError_t e2 = cudaStreamSynchronize(h.s_comp);
+    if (e1 != cudaSuccess || e2 != cudaSuccess) {
+        int where = 0;
+        cudaMemcpy(&where, h.d_fault, sizeof(int), cudaMemcpyDeviceToHost);
+        throw CudaError{GGRM_ERR_CUDA, std::string("CUDA: device fault during GRM accumulation: ") +
+                                           cudaGetErrorString(e2 != cudaSuccess ? e2 : e1) + " (pipeline wait id " + std::to_string(where) + ")"};
+    }
+    collect_timers(h);
+}
+
+}  // namespace ggrm
+
+extern "C" int ggrm_push(ggrm_t* hh, const uint8_t* bed_payload, int64_t snp_begin, int64_t snp_count, int64_t bytes_per_variant) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    push_impl(*h, bed_payload, false, snp_begin, snp_count, bytes_per_variant);
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_push_device(ggrm_t* hh, const uint8_t* d_bed_payload, int64_t snp_begin, int64_t snp_count, int64_t bytes_per_variant) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    push_impl(*h, d_bed_payload, true, snp_begin, snp_count, bytes_per_variant);
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_finish(ggrm_t* hh) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    finish_impl(*h);
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_snp_stats(ggrm_t* hh, int64_t snp_begin, int64_t snp_count, int32_t* n0, int32_t* n1, int32_t* n2, int32_t* nmiss, double* freq) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    if (!h->cfg.keep_stats) throw CudaError{GGRM_ERR_INVALID_OPERATION, "ggrm_snp_stats requires keep_stats"};
+    if (snp_begin < 0 || snp_count < 0 || snp_begin + snp_count > h->cfg.m_total)
+        throw CudaError{GGRM_ERR_COLUMN_RANGE, "invalid SNP range for ggrm_snp_stats"};
+    if (!h->finished) flush_chunk(*h);
+    GGRM_CUDA(cudaStreamSynchronize(h->s_comp));
+    std::vector<int4> c(static_cast<size_t>(snp_count));
+    GGRM_CUDA(cudaMemcpy(c.data(), h->d_counts + snp_begin, c.size() * sizeof(int4), cudaMemcpyDeviceToHost));
+    for (int64_t i = 0; i < snp_count; ++i) {
+        if (n0 != nullptr) n0[i] = c[i].x;
+        if (n1 != nullptr) n1[i] = c[i].y;
+        if (n2 != nullptr) n2[i] = c[i].z;
+        if (nmiss != nullptr) nmiss[i] = c[i].w;
+    }
+    if (freq != nullptr) GGRM_CUDA(cudaMemcpy(freq, h->d_freq + snp_begin, static_cast<size_t>(snp_count) * sizeof(double), cudaMemcpyDeviceToHost));
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_get_timers(ggrm_t* hh, double* out7) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    if (out7 == nullptr) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "null output"};
+    for (int i = 0; i < 5; ++i) out7[i] = h->phase_ms[i];
+    out7[5] = static_cast<double>(h->syrk_launches);
+    out7[6] = static_cast<double>(h->kernel_launches);
+    GGRM_API_END(h)
+}

@@ -1,0 +1,112 @@
+// Internal state of a ggrm handle (one CUDA device).  Not part of the ABI.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/ggrm.h"
+#include "prep_kernels.cuh"
+#include "syrk_f64.cuh"
+#include "syrk_tc.cuh"
+
+namespace ggrm {
+
+struct CudaError {
+    int status;
+    std::string msg;
+};
+
+#define GGRM_CUDA(expr)                                                                                              \
+    do {                                                                                                             \
+        cudaError_t _e = (expr);                                                                                     \
+        if (_e != cudaSuccess) {                                                                                     \
+            throw ::ggrm::CudaError{_e == cudaErrorMemoryAllocation ? GGRM_ERR_OUT_OF_MEMORY : GGRM_ERR_CUDA,        \
+                                    std::string("CUDA: ") + cudaGetErrorString(_e) + " at " #expr};                  \
+        }                                                                                                            \
+    } while (0)
+
+struct GroupState {
+    int64_t begin = 0, end = 0;
+    int buffer[2] = {-1, -1};     // accumulator pool slot per kind (-1 = none yet / released)
+    bool started = false;
+    bool complete = false;        // all SNPs accumulated (+ folded into whole); `done` event recorded
+    bool folded = false;
+    cudaEvent_t done = nullptr;
+};
+
+struct Timer {
+    cudaEvent_t a, b;
+    int phase;
+};
+
+struct Handle {
+    ggrm_config_t cfg{};
+    std::string last_error;
+    int sm_count = 148;
+    // geometry
+    int64_t n_raw = 0, n_out = 0, n_pad = 0, bpv_raw = 0, bpv_pad = 0;
+    int64_t ntiles_side = 0;              // n_pad / 256
+    int64_t k_cap = 0;                    // SNP capacity of one device chunk (multiple of 64)
+    bool fp64 = false;
+    int elem_bytes = 4;
+    int tc_mode = 1;                      // 1 = single-CTA UMMA 128x256, 2 = CTA-pair UMMA 256x256
+    // ownership and work lists
+    std::vector<int32_t> slot_of_host;    // [ntiles_side*(ntiles_side+1)/2] -> slot or -1
+    int64_t owned_tiles = 0;
+    int32_t* d_slot_of = nullptr;
+    TcItem* d_items_tc = nullptr;
+    int num_items_tc = 0;
+    F64Item* d_items_f64 = nullptr;
+    int num_items_f64 = 0;
+    // projection
+    int32_t* d_out_to_raw = nullptr;      // nullptr = identity
+    // streams
+    cudaStream_t s_copy = nullptr, s_comp = nullptr, s_fetch = nullptr;
+    // chunk buffers
+    uint8_t* d_raw[2] = {nullptr, nullptr};
+    cudaEvent_t raw_free[2] = {nullptr, nullptr};
+    cudaEvent_t h2d_done = nullptr;
+    uint8_t* d_dense = nullptr;
+    int4* d_counts = nullptr;             // [m_total] when keep_stats
+    double* d_freq = nullptr;
+    uint2* d_tab16[2] = {nullptr, nullptr};
+    SnpTable* d_tab64[2] = {nullptr, nullptr};
+    void* d_Z[2] = {nullptr, nullptr};
+    CUtensorMap tmap[2];
+    // pinned staging ring (pageable callers)
+    static constexpr int kRingSlots = 4;
+    uint8_t* ring[kRingSlots] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ring_free[kRingSlots] = {nullptr, nullptr, nullptr, nullptr};
+    int64_t ring_bytes = 0;
+    int ring_next = 0;
+    // accumulators
+    int64_t accum_elems = 0;              // owned_tiles * 65536
+    std::vector<void*> pool[2];           // per kind
+    std::vector<int> pool_owner[2];       // group index or -1
+    void* whole[2] = {nullptr, nullptr};  // n_groups>1 && keep_whole
+    std::vector<GroupState> groups;
+    // current chunk
+    int cur_buf = 0;
+    int64_t cur_count = 0, cur_first_snp = -1;
+    int cur_group = -1;
+    int64_t last_snp_pushed = -1;
+    bool finished = false;
+    // fetch staging
+    void* d_stage = nullptr;
+    int64_t stage_bytes = 0;
+    double* d_trace = nullptr;
+    int* d_fault = nullptr;               // mbarrier-timeout location written by a stuck SYRK before it traps
+    // timers
+    std::vector<Timer> timers;
+    double phase_ms[7] = {0, 0, 0, 0, 0, 0, 0};
+    int64_t syrk_launches = 0, kernel_launches = 0;
+};
+
+// implemented in ggrm_api.cu
+void build_ownership_and_items(Handle& h);
+void encode_tensor_map(CUtensorMap* map, void* base, int64_t k_cap, int64_t n_pad, bool fp16);
+
+}  // namespace ggrm

@@ -1,0 +1,361 @@
+// K1-K3 of the GRM path: sample projection (repack), genotype counts + allele frequency + code-policy value
+// tables, and expansion of packed 2-bit genotypes into K-major 16-bit (or FP64) operand panels.
+// HBM-bound byte/integer work: coalesced 16-byte loads, warp-shuffle reductions, smem-staged transposes.
+//
+// Reference semantics reproduced here (all file:line under /root/reference):
+//   decode LUT           src/data/decode_lut.h:40-41          00->2.0  01->NaN  10->1.0  11->0.0
+//   sample projection    src/data/bed_pipe/variant_decoder.cpp:79-126 (scatter, later raw sample wins)
+//   per-SNP process()    include/gelex/internal/genotype_processor/genotype_processor.h:35-58
+//   encode policies      include/gelex/internal/genotype_processor/encode_policy.h:32-81
+//   statistic policies   include/gelex/internal/genotype_processor/statistic_policy.h:43-175
+#pragma once
+#include <cstdint>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include "../../include/ggrm.h"
+
+namespace ggrm {
+
+constexpr int kTile = 256;            // GRM storage tile edge; n is padded to a multiple of this
+constexpr uint8_t kAllMissingByte = 0x55;  // four BED "01" codes
+
+// ------------------------------------------------------------------------------------------------------------------
+// K1a: repack.  raw [c][bpv_raw] -> dense [c][bpv_pad] in GRM row order; rows >= n_out are BED 01 (missing) so that
+// every later kernel can treat padding exactly like a missing call (contributes 0 after mean imputation).
+// out_to_raw == nullptr means identity (the reference's dense path, sample_projection.cpp:51-54).
+// One block per SNP row; a thread produces 4 output bytes (16 samples) per iteration.
+__global__ void __launch_bounds__(256) repack_kernel(const uint8_t* __restrict__ raw, int64_t bpv_raw,
+                                                     uint8_t* __restrict__ dense, int64_t bpv_pad, int64_t n_out,
+                                                     const int32_t* __restrict__ out_to_raw, int64_t snp_count) {
+    const int64_t snp = blockIdx.x;
+    if (snp >= snp_count) return;
+    const uint8_t* src = raw + snp * bpv_raw;
+    uint32_t* dst = reinterpret_cast<uint32_t*>(dense + snp * bpv_pad);
+    const int64_t words = bpv_pad / 4;
+    for (int64_t w = threadIdx.x; w < words; w += blockDim.x) {
+        uint32_t out = 0;
+        const int64_t s0 = w * 16;
+        if (out_to_raw == nullptr) {
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const int64_t byte = w * 4 + b;
+                const int64_t first = byte * 4;
+                uint32_t v = kAllMissingByte;
+                if (first < n_out) {
+                    v = __ldg(src + byte);
+                    const int64_t valid = n_out - first;  // samples of this byte that exist
+                    if (valid < 4) {
+                        const uint32_t keep = (1u << (2 * valid)) - 1u;
+                        v = (v & keep) | (kAllMissingByte & ~keep);
+                    }
+                }
+                out |= v << (8 * b);
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                const int64_t s = s0 + k;
+                uint32_t code = 1u;
+                if (s < n_out) {
+                    const int32_t r = __ldg(out_to_raw + s);
+                    if (r >= 0) code = (__ldg(src + (r >> 2)) >> (2 * (r & 3))) & 3u;
+                }
+                out |= code << (2 * k);
+            }
+        }
+        dst[w] = out;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Code-policy value table of one SNP: z[code] for BED code 0..3 (00=g2, 01=missing, 10=g1, 11=g0), in FP64 with the
+// reference's operation order and no FMA contraction (explicit _rn intrinsics), so that `freq` is bit-identical
+// (integer sum / (2*valid), one IEEE division) and every other quantity agrees to the last ulp or two.
+struct SnpTable {
+    double z[4];
+};
+
+__device__ __forceinline__ void compute_snp_table(int method, int kind, int n0, int n1, int n2, int nmiss,
+                                                  int all_missing_policy, double* freq_out, SnpTable* tab) {
+    const double qnan = __longlong_as_double(0x7ff8000000000000ll);
+    const int validi = n0 + n1 + n2;
+    (void)nmiss;
+    if (validi <= 0) {
+        // genotype_processor.h:38-42: the reference returns early and leaves the column NaN.
+        const double v = (all_missing_policy == GGRM_ALLMISS_SKIP) ? 0.0 : qnan;
+        tab->z[0] = tab->z[1] = tab->z[2] = tab->z[3] = v;
+        *freq_out = 0.0;  // LocusStatistic{} default
+        return;
+    }
+    const double valid = static_cast<double>(validi);
+    const double sum = static_cast<double>(n1 + 2 * n2);  // exact integer
+    const double maf = __ddiv_rn(sum, __dmul_rn(2.0, valid));
+    *freq_out = maf;
+
+    const bool orth = (method == GGRM_ORTH_STANDARDIZE_HWE || method == GGRM_ORTH_CENTER_HWE ||
+                       method == GGRM_ORTH_STANDARDIZE || method == GGRM_ORTH_CENTER);
+    const bool hwe = (method <= GGRM_ORTH_CENTER_HWE);
+    const bool scale = (method == GGRM_STANDARDIZE_HWE || method == GGRM_ORTH_STANDARDIZE_HWE ||
+                        method == GGRM_STANDARDIZE || method == GGRM_ORTH_STANDARDIZE);
+    // encode (encode_policy.h): Add no-op; Dom raw 2->0; Dom orth 1->2p, 2->4p-2
+    double e0 = 0.0, e1 = 1.0, e2 = 2.0;
+    if (kind == GGRM_KIND_DOM) {
+        if (orth) {
+            e2 = __dsub_rn(__dmul_rn(4.0, maf), 2.0);
+            e1 = __dmul_rn(2.0, maf);
+        } else {
+            e2 = 0.0;
+        }
+    }
+    double mean, sd;
+    const double one_m = __dsub_rn(1.0, maf);
+    if (hwe && !orth) {  // HWEPolicy, statistic_policy.h:81-127
+        if (kind == GGRM_KIND_ADD) {
+            mean = __dmul_rn(maf, 2.0);
+            sd = __dsqrt_rn(__dmul_rn(__dmul_rn(2.0, maf), one_m));
+        } else {
+            mean = __dmul_rn(__dmul_rn(2.0, one_m), maf);
+            const double p_sq = __dmul_rn(maf, maf);
+            const double q_sq = __dmul_rn(one_m, one_m);
+            sd = __dsqrt_rn(__dmul_rn(__dmul_rn(__dmul_rn(2.0, maf), one_m), __dadd_rn(p_sq, q_sq)));
+        }
+    } else if (hwe && orth) {  // OrthHWEPolicy, statistic_policy.h:129-175
+        const double dsd = __dmul_rn(__dmul_rn(2.0, maf), one_m);
+        if (kind == GGRM_KIND_ADD) {
+            mean = __dmul_rn(maf, 2.0);
+            sd = __dsqrt_rn(dsd);
+        } else {
+            mean = __dmul_rn(__dmul_rn(2.0, maf), maf);
+            sd = dsd;
+        }
+    } else {  // SamplePolicy, statistic_policy.h:43-79
+        if (kind == GGRM_KIND_ADD) {
+            mean = __dmul_rn(maf, 2.0);
+        } else {
+            const double s = __dadd_rn(__dmul_rn(static_cast<double>(n1), e1), __dmul_rn(static_cast<double>(n2), e2));
+            mean = __ddiv_rn(s, valid);
+        }
+        const double c0 = __dsub_rn(e0, mean), c1 = __dsub_rn(e1, mean), c2 = __dsub_rn(e2, mean);
+        double ss = __dmul_rn(static_cast<double>(n0), __dmul_rn(c0, c0));
+        ss = __dadd_rn(ss, __dmul_rn(static_cast<double>(n1), __dmul_rn(c1, c1)));
+        ss = __dadd_rn(ss, __dmul_rn(static_cast<double>(n2), __dmul_rn(c2, c2)));
+        sd = __dsqrt_rn(__ddiv_rn(ss, __dsub_rn(valid, 1.0)));
+    }
+    double z0 = __dsub_rn(e0, mean), z1 = __dsub_rn(e1, mean), z2 = __dsub_rn(e2, mean);
+    double zm = __dsub_rn(mean, mean);  // missing -> mean -> centred (0, or NaN if mean is not finite)
+    const bool mono = sd < 1e-10;       // MONOMORPHIC_TOL; NaN compares false exactly like the reference
+    if (scale && !mono) {
+        z0 = __ddiv_rn(z0, sd);
+        z1 = __ddiv_rn(z1, sd);
+        z2 = __ddiv_rn(z2, sd);
+        zm = __ddiv_rn(zm, sd);
+    }
+    tab->z[0] = z2;  // BED 00
+    tab->z[1] = zm;  // BED 01
+    tab->z[2] = z1;  // BED 10
+    tab->z[3] = z0;  // BED 11
+}
+
+__device__ __forceinline__ uint16_t to_op16(double v, int fp16) {
+    const float f = __double2float_rn(v);
+    if (fp16) return __half_as_ushort(__float2half_rn(f));
+    return __bfloat16_as_ushort(__float2bfloat16_rn(f));
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// K1b+K2: counts + stats.  One warp per SNP: lanes stride over the dense row in 16-byte words (64 samples each),
+// classify the four 2-bit codes with bit tricks + popc, butterfly-reduce, lane 0 derives frequency and tables.
+//   counts[snp] = {n0, n1, n2, nmiss}     freq[snp]     tab16[kind][snp] = 4 x 16-bit     tab64[kind][snp] = 4 x f64
+struct StatsOut {
+    int4* counts;       // may be nullptr
+    double* freq;       // may be nullptr
+    uint2* tab16[2];    // [kind]; nullptr when that kind / precision is not wanted
+    SnpTable* tab64[2];
+};
+
+__global__ void __launch_bounds__(256) count_stats_kernel(const uint8_t* __restrict__ dense, int64_t bpv_pad,
+                                                          int64_t n_out, int64_t n_pad, int64_t snp_count, int method,
+                                                          int all_missing_policy, int fp16, StatsOut out,
+                                                          int64_t out_offset) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t snp = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + warp;
+    if (snp >= snp_count) return;
+    const uint4* row = reinterpret_cast<const uint4*>(dense + snp * bpv_pad);
+    const int64_t nvec = bpv_pad / 16;
+    int c_miss = 0, c_het = 0, c_hom0 = 0;
+    for (int64_t v = lane; v < nvec; v += 32) {
+        const uint4 w = __ldg(row + v);
+        const uint32_t ws[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t lo = ws[k] & 0x55555555u;
+            const uint32_t hi = (ws[k] >> 1) & 0x55555555u;
+            c_miss += __popc(lo & ~hi);  // 01
+            c_het += __popc(hi & ~lo);   // 10
+            c_hom0 += __popc(hi & lo);   // 11
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        c_miss += __shfl_xor_sync(0xffffffffu, c_miss, o);
+        c_het += __shfl_xor_sync(0xffffffffu, c_het, o);
+        c_hom0 += __shfl_xor_sync(0xffffffffu, c_hom0, o);
+    }
+    if (lane == 0) {
+        const int total = static_cast<int>(n_pad);
+        const int n2 = total - c_miss - c_het - c_hom0;            // 00
+        const int nmiss = c_miss - static_cast<int>(n_pad - n_out);  // padding rows were encoded as missing
+        const int n1 = c_het, n0 = c_hom0;
+        const int64_t o = out_offset + snp;
+        if (out.counts != nullptr) out.counts[o] = make_int4(n0, n1, n2, nmiss);
+        double freq = 0.0;
+#pragma unroll
+        for (int kind = 0; kind < 2; ++kind) {
+            if (out.tab16[kind] == nullptr && out.tab64[kind] == nullptr) continue;
+            SnpTable t;
+            compute_snp_table(method, kind, n0, n1, n2, nmiss, all_missing_policy, &freq, &t);
+            if (out.tab64[kind] != nullptr) out.tab64[kind][snp] = t;
+            if (out.tab16[kind] != nullptr) {
+                const uint32_t a = to_op16(t.z[0], fp16) | (static_cast<uint32_t>(to_op16(t.z[1], fp16)) << 16);
+                const uint32_t b = to_op16(t.z[2], fp16) | (static_cast<uint32_t>(to_op16(t.z[3], fp16)) << 16);
+                out.tab16[kind][snp] = make_uint2(a, b);
+            }
+        }
+        if (out.tab16[0] == nullptr && out.tab64[0] == nullptr && out.tab16[1] == nullptr && out.tab64[1] == nullptr) {
+            SnpTable t;
+            compute_snp_table(method, GGRM_KIND_ADD, n0, n1, n2, nmiss, all_missing_policy, &freq, &t);
+        }
+        if (out.freq != nullptr) out.freq[o] = freq;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// K3: expand to 16-bit operands.  dense [c][bpv_pad] + tab16[c] -> Z [n_pad][k_pad] (K-major: one GRM row = one
+// sample, SNPs contiguous), the layout the TMA/tcgen05 SYRK consumes.  Tile = 64 SNPs x 256 samples:
+//   load : 64 rows x 64 bytes, one 16-byte load per thread, transposed into smem as [byte][snp]
+//   emit : thread (sample, octet) reads 8 contiguous smem bytes (8 SNPs of one sample quad), looks the 8 values up in
+//          the per-SNP tables and writes one 16-byte store; 8 lanes cover one sample's 128 contiguous bytes.
+// SNPs in [snp_count, k_pad) are written as 0 so the SYRK can run whole 64-wide K blocks.
+__global__ void __launch_bounds__(256) expand16_kernel(const uint8_t* __restrict__ dense, int64_t bpv_pad,
+                                                       const uint2* __restrict__ tab16, int64_t snp_count,
+                                                       uint16_t* __restrict__ Z, int64_t k_pad) {
+    __shared__ __align__(16) uint8_t s_t[64][64 + 16];  // [byte][snp], row pitch 80 B keeps 8-byte reads aligned
+    __shared__ uint2 s_tab[64];
+    const int64_t k0 = static_cast<int64_t>(blockIdx.x) * 64;     // first SNP of the tile
+    const int64_t b0 = static_cast<int64_t>(blockIdx.y) * 64;     // first byte (sample/4) of the tile
+    const int tid = threadIdx.x;
+    {
+        const int s = tid >> 2, part = tid & 3;  // SNP row in tile, 16-byte part of its 64 bytes
+        const int64_t snp = k0 + s;
+        uint4 w = make_uint4(0x55555555u, 0x55555555u, 0x55555555u, 0x55555555u);
+        if (snp < snp_count) w = __ldg(reinterpret_cast<const uint4*>(dense + snp * bpv_pad + b0 + part * 16));
+        const uint32_t ws[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int q = 0; q < 16; ++q) s_t[part * 16 + q][s] = static_cast<uint8_t>(ws[q >> 2] >> (8 * (q & 3)));
+        if (tid < 64) s_tab[tid] = (k0 + tid < snp_count) ? __ldg(tab16 + k0 + tid) : make_uint2(0u, 0u);
+    }
+    __syncthreads();
+    const int octet = tid & 7;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+        const int sample = it * 32 + (tid >> 3);  // 0..255 within the tile
+        const uint2 bytes = *reinterpret_cast<const uint2*>(&s_t[sample >> 2][octet * 8]);
+        const int shift = 2 * (sample & 3);
+        uint32_t o[4];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const uint32_t byte = ((u < 4 ? bytes.x : bytes.y) >> (8 * (u & 3))) & 0xFFu;
+            const uint32_t code = (byte >> shift) & 3u;
+            const uint2 t = s_tab[octet * 8 + u];
+            const uint32_t pair = (code & 2u) ? t.y : t.x;
+            const uint32_t val = (code & 1u) ? (pair >> 16) : (pair & 0xFFFFu);
+            if (u & 1) o[u >> 1] |= val << 16; else o[u >> 1] = val;
+        }
+        const int64_t row = b0 * 4 + sample;
+        *reinterpret_cast<uint4*>(Z + row * k_pad + k0 + octet * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+}
+
+// FP64 twin for the DMMA path: Zd [n_pad][k_pad] doubles.  Same tile; a thread writes 8 doubles (64 B).
+__global__ void __launch_bounds__(256) expand64_kernel(const uint8_t* __restrict__ dense, int64_t bpv_pad,
+                                                       const SnpTable* __restrict__ tab64, int64_t snp_count,
+                                                       double* __restrict__ Z, int64_t k_pad) {
+    __shared__ __align__(16) uint8_t s_t[64][64 + 16];
+    __shared__ SnpTable s_tab[64];
+    const int64_t k0 = static_cast<int64_t>(blockIdx.x) * 64;
+    const int64_t b0 = static_cast<int64_t>(blockIdx.y) * 64;
+    const int tid = threadIdx.x;
+    {
+        const int s = tid >> 2, part = tid & 3;
+        const int64_t snp = k0 + s;
+        uint4 w = make_uint4(0x55555555u, 0x55555555u, 0x55555555u, 0x55555555u);
+        if (snp < snp_count) w = __ldg(reinterpret_cast<const uint4*>(dense + snp * bpv_pad + b0 + part * 16));
+        const uint32_t ws[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int q = 0; q < 16; ++q) s_t[part * 16 + q][s] = static_cast<uint8_t>(ws[q >> 2] >> (8 * (q & 3)));
+        if (tid < 64) {
+            SnpTable t;
+            t.z[0] = t.z[1] = t.z[2] = t.z[3] = 0.0;
+            if (k0 + tid < snp_count) t = tab64[k0 + tid];
+            s_tab[tid] = t;
+        }
+    }
+    __syncthreads();
+    const int octet = tid & 7;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+        const int sample = it * 32 + (tid >> 3);
+        const uint2 bytes = *reinterpret_cast<const uint2*>(&s_t[sample >> 2][octet * 8]);
+        const int shift = 2 * (sample & 3);
+        const int64_t row = b0 * 4 + sample;
+        double* dst = Z + row * k_pad + k0 + octet * 8;
+#pragma unroll
+        for (int u = 0; u < 8; u += 2) {
+            const uint32_t c0 = ((((u < 4 ? bytes.x : bytes.y) >> (8 * (u & 3))) & 0xFFu) >> shift) & 3u;
+            const uint32_t c1 = ((((u + 1 < 4 ? bytes.x : bytes.y) >> (8 * ((u + 1) & 3))) & 0xFFu) >> shift) & 3u;
+            *reinterpret_cast<double2*>(dst + u) = make_double2(s_tab[octet * 8 + u].z[c0], s_tab[octet * 8 + u + 1].z[c1]);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Test hook kernels (bit-exact layer): decode to the reference's FP64 column-major chunk, optionally standardised.
+// out[snp * n_out + row]; mode 0 = raw decode (2/1/0/NaN), mode 1 = table lookup (missing -> z[1]).
+__global__ void __launch_bounds__(256) decode_colmajor_kernel(const uint8_t* __restrict__ dense, int64_t bpv_pad,
+                                                              int64_t n_out, int64_t snp_count,
+                                                              const SnpTable* __restrict__ tab64,
+                                                              double* __restrict__ out) {
+    const int64_t snp = blockIdx.y;
+    const int64_t row = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (snp >= snp_count || row >= n_out) return;
+    const uint32_t code = (__ldg(dense + snp * bpv_pad + (row >> 2)) >> (2 * (row & 3))) & 3u;
+    double v;
+    if (tab64 == nullptr) {
+        const double qnan = __longlong_as_double(0x7ff8000000000000ll);
+        v = code == 0u ? 2.0 : (code == 1u ? qnan : (code == 2u ? 1.0 : 0.0));
+    } else {
+        v = tab64[snp].z[code];
+    }
+    out[snp * n_out + row] = v;
+}
+
+// Synthetic payload generator (see synth.h): one thread per output byte.
+}  // namespace ggrm
+
+#include "synth.h"
+
+namespace ggrm {
+__global__ void __launch_bounds__(256) synth_bed_kernel(uint8_t* __restrict__ out, int64_t n, int64_t bpv,
+                                                        int64_t snp_begin, int64_t snp_count, uint64_t seed,
+                                                        uint32_t miss_thr24) {
+    const int64_t snp_local = blockIdx.x;  // one block per SNP row (grid.x may be up to 2^31-1)
+    if (snp_local >= snp_count) return;
+    const int64_t snp = snp_begin + snp_local;
+    const ggrm_snp_thresholds t = ggrm_synth_thresholds(seed, snp);
+    for (int64_t b = threadIdx.x; b < bpv; b += blockDim.x) {
+        out[snp_local * bpv + b] = ggrm_synth_byte(seed, snp, b, n, t, miss_thr24);
+    }
+}
+}  // namespace ggrm

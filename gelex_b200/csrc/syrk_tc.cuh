@@ -1,0 +1,192 @@
+// K4: lower-triangle SYRK  G += Z Z^T  on the 5th-generation tensor cores (tcgen05 + TMEM), replacing cblas_dsyrk
+// (src/data/grm/grm.cpp:51-62).  16-bit operands (BF16 or FP16), FP32 accumulation in TMEM.
+//
+//   Z      [n_pad][k_cap] 16-bit, K-major (row = sample, SNPs contiguous), read by TMA with 128-byte swizzle
+//   G      tile-packed FP32 accumulator: every owned 256x256 tile is two 128-row halves, each stored as
+//          [64 float4-columns][128 rows][4] so that an epilogue warp (one TMEM lane = one row per thread) writes
+//          512 contiguous bytes per instruction
+//   items  persistent work list, ordered by 2048x2048 super-tiles so that CTAs running concurrently share Z panels
+//          in L2 (each panel K-slab leaves HBM about once per super-tile, ~1000 FLOP per HBM byte)
+//
+// Warp roles (256 threads): warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator, warps 4-7 epilogue.
+// Pipelines: smem ring full/empty (TMA <-> MMA), TMEM double buffer full/empty (MMA <-> epilogue).
+//
+// kCtaGroup = 1 : one CTA computes a 128x256 half tile  (UMMA 128x256x16)
+// kCtaGroup = 2 : a CTA pair computes a 256x256 tile     (UMMA 256x256x16, each CTA stages its own 128 A rows and half
+//                 of the B rows, halving smem/L2 operand traffic per FLOP)
+#pragma once
+#include <cstdint>
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include "ptx_sm100.cuh"
+
+namespace ggrm {
+
+struct TcItem {
+    int32_t a_row0;   // first GRM row of the item (128 rows for kCtaGroup 1, 256 for kCtaGroup 2)
+    int32_t b_row0;   // first GRM column (= Z row) of the 256-column block
+    int64_t out_off;  // element offset of the item's first half tile in the accumulator
+};
+
+constexpr int kTcBlockK = 64;                 // 64 x 16-bit = 128 B = one swizzle row
+constexpr int kTcABytes = 128 * 128;          // 128 rows x 128 B
+constexpr int kHalfTileElems = 128 * 256;     // one 128-row half of a storage tile
+
+template <int kCtaGroup>
+struct TcConfig {
+    static constexpr int kBRows = kCtaGroup == 1 ? 256 : 128;  // B rows staged by one CTA
+    static constexpr int kBBytes = kBRows * 128;
+    static constexpr int kStageBytes = kTcABytes + kBBytes;
+    static constexpr int kStages = kCtaGroup == 1 ? 4 : 6;
+    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+    static constexpr uint32_t kUmmaM = 128 * kCtaGroup;
+    static constexpr uint32_t kUmmaN = 256;
+};
+
+template <int kCtaGroup>
+__global__ void __launch_bounds__(256, 1)
+syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ accum, const TcItem* __restrict__ items,
+               int num_items, int num_k_blocks, int k_block0, int accumulate, uint32_t ab_format, int* fault_flag) {
+    using Cfg = TcConfig<kCtaGroup>;
+    constexpr int kStages = Cfg::kStages;
+    extern __shared__ uint8_t smem_raw[];
+    // SWIZZLE_128B operand tiles need 1024-byte alignment.
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + kStages * kTcABytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+    uint64_t* full_bar = bars;
+    uint64_t* empty_bar = bars + kStages;
+    uint64_t* tmem_full_bar = bars + 2 * kStages;
+    uint64_t* tmem_empty_bar = bars + 2 * kStages + 2;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const uint32_t cta_rank = kCtaGroup == 2 ? ptx::cluster_ctarank() : 0u;
+    const bool leader = cta_rank == 0;
+    const int cluster_id = blockIdx.x / kCtaGroup;
+    const int num_clusters = gridDim.x / kCtaGroup;
+
+    if (warp == 0 && ptx::elect_one()) ptx::prefetch_tensormap(&tmap_z);
+    if (warp == 1 && ptx::elect_one()) {
+        for (int s = 0; s < kStages; ++s) {
+            ptx::mbar_init(&full_bar[s], kCtaGroup);  // leader: own arrive(+expect_tx) and, in pair mode, the peer's arrive
+            ptx::mbar_init(&empty_bar[s], 1);         // one tcgen05.commit
+        }
+        for (int s = 0; s < 2; ++s) {
+            ptx::mbar_init(&tmem_full_bar[s], 1);                   // one tcgen05.commit
+            ptx::mbar_init(&tmem_empty_bar[s], 128 * kCtaGroup);    // every epilogue thread of the pair
+        }
+        ptx::fence_mbar_init();
+    }
+    if constexpr (kCtaGroup == 2) ptx::cluster_sync_all();  // peer barriers must exist before anyone signals them
+    if (warp == 2) ptx::tmem_alloc<kCtaGroup>(tmem_ptr_smem, 512);
+    ptx::tc_fence_before();
+    if constexpr (kCtaGroup == 2) ptx::cluster_sync_all(); else __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    if (warp == 0) {
+        // ===================================================== TMA producer
+        uint32_t stage = 0, phase = 0;
+        for (int it = cluster_id; it < num_items; it += num_clusters) {
+            const TcItem item = items[it];
+            const int32_t a_row = item.a_row0 + static_cast<int32_t>(cta_rank) * 128;
+            const int32_t b_row = item.b_row0 + static_cast<int32_t>(cta_rank) * Cfg::kBRows;
+            for (int kb = 0; kb < num_k_blocks; ++kb) {
+                ptx::mbar_wait(&empty_bar[stage], phase ^ 1, fault_flag, 1);
+                if (ptx::elect_one()) {
+                    const int32_t kc = (k_block0 + kb) * kTcBlockK;
+                    uint8_t* sa = smem_a + stage * kTcABytes;
+                    uint8_t* sb = smem_b + stage * Cfg::kBBytes;
+                    if constexpr (kCtaGroup == 1) {
+                        ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+                        ptx::tma_load_2d(&tmap_z, &full_bar[stage], sa, kc, a_row, ptx::kCacheEvictNormal);
+                        ptx::tma_load_2d(&tmap_z, &full_bar[stage], sb, kc, b_row, ptx::kCacheEvictNormal);
+                        ptx::tma_load_2d(&tmap_z, &full_bar[stage], sb + kTcABytes, kc, b_row + 128, ptx::kCacheEvictNormal);
+                    } else {
+                        // both CTAs' bytes are counted on the leader's barrier
+                        if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
+                        else ptx::mbar_arrive_cluster(&full_bar[stage], 0);
+                        ptx::tma_load_2d_pair(&tmap_z, &full_bar[stage], sa, kc, a_row, ptx::kCacheEvictNormal);
+                        ptx::tma_load_2d_pair(&tmap_z, &full_bar[stage], sb, kc, b_row, ptx::kCacheEvictNormal);
+                    }
+                }
+                __syncwarp();
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1 && leader) {
+        // ===================================================== MMA issuer (leader CTA only)
+        const uint32_t idesc = ptx::make_idesc_f16(Cfg::kUmmaM, Cfg::kUmmaN, ab_format);
+        uint32_t stage = 0, phase = 0, local_it = 0;
+        for (int it = cluster_id; it < num_items; it += num_clusters, ++local_it) {
+            const uint32_t as = local_it & 1, aphase = (local_it >> 1) & 1;
+            ptx::mbar_wait(&tmem_empty_bar[as], aphase ^ 1, fault_flag, 2);
+            ptx::tc_fence_after();
+            const uint32_t tmem_d = tmem_base + as * Cfg::kUmmaN;
+            for (int kb = 0; kb < num_k_blocks; ++kb) {
+                ptx::mbar_wait(&full_bar[stage], phase, fault_flag, 3);
+                ptx::tc_fence_after();
+                if (ptx::elect_one()) {
+                    const uint64_t da = ptx::make_smem_desc_sw128(ptx::smem_u32(smem_a + stage * kTcABytes));
+                    const uint64_t db = ptx::make_smem_desc_sw128(ptx::smem_u32(smem_b + stage * Cfg::kBBytes));
+#pragma unroll
+                    for (int k = 0; k < kTcBlockK / 16; ++k) {
+                        // advance 16 elements = 32 bytes inside the 128-byte swizzle row: +2 in the (addr >> 4) field
+                        ptx::umma_f16<kCtaGroup>(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    // frees the smem slot (both CTAs in pair mode) once the MMAs above have read it
+                    if constexpr (kCtaGroup == 1) ptx::umma_commit(&empty_bar[stage]);
+                    else ptx::umma_commit_pair(&empty_bar[stage], 0x3);
+                    if (kb == num_k_blocks - 1) {
+                        if constexpr (kCtaGroup == 1) ptx::umma_commit(&tmem_full_bar[as]);
+                        else ptx::umma_commit_pair(&tmem_full_bar[as], 0x3);
+                    }
+                }
+                __syncwarp();
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp >= 4) {
+        // ===================================================== epilogue: TMEM -> registers -> G (+=)
+        const uint32_t quad = warp & 3;  // TMEM lanes 32*quad .. 32*quad+31 are the ones this warp may read
+        const uint32_t lane = ptx::lane_id();
+        const uint32_t row = quad * 32 + lane;
+        uint32_t local_it = 0;
+        for (int it = cluster_id; it < num_items; it += num_clusters, ++local_it) {
+            const TcItem item = items[it];
+            const uint32_t as = local_it & 1, aphase = (local_it >> 1) & 1;
+            ptx::mbar_wait(&tmem_full_bar[as], aphase, fault_flag, 4);
+            ptx::tc_fence_after();
+            float* out = accum + item.out_off + static_cast<int64_t>(cta_rank) * kHalfTileElems + row * 4;
+#pragma unroll 1
+            for (int chunk = 0; chunk < 8; ++chunk) {
+                uint32_t v[32];
+                ptx::tmem_ld_32x32(tmem_base + ((quad * 32u) << 16) + as * Cfg::kUmmaN + chunk * 32, v);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    float4* dst = reinterpret_cast<float4*>(out + (chunk * 8 + q) * (128 * 4));
+                    float4 r = make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]),
+                                           __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3]));
+                    if (accumulate) {
+                        const float4 o = *dst;
+                        r.x += o.x; r.y += o.y; r.z += o.z; r.w += o.w;
+                    }
+                    *dst = r;
+                }
+            }
+            ptx::tc_fence_before();
+            if constexpr (kCtaGroup == 1) ptx::mbar_arrive(&tmem_empty_bar[as]);
+            else ptx::mbar_arrive_cluster(&tmem_empty_bar[as], 0);
+        }
+    }
+
+    ptx::tc_fence_before();
+    if constexpr (kCtaGroup == 2) ptx::cluster_sync_all(); else __syncthreads();
+    if (warp == 2) ptx::tmem_dealloc<kCtaGroup>(tmem_base, 512);
+}
+
+}  // namespace ggrm

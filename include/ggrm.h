@@ -1,0 +1,174 @@
+/* ggrm.h — C ABI of the B200-native GRM engine (libggrm_b200.so).
+ *
+ * This is the drop-in boundary for the `gelex grm` hot path.  The reference (r1cheu/gelex) has no FFI layer;
+ * the narrowest seam it has is `GrmEngine::compute` (include/gelex/pipeline/grm_engine.h:30-51) whose inner loop
+ * (include/gelex/data/grm/grm.h:94-137) calls, per chunk of SNPs,
+ *     BedPipe::load_chunk        (src/data/genotype/bed_pipe.cpp:107-158)   2-bit decode + sample projection
+ *     process_matrix<GT>         (include/gelex/data/genotype/genotype_processor.h:142-158)   code policy
+ *     GRM::update_grm/cblas_dsyrk (src/data/grm/grm.cpp:42-63)              G_lower += Z Z^T
+ * and then writes float32 row-major lower-triangle rows (src/data/grm/grm_bin_writer.cpp:54-61).
+ * The entry points below replace exactly that: packed BED bytes in, packed lower-triangle float32 rows out.
+ * Plain pointers and sizes only; no C++ or torch types cross this boundary; nothing throws across it.
+ *
+ * Threading: a handle is not thread-safe; distinct handles (one per GPU) may be driven from distinct threads
+ * or processes.  All functions return GGRM_OK (0) or a negative ggrm_status; ggrm_last_error gives the text.
+ */
+#ifndef GGRM_H_
+#define GGRM_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GGRM_ABI_VERSION 1
+
+/* Status codes.  The C++ host shim re-throws each as the GelexException subclass named on the right
+ * (include/gelex/exception.h:26-117) so CLI behaviour (log + exit 1, apps/main.cpp:73-98) is unchanged. */
+typedef enum ggrm_status {
+    GGRM_OK = 0,
+    GGRM_ERR_INVALID_ARGUMENT = -1, /* ArgumentValidationException / InvalidInputException */
+    GGRM_ERR_COLUMN_RANGE = -2,     /* ColumnRangeException (bed_pipe.cpp:38-52)            */
+    GGRM_ERR_INVALID_OPERATION = -3,/* InvalidOperationException (call order)               */
+    GGRM_ERR_OUT_OF_MEMORY = -4,    /* std::bad_alloc                                       */
+    GGRM_ERR_CUDA = -5,             /* GelexException("CUDA: ...")                          */
+    GGRM_ERR_NO_DEVICE = -6,        /* GelexException: no sm_100 device — there is NO CPU fallback */
+    GGRM_ERR_FILE_FORMAT = -7       /* FileFormatException (truncated payload)              */
+} ggrm_status;
+
+/* GenotypeProcessMethod, include/gelex/data/genotype/genotype_processor.h:38-48 (same numeric values). */
+typedef enum ggrm_method {
+    GGRM_STANDARDIZE_HWE = 1,      /* SH  : "Yang" additive / "Zeng" [0,1,0] dominance */
+    GGRM_CENTER_HWE = 2,           /* CH  */
+    GGRM_ORTH_STANDARDIZE_HWE = 3, /* OSH : CLI default (apps/cli/grm/grm_args.cpp:42-48) */
+    GGRM_ORTH_CENTER_HWE = 4,      /* OCH : "Vitezica" with --add --dom */
+    GGRM_STANDARDIZE = 5,          /* S   */
+    GGRM_CENTER = 6,               /* C   */
+    GGRM_ORTH_STANDARDIZE = 7,     /* OS  */
+    GGRM_ORTH_CENTER = 8           /* OC  */
+} ggrm_method;
+
+typedef enum ggrm_precision {
+    GGRM_PREC_BF16 = 0, /* BF16 operands, FP32 accumulate in TMEM (tcgen05); tolerance 1e-4 on G/(trace/n) */
+    GGRM_PREC_FP64 = 1, /* FP64 operands and accumulate (DMMA mma.sync.m8n8k4.f64); tolerance 1e-10       */
+    GGRM_PREC_FP16 = 2  /* FP16 operands (11-bit mantissa), same tcgen05 pipe and throughput as BF16      */
+} ggrm_precision;
+
+enum { GGRM_KIND_ADD = 0, GGRM_KIND_DOM = 1 };
+enum { GGRM_GROUP_WHOLE = -1 };
+
+/* What an all-missing SNP contributes.  The reference leaves the column NaN
+ * (include/gelex/internal/genotype_processor/genotype_processor.h:38-42) and dsyrk then poisons the whole GRM. */
+enum { GGRM_ALLMISS_REFERENCE_NAN = 0, GGRM_ALLMISS_SKIP = 1 };
+
+typedef struct ggrm_handle ggrm_t;
+
+typedef struct ggrm_config {
+    int32_t abi_version;       /* GGRM_ABI_VERSION */
+    int32_t device;            /* CUDA device ordinal this handle owns */
+    int64_t n_raw;             /* samples per SNP row in the BED = FAM lines (metadata.cpp:39-43) */
+    int64_t n_out;             /* GRM rows = sorted, de-duplicated sample IDs (sample_manager.cpp:37-40) */
+    const int32_t* raw_to_out; /* [n_raw] raw sample -> GRM row, -1 = dropped, later raw wins on duplicates
+                                  (sample_projection.cpp:32-55, variant_decoder.cpp:79-126); NULL = identity */
+    int64_t m_total;           /* number of SNPs in the BED (upper bound of any snp index pushed) */
+    int32_t method;            /* ggrm_method */
+    int32_t want_add;          /* accumulate the additive matrix  (GrmType A / AD, grm_work_plan.cpp:38-50) */
+    int32_t want_dom;          /* accumulate the dominance matrix (GrmType D / AD); both = one decode, two SYRKs */
+    int32_t precision;         /* ggrm_precision */
+    int32_t n_groups;          /* >=1.  Groups are chromosome runs (grm_work_plan.cpp:54-81); 1 = no LOCO */
+    const int64_t* group_begin;/* [n_groups] first SNP index of each group; NULL iff n_groups==1 (=> [0,m_total)) */
+    const int64_t* group_end;  /* [n_groups] one past the last SNP index */
+    int32_t keep_whole;        /* n_groups>1: also keep whole = sum of group partials (LOCO by subtraction) */
+    int32_t keep_stats;        /* retain per-SNP counts + allele frequency for ggrm_snp_stats */
+    int32_t all_missing_policy;/* GGRM_ALLMISS_* */
+    int32_t tile_rank;         /* 2D-tile partition: this handle owns every tile whose LPT slot % tile_world == tile_rank */
+    int32_t tile_world;        /* 1 = own all tiles (single GPU or SNP-shard mode) */
+    int64_t chunk_snps;        /* device K-chunk (SNPs expanded to 16-bit operands at once); 0 = auto */
+    int32_t max_resident_groups; /* accumulator pool size per kind; 0 = as many as fit / n_groups */
+    int32_t reserved;
+} ggrm_config_t;
+
+/* Create / destroy.  Fails with GGRM_ERR_NO_DEVICE when no sm_100 GPU is present (no CPU fallback). */
+int ggrm_create(const ggrm_config_t* cfg, ggrm_t** out);
+void ggrm_destroy(ggrm_t* h);
+const char* ggrm_last_error(const ggrm_t* h); /* h may be NULL: error of the last failed ggrm_create on this thread */
+
+/* Feed packed BED payload: `snp_count` SNP rows of `bytes_per_variant` = ceil(n_raw/4) bytes, the bytes
+ * BedMmapReader::chunk_ptr(snp_begin, snp_count) points at (mmap_reader.cpp:96-119).  SNP indices must be pushed in
+ * increasing order; ranges may skip SNPs (SNP-sharded multi-GPU) but never overlap.  The caller keeps ownership:
+ * pageable memory is staged through the library's pinned ring (may block while the ring is full); memory that is
+ * already pinned (cudaHostRegister/cudaHostAlloc) is copied from directly and must stay valid until ggrm_finish. */
+int ggrm_push(ggrm_t* h, const uint8_t* bed_payload, int64_t snp_begin, int64_t snp_count, int64_t bytes_per_variant);
+/* Same, payload already resident in device memory of cfg.device (used by bench.py's HBM-resident leg). */
+int ggrm_push_device(ggrm_t* h, const uint8_t* d_bed_payload, int64_t snp_begin, int64_t snp_count,
+                     int64_t bytes_per_variant);
+/* Drain: every pushed SNP is accumulated, every group is complete.  Blocks until the device is idle. */
+int ggrm_finish(ggrm_t* h);
+
+/* Bit-exact test hook: per-SNP genotype counts after projection (n0 = #g==0, n1, n2 = #A1A1, nmiss) and the A1
+ * allele frequency `maf` of genotype_processor.h:44.  Requires keep_stats.  Any output pointer may be NULL. */
+int ggrm_snp_stats(ggrm_t* h, int64_t snp_begin, int64_t snp_count, int32_t* n0, int32_t* n1, int32_t* n2,
+                   int32_t* nmiss, double* freq);
+
+/* Read rows [row_begin, row_begin+row_count) of matrix (kind, group) as packed row-major lower-triangle float32 —
+ * exactly the .bin byte order of grm_bin_writer.cpp:54-61: row i contributes i+1 values (i,0..i).
+ * out_lower_rows (host, caller-owned) must hold sum_{i}(i+1) floats.  trace_out (may be NULL) receives the FP64
+ * sum of the diagonal entries in the requested rows (GrmResult::denominator = trace/n, grm.h:134).
+ * group = GGRM_GROUP_WHOLE for the whole-genome matrix (n_groups==1, or keep_whole).  A group may be fetched as soon
+ * as a SNP of a later group has been pushed (or after ggrm_finish).  In tile mode (tile_world>1) entries of tiles
+ * this handle does not own are returned as 0 so per-rank results can be summed or written at their own offsets. */
+int ggrm_fetch(ggrm_t* h, int kind, int group, int64_t row_begin, int64_t row_count, float* out_lower_rows,
+               double* trace_out);
+/* Same rows in FP64 (only meaningful for GGRM_PREC_FP64; FP32 accumulators are widened). */
+int ggrm_fetch_f64(ggrm_t* h, int kind, int group, int64_t row_begin, int64_t row_count, double* out_lower_rows,
+                   double* trace_out);
+/* Return the accumulator of a fetched group to the pool (needed only when n_groups > max_resident_groups). */
+int ggrm_release_group(ggrm_t* h, int kind, int group);
+
+/* Multi-GPU SNP-shard mode: device pointer + element count of the tile-packed accumulator of (kind, group) so the
+ * host plumbing (NCCL / torch.distributed, or ggrm_reduce_peer) can sum partial GRMs across ranks in place.
+ * Element type is float (BF16/FP16 precision) or double (FP64). */
+int ggrm_accum_buffer(ggrm_t* h, int kind, int group, void** d_ptr, int64_t* n_elems, int32_t* elem_bytes);
+/* Sum-reduce over NVLink peer memory without NCCL: `peers` are the accum buffers of the other ranks (device pointers
+ * mapped into this process, e.g. cudaIpcOpenMemHandle); this rank reduces the slice [slice_begin, slice_end) of
+ * elements into its own buffer with one kernel that reads all peers (reduce-scatter by slices).  */
+int ggrm_reduce_peer(ggrm_t* h, int kind, int group, const void* const* peers, int n_peers, int64_t slice_begin,
+                     int64_t slice_end);
+
+/* Next-row helpers on data already resident: normalised and leave-one-chromosome-out matrices,
+ * G/(trace/n) (grm_loader.cpp:125-165) and (G_whole - G_chr)/(k_whole - k_chr) (loco_grm_loader.cpp:62-76),
+ * returned as packed lower rows in FP64. */
+int ggrm_fetch_normalized(ggrm_t* h, int kind, int group, int64_t row_begin, int64_t row_count, double* out_lower_rows);
+int ggrm_fetch_loco(ggrm_t* h, int kind, int group, int64_t row_begin, int64_t row_count, double* out_lower_rows);
+
+/* Phase timers (CUDA events on the handle's streams), milliseconds accumulated since create:
+ * [0] H2D copies  [1] repack+count+stats  [2] expand  [3] SYRK  [4] pack+D2H  [5] SYRK launches  [6] all kernels launched */
+int ggrm_get_timers(ggrm_t* h, double* out7);
+
+/* ---- Stateless test hooks (CUDA kernels; bit-exact layers of SURVEY §8c) ------------------------------------ */
+/* Decode `snp_count` packed SNP rows into a column-major n_out x snp_count FP64 matrix on the host, with the same
+ * values BedPipe::load_chunk produces: 2.0 / 1.0 / 0.0 / NaN (decode_lut.h:40-41), rows never written stay NaN. */
+int ggrm_decode_chunk(int device, const uint8_t* bed_payload, int64_t snp_count, int64_t bytes_per_variant,
+                      int64_t n_raw, int64_t n_out, const int32_t* raw_to_out, double* out_colmajor);
+/* Decode + code policy (process_matrix<GT>) in FP64: out is column-major n_out x snp_count, freq[snp_count]. */
+int ggrm_standardise_chunk(int device, const uint8_t* bed_payload, int64_t snp_count, int64_t bytes_per_variant,
+                           int64_t n_raw, int64_t n_out, const int32_t* raw_to_out, int method, int kind,
+                           int all_missing_policy, double* out_colmajor, double* freq);
+
+/* ---- Synthetic PLINK BED payload: p_j~U(0.05,0.5), HWE genotypes, i.i.d. missing -------------------
+ * Counter-based integer RNG, bit-identical on host and device.  Writes snp_count rows of ceil(n/4) bytes for SNPs
+ * [snp_begin, snp_begin+snp_count); padding bits of the last byte are 0. */
+int ggrm_synth_bed_host(uint8_t* out, int64_t n, int64_t snp_begin, int64_t snp_count, uint64_t seed,
+                        double missing_rate);
+int ggrm_synth_bed_device(int device, uint8_t* d_out, int64_t n, int64_t snp_begin, int64_t snp_count, uint64_t seed,
+                          double missing_rate);
+
+/* Library / device facts for the harness. */
+int ggrm_device_count(void);
+const char* ggrm_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GGRM_H_ */
