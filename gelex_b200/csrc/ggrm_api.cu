@@ -158,6 +158,8 @@ static void free_handle(Handle* h) {
     }
     for (int i = 0; i < 2; ++i) if (h->raw_free[i] != nullptr) cudaEventDestroy(h->raw_free[i]);
     if (h->h2d_done != nullptr) cudaEventDestroy(h->h2d_done);
+    if (h->pass_begin != nullptr) cudaEventDestroy(h->pass_begin);
+    if (h->pass_end != nullptr) cudaEventDestroy(h->pass_end);
     for (auto& g : h->groups) if (g.done != nullptr) cudaEventDestroy(g.done);
     for (auto& t : h->timers) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
     if (h->s_copy != nullptr) cudaStreamDestroy(h->s_copy);

@@ -89,7 +89,7 @@ static void fetch_typed(Handle& h, int kind, int group, int64_t row_begin, int64
         GGRM_CUDA(cudaMalloc(&h.d_stage, static_cast<size_t>(h.stage_bytes)));
     }
     const int64_t stage_elems = h.stage_bytes / static_cast<int64_t>(sizeof(TOut));
-    phase_begin(h, h.s_fetch, 4);
+    const size_t tfetch = phase_begin(h, h.s_fetch, 4);
     GGRM_CUDA(cudaMemsetAsync(h.d_trace, 0, sizeof(double), h.s_fetch));
     int64_t r = row_begin;
     const int64_t r_end = row_begin + row_count;
@@ -115,7 +115,7 @@ static void fetch_typed(Handle& h, int kind, int group, int64_t row_begin, int64
     }
     double tr = 0.0;
     GGRM_CUDA(cudaMemcpyAsync(&tr, h.d_trace, sizeof(double), cudaMemcpyDeviceToHost, h.s_fetch));
-    phase_end(h, h.s_fetch);
+    phase_end(h, h.s_fetch, tfetch);
     GGRM_CUDA(cudaStreamSynchronize(h.s_fetch));
     if (trace_out != nullptr) *trace_out = tr;
     if (h.finished) collect_timers(h);

@@ -2,15 +2,16 @@
 
 namespace ggrm {
 
-static void phase_begin(Handle& h, cudaStream_t s, int phase) {
+static size_t phase_begin(Handle& h, cudaStream_t s, int phase) {
     Timer t;
     GGRM_CUDA(cudaEventCreate(&t.a));
     GGRM_CUDA(cudaEventCreate(&t.b));
     t.phase = phase;
     GGRM_CUDA(cudaEventRecord(t.a, s));
     h.timers.push_back(t);
+    return h.timers.size() - 1;
 }
-static void phase_end(Handle& h, cudaStream_t s) { GGRM_CUDA(cudaEventRecord(h.timers.back().b, s)); }
+static void phase_end(Handle& h, cudaStream_t s, size_t idx) { GGRM_CUDA(cudaEventRecord(h.timers[idx].b, s)); }
 
 static void collect_timers(Handle& h) {
     for (auto& t : h.timers) {
@@ -19,6 +20,7 @@ static void collect_timers(Handle& h) {
         cudaEventDestroy(t.a);
         cudaEventDestroy(t.b);
     }
+    cudaGetLastError();  // an unrecorded timer event must not poison later error checks
     h.timers.clear();
 }
 
@@ -122,7 +124,7 @@ static void flush_chunk(Handle& h) {
     GGRM_CUDA(cudaStreamWaitEvent(h.s_comp, h.h2d_done, 0));
     start_group(h, g);
 
-    phase_begin(h, h.s_comp, 1);
+    size_t ti = phase_begin(h, h.s_comp, 1);
     repack_kernel<<<static_cast<unsigned>(c), 256, 0, h.s_comp>>>(h.d_raw[b], h.bpv_raw, h.d_dense, h.bpv_pad, h.n_out, h.d_out_to_raw, c);
     GGRM_CUDA(cudaGetLastError());
     GGRM_CUDA(cudaEventRecord(h.raw_free[b], h.s_comp));
@@ -137,23 +139,23 @@ static void flush_chunk(Handle& h) {
         h.d_dense, h.bpv_pad, h.n_out, h.n_pad, c, h.cfg.method, h.cfg.all_missing_policy,
         h.cfg.precision == GGRM_PREC_FP16 ? 1 : 0, so, h.cur_first_snp);
     GGRM_CUDA(cudaGetLastError());
-    phase_end(h, h.s_comp);
+    phase_end(h, h.s_comp, ti);
     h.kernel_launches += 2;
 
     const dim3 egrid(static_cast<unsigned>((c + 63) / 64), static_cast<unsigned>(h.bpv_pad / 64));
     for (int kind = 0; kind < 2; ++kind) {
         if (h.d_Z[kind] == nullptr) continue;
-        phase_begin(h, h.s_comp, 2);
+        ti = phase_begin(h, h.s_comp, 2);
         if (h.fp64)
             expand64_kernel<<<egrid, 256, 0, h.s_comp>>>(h.d_dense, h.bpv_pad, h.d_tab64[kind], c, static_cast<double*>(h.d_Z[kind]), h.k_cap);
         else
             expand16_kernel<<<egrid, 256, 0, h.s_comp>>>(h.d_dense, h.bpv_pad, h.d_tab16[kind], c, static_cast<uint16_t*>(h.d_Z[kind]), h.k_cap);
         GGRM_CUDA(cudaGetLastError());
-        phase_end(h, h.s_comp);
+        phase_end(h, h.s_comp, ti);
         ++h.kernel_launches;
-        phase_begin(h, h.s_comp, 3);
+        ti = phase_begin(h, h.s_comp, 3);
         launch_syrk(h, kind, g, c);
-        phase_end(h, h.s_comp);
+        phase_end(h, h.s_comp, ti);
     }
     h.cur_buf ^= 1;
     h.cur_count = 0;
@@ -207,7 +209,15 @@ static void push_impl(Handle& h, const uint8_t* payload, bool is_device, int64_t
         if (cudaPointerGetAttributes(&attr, payload) == cudaSuccess) pinned = attr.type == cudaMemoryTypeHost;
         else cudaGetLastError();
     }
-    phase_begin(h, h.s_copy, 0);
+    if (!h.pass_open) {
+        if (h.pass_begin == nullptr) {
+            GGRM_CUDA(cudaEventCreate(&h.pass_begin));
+            GGRM_CUDA(cudaEventCreate(&h.pass_end));
+        }
+        GGRM_CUDA(cudaEventRecord(h.pass_begin, h.s_copy));
+        h.pass_open = true;
+    }
+    const size_t tcopy = phase_begin(h, h.s_copy, 0);
     const int64_t end = snp_begin + snp_count;
     int64_t s = snp_begin;
     while (s < end) {
@@ -233,7 +243,7 @@ static void push_impl(Handle& h, const uint8_t* payload, bool is_device, int64_t
             s += take;
         }
     }
-    phase_end(h, h.s_copy);
+    phase_end(h, h.s_copy, tcopy);
     h.last_snp_pushed = end - 1;
 }
 
@@ -243,6 +253,7 @@ static void finish_impl(Handle& h) {
         for (size_t g = 0; g < h.groups.size(); ++g)
             if (h.groups[g].started) complete_group(h, static_cast<int>(g));
         h.finished = true;
+        if (h.pass_open) GGRM_CUDA(cudaEventRecord(h.pass_end, h.s_comp));
     }
     const cudaError_t e1 = cudaStreamSynchronize(h.s_copy);
     const cudaError_t e2 = cudaStreamSynchronize(h.s_comp);
@@ -253,6 +264,35 @@ static void finish_impl(Handle& h) {
                                            cudaGetErrorString(e2 != cudaSuccess ? e2 : e1) + " (pipeline wait id " + std::to_string(where) + ")"};
     }
     collect_timers(h);
+    if (h.pass_open) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, h.pass_begin, h.pass_end) == cudaSuccess) h.pass_ms += ms;
+        cudaGetLastError();
+        h.pass_open = false;
+    }
+}
+
+// Re-arm a finished handle for another pass over (the same or other) SNPs: accumulators are zeroed lazily when their
+// group restarts, statistics are overwritten, buffers and work lists are reused.  Timers keep accumulating.
+static void reset_impl(Handle& h) {
+    GGRM_CUDA(cudaStreamSynchronize(h.s_copy));
+    GGRM_CUDA(cudaStreamSynchronize(h.s_comp));
+    GGRM_CUDA(cudaStreamSynchronize(h.s_fetch));
+    for (auto& g : h.groups) {
+        g.buffer[0] = g.buffer[1] = -1;
+        g.started = g.complete = g.folded = false;
+    }
+    for (int kind = 0; kind < 2; ++kind) {
+        std::fill(h.pool_owner[kind].begin(), h.pool_owner[kind].end(), -1);
+        if (h.whole[kind] != nullptr)
+            GGRM_CUDA(cudaMemsetAsync(h.whole[kind], 0, static_cast<size_t>(std::max<int64_t>(h.accum_elems, 4)) * h.elem_bytes, h.s_comp));
+    }
+    h.cur_count = 0;
+    h.cur_first_snp = -1;
+    h.cur_group = -1;
+    h.last_snp_pushed = -1;
+    h.finished = false;
+    h.pass_open = false;
 }
 
 }  // namespace ggrm
@@ -268,6 +308,13 @@ extern "C" int ggrm_push_device(ggrm_t* hh, const uint8_t* d_bed_payload, int64_
     Handle* h = reinterpret_cast<Handle*>(hh);
     GGRM_API_BEGIN(h)
     push_impl(*h, d_bed_payload, true, snp_begin, snp_count, bytes_per_variant);
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_reset(ggrm_t* hh) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    reset_impl(*h);
     GGRM_API_END(h)
 }
 
@@ -298,12 +345,13 @@ extern "C" int ggrm_snp_stats(ggrm_t* hh, int64_t snp_begin, int64_t snp_count, 
     GGRM_API_END(h)
 }
 
-extern "C" int ggrm_get_timers(ggrm_t* hh, double* out7) {
+extern "C" int ggrm_get_timers(ggrm_t* hh, double* out8) {
     Handle* h = reinterpret_cast<Handle*>(hh);
     GGRM_API_BEGIN(h)
-    if (out7 == nullptr) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "null output"};
-    for (int i = 0; i < 5; ++i) out7[i] = h->phase_ms[i];
-    out7[5] = static_cast<double>(h->syrk_launches);
-    out7[6] = static_cast<double>(h->kernel_launches);
+    if (out8 == nullptr) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "null output"};
+    for (int i = 0; i < 5; ++i) out8[i] = h->phase_ms[i];
+    out8[5] = static_cast<double>(h->syrk_launches);
+    out8[6] = static_cast<double>(h->kernel_launches);
+    out8[7] = h->pass_ms;
     GGRM_API_END(h)
 }

@@ -102,6 +102,9 @@ struct Handle {
     // timers
     std::vector<Timer> timers;
     double phase_ms[7] = {0, 0, 0, 0, 0, 0, 0};
+    cudaEvent_t pass_begin = nullptr, pass_end = nullptr;  // first push enqueued -> last accumulation done
+    bool pass_open = false;
+    double pass_ms = 0;
     int64_t syrk_launches = 0, kernel_launches = 0;
 };
 

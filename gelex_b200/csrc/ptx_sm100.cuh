@@ -70,7 +70,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
     asm volatile(
         "{\n\t"
         ".reg .pred P;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2, 0x989680;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2, 20000;\n\t"
         "selp.u32 %0, 1, 0, P;\n\t"
         "}"
         : "=r"(ok)
@@ -78,12 +78,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
-// Bounded wait: a pipeline bug must never hang the GPU box.  After ~2^22 failed probes (each probe sleeps up to the
-// hardware time limit, so this is seconds, far beyond any legitimate wait) the kernel records where it was stuck and traps.
+// Bounded wait: a pipeline bug must never hang the GPU box.  If a wait lasts longer than 4 s of wall clock (any legitimate
+// wait is bounded by one SYRK launch, well under a second) the kernel records where it was stuck and traps.
+__device__ __forceinline__ uint64_t global_timer_ns() {
+    uint64_t t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int* fault_flag, int where) {
+    if (mbar_try_wait(bar, parity)) return;
+    const uint64_t t0 = global_timer_ns();
     uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if (++spins > (1u << 22)) {
+        if ((++spins & 0xFFu) == 0 && global_timer_ns() - t0 > 4000000000ull) {
             if (fault_flag != nullptr) {
                 atomicExch(fault_flag, where);
                 __threadfence_system();

@@ -105,6 +105,9 @@ int ggrm_push_device(ggrm_t* h, const uint8_t* d_bed_payload, int64_t snp_begin,
                      int64_t bytes_per_variant);
 /* Drain: every pushed SNP is accumulated, every group is complete.  Blocks until the device is idle. */
 int ggrm_finish(ggrm_t* h);
+/* Re-arm the handle for another pass (e.g. the dominance pass of a second invocation, or a benchmark step): all
+ * accumulators read as zero again, buffers / work lists / streams are reused. */
+int ggrm_reset(ggrm_t* h);
 
 /* Bit-exact test hook: per-SNP genotype counts after projection (n0 = #g==0, n1, n2 = #A1A1, nmiss) and the A1
  * allele frequency `maf` of genotype_processor.h:44.  Requires keep_stats.  Any output pointer may be NULL. */
@@ -143,8 +146,9 @@ int ggrm_fetch_normalized(ggrm_t* h, int kind, int group, int64_t row_begin, int
 int ggrm_fetch_loco(ggrm_t* h, int kind, int group, int64_t row_begin, int64_t row_count, double* out_lower_rows);
 
 /* Phase timers (CUDA events on the handle's streams), milliseconds accumulated since create:
- * [0] H2D copies  [1] repack+count+stats  [2] expand  [3] SYRK  [4] pack+D2H  [5] SYRK launches  [6] all kernels launched */
-int ggrm_get_timers(ggrm_t* h, double* out7);
+ * [0] H2D copies  [1] repack+count+stats  [2] expand  [3] SYRK  [4] pack+D2H  [5] SYRK launches  [6] all kernels launched
+ * [7] passes: first push enqueued -> last accumulation finished (events on the copy / compute streams) */
+int ggrm_get_timers(ggrm_t* h, double* out8);
 
 /* ---- Stateless test hooks (CUDA kernels; bit-exact layers of SURVEY §8c) ------------------------------------ */
 /* Decode `snp_count` packed SNP rows into a column-major n_out x snp_count FP64 matrix on the host, with the same
