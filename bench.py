@@ -1,0 +1,344 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the `gelex grm` hot path (BASELINE.json): Yang additive GRM (StandardizeHWE + Add),
+50 000 samples x 500 000 SNPs, synthetic PLINK BED payload (p~U(0.05,0.5), HWE, 1 % missing).
+
+  python bench.py --gpus N --steps K --warmup W            # this repo: B200 engine through the C ABI
+  python bench.py --impl reference --gpus N --steps K ...  # the reference's own CPU path (oracle/_ref) on the host cores
+
+A "step" = one full GRM build (one pass of decode -> counts/frequencies -> standardise -> SYRK over every SNP).
+  value : effective TFLOP/s = n(n+1)m / t with the packed BED already resident in HBM (6.25 GB > L2, so no L2 flush needed)
+  e2e   : same metric through ggrm_push (pinned HOST payload -> H2D inside the timed region) .. ggrm_finish .. ggrm_fetch
+          (full float32 lower triangle, the .bin payload, D2H into host memory)
+N > 1   : SNP-sharded ("strong" scaling: total work fixed), one process per GPU, partial GRMs summed over NVLink
+          (NCCL reduce via torch.distributed) inside the timed region.
+One JSON line on stdout (rank 0)."""
+import argparse
+import ctypes
+import json
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+
+N_SAMPLES = int(os.environ.get("GGRM_BENCH_N", 50000))
+M_SNPS = int(os.environ.get("GGRM_BENCH_M", 500000))
+SEED = 20261104 + 2
+MISSING = 0.01
+METHOD = 1  # StandardizeHWE ("Yang" additive)
+METRIC = "GRM build effective TFLOP/s (n(n+1)m FLOPs / wall-s), Yang additive GRM, 50k samples x 500k SNPs"
+REF_BIN = ROOT / "oracle" / "_ref" / "gelex_ref"
+
+
+def flops(n, m):
+    return float(n) * (n + 1.0) * m
+
+
+# ---------------------------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.rows = []
+        self.proc = None
+        self.gpu = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+
+    def stop(self, t0=None, t1=None):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        rows = [r for t, r in self.rows if (t0 is None or t >= t0) and (t1 is None or t <= t1)] or [r for _, r in self.rows]
+        sm, mx, pw, reasons = [], [], [], set()
+        for r in rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------------------------- CPU reference arm
+def cpu_threads():
+    return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+
+
+def write_sample_plink(prefix, n, m):
+    """Synthetic PLINK triple for the CPU legs (same generator, same seed as the GPU run; FAM in sorted order = dense path)."""
+    import gelex_b200 as g
+    import plink_io
+
+    payload = g.synth_bed_host(n, 0, m, SEED, MISSING)
+    bounds = [round(m * i / 22) for i in range(23)]
+    chroms = [str(c + 1) for c in range(22) for _ in range(bounds[c + 1] - bounds[c])]
+    plink_io.write_plink(prefix, payload, [("F", f"s{i:07d}") for i in range(n)], chroms)
+    return payload
+
+
+def run_ref_once(prefix, out, threads, chunk=10000):
+    r = subprocess.run([str(REF_BIN), "grm", str(prefix), str(out), str(METHOD), "A", "0", str(chunk), str(threads)],
+                       capture_output=True, text=True, check=True)
+    return json.loads(r.stdout.strip().splitlines()[-1])
+
+
+def run_port_once(payload, n, threads):
+    import oracle_lib as o
+
+    os.environ["OMP_NUM_THREADS"] = str(threads)
+    t0 = time.time()
+    o.grm_compute(payload, n, METHOD, 0, chunk=2000)
+    return {"wall_s": time.time() - t0, "blas": "none (plain C oracle port)"}
+
+
+def cpu_sample_shape(budget_s, threads):
+    """Pick a bounded sample (n_s, m_s) of the workload that costs about budget_s seconds on this host."""
+    n_s = int(os.environ.get("GGRM_BENCH_CPU_N", 8000))
+    tmp = Path(tempfile.mkdtemp(prefix="ggrm_probe_"))
+    try:
+        have_ref = REF_BIN.exists()
+        pn, pm = (2000, 4000) if have_ref else (600, 1500)
+        payload = write_sample_plink(tmp / "probe", pn, pm)
+        t = run_ref_once(tmp / "probe", tmp / "o", threads)["wall_s"] if have_ref else run_port_once(payload, pn, threads)["wall_s"]
+        rate = flops(pn, pm) / max(t, 1e-3)
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    if not have_ref:
+        n_s = 1500
+    m_s = int(min(50000, max(2000, budget_s * rate * 1.5 / (n_s * (n_s + 1.0)))))  # larger problems run closer to BLAS peak
+    return n_s, m_s
+
+
+def cpu_leg(steps, warmup, budget_s):
+    """Times the reference's own CPU implementation (oracle/_ref, else the oracle port) on a bounded sample."""
+    threads = cpu_threads()
+    n_s, m_s = cpu_sample_shape(budget_s, threads)
+    tmp = Path(tempfile.mkdtemp(prefix="ggrm_cpu_"))
+    try:
+        payload = write_sample_plink(tmp / "sample", n_s, m_s)
+        kind = "reference" if REF_BIN.exists() else "port"
+        walls, info = [], {}
+        for i in range(warmup + steps):
+            info = run_ref_once(tmp / "sample", tmp / "out", threads) if kind == "reference" else run_port_once(payload, n_s, threads)
+            if i >= warmup:
+                walls.append(info["wall_s"])
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    wall = sum(walls) / len(walls)
+    return {"value": flops(n_s, m_s) / wall / 1e12, "unit": "TFLOP/s", "cores": threads, "kind": kind,
+            "sample": f"{n_s} samples x {m_s} SNPs of the same synthetic workload, GrmEngine::compute incl. .bin/.id write, chunk 10000, "
+                      f"{threads} threads, {info.get('blas', '')}".strip(),
+            "wall_s": wall}, n_s, m_s
+
+
+# ---------------------------------------------------------------------------------------------------------------- GPU arm
+class DevPtr:
+    """Expose a raw device pointer to torch (zero-copy) through __cuda_array_interface__."""
+
+    def __init__(self, ptr, n_elems, typestr):
+        self.__cuda_array_interface__ = {"shape": (int(n_elems),), "typestr": typestr, "data": (int(ptr), False), "version": 3}
+
+
+def peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return float(d.get("bf16_tflops_sustained", d.get("bf16_tflops", 1400.0))), float(d.get("bf16_tflops", 1590.0)), "measured"
+    return 1400.0, 1590.0, "fallback"
+
+
+def gpu_arm(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import gelex_b200 as g
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run --nproc-per-node {args.gpus}")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    n, m = N_SAMPLES, M_SNPS
+    bpv = (n + 3) // 4
+    prec = {"fp16": g.PREC_FP16, "bf16": g.PREC_BF16, "fp64": g.PREC_FP64}[args.precision]
+    # SNP shard of this rank (contiguous, cut on 64-SNP boundaries)
+    cuts = [min(m, ((m * r // world) + 63) // 64 * 64) for r in range(world)] + [m]
+    s0, s1 = cuts[rank], cuts[rank + 1]
+    ms = s1 - s0
+    d_bed = torch.empty(ms * bpv, dtype=torch.uint8, device="cuda")
+    for s in range(0, ms, 32768):
+        c = min(32768, ms - s)
+        g.synth_bed_device(d_bed.data_ptr() + s * bpv, n, s0 + s, c, SEED, MISSING, device=local)
+    h_bed = torch.empty(ms * bpv, dtype=torch.uint8, pin_memory=True)
+    h_bed.copy_(d_bed)
+    torch.cuda.synchronize()
+    acc = g.Accumulator(n, m, method=METHOD, precision=prec, device=local)
+    out_elems = g.tri(n)
+    h_out = torch.empty(out_elems, dtype=torch.float32, pin_memory=True) if rank == 0 else None
+    dptr, n_el, eb = None, 0, 4
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce_partials():
+        nonlocal dptr, n_el, eb
+        if world == 1:
+            return
+        dptr, n_el, eb = acc.accum_buffer(g.KIND_ADD, g.GROUP_WHOLE)
+        t = torch.as_tensor(DevPtr(dptr, n_el, "<f4" if eb == 4 else "<f8"), device="cuda")
+        dist.reduce(t, dst=0, op=dist.ReduceOp.SUM)
+        torch.cuda.synchronize()
+
+    def step_resident():
+        acc.reset()
+        acc.push_device(d_bed.data_ptr(), s0, ms)
+        acc.finish()
+        reduce_partials()
+
+    def step_e2e():
+        acc.reset()
+        acc.push_ptr(h_bed.data_ptr(), s0, ms)
+        acc.finish()
+        reduce_partials()
+        if rank == 0:
+            acc.lib.ggrm_fetch(acc.h, g.KIND_ADD, g.GROUP_WHOLE, 0, n, ctypes.c_void_p(h_out.data_ptr()), None)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        before = acc.timers()
+        w0 = time.time()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for _ in range(steps):
+            fn()
+        ev1.record()
+        barrier()
+        w1 = time.time()
+        after = acc.timers()
+        dt = w1 - w0
+        if world > 1:
+            t = torch.tensor([dt], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        return dt, {k: after[k] - before[k] for k in after}, (w0, w1)
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    dt, tm, win = timed(step_resident, args.steps, args.warmup)
+    clocks = sampler.stop(*win) if rank == 0 else None
+    dt_e, tm_e, _ = timed(step_e2e, args.steps, max(1, args.warmup // 2))
+    fl = flops(n, m)
+    line = None
+    if rank == 0:
+        sustained, burst, how = peaks()
+        syrk_ms = tm["syrk_ms"] / args.steps                      # this rank's SYRK kernel time per step (CUDA events)
+        launches = max(1.0, tm["syrk_launches"] / args.steps)
+        fl_rank = flops(n, ms)
+        achieved = fl_rank / (syrk_ms * 1e-3) / 1e12 if syrk_ms > 0 else 0.0
+        traffic = None
+        tp = ROOT / "profiles" / "roofline_traffic.json"
+        if tp.exists():
+            traffic = json.loads(tp.read_text()).get("syrk_dram_bytes_per_launch")
+        line = {
+            "metric": METRIC, "value": fl / (dt / args.steps) / 1e12, "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "wall_s_per_grm": dt / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": {"fp16": "f16 operands, f32 accumulate (tcgen05 kind::f16)", "bf16": "bf16 operands, f32 accumulate (tcgen05 kind::f16)",
+                      "fp64": "f64 (DMMA)"}[args.precision],
+            "data": "synthetic",
+            "config": {"workload": f"configs[1]: Yang additive GRM (StandardizeHWE+Add), {n} samples x {m} SNPs, packed 2-bit PLINK BED "
+                                   f"({m * bpv / 1e9:.2f} GB), 1 % missing, seed {SEED}",
+                       "partition": "single GPU" if world == 1 else f"SNP-sharded over {world} GPUs + NCCL sum-reduce of FP32 partial GRMs",
+                       "l2": "inputs (packed BED 6.25 GB, 16-bit operand slabs 0.8 GB, accumulator 5 GB) are larger than the 126 MB L2; no flush needed",
+                       "timing": "barrier + cuda synchronize on both sides, max over ranks; kernel phases by CUDA events on the library's streams",
+                       "chunk_snps": int(os.environ.get("GGRM_CHUNK_SNPS", 8192))},
+            "device_pass_ms_per_step": tm["pass_ms"] / args.steps,
+            "phases_ms_per_step": {k: tm[k] / args.steps for k in ("h2d_ms", "prep_ms", "expand_ms", "syrk_ms")},
+            "gpu_launches": int(tm["kernel_launches"]),
+            "clocks": clocks,
+            "e2e": {"value": fl / (dt_e / args.steps) / 1e12, "unit": "TFLOP/s", "wall_s_per_grm": dt_e / args.steps,
+                    "h2d_bytes_per_step": int(ms * bpv), "d2h_bytes_per_step": int(out_elems * 4),
+                    "path": "ggrm_reset -> ggrm_push(pinned host BED) -> ggrm_finish -> ggrm_fetch(float32 lower triangle to host)",
+                    "phases_ms_per_step": {k: tm_e[k] / args.steps for k in ("h2d_ms", "prep_ms", "expand_ms", "syrk_ms", "fetch_ms")}},
+            "roofline": {"bound": "tensor", "achieved": achieved, "peak": sustained, "unit": "TFLOP/s", "frac": achieved / sustained,
+                         "traffic": traffic, "kernel": "syrk_tc_kernel<2> (tcgen05 cta_group::2, UMMA 256x256x16)",
+                         "flops_per_launch": fl_rank / launches, "avg_launch_ms": syrk_ms / launches, "launches_per_step": launches,
+                         "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({how}); burst peak {burst} -> frac {achieved / burst:.3f}"},
+        }
+    acc.close()
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cb, _, _ = cpu_leg(1, 0, args.cpu_budget)
+        line["cpu_baseline"] = cb
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    cb, n_s, m_s = cpu_leg(args.steps, args.warmup, args.cpu_budget)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "TFLOP/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": cb["wall_s"] * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"configs[1]: Yang additive GRM (StandardizeHWE+Add), {N_SAMPLES} samples x {M_SNPS} SNPs; each step = bounded sample "
+                                   f"{n_s} x {m_s} of it (the CPU path needs hours and 40 GB for the full shape)"},
+            "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default=os.environ.get("GGRM_BENCH_PRECISION", "fp16"), choices=["fp16", "bf16", "fp64"])
+    ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work per reference step")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -196,7 +196,8 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
     h->ntiles_side = h->n_pad / kTile;
     h->fp64 = cfg->precision == GGRM_PREC_FP64;
     h->elem_bytes = h->fp64 ? 8 : 4;
-    if (const char* e = std::getenv("GGRM_TC_MODE")) h->tc_mode = std::atoi(e) == 2 ? 2 : 1;
+    h->tc_mode = 2;  // CTA-pair UMMA 256x256x16 (measured ~20 % faster than the single-CTA 128x256 form)
+    if (const char* e = std::getenv("GGRM_TC_MODE")) h->tc_mode = std::atoi(e) == 1 ? 1 : 2;
 
     // groups
     h->groups.resize(static_cast<size_t>(cfg->n_groups));
@@ -254,8 +255,13 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
     if (cfg->chunk_snps > 0) {
         k_cap = round_up(cfg->chunk_snps, 64);
     } else {
+        // Measured on B200 (profiles/r01_chunk_sweep.md): K slabs of ~8k SNPs keep concurrently running CTAs close
+        // together in K, so Z panels are re-read from L2 instead of HBM; the per-slab accumulator read-modify-write
+        // is hidden behind the next tile's MMAs.  Longer slabs lose L2 reuse, shorter ones expose the epilogue.
+        int64_t target = 8192;
+        if (const char* e = std::getenv("GGRM_CHUNK_SNPS")) target = std::max<int64_t>(64, std::atoll(e));
         const int64_t budget = std::min<int64_t>(int64_t{24} << 30, avail / 2);
-        k_cap = std::max<int64_t>(1024, std::min<int64_t>(65536, budget / per_snp / 1024 * 1024));
+        k_cap = std::max<int64_t>(1024, std::min<int64_t>(target, budget / per_snp / 1024 * 1024));
     }
     k_cap = std::min<int64_t>(k_cap, round_up(cfg->m_total, 64));
     if (k_cap * per_snp > avail)

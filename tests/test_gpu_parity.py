@@ -1,0 +1,339 @@
+"""GPU parity tests (run with `-m gpu` on a B200).  Everything goes through the C ABI (include/ggrm.h) and is checked
+against the CPU oracle (oracle/grm_oracle.c, itself pinned to the reference) and the committed golden fixtures.
+
+Tolerances (north star): decode, counts, allele frequencies bit-exact; GRM entries on G/(trace/n):
+  FP64 path <= 1e-10;  16-bit/FP32 path <= 1e-4 at the named shapes (m >= 50 000).  The rounding error of 16-bit
+  operands averages out as 1/sqrt(m), so for the small m used here the bound is scaled: tol16(m) = 1e-4*sqrt(5e4/m).
+"""
+import numpy as np
+import pytest
+
+import gelex_b200 as g
+import oracle_lib as o
+import plink_io
+from test_oracle_golden import load_dense, load_tiny, same, close
+
+pytestmark = pytest.mark.gpu
+TOL64 = 1e-10
+
+
+def tol16(m):
+    return 1e-4 * max(1.0, (5e4 / m) ** 0.5)
+
+
+def norm_packed(packed):
+    packed = np.asarray(packed, dtype=np.float64)
+    n = int((np.sqrt(8 * packed.size + 1) - 1) / 2)
+    diag = np.cumsum(np.arange(1, n + 1)) - 1
+    return packed / (packed[diag].sum() / n)
+
+
+def norm_ref(G):
+    n = G.shape[0]
+    return G[np.tril_indices(n)] / (np.trace(G) / n)
+
+
+def run_gpu(payload, n_raw, m, method, kinds, precision, chunk=0, push=997, **kw):
+    acc = g.Accumulator(n_raw, m, method=method, want_add=0 in kinds, want_dom=1 in kinds, precision=precision,
+                        chunk_snps=chunk, keep_stats=True, **kw)
+    for s in range(0, m, push):
+        acc.push(payload[s:min(m, s + push)], s)
+    acc.finish()
+    return acc
+
+
+# ------------------------------------------------------------------------------------------------ bit-exact layers
+def test_decode_bit_exact_dense_and_sparse():
+    rng = np.random.default_rng(0)
+    for n in (1000, 1001, 1003, 257):  # n % 4 != 0 exercises the tail byte
+        bed = g.synth_bed_host(n, 0, 200, 11, 0.03)
+        assert same(g.decode_chunk(bed, n), o.decode_chunk(bed, n))
+        perm = rng.permutation(n)
+        fam = [(f"fam{(i % 5) + 1}", f"s{perm[i]}") for i in range(n)]
+        fam[7] = fam[3]  # duplicated ID: later raw sample wins
+        ids, r2o = plink_io.sample_order(fam)
+        assert same(g.decode_chunk(bed, n, len(ids), r2o), o.decode_chunk(bed, n, len(ids), r2o))
+
+
+def test_decode_with_dropped_samples():
+    n = 500
+    bed = g.synth_bed_host(n, 0, 64, 5, 0.05)
+    keep = np.arange(n) % 3 != 0
+    r2o = np.full(n, -1, dtype=np.int32)
+    r2o[keep] = np.random.default_rng(1).permutation(int(keep.sum())).astype(np.int32)
+    n_out = int(keep.sum())
+    assert same(g.decode_chunk(bed, n, n_out, r2o), o.decode_chunk(bed, n, n_out, r2o))
+
+
+def test_decode_matches_reference_golden(golden_dir):
+    payload, n_raw, ids, r2o, _ = load_tiny(golden_dir)
+    gold = np.load(golden_dir / "tiny_chunks.npz")
+    assert same(g.decode_chunk(payload, n_raw, len(ids), r2o), gold["raw"])
+    dpayload, dn, _ = load_dense(golden_dir)
+    assert same(g.decode_chunk(dpayload, dn), np.load(golden_dir / "dense_chunks.npz")["raw"])
+
+
+@pytest.mark.parametrize("method", range(1, 9))
+@pytest.mark.parametrize("kind", ["A", "D"])
+def test_standardise_matches_reference_golden(golden_dir, method, kind):
+    payload, n_raw, ids, r2o, _ = load_tiny(golden_dir)
+    gold = np.load(golden_dir / "tiny_chunks.npz")
+    z, freq = g.standardise_chunk(payload, n_raw, method, 0 if kind == "A" else 1, n_out=len(ids), raw_to_out=r2o)
+    assert np.array_equal(freq, gold[f"freq_{method}_{kind}"])  # bit-exact allele frequencies
+    assert close(z, gold[f"z_{method}_{kind}"], rtol=1e-12, atol=1e-13)
+
+
+def test_standardise_vs_oracle_random():
+    n = 1537
+    bed = g.synth_bed_host(n, 0, 300, 3, 0.04)
+    raw = o.decode_chunk(bed, n)
+    for method in range(1, 9):
+        for kind in (0, 1):
+            z, f = g.standardise_chunk(bed, n, method, kind)
+            zr, fr = o.process_matrix(raw, method, kind)
+            assert np.array_equal(f, fr)
+            assert close(z, zr, rtol=1e-12, atol=1e-13)
+
+
+def test_all_missing_snp_policy():
+    n = 64
+    geno = np.random.default_rng(2).integers(0, 3, size=(n, 6)).astype(np.float64)
+    geno[:, 2] = np.nan
+    bed = plink_io.encode_matrix(geno)
+    z, f = g.standardise_chunk(bed, n, 1, 0)  # reference behaviour: the column stays NaN
+    zr, fr = o.process_matrix(o.decode_chunk(bed, n), 1, 0)
+    assert same(np.isnan(z), np.isnan(zr)) and np.all(np.isnan(z[:, 2])) and f[2] == fr[2] == 0.0
+    z2, _ = g.standardise_chunk(bed, n, 1, 0, all_missing_policy=g._lib.ALLMISS_SKIP)
+    assert np.all(z2[:, 2] == 0.0)
+
+
+def test_snp_counts_and_freq_bit_exact():
+    n, m = 2001, 1500
+    bed = g.synth_bed_host(n, 0, m, 21, 0.02)
+    acc = run_gpu(bed, n, m, 1, (0,), g.PREC_FP16)
+    n0, n1, n2, nm, f = acc.snp_stats(0, m)
+    acc.close()
+    raw = o.decode_chunk(bed, n)
+    assert np.array_equal(nm, np.isnan(raw).sum(axis=0))
+    assert np.array_equal(n0, (raw == 0).sum(axis=0)) and np.array_equal(n1, (raw == 1).sum(axis=0))
+    assert np.array_equal(n2, (raw == 2).sum(axis=0))
+    _, fr = o.process_matrix(raw, 1, 0)
+    assert np.array_equal(f, fr)
+
+
+# ------------------------------------------------------------------------------------------------ GRM entries
+@pytest.mark.parametrize("method,kinds", [(1, (0,)), (3, (0, 1)), (4, (0, 1)), (5, (1,)), (8, (0, 1)), (2, (1,))])
+def test_grm_fp64_vs_oracle(method, kinds):
+    n, m = 777, 2100
+    bed = g.synth_bed_host(n, 0, m, 31, 0.02)
+    acc = run_gpu(bed, n, m, method, kinds, g.PREC_FP64, chunk=640)
+    for kind in kinds:
+        packed, tr = acc.fetch(kind, g.GROUP_WHOLE, dtype=np.float64)
+        G, den, _ = o.grm_compute(bed, n, method, kind, chunk=500)
+        assert abs(tr / n - den) <= 1e-9 * abs(den)
+        assert np.max(np.abs(norm_packed(packed) - norm_ref(G))) <= TOL64
+        # on-disk float32 view: identical after rounding or within 1 float32 ulp
+        f32, _ = acc.fetch(kind, g.GROUP_WHOLE, dtype=np.float32)
+        ref32 = o.pack_lower_f32(G)
+        assert np.all(np.abs(f32 - ref32) <= np.spacing(np.abs(ref32)))
+    acc.close()
+
+
+@pytest.mark.parametrize("precision", [g.PREC_BF16, g.PREC_FP16])
+@pytest.mark.parametrize("method,kinds", [(1, (0,)), (3, (0, 1)), (4, (0, 1)), (6, (0, 1))])
+def test_grm_16bit_vs_oracle(precision, method, kinds):
+    n, m = 1100, 6000
+    bed = g.synth_bed_host(n, 0, m, 41, 0.01)
+    acc = run_gpu(bed, n, m, method, kinds, precision, chunk=2048)
+    for kind in kinds:
+        packed, tr = acc.fetch(kind, g.GROUP_WHOLE)
+        G, den, _ = o.grm_compute(bed, n, method, kind, chunk=2000)
+        err = np.max(np.abs(norm_packed(packed) - norm_ref(G)))
+        assert err <= tol16(m) * (8.0 if precision == g.PREC_BF16 else 1.0), err  # BF16 has 3 fewer mantissa bits
+        assert abs(tr / n - den) <= 2e-3 * abs(den)
+    acc.close()
+
+
+def test_chunk_size_and_push_size_invariance_fp64():
+    # reference tests/test_grm.cpp:187-225 (chunk 1 / 7 / m / m+100 within 1e-10) restated for device chunks and pushes
+    n, m = 300, 700
+    bed = g.synth_bed_host(n, 0, m, 51, 0.02)
+    base = None
+    for chunk, push in ((64, 1), (448, 7), (0, m), (1024, 333)):
+        acc = run_gpu(bed, n, m, 3, (0,), g.PREC_FP64, chunk=chunk, push=push)
+        packed, _ = acc.fetch(0, g.GROUP_WHOLE, dtype=np.float64)
+        acc.close()
+        if base is None:
+            base = norm_packed(packed)
+        assert np.max(np.abs(norm_packed(packed) - base)) <= TOL64
+
+
+def test_tc_single_cta_and_pair_kernels_agree(monkeypatch):
+    n, m = 1300, 4000
+    bed = g.synth_bed_host(n, 0, m, 61, 0.01)
+    outs = []
+    for mode in ("1", "2"):
+        monkeypatch.setenv("GGRM_TC_MODE", mode)
+        acc = run_gpu(bed, n, m, 1, (0,), g.PREC_FP16, chunk=1024)
+        outs.append(acc.fetch(0, g.GROUP_WHOLE)[0])
+        acc.close()
+    # same operands, same K order per tile: results agree to FP32 rounding of the accumulation
+    assert np.max(np.abs(norm_packed(outs[0]) - norm_packed(outs[1]))) <= 1e-6
+
+
+def test_projection_row_order_and_golden_bin(golden_dir):
+    # shuffled FAM with a duplicated ID: rows must come out in sorted-ID order
+    payload, n_raw, ids, r2o, chroms = load_tiny(golden_dir)
+    n, m = len(ids), len(chroms)
+    for tag, method, kind in (("SH.add", 1, 0), ("OSH.dom", 3, 1), ("OCH.add", 4, 0), ("OCH.dom", 4, 1)):
+        acc = run_gpu(payload, n_raw, m, method, (kind,), g.PREC_FP64, n_out=n, raw_to_out=r2o, push=13)
+        got, _ = acc.fetch(kind, g.GROUP_WHOLE, dtype=np.float32)
+        acc.close()
+        ref = plink_io.read_bin(golden_dir / f"tiny_{tag}.bin", n)
+        assert np.all(np.abs(got - ref) <= np.spacing(np.abs(ref)) + 1e-30), tag
+
+
+def test_reference_nan_poisoning_is_reproduced(golden_dir):
+    # tiny SNP 11 has one valid call: Standardize (sample sd, valid-1 = 0) yields NaN and poisons the matrix in the
+    # reference (tiny_S.*.bin are all-NaN); the default policy reproduces that bit for bit.
+    payload, n_raw, ids, r2o, chroms = load_tiny(golden_dir)
+    n, m = len(ids), len(chroms)
+    acc = run_gpu(payload, n_raw, m, 5, (0, 1), g.PREC_FP64, n_out=n, raw_to_out=r2o)
+    for kind, tag in ((0, "S.add"), (1, "S.dom")):
+        got, _ = acc.fetch(kind, g.GROUP_WHOLE, dtype=np.float32)
+        ref = plink_io.read_bin(golden_dir / f"tiny_{tag}.bin", n)
+        assert np.array_equal(np.isnan(got), np.isnan(ref))
+    acc.close()
+
+
+def test_loco_groups_whole_and_subtraction(golden_dir):
+    payload, n_raw, ids, r2o, chroms = load_tiny(golden_dir)
+    n, m = len(ids), len(chroms)
+    runs = plink_io.chrom_runs(chroms)
+    groups = [(b, e) for _, b, e in runs]
+    acc = run_gpu(payload, n_raw, m, 4, (0, 1), g.PREC_FP64, n_out=n, raw_to_out=r2o, groups=groups, keep_whole=True, push=10)
+    gold = np.load(golden_dir / "tiny_loaders.npz")
+    for kind, kname in ((0, "add"), (1, "dom")):
+        whole, _ = acc.fetch(kind, g.GROUP_WHOLE, dtype=np.float32)
+        ref_w = plink_io.read_bin(golden_dir / f"tiny_OCH.{kname}.bin", n)
+        assert np.all(np.abs(whole - ref_w) <= 2 * np.spacing(np.abs(ref_w)) + 1e-6)  # whole = sum of partials
+        for gi, (name, _, _) in enumerate(runs):
+            part, _ = acc.fetch(kind, gi, dtype=np.float32)
+            ref = plink_io.read_bin(golden_dir / f"tiny_OCH.{kname}.chr{name}.bin", n)
+            assert np.all(np.abs(part - ref) <= np.spacing(np.abs(ref)) + 1e-30), (kname, name)
+    # consumer-side arithmetic on device: (G_w - G_c)/(k_w - k_c) as LocoGRMLoader computes it
+    for gi, (name, _, _) in enumerate(runs):
+        loco = acc.fetch_loco(0, gi)
+        ref = gold[f"OCH_add_loco_chr{name}"][np.tril_indices(n)]
+        assert np.allclose(loco, ref, rtol=1e-5, atol=1e-6)  # the reference works from float32 files
+    acc.close()
+    acc = run_gpu(payload, n_raw, m, 1, (0,), g.PREC_FP64, n_out=n, raw_to_out=r2o)
+    nrm = acc.fetch_normalized(0, g.GROUP_WHOLE)
+    assert np.allclose(nrm, gold["SH_add_normalized"][np.tril_indices(n)], rtol=1e-6, atol=1e-7)
+    acc.close()
+
+
+def test_group_pool_release_and_row_range_fetch():
+    n, m = 520, 900
+    bed = g.synth_bed_host(n, 0, m, 71, 0.01)
+    groups = [(0, 200), (200, 450), (450, 900)]
+    acc = g.Accumulator(n, m, method=1, precision=g.PREC_FP64, groups=groups, keep_whole=True, max_resident_groups=1)
+    fetched = []
+    for gi, (b, e) in enumerate(groups):
+        acc.push(bed[b:e], b)
+        if gi > 0:  # previous group is complete as soon as a later group has been pushed
+            fetched.append(acc.fetch(0, gi - 1, dtype=np.float64)[0])
+            acc.release_group(0, gi - 1)
+    acc.finish()
+    fetched.append(acc.fetch(0, 2, dtype=np.float64)[0])
+    whole, _ = acc.fetch(0, g.GROUP_WHOLE, dtype=np.float64)
+    assert np.allclose(whole, sum(fetched), rtol=1e-12, atol=1e-9)
+    for gi, (b, e) in enumerate(groups):
+        G, _, _ = o.grm_compute(bed, n, 1, 0, ranges=[(b, e)])
+        assert np.allclose(fetched[gi], G[np.tril_indices(n)], rtol=1e-10, atol=1e-9)
+    # row-range fetch returns exactly the corresponding slice of the packed file
+    part, tr = acc.fetch(0, g.GROUP_WHOLE, row_begin=100, row_count=57, dtype=np.float64)
+    assert np.array_equal(part, whole[g.tri(100):g.tri(157)])
+    diag = np.cumsum(np.arange(1, n + 1)) - 1
+    assert abs(tr - whole[diag[100:157]].sum()) <= 1e-9 * abs(tr)
+    acc.close()
+
+
+def test_tile_partition_and_snp_shard_recombine():
+    # multi-GPU decompositions emulated on one device: tile ranks own disjoint tiles (sum = whole);
+    # SNP shards hold partial sums (sum = whole); peer reduce kernel sums accumulators in place.
+    n, m = 2300, 1200   # 9 x 9 tiles of 256 -> 3 super-tiles
+    bed = g.synth_bed_host(n, 0, m, 81, 0.01)
+    full = run_gpu(bed, n, m, 1, (0,), g.PREC_FP64)
+    whole, _ = full.fetch(0, g.GROUP_WHOLE, dtype=np.float64)
+    parts = []
+    for r in range(3):
+        acc = run_gpu(bed, n, m, 1, (0,), g.PREC_FP64, tile_rank=r, tile_world=3)
+        parts.append(acc.fetch(0, g.GROUP_WHOLE, dtype=np.float64)[0])
+        acc.close()
+    assert all(np.count_nonzero(p) > 0 for p in parts)
+    assert np.array_equal(sum(parts), whole)  # every entry is owned by exactly one rank
+    a = g.Accumulator(n, m, method=1, precision=g.PREC_FP64)
+    b = g.Accumulator(n, m, method=1, precision=g.PREC_FP64)
+    a.push(bed[:500], 0)
+    b.push(bed[500:], 500)
+    a.finish()
+    b.finish()
+    pa, na, _ = a.accum_buffer(0, g.GROUP_WHOLE)
+    pb, nb, _ = b.accum_buffer(0, g.GROUP_WHOLE)
+    assert na == nb
+    a.reduce_peer(0, g.GROUP_WHOLE, [pb], 0, na)
+    summed, _ = a.fetch(0, g.GROUP_WHOLE, dtype=np.float64)
+    assert np.allclose(summed, whole, rtol=1e-12, atol=1e-9)
+    for x in (a, b, full):
+        x.close()
+
+
+def test_error_codes_follow_reference_semantics():
+    acc = g.Accumulator(100, 50, method=1, precision=g.PREC_FP64)
+    bed = g.synth_bed_host(100, 0, 50, 1, 0.0)
+    with pytest.raises(g.GrmError) as e:
+        acc.push(bed[:10], 45)  # bed_pipe.cpp:38-52 ColumnRangeException
+    assert e.value.status == -2 and "invalid chunk range" in e.value.message
+    acc.push(bed[:10], 0)
+    with pytest.raises(g.GrmError) as e:
+        acc.push(bed[:10], 5)   # overlapping range
+    assert e.value.status == -3
+    with pytest.raises(g.GrmError) as e:
+        acc.fetch(1, g.GROUP_WHOLE)  # dominance was not requested
+    assert e.value.status == -3
+    acc.close()
+    with pytest.raises(g.GrmError) as e:
+        g.Accumulator(100, 50, method=9)
+    assert e.value.status == -1 and "Invalid genotype process method" in e.value.message
+
+
+def test_reset_allows_a_second_pass():
+    n, m = 400, 600
+    bed = g.synth_bed_host(n, 0, m, 91, 0.01)
+    acc = run_gpu(bed, n, m, 1, (0,), g.PREC_FP16)
+    first, _ = acc.fetch(0, g.GROUP_WHOLE)
+    acc.reset()
+    acc.push(bed, 0)
+    acc.finish()
+    second, _ = acc.fetch(0, g.GROUP_WHOLE)
+    assert np.array_equal(first, second)
+    acc.close()
+
+
+def test_c1_shape_tolerance_16bit():
+    # Config C1 (2 000 x 50 000, Yang additive = StandardizeHWE + Add): the 1e-4 bound at a named shape.
+    # The CPU oracle would need minutes at this size, so the FP64 tensor-core path (itself within 1e-10 of the oracle
+    # above) is the comparison; entries are checked on G/(trace/n).
+    n, m = 2000, 50000
+    bed = g.synth_bed_host(n, 0, m, 20261105, 0.01)
+    ref = run_gpu(bed, n, m, 1, (0,), g.PREC_FP64, push=10000)
+    r, _ = ref.fetch(0, g.GROUP_WHOLE, dtype=np.float64)
+    ref.close()
+    rn = norm_packed(r)
+    for prec, bound in ((g.PREC_FP16, 1e-4), (g.PREC_BF16, 2e-4)):
+        acc = run_gpu(bed, n, m, 1, (0,), prec, push=10000)
+        p, _ = acc.fetch(0, g.GROUP_WHOLE)
+        acc.close()
+        err = np.max(np.abs(norm_packed(p) - rn))
+        assert err <= bound, (prec, err)
