@@ -70,7 +70,7 @@ def process_column(col, method, kind):
 
 def process_matrix(chunk_nc, method, kind):
     """chunk_nc: (n, c) array; returns processed (n, c) and freqs."""
-    z = np.ascontiguousarray(np.asarray(chunk_nc, dtype=np.float64).T)  # (c, n) C-order == column-major n x c
+    z = np.array(np.asarray(chunk_nc, dtype=np.float64).T, order="C", copy=True)  # (c, n) C-order == column-major n x c; never alias the input
     freqs = np.empty(z.shape[0], dtype=np.float64)
     lib().oracle_process_matrix(_p(z), z.shape[1], z.shape[0], method, kind, _p(freqs))
     return z.T, freqs
