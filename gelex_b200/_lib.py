@@ -66,7 +66,7 @@ EXPORTS = [
     "ggrm_create", "ggrm_destroy", "ggrm_last_error", "ggrm_push", "ggrm_push_device", "ggrm_finish", "ggrm_reset", "ggrm_snp_stats",
     "ggrm_fetch", "ggrm_fetch_f64", "ggrm_release_group", "ggrm_accum_buffer", "ggrm_reduce_peer",
     "ggrm_fetch_normalized", "ggrm_fetch_loco", "ggrm_get_timers", "ggrm_decode_chunk", "ggrm_standardise_chunk",
-    "ggrm_synth_bed_host", "ggrm_synth_bed_device", "ggrm_device_count", "ggrm_version",
+    "ggrm_synth_bed_host", "ggrm_synth_bed_device", "ggrm_device_count", "ggrm_version", "ggrm_enable_peer_access",
 ]
 
 _lib = None

@@ -197,6 +197,7 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
     h->fp64 = cfg->precision == GGRM_PREC_FP64;
     h->elem_bytes = h->fp64 ? 8 : 4;
     h->tc_mode = 2;  // CTA-pair UMMA 256x256x16 (measured ~20 % faster than the single-CTA 128x256 form)
+    if (const char* e = std::getenv("GGRM_CACHE_HINTS")) h->cache_hints = std::atoi(e) & 3;
     if (const char* e = std::getenv("GGRM_TC_MODE")) h->tc_mode = std::atoi(e) == 1 ? 1 : 2;
 
     // groups

@@ -91,6 +91,19 @@ extern "C" int ggrm_standardise_chunk(int device, const uint8_t* bed_payload, in
     GGRM_STATELESS_END
 }
 
+extern "C" int ggrm_enable_peer_access(int device, int peer_device) {
+    GGRM_STATELESS_BEGIN
+    check_device(device, nullptr);
+    if (device == peer_device) return GGRM_OK;
+    int can = 0;
+    GGRM_CUDA(cudaDeviceCanAccessPeer(&can, device, peer_device));
+    if (!can) throw CudaError{GGRM_ERR_CUDA, "CUDA: device " + std::to_string(device) + " cannot access peer " + std::to_string(peer_device)};
+    const cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+    else GGRM_CUDA(e);
+    GGRM_STATELESS_END
+}
+
 static uint32_t miss_threshold(double missing_rate) {
     if (!(missing_rate > 0.0)) return 0u;
     if (missing_rate >= 1.0) return 1u << 24;

@@ -103,11 +103,11 @@ static void launch_syrk(Handle& h, int kind, int g, int64_t c) {
             lc.attrs = attr;
             lc.numAttrs = 1;
             GGRM_CUDA(cudaLaunchKernelEx(&lc, syrk_tc_kernel<2>, h.tmap[kind], static_cast<float*>(accum),
-                                         static_cast<const TcItem*>(h.d_items_tc), h.num_items_tc, nkb, 0, 1, fmt, h.d_fault));
+                                         static_cast<const TcItem*>(h.d_items_tc), h.num_items_tc, nkb, 0, 1, fmt, h.cache_hints, h.d_fault));
         } else {
             const int grid = std::min(h.num_items_tc, h.sm_count);
             syrk_tc_kernel<1><<<grid, 256, TcConfig<1>::kSmemBytes, h.s_comp>>>(h.tmap[kind], static_cast<float*>(accum), h.d_items_tc,
-                                                                                h.num_items_tc, nkb, 0, 1, fmt, h.d_fault);
+                                                                                h.num_items_tc, nkb, 0, 1, fmt, h.cache_hints, h.d_fault);
             GGRM_CUDA(cudaGetLastError());
         }
     }

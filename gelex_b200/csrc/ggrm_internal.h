@@ -52,6 +52,7 @@ struct Handle {
     int64_t k_cap = 0;                    // SNP capacity of one device chunk (multiple of 64)
     bool fp64 = false;
     int elem_bytes = 4;
+    int cache_hints = 3;                  // bit 0: Z panels evict_last, bit 1: accumulator stream evict_first (GGRM_CACHE_HINTS)
     int tc_mode = 1;                      // 1 = single-CTA UMMA 128x256, 2 = CTA-pair UMMA 256x256
     // ownership and work lists
     std::vector<int32_t> slot_of_host;    // [ntiles_side*(ntiles_side+1)/2] -> slot or -1

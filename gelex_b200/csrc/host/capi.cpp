@@ -1,0 +1,92 @@
+// C entry point over the C++ host engine (for ctypes tests and for embedding); never throws.
+#include <cstring>
+#include <string>
+
+#include "exceptions.h"
+#include "grm_engine.h"
+#include "plink_meta.h"
+
+using namespace gelex::b200;
+
+static void set_err(char* err, int err_len, const std::string& m) {
+    if (err == nullptr || err_len <= 0) return;
+    std::strncpy(err, m.c_str(), static_cast<size_t>(err_len - 1));
+    err[err_len - 1] = '\0';
+}
+
+extern "C" int gelex_b200_grm_run(const char* bfile, const char* out_prefix, int method, int mode, int do_loco, int chunk_size,
+                                  int precision, int n_gpus, int write_whole, char* err, int err_len) {
+    try {
+        if (bfile == nullptr || out_prefix == nullptr) throw ArgumentValidationException("null argument");
+        if (method < 1 || method > 8) throw InvalidInputException("Invalid genotype process method.");
+        GrmEngine::Config cfg;
+        cfg.bed_path = format_bed_path(bfile);
+        cfg.mode = mode == 2 ? GrmType::AD : (mode == 1 ? GrmType::D : GrmType::A);
+        cfg.method = static_cast<GenotypeProcessMethod>(method);
+        cfg.do_loco = do_loco != 0;
+        cfg.out_prefix = out_prefix;
+        cfg.chunk_size = chunk_size;
+        cfg.precision = precision;
+        cfg.write_whole = write_whole != 0;
+        cfg.gpus.clear();
+        for (int i = 0; i < (n_gpus > 0 ? n_gpus : 1); ++i) cfg.gpus.push_back(i);
+        GrmEngine engine(cfg);
+        engine.compute();
+        set_err(err, err_len, "");
+        return 0;
+    } catch (const FileNotFoundException& e) { set_err(err, err_len, std::string("FileNotFoundException: ") + e.what()); return -10;
+    } catch (const FileOpenException& e) { set_err(err, err_len, std::string("FileOpenException: ") + e.what()); return -11;
+    } catch (const FileFormatException& e) { set_err(err, err_len, std::string("FileFormatException: ") + e.what()); return GGRM_ERR_FILE_FORMAT;
+    } catch (const FileWriteException& e) { set_err(err, err_len, std::string("FileWriteException: ") + e.what()); return -12;
+    } catch (const ColumnRangeException& e) { set_err(err, err_len, std::string("ColumnRangeException: ") + e.what()); return GGRM_ERR_COLUMN_RANGE;
+    } catch (const ArgumentValidationException& e) { set_err(err, err_len, std::string("ArgumentValidationException: ") + e.what()); return GGRM_ERR_INVALID_ARGUMENT;
+    } catch (const InvalidInputException& e) { set_err(err, err_len, std::string("InvalidInputException: ") + e.what()); return GGRM_ERR_INVALID_ARGUMENT;
+    } catch (const InvalidOperationException& e) { set_err(err, err_len, std::string("InvalidOperationException: ") + e.what()); return GGRM_ERR_INVALID_OPERATION;
+    } catch (const GelexException& e) { set_err(err, err_len, std::string("GelexException: ") + e.what()); return GGRM_ERR_CUDA;
+    } catch (const std::bad_alloc&) { set_err(err, err_len, "std::bad_alloc"); return GGRM_ERR_OUT_OF_MEMORY;
+    } catch (const std::exception& e) { set_err(err, err_len, std::string("std::exception: ") + e.what()); return -99; }
+}
+
+// Metadata-only entry (no GPU needed): sample order, projection and chromosome runs as the engine will use them.
+// ids_out: n_out lines "FID\tIID\n" (the .id payload) written into buf (truncated to buf_len); returns n_out or < 0.
+extern "C" int64_t gelex_b200_plan(const char* bfile, int mode, int do_loco, int32_t* raw_to_out, int64_t raw_cap, int64_t* n_raw_out,
+                                   int64_t* m_out, int* dense_out, char* names_buf, int names_len, int64_t* group_begin,
+                                   int64_t* group_end, int group_cap, int* n_items_out, char* err, int err_len) {
+    try {
+        std::filesystem::path bed = format_bed_path(bfile), fam = bed, bim = bed;
+        fam.replace_extension(".fam");
+        bim.replace_extension(".bim");
+        const auto raw = load_fam_ids(fam);
+        const auto order = make_sample_order(raw);
+        const auto chroms = load_bim_chromosomes(bim);
+        if (n_raw_out) *n_raw_out = static_cast<int64_t>(raw.size());
+        if (m_out) *m_out = static_cast<int64_t>(count_total_lines(bim));
+        if (dense_out) *dense_out = order.dense ? 1 : 0;
+        if (raw_to_out)
+            for (int64_t i = 0; i < static_cast<int64_t>(raw.size()) && i < raw_cap; ++i) raw_to_out[i] = order.raw_to_out[static_cast<size_t>(i)];
+        std::string suffix;
+        size_t ng = 0;
+        const auto items = GrmEngine::build_plan(chroms, mode == 2 ? GrmType::AD : (mode == 1 ? GrmType::D : GrmType::A), do_loco != 0, &suffix, &ng);
+        std::string names;
+        int gi = 0;
+        for (const auto& it : items) {
+            names += it.output_name + "\n";
+            if (gi < group_cap && group_begin && group_end) {
+                group_begin[gi] = it.ranges[0].first;
+                group_end[gi] = it.ranges[0].second;
+            }
+            ++gi;
+        }
+        names += suffix + "\n";
+        if (names_buf && names_len > 0) {
+            std::strncpy(names_buf, names.c_str(), static_cast<size_t>(names_len - 1));
+            names_buf[names_len - 1] = '\0';
+        }
+        if (n_items_out) *n_items_out = static_cast<int>(items.size());
+        set_err(err, err_len, "");
+        return static_cast<int64_t>(order.ids.size());
+    } catch (const std::exception& e) {
+        set_err(err, err_len, e.what());
+        return -1;
+    }
+}

@@ -1,0 +1,93 @@
+// B200 GrmEngine: same Config in, same files + events out as the reference's gelex::GrmEngine
+// (include/gelex/pipeline/grm_engine.h:30-51, src/pipeline/grm_engine.cpp:52-124), with the chunk loop of
+// include/gelex/data/grm/grm.h:94-137 replaced by the C ABI of include/ggrm.h.
+//
+// Differences that are improvements, not behaviour changes:
+//   * AD mode decodes once and runs two SYRKs per slab (the reference re-reads the BED per work item, grm_work_plan.cpp:95-103)
+//   * --loco produces every per-chromosome partial in ONE pass; with write_whole the whole-genome matrix is the device-side
+//     sum of the partials (the reference needs a second invocation)
+//   * .bin files are written from row blocks fetched in file order (large sequential writes instead of one 4-byte
+//     ostream::write per element, grm_bin_writer.cpp:54-61); bytes are identical.
+#pragma once
+#include <cstdint>
+#include <filesystem>
+#include <functional>
+#include <string>
+#include <variant>
+#include <vector>
+
+#include "../../../include/ggrm.h"
+
+namespace gelex::b200 {
+
+enum class GrmType : uint8_t { A, D, AD };  // include/gelex/types/freq_effect.h
+
+enum class GenotypeProcessMethod : uint8_t {  // include/gelex/data/genotype/genotype_processor.h:38-48
+    StandardizeHWE = 1, CenterHWE, OrthStandardizeHWE, OrthCenterHWE, Standardize, Center, OrthStandardize, OrthCenter
+};
+// "SH" / "StandardizeHWE" / ... case-insensitive (apps/cli/cli_helper.h:41-82); throws InvalidInputException.
+GenotypeProcessMethod parse_genotype_process_method(const std::string& value);
+const char* method_name(GenotypeProcessMethod m);
+
+// Events, include/gelex/infra/logging/grm_event.h:28-67 (same names and field meanings).
+struct GrmConfigLoadedEvent { std::string method; GrmType mode; bool do_loco; };
+struct GrmDataLoadedEvent { size_t num_samples; size_t num_snps; };
+struct GrmComputeStartedEvent { size_t total_snps; };
+struct GrmProgressEvent { size_t current; size_t total; bool done; };
+struct GrmFilesWrittenEvent { size_t num_files; std::string output_dir; std::string file_pattern; };
+using GrmEvent = std::variant<GrmConfigLoadedEvent, GrmDataLoadedEvent, GrmComputeStartedEvent, GrmProgressEvent, GrmFilesWrittenEvent>;
+using GrmObserver = std::function<void(const GrmEvent&)>;
+
+struct GrmWorkItem {  // src/pipeline/grm_work_plan.h:34-39
+    std::vector<std::pair<int64_t, int64_t>> ranges;
+    bool is_additive;
+    std::string output_name;
+    int group;  // index into the chromosome runs, -1 = whole genome
+};
+
+class GrmEngine {
+   public:
+    struct Config {
+        // --- the reference's fields (grm_engine.h:33-43) ---
+        std::filesystem::path bed_path;
+        GrmType mode = GrmType::A;
+        GenotypeProcessMethod method = GenotypeProcessMethod::OrthStandardizeHWE;
+        bool do_loco = false;
+        std::string out_prefix = "grm";
+        int chunk_size = 10000;  // host push granularity = progress-event granularity (grm.h:111-132)
+        // --- opt-in additions (SURVEY §5 "config / flag system") ---
+        int precision = GGRM_PREC_FP16;  // GGRM_PREC_FP16 | GGRM_PREC_BF16 | GGRM_PREC_FP64
+        std::vector<int> gpus = {0};     // device ordinals; >1 = SNP-sharded (or chromosome-sharded with --loco)
+        bool write_whole = false;        // with do_loco: also write <out>.<add|dom>.{bin,id} from the sum of partials
+        bool skip_all_missing = false;   // GGRM_ALLMISS_SKIP instead of the reference's NaN poisoning
+    };
+
+    explicit GrmEngine(Config config);
+    void compute(const GrmObserver& observer = {});
+
+    // What the last compute() did (for the CLI's closing line and for tests).
+    struct Summary {
+        size_t num_samples = 0, num_snps = 0, num_files = 0;
+        double wall_s = 0, device_pass_ms = 0, syrk_ms = 0, write_s = 0;
+        std::vector<std::string> files;
+    };
+    const Summary& summary() const { return summary_; }
+
+    // Work plan exactly as GrmNormalPlan / GrmLocoPlan build it (src/pipeline/grm_work_plan.cpp:83-147).
+    static std::vector<GrmWorkItem> build_plan(const std::vector<std::string>& chroms, GrmType mode, bool do_loco,
+                                               std::string* output_pattern_suffix, size_t* num_groups);
+
+   private:
+    Config config_;
+    Summary summary_;
+};
+
+// Writers with the reference's byte layouts (grm_bin_writer.cpp:34-69, grm_id_writer.cpp:41-54).
+void write_id_file(const std::filesystem::path& path, const std::vector<std::string>& sorted_ids);
+
+}  // namespace gelex::b200
+
+// C entry point for tests / bindings: runs GrmEngine::compute; returns 0 or the ggrm_status-like negative code,
+// error text in err (NUL-terminated, truncated to err_len).  mode: 0 = A, 1 = D, 2 = AD.
+extern "C" int gelex_b200_grm_run(const char* bfile, const char* out_prefix, int method, int mode, int do_loco, int chunk_size,
+                                  int precision, int n_gpus, int write_whole, char* err, int err_len);

@@ -128,6 +128,27 @@ constexpr uint64_t kCacheEvictNormal = 0x1000000000000000ull;
 constexpr uint64_t kCacheEvictFirst = 0x12F0000000000000ull;
 constexpr uint64_t kCacheEvictLast = 0x14F0000000000000ull;
 
+// ---------------------------------------------------------------- streaming global access (accumulator read-modify-write)
+// The FP32 accumulator is touched once per slab; it must not push the Z operand panels (re-read by many CTAs) out of L2.
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ float4 ld_stream_f4(const float4* ptr, uint64_t policy) {
+    float4 r;
+    asm volatile("ld.global.L1::no_allocate.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(ptr), "l"(policy)
+                 : "memory");
+    return r;
+}
+__device__ __forceinline__ void st_stream_f4(float4* ptr, const float4& v, uint64_t policy) {
+    asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(ptr), "f"(v.x), "f"(v.y),
+                 "f"(v.z), "f"(v.w), "l"(policy)
+                 : "memory");
+}
+
 // ---------------------------------------------------------------- tcgen05 / TMEM
 template <int kCtaGroup>
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t ncols) {

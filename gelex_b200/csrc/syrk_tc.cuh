@@ -47,7 +47,7 @@ struct TcConfig {
 template <int kCtaGroup>
 __global__ void __launch_bounds__(256, 1)
 syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ accum, const TcItem* __restrict__ items,
-               int num_items, int num_k_blocks, int k_block0, int accumulate, uint32_t ab_format, int* fault_flag) {
+               int num_items, int num_k_blocks, int k_block0, int accumulate, uint32_t ab_format, int cache_hints, int* fault_flag) {
     using Cfg = TcConfig<kCtaGroup>;
     constexpr int kStages = Cfg::kStages;
     extern __shared__ uint8_t smem_raw[];
@@ -90,6 +90,8 @@ syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ a
     if (warp == 0) {
         // ===================================================== TMA producer
         uint32_t stage = 0, phase = 0;
+        // cache_hints bit 0: keep Z panels in L2 (evict_last) — they are re-read by every CTA of the super-tile
+        const uint64_t z_hint = (cache_hints & 1) ? ptx::kCacheEvictLast : ptx::kCacheEvictNormal;
         for (int it = cluster_id; it < num_items; it += num_clusters) {
             const TcItem item = items[it];
             const int32_t a_row = item.a_row0 + static_cast<int32_t>(cta_rank) * 128;
@@ -102,15 +104,15 @@ syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ a
                     uint8_t* sb = smem_b + stage * Cfg::kBBytes;
                     if constexpr (kCtaGroup == 1) {
                         ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-                        ptx::tma_load_2d(&tmap_z, &full_bar[stage], sa, kc, a_row, ptx::kCacheEvictNormal);
-                        ptx::tma_load_2d(&tmap_z, &full_bar[stage], sb, kc, b_row, ptx::kCacheEvictNormal);
-                        ptx::tma_load_2d(&tmap_z, &full_bar[stage], sb + kTcABytes, kc, b_row + 128, ptx::kCacheEvictNormal);
+                        ptx::tma_load_2d(&tmap_z, &full_bar[stage], sa, kc, a_row, z_hint);
+                        ptx::tma_load_2d(&tmap_z, &full_bar[stage], sb, kc, b_row, z_hint);
+                        ptx::tma_load_2d(&tmap_z, &full_bar[stage], sb + kTcABytes, kc, b_row + 128, z_hint);
                     } else {
                         // both CTAs' bytes are counted on the leader's barrier
                         if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
                         else ptx::mbar_arrive_cluster(&full_bar[stage], 0);
-                        ptx::tma_load_2d_pair(&tmap_z, &full_bar[stage], sa, kc, a_row, ptx::kCacheEvictNormal);
-                        ptx::tma_load_2d_pair(&tmap_z, &full_bar[stage], sb, kc, b_row, ptx::kCacheEvictNormal);
+                        ptx::tma_load_2d_pair(&tmap_z, &full_bar[stage], sa, kc, a_row, z_hint);
+                        ptx::tma_load_2d_pair(&tmap_z, &full_bar[stage], sb, kc, b_row, z_hint);
                     }
                 }
                 __syncwarp();
@@ -155,6 +157,8 @@ syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ a
         const uint32_t lane = ptx::lane_id();
         const uint32_t row = quad * 32 + lane;
         uint32_t local_it = 0;
+        const uint64_t stream_policy = ptx::l2_policy_evict_first();
+        const bool stream = (cache_hints & 2) != 0;  // bit 1: accumulator read-modify-write bypasses L1 and is first to leave L2
         for (int it = cluster_id; it < num_items; it += num_clusters, ++local_it) {
             const TcItem item = items[it];
             const uint32_t as = local_it & 1, aphase = (local_it >> 1) & 1;
@@ -172,10 +176,10 @@ syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ a
                     float4 r = make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]),
                                            __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3]));
                     if (accumulate) {
-                        const float4 o = *dst;
+                        const float4 o = stream ? ptx::ld_stream_f4(dst, stream_policy) : *dst;
                         r.x += o.x; r.y += o.y; r.z += o.z; r.w += o.w;
                     }
-                    *dst = r;
+                    if (stream) ptx::st_stream_f4(dst, r, stream_policy); else *dst = r;
                 }
             }
             ptx::tc_fence_before();

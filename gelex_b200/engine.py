@@ -1,0 +1,68 @@
+"""ctypes access to the C++ host engine (libggrm_host.so): the GrmEngine mirror of the reference
+(include/gelex/pipeline/grm_engine.h:30-51) and its metadata planner.  Marshalling only."""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+from . import _lib
+
+HOST_LIB_PATH = Path(__file__).resolve().parent / "libggrm_host.so"
+CLI_PATH = Path(__file__).resolve().parent / "gelex-b200"
+MODES = {"A": 0, "D": 1, "AD": 2}
+_host = None
+
+
+class EngineError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__(message)
+        self.status = status
+        self.message = message
+
+
+def load_host():
+    global _host
+    if _host is None:
+        _lib.load()  # dependency (resolved through rpath $ORIGIN as well)
+        if not HOST_LIB_PATH.exists():
+            raise ImportError(f"{HOST_LIB_PATH} not built; run __graft_entry__.build()")
+        h = C.CDLL(str(HOST_LIB_PATH))
+        h.gelex_b200_grm_run.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]
+        h.gelex_b200_plan.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64),
+                                      C.POINTER(C.c_int), C.c_char_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.c_char_p, C.c_int]
+        h.gelex_b200_plan.restype = C.c_int64
+        _host = h
+    return _host
+
+
+def grm_run(bfile, out_prefix, method="OSH", mode="A", loco=False, chunk_size=10000, precision=_lib.PREC_FP16, n_gpus=1, write_whole=False):
+    """GrmEngine::compute through the C entry point; raises EngineError("<ExceptionName>: message")."""
+    h = load_host()
+    m = _lib.METHODS[method] if isinstance(method, str) else int(method)
+    err = C.create_string_buffer(2048)
+    st = h.gelex_b200_grm_run(str(bfile).encode(), str(out_prefix).encode(), m, MODES[mode], int(loco), int(chunk_size), int(precision),
+                              int(n_gpus), int(write_whole), err, len(err))
+    if st != 0:
+        raise EngineError(st, err.value.decode())
+
+
+def plan(bfile, mode="A", loco=False, max_samples=1 << 22, max_items=4096):
+    """Metadata the engine derives from .fam/.bim (no GPU needed): row order projection, SNP count, work items."""
+    h = load_host()
+    r2o = np.full(max_samples, -2, dtype=np.int32)
+    n_raw, m, dense, n_items = C.c_int64(), C.c_int64(), C.c_int(), C.c_int()
+    names = C.create_string_buffer(1 << 20)
+    gb = np.zeros(max_items, dtype=np.int64)
+    ge = np.zeros(max_items, dtype=np.int64)
+    err = C.create_string_buffer(2048)
+    n_out = h.gelex_b200_plan(str(bfile).encode(), MODES[mode], int(loco), r2o.ctypes.data_as(C.c_void_p), max_samples, C.byref(n_raw), C.byref(m),
+                              C.byref(dense), names, len(names), gb.ctypes.data_as(C.c_void_p), ge.ctypes.data_as(C.c_void_p), max_items,
+                              C.byref(n_items), err, len(err))
+    if n_out < 0:
+        raise EngineError(int(n_out), err.value.decode())
+    lines = names.value.decode().split("\n")
+    k = n_items.value
+    return {"n_out": int(n_out), "n_raw": n_raw.value, "m": m.value, "dense": bool(dense.value), "raw_to_out": r2o[:n_raw.value].copy(),
+            "items": [(lines[i], int(gb[i]), int(ge[i])) for i in range(k)], "pattern_suffix": lines[k]}

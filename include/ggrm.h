@@ -168,6 +168,11 @@ int ggrm_synth_bed_host(uint8_t* out, int64_t n, int64_t snp_begin, int64_t snp_
 int ggrm_synth_bed_device(int device, uint8_t* d_out, int64_t n, int64_t snp_begin, int64_t snp_count, uint64_t seed,
                           double missing_rate);
 
+/* Single-process multi-GPU host (the C++ GrmEngine): let kernels on `device` read device memory of `peer_device`
+ * over NVLink (cudaDeviceEnablePeerAccess; idempotent), so ggrm_reduce_peer can take the peers' ggrm_accum_buffer
+ * pointers directly. */
+int ggrm_enable_peer_access(int device, int peer_device);
+
 /* Library / device facts for the harness. */
 int ggrm_device_count(void);
 const char* ggrm_version(void);

@@ -1,0 +1,133 @@
+"""Host-side logic of the C++ engine (FAM/BIM parsing, row order, work plan, file validation, error behaviour).
+CPU-only parts run everywhere; the end-to-end file parity tests need a B200 and are marked gpu."""
+import shutil
+import subprocess
+
+import numpy as np
+import pytest
+
+import gelex_b200 as g
+from gelex_b200 import engine
+import plink_io
+
+
+def test_plan_matches_reference_row_order_and_items(golden_dir):
+    p = engine.plan(golden_dir / "tiny", mode="AD", loco=True)
+    fam = [tuple(l.split()[:2]) for l in open(golden_dir / "tiny.fam")]
+    ids, r2o = plink_io.sample_order(fam)
+    assert p["n_raw"] == 37 and p["n_out"] == 36 and p["m"] == 96 and not p["dense"]
+    assert np.array_equal(p["raw_to_out"], r2o)
+    # GrmLocoPlan: for each chromosome run, add then dom; names add.chr<NAME> (grm_work_plan.cpp:122-147)
+    assert [i[0] for i in p["items"]] == ["add.chr1", "dom.chr1", "add.chr2", "dom.chr2", "add.chrX", "dom.chrX", "add.chr7", "dom.chr7"]
+    assert [i[1:] for i in p["items"][::2]] == [(0, 30), (30, 55), (55, 72), (72, 96)]
+    assert p["pattern_suffix"] == ".{add|dom}.chr{1..4}.{bin|id}"
+    q = engine.plan(golden_dir / "dense", mode="D", loco=False)
+    assert q["dense"] and q["items"] == [("dom", 0, 50)] and q["pattern_suffix"] == ".dom.{bin|id}"
+
+
+def test_fam_delimiter_detection_and_errors(tmp_path):
+    payload = plink_io.encode_matrix(np.zeros((3, 2)))
+    plink_io.write_plink(tmp_path / "t", payload, [("f b", "i1"), ("f a", "i2"), ("f a", "i0")], ["1", "1"], fam_delim="\t")
+    p = engine.plan(tmp_path / "t")  # tab-delimited: FID may contain a space (parser.cpp:105-116)
+    assert p["raw_to_out"].tolist() == [2, 1, 0]
+    (tmp_path / "bad.fam").write_text("onlyonefield\n")
+    (tmp_path / "bad.bim").write_text("1\ts\t0\t1\tA\tG\n")
+    (tmp_path / "bad.bed").write_bytes(bytes([0x6C, 0x1B, 0x01, 0]))
+    with pytest.raises(engine.EngineError) as e:
+        engine.plan(tmp_path / "bad")
+    assert "1: failed to parse FID and IID (missing delimiter)" in e.value.message
+    (tmp_path / "bad.fam").write_text("f\ti\t0\t0\t1\t-9\n")
+    (tmp_path / "bad.bim").write_text("1\ts\t0\t1\tA\n")
+    with pytest.raises(engine.EngineError) as e:
+        engine.plan(tmp_path / "bad")
+    assert "1: has 5 columns, expected 6" in e.value.message  # bim_loader.cpp:69-74
+    with pytest.raises(engine.EngineError) as e:
+        engine.plan(tmp_path / "missing")
+    assert "file not found" in e.value.message  # bed_path.cpp:33-37
+
+
+def test_bed_validation_errors_precede_any_gpu_work(tmp_path):
+    # reference tests/test_bed_pipe.cpp:154-257: bad magic, truncated file -> FileFormatException
+    payload = plink_io.encode_matrix(np.zeros((8, 5)))
+    plink_io.write_plink(tmp_path / "ok", payload, [("F", f"s{i}") for i in range(8)], ["1"] * 5)
+    raw = (tmp_path / "ok.bed").read_bytes()
+    for name, content, msg in (("magic", bytes([0x6C, 0x1B, 0x00]) + raw[3:], "invalid BED magic number"),
+                               ("trunc", raw[:-3], "bed file truncated. Expected 13 bytes, got 10"),
+                               ("short", raw[:3], "bed file too short")):
+        for ext in ("bim", "fam"):
+            shutil.copy(tmp_path / f"ok.{ext}", tmp_path / f"{name}.{ext}")
+        (tmp_path / f"{name}.bed").write_bytes(content)
+        with pytest.raises(engine.EngineError) as e:
+            engine.grm_run(tmp_path / name, tmp_path / "out")
+        assert e.value.message.startswith("FileFormatException") and msg in e.value.message
+    (tmp_path / "nobim.bed").write_bytes(raw)
+    shutil.copy(tmp_path / "ok.fam", tmp_path / "nobim.fam")
+    with pytest.raises(engine.EngineError) as e:
+        engine.grm_run(tmp_path / "nobim", tmp_path / "out")
+    assert "nobim.bim: not found" in e.value.message
+
+
+def test_engine_fails_loudly_without_gpu(golden_dir, tmp_path):
+    if g.device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(engine.EngineError) as e:
+        engine.grm_run(golden_dir / "tiny", tmp_path / "o")
+    assert "no CPU fallback" in e.value.message
+    r = subprocess.run([str(engine.CLI_PATH), "grm", "-b", str(golden_dir / "tiny"), "-o", str(tmp_path / "o")], capture_output=True, text=True)
+    assert r.returncode == 1 and "no CPU fallback" in r.stderr  # apps/main.cpp:73-98: log the error, exit code 1
+
+
+# ------------------------------------------------------------------------------------------------ end to end (GPU)
+def assert_bin_close(path, ref_path, n, ulps=1):
+    got, ref = plink_io.read_bin(path, n), plink_io.read_bin(ref_path, n)
+    assert np.array_equal(np.isnan(got), np.isnan(ref))
+    m = ~np.isnan(ref)
+    assert np.all(np.abs(got[m] - ref[m]) <= ulps * np.spacing(np.abs(ref[m])) + 1e-30), path
+
+
+@pytest.mark.gpu
+def test_engine_files_match_reference_outputs(golden_dir, tmp_path):
+    n = 36
+    engine.grm_run(golden_dir / "tiny", tmp_path / "SH", method="SH", mode="A", chunk_size=25, precision=g.PREC_FP64)
+    assert_bin_close(tmp_path / "SH.add.bin", golden_dir / "tiny_SH.add.bin", n)
+    assert (tmp_path / "SH.add.id").read_bytes() == (golden_dir / "tiny_SH.add.id").read_bytes()
+    engine.grm_run(golden_dir / "tiny", tmp_path / "OSH", method="OSH", mode="AD", precision=g.PREC_FP64)  # one decode, two SYRKs
+    for k in ("add", "dom"):
+        assert_bin_close(tmp_path / f"OSH.{k}.bin", golden_dir / f"tiny_OSH.{k}.bin", n)
+        assert (tmp_path / f"OSH.{k}.id").read_bytes() == (golden_dir / f"tiny_OSH.{k}.id").read_bytes()
+    engine.grm_run(golden_dir / "dense", tmp_path / "dSH", method=1, mode="A", precision=g.PREC_FP64)  # dense (identity) projection
+    assert_bin_close(tmp_path / "dSH.add.bin", golden_dir / "dense_SH.add.bin", 40)
+
+
+@pytest.mark.gpu
+def test_engine_loco_one_pass_matches_reference_two_invocations(golden_dir, tmp_path):
+    n = 36
+    engine.grm_run(golden_dir / "tiny", tmp_path / "OCH", method="OCH", mode="AD", loco=True, chunk_size=7, precision=g.PREC_FP64, write_whole=True)
+    names = sorted(p.name for p in tmp_path.iterdir())
+    expect = sorted(f"OCH.{k}{c}.{e}" for k in ("add", "dom") for c in ("", ".chr1", ".chr2", ".chrX", ".chr7") for e in ("bin", "id"))
+    assert names == expect
+    for k in ("add", "dom"):
+        for c in ("1", "2", "X", "7"):
+            assert_bin_close(tmp_path / f"OCH.{k}.chr{c}.bin", golden_dir / f"tiny_OCH.{k}.chr{c}.bin", n)
+        assert_bin_close(tmp_path / f"OCH.{k}.bin", golden_dir / f"tiny_OCH.{k}.bin", n, ulps=4)  # whole = sum of 4 partials
+    # without --with-whole the file set is exactly the reference's (no whole-genome files)
+    out2 = tmp_path / "ref_like"
+    out2.mkdir()
+    engine.grm_run(golden_dir / "tiny", out2 / "g", method="OCH", mode="A", loco=True, precision=g.PREC_FP64)
+    assert sorted(p.name for p in out2.iterdir()) == sorted(f"g.add.chr{c}.{e}" for c in ("1", "2", "X", "7") for e in ("bin", "id"))
+
+
+@pytest.mark.gpu
+def test_cli_is_a_drop_in(golden_dir, tmp_path):
+    r = subprocess.run([str(engine.CLI_PATH), "grm", "-b", str(golden_dir / "tiny"), "--gm", "SH", "--add", "-c", "25", "--precision", "fp64",
+                        "-o", str(tmp_path / "cli")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "Samples    : 36 samples" in r.stdout and "Pattern     : " + str(tmp_path / "cli") + ".add.{bin|id}" in r.stdout
+    assert (tmp_path / "cli.log").exists()
+    assert_bin_close(tmp_path / "cli.add.bin", golden_dir / "tiny_SH.add.bin", 36)
+    # default flags: OSH, additive, fp16 operands -> within the 16-bit tolerance of the reference file (normalised)
+    r = subprocess.run([str(engine.CLI_PATH), "grm", "-b", str(golden_dir / "tiny"), "-o", str(tmp_path / "d")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    got, ref = plink_io.read_bin(tmp_path / "d.add.bin", 36).astype(np.float64), plink_io.read_bin(golden_dir / "tiny_OSH.add.bin", 36).astype(np.float64)
+    diag = np.cumsum(np.arange(1, 37)) - 1
+    assert np.max(np.abs(got / (got[diag].sum() / 36) - ref / (ref[diag].sum() / 36))) < 5e-3  # m = 96 only
