@@ -189,8 +189,9 @@ def gpu_arm(args):
     bpv = (n + 3) // 4
     prec = {"fp16": g.PREC_FP16, "bf16": g.PREC_BF16, "fp64": g.PREC_FP64}[args.precision]
     # SNP shard of this rank (contiguous, cut on 64-SNP boundaries)
-    cuts = [min(m, ((m * r // world) + 63) // 64 * 64) for r in range(world)] + [m]
-    s0, s1 = cuts[rank], cuts[rank + 1]
+    from gelex_b200.sharding import snp_shards
+
+    s0, s1 = snp_shards(m, world)[rank]
     ms = s1 - s0
     d_bed = torch.empty(ms * bpv, dtype=torch.uint8, device="cuda")
     for s in range(0, ms, 32768):

@@ -1,0 +1,49 @@
+"""Multi-GPU partition rules of the GRM path, shared by bench.py, the tests and mirrored by the C++ host
+(gelex_b200/csrc/host/grm_engine.cpp: run_multi_gpu).  Pure integer logic, no device code.
+
+  SNP-shard   contiguous SNP ranges cut on 64-SNP (one UMMA K block) boundaries; every rank holds a partial GRM over all
+              tiles; one sum-reduce of the FP32 accumulators finishes the matrix.
+  LOCO-shard  whole chromosome runs dealt to ranks by LPT on their SNP counts: each partial is produced by exactly one
+              rank and needs no reduce.
+  tile-shard  (n >= ~100k) 8x8-tile super-tiles of the lower triangle dealt by LPT; every rank streams all SNPs but owns
+              disjoint output tiles; no collective on the output (ggrm_config_t.tile_rank / tile_world).
+"""
+from __future__ import annotations
+
+
+def snp_shards(m: int, world: int, align: int = 64):
+    """[(begin, end)] per rank: contiguous, disjoint, covering [0, m), interior cuts multiples of `align`."""
+    cuts = [min(m, ((m * r // world) + align - 1) // align * align) for r in range(world)] + [m]
+    return [(cuts[r], max(cuts[r], cuts[r + 1])) for r in range(world)]
+
+
+def lpt_assign(costs, world: int):
+    """Longest-processing-time-first: returns owner[i] for each cost; ties resolved like the C++ host (stable sort, first least-loaded rank)."""
+    order = sorted(range(len(costs)), key=lambda i: -costs[i])
+    load = [0] * world
+    owner = [0] * len(costs)
+    for i in order:
+        r = min(range(world), key=lambda k: load[k])
+        owner[i] = r
+        load[r] += costs[i]
+    return owner
+
+
+def chromosome_shards(groups, world: int):
+    """groups: [(begin, end)] chromosome runs -> per-rank ascending lists of group indices."""
+    owner = lpt_assign([e - b for b, e in groups], world)
+    return [[g for g in range(len(groups)) if owner[g] == r] for r in range(world)]
+
+
+def supertile_owners(n: int, world: int, tile: int = 256, st: int = 8):
+    """Owner rank of each (si, sj<=si) super-tile, in row-major super-tile order — the rule ggrm_create applies."""
+    t = (n + tile - 1) // tile
+    nst = (t + st - 1) // st
+    supers, costs = [], []
+    for si in range(nst):
+        for sj in range(si + 1):
+            c = sum(1 for i in range(si * st, min(t, (si + 1) * st)) for j in range(sj * st, min(t, (sj + 1) * st)) if j <= i)
+            supers.append((si, sj))
+            costs.append(c)
+    owner = lpt_assign(costs, world) if world > 1 else [0] * len(costs)
+    return supers, costs, owner

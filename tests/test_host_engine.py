@@ -118,6 +118,27 @@ def test_engine_loco_one_pass_matches_reference_two_invocations(golden_dir, tmp_
 
 
 @pytest.mark.gpu
+def test_engine_multi_gpu_matches_single_gpu(tmp_path):
+    if g.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    n, m = 1500, 5000
+    payload = g.synth_bed_host(n, 0, m, 17, 0.01)
+    bounds = [round(m * i / 5) for i in range(6)]
+    chroms = [str(c + 1) for c in range(5) for _ in range(bounds[c + 1] - bounds[c])]
+    plink_io.write_plink(tmp_path / "d", payload, [("F", f"s{i:05d}") for i in range(n)], chroms)
+    # SNP-sharded whole-genome matrix: partial GRMs summed over NVLink peer memory (ggrm_reduce_peer)
+    engine.grm_run(tmp_path / "d", tmp_path / "g1", method="SH", precision=g.PREC_FP64, n_gpus=1)
+    engine.grm_run(tmp_path / "d", tmp_path / "g2", method="SH", precision=g.PREC_FP64, n_gpus=2)
+    assert_bin_close(tmp_path / "g2.add.bin", tmp_path / "g1.add.bin", n, ulps=2)
+    # LOCO: chromosome runs dealt to GPUs, whole = cross-GPU sum of per-GPU wholes
+    engine.grm_run(tmp_path / "d", tmp_path / "l1", method="OCH", mode="AD", loco=True, precision=g.PREC_FP64, n_gpus=1, write_whole=True)
+    engine.grm_run(tmp_path / "d", tmp_path / "l2", method="OCH", mode="AD", loco=True, precision=g.PREC_FP64, n_gpus=2, write_whole=True)
+    for k in ("add", "dom"):
+        for c in ("", ".chr1", ".chr2", ".chr3", ".chr4", ".chr5"):
+            assert_bin_close(tmp_path / f"l2.{k}{c}.bin", tmp_path / f"l1.{k}{c}.bin", n, ulps=2 if c == "" else 0)
+
+
+@pytest.mark.gpu
 def test_cli_is_a_drop_in(golden_dir, tmp_path):
     r = subprocess.run([str(engine.CLI_PATH), "grm", "-b", str(golden_dir / "tiny"), "--gm", "SH", "--add", "-c", "25", "--precision", "fp64",
                         "-o", str(tmp_path / "cli")], capture_output=True, text=True)

@@ -1,0 +1,72 @@
+"""Multi-GPU partition logic on CPU: integer rules, and a world_size-2 gloo run that shards SNPs across two processes,
+accumulates each shard with the CPU oracle and sum-reduces — the plumbing bench.py uses with NCCL on real GPUs."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from gelex_b200 import sharding
+
+
+def test_snp_shards_cover_and_align():
+    for m, w in ((500000, 8), (500000, 3), (131, 4), (63, 2), (64, 2), (1, 8), (600000, 7)):
+        sh = sharding.snp_shards(m, w)
+        assert len(sh) == w and sh[0][0] == 0 and sh[-1][1] == m
+        for (b0, e0), (b1, e1) in zip(sh, sh[1:]):
+            assert e0 == b1 and b0 <= e0
+        assert all(b % 64 == 0 or b == m for b, _ in sh)
+
+
+def test_chromosome_lpt_is_balanced_and_complete():
+    sizes = [41000, 40000, 33000, 31000, 30000, 28000, 26000, 24000, 20000, 22000, 22000, 22000, 16000, 15000, 14000, 15000, 14000, 13000, 10000, 11000, 6500, 6500]
+    groups, s = [], 0
+    for z in sizes:
+        groups.append((s, s + z))
+        s += z
+    for w in (2, 4, 8):
+        sh = sharding.chromosome_shards(groups, w)
+        assert sorted(g for r in sh for g in r) == list(range(22))
+        loads = [sum(sizes[g] for g in r) for r in sh]
+        assert max(loads) <= 1.12 * sum(sizes) / w
+        assert all(r == sorted(r) for r in sh)
+
+
+def test_supertile_ownership_partitions_the_triangle():
+    for n, w in ((200000, 8), (50000, 4), (2300, 3)):
+        supers, costs, owner = sharding.supertile_owners(n, w)
+        t = (n + 255) // 256
+        assert sum(costs) == t * (t + 1) // 2
+        loads = [sum(c for c, o in zip(costs, owner) if o == r) for r in range(w)]
+        assert max(loads) - min(loads) <= 64
+
+
+def _worker(rank, world, port, tmpdir):
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__))))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import gelex_b200 as g
+    import oracle_lib as o
+
+    n, m = 96, 400
+    bed = g.synth_bed_host(n, 0, m, 5, 0.02)
+    b, e = sharding.snp_shards(m, world)[rank]
+    part, _, _ = o.grm_compute(bed, n, 1, 0, ranges=[(b, e)] if e > b else [(0, 1)])
+    if e <= b:
+        part = np.zeros_like(part)
+    t = torch.from_numpy(np.ascontiguousarray(part))
+    dist.reduce(t, dst=0, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        whole, _, _ = o.grm_compute(bed, n, 1, 0)
+        np.save(os.path.join(tmpdir, "err.npy"), np.array([np.max(np.abs(t.numpy() - whole))]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_snp_shard_reduce_world2_gloo(tmp_path):
+    port = 29500 + (os.getpid() % 2000)
+    mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    assert np.load(tmp_path / "err.npy")[0] < 1e-9
