@@ -234,6 +234,8 @@ def gpu_arm(args):
         if rank == 0:
             acc.lib.ggrm_fetch(acc.h, g.KIND_ADD, g.GROUP_WHOLE, 0, n, ctypes.c_void_p(h_out.data_ptr()), None)
 
+    wall_checks = []
+
     def timed(fn, steps, warmup):
         for _ in range(warmup):
             fn()
@@ -248,7 +250,10 @@ def gpu_arm(args):
         barrier()
         w1 = time.time()
         after = acc.timers()
-        dt = w1 - w0
+        # device clock: ev0/ev1 sit on torch's (idle) stream; every step ends host-synchronously (ggrm_finish / fetch / NCCL
+        # + synchronize), so the two records bracket exactly the device work of the K steps.  Wall time is the cross-check.
+        dt = ev0.elapsed_time(ev1) * 1e-3
+        wall_checks.append((dt, w1 - w0))
         if world > 1:
             t = torch.tensor([dt], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -284,9 +289,10 @@ def gpu_arm(args):
                                    f"({m * bpv / 1e9:.2f} GB), 1 % missing, seed {SEED}",
                        "partition": "single GPU" if world == 1 else f"SNP-sharded over {world} GPUs + NCCL sum-reduce of FP32 partial GRMs",
                        "l2": "inputs (packed BED 6.25 GB, 16-bit operand slabs 0.8 GB, accumulator 5 GB) are larger than the 126 MB L2; no flush needed",
-                       "timing": "barrier + cuda synchronize on both sides, max over ranks; kernel phases by CUDA events on the library's streams",
-                       "chunk_snps": int(os.environ.get("GGRM_CHUNK_SNPS", 8192))},
+                       "timing": "CUDA events around the K steps, barrier + cuda synchronize on both sides, max over ranks; kernel phases by CUDA events on the library's streams",
+                       "chunk_snps": int(os.environ.get("GGRM_CHUNK_SNPS", 16384))},
             "device_pass_ms_per_step": tm["pass_ms"] / args.steps,
+            "wall_clock_ms_per_step": wall_checks[0][1] / args.steps * 1e3,
             "phases_ms_per_step": {k: tm[k] / args.steps for k in ("h2d_ms", "prep_ms", "expand_ms", "syrk_ms")},
             "gpu_launches": int(tm["kernel_launches"]),
             "clocks": clocks,

@@ -78,8 +78,8 @@ void build_ownership_and_items(Handle& h) {
         }
     }
     h.slot_of_host.assign(static_cast<size_t>(T * (T + 1) / 2), -1);
-    std::vector<TcItem> tc;
-    std::vector<F64Item> f64;
+    struct Owned { int64_t I, J; int32_t slot; };
+    std::vector<Owned> owned;
     int32_t slot = 0;
     for (const Super& s : supers) {
         if (s.owner != h.cfg.tile_rank) continue;
@@ -87,22 +87,40 @@ void build_ownership_and_items(Handle& h) {
             for (int64_t J = s.sj * ST; J < std::min(T, (s.sj + 1) * ST); ++J) {
                 if (J > I) continue;
                 h.slot_of_host[static_cast<size_t>(I * (I + 1) / 2 + J)] = slot;
-                const int64_t off = static_cast<int64_t>(slot) * 65536;
-                if (h.fp64) {
-                    for (int bi = 0; bi < 4; ++bi)
-                        for (int bj = 0; bj < 4; ++bj) {
-                            if (I == J && bj > bi) continue;
-                            f64.push_back({static_cast<int32_t>(I * 256 + bi * 64), static_cast<int32_t>(J * 256 + bj * 64),
-                                           off + static_cast<int64_t>(bi) * 64 * 256 + bj * 64});
-                        }
-                } else if (h.tc_mode == 2) {
-                    tc.push_back({static_cast<int32_t>(I * 256), static_cast<int32_t>(J * 256), off});
-                } else {
-                    tc.push_back({static_cast<int32_t>(I * 256), static_cast<int32_t>(J * 256), off});
-                    tc.push_back({static_cast<int32_t>(I * 256 + 128), static_cast<int32_t>(J * 256), off + kHalfTileElems});
-                }
+                owned.push_back({I, J, slot});
                 ++slot;
             }
+        }
+    }
+    // Scheduling order (storage slots stay in super-tile order).  strip_h > 0: horizontal strips of strip_h tile rows,
+    // walked column by column (snake: odd strips right-to-left), so that the ~sm_count/2 tiles in flight at any time
+    // share strip_h row panels and ~sm_count/(2*strip_h) column panels, and consecutive waves keep the row panels in L2.
+    if (h.strip_h > 0 && !h.fp64) {
+        const int64_t sh = h.strip_h;
+        std::stable_sort(owned.begin(), owned.end(), [sh](const Owned& a, const Owned& b) {
+            const int64_t sa = a.I / sh, sb = b.I / sh;
+            if (sa != sb) return sa < sb;
+            if (a.J != b.J) return (sa & 1) ? a.J > b.J : a.J < b.J;
+            return a.I < b.I;
+        });
+    }
+    std::vector<TcItem> tc;
+    std::vector<F64Item> f64;
+    for (const Owned& o : owned) {
+        const int64_t I = o.I, J = o.J;
+        const int64_t off = static_cast<int64_t>(o.slot) * 65536;
+        if (h.fp64) {
+            for (int bi = 0; bi < 4; ++bi)
+                for (int bj = 0; bj < 4; ++bj) {
+                    if (I == J && bj > bi) continue;
+                    f64.push_back({static_cast<int32_t>(I * 256 + bi * 64), static_cast<int32_t>(J * 256 + bj * 64),
+                                   off + static_cast<int64_t>(bi) * 64 * 256 + bj * 64});
+                }
+        } else if (h.tc_mode == 2) {
+            tc.push_back({static_cast<int32_t>(I * 256), static_cast<int32_t>(J * 256), off});
+        } else {
+            tc.push_back({static_cast<int32_t>(I * 256), static_cast<int32_t>(J * 256), off});
+            tc.push_back({static_cast<int32_t>(I * 256 + 128), static_cast<int32_t>(J * 256), off + kHalfTileElems});
         }
     }
     h.owned_tiles = slot;
@@ -148,21 +166,26 @@ static void free_handle(Handle* h) {
     fr(h->d_slot_of); fr(h->d_items_tc); fr(h->d_items_f64); fr(h->d_out_to_raw);
     fr(h->d_raw[0]); fr(h->d_raw[1]); fr(h->d_dense); fr(h->d_counts); fr(h->d_freq);
     for (int k = 0; k < 2; ++k) {
-        fr(h->d_tab16[k]); fr(h->d_tab64[k]); fr(h->d_Z[k]); fr(h->whole[k]);
+        fr(h->d_tab16[k]); fr(h->d_tab64[k]); fr(h->d_Z[k][0]); fr(h->d_Z[k][1]); fr(h->whole[k]);
         for (void* p : h->pool[k]) fr(p);
     }
-    fr(h->d_stage); fr(h->d_trace); fr(h->d_fault);
+    fr(h->d_stage); fr(h->d_trace); fr(h->d_fault); fr(h->d_wave_ctr);
     for (int i = 0; i < Handle::kRingSlots; ++i) {
         if (h->ring[i] != nullptr) cudaFreeHost(h->ring[i]);
         if (h->ring_free[i] != nullptr) cudaEventDestroy(h->ring_free[i]);
     }
-    for (int i = 0; i < 2; ++i) if (h->raw_free[i] != nullptr) cudaEventDestroy(h->raw_free[i]);
+    for (int i = 0; i < 2; ++i) {
+        if (h->raw_free[i] != nullptr) cudaEventDestroy(h->raw_free[i]);
+        if (h->prep_done[i] != nullptr) cudaEventDestroy(h->prep_done[i]);
+        if (h->z_free[i] != nullptr) cudaEventDestroy(h->z_free[i]);
+    }
     if (h->h2d_done != nullptr) cudaEventDestroy(h->h2d_done);
     if (h->pass_begin != nullptr) cudaEventDestroy(h->pass_begin);
     if (h->pass_end != nullptr) cudaEventDestroy(h->pass_end);
     for (auto& g : h->groups) if (g.done != nullptr) cudaEventDestroy(g.done);
     for (auto& t : h->timers) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
     if (h->s_copy != nullptr) cudaStreamDestroy(h->s_copy);
+    if (h->s_prep != nullptr) cudaStreamDestroy(h->s_prep);
     if (h->s_comp != nullptr) cudaStreamDestroy(h->s_comp);
     if (h->s_fetch != nullptr) cudaStreamDestroy(h->s_fetch);
     delete h;
@@ -197,8 +220,9 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
     h->fp64 = cfg->precision == GGRM_PREC_FP64;
     h->elem_bytes = h->fp64 ? 8 : 4;
     h->tc_mode = 2;  // CTA-pair UMMA 256x256x16 (measured ~20 % faster than the single-CTA 128x256 form)
-    if (const char* e = std::getenv("GGRM_CACHE_HINTS")) h->cache_hints = std::atoi(e) & 3;
+    if (const char* e = std::getenv("GGRM_CACHE_HINTS")) h->cache_hints = std::atoi(e) & 7;
     if (const char* e = std::getenv("GGRM_TC_MODE")) h->tc_mode = std::atoi(e) == 1 ? 1 : 2;
+    if (const char* e = std::getenv("GGRM_STRIP_H")) h->strip_h = std::max(0, std::atoi(e));
 
     // groups
     h->groups.resize(static_cast<size_t>(cfg->n_groups));
@@ -229,9 +253,20 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
 
     GGRM_CUDA(cudaStreamCreateWithFlags(&h->s_copy, cudaStreamNonBlocking));
     GGRM_CUDA(cudaStreamCreateWithFlags(&h->s_comp, cudaStreamNonBlocking));
+    {
+        // K1-K3 blocks are small; a higher priority lets them slot in beside the persistent SYRK CTAs as soon as they are ready
+        int prio_lo = 0, prio_hi = 0;
+        GGRM_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+        GGRM_CUDA(cudaStreamCreateWithPriority(&h->s_prep, cudaStreamNonBlocking, prio_hi));
+    }
+    if (const char* e = std::getenv("GGRM_OVERLAP_PREP")) h->overlap_prep = std::atoi(e) != 0;
     GGRM_CUDA(cudaStreamCreateWithFlags(&h->s_fetch, cudaStreamNonBlocking));
     GGRM_CUDA(cudaEventCreateWithFlags(&h->h2d_done, cudaEventDisableTiming));
-    for (int i = 0; i < 2; ++i) GGRM_CUDA(cudaEventCreateWithFlags(&h->raw_free[i], cudaEventDisableTiming));
+    for (int i = 0; i < 2; ++i) {
+        GGRM_CUDA(cudaEventCreateWithFlags(&h->raw_free[i], cudaEventDisableTiming));
+        GGRM_CUDA(cudaEventCreateWithFlags(&h->prep_done[i], cudaEventDisableTiming));
+        GGRM_CUDA(cudaEventCreateWithFlags(&h->z_free[i], cudaEventDisableTiming));
+    }
 
     build_ownership_and_items(*h);
 
@@ -242,7 +277,7 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
     const int64_t accum_bytes = std::max<int64_t>(h->accum_elems, 4) * h->elem_bytes;
     const bool want_whole = cfg->n_groups > 1 && cfg->keep_whole;
     const int64_t z_elem = h->fp64 ? 8 : 2;
-    const int64_t per_snp = h->n_pad * z_elem * kinds + 2 * h->bpv_raw + h->bpv_pad + 128;
+    const int64_t per_snp = 2 * h->n_pad * z_elem * kinds + 2 * h->bpv_raw + h->bpv_pad + 128;
     int64_t avail = static_cast<int64_t>(free_b) - (int64_t{1} << 30) - (want_whole ? accum_bytes * kinds : 0);
     const int64_t min_chunk = std::min<int64_t>(round_up(cfg->m_total, 64), 4096) * per_snp;
     int pool_n = 1;
@@ -256,10 +291,13 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
     if (cfg->chunk_snps > 0) {
         k_cap = round_up(cfg->chunk_snps, 64);
     } else {
-        // Measured on B200 (profiles/r01_chunk_sweep.md): K slabs of ~8k SNPs keep concurrently running CTAs close
-        // together in K, so Z panels are re-read from L2 instead of HBM; the per-slab accumulator read-modify-write
-        // is hidden behind the next tile's MMAs.  Longer slabs lose L2 reuse, shorter ones expose the epilogue.
-        int64_t target = 8192;
+        // Measured on B200 (profiles/r01_summary.md, "wave pacing"): with the producers paced wave by wave the Z traffic per
+        // SNP no longer depends on the slab length (tiles in flight share panels through L2 whatever K is), while the FP32
+        // accumulator read-modify-write (2 x 5 GB at n = 50k) is paid once per slab - so long slabs win on speed (+1.5 % from
+        // 16k to 32k).  Accuracy caps it: the tensor core truncates when it adds into the FP32 TMEM accumulator, which biases
+        // large positive sums (the diagonal, ~1 per SNP) by about -5.4e-9 x K relative: 16k SNPs keeps that under 1e-4
+        // (tools/precision_probe.py; the bias is uniform, so G/(trace/n) is unaffected either way).
+        int64_t target = 16384;
         if (const char* e = std::getenv("GGRM_CHUNK_SNPS")) target = std::max<int64_t>(64, std::atoll(e));
         const int64_t budget = std::min<int64_t>(int64_t{24} << 30, avail / 2);
         k_cap = std::max<int64_t>(1024, std::min<int64_t>(target, budget / per_snp / 1024 * 1024));
@@ -282,12 +320,12 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
             GGRM_CUDA(cudaMalloc(&h->whole[kind], static_cast<size_t>(accum_bytes)));
             GGRM_CUDA(cudaMemsetAsync(h->whole[kind], 0, static_cast<size_t>(accum_bytes), h->s_comp));
         }
-        GGRM_CUDA(cudaMalloc(&h->d_Z[kind], static_cast<size_t>(h->n_pad * k_cap * z_elem)));
+        for (int b = 0; b < 2; ++b) GGRM_CUDA(cudaMalloc(&h->d_Z[kind][b], static_cast<size_t>(h->n_pad * k_cap * z_elem)));
         if (h->fp64) {
             GGRM_CUDA(cudaMalloc(&h->d_tab64[kind], static_cast<size_t>(k_cap) * sizeof(SnpTable)));
         } else {
             GGRM_CUDA(cudaMalloc(&h->d_tab16[kind], static_cast<size_t>(k_cap) * sizeof(uint2)));
-            encode_tensor_map(&h->tmap[kind], h->d_Z[kind], k_cap, h->n_pad, cfg->precision == GGRM_PREC_FP16);
+            for (int b = 0; b < 2; ++b) encode_tensor_map(&h->tmap[kind][b], h->d_Z[kind][b], k_cap, h->n_pad, cfg->precision == GGRM_PREC_FP16);
         }
     }
     for (int i = 0; i < 2; ++i) GGRM_CUDA(cudaMalloc(&h->d_raw[i], static_cast<size_t>(k_cap * h->bpv_raw)));
@@ -299,12 +337,20 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
         GGRM_CUDA(cudaMemsetAsync(h->d_freq, 0, static_cast<size_t>(cfg->m_total) * sizeof(double), h->s_comp));
     }
     GGRM_CUDA(cudaMalloc(&h->d_trace, sizeof(double)));
+    GGRM_CUDA(cudaMalloc(&h->d_wave_ctr, sizeof(unsigned long long)));
+    GGRM_CUDA(cudaMemsetAsync(h->d_wave_ctr, 0, sizeof(unsigned long long), h->s_comp));
+    if (const char* e = std::getenv("GGRM_WAVE_SYNC")) h->sync_every = std::max(0, std::atoi(e));
     GGRM_CUDA(cudaMalloc(&h->d_fault, sizeof(int)));
     GGRM_CUDA(cudaMemsetAsync(h->d_fault, 0, sizeof(int), h->s_comp));
 
     if (!h->fp64) {
         GGRM_CUDA(cudaFuncSetAttribute(syrk_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcConfig<1>::kSmemBytes));
         GGRM_CUDA(cudaFuncSetAttribute(syrk_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcConfig<2>::kSmemBytes));
+        // Ask for the largest smem carve-out (228 KB): the ring needs ~194 KB, and the ~30 KB left over is what lets K1-K3
+        // blocks of the next slab (<= 6.6 KB each) become resident beside the persistent SYRK CTA.  With the default
+        // (smallest fitting carve-out, 196 KB) they were starved until the SYRK kernel exited.
+        GGRM_CUDA(cudaFuncSetAttribute(syrk_tc_kernel<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        GGRM_CUDA(cudaFuncSetAttribute(syrk_tc_kernel<2>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     }
     GGRM_CUDA(cudaStreamSynchronize(h->s_comp));
 }

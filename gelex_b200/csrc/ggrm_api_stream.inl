@@ -14,6 +14,20 @@ static size_t phase_begin(Handle& h, cudaStream_t s, int phase) {
 static void phase_end(Handle& h, cudaStream_t s, size_t idx) { GGRM_CUDA(cudaEventRecord(h.timers[idx].b, s)); }
 
 static void collect_timers(Handle& h) {
+    if (std::getenv("GGRM_DEBUG_GAPS") != nullptr) {  // developer aid: idle time on s_comp between consecutive SYRK phases
+        const Timer* prev = nullptr;
+        double gap_sum = 0;
+        int n = 0;
+        for (auto& t : h.timers) {
+            if (t.phase != 3) continue;
+            if (prev != nullptr) {
+                float ms = 0.f;
+                if (cudaEventElapsedTime(&ms, prev->b, t.a) == cudaSuccess) { gap_sum += ms; ++n; }
+            }
+            prev = &t;
+        }
+        std::fprintf(stderr, "[ggrm] SYRK gaps: %d gaps, total %.3f ms\n", n, gap_sum);
+    }
     for (auto& t : h.timers) {
         float ms = 0.f;
         if (cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess) h.phase_ms[t.phase] += ms;
@@ -75,19 +89,20 @@ static void complete_group(Handle& h, int g) {
     gs.complete = true;
 }
 
-static void launch_syrk(Handle& h, int kind, int g, int64_t c) {
+static void launch_syrk(Handle& h, int kind, int g, int64_t c, int zb) {
     const GroupState& gs = h.groups[g];
     void* accum = h.pool[kind][gs.buffer[kind]];
     if (h.fp64) {
         if (h.num_items_f64 == 0) return;
         const int grid = std::min(h.num_items_f64, h.sm_count * 6);
-        syrk_f64_kernel<<<grid, 128, 0, h.s_comp>>>(static_cast<const double*>(h.d_Z[kind]), h.k_cap, c, static_cast<double*>(accum),
+        syrk_f64_kernel<<<grid, 128, 0, h.s_comp>>>(static_cast<const double*>(h.d_Z[kind][zb]), h.k_cap, c, static_cast<double*>(accum),
                                                     h.d_items_f64, h.num_items_f64, 1);
         GGRM_CUDA(cudaGetLastError());
     } else {
         if (h.num_items_tc == 0) return;
         const int nkb = static_cast<int>(round_up(c, 64) / 64);
         const uint32_t fmt = h.cfg.precision == GGRM_PREC_FP16 ? 0u : 1u;
+        int grid_ctas = 0, n_clusters = 1;
         if (h.tc_mode == 2) {
             const int clusters = std::min(h.num_items_tc, h.sm_count / 2);
             cudaLaunchConfig_t lc{};
@@ -102,32 +117,47 @@ static void launch_syrk(Handle& h, int kind, int g, int64_t c) {
             attr[0].val.clusterDim.z = 1;
             lc.attrs = attr;
             lc.numAttrs = 1;
-            GGRM_CUDA(cudaLaunchKernelEx(&lc, syrk_tc_kernel<2>, h.tmap[kind], static_cast<float*>(accum),
-                                         static_cast<const TcItem*>(h.d_items_tc), h.num_items_tc, nkb, 0, 1, fmt, h.cache_hints, h.d_fault));
+            GGRM_CUDA(cudaLaunchKernelEx(&lc, syrk_tc_kernel<2>, h.tmap[kind][zb], static_cast<float*>(accum),
+                                         static_cast<const TcItem*>(h.d_items_tc), h.num_items_tc, nkb, 0, 1, fmt, h.cache_hints, h.d_fault,
+                                         h.d_wave_ctr, h.wave_base, h.sync_every));
+            grid_ctas = 2 * clusters;
+            n_clusters = clusters;
         } else {
             const int grid = std::min(h.num_items_tc, h.sm_count);
-            syrk_tc_kernel<1><<<grid, 256, TcConfig<1>::kSmemBytes, h.s_comp>>>(h.tmap[kind], static_cast<float*>(accum), h.d_items_tc,
-                                                                                h.num_items_tc, nkb, 0, 1, fmt, h.cache_hints, h.d_fault);
+            syrk_tc_kernel<1><<<grid, 256, TcConfig<1>::kSmemBytes, h.s_comp>>>(h.tmap[kind][zb], static_cast<float*>(accum), h.d_items_tc,
+                                                                                h.num_items_tc, nkb, 0, 1, fmt, h.cache_hints, h.d_fault,
+                                                                                h.d_wave_ctr, h.wave_base, h.sync_every);
             GGRM_CUDA(cudaGetLastError());
+            grid_ctas = grid;
+            n_clusters = grid;
+        }
+        if (h.sync_every > 0) {  // every CTA checks in once per pacing point (see syrk_tc.cuh)
+            const int waves = (h.num_items_tc + n_clusters - 1) / n_clusters;
+            if (waves > 1) h.wave_base += static_cast<unsigned long long>((waves - 1) / h.sync_every) * static_cast<unsigned long long>(grid_ctas);
         }
     }
     ++h.syrk_launches;
     ++h.kernel_launches;
 }
 
+
 static void flush_chunk(Handle& h) {
     if (h.cur_count == 0) return;
     const int b = h.cur_buf;
+    const int zb = h.z_buf;
     const int64_t c = h.cur_count;
     const int g = h.cur_group;
+    // K1-K3 of this slab run on s_prep (beside the previous slab's SYRK, which owns s_comp); serial mode uses s_comp for both
+    cudaStream_t sp = h.overlap_prep ? h.s_prep : h.s_comp;
     GGRM_CUDA(cudaEventRecord(h.h2d_done, h.s_copy));
-    GGRM_CUDA(cudaStreamWaitEvent(h.s_comp, h.h2d_done, 0));
+    GGRM_CUDA(cudaStreamWaitEvent(sp, h.h2d_done, 0));
+    GGRM_CUDA(cudaStreamWaitEvent(sp, h.z_free[zb], 0));  // the SYRKs of two slabs ago have finished reading Z[.][zb]
     start_group(h, g);
 
-    size_t ti = phase_begin(h, h.s_comp, 1);
-    repack_kernel<<<static_cast<unsigned>(c), 256, 0, h.s_comp>>>(h.d_raw[b], h.bpv_raw, h.d_dense, h.bpv_pad, h.n_out, h.d_out_to_raw, c);
+    size_t ti = phase_begin(h, sp, 1);
+    repack_kernel<<<static_cast<unsigned>(c), 256, 0, sp>>>(h.d_raw[b], h.bpv_raw, h.d_dense, h.bpv_pad, h.n_out, h.d_out_to_raw, c);
     GGRM_CUDA(cudaGetLastError());
-    GGRM_CUDA(cudaEventRecord(h.raw_free[b], h.s_comp));
+    GGRM_CUDA(cudaEventRecord(h.raw_free[b], sp));
     StatsOut so{};
     so.counts = h.d_counts;
     so.freq = h.d_freq;
@@ -135,28 +165,35 @@ static void flush_chunk(Handle& h) {
         so.tab16[kind] = h.d_tab16[kind];
         so.tab64[kind] = h.d_tab64[kind];
     }
-    count_stats_kernel<<<static_cast<unsigned>((c + 7) / 8), 256, 0, h.s_comp>>>(
+    count_stats_kernel<<<static_cast<unsigned>((c + 7) / 8), 256, 0, sp>>>(
         h.d_dense, h.bpv_pad, h.n_out, h.n_pad, c, h.cfg.method, h.cfg.all_missing_policy,
         h.cfg.precision == GGRM_PREC_FP16 ? 1 : 0, so, h.cur_first_snp);
     GGRM_CUDA(cudaGetLastError());
-    phase_end(h, h.s_comp, ti);
+    phase_end(h, sp, ti);
     h.kernel_launches += 2;
 
     const dim3 egrid(static_cast<unsigned>((c + 63) / 64), static_cast<unsigned>(h.bpv_pad / 64));
+    ti = phase_begin(h, sp, 2);
     for (int kind = 0; kind < 2; ++kind) {
-        if (h.d_Z[kind] == nullptr) continue;
-        ti = phase_begin(h, h.s_comp, 2);
+        if (h.d_Z[kind][zb] == nullptr) continue;
         if (h.fp64)
-            expand64_kernel<<<egrid, 256, 0, h.s_comp>>>(h.d_dense, h.bpv_pad, h.d_tab64[kind], c, static_cast<double*>(h.d_Z[kind]), h.k_cap);
+            expand64_kernel<<<egrid, 256, 0, sp>>>(h.d_dense, h.bpv_pad, h.d_tab64[kind], c, static_cast<double*>(h.d_Z[kind][zb]), h.k_cap);
         else
-            expand16_kernel<<<egrid, 256, 0, h.s_comp>>>(h.d_dense, h.bpv_pad, h.d_tab16[kind], c, static_cast<uint16_t*>(h.d_Z[kind]), h.k_cap);
+            expand16_kernel<<<egrid, 256, 0, sp>>>(h.d_dense, h.bpv_pad, h.d_tab16[kind], c, static_cast<uint16_t*>(h.d_Z[kind][zb]), h.k_cap);
         GGRM_CUDA(cudaGetLastError());
-        phase_end(h, h.s_comp, ti);
         ++h.kernel_launches;
-        ti = phase_begin(h, h.s_comp, 3);
-        launch_syrk(h, kind, g, c);
-        phase_end(h, h.s_comp, ti);
     }
+    phase_end(h, sp, ti);
+    GGRM_CUDA(cudaEventRecord(h.prep_done[zb], sp));
+    GGRM_CUDA(cudaStreamWaitEvent(h.s_comp, h.prep_done[zb], 0));
+    ti = phase_begin(h, h.s_comp, 3);
+    for (int kind = 0; kind < 2; ++kind) {
+        if (h.d_Z[kind][zb] == nullptr) continue;
+        launch_syrk(h, kind, g, c, zb);
+    }
+    phase_end(h, h.s_comp, ti);
+    GGRM_CUDA(cudaEventRecord(h.z_free[zb], h.s_comp));
+    h.z_buf ^= 1;
     h.cur_buf ^= 1;
     h.cur_count = 0;
     h.cur_first_snp = -1;
@@ -255,7 +292,9 @@ static void finish_impl(Handle& h) {
         h.finished = true;
         if (h.pass_open) GGRM_CUDA(cudaEventRecord(h.pass_end, h.s_comp));
     }
-    const cudaError_t e1 = cudaStreamSynchronize(h.s_copy);
+    cudaError_t e1 = cudaStreamSynchronize(h.s_copy);
+    const cudaError_t e1b = cudaStreamSynchronize(h.s_prep);
+    if (e1 == cudaSuccess) e1 = e1b;
     const cudaError_t e2 = cudaStreamSynchronize(h.s_comp);
     if (e1 != cudaSuccess || e2 != cudaSuccess) {
         int where = 0;
@@ -276,6 +315,7 @@ static void finish_impl(Handle& h) {
 // group restarts, statistics are overwritten, buffers and work lists are reused.  Timers keep accumulating.
 static void reset_impl(Handle& h) {
     GGRM_CUDA(cudaStreamSynchronize(h.s_copy));
+    GGRM_CUDA(cudaStreamSynchronize(h.s_prep));
     GGRM_CUDA(cudaStreamSynchronize(h.s_comp));
     GGRM_CUDA(cudaStreamSynchronize(h.s_fetch));
     for (auto& g : h.groups) {
@@ -332,6 +372,7 @@ extern "C" int ggrm_snp_stats(ggrm_t* hh, int64_t snp_begin, int64_t snp_count, 
     if (snp_begin < 0 || snp_count < 0 || snp_begin + snp_count > h->cfg.m_total)
         throw CudaError{GGRM_ERR_COLUMN_RANGE, "invalid SNP range for ggrm_snp_stats"};
     if (!h->finished) flush_chunk(*h);
+    GGRM_CUDA(cudaStreamSynchronize(h->s_prep));
     GGRM_CUDA(cudaStreamSynchronize(h->s_comp));
     std::vector<int4> c(static_cast<size_t>(snp_count));
     GGRM_CUDA(cudaMemcpy(c.data(), h->d_counts + snp_begin, c.size() * sizeof(int4), cudaMemcpyDeviceToHost));

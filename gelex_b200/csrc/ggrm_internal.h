@@ -53,6 +53,7 @@ struct Handle {
     bool fp64 = false;
     int elem_bytes = 4;
     int cache_hints = 3;                  // bit 0: Z panels evict_last, bit 1: accumulator stream evict_first (GGRM_CACHE_HINTS)
+    int strip_h = 8;                      // SYRK item order: 0 = by 8x8 super-tile, h>0 = strips of h tile rows (GGRM_STRIP_H)
     int tc_mode = 1;                      // 1 = single-CTA UMMA 128x256, 2 = CTA-pair UMMA 256x256
     // ownership and work lists
     std::vector<int32_t> slot_of_host;    // [ntiles_side*(ntiles_side+1)/2] -> slot or -1
@@ -65,7 +66,7 @@ struct Handle {
     // projection
     int32_t* d_out_to_raw = nullptr;      // nullptr = identity
     // streams
-    cudaStream_t s_copy = nullptr, s_comp = nullptr, s_fetch = nullptr;
+    cudaStream_t s_copy = nullptr, s_prep = nullptr, s_comp = nullptr, s_fetch = nullptr;  // H2D | K1-K3 | K4,K6 | K5+D2H
     // chunk buffers
     uint8_t* d_raw[2] = {nullptr, nullptr};
     cudaEvent_t raw_free[2] = {nullptr, nullptr};
@@ -75,8 +76,13 @@ struct Handle {
     double* d_freq = nullptr;
     uint2* d_tab16[2] = {nullptr, nullptr};
     SnpTable* d_tab64[2] = {nullptr, nullptr};
-    void* d_Z[2] = {nullptr, nullptr};
-    CUtensorMap tmap[2];
+    // operand slabs are double buffered so that K1-K3 of slab i+1 (s_prep) overlap the SYRK of slab i (s_comp)
+    void* d_Z[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};   // [kind][z_buf]
+    CUtensorMap tmap[2][2];
+    cudaEvent_t prep_done[2] = {nullptr, nullptr};                 // recorded on s_prep after the expands into Z[.][b]
+    cudaEvent_t z_free[2] = {nullptr, nullptr};                    // recorded on s_comp after the SYRKs that read Z[.][b]
+    int z_buf = 0;
+    bool overlap_prep = true;                                      // GGRM_OVERLAP_PREP=0: run K1-K3 on s_comp (serial)
     // pinned staging ring (pageable callers)
     static constexpr int kRingSlots = 4;
     uint8_t* ring[kRingSlots] = {nullptr, nullptr, nullptr, nullptr};
@@ -99,6 +105,9 @@ struct Handle {
     void* d_stage = nullptr;
     int64_t stage_bytes = 0;
     double* d_trace = nullptr;
+    unsigned long long* d_wave_ctr = nullptr;  // SYRK wave pacing counter (monotonic; wave_base = value all earlier launches add up to)
+    unsigned long long wave_base = 0;
+    int sync_every = 1;                   // waves between pacing points, 0 = off (GGRM_WAVE_SYNC)
     int* d_fault = nullptr;               // mbarrier-timeout location written by a stuck SYRK before it traps
     // timers
     std::vector<Timer> timers;

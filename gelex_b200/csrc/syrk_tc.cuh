@@ -47,7 +47,8 @@ struct TcConfig {
 template <int kCtaGroup>
 __global__ void __launch_bounds__(256, 1)
 syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ accum, const TcItem* __restrict__ items,
-               int num_items, int num_k_blocks, int k_block0, int accumulate, uint32_t ab_format, int cache_hints, int* fault_flag) {
+               int num_items, int num_k_blocks, int k_block0, int accumulate, uint32_t ab_format, int cache_hints, int* fault_flag,
+               unsigned long long* wave_ctr, unsigned long long wave_base, int sync_every) {
     using Cfg = TcConfig<kCtaGroup>;
     constexpr int kStages = Cfg::kStages;
     extern __shared__ uint8_t smem_raw[];
@@ -91,8 +92,26 @@ syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ a
         // ===================================================== TMA producer
         uint32_t stage = 0, phase = 0;
         // cache_hints bit 0: keep Z panels in L2 (evict_last) — they are re-read by every CTA of the super-tile
+        // cache_hints bit 2: only the row (A) panels are kept; column (B) panels change every wave and are marked evict_first
         const uint64_t z_hint = (cache_hints & 1) ? ptx::kCacheEvictLast : ptx::kCacheEvictNormal;
-        for (int it = cluster_id; it < num_items; it += num_clusters) {
+        const uint64_t b_hint = (cache_hints & 4) ? ptx::kCacheEvictFirst : z_hint;
+        // Wave pacing (sync_every > 0): every sync_every-th wave, each CTA's producer checks in on a global counter and
+        // waits (bounded) until all CTAs have — the tiles in flight then stay within a few K blocks of each other, so a Z
+        // panel needed by several CTAs is fetched from HBM once and hit in L2 by the rest.  Purely a timing hint: on
+        // timeout the producer just proceeds.
+        int wave = 0;
+        unsigned long long syncs_done = 0;
+        for (int it = cluster_id; it < num_items; it += num_clusters, ++wave) {
+            if (sync_every > 0 && wave > 0 && wave % sync_every == 0) {
+                ++syncs_done;
+                if (ptx::elect_one()) {
+                    atomicAdd(wave_ctr, 1ull);
+                    const unsigned long long target = wave_base + syncs_done * gridDim.x;
+                    const uint64_t t0 = ptx::global_timer_ns();
+                    while (ptx::ld_relaxed_gpu_u64(wave_ctr) < target && ptx::global_timer_ns() - t0 < 200000ull) __nanosleep(100);
+                }
+                __syncwarp();
+            }
             const TcItem item = items[it];
             const int32_t a_row = item.a_row0 + static_cast<int32_t>(cta_rank) * 128;
             const int32_t b_row = item.b_row0 + static_cast<int32_t>(cta_rank) * Cfg::kBRows;
@@ -105,19 +124,24 @@ syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ a
                     if constexpr (kCtaGroup == 1) {
                         ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
                         ptx::tma_load_2d(&tmap_z, &full_bar[stage], sa, kc, a_row, z_hint);
-                        ptx::tma_load_2d(&tmap_z, &full_bar[stage], sb, kc, b_row, z_hint);
-                        ptx::tma_load_2d(&tmap_z, &full_bar[stage], sb + kTcABytes, kc, b_row + 128, z_hint);
+                        ptx::tma_load_2d(&tmap_z, &full_bar[stage], sb, kc, b_row, b_hint);
+                        ptx::tma_load_2d(&tmap_z, &full_bar[stage], sb + kTcABytes, kc, b_row + 128, b_hint);
                     } else {
                         // both CTAs' bytes are counted on the leader's barrier
                         if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
                         else ptx::mbar_arrive_cluster(&full_bar[stage], 0);
                         ptx::tma_load_2d_pair(&tmap_z, &full_bar[stage], sa, kc, a_row, z_hint);
-                        ptx::tma_load_2d_pair(&tmap_z, &full_bar[stage], sb, kc, b_row, z_hint);
+                        ptx::tma_load_2d_pair(&tmap_z, &full_bar[stage], sb, kc, b_row, b_hint);
                     }
                 }
                 __syncwarp();
                 if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
+        }
+        if (sync_every > 0) {  // check in for the sync points of waves this CTA had no tile in
+            const int waves = (num_items + num_clusters - 1) / num_clusters;
+            const unsigned long long total = waves > 1 ? static_cast<unsigned long long>((waves - 1) / sync_every) : 0ull;
+            if (total > syncs_done && ptx::elect_one()) atomicAdd(wave_ctr, total - syncs_done);
         }
     } else if (warp == 1 && leader) {
         // ===================================================== MMA issuer (leader CTA only)
