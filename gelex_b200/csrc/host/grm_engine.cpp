@@ -315,6 +315,7 @@ void run_multi_gpu(const RunContext& rc, double* pass_ms, double* syrk_ms) {
         ~Cleanup() { for (ggrm_t* h : *hs) if (h != nullptr) ggrm_destroy(h); }
     } cleanup{&handles};
     const bool want_whole = !rc.loco || rc.cfg->write_whole;
+    std::vector<std::vector<int>> mine(ng);  // outlives the worker threads (joined below), which read it by reference
     if (rc.loco) {
         // chromosome runs are dealt to GPUs by LPT on their SNP counts: every partial is produced by ONE GPU, no reduce
         std::vector<size_t> order(rc.groups.size());
@@ -322,7 +323,6 @@ void run_multi_gpu(const RunContext& rc, double* pass_ms, double* syrk_ms) {
         std::stable_sort(order.begin(), order.end(), [&](size_t a, size_t b) {
             return rc.groups[a].end - rc.groups[a].begin > rc.groups[b].end - rc.groups[b].begin;
         });
-        std::vector<std::vector<int>> mine(ng);
         std::vector<int64_t> load(ng, 0);
         for (size_t g : order) {
             const size_t r = static_cast<size_t>(std::min_element(load.begin(), load.end()) - load.begin());
