@@ -202,8 +202,7 @@ def gpu_arm(args):
     torch.cuda.synchronize()
     acc = g.Accumulator(n, m, method=METHOD, precision=prec, device=local)
     out_elems = g.tri(n)
-    h_out = torch.empty(out_elems, dtype=torch.float32, pin_memory=True) if rank == 0 else None
-    dptr, n_el, eb = None, 0, 4
+    h_full = torch.empty(out_elems, dtype=torch.float32, pin_memory=True) if (world > 1 and args.reduce == "nccl" and rank == 0) else None
 
     def barrier():
         torch.cuda.synchronize()
@@ -211,14 +210,47 @@ def gpu_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # ---- N > 1: SNP-sharded partial GRMs, then a reduce-scatter by row slices over NVLink peer memory: rank r sums ITS rows
+    # from every peer's accumulator with one kernel of plain P2P loads (ggrm_reduce_peer on CUDA-IPC mapped pointers), and in
+    # the e2e leg fetches only those rows, so the D2H of the 5 GB result is spread over all ranks' PCIe links.
+    from gelex_b200.sharding import row_slices
+
+    r0, r1 = row_slices(n, world)[rank]
+    my_out_elems = g.tri(r1) - g.tri(r0)
+    h_out = torch.empty(max(1, my_out_elems), dtype=torch.float32, pin_memory=True)
+    peers = []
+    state = {"ready": False, "slice": (0, 0)}
+
+    def setup_peers():
+        # accumulator addresses are stable across ggrm_reset; export once after the first finished pass
+        mine = acc.ipc_export(g.KIND_ADD, g.GROUP_WHOLE)
+        handles = [None] * world
+        dist.all_gather_object(handles, mine)
+        for r in range(world):
+            if r != rank:
+                peers.append(g.ipc_open(handles[r], device=local))
+        state["slice"] = acc.row_slice(r0, r1)
+        state["ready"] = True
+
     def reduce_partials():
-        nonlocal dptr, n_el, eb
         if world == 1:
             return
-        dptr, n_el, eb = acc.accum_buffer(g.KIND_ADD, g.GROUP_WHOLE)
-        t = torch.as_tensor(DevPtr(dptr, n_el, "<f4" if eb == 4 else "<f8"), device="cuda")
-        dist.reduce(t, dst=0, op=dist.ReduceOp.SUM)
-        torch.cuda.synchronize()
+        if args.reduce == "nccl":
+            dptr, n_el, eb = acc.accum_buffer(g.KIND_ADD, g.GROUP_WHOLE)
+            t = torch.as_tensor(DevPtr(dptr, n_el, "<f4" if eb == 4 else "<f8"), device="cuda")
+            dist.reduce(t, dst=0, op=dist.ReduceOp.SUM)
+            torch.cuda.synchronize()
+            return
+        if not state["ready"]:
+            setup_peers()
+        dist.barrier()                      # every rank's partial is complete (ggrm_finish returned everywhere)
+        eb_, ee_ = state["slice"]
+        t_r = time.time()
+        if ee_ > eb_:
+            acc.reduce_peer(g.KIND_ADD, g.GROUP_WHOLE, peers, eb_, ee_)   # synchronous: returns when this rank's rows are final
+        state["reduce_s"] = state.get("reduce_s", 0.0) + (time.time() - t_r)
+        state["reduce_n"] = state.get("reduce_n", 0) + 1
+        dist.barrier()                      # peers have finished reading this rank's buffer before the next pass zeroes it
 
     def step_resident():
         acc.reset()
@@ -226,13 +258,19 @@ def gpu_arm(args):
         acc.finish()
         reduce_partials()
 
+    def fetch_mine():
+        if world > 1 and args.reduce == "nccl":
+            if rank == 0:
+                acc.lib.ggrm_fetch(acc.h, g.KIND_ADD, g.GROUP_WHOLE, 0, n, ctypes.c_void_p(h_full.data_ptr()), None)
+        elif r1 > r0:
+            acc.lib.ggrm_fetch(acc.h, g.KIND_ADD, g.GROUP_WHOLE, r0, r1 - r0, ctypes.c_void_p(h_out.data_ptr()), None)
+
     def step_e2e():
         acc.reset()
         acc.push_ptr(h_bed.data_ptr(), s0, ms)
         acc.finish()
         reduce_partials()
-        if rank == 0:
-            acc.lib.ggrm_fetch(acc.h, g.KIND_ADD, g.GROUP_WHOLE, 0, n, ctypes.c_void_p(h_out.data_ptr()), None)
+        fetch_mine()
 
     wall_checks = []
 
@@ -287,7 +325,8 @@ def gpu_arm(args):
             "data": "synthetic",
             "config": {"workload": f"configs[1]: Yang additive GRM (StandardizeHWE+Add), {n} samples x {m} SNPs, packed 2-bit PLINK BED "
                                    f"({m * bpv / 1e9:.2f} GB), 1 % missing, seed {SEED}",
-                       "partition": "single GPU" if world == 1 else f"SNP-sharded over {world} GPUs + NCCL sum-reduce of FP32 partial GRMs",
+                       "partition": "single GPU" if world == 1 else (f"SNP-sharded over {world} GPUs + NCCL sum-reduce of FP32 partial GRMs to rank 0" if args.reduce == "nccl" else
+                                      f"SNP-sharded over {world} GPUs + reduce-scatter of FP32 partial GRMs by 2048-row slices over NVLink peer memory (CUDA IPC, P2P loads); each rank fetches its own rows"),
                        "l2": "inputs (packed BED 6.25 GB, 16-bit operand slabs 0.8 GB, accumulator 5 GB) are larger than the 126 MB L2; no flush needed",
                        "timing": "CUDA events around the K steps, barrier + cuda synchronize on both sides, max over ranks; kernel phases by CUDA events on the library's streams",
                        "chunk_snps": int(os.environ.get("GGRM_CHUNK_SNPS", 16384))},
@@ -295,16 +334,20 @@ def gpu_arm(args):
             "wall_clock_ms_per_step": wall_checks[0][1] / args.steps * 1e3,
             "phases_ms_per_step": {k: tm[k] / args.steps for k in ("h2d_ms", "prep_ms", "expand_ms", "syrk_ms")},
             "gpu_launches": int(tm["kernel_launches"]),
+            "reduce_ms_per_call_rank0": (state.get("reduce_s", 0.0) / max(1, state.get("reduce_n", 0)) * 1e3) if world > 1 else None,
+            "reduce_bytes_over_nvlink_rank0": int((state["slice"][1] - state["slice"][0]) * 4 * (world - 1)) if world > 1 and args.reduce == "peer" else None,
             "clocks": clocks,
             "e2e": {"value": fl / (dt_e / args.steps) / 1e12, "unit": "TFLOP/s", "wall_s_per_grm": dt_e / args.steps,
                     "h2d_bytes_per_step": int(ms * bpv), "d2h_bytes_per_step": int(out_elems * 4),
-                    "path": "ggrm_reset -> ggrm_push(pinned host BED) -> ggrm_finish -> ggrm_fetch(float32 lower triangle to host)",
+                    "path": "ggrm_reset -> ggrm_push(pinned host BED) -> ggrm_finish -> [N>1: ggrm_reduce_peer on own row slice] -> ggrm_fetch(float32 lower-triangle rows to host; N>1: each rank its own rows, bytes summed over ranks)",
                     "phases_ms_per_step": {k: tm_e[k] / args.steps for k in ("h2d_ms", "prep_ms", "expand_ms", "syrk_ms", "fetch_ms")}},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": sustained, "unit": "TFLOP/s", "frac": achieved / sustained,
                          "traffic": traffic, "kernel": "syrk_tc_kernel<2> (tcgen05 cta_group::2, UMMA 256x256x16)",
                          "flops_per_launch": fl_rank / launches, "avg_launch_ms": syrk_ms / launches, "launches_per_step": launches,
                          "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({how}); burst peak {burst} -> frac {achieved / burst:.3f}"},
         }
+    for p_ in peers:
+        g.ipc_close(p_, device=local)
     acc.close()
     if rank == 0 and world == 1 and not args.no_cpu:
         cb, _, _ = cpu_leg(1, 0, args.cpu_budget)
@@ -332,6 +375,9 @@ def reference_arm(args):
 
 
 def main():
+    # keep stdout to the one JSON line: NCCL's "NCCL version ..." banner goes to stdout at NCCL_DEBUG=VERSION
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+        os.environ["NCCL_DEBUG"] = "WARN"
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
@@ -340,6 +386,7 @@ def main():
     ap.add_argument("--precision", default=os.environ.get("GGRM_BENCH_PRECISION", "fp16"), choices=["fp16", "bf16", "fp64"])
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work per reference step")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--reduce", default="peer", choices=["peer", "nccl"], help="N>1: partial-GRM reduction (peer = own P2P kernel, nccl = dist.reduce)")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)

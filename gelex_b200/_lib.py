@@ -67,6 +67,7 @@ EXPORTS = [
     "ggrm_fetch", "ggrm_fetch_f64", "ggrm_release_group", "ggrm_accum_buffer", "ggrm_reduce_peer",
     "ggrm_fetch_normalized", "ggrm_fetch_loco", "ggrm_get_timers", "ggrm_decode_chunk", "ggrm_standardise_chunk",
     "ggrm_synth_bed_host", "ggrm_synth_bed_device", "ggrm_device_count", "ggrm_version", "ggrm_enable_peer_access",
+    "ggrm_ipc_export", "ggrm_ipc_open", "ggrm_ipc_close", "ggrm_row_slice",
 ]
 
 _lib = None
@@ -99,6 +100,10 @@ def load() -> C.CDLL:
     lib.ggrm_fetch_normalized.argtypes = [vp, C.c_int, C.c_int, i64, i64, vp]
     lib.ggrm_fetch_loco.argtypes = [vp, C.c_int, C.c_int, i64, i64, vp]
     lib.ggrm_get_timers.argtypes = [vp, C.POINTER(dbl)]
+    lib.ggrm_ipc_export.argtypes = [vp, C.c_int, C.c_int, vp]
+    lib.ggrm_ipc_open.argtypes = [C.c_int, vp, C.POINTER(vp)]
+    lib.ggrm_ipc_close.argtypes = [C.c_int, vp]
+    lib.ggrm_row_slice.argtypes = [vp, i64, i64, C.POINTER(i64), C.POINTER(i64)]
     lib.ggrm_decode_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, vp]
     lib.ggrm_standardise_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, C.c_int, C.c_int, C.c_int, vp, vp]
     lib.ggrm_synth_bed_host.argtypes = [vp, i64, i64, i64, u64, dbl]
@@ -241,6 +246,16 @@ class Accumulator:
         arr = (C.c_void_p * max(1, len(peer_ptrs)))(*peer_ptrs)
         self._check(self.lib.ggrm_reduce_peer(self.h, kind, group, arr, len(peer_ptrs), slice_begin, slice_end))
 
+    def ipc_export(self, kind=KIND_ADD, group=GROUP_WHOLE) -> bytes:
+        buf = C.create_string_buffer(64)
+        self._check(self.lib.ggrm_ipc_export(self.h, kind, group, buf))
+        return buf.raw
+
+    def row_slice(self, row_begin: int, row_end: int):
+        b, e = C.c_int64(), C.c_int64()
+        self._check(self.lib.ggrm_row_slice(self.h, row_begin, row_end, C.byref(b), C.byref(e)))
+        return b.value, e.value
+
     def timers(self):
         out = (C.c_double * 8)()
         self._check(self.lib.ggrm_get_timers(self.h, out))
@@ -291,6 +306,22 @@ def synth_bed_host(n, snp_begin, snp_count, seed, missing_rate=0.01):
 def synth_bed_device(dev_ptr, n, snp_begin, snp_count, seed, missing_rate=0.01, device=0):
     lib = load()
     st = lib.ggrm_synth_bed_device(device, C.c_void_p(dev_ptr), n, snp_begin, snp_count, seed, missing_rate)
+    if st != 0:
+        raise GrmError(st, lib.ggrm_last_error(None).decode())
+
+
+def ipc_open(handle: bytes, device=0) -> int:
+    lib = load()
+    p = C.c_void_p()
+    st = lib.ggrm_ipc_open(device, C.c_char_p(handle), C.byref(p))
+    if st != 0:
+        raise GrmError(st, lib.ggrm_last_error(None).decode())
+    return p.value
+
+
+def ipc_close(ptr: int, device=0):
+    lib = load()
+    st = lib.ggrm_ipc_close(device, C.c_void_p(ptr))
     if st != 0:
         raise GrmError(st, lib.ggrm_last_error(None).decode())
 

@@ -198,12 +198,42 @@ extern "C" int ggrm_reduce_peer(ggrm_t* hh, int kind, int group, const void* con
     for (int i = 0; i < n_peers; ++i) pp.p[i] = peers[i];
     const int64_t len = slice_end - slice_begin;
     if (len > 0 && n_peers > 0) {
-        const int blocks = static_cast<int>(std::min<int64_t>((len / 4 + 255) / 256, h->sm_count * 8));
+        const int64_t span = 256 * (16 / h->elem_bytes) * 4;  // elements one block covers per sweep (see reduce_peers_kernel)
+        const int blocks = static_cast<int>(std::min<int64_t>((len + span - 1) / span, h->sm_count * 8));
         if (h->fp64) reduce_peers_kernel<double><<<blocks, 256, 0, h->s_comp>>>(static_cast<double*>(mine), pp, n_peers, slice_begin, slice_end);
         else reduce_peers_kernel<float><<<blocks, 256, 0, h->s_comp>>>(static_cast<float*>(mine), pp, n_peers, slice_begin, slice_end);
         GGRM_CUDA(cudaGetLastError());
         ++h->kernel_launches;
     }
     GGRM_CUDA(cudaStreamSynchronize(h->s_comp));
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_ipc_export(ggrm_t* hh, int kind, int group, void* handle64) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ggrm.h documents a 64-byte handle");
+    if (handle64 == nullptr) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "null handle buffer"};
+    cudaEvent_t ev = nullptr;
+    void* p = resolve_accum(*h, kind, group, &ev);
+    cudaIpcMemHandle_t ipc;
+    GGRM_CUDA(cudaIpcGetMemHandle(&ipc, p));
+    std::memcpy(handle64, &ipc, sizeof(ipc));
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_row_slice(ggrm_t* hh, int64_t row_begin, int64_t row_end, int64_t* elem_begin, int64_t* elem_end) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    if (h->cfg.tile_world != 1) throw CudaError{GGRM_ERR_INVALID_OPERATION, "row slices are defined for handles that own every tile"};
+    if (row_begin < 0 || row_end < row_begin || row_end > h->n_out || ((row_begin % 2048) != 0 && row_begin != h->n_out) ||
+        ((row_end % 2048) != 0 && row_end != h->n_out))
+        throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "row slice must be cut on multiples of 2048 rows (one super-row of tiles)"};
+    // storage slots are numbered super-row by super-row (build_ownership_and_items), so the tiles of tile rows [A, B) are the
+    // contiguous slots [A(A+1)/2, B(B+1)/2)
+    const int64_t A = row_begin == h->n_out ? h->ntiles_side : row_begin / kTile;
+    const int64_t B = row_end == h->n_out ? h->ntiles_side : row_end / kTile;
+    if (elem_begin != nullptr) *elem_begin = A * (A + 1) / 2 * 65536;
+    if (elem_end != nullptr) *elem_end = B * (B + 1) / 2 * 65536;
     GGRM_API_END(h)
 }

@@ -104,6 +104,23 @@ extern "C" int ggrm_enable_peer_access(int device, int peer_device) {
     GGRM_STATELESS_END
 }
 
+extern "C" int ggrm_ipc_open(int device, const void* handle64, void** d_ptr) {
+    GGRM_STATELESS_BEGIN
+    if (handle64 == nullptr || d_ptr == nullptr) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "null argument"};
+    check_device(device, nullptr);
+    cudaIpcMemHandle_t ipc;
+    std::memcpy(&ipc, handle64, sizeof(ipc));
+    GGRM_CUDA(cudaIpcOpenMemHandle(d_ptr, ipc, cudaIpcMemLazyEnablePeerAccess));
+    GGRM_STATELESS_END
+}
+
+extern "C" int ggrm_ipc_close(int device, void* d_ptr) {
+    GGRM_STATELESS_BEGIN
+    check_device(device, nullptr);
+    if (d_ptr != nullptr) GGRM_CUDA(cudaIpcCloseMemHandle(d_ptr));
+    GGRM_STATELESS_END
+}
+
 static uint32_t miss_threshold(double missing_rate) {
     if (!(missing_rate > 0.0)) return 0u;
     if (missing_rate >= 1.0) return 1u << 24;

@@ -77,35 +77,57 @@ struct PeerPtrs {
     const void* p[kMaxPeers];
 };
 
+// 16-byte streaming load (peer memory over NVLink, or local HBM that will not be re-read): bypass L1.
+__device__ __forceinline__ uint4 ld_stream_u4(const void* p) {
+    uint4 v;
+    asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+
+// mine[begin, end) += sum_p peers[p][begin, end).  NVLink P2P loads have microseconds of latency, so every thread keeps
+// kChunks x (1 + n_peers) independent 16-byte loads in flight (all issued before the first add); a block sweeps
+// kChunks x 4 KB contiguous pieces so each warp-level request is a full 512-byte line group.
 template <typename T>
 __global__ void __launch_bounds__(256) reduce_peers_kernel(T* __restrict__ mine, PeerPtrs peers, int n_peers,
                                                            int64_t begin, int64_t end) {
-    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x * 4;
-    for (int64_t i = begin + (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 4; i < end; i += stride) {
-        if constexpr (sizeof(T) == 4) {
-            float4 a = *reinterpret_cast<const float4*>(mine + i);
+    constexpr int kVec = 16 / static_cast<int>(sizeof(T));   // elements per 16-byte access
+    constexpr int kChunks = 4;
+    const int64_t block_span = static_cast<int64_t>(blockDim.x) * kVec * kChunks;
+    for (int64_t base = begin + static_cast<int64_t>(blockIdx.x) * block_span; base < end; base += static_cast<int64_t>(gridDim.x) * block_span) {
+        uint4 a[kChunks];
+        uint4 b[kChunks];
+        int64_t idx[kChunks];
 #pragma unroll
-            for (int p = 0; p < kMaxPeers; ++p) {
-                if (p < n_peers) {
-                    const float4 b = *reinterpret_cast<const float4*>(static_cast<const T*>(peers.p[p]) + i);
-                    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+        for (int u = 0; u < kChunks; ++u) {
+            idx[u] = base + (static_cast<int64_t>(u) * blockDim.x + threadIdx.x) * kVec;
+            if (idx[u] < end) a[u] = ld_stream_u4(mine + idx[u]);
+        }
+        for (int p = 0; p < n_peers; ++p) {
+            const T* src = static_cast<const T*>(peers.p[p]);
+#pragma unroll
+            for (int u = 0; u < kChunks; ++u)
+                if (idx[u] < end) b[u] = ld_stream_u4(src + idx[u]);
+#pragma unroll
+            for (int u = 0; u < kChunks; ++u) {
+                if (idx[u] >= end) continue;
+                if constexpr (sizeof(T) == 4) {
+                    a[u].x = __float_as_uint(__uint_as_float(a[u].x) + __uint_as_float(b[u].x));
+                    a[u].y = __float_as_uint(__uint_as_float(a[u].y) + __uint_as_float(b[u].y));
+                    a[u].z = __float_as_uint(__uint_as_float(a[u].z) + __uint_as_float(b[u].z));
+                    a[u].w = __float_as_uint(__uint_as_float(a[u].w) + __uint_as_float(b[u].w));
+                } else {
+                    const double a0 = __hiloint2double(static_cast<int>(a[u].y), static_cast<int>(a[u].x)) +
+                                      __hiloint2double(static_cast<int>(b[u].y), static_cast<int>(b[u].x));
+                    const double a1 = __hiloint2double(static_cast<int>(a[u].w), static_cast<int>(a[u].z)) +
+                                      __hiloint2double(static_cast<int>(b[u].w), static_cast<int>(b[u].z));
+                    a[u].x = static_cast<uint32_t>(__double2loint(a0)); a[u].y = static_cast<uint32_t>(__double2hiint(a0));
+                    a[u].z = static_cast<uint32_t>(__double2loint(a1)); a[u].w = static_cast<uint32_t>(__double2hiint(a1));
                 }
-            }
-            *reinterpret_cast<float4*>(mine + i) = a;
-        } else {
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                double2 a = *reinterpret_cast<const double2*>(mine + i + 2 * h);
-#pragma unroll
-                for (int p = 0; p < kMaxPeers; ++p) {
-                    if (p < n_peers) {
-                        const double2 b = *reinterpret_cast<const double2*>(static_cast<const T*>(peers.p[p]) + i + 2 * h);
-                        a.x += b.x; a.y += b.y;
-                    }
-                }
-                *reinterpret_cast<double2*>(mine + i + 2 * h) = a;
             }
         }
+#pragma unroll
+        for (int u = 0; u < kChunks; ++u)
+            if (idx[u] < end) *reinterpret_cast<uint4*>(mine + idx[u]) = a[u];
     }
 }
 

@@ -5,6 +5,9 @@
               tiles; one sum-reduce of the FP32 accumulators finishes the matrix.
   LOCO-shard  whole chromosome runs dealt to ranks by LPT on their SNP counts: each partial is produced by exactly one
               rank and needs no reduce.
+  row-slice   after an SNP-shard pass: GRM rows are cut on 2048-row (8-tile super-row) boundaries into `world` ranges of
+              about equal triangle area; rank r sum-reduces ITS rows from every peer's partial (reduce-scatter over NVLink
+              peer memory) and fetches / writes only those rows, so read-out and file writing scale with the GPU count.
   tile-shard  (n >= ~100k) 8x8-tile super-tiles of the lower triangle dealt by LPT; every rank streams all SNPs but owns
               disjoint output tiles; no collective on the output (ggrm_config_t.tile_rank / tile_world).
 """
@@ -47,3 +50,23 @@ def supertile_owners(n: int, world: int, tile: int = 256, st: int = 8):
             costs.append(c)
     owner = lpt_assign(costs, world) if world > 1 else [0] * len(costs)
     return supers, costs, owner
+
+
+def row_slices(n: int, world: int, tile: int = 256, st: int = 8):
+    """[(row_begin, row_end)] per rank: contiguous, covering [0, n), cuts on multiples of tile*st rows, balanced on the
+    number of lower-triangle tiles (rank r gets the super-rows whose cumulative tile count first reaches (r+1)/world)."""
+    t = (n + tile - 1) // tile
+    nsr = (t + st - 1) // st
+    cum = [min(t, (s + 1) * st) * (min(t, (s + 1) * st) + 1) // 2 for s in range(nsr)]  # tiles in super-rows 0..s
+    total = cum[-1]
+    cuts, s = [0], 0
+    for r in range(1, world):
+        target = total * r / world
+        while s < nsr and cum[s] < target:
+            s += 1
+        # cut after super-row s or before it, whichever lands closer to the target
+        lo = cum[s - 1] if s > 0 else 0
+        c = s + 1 if s < nsr and (cum[s] - target) <= (target - lo) else s
+        cuts.append(max(cuts[-1], min(nsr, c)))
+    cuts.append(nsr)
+    return [(min(n, cuts[r] * tile * st), min(n, cuts[r + 1] * tile * st)) for r in range(world)]

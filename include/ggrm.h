@@ -139,6 +139,19 @@ int ggrm_accum_buffer(ggrm_t* h, int kind, int group, void** d_ptr, int64_t* n_e
 int ggrm_reduce_peer(ggrm_t* h, int kind, int group, const void* const* peers, int n_peers, int64_t slice_begin,
                      int64_t slice_end);
 
+/* Multi-PROCESS form of the same (one process per GPU, torch.distributed-style launch): export the accumulator of
+ * (kind, group) as a CUDA IPC handle (64 bytes, cudaIpcMemHandle_t), ship it to the other ranks over any host channel,
+ * open it there (maps the peer's memory over NVLink, enabling peer access lazily) and pass the mapped pointers to
+ * ggrm_reduce_peer.  Row ranges whose tiles are contiguous in the accumulator (whole 8-tile super-rows, 2048 rows) are
+ * given by ggrm_row_slice, so rank r reduces and then fetches/writes only its own rows of the .bin file. */
+int ggrm_ipc_export(ggrm_t* h, int kind, int group, void* handle64);
+int ggrm_ipc_open(int device, const void* handle64, void** d_ptr);
+int ggrm_ipc_close(int device, void* d_ptr);
+/* Element range [*elem_begin, *elem_end) of the tile-packed accumulator that holds every tile of GRM rows
+ * [row_begin, row_end); both must be multiples of 2048 or equal to n_out (tile_world == 1); row_begin == row_end gives an
+ * empty range. */
+int ggrm_row_slice(ggrm_t* h, int64_t row_begin, int64_t row_end, int64_t* elem_begin, int64_t* elem_end);
+
 /* Next-row helpers on data already resident: normalised and leave-one-chromosome-out matrices,
  * G/(trace/n) (grm_loader.cpp:125-165) and (G_whole - G_chr)/(k_whole - k_chr) (loco_grm_loader.cpp:62-76),
  * returned as packed lower rows in FP64. */

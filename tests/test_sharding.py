@@ -70,3 +70,16 @@ def test_snp_shard_reduce_world2_gloo(tmp_path):
     port = 29500 + (os.getpid() % 2000)
     mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     assert np.load(tmp_path / "err.npy")[0] < 1e-9
+
+
+def test_row_slices_cover_align_and_balance():
+    for n in (1000, 4500, 50000, 200000):
+        for w in (1, 2, 3, 4, 8):
+            sl = sharding.row_slices(n, w)
+            assert len(sl) == w and sl[0][0] == 0 and sl[-1][1] == n
+            assert all(sl[r][1] == sl[r + 1][0] for r in range(w - 1))
+            assert all((b % 2048 == 0 or b == n) and (e % 2048 == 0 or e == n) for b, e in sl)
+    areas = [(e * (e + 1) - b * (b + 1)) / 2 for b, e in sharding.row_slices(50000, 8)]
+    assert max(areas) <= 1.25 * sum(areas) / 8   # coarse (25 super-rows over 8 ranks) but bounded
+    areas = [(e * (e + 1) - b * (b + 1)) / 2 for b, e in sharding.row_slices(200000, 8)]
+    assert max(areas) <= 1.10 * sum(areas) / 8
