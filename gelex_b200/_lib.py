@@ -63,11 +63,12 @@ class Config(C.Structure):
 
 
 EXPORTS = [
-    "ggrm_create", "ggrm_destroy", "ggrm_last_error", "ggrm_push", "ggrm_push_device", "ggrm_finish", "ggrm_reset", "ggrm_snp_stats",
+    "ggrm_create", "ggrm_destroy", "ggrm_last_error", "ggrm_push", "ggrm_push_device", "ggrm_finish", "ggrm_finish_async", "ggrm_reset", "ggrm_snp_stats",
     "ggrm_fetch", "ggrm_fetch_f64", "ggrm_release_group", "ggrm_accum_buffer", "ggrm_reduce_peer",
     "ggrm_fetch_normalized", "ggrm_fetch_loco", "ggrm_get_timers", "ggrm_decode_chunk", "ggrm_standardise_chunk",
     "ggrm_synth_bed_host", "ggrm_synth_bed_device", "ggrm_device_count", "ggrm_version", "ggrm_enable_peer_access",
     "ggrm_ipc_export", "ggrm_ipc_open", "ggrm_ipc_close", "ggrm_row_slice",
+    "ggrm_fetch_block", "ggrm_owned_supertiles", "ggrm_host_alloc", "ggrm_host_free",
 ]
 
 _lib = None
@@ -90,6 +91,7 @@ def load() -> C.CDLL:
     lib.ggrm_push.argtypes = [vp, vp, i64, i64, i64]
     lib.ggrm_push_device.argtypes = [vp, vp, i64, i64, i64]
     lib.ggrm_finish.argtypes = [vp]
+    lib.ggrm_finish_async.argtypes = [vp]
     lib.ggrm_reset.argtypes = [vp]
     lib.ggrm_snp_stats.argtypes = [vp, i64, i64, vp, vp, vp, vp, vp]
     lib.ggrm_fetch.argtypes = [vp, C.c_int, C.c_int, i64, i64, vp, C.POINTER(dbl)]
@@ -104,6 +106,10 @@ def load() -> C.CDLL:
     lib.ggrm_ipc_open.argtypes = [C.c_int, vp, C.POINTER(vp)]
     lib.ggrm_ipc_close.argtypes = [C.c_int, vp]
     lib.ggrm_row_slice.argtypes = [vp, i64, i64, C.POINTER(i64), C.POINTER(i64)]
+    lib.ggrm_fetch_block.argtypes = [vp, C.c_int, C.c_int, i64, i64, i64, i64, vp, i64]
+    lib.ggrm_owned_supertiles.argtypes = [vp, C.POINTER(i64), C.POINTER(i64), i64, C.POINTER(i64)]
+    lib.ggrm_host_alloc.argtypes = [i64, C.POINTER(vp)]
+    lib.ggrm_host_free.argtypes = [vp]
     lib.ggrm_decode_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, vp]
     lib.ggrm_standardise_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, C.c_int, C.c_int, C.c_int, vp, vp]
     lib.ggrm_synth_bed_host.argtypes = [vp, i64, i64, i64, u64, dbl]
@@ -203,6 +209,9 @@ class Accumulator:
     def finish(self):
         self._check(self.lib.ggrm_finish(self.h))
 
+    def finish_async(self):
+        self._check(self.lib.ggrm_finish_async(self.h))
+
     def reset(self):
         self._check(self.lib.ggrm_reset(self.h))
 
@@ -255,6 +264,19 @@ class Accumulator:
         b, e = C.c_int64(), C.c_int64()
         self._check(self.lib.ggrm_row_slice(self.h, row_begin, row_end, C.byref(b), C.byref(e)))
         return b.value, e.value
+
+    def fetch_block(self, kind, group, row_begin, row_count, col_begin, col_count):
+        out = np.empty((row_count, col_count), dtype=np.float32)
+        self._check(self.lib.ggrm_fetch_block(self.h, kind, group, row_begin, row_count, col_begin, col_count, _ptr(out), col_count))
+        return out
+
+    def owned_supertiles(self):
+        cnt = C.c_int64()
+        self._check(self.lib.ggrm_owned_supertiles(self.h, None, None, 0, C.byref(cnt)))
+        r = (C.c_int64 * max(1, cnt.value))()
+        c = (C.c_int64 * max(1, cnt.value))()
+        self._check(self.lib.ggrm_owned_supertiles(self.h, r, c, cnt.value, C.byref(cnt)))
+        return [(r[i], c[i]) for i in range(cnt.value)]
 
     def timers(self):
         out = (C.c_double * 8)()

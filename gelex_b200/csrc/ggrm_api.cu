@@ -78,11 +78,14 @@ void build_ownership_and_items(Handle& h) {
         }
     }
     h.slot_of_host.assign(static_cast<size_t>(T * (T + 1) / 2), -1);
+    h.owned_supers.clear();
     struct Owned { int64_t I, J; int32_t slot; };
     std::vector<Owned> owned;
     int32_t slot = 0;
     for (const Super& s : supers) {
         if (s.owner != h.cfg.tile_rank) continue;
+        h.owned_supers.push_back(s.si);
+        h.owned_supers.push_back(s.sj);
         for (int64_t I = s.si * ST; I < std::min(T, (s.si + 1) * ST); ++I) {
             for (int64_t J = s.sj * ST; J < std::min(T, (s.sj + 1) * ST); ++J) {
                 if (J > I) continue;
@@ -103,6 +106,31 @@ void build_ownership_and_items(Handle& h) {
             if (a.J != b.J) return (sa & 1) ? a.J > b.J : a.J < b.J;
             return a.I < b.I;
         });
+    }
+    // Row bands for the final slab (see Handle::band_*): close a band at a strip boundary once it holds its share of tiles.
+    h.band_item_end.clear();
+    h.band_row_end.clear();
+    if (h.strip_h > 0 && !h.fp64 && !owned.empty()) {
+        int nb = 8;
+        if (const char* e = std::getenv("GGRM_FETCH_BANDS")) nb = std::max(1, std::min(32, std::atoi(e)));
+        const int64_t total = static_cast<int64_t>(owned.size());
+        int64_t min_tiles = 2048;  // ~28 waves of 74 CTA pairs per band: the extra tail wave costs ~2 % of the last slab only
+        if (const char* e = std::getenv("GGRM_BAND_MIN_TILES")) min_tiles = std::max<int64_t>(1, std::atoll(e));
+        const int bands = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(nb, total / min_tiles)));
+        const int items_per_tile = h.tc_mode == 2 ? 1 : 2;
+        for (int64_t i = 0; i < total; ++i) {
+            const bool strip_ends = i + 1 == total || owned[static_cast<size_t>(i + 1)].I / h.strip_h != owned[static_cast<size_t>(i)].I / h.strip_h;
+            const int64_t b = static_cast<int64_t>(h.band_item_end.size());
+            if (strip_ends && (i + 1 == total || (b + 1 < bands && i + 1 >= (b + 1) * total / bands))) {
+                h.band_item_end.push_back(static_cast<int>((i + 1) * items_per_tile));
+                h.band_row_end.push_back(i + 1 == total ? h.n_out : std::min<int64_t>(h.n_out, (owned[static_cast<size_t>(i)].I / h.strip_h + 1) * h.strip_h * kTile));
+            }
+        }
+        for (size_t b = h.band_done.size(); b < h.band_item_end.size(); ++b) {
+            cudaEvent_t ev = nullptr;
+            GGRM_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+            h.band_done.push_back(ev);
+        }
     }
     std::vector<TcItem> tc;
     std::vector<F64Item> f64;
@@ -183,6 +211,7 @@ static void free_handle(Handle* h) {
     if (h->pass_begin != nullptr) cudaEventDestroy(h->pass_begin);
     if (h->pass_end != nullptr) cudaEventDestroy(h->pass_end);
     for (auto& g : h->groups) if (g.done != nullptr) cudaEventDestroy(g.done);
+    for (cudaEvent_t ev : h->band_done) cudaEventDestroy(ev);
     for (auto& t : h->timers) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
     if (h->s_copy != nullptr) cudaStreamDestroy(h->s_copy);
     if (h->s_prep != nullptr) cudaStreamDestroy(h->s_prep);

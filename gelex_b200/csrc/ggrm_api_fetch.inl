@@ -7,14 +7,22 @@ static inline int64_t tri(int64_t i) { return i * (i + 1) / 2; }
 
 // Resolve (kind, group) to a device accumulator; makes sure the data is final and returns the event to wait on
 // (nullptr when the device is already idle for it).
-static void* resolve_accum(Handle& h, int kind, int group, cudaEvent_t* wait_on) {
+static void* resolve_accum(Handle& h, int kind, int group, cudaEvent_t* wait_on, bool* banded = nullptr) {
     *wait_on = nullptr;
+    if (banded != nullptr) *banded = false;
     if (kind != GGRM_KIND_ADD && kind != GGRM_KIND_DOM) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "kind must be 0 (add) or 1 (dom)"};
     if (h.pool[kind].empty()) throw CudaError{GGRM_ERR_INVALID_OPERATION, kind == 0 ? "additive matrix was not requested" : "dominance matrix was not requested"};
     const int ng = static_cast<int>(h.groups.size());
     if (group == GGRM_GROUP_WHOLE && ng > 1) {
         if (h.whole[kind] == nullptr) throw CudaError{GGRM_ERR_INVALID_OPERATION, "whole-genome matrix requires keep_whole when n_groups > 1"};
         if (!h.finished) throw CudaError{GGRM_ERR_INVALID_OPERATION, "whole-genome matrix is available after ggrm_finish"};
+        if (h.banded_whole) {
+            if (banded != nullptr) *banded = true;               // caller waits band by band
+            else *wait_on = h.band_done.back();
+        } else {
+            for (auto it = h.groups.rbegin(); it != h.groups.rend(); ++it)
+                if (it->complete) { *wait_on = it->done; break; }  // the last fold into `whole` precedes it on the compute stream
+        }
         return h.whole[kind];
     }
     const int g = group == GGRM_GROUP_WHOLE ? 0 : group;
@@ -22,13 +30,14 @@ static void* resolve_accum(Handle& h, int kind, int group, cudaEvent_t* wait_on)
     GroupState& gs = h.groups[g];
     if (!gs.started) {
         if (!h.finished && !(h.cur_group > g)) throw CudaError{GGRM_ERR_INVALID_OPERATION, "group is not complete yet: push a later group or call ggrm_finish"};
-        start_group(h, g);  // no SNP of this group was pushed on this handle: an all-zero partial
+        start_group(h, g, true);  // no SNP of this group was pushed on this handle: an all-zero partial
         gs.folded = true;
         complete_group(h, g);
     }
     if (!gs.complete) throw CudaError{GGRM_ERR_INVALID_OPERATION, "group is not complete yet: push a later group or call ggrm_finish"};
     if (gs.buffer[kind] < 0) throw CudaError{GGRM_ERR_INVALID_OPERATION, "group accumulator was released"};
     *wait_on = gs.done;
+    if (banded != nullptr && g == h.banded_group) *banded = true;  // rows become final band by band (Handle::band_done)
     return h.pool[kind][gs.buffer[kind]];
 }
 
@@ -66,8 +75,10 @@ static void fetch_typed(Handle& h, int kind, int group, int64_t row_begin, int64
     if (out == nullptr && row_count > 0) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "null output buffer"};
     if (mode != 0 && h.cfg.tile_world > 1) throw CudaError{GGRM_ERR_INVALID_OPERATION, "normalised / LOCO read-out needs the full trace: not available in 2D-tile mode"};
     cudaEvent_t ev = nullptr;
-    const TAcc* A = static_cast<const TAcc*>(resolve_accum(h, kind, group, &ev));
-    if (ev != nullptr) GGRM_CUDA(cudaStreamWaitEvent(h.s_fetch, ev, 0));
+    bool banded = false;
+    const TAcc* A = static_cast<const TAcc*>(resolve_accum(h, kind, group, &ev, mode == 0 ? &banded : nullptr));
+    if (ev != nullptr && !banded) GGRM_CUDA(cudaStreamWaitEvent(h.s_fetch, ev, 0));
+    int band_waited = -1;
     const TAcc* B = nullptr;
     double scale = 1.0;
     if (mode == 1) {
@@ -96,9 +107,19 @@ static void fetch_typed(Handle& h, int kind, int group, int64_t row_begin, int64
     int64_t written = 0;
     while (r < r_end) {
         int64_t cnt = 1;
+        int64_t limit = r_end;
+        if (banded) {  // rows of band b are final once band_done[b] has fired: never pack across a band boundary
+            int b = std::max(band_waited, 0);
+            while (h.band_row_end[static_cast<size_t>(b)] <= r) ++b;
+            limit = std::min(limit, h.band_row_end[static_cast<size_t>(b)]);
+            if (b > band_waited) {
+                GGRM_CUDA(cudaStreamWaitEvent(h.s_fetch, h.band_done[static_cast<size_t>(b)], 0));
+                band_waited = b;
+            }
+        }
         // largest cnt with tri(r+cnt) - tri(r) <= stage_elems (at least one row; a row always fits by construction)
         {
-            int64_t lo = 1, hi = r_end - r;
+            int64_t lo = 1, hi = limit - r;
             while (lo < hi) {
                 const int64_t mid = (lo + hi + 1) / 2;
                 if (tri(r + mid) - tri(r) <= stage_elems) lo = mid; else hi = mid - 1;
@@ -118,6 +139,46 @@ static void fetch_typed(Handle& h, int kind, int group, int64_t row_begin, int64
     phase_end(h, h.s_fetch, tfetch);
     GGRM_CUDA(cudaStreamSynchronize(h.s_fetch));
     if (trace_out != nullptr) *trace_out = tr;
+    if (h.finished) collect_timers(h);
+}
+
+// Rectangular block of the lower triangle -> host buffer with leading dimension ld (elements).  Used by the 2D-tile
+// writer: one call per owned 2048x2048 super-tile, rows then pwrite()n at their .bin offsets.
+template <typename TAcc>
+static void fetch_block_typed(Handle& h, int kind, int group, int64_t row_begin, int64_t row_count, int64_t col_begin, int64_t col_count,
+                              float* out, int64_t ld) {
+    if (row_begin < 0 || row_count < 0 || row_begin + row_count > h.n_out || col_begin < 0 || col_count < 0 || col_begin + col_count > h.n_out)
+        throw CudaError{GGRM_ERR_COLUMN_RANGE, "block outside [0, n_out) x [0, n_out)"};
+    if (row_count == 0 || col_count == 0) return;
+    if (out == nullptr) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "null output buffer"};
+    if (ld < col_count) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "leading dimension smaller than col_count"};
+    cudaEvent_t ev = nullptr;
+    bool banded = false;
+    const TAcc* A = static_cast<const TAcc*>(resolve_accum(h, kind, group, &ev, &banded));
+    if (banded) {
+        size_t b = 0;
+        while (h.band_row_end[b] < row_begin + row_count) ++b;
+        ev = h.band_done[b];
+    }
+    if (ev != nullptr) GGRM_CUDA(cudaStreamWaitEvent(h.s_fetch, ev, 0));
+    if (h.d_stage == nullptr) {
+        const int64_t want = std::min<int64_t>(int64_t{256} << 20, std::max<int64_t>(tri(h.n_out) * 8, h.n_out * 8 + 1024));
+        h.stage_bytes = std::max<int64_t>(want, h.n_out * 8);
+        GGRM_CUDA(cudaMalloc(&h.d_stage, static_cast<size_t>(h.stage_bytes)));
+    }
+    const int64_t rows_per_pass = std::max<int64_t>(1, h.stage_bytes / (col_count * static_cast<int64_t>(sizeof(float))));
+    const size_t tfetch = phase_begin(h, h.s_fetch, 4);
+    for (int64_t r = 0; r < row_count; r += rows_per_pass) {
+        const int64_t cnt = std::min(rows_per_pass, row_count - r);
+        pack_block_kernel<TAcc, float><<<static_cast<unsigned>(cnt), 256, 0, h.s_fetch>>>(A, h.d_slot_of, row_begin + r, cnt, col_begin, col_count,
+                                                                                         static_cast<float*>(h.d_stage));
+        GGRM_CUDA(cudaGetLastError());
+        ++h.kernel_launches;
+        GGRM_CUDA(cudaMemcpy2DAsync(out + r * ld, static_cast<size_t>(ld) * sizeof(float), h.d_stage, static_cast<size_t>(col_count) * sizeof(float),
+                                    static_cast<size_t>(col_count) * sizeof(float), static_cast<size_t>(cnt), cudaMemcpyDeviceToHost, h.s_fetch));
+    }
+    phase_end(h, h.s_fetch, tfetch);
+    GGRM_CUDA(cudaStreamSynchronize(h.s_fetch));
     if (h.finished) collect_timers(h);
 }
 
@@ -155,6 +216,29 @@ extern "C" int ggrm_fetch_loco(ggrm_t* hh, int kind, int group, int64_t row_begi
     GGRM_API_BEGIN(h)
     if (h->groups.size() < 2) throw CudaError{GGRM_ERR_INVALID_OPERATION, "LOCO read-out needs n_groups > 1 and keep_whole"};
     fetch_dispatch<double>(*h, kind, group, row_begin, row_count, out_lower_rows, nullptr, 2);
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_fetch_block(ggrm_t* hh, int kind, int group, int64_t row_begin, int64_t row_count, int64_t col_begin, int64_t col_count,
+                                float* out, int64_t ld) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    if (h->fp64) fetch_block_typed<double>(*h, kind, group, row_begin, row_count, col_begin, col_count, out, ld);
+    else fetch_block_typed<float>(*h, kind, group, row_begin, row_count, col_begin, col_count, out, ld);
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_owned_supertiles(ggrm_t* hh, int64_t* super_rows, int64_t* super_cols, int64_t capacity, int64_t* count) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    const int64_t n = static_cast<int64_t>(h->owned_supers.size() / 2);
+    if (count != nullptr) *count = n;
+    if (super_rows != nullptr && super_cols != nullptr) {
+        for (int64_t i = 0; i < std::min(n, capacity); ++i) {
+            super_rows[i] = h->owned_supers[static_cast<size_t>(2 * i)];
+            super_cols[i] = h->owned_supers[static_cast<size_t>(2 * i + 1)];
+        }
+    }
     GGRM_API_END(h)
 }
 

@@ -121,6 +121,20 @@ extern "C" int ggrm_ipc_close(int device, void* d_ptr) {
     GGRM_STATELESS_END
 }
 
+extern "C" int ggrm_host_alloc(int64_t bytes, void** out) {
+    GGRM_STATELESS_BEGIN
+    if (out == nullptr || bytes <= 0) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "invalid pinned allocation request"};
+    *out = nullptr;
+    GGRM_CUDA(cudaHostAlloc(out, static_cast<size_t>(bytes), cudaHostAllocPortable));
+    GGRM_STATELESS_END
+}
+
+extern "C" int ggrm_host_free(void* p) {
+    GGRM_STATELESS_BEGIN
+    if (p != nullptr) GGRM_CUDA(cudaFreeHost(p));
+    GGRM_STATELESS_END
+}
+
 static uint32_t miss_threshold(double missing_rate) {
     if (!(missing_rate > 0.0)) return 0u;
     if (missing_rate >= 1.0) return 1u << 24;

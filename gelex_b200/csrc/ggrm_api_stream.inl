@@ -28,14 +28,19 @@ static void collect_timers(Handle& h) {
         }
         std::fprintf(stderr, "[ggrm] SYRK gaps: %d gaps, total %.3f ms\n", n, gap_sum);
     }
+    std::vector<Timer> pending;  // still running (ggrm_finish_async + partial read-out): collected by a later call
     for (auto& t : h.timers) {
+        if (cudaEventQuery(t.b) == cudaErrorNotReady) {
+            pending.push_back(t);
+            continue;
+        }
         float ms = 0.f;
         if (cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess) h.phase_ms[t.phase] += ms;
         cudaEventDestroy(t.a);
         cudaEventDestroy(t.b);
     }
     cudaGetLastError();  // an unrecorded timer event must not poison later error checks
-    h.timers.clear();
+    h.timers.swap(pending);
 }
 
 static int group_of(const Handle& h, int64_t snp) {
@@ -49,7 +54,9 @@ static int group_of(const Handle& h, int64_t snp) {
     return -1;
 }
 
-static void start_group(Handle& h, int g) {
+// zero = the accumulator must read as zero before the first SYRK.  The tcgen05 path does not need that: its first slab
+// stores every element of every owned tile (accumulate = 0), which saves a 5 GB memset and a 5 GB read per group at n = 50k.
+static void start_group(Handle& h, int g, bool zero) {
     GroupState& gs = h.groups[g];
     if (gs.started) return;
     for (int kind = 0; kind < 2; ++kind) {
@@ -62,7 +69,11 @@ static void start_group(Handle& h, int g) {
                             "accumulator pool exhausted: fetch and ggrm_release_group completed groups, or raise max_resident_groups"};
         h.pool_owner[kind][slot] = g;
         gs.buffer[kind] = slot;
-        GGRM_CUDA(cudaMemsetAsync(h.pool[kind][slot], 0, static_cast<size_t>(std::max<int64_t>(h.accum_elems, 4)) * h.elem_bytes, h.s_comp));
+        gs.touched[kind] = false;
+        if (zero) {
+            GGRM_CUDA(cudaMemsetAsync(h.pool[kind][slot], 0, static_cast<size_t>(std::max<int64_t>(h.accum_elems, 4)) * h.elem_bytes, h.s_comp));
+            gs.touched[kind] = true;
+        }
     }
     gs.started = true;
 }
@@ -89,22 +100,24 @@ static void complete_group(Handle& h, int g) {
     gs.complete = true;
 }
 
-static void launch_syrk(Handle& h, int kind, int g, int64_t c, int zb) {
-    const GroupState& gs = h.groups[g];
+// items [item_begin, item_begin + item_count) of the tcgen05 work list (the whole list except in the banded final slab)
+static void launch_syrk(Handle& h, int kind, int g, int64_t c, int zb, float* fold, int accumulate, int item_begin, int item_count) {
+    GroupState& gs = h.groups[g];
     void* accum = h.pool[kind][gs.buffer[kind]];
     if (h.fp64) {
         if (h.num_items_f64 == 0) return;
         const int grid = std::min(h.num_items_f64, h.sm_count * 6);
         syrk_f64_kernel<<<grid, 128, 0, h.s_comp>>>(static_cast<const double*>(h.d_Z[kind][zb]), h.k_cap, c, static_cast<double*>(accum),
-                                                    h.d_items_f64, h.num_items_f64, 1);
+                                                    h.d_items_f64, h.num_items_f64, accumulate);
         GGRM_CUDA(cudaGetLastError());
     } else {
-        if (h.num_items_tc == 0) return;
+        if (item_count <= 0) return;
+        const TcItem* items = h.d_items_tc + item_begin;
         const int nkb = static_cast<int>(round_up(c, 64) / 64);
         const uint32_t fmt = h.cfg.precision == GGRM_PREC_FP16 ? 0u : 1u;
         int grid_ctas = 0, n_clusters = 1;
         if (h.tc_mode == 2) {
-            const int clusters = std::min(h.num_items_tc, h.sm_count / 2);
+            const int clusters = std::min(item_count, h.sm_count / 2);
             cudaLaunchConfig_t lc{};
             lc.gridDim = dim3(static_cast<unsigned>(2 * clusters));
             lc.blockDim = dim3(256);
@@ -118,21 +131,21 @@ static void launch_syrk(Handle& h, int kind, int g, int64_t c, int zb) {
             lc.attrs = attr;
             lc.numAttrs = 1;
             GGRM_CUDA(cudaLaunchKernelEx(&lc, syrk_tc_kernel<2>, h.tmap[kind][zb], static_cast<float*>(accum),
-                                         static_cast<const TcItem*>(h.d_items_tc), h.num_items_tc, nkb, 0, 1, fmt, h.cache_hints, h.d_fault,
-                                         h.d_wave_ctr, h.wave_base, h.sync_every));
+                                         items, item_count, nkb, 0, accumulate, fmt, h.cache_hints, h.d_fault,
+                                         h.d_wave_ctr, h.wave_base, h.sync_every, fold));
             grid_ctas = 2 * clusters;
             n_clusters = clusters;
         } else {
-            const int grid = std::min(h.num_items_tc, h.sm_count);
-            syrk_tc_kernel<1><<<grid, 256, TcConfig<1>::kSmemBytes, h.s_comp>>>(h.tmap[kind][zb], static_cast<float*>(accum), h.d_items_tc,
-                                                                                h.num_items_tc, nkb, 0, 1, fmt, h.cache_hints, h.d_fault,
-                                                                                h.d_wave_ctr, h.wave_base, h.sync_every);
+            const int grid = std::min(item_count, h.sm_count);
+            syrk_tc_kernel<1><<<grid, 256, TcConfig<1>::kSmemBytes, h.s_comp>>>(h.tmap[kind][zb], static_cast<float*>(accum), items,
+                                                                                item_count, nkb, 0, accumulate, fmt, h.cache_hints, h.d_fault,
+                                                                                h.d_wave_ctr, h.wave_base, h.sync_every, fold);
             GGRM_CUDA(cudaGetLastError());
             grid_ctas = grid;
             n_clusters = grid;
         }
         if (h.sync_every > 0) {  // every CTA checks in once per pacing point (see syrk_tc.cuh)
-            const int waves = (h.num_items_tc + n_clusters - 1) / n_clusters;
+            const int waves = (item_count + n_clusters - 1) / n_clusters;
             if (waves > 1) h.wave_base += static_cast<unsigned long long>((waves - 1) / h.sync_every) * static_cast<unsigned long long>(grid_ctas);
         }
     }
@@ -141,7 +154,7 @@ static void launch_syrk(Handle& h, int kind, int g, int64_t c, int zb) {
 }
 
 
-static void flush_chunk(Handle& h) {
+static void flush_chunk(Handle& h, bool final_flush = false) {
     if (h.cur_count == 0) return;
     const int b = h.cur_buf;
     const int zb = h.z_buf;
@@ -152,7 +165,7 @@ static void flush_chunk(Handle& h) {
     GGRM_CUDA(cudaEventRecord(h.h2d_done, h.s_copy));
     GGRM_CUDA(cudaStreamWaitEvent(sp, h.h2d_done, 0));
     GGRM_CUDA(cudaStreamWaitEvent(sp, h.z_free[zb], 0));  // the SYRKs of two slabs ago have finished reading Z[.][zb]
-    start_group(h, g);
+    start_group(h, g, h.fp64);
 
     size_t ti = phase_begin(h, sp, 1);
     repack_kernel<<<static_cast<unsigned>(c), 256, 0, sp>>>(h.d_raw[b], h.bpv_raw, h.d_dense, h.bpv_pad, h.n_out, h.d_out_to_raw, c);
@@ -187,10 +200,30 @@ static void flush_chunk(Handle& h) {
     GGRM_CUDA(cudaEventRecord(h.prep_done[zb], sp));
     GGRM_CUDA(cudaStreamWaitEvent(h.s_comp, h.prep_done[zb], 0));
     ti = phase_begin(h, h.s_comp, 3);
-    for (int kind = 0; kind < 2; ++kind) {
-        if (h.d_Z[kind][zb] == nullptr) continue;
-        launch_syrk(h, kind, g, c, zb);
+    // last slab of a chromosome whose partial also feeds `whole`: fold inside the SYRK epilogue (tcgen05 path)
+    const bool fold_here = !h.fp64 && !h.groups[g].folded && h.cur_first_snp + c == h.groups[g].end;
+    int accumulate[2];
+    for (int kind = 0; kind < 2; ++kind) {  // first slab of a group stores, later slabs add (see start_group)
+        accumulate[kind] = h.groups[g].touched[kind] ? 1 : 0;
+        h.groups[g].touched[kind] = true;
     }
+    const bool banded = final_flush && !h.fp64 && h.band_item_end.size() > 1;
+    const size_t nbands = banded ? h.band_item_end.size() : 1;
+    int item_begin = 0;
+    for (size_t b = 0; b < nbands; ++b) {
+        const int item_end = banded ? h.band_item_end[b] : h.num_items_tc;
+        for (int kind = 0; kind < 2; ++kind) {
+            if (h.d_Z[kind][zb] == nullptr) continue;
+            launch_syrk(h, kind, g, c, zb, fold_here ? static_cast<float*>(h.whole[kind]) : nullptr, accumulate[kind], item_begin, item_end - item_begin);
+        }
+        if (banded) GGRM_CUDA(cudaEventRecord(h.band_done[b], h.s_comp));
+        item_begin = item_end;
+    }
+    if (banded) {
+        h.banded_group = g;
+        h.banded_whole = fold_here;
+    }
+    if (fold_here) h.groups[g].folded = true;
     phase_end(h, h.s_comp, ti);
     GGRM_CUDA(cudaEventRecord(h.z_free[zb], h.s_comp));
     h.z_buf ^= 1;
@@ -267,14 +300,19 @@ static void push_impl(Handle& h, const uint8_t* payload, bool is_device, int64_t
         }
         const int64_t run_end = std::min(end, h.groups[g].end);
         while (s < run_end) {
-            if (h.cur_count > 0 && (g != h.cur_group || s != h.cur_first_snp + h.cur_count || h.cur_count == h.k_cap)) flush_chunk(h);
+            if (h.cur_count > 0 && (g != h.cur_group || s != h.cur_first_snp + h.cur_count || h.cur_count == h.cur_cap)) flush_chunk(h);
             if (h.cur_count == 0) {
                 for (int og = 0; og < g; ++og)
                     if (h.groups[og].started && !h.groups[og].complete) complete_group(h, og);
                 h.cur_group = g;
                 h.cur_first_snp = s;
+                // equal slabs: the rest of the group in ceil(rest / k_cap) pieces (every launch pays the same 2 x accumulator
+                // read-modify-write, so a short tail slab would be HBM-bound)
+                const int64_t rest = h.groups[g].end - s;
+                const int64_t pieces = (rest + h.k_cap - 1) / h.k_cap;
+                h.cur_cap = std::min<int64_t>(h.k_cap, round_up((rest + pieces - 1) / pieces, 64));
             }
-            const int64_t take = std::min(run_end - s, h.k_cap - h.cur_count);
+            const int64_t take = std::min(run_end - s, h.cur_cap - h.cur_count);
             copy_rows(h, payload + (s - snp_begin) * h.bpv_raw, is_device, pinned, take, h.d_raw[h.cur_buf] + h.cur_count * h.bpv_raw);
             h.cur_count += take;
             s += take;
@@ -284,14 +322,18 @@ static void push_impl(Handle& h, const uint8_t* payload, bool is_device, int64_t
     h.last_snp_pushed = end - 1;
 }
 
-static void finish_impl(Handle& h) {
-    if (!h.finished) {
-        flush_chunk(h);
-        for (size_t g = 0; g < h.groups.size(); ++g)
-            if (h.groups[g].started) complete_group(h, static_cast<int>(g));
-        h.finished = true;
-        if (h.pass_open) GGRM_CUDA(cudaEventRecord(h.pass_end, h.s_comp));
-    }
+// Enqueue the rest of the pass (last slab band by band, folds, completion events) without waiting for the device.
+static void finish_enqueue(Handle& h) {
+    if (h.finished) return;
+    flush_chunk(h, true);
+    for (size_t g = 0; g < h.groups.size(); ++g)
+        if (h.groups[g].started) complete_group(h, static_cast<int>(g));
+    h.finished = true;
+    if (h.pass_open) GGRM_CUDA(cudaEventRecord(h.pass_end, h.s_comp));
+}
+
+// Wait for the device, surface faults, collect timers.
+static void finish_sync(Handle& h) {
     cudaError_t e1 = cudaStreamSynchronize(h.s_copy);
     const cudaError_t e1b = cudaStreamSynchronize(h.s_prep);
     if (e1 == cudaSuccess) e1 = e1b;
@@ -311,16 +353,23 @@ static void finish_impl(Handle& h) {
     }
 }
 
+static void finish_impl(Handle& h) {
+    finish_enqueue(h);
+    finish_sync(h);
+}
+
 // Re-arm a finished handle for another pass over (the same or other) SNPs: accumulators are zeroed lazily when their
 // group restarts, statistics are overwritten, buffers and work lists are reused.  Timers keep accumulating.
 static void reset_impl(Handle& h) {
-    GGRM_CUDA(cudaStreamSynchronize(h.s_copy));
-    GGRM_CUDA(cudaStreamSynchronize(h.s_prep));
-    GGRM_CUDA(cudaStreamSynchronize(h.s_comp));
     GGRM_CUDA(cudaStreamSynchronize(h.s_fetch));
+    if (!h.finished) h.pass_open = false;  // abandoned pass: no end event to measure against
+    finish_sync(h);  // also closes a pass that was finished with ggrm_finish_async and read out without a blocking finish
+    h.banded_group = -1;
+    h.banded_whole = false;
     for (auto& g : h.groups) {
         g.buffer[0] = g.buffer[1] = -1;
         g.started = g.complete = g.folded = false;
+        g.touched[0] = g.touched[1] = false;
     }
     for (int kind = 0; kind < 2; ++kind) {
         std::fill(h.pool_owner[kind].begin(), h.pool_owner[kind].end(), -1);
@@ -362,6 +411,13 @@ extern "C" int ggrm_finish(ggrm_t* hh) {
     Handle* h = reinterpret_cast<Handle*>(hh);
     GGRM_API_BEGIN(h)
     finish_impl(*h);
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_finish_async(ggrm_t* hh) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    finish_enqueue(*h);
     GGRM_API_END(h)
 }
 

@@ -32,6 +32,7 @@ struct GroupState {
     int64_t begin = 0, end = 0;
     int buffer[2] = {-1, -1};     // accumulator pool slot per kind (-1 = none yet / released)
     bool started = false;
+    bool touched[2] = {false, false};  // a SYRK has written this group's accumulator of that kind (first slab stores, later slabs add)
     bool complete = false;        // all SNPs accumulated (+ folded into whole); `done` event recorded
     bool folded = false;
     cudaEvent_t done = nullptr;
@@ -58,11 +59,20 @@ struct Handle {
     // ownership and work lists
     std::vector<int32_t> slot_of_host;    // [ntiles_side*(ntiles_side+1)/2] -> slot or -1
     int64_t owned_tiles = 0;
+    std::vector<int64_t> owned_supers;    // (super-row, super-col) pairs of the 2048x2048 super-tiles this handle owns, storage order
     int32_t* d_slot_of = nullptr;
     TcItem* d_items_tc = nullptr;
     int num_items_tc = 0;
     F64Item* d_items_f64 = nullptr;
     int num_items_f64 = 0;
+    // Row bands of the tcgen05 work list (whole strips of strip_h tile rows, ~equal tile counts).  The LAST slab of a pass is
+    // launched band by band with an event after each, so the read-out of the first rows (pack + D2H on s_fetch) overlaps the
+    // SYRK of the later bands (ggrm_finish_async + ggrm_fetch*).
+    std::vector<int> band_item_end;       // exclusive item index per band
+    std::vector<int64_t> band_row_end;    // exclusive GRM row per band
+    std::vector<cudaEvent_t> band_done;
+    int banded_group = -1;                // group whose partial was finished band by band in the final flush (-1: none)
+    bool banded_whole = false;            // ... and `whole` too (its last fold happened inside those launches)
     // projection
     int32_t* d_out_to_raw = nullptr;      // nullptr = identity
     // streams
@@ -98,6 +108,7 @@ struct Handle {
     // current chunk
     int cur_buf = 0;
     int64_t cur_count = 0, cur_first_snp = -1;
+    int64_t cur_cap = 0;                  // SNP capacity of the slab being filled: the rest of its group cut into equal slabs <= k_cap
     int cur_group = -1;
     int64_t last_snp_pushed = -1;
     bool finished = false;

@@ -1,4 +1,5 @@
 // C entry point over the C++ host engine (for ctypes tests and for embedding); never throws.
+#include <cstdlib>
 #include <cstring>
 #include <string>
 
@@ -16,6 +17,11 @@ static void set_err(char* err, int err_len, const std::string& m) {
 
 extern "C" int gelex_b200_grm_run(const char* bfile, const char* out_prefix, int method, int mode, int do_loco, int chunk_size,
                                   int precision, int n_gpus, int write_whole, char* err, int err_len) {
+    return gelex_b200_grm_run_ex(bfile, out_prefix, method, mode, do_loco, chunk_size, precision, n_gpus, write_whole, 0, 4, err, err_len);
+}
+
+extern "C" int gelex_b200_grm_run_ex(const char* bfile, const char* out_prefix, int method, int mode, int do_loco, int chunk_size,
+                                     int precision, int n_gpus, int write_whole, int partition, int writer_threads, char* err, int err_len) {
     try {
         if (bfile == nullptr || out_prefix == nullptr) throw ArgumentValidationException("null argument");
         if (method < 1 || method > 8) throw InvalidInputException("Invalid genotype process method.");
@@ -28,8 +34,16 @@ extern "C" int gelex_b200_grm_run(const char* bfile, const char* out_prefix, int
         cfg.chunk_size = chunk_size;
         cfg.precision = precision;
         cfg.write_whole = write_whole != 0;
+        if (partition < 0 || partition > 2) throw ArgumentValidationException("partition must be 0 (auto), 1 (snp) or 2 (tile)");
+        cfg.partition = static_cast<Partition>(partition);
+        cfg.writer_threads = writer_threads;
         cfg.gpus.clear();
-        for (int i = 0; i < (n_gpus > 0 ? n_gpus : 1); ++i) cfg.gpus.push_back(i);
+        // Test aid: GELEX_B200_OVERSUBSCRIBE=1 maps rank i to device i % device_count, so the multi-GPU decompositions (several
+        // handles, peer reduce, concurrent writers) can be exercised on a one-GPU box.  Never set by the CLI.
+        const char* over = std::getenv("GELEX_B200_OVERSUBSCRIBE");
+        const int devs = ggrm_device_count();
+        for (int i = 0; i < (n_gpus > 0 ? n_gpus : 1); ++i)
+            cfg.gpus.push_back(over != nullptr && over[0] == '1' && devs > 0 ? i % devs : i);
         GrmEngine engine(cfg);
         engine.compute();
         set_err(err, err_len, "");

@@ -36,6 +36,7 @@ struct Logger {
 const char* kUsage =
     "Usage: gelex-b200 grm [--help] --bfile <BFILE> [--out <OUT>] [--geno-method <STR>] [--chunk-size <SIZE>]\n"
     "                      [--threads <N>] [--add] [--dom] [--loco] [--gpus <N>] [--precision <fp16|bf16|fp64>]\n"
+    "                      [--partition <auto|snp|tile>] [--writer-threads <N>]\n"
     "                      [--with-whole] [--skip-all-missing]\n\n"
     "Compute genomic relationship matrix (GRM) from PLINK binary files and output in GCTA format\n\n"
     "Data Files:\n"
@@ -52,14 +53,16 @@ const char* kUsage =
     "B200 engine options:\n"
     "  --gpus <N>                 Number of GPUs of this node to use [default: 1]\n"
     "  --precision <P>            fp16 (default) | bf16 : 16-bit operands, FP32 accumulate on tcgen05; fp64 : DMMA\n"
+    "  --partition <auto|snp|tile> Multi-GPU split: SNP shards + one reduce-scatter, or 2D output tiles (auto: tile from 100k samples)\n"
+    "  --writer-threads <N>       pwrite threads per GPU draining the read-out ring [default: 4]\n"
     "  --with-whole               With --loco also write the whole-genome matrix (sum of the partials, same pass)\n"
     "  --skip-all-missing         Treat an all-missing SNP as contributing 0 (the reference lets it poison the GRM with NaN)\n";
 
 std::string mode_name(GrmType m) { return m == GrmType::A ? "A" : (m == GrmType::D ? "D" : "AD"); }
 
 int run_grm(int argc, char** argv, Logger& log) {
-    std::string bfile, out = "grm", gm = "OSH", precision = "fp16";
-    int chunk = 10000, gpus = 1;
+    std::string bfile, out = "grm", gm = "OSH", precision = "fp16", partition = "auto";
+    int chunk = 10000, gpus = 1, writer_threads = 4;
     int threads = static_cast<int>(std::thread::hardware_concurrency() / 2);
     bool add = false, dom = false, loco = false, with_whole = false, skip_missing = false;
     auto need = [&](int& i) -> std::string {
@@ -89,6 +92,8 @@ int run_grm(int argc, char** argv, Logger& log) {
         else if (a == "--loco") loco = true;
         else if (a == "--gpus") gpus = to_int(need(i), "--gpus");
         else if (a == "--precision") precision = need(i);
+        else if (a == "--partition") partition = need(i);
+        else if (a == "--writer-threads") writer_threads = to_int(need(i), "--writer-threads");
         else if (a == "--with-whole") with_whole = true;
         else if (a == "--skip-all-missing") skip_missing = true;
         else throw ArgumentValidationException("Unknown argument: " + a);
@@ -111,6 +116,12 @@ int run_grm(int argc, char** argv, Logger& log) {
     if (gpus < 1) throw ArgumentValidationException("--gpus must be >= 1");
     cfg.gpus.clear();
     for (int g = 0; g < gpus; ++g) cfg.gpus.push_back(g);
+    if (partition == "auto") cfg.partition = Partition::Auto;
+    else if (partition == "snp") cfg.partition = Partition::SnpShard;
+    else if (partition == "tile") cfg.partition = Partition::Tile;
+    else throw ArgumentValidationException("--partition must be auto, snp or tile");
+    if (writer_threads < 1) throw ArgumentValidationException("--writer-threads must be >= 1");
+    cfg.writer_threads = writer_threads;
     cfg.write_whole = with_whole;
     cfg.skip_all_missing = skip_missing;
 
@@ -155,7 +166,8 @@ int run_grm(int argc, char** argv, Logger& log) {
     });
     const auto& sm = engine.summary();
     char line[256];
-    std::snprintf(line, sizeof(line), "  Device      : accumulate %.1f ms (SYRK %.1f ms), file write %.2f s", sm.device_pass_ms, sm.syrk_ms, sm.write_s);
+    std::snprintf(line, sizeof(line), "  Device      : accumulate %.1f ms (SYRK %.1f ms), read-out + file write %.2f s, engine wall %.2f s", sm.device_pass_ms,
+                  sm.syrk_ms, sm.write_s, sm.wall_s);
     log.info(line);
     return 0;
 }

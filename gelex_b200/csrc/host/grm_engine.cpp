@@ -11,6 +11,11 @@
 #include <numeric>
 #include <thread>
 #include <unordered_map>
+#include <condition_variable>
+#include <deque>
+
+#include <fcntl.h>
+#include <unistd.h>
 
 #include "exceptions.h"
 #include "plink_meta.h"
@@ -27,39 +32,196 @@ double since(Clock::time_point t0) { return std::chrono::duration<double>(Clock:
 void check(ggrm_t* h, int status) {
     if (status != GGRM_OK) throw_status(status, ggrm_last_error(h));
 }
+inline void check_status(ggrm_t* h, int status) { check(h, status); }
 
 struct HandleGuard {
     ggrm_t* h = nullptr;
     ~HandleGuard() { if (h != nullptr) ggrm_destroy(h); }
 };
 
-// .bin: row-major lower triangle incl. diagonal as float32, no header (grm_bin_writer.cpp:54-61).  Rows are fetched
-// in file order in blocks of <= 64 MiB and written with one fwrite per block.
-void write_bin_file(ggrm_t* h, int kind, int group, int64_t n, const fs::path& path, double* write_s) {
-    std::FILE* f = std::fopen(path.c_str(), "wb");
-    if (f == nullptr) throw FileOpenException(path.string() + ": failed to open file");
-    const int64_t max_elems = int64_t{16} << 20;
-    std::vector<float> buf(static_cast<size_t>(std::max<int64_t>(n, std::min<int64_t>(max_elems, n * (n + 1) / 2))));
-    int64_t r = 0;
-    while (r < n) {
+// ---------------------------------------------------------------------------------------------------------------
+// .bin writer.  Byte layout = grm_bin_writer.cpp:54-61 (row-major lower triangle incl. diagonal, float32, no header).
+// The reference issues one 4-byte ostream::write per element; here rows come off the GPU in blocks (ggrm_fetch /
+// ggrm_fetch_block into a ring of page-locked buffers) and a small pool of threads pwrite()s each block at its file
+// offset while the next block is already crossing PCIe.  Several GPUs (row slices, or 2D tiles) write disjoint byte
+// ranges of the same pre-sized file concurrently.
+struct BinFile {
+    int fd = -1;
+    std::string path;
+    BinFile() = default;
+    BinFile(const BinFile&) = delete;
+    BinFile& operator=(const BinFile&) = delete;
+    ~BinFile() { if (fd >= 0) ::close(fd); }
+    // create = truncate + size the file (one caller); otherwise open an existing, already sized file for writing
+    void open(const fs::path& p, int64_t n, bool create) {
+        path = p.string();
+        fd = ::open(path.c_str(), create ? (O_WRONLY | O_CREAT | O_TRUNC) : O_WRONLY, 0644);
+        if (fd < 0) throw FileOpenException(path + ": failed to open file");
+        if (create && ::ftruncate(fd, static_cast<off_t>(n * (n + 1) / 2 * static_cast<int64_t>(sizeof(float)))) != 0)
+            throw FileWriteException(path + ": failed to write GRM data to binary file");
+    }
+    void close_checked() {
+        if (fd >= 0 && ::close(fd) != 0) {
+            fd = -1;
+            throw FileWriteException(path + ": failed to write GRM data to binary file");
+        }
+        fd = -1;
+    }
+};
+
+struct Segment { int64_t src_elem, file_byte, bytes; };  // buffer elements [src_elem, +bytes/4) -> file bytes [file_byte, +bytes)
+
+class WriterPool {
+   public:
+    WriterPool(int threads, int buffers, int64_t buffer_elems) : elems_(buffer_elems) {
+        for (int i = 0; i < buffers; ++i) {
+            void* p = nullptr;
+            if (ggrm_host_alloc(buffer_elems * static_cast<int64_t>(sizeof(float)), &p) != GGRM_OK || p == nullptr) {
+                pageable_.emplace_back(static_cast<size_t>(buffer_elems));  // pinned memory exhausted: slower, still correct
+                p = pageable_.back().data();
+            } else {
+                pinned_.push_back(p);
+            }
+            free_.push_back(static_cast<float*>(p));
+        }
+        for (int t = 0; t < std::max(1, threads); ++t) workers_.emplace_back([this] { run(); });
+    }
+    ~WriterPool() {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            stop_ = true;
+        }
+        cv_job_.notify_all();
+        for (auto& w : workers_) w.join();
+        for (void* p : pinned_) ggrm_host_free(p);
+    }
+    int64_t buffer_elems() const { return elems_; }
+    float* acquire() {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_free_.wait(lk, [this] { return !free_.empty() || failed_; });
+        if (failed_) throw FileWriteException(failed_path_ + ": failed to write GRM data to binary file");
+        float* b = free_.back();
+        free_.pop_back();
+        return b;
+    }
+    void submit(const BinFile& file, float* buf, std::vector<Segment> segs) {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            jobs_.push_back({file.fd, &file.path, buf, std::move(segs)});
+            ++inflight_;
+        }
+        cv_job_.notify_one();
+    }
+    void drain() {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_free_.wait(lk, [this] { return inflight_ == 0; });
+        if (failed_) throw FileWriteException(failed_path_ + ": failed to write GRM data to binary file");
+    }
+    double busy_s() const { return busy_s_; }
+
+   private:
+    struct Job { int fd; const std::string* path; float* buf; std::vector<Segment> segs; };
+    void run() {
+        for (;;) {
+            Job job;
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_job_.wait(lk, [this] { return stop_ || !jobs_.empty(); });
+                if (jobs_.empty()) return;
+                job = std::move(jobs_.front());
+                jobs_.pop_front();
+            }
+            const auto t0 = Clock::now();
+            bool ok = true;
+            for (const Segment& sg : job.segs) {
+                const char* src = reinterpret_cast<const char*>(job.buf + sg.src_elem);
+                int64_t done = 0;
+                while (ok && done < sg.bytes) {
+                    const ssize_t w = ::pwrite(job.fd, src + done, static_cast<size_t>(sg.bytes - done), static_cast<off_t>(sg.file_byte + done));
+                    if (w <= 0) ok = false; else done += w;
+                }
+                if (!ok) break;
+            }
+            const double dt = since(t0);
+            {
+                std::lock_guard<std::mutex> lk(mu_);
+                if (!ok && !failed_) {
+                    failed_ = true;
+                    failed_path_ = *job.path;
+                }
+                busy_s_ += dt;
+                free_.push_back(job.buf);
+                --inflight_;
+            }
+            cv_free_.notify_all();
+        }
+    }
+    std::string failed_path_;
+    int64_t elems_;
+    std::mutex mu_;
+    std::condition_variable cv_job_, cv_free_;
+    std::deque<Job> jobs_;
+    std::vector<float*> free_;
+    std::vector<void*> pinned_;
+    std::vector<std::vector<float>> pageable_;
+    std::vector<std::thread> workers_;
+    int inflight_ = 0;
+    bool stop_ = false, failed_ = false;
+    double busy_s_ = 0;
+};
+
+inline int64_t tri(int64_t i) { return i * (i + 1) / 2; }
+
+// Rows [r0, r1) of matrix (kind, group) -> their byte range of the file, in blocks of whole rows.
+void write_packed_rows(ggrm_t* h, int kind, int group, int64_t r0, int64_t r1, const BinFile& file, WriterPool& pool) {
+    int64_t r = r0;
+    while (r < r1) {
         int64_t cnt = 1;
-        while (r + cnt < n && (r + cnt + 1) * (r + cnt + 2) / 2 - r * (r + 1) / 2 <= static_cast<int64_t>(buf.size())) ++cnt;
-        const int64_t elems = (r + cnt) * (r + cnt + 1) / 2 - r * (r + 1) / 2;
-        const int st = ggrm_fetch(h, kind, group, r, cnt, buf.data(), nullptr);
+        {
+            int64_t lo = 1, hi = r1 - r;  // largest cnt whose rows fit one buffer (a single row always fits: buffers hold >= n floats)
+            while (lo < hi) {
+                const int64_t mid = (lo + hi + 1) / 2;
+                if (tri(r + mid) - tri(r) <= pool.buffer_elems()) lo = mid; else hi = mid - 1;
+            }
+            cnt = lo;
+        }
+        float* buf = pool.acquire();
+        const int st = ggrm_fetch(h, kind, group, r, cnt, buf, nullptr);
         if (st != GGRM_OK) {
-            std::fclose(f);
+            pool.submit(file, buf, {});
             throw_status(st, ggrm_last_error(h));
         }
-        const auto t0 = Clock::now();
-        const size_t w = std::fwrite(buf.data(), sizeof(float), static_cast<size_t>(elems), f);
-        if (write_s != nullptr) *write_s += since(t0);
-        if (w != static_cast<size_t>(elems)) {
-            std::fclose(f);
-            throw FileWriteException(path.string() + ": failed to write GRM data to binary file");
-        }
+        pool.submit(file, buf, {Segment{0, tri(r) * 4, (tri(r + cnt) - tri(r)) * 4}});
         r += cnt;
     }
-    if (std::fclose(f) != 0) throw FileWriteException(path.string() + ": failed to write GRM data to binary file");
+}
+
+// 2D-tile mode: every 2048 x 2048 super-tile this handle owns -> row segments at their own offsets.
+void write_owned_supertiles(ggrm_t* h, int kind, int group, int64_t n, const BinFile& file, WriterPool& pool) {
+    constexpr int64_t kSuper = 2048;
+    int64_t count = 0;
+    check_status(h, ggrm_owned_supertiles(h, nullptr, nullptr, 0, &count));
+    std::vector<int64_t> sr(static_cast<size_t>(std::max<int64_t>(1, count))), sc(sr.size());
+    check_status(h, ggrm_owned_supertiles(h, sr.data(), sc.data(), count, &count));
+    for (int64_t t = 0; t < count; ++t) {
+        const int64_t row0 = sr[static_cast<size_t>(t)] * kSuper, col0 = sc[static_cast<size_t>(t)] * kSuper;
+        const int64_t rows = std::min(kSuper, n - row0), cols = std::min(kSuper, n - col0);
+        if (rows <= 0 || cols <= 0) continue;
+        float* buf = pool.acquire();
+        const int st = ggrm_fetch_block(h, kind, group, row0, rows, col0, cols, buf, cols);
+        if (st != GGRM_OK) {
+            pool.submit(file, buf, {});
+            throw_status(st, ggrm_last_error(h));
+        }
+        std::vector<Segment> segs;
+        segs.reserve(static_cast<size_t>(rows));
+        for (int64_t i = 0; i < rows; ++i) {
+            const int64_t gi = row0 + i;
+            const int64_t len = std::min(cols, gi + 1 - col0);
+            if (len > 0) segs.push_back(Segment{i * cols, (tri(gi) + col0) * 4, len * 4});
+        }
+        pool.submit(file, buf, std::move(segs));
+    }
 }
 
 std::string lower(std::string s) {
@@ -141,6 +303,9 @@ GrmEngine::GrmEngine(Config config) : config_(std::move(config)) {}
 
 namespace {
 
+constexpr int64_t kSuperRows = 2048;          // ownership / row-slice granularity of the device library (8 tiles of 256)
+constexpr int64_t kWriterBufferElems = int64_t{4} << 20;  // 16 MiB: one 2048 x 2048 super-tile, or ~80 rows at n = 50 000
+
 struct RunContext {
     const GrmEngine::Config* cfg;
     const SampleOrder* order;
@@ -156,7 +321,14 @@ struct RunContext {
     double* write_s;
 };
 
-ggrm_t* create_handle(const RunContext& rc, int device, const std::vector<int>& my_groups, bool keep_whole) {
+// Which part of an output file a handle contributes.
+struct WritePart {
+    enum Kind { AllRows, RowSlice, OwnedTiles } kind = AllRows;
+    int64_t r0 = 0, r1 = 0;   // RowSlice
+    bool create = true;        // this caller creates + sizes the .bin and writes the .id (otherwise the main thread did)
+};
+
+ggrm_t* create_handle(const RunContext& rc, int device, const std::vector<int>& my_groups, bool keep_whole, int tile_rank = 0, int tile_world = 1) {
     ggrm_config_t c{};
     c.abi_version = GGRM_ABI_VERSION;
     c.device = device;
@@ -178,8 +350,8 @@ ggrm_t* create_handle(const RunContext& rc, int device, const std::vector<int>& 
     c.group_end = ge.data();
     c.keep_whole = keep_whole ? 1 : 0;
     c.all_missing_policy = rc.cfg->skip_all_missing ? GGRM_ALLMISS_SKIP : GGRM_ALLMISS_REFERENCE_NAN;
-    c.tile_rank = 0;
-    c.tile_world = 1;
+    c.tile_rank = tile_rank;
+    c.tile_world = tile_world;
     ggrm_t* h = nullptr;
     const int st = ggrm_create(&c, &h);
     if (st != GGRM_OK) throw_status(st, ggrm_last_error(nullptr));
@@ -194,7 +366,7 @@ void emit_progress(const RunContext& rc, size_t current, size_t total) {
 }
 
 // Push SNPs [begin, end) in host chunks of cfg.chunk_size (the reference's load_chunk granularity).
-void push_range(const RunContext& rc, ggrm_t* h, int64_t begin, int64_t end, int64_t item_total, int64_t* item_done) {
+void push_range(const RunContext& rc, ggrm_t* h, int64_t begin, int64_t end, int64_t item_total, int64_t* item_done, bool report = true) {
     for (int64_t s = begin; s < end; s += rc.cfg->chunk_size) {
         const int64_t c = std::min<int64_t>(rc.cfg->chunk_size, end - s);
         if (s < 0 || s + c > rc.m || c <= 0)  // validate_chunk_range, bed_pipe.cpp:38-52
@@ -203,56 +375,104 @@ void push_range(const RunContext& rc, ggrm_t* h, int64_t begin, int64_t end, int
         if (p == nullptr) throw FileFormatException("BedPipe::load_chunk: mapped BED payload is truncated");
         check(h, ggrm_push(h, p, s, c, rc.bpv));
         *item_done += c;
-        emit_progress(rc, static_cast<size_t>(*item_done), static_cast<size_t>(item_total));
+        if (report) emit_progress(rc, static_cast<size_t>(*item_done), static_cast<size_t>(item_total));
     }
 }
 
-void write_outputs(const RunContext& rc, ggrm_t* h, int local_group, const std::string& suffix /* "" or ".chrNAME" */) {
+std::string output_base(const RunContext& rc, int kind, const std::string& suffix) {
+    return rc.cfg->out_prefix + "." + (kind == 0 ? "add" : "dom") + suffix;
+}
+
+void register_files(const RunContext& rc, const std::string& base) {
+    std::lock_guard<std::mutex> lk(*rc.mu);
+    rc.files->push_back(base + ".bin");
+    rc.files->push_back(base + ".id");
+}
+
+// Main-thread step of the multi-writer modes: size every .bin, write every .id, before any GPU thread opens them.
+void precreate_outputs(const RunContext& rc, const std::vector<std::string>& suffixes) {
+    for (const std::string& suffix : suffixes)
+        for (int kind = 0; kind < 2; ++kind) {
+            if (!(kind == 0 ? rc.want_add : rc.want_dom)) continue;
+            const std::string base = output_base(rc, kind, suffix);
+            BinFile f;
+            f.open(base + ".bin", rc.n_out, true);
+            f.close_checked();
+            write_id_file(base + ".id", rc.order->ids);
+            register_files(rc, base);
+        }
+}
+
+void write_outputs(const RunContext& rc, ggrm_t* h, int local_group, const std::string& suffix /* "" or ".chrNAME" */, const WritePart& part,
+                   WriterPool& pool) {
+    const auto t0 = Clock::now();
     for (int kind = 0; kind < 2; ++kind) {
         if (!(kind == 0 ? rc.want_add : rc.want_dom)) continue;
-        const std::string base = rc.cfg->out_prefix + "." + (kind == 0 ? "add" : "dom") + suffix;
-        double ws = 0;
-        write_bin_file(h, kind, local_group, rc.n_out, base + ".bin", &ws);
-        write_id_file(base + ".id", rc.order->ids);
-        std::lock_guard<std::mutex> lk(*rc.mu);
-        rc.files->push_back(base + ".bin");
-        rc.files->push_back(base + ".id");
-        *rc.write_s += ws;
+        const std::string base = output_base(rc, kind, suffix);
+        BinFile f;
+        f.open(base + ".bin", rc.n_out, part.create);
+        try {
+            switch (part.kind) {
+                case WritePart::AllRows: write_packed_rows(h, kind, local_group, 0, rc.n_out, f, pool); break;
+                case WritePart::RowSlice: write_packed_rows(h, kind, local_group, part.r0, part.r1, f, pool); break;
+                case WritePart::OwnedTiles: write_owned_supertiles(h, kind, local_group, rc.n_out, f, pool); break;
+            }
+        } catch (...) {
+            try { pool.drain(); } catch (...) {}  // no writer may still hold the descriptor when it closes
+            throw;
+        }
+        pool.drain();
+        f.close_checked();
+        if (part.create) {
+            write_id_file(base + ".id", rc.order->ids);
+            register_files(rc, base);
+        }
     }
+    std::lock_guard<std::mutex> lk(*rc.mu);
+    *rc.write_s += since(t0);
+}
+
+void note_timers(const RunContext& rc, ggrm_t* h, double* pass_ms, double* syrk_ms) {
+    double t[8] = {0};
+    ggrm_get_timers(h, t);
+    std::lock_guard<std::mutex> lk(*rc.mu);
+    *pass_ms = std::max(*pass_ms, t[7]);
+    *syrk_ms = std::max(*syrk_ms, t[3]);
 }
 
 // One GPU, a list of groups (chromosome runs) in SNP order.  Group g is written while the GPU already works on g+1.
+// `part` says which piece of every group's file this handle writes (all rows, or the tiles it owns in 2D-tile mode).
 void run_groups_on_device(const RunContext& rc, int device, const std::vector<int>& my_groups, bool keep_whole, ggrm_t** keep_handle,
-                          double* pass_ms, double* syrk_ms) {
+                          double* pass_ms, double* syrk_ms, const WritePart& part, int tile_rank, int tile_world, bool report, bool write_whole_here) {
     HandleGuard hg;
-    hg.h = create_handle(rc, device, my_groups, keep_whole);
+    hg.h = create_handle(rc, device, my_groups, keep_whole, tile_rank, tile_world);
+    WriterPool pool(rc.cfg->writer_threads, rc.cfg->writer_threads + 2, std::max<int64_t>(kWriterBufferElems, rc.n_out));
     int pending = -1;  // local index of a group that is complete on the device but not yet written
+    auto group_name = [&](int li) { return ".chr" + rc.groups[static_cast<size_t>(my_groups[static_cast<size_t>(li)])].name; };
     for (size_t li = 0; li < my_groups.size(); ++li) {
         const ChrRun& run = rc.groups[static_cast<size_t>(my_groups[li])];
         int64_t done = 0;
         // first chunk of this group makes the previous group fetchable
         const int64_t first_end = std::min<int64_t>(run.end, run.begin + rc.cfg->chunk_size);
-        push_range(rc, hg.h, run.begin, first_end, run.end - run.begin, &done);
+        push_range(rc, hg.h, run.begin, first_end, run.end - run.begin, &done, report);
         if (pending >= 0) {
-            write_outputs(rc, hg.h, pending, ".chr" + rc.groups[static_cast<size_t>(my_groups[static_cast<size_t>(pending)])].name);
+            write_outputs(rc, hg.h, pending, group_name(pending), part, pool);
             for (int kind = 0; kind < 2; ++kind)
                 if (kind == 0 ? rc.want_add : rc.want_dom) check(hg.h, ggrm_release_group(hg.h, kind, pending));
             pending = -1;
         }
-        push_range(rc, hg.h, first_end, run.end, run.end - run.begin, &done);
+        push_range(rc, hg.h, first_end, run.end, run.end - run.begin, &done, report);
         if (rc.loco) pending = static_cast<int>(li);
     }
+    // The matrix still accumulating when the last SNP is pushed (the whole-genome one, or the last chromosome) is read out
+    // through ggrm_finish_async: its first row bands cross PCIe while the last slab is still on the tensor cores.
+    const bool whole_here = !rc.loco && (write_whole_here || part.kind == WritePart::OwnedTiles);
+    check(hg.h, ggrm_finish_async(hg.h));
+    if (rc.loco && pending >= 0) write_outputs(rc, hg.h, pending, group_name(pending), part, pool);
+    if (whole_here) write_outputs(rc, hg.h, GGRM_GROUP_WHOLE, "", part, pool);
     check(hg.h, ggrm_finish(hg.h));
-    if (rc.loco) {
-        if (pending >= 0) write_outputs(rc, hg.h, pending, ".chr" + rc.groups[static_cast<size_t>(my_groups[static_cast<size_t>(pending)])].name);
-    }
-    double t[8] = {0};
-    ggrm_get_timers(hg.h, t);
-    {
-        std::lock_guard<std::mutex> lk(*rc.mu);
-        *pass_ms = std::max(*pass_ms, t[7]);
-        *syrk_ms = std::max(*syrk_ms, t[3]);
-    }
+    note_timers(rc, hg.h, pass_ms, syrk_ms);
+    if (rc.loco && keep_whole && (write_whole_here || part.kind == WritePart::OwnedTiles)) write_outputs(rc, hg.h, GGRM_GROUP_WHOLE, "", part, pool);
     if (keep_handle != nullptr) {
         *keep_handle = hg.h;
         hg.h = nullptr;
@@ -266,45 +486,97 @@ void run_shard_on_device(const RunContext& rc, int device, int64_t begin, int64_
     int64_t done = 0;
     push_range(rc, hg.h, begin, end, end - begin, &done);
     check(hg.h, ggrm_finish(hg.h));
-    double t[8] = {0};
-    ggrm_get_timers(hg.h, t);
-    {
-        std::lock_guard<std::mutex> lk(*rc.mu);
-        *pass_ms = std::max(*pass_ms, t[7]);
-        *syrk_ms = std::max(*syrk_ms, t[3]);
-    }
+    note_timers(rc, hg.h, pass_ms, syrk_ms);
     *keep_handle = hg.h;
     hg.h = nullptr;
 }
 
-// Sum the whole-genome accumulators of all handles into handles[0] over NVLink peer memory (no NCCL: one process owns
-// every GPU, so peers' device pointers are directly addressable once peer access is enabled).
-void reduce_onto_first(const RunContext& rc, const std::vector<ggrm_t*>& handles, const std::vector<int>& devices) {
-    if (handles.size() < 2) return;
-    for (size_t p = 1; p < devices.size(); ++p) {
-        const int st = ggrm_enable_peer_access(devices[0], devices[p]);
-        if (st != GGRM_OK) throw_status(st, ggrm_last_error(nullptr));
+// Rows cut on super-row (2048) boundaries into `parts` ranges of about equal lower-triangle area (the same rule as
+// gelex_b200/sharding.py::row_slices, which the gloo test covers).
+std::vector<std::pair<int64_t, int64_t>> row_slices(int64_t n, int parts) {
+    const int64_t t = (n + 255) / 256, st = 8;
+    const int64_t nsr = (t + st - 1) / st;
+    std::vector<int64_t> cum(static_cast<size_t>(nsr));
+    for (int64_t s = 0; s < nsr; ++s) {
+        const int64_t rows = std::min(t, (s + 1) * st);
+        cum[static_cast<size_t>(s)] = rows * (rows + 1) / 2;
     }
-    for (int kind = 0; kind < 2; ++kind) {
-        if (!(kind == 0 ? rc.want_add : rc.want_dom)) continue;
-        std::vector<const void*> peers;
-        int64_t n_elems = 0;
-        for (size_t p = 0; p < handles.size(); ++p) {
-            void* ptr = nullptr;
-            int64_t ne = 0;
-            int32_t eb = 0;
-            check(handles[p], ggrm_accum_buffer(handles[p], kind, GGRM_GROUP_WHOLE, &ptr, &ne, &eb));
-            if (p == 0) n_elems = ne;
-            else peers.push_back(ptr);
-        }
-        for (size_t off = 0; off < peers.size(); off += 7) {  // ggrm_reduce_peer takes up to 7 peers per call
-            const int cnt = static_cast<int>(std::min<size_t>(7, peers.size() - off));
-            check(handles[0], ggrm_reduce_peer(handles[0], kind, GGRM_GROUP_WHOLE, peers.data() + off, cnt, 0, n_elems));
-        }
+    const double total = static_cast<double>(cum.back());
+    std::vector<int64_t> cuts{0};
+    int64_t s = 0;
+    for (int r = 1; r < parts; ++r) {
+        const double target = total * r / parts;
+        while (s < nsr && static_cast<double>(cum[static_cast<size_t>(s)]) < target) ++s;
+        const double lo = s > 0 ? static_cast<double>(cum[static_cast<size_t>(s - 1)]) : 0.0;
+        const int64_t c = (s < nsr && static_cast<double>(cum[static_cast<size_t>(s)]) - target <= target - lo) ? s + 1 : s;
+        cuts.push_back(std::max(cuts.back(), std::min(nsr, c)));
     }
+    cuts.push_back(nsr);
+    std::vector<std::pair<int64_t, int64_t>> out;
+    for (int r = 0; r < parts; ++r)
+        out.emplace_back(std::min(n, cuts[static_cast<size_t>(r)] * kSuperRows), std::min(n, cuts[static_cast<size_t>(r + 1)] * kSuperRows));
+    return out;
 }
 
-void run_multi_gpu(const RunContext& rc, double* pass_ms, double* syrk_ms) {
+// Whole-genome matrix held as partial sums on several GPUs -> file.  Reduce-scatter by row slices over NVLink peer memory
+// (one process owns every GPU, so peers' device pointers are addressable once peer access is on; no NCCL): GPU r sums ITS
+// rows from every peer's accumulator and then writes only those rows, so the read-out uses every GPU's PCIe link and the
+// file is written by several threads at once.
+void reduce_scatter_and_write(const RunContext& rc, const std::vector<ggrm_t*>& handles, const std::vector<int>& devices) {
+    const size_t ng = handles.size();
+    for (size_t a = 0; a < ng; ++a)
+        for (size_t b = 0; b < ng; ++b)
+            if (a != b) {
+                const int st = ggrm_enable_peer_access(devices[a], devices[b]);
+                if (st != GGRM_OK) throw_status(st, ggrm_last_error(nullptr));
+            }
+    std::vector<std::vector<const void*>> accum(2, std::vector<const void*>(ng, nullptr));
+    for (int kind = 0; kind < 2; ++kind) {
+        if (!(kind == 0 ? rc.want_add : rc.want_dom)) continue;
+        for (size_t p = 0; p < ng; ++p) {
+            void* ptr = nullptr;
+            check(handles[p], ggrm_accum_buffer(handles[p], kind, GGRM_GROUP_WHOLE, &ptr, nullptr, nullptr));
+            accum[static_cast<size_t>(kind)][p] = ptr;
+        }
+    }
+    precreate_outputs(rc, {""});
+    const auto slices = row_slices(rc.n_out, static_cast<int>(ng));
+    std::vector<std::exception_ptr> errors(ng);
+    std::vector<std::thread> threads;
+    for (size_t r = 0; r < ng; ++r) {
+        threads.emplace_back([&, r] {
+            try {
+                const auto [r0, r1] = slices[r];
+                if (r1 <= r0) return;
+                int64_t eb = 0, ee = 0;
+                check(handles[r], ggrm_row_slice(handles[r], r0, r1, &eb, &ee));
+                for (int kind = 0; kind < 2; ++kind) {
+                    if (!(kind == 0 ? rc.want_add : rc.want_dom)) continue;
+                    std::vector<const void*> peers;
+                    for (size_t p = 0; p < ng; ++p)
+                        if (p != r) peers.push_back(accum[static_cast<size_t>(kind)][p]);
+                    for (size_t off = 0; off < peers.size(); off += 7) {  // ggrm_reduce_peer takes up to 7 peers per call
+                        const int cnt = static_cast<int>(std::min<size_t>(7, peers.size() - off));
+                        check(handles[r], ggrm_reduce_peer(handles[r], kind, GGRM_GROUP_WHOLE, peers.data() + off, cnt, eb, ee));
+                    }
+                }
+                WriterPool pool(rc.cfg->writer_threads, rc.cfg->writer_threads + 2, std::max<int64_t>(kWriterBufferElems, rc.n_out));
+                WritePart part;
+                part.kind = WritePart::RowSlice;
+                part.r0 = r0;
+                part.r1 = r1;
+                part.create = false;
+                write_outputs(rc, handles[r], GGRM_GROUP_WHOLE, "", part, pool);
+            } catch (...) {
+                errors[r] = std::current_exception();
+            }
+        });
+    }
+    for (auto& t : threads) t.join();
+    for (auto& e : errors) if (e) std::rethrow_exception(e);
+}
+
+void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double* syrk_ms) {
     const std::vector<int>& gpus = rc.cfg->gpus;
     const size_t ng = gpus.size();
     std::vector<ggrm_t*> handles(ng, nullptr);
@@ -315,8 +587,31 @@ void run_multi_gpu(const RunContext& rc, double* pass_ms, double* syrk_ms) {
         ~Cleanup() { for (ggrm_t* h : *hs) if (h != nullptr) ggrm_destroy(h); }
     } cleanup{&handles};
     const bool want_whole = !rc.loco || rc.cfg->write_whole;
-    std::vector<std::vector<int>> mine(ng);  // outlives the worker threads (joined below), which read it by reference
-    if (rc.loco) {
+    // function scope: these outlive the worker threads (joined below), which read them by reference
+    std::vector<std::vector<int>> mine(ng);
+    std::vector<int> all;
+    if (tile_mode) {
+        // 2D output tiles: every GPU streams ALL SNPs, owns disjoint 2048 x 2048 super-tiles of every matrix and writes them
+        // straight to their file offsets.  No collective anywhere on the path.
+        std::vector<std::string> suffixes;
+        if (rc.loco) for (const ChrRun& g : rc.groups) suffixes.push_back(".chr" + g.name);
+        if (want_whole) suffixes.emplace_back("");
+        precreate_outputs(rc, suffixes);
+        all.resize(rc.groups.size());
+        std::iota(all.begin(), all.end(), 0);
+        for (size_t r = 0; r < ng; ++r) {
+            threads.emplace_back([&, r] {
+                try {
+                    WritePart part;
+                    part.kind = WritePart::OwnedTiles;
+                    part.create = false;
+                    run_groups_on_device(rc, gpus[r], all, rc.loco && want_whole, nullptr, pass_ms, syrk_ms, part, static_cast<int>(r), static_cast<int>(ng), r == 0, false);
+                } catch (...) {
+                    errors[r] = std::current_exception();
+                }
+            });
+        }
+    } else if (rc.loco) {
         // chromosome runs are dealt to GPUs by LPT on their SNP counts: every partial is produced by ONE GPU, no reduce
         std::vector<size_t> order(rc.groups.size());
         std::iota(order.begin(), order.end(), size_t{0});
@@ -333,7 +628,8 @@ void run_multi_gpu(const RunContext& rc, double* pass_ms, double* syrk_ms) {
             std::sort(mine[r].begin(), mine[r].end());
             threads.emplace_back([&, r] {
                 try {
-                    if (!mine[r].empty()) run_groups_on_device(rc, gpus[r], mine[r], want_whole, want_whole ? &handles[r] : nullptr, pass_ms, syrk_ms);
+                    if (!mine[r].empty())
+                        run_groups_on_device(rc, gpus[r], mine[r], want_whole, want_whole ? &handles[r] : nullptr, pass_ms, syrk_ms, WritePart{}, 0, 1, true, false);
                 } catch (...) {
                     errors[r] = std::current_exception();
                 }
@@ -354,7 +650,7 @@ void run_multi_gpu(const RunContext& rc, double* pass_ms, double* syrk_ms) {
     }
     for (auto& t : threads) t.join();
     for (auto& e : errors) if (e) std::rethrow_exception(e);
-    if (want_whole) {
+    if (want_whole && !tile_mode) {
         std::vector<ggrm_t*> live;
         std::vector<int> devs;
         for (size_t r = 0; r < ng; ++r)
@@ -362,10 +658,7 @@ void run_multi_gpu(const RunContext& rc, double* pass_ms, double* syrk_ms) {
                 live.push_back(handles[r]);
                 devs.push_back(gpus[r]);
             }
-        if (!live.empty()) {
-            reduce_onto_first(rc, live, devs);
-            write_outputs(rc, live[0], GGRM_GROUP_WHOLE, "");
-        }
+        if (!live.empty()) reduce_scatter_and_write(rc, live, devs);
     }
 }
 
@@ -419,19 +712,19 @@ void GrmEngine::compute(const GrmObserver& observer) {
     rc.write_s = &write_s;
 
     const int n_gpus = static_cast<int>(config_.gpus.size());
+    if (config_.writer_threads < 1) throw ArgumentValidationException("writer_threads must be >= 1");
     if (items.empty() || rc.groups.empty() || chroms.empty()) {
         // nothing to accumulate (empty BIM is rejected earlier as "is empty")
     } else if (n_gpus == 1) {
         std::vector<int> all(rc.groups.size());
         std::iota(all.begin(), all.end(), 0);
-        ggrm_t* h = nullptr;
-        const bool need_handle = !config_.do_loco || config_.write_whole;
-        run_groups_on_device(rc, config_.gpus[0], all, config_.do_loco && config_.write_whole, need_handle ? &h : nullptr, &pass_ms, &syrk_ms);
-        HandleGuard hg;
-        hg.h = h;
-        if (need_handle) write_outputs(rc, h, GGRM_GROUP_WHOLE, "");
+        // one GPU writes everything itself, the whole-genome matrix included (non-LOCO: the only output; LOCO: with write_whole)
+        run_groups_on_device(rc, config_.gpus[0], all, config_.do_loco && config_.write_whole, nullptr, &pass_ms, &syrk_ms, WritePart{}, 0, 1, true,
+                             !config_.do_loco || config_.write_whole);
     } else {
-        run_multi_gpu(rc, &pass_ms, &syrk_ms);
+        // SNP shards (+ one reduce) while the FP32 triangle fits comfortably per GPU, 2D output tiles from n >= 100 000
+        const bool tile_mode = config_.partition == Partition::Tile || (config_.partition == Partition::Auto && rc.n_out >= 100000);
+        run_multi_gpu(rc, tile_mode, &pass_ms, &syrk_ms);
     }
 
     if (observer) {

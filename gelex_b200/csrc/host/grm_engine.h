@@ -6,8 +6,9 @@
 //   * AD mode decodes once and runs two SYRKs per slab (the reference re-reads the BED per work item, grm_work_plan.cpp:95-103)
 //   * --loco produces every per-chromosome partial in ONE pass; with write_whole the whole-genome matrix is the device-side
 //     sum of the partials (the reference needs a second invocation)
-//   * .bin files are written from row blocks fetched in file order (large sequential writes instead of one 4-byte
-//     ostream::write per element, grm_bin_writer.cpp:54-61); bytes are identical.
+//   * .bin files are written from row blocks (or, in 2D-tile mode, 2048 x 2048 super-tiles) fetched into page-locked buffers and
+//     pwrite()n at their offsets by a thread pool - several GPUs write disjoint byte ranges of one file at once - instead of
+//     one 4-byte ostream::write per element (grm_bin_writer.cpp:54-61); bytes are identical.
 #pragma once
 #include <cstdint>
 #include <filesystem>
@@ -45,6 +46,10 @@ struct GrmWorkItem {  // src/pipeline/grm_work_plan.h:34-39
     int group;  // index into the chromosome runs, -1 = whole genome
 };
 
+// Multi-GPU decomposition.  Auto = SNP shards (chromosome shards with --loco) below 100 000 samples, 2D output
+// tiles from there on.
+enum class Partition : uint8_t { Auto, SnpShard, Tile };
+
 class GrmEngine {
    public:
     struct Config {
@@ -60,6 +65,8 @@ class GrmEngine {
         std::vector<int> gpus = {0};     // device ordinals; >1 = SNP-sharded (or chromosome-sharded with --loco)
         bool write_whole = false;        // with do_loco: also write <out>.<add|dom>.{bin,id} from the sum of partials
         bool skip_all_missing = false;   // GGRM_ALLMISS_SKIP instead of the reference's NaN poisoning
+        Partition partition = Partition::Auto;
+        int writer_threads = 4;          // pwrite threads per GPU draining the page-locked read-out ring
     };
 
     explicit GrmEngine(Config config);
@@ -89,5 +96,8 @@ void write_id_file(const std::filesystem::path& path, const std::vector<std::str
 
 // C entry point for tests / bindings: runs GrmEngine::compute; returns 0 or the ggrm_status-like negative code,
 // error text in err (NUL-terminated, truncated to err_len).  mode: 0 = A, 1 = D, 2 = AD.
+// _ex adds: partition 0 = auto, 1 = SNP shards, 2 = 2D tiles; writer_threads >= 1.
+extern "C" int gelex_b200_grm_run_ex(const char* bfile, const char* out_prefix, int method, int mode, int do_loco, int chunk_size,
+                                     int precision, int n_gpus, int write_whole, int partition, int writer_threads, char* err, int err_len);
 extern "C" int gelex_b200_grm_run(const char* bfile, const char* out_prefix, int method, int mode, int do_loco, int chunk_size,
                                   int precision, int n_gpus, int write_whole, char* err, int err_len);

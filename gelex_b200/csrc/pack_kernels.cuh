@@ -53,6 +53,29 @@ __global__ void __launch_bounds__(256) pack_rows_kernel(const TAcc* __restrict__
     }
 }
 
+// Rectangular read-out for the 2D-tile multi-GPU mode: rows [row_begin, +row_count) x columns [col_begin, +col_count) of
+// the lower triangle as a dense row-major [row_count][col_count] block (entries above the diagonal or in tiles this
+// handle does not own read as 0), so a rank can ship exactly the super-tiles it owns to their offsets in the .bin file.
+template <typename TAcc, typename TOut>
+__global__ void __launch_bounds__(256) pack_block_kernel(const TAcc* __restrict__ A, const int32_t* __restrict__ slot_of,
+                                                         int64_t row_begin, int64_t row_count, int64_t col_begin,
+                                                         int64_t col_count, TOut* __restrict__ out) {
+    if (blockIdx.x >= row_count) return;
+    const int64_t i = row_begin + blockIdx.x;
+    const int64_t I = i >> 8;
+    const int r = static_cast<int>(i & 255);
+    TOut* dst = out + static_cast<int64_t>(blockIdx.x) * col_count;
+    for (int64_t jl = threadIdx.x; jl < col_count; jl += blockDim.x) {
+        const int64_t j = col_begin + jl;
+        TOut v = TOut(0);
+        if (j <= i) {
+            const int32_t slot = slot_of[I * (I + 1) / 2 + (j >> 8)];
+            if (slot >= 0) v = static_cast<TOut>(A[static_cast<int64_t>(slot) * 65536 + tile_elem_offset<TAcc>(r, static_cast<int>(j & 255))]);
+        }
+        dst[jl] = v;
+    }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) axpy_accum_kernel(T* __restrict__ dst, const T* __restrict__ src, int64_t n) {
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x * 4;

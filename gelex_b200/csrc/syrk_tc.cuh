@@ -48,7 +48,7 @@ template <int kCtaGroup>
 __global__ void __launch_bounds__(256, 1)
 syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ accum, const TcItem* __restrict__ items,
                int num_items, int num_k_blocks, int k_block0, int accumulate, uint32_t ab_format, int cache_hints, int* fault_flag,
-               unsigned long long* wave_ctr, unsigned long long wave_base, int sync_every) {
+               unsigned long long* wave_ctr, unsigned long long wave_base, int sync_every, float* __restrict__ fold) {
     using Cfg = TcConfig<kCtaGroup>;
     constexpr int kStages = Cfg::kStages;
     extern __shared__ uint8_t smem_raw[];
@@ -188,7 +188,11 @@ syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ a
             const uint32_t as = local_it & 1, aphase = (local_it >> 1) & 1;
             ptx::mbar_wait(&tmem_full_bar[as], aphase, fault_flag, 4);
             ptx::tc_fence_after();
-            float* out = accum + item.out_off + static_cast<int64_t>(cta_rank) * kHalfTileElems + row * 4;
+            const int64_t tile_off = item.out_off + static_cast<int64_t>(cta_rank) * kHalfTileElems + row * 4;
+            float* out = accum + tile_off;
+            // LOCO: on the last slab of a chromosome the finished partial is also added into the whole-genome accumulator here,
+            // while the tile is in registers (replaces a separate 3-access whole += partial pass over 5 GB per chromosome)
+            float* out2 = fold != nullptr ? fold + tile_off : nullptr;
 #pragma unroll 1
             for (int chunk = 0; chunk < 8; ++chunk) {
                 uint32_t v[32];
@@ -204,6 +208,12 @@ syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ a
                         r.x += o.x; r.y += o.y; r.z += o.z; r.w += o.w;
                     }
                     if (stream) ptx::st_stream_f4(dst, r, stream_policy); else *dst = r;
+                    if (out2 != nullptr) {
+                        float4* dst2 = reinterpret_cast<float4*>(out2 + (chunk * 8 + q) * (128 * 4));
+                        float4 w = stream ? ptx::ld_stream_f4(dst2, stream_policy) : *dst2;
+                        w.x += r.x; w.y += r.y; w.z += r.z; w.w += r.w;
+                        if (stream) ptx::st_stream_f4(dst2, w, stream_policy); else *dst2 = w;
+                    }
                 }
             }
             ptx::tc_fence_before();

@@ -30,6 +30,8 @@ def load_host():
             raise ImportError(f"{HOST_LIB_PATH} not built; run __graft_entry__.build()")
         h = C.CDLL(str(HOST_LIB_PATH))
         h.gelex_b200_grm_run.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]
+        h.gelex_b200_grm_run_ex.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                            C.c_char_p, C.c_int]
         h.gelex_b200_plan.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64),
                                       C.POINTER(C.c_int), C.c_char_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.c_char_p, C.c_int]
         h.gelex_b200_plan.restype = C.c_int64
@@ -37,13 +39,17 @@ def load_host():
     return _host
 
 
-def grm_run(bfile, out_prefix, method="OSH", mode="A", loco=False, chunk_size=10000, precision=_lib.PREC_FP16, n_gpus=1, write_whole=False):
+PARTITIONS = {"auto": 0, "snp": 1, "tile": 2}
+
+
+def grm_run(bfile, out_prefix, method="OSH", mode="A", loco=False, chunk_size=10000, precision=_lib.PREC_FP16, n_gpus=1, write_whole=False,
+            partition="auto", writer_threads=4):
     """GrmEngine::compute through the C entry point; raises EngineError("<ExceptionName>: message")."""
     h = load_host()
     m = _lib.METHODS[method] if isinstance(method, str) else int(method)
     err = C.create_string_buffer(2048)
-    st = h.gelex_b200_grm_run(str(bfile).encode(), str(out_prefix).encode(), m, MODES[mode], int(loco), int(chunk_size), int(precision),
-                              int(n_gpus), int(write_whole), err, len(err))
+    st = h.gelex_b200_grm_run_ex(str(bfile).encode(), str(out_prefix).encode(), m, MODES[mode], int(loco), int(chunk_size), int(precision),
+                                 int(n_gpus), int(write_whole), PARTITIONS[partition], int(writer_threads), err, len(err))
     if st != 0:
         raise EngineError(st, err.value.decode())
 

@@ -105,6 +105,12 @@ int ggrm_push_device(ggrm_t* h, const uint8_t* d_bed_payload, int64_t snp_begin,
                      int64_t bytes_per_variant);
 /* Drain: every pushed SNP is accumulated, every group is complete.  Blocks until the device is idle. */
 int ggrm_finish(ggrm_t* h);
+/* Same, but returns as soon as the rest of the pass is ENQUEUED.  The last slab is accumulated in row bands, so a read-out
+ * that follows (ggrm_fetch / ggrm_fetch_f64 / ggrm_fetch_block, which wait on the device for exactly the rows they return)
+ * starts with the first rows while the later bands are still on the tensor cores: the D2H of a 5 GB matrix overlaps the
+ * tail of the accumulation instead of following it.  After it only ggrm_fetch*, ggrm_finish (blocks, reports device faults),
+ * ggrm_reset, ggrm_get_timers and ggrm_destroy may be called; no further ggrm_push. */
+int ggrm_finish_async(ggrm_t* h);
 /* Re-arm the handle for another pass (e.g. the dominance pass of a second invocation, or a benchmark step): all
  * accumulators read as zero again, buffers / work lists / streams are reused. */
 int ggrm_reset(ggrm_t* h);
@@ -123,6 +129,17 @@ int ggrm_snp_stats(ggrm_t* h, int64_t snp_begin, int64_t snp_count, int32_t* n0,
  * this handle does not own are returned as 0 so per-rank results can be summed or written at their own offsets. */
 int ggrm_fetch(ggrm_t* h, int kind, int group, int64_t row_begin, int64_t row_count, float* out_lower_rows,
                double* trace_out);
+/* 2D-tile mode read-out: the dense block rows [row_begin, +row_count) x columns [col_begin, +col_count) of the lower
+ * triangle as float32 into `out` (host, caller-owned, row-major with leading dimension `ld` >= col_count elements).
+ * Entries above the diagonal, and entries of tiles this handle does not own, are written as 0.  The writer calls it once
+ * per owned super-tile (ggrm_owned_supertiles) and stores row i of the block at file offset 4*(i(i+1)/2 + col_begin),
+ * min(col_count, i + 1 - col_begin) values - which is how "each GPU's own tiles go straight to the writer". */
+int ggrm_fetch_block(ggrm_t* h, int kind, int group, int64_t row_begin, int64_t row_count, int64_t col_begin,
+                     int64_t col_count, float* out, int64_t ld);
+/* The 2048 x 2048 super-tiles (units of tile ownership, cfg.tile_rank / tile_world) this handle owns, as (super-row,
+ * super-column) index pairs, super-column <= super-row; entry rows/cols = index * 2048.  *count receives the number
+ * owned; at most `capacity` pairs are stored (either array may be NULL to query the count only). */
+int ggrm_owned_supertiles(ggrm_t* h, int64_t* super_rows, int64_t* super_cols, int64_t capacity, int64_t* count);
 /* Same rows in FP64 (only meaningful for GGRM_PREC_FP64; FP32 accumulators are widened). */
 int ggrm_fetch_f64(ggrm_t* h, int kind, int group, int64_t row_begin, int64_t row_count, double* out_lower_rows,
                    double* trace_out);
@@ -185,6 +202,12 @@ int ggrm_synth_bed_device(int device, uint8_t* d_out, int64_t n, int64_t snp_beg
  * over NVLink (cudaDeviceEnablePeerAccess; idempotent), so ggrm_reduce_peer can take the peers' ggrm_accum_buffer
  * pointers directly. */
 int ggrm_enable_peer_access(int device, int peer_device);
+
+/* Page-locked host memory for callers that want ggrm_push / ggrm_fetch* to copy without staging (the host engine's
+ * read-out ring).  Plain cudaHostAlloc / cudaFreeHost, exposed so that a host written against this header needs no CUDA
+ * headers of its own. */
+int ggrm_host_alloc(int64_t bytes, void** out);
+int ggrm_host_free(void* p);
 
 /* Library / device facts for the harness. */
 int ggrm_device_count(void);

@@ -289,6 +289,90 @@ def test_tile_partition_and_snp_shard_recombine():
         x.close()
 
 
+def test_fetch_block_and_owned_supertiles():
+    # rectangular read-out used by the 2D-tile writer: blocks agree with the packed rows, zeros above the diagonal and in
+    # tiles of other ranks; the owned super-tile lists of all ranks partition the triangle
+    n, m = 4300, 700   # 3 super-rows of 2048
+    bed = g.synth_bed_host(n, 0, m, 83, 0.01)
+    full = run_gpu(bed, n, m, 1, (0,), g.PREC_FP64)
+    whole, _ = full.fetch(0, g.GROUP_WHOLE, dtype=np.float64)
+    dense = np.zeros((n, n))
+    dense[np.tril_indices(n)] = whole
+    assert full.owned_supertiles() == [(0, 0), (1, 0), (1, 1), (2, 0), (2, 1), (2, 2)]
+    blk = full.fetch_block(0, g.GROUP_WHOLE, 2048, 2048, 0, 2048)
+    assert np.array_equal(blk, dense[2048:4096, 0:2048].astype(np.float32))
+    blk = full.fetch_block(0, g.GROUP_WHOLE, 4096, n - 4096, 4096, n - 4096)  # ragged diagonal super-tile
+    assert np.array_equal(blk, dense[4096:, 4096:].astype(np.float32))
+    blk = full.fetch_block(0, g.GROUP_WHOLE, 100, 57, 31, 400)  # arbitrary block crossing the diagonal
+    assert np.array_equal(blk, dense[100:157, 31:431].astype(np.float32))
+    full.close()
+    seen = []
+    acc16 = np.zeros((n, n), dtype=np.float32)
+    for r in range(2):
+        acc = run_gpu(bed, n, m, 1, (0,), g.PREC_FP16, tile_rank=r, tile_world=2)
+        mine = acc.owned_supertiles()
+        assert mine, "every rank owns something"
+        seen += mine
+        for si, sj in mine:
+            r0, c0 = si * 2048, sj * 2048
+            rows, cols = min(2048, n - r0), min(2048, n - c0)
+            acc16[r0:r0 + rows, c0:c0 + cols] += acc.fetch_block(0, g.GROUP_WHOLE, r0, rows, c0, cols)
+        # a block of a super-tile this rank does NOT own reads as zeros
+        other = next(t for t in [(0, 0), (1, 0), (1, 1), (2, 0), (2, 1), (2, 2)] if t not in mine)
+        z = acc.fetch_block(0, g.GROUP_WHOLE, other[0] * 2048, min(2048, n - other[0] * 2048), other[1] * 2048, min(2048, n - other[1] * 2048))
+        assert not z.any()
+        acc.close()
+    assert sorted(seen) == [(0, 0), (1, 0), (1, 1), (2, 0), (2, 1), (2, 2)]
+    one = run_gpu(bed, n, m, 1, (0,), g.PREC_FP16)
+    p16, _ = one.fetch(0, g.GROUP_WHOLE)
+    one.close()
+    assert np.array_equal(acc16[np.tril_indices(n)], p16)  # tile ranks reproduce the single-GPU FP32 values bit for bit
+
+
+def test_finish_async_banded_readout_matches_blocking(monkeypatch):
+    # ggrm_finish_async: the last slab is accumulated in row bands and every read-out waits only for the bands it needs.
+    # Same kernels, same order per tile -> identical bits to the blocking path, for full and piecewise reads, LOCO partials
+    # and the whole-genome sum folded inside the last slab.
+    monkeypatch.setenv("GGRM_BAND_MIN_TILES", "4")  # n = 4300 has 153 tiles in 3 strips: force one band per strip
+    n, m = 4300, 1500
+    bed = g.synth_bed_host(n, 0, m, 91, 0.01)
+    groups = [(0, 400), (400, 1500)]
+
+    def build(async_finish, **kw):
+        acc = g.Accumulator(n, m, method=3, want_add=True, want_dom=True, precision=g.PREC_FP16, chunk_snps=512, **kw)
+        for s in range(0, m, 300):
+            acc.push(bed[s:min(m, s + 300)], s)
+        (acc.finish_async if async_finish else acc.finish)()
+        return acc
+
+    for kw in ({}, {"groups": groups, "keep_whole": True}):
+        ref = build(False, **kw)
+        acc = build(True, **kw)
+        targets = [(k, g.GROUP_WHOLE) for k in (0, 1)] + ([(0, 1), (1, 0)] if kw else [])
+        for kind, group in targets:
+            want, tr_want = ref.fetch(kind, group)
+            got, tr = acc.fetch(kind, group)
+            assert np.array_equal(got, want) and tr == tr_want, (kw, kind, group)
+        # piecewise, out of order, straddling the 2048-row band boundaries; rectangular blocks
+        want, _ = ref.fetch(0, g.GROUP_WHOLE)
+        acc2 = build(True, **kw)
+        for r0, cnt in ((4000, 300), (2000, 100), (0, 2048), (2048, 1952)):
+            part, _ = acc2.fetch(0, g.GROUP_WHOLE, r0, cnt)
+            assert np.array_equal(part, want[g.tri(r0):g.tri(r0 + cnt)])
+        blk = acc2.fetch_block(0, g.GROUP_WHOLE, 4096, n - 4096, 2048, 2048)
+        dense = np.zeros((n, n), dtype=np.float32)
+        dense[np.tril_indices(n)] = want
+        assert np.array_equal(blk, dense[4096:, 2048:4096])
+        acc2.finish()  # blocking finish after the async one is allowed and reports device faults
+        t = acc2.timers()
+        assert t["pass_ms"] > 0 and t["syrk_launches"] >= 3
+        acc2.reset()   # and the handle can be re-armed
+        acc2.push(bed[:300], 0)
+        acc2.finish()
+        for a in (ref, acc, acc2):
+            a.close()
+
+
 def test_error_codes_follow_reference_semantics():
     acc = g.Accumulator(100, 50, method=1, precision=g.PREC_FP64)
     bed = g.synth_bed_host(100, 0, 50, 1, 0.0)
