@@ -82,6 +82,30 @@ class ClockSampler:
                 "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """Multi-rank runs: keep this rank's threads (and, by first touch, its pinned buffers) on the NUMA node its GPU hangs off, so
+    the eight ranks' H2D/D2H streams do not all cross the socket interconnect.  Best effort; returns a note for the JSON line."""
+    try:
+        bus = subprocess.run(["nvidia-smi", f"--id={local_rank}", "--query-gpu=pci.bus_id", "--format=csv,noheader"], capture_output=True,
+                             text=True, timeout=20).stdout.strip().lower()
+        if bus.startswith("00000000:"):
+            bus = bus[4:]  # sysfs uses a 4-digit PCI domain
+        node = int((Path("/sys/bus/pci/devices") / bus / "numa_node").read_text())
+        if node < 0:
+            return "numa: single node"
+        cpus = set()
+        for part in (Path(f"/sys/devices/system/node/node{node}") / "cpulist").read_text().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return f"numa: node {node} has no allowed cpus"
+        os.sched_setaffinity(0, cpus)
+        return f"numa: rank bound to node {node} ({len(cpus)} cpus)"
+    except Exception as e:  # noqa: BLE001
+        return f"numa: not bound ({type(e).__name__})"
+
+
 # ---------------------------------------------------------------------------------------------------------------- CPU reference arm
 def cpu_threads():
     return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
@@ -182,6 +206,7 @@ def gpu_arm(args):
     local = int(os.environ.get("LOCAL_RANK", 0))
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run --nproc-per-node {args.gpus}")
+    numa_note = bind_to_gpu_numa_node(local) if world > 1 else "numa: single rank, not bound"
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -317,10 +342,11 @@ def gpu_arm(args):
         launches = max(1.0, tm["syrk_launches"] / args.steps)
         fl_rank = flops(n, ms)
         achieved = fl_rank / (syrk_ms * 1e-3) / 1e12 if syrk_ms > 0 else 0.0
-        traffic = None
+        traffic, traffic_launch = None, None
         tp = ROOT / "profiles" / "roofline_traffic.json"
         if tp.exists():
-            traffic = json.loads(tp.read_text()).get("syrk_dram_bytes_per_launch")
+            tj = json.loads(tp.read_text())
+            traffic, traffic_launch = tj.get("syrk_dram_bytes_per_launch"), tj.get("launch")
         line = {
             "metric": METRIC, "value": fl / (dt / args.steps) / 1e12, "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "wall_s_per_grm": dt / args.steps,
@@ -334,7 +360,7 @@ def gpu_arm(args):
                                       f"SNP-sharded over {world} GPUs + reduce-scatter of FP32 partial GRMs by 2048-row slices over NVLink peer memory (CUDA IPC, P2P loads); each rank fetches its own rows"),
                        "l2": "inputs (packed BED 6.25 GB, 16-bit operand slabs 0.8 GB, accumulator 5 GB) are larger than the 126 MB L2; no flush needed",
                        "timing": "CUDA events around the K steps, barrier + cuda synchronize on both sides, max over ranks; kernel phases by CUDA events on the library's streams",
-                       "chunk_snps": int(os.environ.get("GGRM_CHUNK_SNPS", 16384))},
+                       "chunk_snps": int(os.environ.get("GGRM_CHUNK_SNPS", 16384)), "host": numa_note},
             "device_pass_ms_per_step": tm["pass_ms"] / args.steps,
             "wall_clock_ms_per_step": wall_checks[0][1] / args.steps * 1e3,
             "phases_ms_per_step": {k: tm[k] / args.steps for k in ("h2d_ms", "prep_ms", "expand_ms", "syrk_ms")},
@@ -348,7 +374,11 @@ def gpu_arm(args):
                     "phases_ms_per_step": {k: tm_e[k] / args.steps for k in ("h2d_ms", "prep_ms", "expand_ms", "syrk_ms", "fetch_ms")}},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": sustained, "unit": "TFLOP/s", "frac": achieved / sustained,
                          "traffic": traffic, "kernel": "syrk_tc_kernel<2> (tcgen05 cta_group::2, UMMA 256x256x16)",
+                         "traffic_launch": traffic_launch,
                          "flops_per_launch": fl_rank / launches, "avg_launch_ms": syrk_ms / launches, "launches_per_step": launches,
+                         "launch_note": "achieved = this rank's credited flops of a step / its summed SYRK launch time (CUDA events on the library's compute "
+                                        "stream); a step is ceil(m_rank/16384) equal slabs, the last one launched as up to 8 row bands; traffic is the ncu "
+                                        "--set full DRAM bytes of ONE steady-state 16384-SNP slab launch (traffic_launch)",
                          "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({how}); burst peak {burst} -> frac {achieved / burst:.3f}"},
         }
     for p_ in peers:

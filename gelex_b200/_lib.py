@@ -68,7 +68,7 @@ EXPORTS = [
     "ggrm_fetch_normalized", "ggrm_fetch_loco", "ggrm_get_timers", "ggrm_decode_chunk", "ggrm_standardise_chunk",
     "ggrm_synth_bed_host", "ggrm_synth_bed_device", "ggrm_device_count", "ggrm_version", "ggrm_enable_peer_access",
     "ggrm_ipc_export", "ggrm_ipc_open", "ggrm_ipc_close", "ggrm_row_slice",
-    "ggrm_fetch_block", "ggrm_owned_supertiles", "ggrm_host_alloc", "ggrm_host_free",
+    "ggrm_fetch_block", "ggrm_owned_supertiles", "ggrm_host_alloc", "ggrm_host_free", "ggrm_bin_to_dense", "ggrm_assoc_chunk",
 ]
 
 _lib = None
@@ -108,10 +108,12 @@ def load() -> C.CDLL:
     lib.ggrm_row_slice.argtypes = [vp, i64, i64, C.POINTER(i64), C.POINTER(i64)]
     lib.ggrm_fetch_block.argtypes = [vp, C.c_int, C.c_int, i64, i64, i64, i64, vp, i64]
     lib.ggrm_owned_supertiles.argtypes = [vp, C.POINTER(i64), C.POINTER(i64), i64, C.POINTER(i64)]
+    lib.ggrm_bin_to_dense.argtypes = [C.c_int, vp, vp, i64, vp, i64, dbl, vp]
     lib.ggrm_host_alloc.argtypes = [i64, C.POINTER(vp)]
     lib.ggrm_host_free.argtypes = [vp]
     lib.ggrm_decode_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, vp]
     lib.ggrm_standardise_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, C.c_int, C.c_int, C.c_int, vp, vp]
+    lib.ggrm_assoc_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, C.c_int, C.c_int, vp, vp]
     lib.ggrm_synth_bed_host.argtypes = [vp, i64, i64, i64, u64, dbl]
     lib.ggrm_synth_bed_device.argtypes = [C.c_int, vp, i64, i64, i64, u64, dbl]
     lib.ggrm_device_count.argtypes = []
@@ -311,6 +313,23 @@ def standardise_chunk(payload, n_raw, method, kind, n_out=None, raw_to_out=None,
     m = METHODS[method] if isinstance(method, str) else int(method)
     st = lib.ggrm_standardise_chunk(device, _ptr(payload), c, bpv, n_raw, n_out, _ptr(r2o), m, kind, all_missing_policy,
                                     _ptr(out), _ptr(freq))
+    if st != 0:
+        raise GrmError(st, lib.ggrm_last_error(None).decode())
+    return out.T, freq
+
+
+def assoc_chunk(payload, n_raw, method, kind, n_out=None, raw_to_out=None, device=0):
+    """dispatch_assoc_chunk_by_method (assoc_detail.cpp:28-47): decode + centre-family code policy + per-SNP A1 frequency."""
+    lib = load()
+    n_out = n_raw if n_out is None else n_out
+    bpv = (n_raw + 3) // 4
+    payload = np.ascontiguousarray(payload, dtype=np.uint8)
+    c = payload.size // bpv
+    out = np.empty((c, n_out), dtype=np.float64)
+    freq = np.empty(c, dtype=np.float64)
+    r2o = None if raw_to_out is None else np.ascontiguousarray(raw_to_out, dtype=np.int32)
+    m = METHODS[method] if isinstance(method, str) else int(method)
+    st = lib.ggrm_assoc_chunk(device, _ptr(payload), c, bpv, n_raw, n_out, _ptr(r2o), m, kind, _ptr(out), _ptr(freq))
     if st != 0:
         raise GrmError(st, lib.ggrm_last_error(None).decode())
     return out.T, freq

@@ -91,6 +91,20 @@ extern "C" int ggrm_standardise_chunk(int device, const uint8_t* bed_payload, in
     GGRM_STATELESS_END
 }
 
+// dispatch_assoc_chunk_by_method (src/pipeline/assoc_detail.cpp:28-47): the GWAS scan's chunk pre-processing is the same decode +
+// code policy, restricted to the centre-family methods, with the per-SNP A1 frequencies handed to the result writer.
+extern "C" int ggrm_assoc_chunk(int device, const uint8_t* bed_payload, int64_t snp_count, int64_t bytes_per_variant, int64_t n_raw,
+                                int64_t n_out, const int32_t* raw_to_out, int method, int kind, double* out_colmajor, double* freq) {
+    GGRM_STATELESS_BEGIN
+    if (method != GGRM_CENTER_HWE && method != GGRM_ORTH_CENTER_HWE && method != GGRM_CENTER && method != GGRM_ORTH_CENTER)
+        throw CudaError{GGRM_ERR_INVALID_ARGUMENT,
+                        "assoc --geno-method supports only center-family methods: 2 (center-hwe), 4 (orth-center-hwe), 6 (center), 8 (orth-center)"};
+    if (kind != GGRM_KIND_ADD && kind != GGRM_KIND_DOM) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "kind must be 0 (add) or 1 (dom)"};
+    decode_common(device, bed_payload, snp_count, bytes_per_variant, n_raw, n_out, raw_to_out, method, kind, GGRM_ALLMISS_REFERENCE_NAN, true,
+                  out_colmajor, freq);
+    GGRM_STATELESS_END
+}
+
 extern "C" int ggrm_enable_peer_access(int device, int peer_device) {
     GGRM_STATELESS_BEGIN
     check_device(device, nullptr);
@@ -118,6 +132,36 @@ extern "C" int ggrm_ipc_close(int device, void* d_ptr) {
     GGRM_STATELESS_BEGIN
     check_device(device, nullptr);
     if (d_ptr != nullptr) GGRM_CUDA(cudaIpcCloseMemHandle(d_ptr));
+    GGRM_STATELESS_END
+}
+
+extern "C" int ggrm_bin_to_dense(int device, const float* whole_packed, const float* chr_packed, int64_t n_file, const int64_t* target_to_file,
+                                 int64_t n_target, double denominator, double* out_colmajor) {
+    GGRM_STATELESS_BEGIN
+    check_device(device, nullptr);
+    if (whole_packed == nullptr || out_colmajor == nullptr) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "null argument"};
+    if (n_file <= 0 || n_target <= 0 || n_file > (int64_t{1} << 30) || n_target > (int64_t{1} << 30))
+        throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "matrix sizes must be positive"};
+    if (target_to_file == nullptr && n_target != n_file) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "identity map requires n_target == n_file"};
+    if (target_to_file != nullptr)
+        for (int64_t t = 0; t < n_target; ++t)
+            if (target_to_file[t] < -1 || target_to_file[t] >= n_file) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "target_to_file entry out of range"};
+    const size_t packed = static_cast<size_t>(n_file) * static_cast<size_t>(n_file + 1) / 2;
+    ScratchFree sf;
+    float* d_w = sf.alloc<float>(packed);
+    float* d_c = chr_packed != nullptr ? sf.alloc<float>(packed) : nullptr;
+    double* d_out = sf.alloc<double>(static_cast<size_t>(n_target) * static_cast<size_t>(n_target));
+    int64_t* d_map = nullptr;
+    GGRM_CUDA(cudaMemcpy(d_w, whole_packed, packed * sizeof(float), cudaMemcpyHostToDevice));
+    if (d_c != nullptr) GGRM_CUDA(cudaMemcpy(d_c, chr_packed, packed * sizeof(float), cudaMemcpyHostToDevice));
+    if (target_to_file != nullptr) {
+        d_map = sf.alloc<int64_t>(static_cast<size_t>(n_target));
+        GGRM_CUDA(cudaMemcpy(d_map, target_to_file, static_cast<size_t>(n_target) * sizeof(int64_t), cudaMemcpyHostToDevice));
+    }
+    const unsigned nb = static_cast<unsigned>((n_target + 31) / 32);
+    bin_to_dense_kernel<<<dim3(nb, nb), 256>>>(d_w, d_c, d_map, n_target, denominator, d_out);
+    GGRM_CUDA(cudaGetLastError());
+    GGRM_CUDA(cudaMemcpy(out_colmajor, d_out, static_cast<size_t>(n_target) * static_cast<size_t>(n_target) * sizeof(double), cudaMemcpyDeviceToHost));
     GGRM_STATELESS_END
 }
 

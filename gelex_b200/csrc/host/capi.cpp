@@ -5,6 +5,7 @@
 
 #include "exceptions.h"
 #include "grm_engine.h"
+#include "grm_loader.h"
 #include "plink_meta.h"
 
 using namespace gelex::b200;
@@ -103,4 +104,48 @@ extern "C" int64_t gelex_b200_plan(const char* bfile, int mode, int do_loco, int
         set_err(err, err_len, e.what());
         return -1;
     }
+}
+
+// GrmLoader / LocoGRMLoader through C (tests, bindings).  ids = n_ids canonical sample ids "FID\x1FIID" separated by '\n' with
+// their target rows in `targets` (n_ids == 0: no id_map, the file's own order).  chr_prefix NULL/"" -> GrmLoader::load (normalize != 0)
+// or load_unnormalized; otherwise LocoGRMLoader(prefix, id_map).load_loco_grm(chr_prefix, id_map).  Returns the matrix size (the
+// column-major matrix is written to out when out_cap >= size^2; call with out == NULL to query) or a negative status.
+extern "C" int64_t gelex_b200_grm_load(const char* prefix, const char* chr_prefix, int normalize, const char* ids, const int64_t* targets,
+                                       int64_t n_ids, double* out, int64_t out_cap, char* err, int err_len) {
+    try {
+        if (prefix == nullptr) throw ArgumentValidationException("null argument");
+        IdMap id_map;
+        if (n_ids > 0) {
+            if (ids == nullptr || targets == nullptr) throw ArgumentValidationException("null id list");
+            const std::string all(ids);
+            size_t pos = 0;
+            for (int64_t k = 0; k < n_ids; ++k) {
+                const size_t nl = all.find('\n', pos);
+                id_map[all.substr(pos, nl == std::string::npos ? std::string::npos : nl - pos)] = targets[k];
+                pos = nl == std::string::npos ? all.size() : nl + 1;
+            }
+        }
+        DenseMatrix m;
+        if (chr_prefix != nullptr && chr_prefix[0] != '\0') {
+            if (n_ids == 0) {  // every sample of the whole-genome file, in file order
+                const GrmLoader probe(prefix);
+                for (int64_t i = 0; i < probe.num_samples(); ++i) id_map[probe.sample_ids()[static_cast<size_t>(i)]] = i;
+            }
+            const LocoGRMLoader loco(prefix, id_map);
+            m = loco.load_loco_grm(chr_prefix, id_map);
+        } else {
+            const GrmLoader loader(prefix);
+            if (n_ids > 0) m = normalize ? loader.load(id_map) : loader.load_unnormalized(id_map);
+            else m = normalize ? loader.load() : loader.load_unnormalized();
+        }
+        if (out != nullptr && out_cap >= m.n * m.n) std::memcpy(out, m.data.data(), m.data.size() * sizeof(double));
+        set_err(err, err_len, "");
+        return m.n;
+    } catch (const FileNotFoundException& e) { set_err(err, err_len, std::string("FileNotFoundException: ") + e.what()); return -10;
+    } catch (const FileOpenException& e) { set_err(err, err_len, std::string("FileOpenException: ") + e.what()); return -11;
+    } catch (const FileFormatException& e) { set_err(err, err_len, std::string("FileFormatException: ") + e.what()); return GGRM_ERR_FILE_FORMAT;
+    } catch (const InvalidInputException& e) { set_err(err, err_len, std::string("InvalidInputException: ") + e.what()); return GGRM_ERR_INVALID_ARGUMENT;
+    } catch (const GelexException& e) { set_err(err, err_len, std::string("GelexException: ") + e.what()); return GGRM_ERR_CUDA;
+    } catch (const std::bad_alloc&) { set_err(err, err_len, "std::bad_alloc"); return GGRM_ERR_OUT_OF_MEMORY;
+    } catch (const std::exception& e) { set_err(err, err_len, std::string("std::exception: ") + e.what()); return -99; }
 }

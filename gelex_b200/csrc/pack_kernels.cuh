@@ -95,6 +95,48 @@ __global__ void __launch_bounds__(256) axpy_accum_kernel(T* __restrict__ dst, co
     }
 }
 
+// Consumer side of the .bin format: packed float32 lower rows of one or two files already on the device ->
+// the dense symmetric FP64 matrix GrmLoader / LocoGRMLoader hand to the solvers (src/data/grm/grm_loader.cpp:125-243,
+// loco_grm_loader.cpp:62-76):  out(i, j) = (W(f(i), f(j)) - C(f(i), f(j))) / denom, f = target row -> file row (-1: the
+// target has no sample in the file, its row and column stay 0), column-major.  One 32 x 32 tile per block, lower block
+// triangle only: the tile is gathered once with its contiguous file index on threadIdx.x and written twice (as is and
+// transposed through shared memory), so both the reads and the 8-byte writes are coalesced for the identity map.
+__global__ void __launch_bounds__(256) bin_to_dense_kernel(const float* __restrict__ W, const float* __restrict__ C,
+                                                           const int64_t* __restrict__ target_to_file, int64_t n_target,
+                                                           double denom, double* __restrict__ out) {
+    const int64_t bi = blockIdx.y, bj = blockIdx.x;
+    if (bj > bi) return;
+    __shared__ double tile[32][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+    const int64_t tj = bj * 32 + tx;
+    const int64_t fj = tj < n_target ? (target_to_file != nullptr ? target_to_file[tj] : tj) : -1;
+#pragma unroll
+    for (int r = ty; r < 32; r += 8) {
+        const int64_t ti = bi * 32 + r;
+        const int64_t fi = ti < n_target ? (target_to_file != nullptr ? target_to_file[ti] : ti) : -1;
+        double v = 0.0;
+        if (fi >= 0 && fj >= 0) {
+            const int64_t a = fi > fj ? fi : fj, b = fi > fj ? fj : fi;
+            const int64_t off = a * (a + 1) / 2 + b;
+            v = static_cast<double>(W[off]);
+            if (C != nullptr) v -= static_cast<double>(C[off]);
+            v = __ddiv_rn(v, denom);
+        }
+        tile[r][tx] = v;  // tile[row i][col j]
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = ty; r < 32; r += 8) {
+        // out(i, j) at out[j * n + i]: column j = bj*32 + r, rows i = bi*32 + tx contiguous
+        const int64_t j = bj * 32 + r, i = bi * 32 + tx;
+        if (j < n_target && i < n_target) out[j * n_target + i] = tile[tx][r];
+        if (bi != bj) {  // mirror: out(j, i) at out[i * n + j]: column i = bi*32 + r, rows j = bj*32 + tx contiguous
+            const int64_t i2 = bi * 32 + r, j2 = bj * 32 + tx;
+            if (i2 < n_target && j2 < n_target) out[i2 * n_target + j2] = tile[r][tx];
+        }
+    }
+}
+
 constexpr int kMaxPeers = 7;
 struct PeerPtrs {
     const void* p[kMaxPeers];

@@ -35,6 +35,8 @@ def load_host():
         h.gelex_b200_plan.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64),
                                       C.POINTER(C.c_int), C.c_char_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.c_char_p, C.c_int]
         h.gelex_b200_plan.restype = C.c_int64
+        h.gelex_b200_grm_load.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_char_p, C.c_int]
+        h.gelex_b200_grm_load.restype = C.c_int64
         _host = h
     return _host
 
@@ -72,3 +74,29 @@ def plan(bfile, mode="A", loco=False, max_samples=1 << 22, max_items=4096):
     k = n_items.value
     return {"n_out": int(n_out), "n_raw": n_raw.value, "m": m.value, "dense": bool(dense.value), "raw_to_out": r2o[:n_raw.value].copy(),
             "items": [(lines[i], int(gb[i]), int(ge[i])) for i in range(k)], "pattern_suffix": lines[k]}
+
+
+def load_grm(prefix, chr_prefix=None, normalize=True, id_map=None):
+    """GrmLoader::load / load_unnormalized (optionally filtered + reordered by id_map = {(fid, iid): target_row}) or, with chr_prefix,
+    LocoGRMLoader::load_loco_grm: dense symmetric FP64 matrix as the reference's consumers receive it.  The expansion runs on the GPU."""
+    h = load_host()
+    ids, targets, n_ids = None, None, 0
+    if id_map:
+        keys = list(id_map.keys())
+        ids = "\n".join(f"{fid}\x1f{iid}" for fid, iid in keys).encode()
+        targets = np.array([id_map[k] for k in keys], dtype=np.int64)
+        n_ids = len(keys)
+    err = C.create_string_buffer(2048)
+    cp = str(chr_prefix).encode() if chr_prefix else None
+    tp = targets.ctypes.data_as(C.c_void_p) if targets is not None else None
+    if n_ids:
+        n = int(targets.max()) + 1
+    else:
+        id_path = Path(str(prefix) + ".id")
+        n = sum(1 for ln in id_path.read_text().split("\n") if ln) if id_path.exists() else 0
+    out = np.empty((n, n), dtype=np.float64, order="F")
+    got = h.gelex_b200_grm_load(str(prefix).encode(), cp, int(normalize), ids, tp, n_ids, out.ctypes.data_as(C.c_void_p), n * n, err, len(err))
+    if got < 0:
+        raise EngineError(int(got), err.value.decode())
+    assert got == n, (got, n)
+    return out

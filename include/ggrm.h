@@ -175,6 +175,16 @@ int ggrm_row_slice(ggrm_t* h, int64_t row_begin, int64_t row_end, int64_t* elem_
 int ggrm_fetch_normalized(ggrm_t* h, int kind, int group, int64_t row_begin, int64_t row_count, double* out_lower_rows);
 int ggrm_fetch_loco(ggrm_t* h, int kind, int group, int64_t row_begin, int64_t row_count, double* out_lower_rows);
 
+/* The same consumer-side arithmetic from FILES (the reader half of SURVEY 8f-1): `whole_packed` (and optionally
+ * `chr_packed`) are the float32 payloads of .bin files with n_file samples (host pointers, e.g. the mmap).  Writes the
+ * dense symmetric column-major FP64 matrix out(i, j) = (W(f(i), f(j)) - C(f(i), f(j))) / denominator for i, j < n_target,
+ * f = target_to_file (NULL = identity; -1 = no such sample: row and column are 0) - GrmLoader::load_unnormalized(id_map)
+ * (grm_loader.cpp:171-231) with denominator 1, GrmLoader::load (:125-131) with trace/n, LocoGRMLoader::load_loco_grm
+ * (loco_grm_loader.cpp:62-76) with chr_packed and k_whole - k_chr.  The caller computes the denominators from the file
+ * diagonals (n values) so their summation order is the reference's. */
+int ggrm_bin_to_dense(int device, const float* whole_packed, const float* chr_packed, int64_t n_file,
+                      const int64_t* target_to_file, int64_t n_target, double denominator, double* out_colmajor);
+
 /* Phase timers (CUDA events on the handle's streams), milliseconds accumulated since create:
  * [0] H2D copies  [1] repack+count+stats  [2] expand  [3] SYRK  [4] pack+D2H  [5] SYRK launches  [6] all kernels launched
  * [7] passes: first push enqueued -> last accumulation finished (events on the copy / compute streams) */
@@ -189,6 +199,13 @@ int ggrm_decode_chunk(int device, const uint8_t* bed_payload, int64_t snp_count,
 int ggrm_standardise_chunk(int device, const uint8_t* bed_payload, int64_t snp_count, int64_t bytes_per_variant,
                            int64_t n_raw, int64_t n_out, const int32_t* raw_to_out, int method, int kind,
                            int all_missing_policy, double* out_colmajor, double* freq);
+
+/* Next consumer of the same two stages: the GWAS scan's chunk pre-processing,
+ * dispatch_assoc_chunk_by_method (src/pipeline/assoc_detail.cpp:28-47) = load_chunk + process_matrix<GT>(method, Z, &freqs)
+ * restricted to the centre-family methods 2, 4, 6, 8 (anything else: GGRM_ERR_INVALID_ARGUMENT with the reference's
+ * message).  kind = 0 additive model, 1 dominance model.  Output as ggrm_standardise_chunk. */
+int ggrm_assoc_chunk(int device, const uint8_t* bed_payload, int64_t snp_count, int64_t bytes_per_variant, int64_t n_raw,
+                     int64_t n_out, const int32_t* raw_to_out, int method, int kind, double* out_colmajor, double* freq);
 
 /* ---- Synthetic PLINK BED payload: p_j~U(0.05,0.5), HWE genotypes, i.i.d. missing -------------------
  * Counter-based integer RNG, bit-identical on host and device.  Writes snp_count rows of ceil(n/4) bytes for SNPs

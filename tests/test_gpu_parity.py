@@ -95,6 +95,30 @@ def test_standardise_vs_oracle_random():
             assert close(z, zr, rtol=1e-12, atol=1e-13)
 
 
+def test_assoc_chunk_preprocessing_center_family_only(golden_dir):
+    # the GWAS scan's chunk pre-processing (assoc_detail.cpp:28-47) reuses the decode + policy kernels; only the
+    # centre-family methods are accepted, with the reference's message otherwise
+    n = 1201
+    fam = [(f"f{i % 3}", f"s{(i * 7919) % n}") for i in range(n)]  # shuffled IDs: the projection is part of the stage
+    ids, r2o = plink_io.sample_order(fam)
+    bed = g.synth_bed_host(n, 0, 150, 13, 0.03)
+    raw = o.decode_chunk(bed, n, len(ids), r2o)
+    for method in (2, 4, 6, 8):
+        for kind in (0, 1):
+            z, f = g.assoc_chunk(bed, n, method, kind, n_out=len(ids), raw_to_out=r2o)
+            zr, fr = o.process_matrix(raw, method, kind)
+            assert np.array_equal(f, fr)  # A1 frequency written to the .gwas.tsv: bit-exact
+            assert close(z, zr, rtol=1e-12, atol=1e-13)
+    d = np.load(golden_dir / "tiny_chunks.npz")  # outputs of the unmodified reference's process_matrix
+    bedt, n_raw_t, ids_t, r2o_t, _ = load_tiny(golden_dir)
+    z, f = g.assoc_chunk(bedt, n_raw_t, 4, 1, n_out=len(ids_t), raw_to_out=r2o_t)
+    assert np.array_equal(f, d["freq_4_D"]) and close(z, d["z_4_D"], rtol=1e-12, atol=1e-13)
+    for method in (1, 3, 5, 7):
+        with pytest.raises(g.GrmError) as e:
+            g.assoc_chunk(bed, n, method, 0, n_out=len(ids), raw_to_out=r2o)
+        assert e.value.status == -1 and "supports only center-family methods" in e.value.message
+
+
 def test_all_missing_snp_policy():
     n = 64
     geno = np.random.default_rng(2).integers(0, 3, size=(n, 6)).astype(np.float64)

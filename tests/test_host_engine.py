@@ -179,3 +179,84 @@ def test_cli_is_a_drop_in(golden_dir, tmp_path):
     got, ref = plink_io.read_bin(tmp_path / "d.add.bin", 36).astype(np.float64), plink_io.read_bin(golden_dir / "tiny_OSH.add.bin", 36).astype(np.float64)
     diag = np.cumsum(np.arange(1, 37)) - 1
     assert np.max(np.abs(got / (got[diag].sum() / 36) - ref / (ref[diag].sum() / 36))) < 5e-3  # m = 96 only
+
+
+# ------------------------------------------------------------------------------------------------ consumer side
+def test_grm_loader_validation_errors_need_no_gpu(golden_dir, tmp_path):
+    # GrmLoader::GrmLoader (grm_loader.cpp:47-123): id parsing and the exact-size check happen before any device work
+    import shutil
+
+    shutil.copy(golden_dir / "tiny_SH.add.id", tmp_path / "x.add.id")
+    (tmp_path / "x.add.bin").write_bytes((golden_dir / "tiny_SH.add.bin").read_bytes()[:-4])
+    with pytest.raises(engine.EngineError, match="FileFormatException.*file size mismatch. Expected 2664 bytes \\(36 samples\\), got 2660 bytes"):
+        engine.load_grm(tmp_path / "x.add")
+    (tmp_path / "y.id").write_text("F1 s1\n")
+    (tmp_path / "y.bin").write_bytes(b"\0" * 4)
+    with pytest.raises(engine.EngineError, match="FileFormatException.*invalid ID line 'F1 s1' \\(expected FID and IID\\)"):
+        engine.load_grm(tmp_path / "y")
+    (tmp_path / "z.id").write_text("\n\n")
+    (tmp_path / "z.bin").write_bytes(b"")
+    with pytest.raises(engine.EngineError, match="FileFormatException.*no sample IDs found"):
+        engine.load_grm(tmp_path / "z")
+    with pytest.raises(engine.EngineError, match="InvalidInputException.*sample ID 'nope.*' not found in GRM file"):
+        engine.load_grm(golden_dir / "tiny_SH.add", id_map={("nope", "x"): 0})
+    with pytest.raises(engine.EngineError, match="InvalidInputException: LOCO error: GRM file not found"):
+        engine.load_grm(golden_dir / "tiny_OCH.add", chr_prefix=tmp_path / "missing.chr9")
+
+
+@pytest.mark.gpu
+def test_grm_loaders_match_reference_outputs(golden_dir):
+    # The fixtures are the dense matrices the UNMODIFIED reference's GrmLoader::load and LocoGRMLoader::load_loco_grm returned for the
+    # golden .bin files (tests/golden/make_golden.py).  Same float32 inputs, same FP64 operations in the same order -> same bits.
+    gold = np.load(golden_dir / "tiny_loaders.npz")
+    got = engine.load_grm(golden_dir / "tiny_SH.add")
+    assert np.array_equal(got, gold["SH_add_normalized"])
+    for c in ("1", "2", "X", "7"):
+        got = engine.load_grm(golden_dir / "tiny_OCH.add", chr_prefix=str(golden_dir / "tiny_OCH.add") + f".chr{c}")
+        assert np.array_equal(got, gold[f"OCH_add_loco_chr{c}"]), c
+    # filter + reorder (GrmLoader::load_unnormalized(id_map), grm_loader.cpp:171-231) against a numpy statement of the same rule
+    n = 36
+    packed = plink_io.read_bin(golden_dir / "tiny_SH.add.bin", n).astype(np.float64)
+    full = np.zeros((n, n))
+    full[np.tril_indices(n)] = packed
+    full = full + np.tril(full, -1).T
+    ids = [tuple(ln.split("\t")) for ln in (golden_dir / "tiny_SH.add.id").read_text().split("\n") if ln]
+    rng = np.random.default_rng(5)
+    pick = rng.permutation(n)[:20]
+    id_map = {ids[f]: t for t, f in zip([0, 2, 3, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19, 21, 22], pick)}  # rows 1, 4, 20 stay empty
+    want = np.zeros((23, 23))
+    for (fa, ta) in zip(pick, id_map.values()):
+        for (fb, tb) in zip(pick, id_map.values()):
+            want[ta, tb] = full[fa, fb]
+    got = engine.load_grm(golden_dir / "tiny_SH.add", normalize=False, id_map=id_map)
+    assert np.array_equal(got, want)
+    got = engine.load_grm(golden_dir / "tiny_SH.add", normalize=True, id_map=id_map)
+    tr = 0.0
+    for t in range(23):
+        tr += want[t, t]
+    assert np.array_equal(got, want / (tr / 23))
+
+
+@pytest.mark.gpu
+def test_grm_loader_large_roundtrip_from_engine_files(tmp_path):
+    # files written by the engine (LOCO + whole) -> loaders -> the same matrices the resident accumulators give (ggrm_fetch_loco),
+    # at a size with many 32 x 32 loader tiles and a ragged edge
+    n, m = 1111, 900
+    payload = g.synth_bed_host(n, 0, m, 29, 0.01)
+    chroms = ["1"] * 300 + ["2"] * 600
+    plink_io.write_plink(tmp_path / "d", payload, [("F", f"s{i:05d}") for i in range(n)], chroms)
+    engine.grm_run(tmp_path / "d", tmp_path / "o", method="OSH", mode="A", loco=True, precision=g.PREC_FP64, write_whole=True)
+    w = plink_io.read_bin(tmp_path / "o.add.bin", n).astype(np.float64)
+    for ci, c in enumerate(("1", "2")):
+        p = plink_io.read_bin(tmp_path / f"o.add.chr{c}.bin", n).astype(np.float64)
+        diag = np.cumsum(np.arange(1, n + 1)) - 1
+        kw = kc = 0.0
+        for i in range(n):
+            kw += w[diag[i]]
+            kc += p[diag[i]]
+        want = np.zeros((n, n))
+        want[np.tril_indices(n)] = (w - p) / (kw / n - kc / n)
+        want = want + np.tril(want, -1).T
+        got = engine.load_grm(tmp_path / "o.add", chr_prefix=tmp_path / f"o.add.chr{c}")
+        assert np.array_equal(got, want), c
+        assert np.array_equal(got, got.T)
