@@ -108,7 +108,7 @@ def load() -> C.CDLL:
     lib.ggrm_row_slice.argtypes = [vp, i64, i64, C.POINTER(i64), C.POINTER(i64)]
     lib.ggrm_fetch_block.argtypes = [vp, C.c_int, C.c_int, i64, i64, i64, i64, vp, i64]
     lib.ggrm_owned_supertiles.argtypes = [vp, C.POINTER(i64), C.POINTER(i64), i64, C.POINTER(i64)]
-    lib.ggrm_bin_to_dense.argtypes = [C.c_int, vp, vp, i64, vp, i64, dbl, vp]
+    lib.ggrm_bin_to_dense.argtypes = [C.c_int, vp, i64, vp, vp, i64, vp, i64, dbl, vp]
     lib.ggrm_host_alloc.argtypes = [i64, C.POINTER(vp)]
     lib.ggrm_host_free.argtypes = [vp]
     lib.ggrm_decode_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, vp]

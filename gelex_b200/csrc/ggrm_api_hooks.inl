@@ -135,31 +135,44 @@ extern "C" int ggrm_ipc_close(int device, void* d_ptr) {
     GGRM_STATELESS_END
 }
 
-extern "C" int ggrm_bin_to_dense(int device, const float* whole_packed, const float* chr_packed, int64_t n_file, const int64_t* target_to_file,
-                                 int64_t n_target, double denominator, double* out_colmajor) {
+extern "C" int ggrm_bin_to_dense(int device, const float* whole_packed, int64_t n_whole, const int64_t* target_to_whole, const float* chr_packed,
+                                 int64_t n_chr, const int64_t* target_to_chr, int64_t n_target, double denominator, double* out_colmajor) {
     GGRM_STATELESS_BEGIN
     check_device(device, nullptr);
     if (whole_packed == nullptr || out_colmajor == nullptr) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "null argument"};
-    if (n_file <= 0 || n_target <= 0 || n_file > (int64_t{1} << 30) || n_target > (int64_t{1} << 30))
+    const int64_t lim = int64_t{1} << 30;
+    if (n_whole <= 0 || n_target <= 0 || n_whole > lim || n_target > lim || (chr_packed != nullptr && (n_chr <= 0 || n_chr > lim)))
         throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "matrix sizes must be positive"};
-    if (target_to_file == nullptr && n_target != n_file) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "identity map requires n_target == n_file"};
-    if (target_to_file != nullptr)
+    auto check_map = [&](const int64_t* map, int64_t n_file) {
+        if (map == nullptr) {
+            if (n_target != n_file) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "identity map requires n_target == n_file"};
+            return;
+        }
         for (int64_t t = 0; t < n_target; ++t)
-            if (target_to_file[t] < -1 || target_to_file[t] >= n_file) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "target_to_file entry out of range"};
-    const size_t packed = static_cast<size_t>(n_file) * static_cast<size_t>(n_file + 1) / 2;
+            if (map[t] < -1 || map[t] >= n_file) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "target map entry out of range"};
+    };
+    check_map(target_to_whole, n_whole);
+    if (chr_packed != nullptr) check_map(target_to_chr, n_chr);
     ScratchFree sf;
-    float* d_w = sf.alloc<float>(packed);
-    float* d_c = chr_packed != nullptr ? sf.alloc<float>(packed) : nullptr;
+    auto upload_packed = [&](const float* src, int64_t n) {
+        const size_t packed = static_cast<size_t>(n) * static_cast<size_t>(n + 1) / 2;
+        float* d = sf.alloc<float>(packed);
+        GGRM_CUDA(cudaMemcpy(d, src, packed * sizeof(float), cudaMemcpyHostToDevice));
+        return d;
+    };
+    auto upload_map = [&](const int64_t* map) -> int64_t* {
+        if (map == nullptr) return nullptr;
+        int64_t* d = sf.alloc<int64_t>(static_cast<size_t>(n_target));
+        GGRM_CUDA(cudaMemcpy(d, map, static_cast<size_t>(n_target) * sizeof(int64_t), cudaMemcpyHostToDevice));
+        return d;
+    };
+    const float* d_w = upload_packed(whole_packed, n_whole);
+    const float* d_c = chr_packed != nullptr ? upload_packed(chr_packed, n_chr) : nullptr;
+    const int64_t* d_mw = upload_map(target_to_whole);
+    const int64_t* d_mc = chr_packed != nullptr ? upload_map(target_to_chr) : nullptr;
     double* d_out = sf.alloc<double>(static_cast<size_t>(n_target) * static_cast<size_t>(n_target));
-    int64_t* d_map = nullptr;
-    GGRM_CUDA(cudaMemcpy(d_w, whole_packed, packed * sizeof(float), cudaMemcpyHostToDevice));
-    if (d_c != nullptr) GGRM_CUDA(cudaMemcpy(d_c, chr_packed, packed * sizeof(float), cudaMemcpyHostToDevice));
-    if (target_to_file != nullptr) {
-        d_map = sf.alloc<int64_t>(static_cast<size_t>(n_target));
-        GGRM_CUDA(cudaMemcpy(d_map, target_to_file, static_cast<size_t>(n_target) * sizeof(int64_t), cudaMemcpyHostToDevice));
-    }
     const unsigned nb = static_cast<unsigned>((n_target + 31) / 32);
-    bin_to_dense_kernel<<<dim3(nb, nb), 256>>>(d_w, d_c, d_map, n_target, denominator, d_out);
+    bin_to_dense_kernel<<<dim3(nb, nb), 256>>>(d_w, d_c, d_mw, d_mc, n_target, denominator, d_out);
     GGRM_CUDA(cudaGetLastError());
     GGRM_CUDA(cudaMemcpy(out_colmajor, d_out, static_cast<size_t>(n_target) * static_cast<size_t>(n_target) * sizeof(double), cudaMemcpyDeviceToHost));
     GGRM_STATELESS_END

@@ -100,8 +100,8 @@ DenseMatrix GrmLoader::expand(const std::vector<int64_t>* target_to_file, int64_
     out.n = n_target;
     if (n_target == 0) return out;
     out.data.resize(static_cast<size_t>(n_target) * static_cast<size_t>(n_target));
-    const int st = ggrm_bin_to_dense(device_, data_, nullptr, num_samples_, target_to_file != nullptr ? target_to_file->data() : nullptr, n_target,
-                                     denominator, out.data.data());
+    const int st = ggrm_bin_to_dense(device_, data_, num_samples_, target_to_file != nullptr ? target_to_file->data() : nullptr, nullptr, 0, nullptr,
+                                     n_target, denominator, out.data.data());
     if (st != GGRM_OK) throw_status(st, ggrm_last_error(nullptr));
     return out;
 }
@@ -143,15 +143,14 @@ DenseMatrix LocoGRMLoader::load_loco_grm(const fs::path& chr_grm_prefix, const I
     if (k_loco <= 0)
         throw InvalidInputException("LOCO error: Chromosome GRM denominator (" + std::to_string(k_i) + ") is greater than or equal to Whole GRM denominator (" +
                                     std::to_string(k_whole_) + ")");
-    // One kernel subtracts the two packed triangles, so both files must list the same samples in the same rows (they do when
-    // they come from one `gelex grm --loco` run: every .id file is the same sorted list, grm_engine.cpp:93-96).
-    if (n_chr != n_target_ || chr.num_samples() != whole_.num_samples() || chr_map != whole_map_)
-        throw InvalidInputException("LOCO error: " + bin_path.string() + " does not list the same samples in the same order as the whole-genome GRM");
+    // the two files are aligned through the SAME id_map (each by its own .id list), as in the reference
+    if (n_chr != n_target_) throw InvalidInputException("LOCO error: " + bin_path.string() + " maps to a different matrix size than the whole-genome GRM");
     DenseMatrix out;
     out.n = n_target_;
     if (n_target_ == 0) return out;
     out.data.resize(static_cast<size_t>(n_target_) * static_cast<size_t>(n_target_));
-    const int st = ggrm_bin_to_dense(device_, whole_.packed(), chr.packed(), whole_.num_samples(), whole_map_.data(), n_target_, k_loco, out.data.data());
+    const int st = ggrm_bin_to_dense(device_, whole_.packed(), whole_.num_samples(), whole_map_.data(), chr.packed(), chr.num_samples(), chr_map.data(),
+                                     n_target_, k_loco, out.data.data());
     if (st != GGRM_OK) throw_status(st, ggrm_last_error(nullptr));
     return out;
 }

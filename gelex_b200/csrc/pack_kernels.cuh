@@ -97,29 +97,37 @@ __global__ void __launch_bounds__(256) axpy_accum_kernel(T* __restrict__ dst, co
 
 // Consumer side of the .bin format: packed float32 lower rows of one or two files already on the device ->
 // the dense symmetric FP64 matrix GrmLoader / LocoGRMLoader hand to the solvers (src/data/grm/grm_loader.cpp:125-243,
-// loco_grm_loader.cpp:62-76):  out(i, j) = (W(f(i), f(j)) - C(f(i), f(j))) / denom, f = target row -> file row (-1: the
-// target has no sample in the file, its row and column stay 0), column-major.  One 32 x 32 tile per block, lower block
+// loco_grm_loader.cpp:62-76):  out(i, j) = (W(fw(i), fw(j)) - C(fc(i), fc(j))) / denom, fw / fc = target row -> row of that file
+// (-1: the target has no sample there and contributes 0), column-major.  One 32 x 32 tile per block, lower block
 // triangle only: the tile is gathered once with its contiguous file index on threadIdx.x and written twice (as is and
 // transposed through shared memory), so both the reads and the 8-byte writes are coalesced for the identity map.
 __global__ void __launch_bounds__(256) bin_to_dense_kernel(const float* __restrict__ W, const float* __restrict__ C,
-                                                           const int64_t* __restrict__ target_to_file, int64_t n_target,
-                                                           double denom, double* __restrict__ out) {
+                                                           const int64_t* __restrict__ map_w, const int64_t* __restrict__ map_c,
+                                                           int64_t n_target, double denom, double* __restrict__ out) {
     const int64_t bi = blockIdx.y, bj = blockIdx.x;
     if (bj > bi) return;
     __shared__ double tile[32][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
     const int64_t tj = bj * 32 + tx;
-    const int64_t fj = tj < n_target ? (target_to_file != nullptr ? target_to_file[tj] : tj) : -1;
+    const int64_t wj = tj < n_target ? (map_w != nullptr ? map_w[tj] : tj) : -1;
+    const int64_t cj = C != nullptr && tj < n_target ? (map_c != nullptr ? map_c[tj] : tj) : -1;
 #pragma unroll
     for (int r = ty; r < 32; r += 8) {
         const int64_t ti = bi * 32 + r;
-        const int64_t fi = ti < n_target ? (target_to_file != nullptr ? target_to_file[ti] : ti) : -1;
         double v = 0.0;
-        if (fi >= 0 && fj >= 0) {
-            const int64_t a = fi > fj ? fi : fj, b = fi > fj ? fj : fi;
-            const int64_t off = a * (a + 1) / 2 + b;
-            v = static_cast<double>(W[off]);
-            if (C != nullptr) v -= static_cast<double>(C[off]);
+        if (ti < n_target) {
+            const int64_t wi = map_w != nullptr ? map_w[ti] : ti;
+            if (wi >= 0 && wj >= 0) {
+                const int64_t a = wi > wj ? wi : wj, b = wi > wj ? wj : wi;
+                v = static_cast<double>(W[a * (a + 1) / 2 + b]);
+            }
+            if (C != nullptr) {
+                const int64_t ci = map_c != nullptr ? map_c[ti] : ti;
+                if (ci >= 0 && cj >= 0) {
+                    const int64_t a = ci > cj ? ci : cj, b = ci > cj ? cj : ci;
+                    v -= static_cast<double>(C[a * (a + 1) / 2 + b]);
+                }
+            }
             v = __ddiv_rn(v, denom);
         }
         tile[r][tx] = v;  // tile[row i][col j]

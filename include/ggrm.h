@@ -175,15 +175,17 @@ int ggrm_row_slice(ggrm_t* h, int64_t row_begin, int64_t row_end, int64_t* elem_
 int ggrm_fetch_normalized(ggrm_t* h, int kind, int group, int64_t row_begin, int64_t row_count, double* out_lower_rows);
 int ggrm_fetch_loco(ggrm_t* h, int kind, int group, int64_t row_begin, int64_t row_count, double* out_lower_rows);
 
-/* The same consumer-side arithmetic from FILES (the reader half of SURVEY 8f-1): `whole_packed` (and optionally
- * `chr_packed`) are the float32 payloads of .bin files with n_file samples (host pointers, e.g. the mmap).  Writes the
- * dense symmetric column-major FP64 matrix out(i, j) = (W(f(i), f(j)) - C(f(i), f(j))) / denominator for i, j < n_target,
- * f = target_to_file (NULL = identity; -1 = no such sample: row and column are 0) - GrmLoader::load_unnormalized(id_map)
- * (grm_loader.cpp:171-231) with denominator 1, GrmLoader::load (:125-131) with trace/n, LocoGRMLoader::load_loco_grm
- * (loco_grm_loader.cpp:62-76) with chr_packed and k_whole - k_chr.  The caller computes the denominators from the file
- * diagonals (n values) so their summation order is the reference's. */
-int ggrm_bin_to_dense(int device, const float* whole_packed, const float* chr_packed, int64_t n_file,
-                      const int64_t* target_to_file, int64_t n_target, double denominator, double* out_colmajor);
+/* The same consumer-side arithmetic from FILES (the reader half of SURVEY 8f-1): `whole_packed` (n_whole samples) and
+ * optionally `chr_packed` (n_chr samples) are the float32 payloads of .bin files (host pointers, e.g. the mmap).  Writes
+ * the dense symmetric column-major FP64 matrix
+ *     out(i, j) = (W(fw(i), fw(j)) - C(fc(i), fc(j))) / denominator,   i, j < n_target,
+ * fw = target_to_whole, fc = target_to_chr (NULL = identity; -1 = the target has no sample in that file and contributes
+ * 0): GrmLoader::load_unnormalized(id_map) (grm_loader.cpp:171-231) with denominator 1, GrmLoader::load (:125-131) with
+ * trace/n, LocoGRMLoader::load_loco_grm (loco_grm_loader.cpp:46-77) with the chromosome file and k_whole - k_chr.  The
+ * caller computes the denominators from the file diagonals (n values) so their summation order is the reference's. */
+int ggrm_bin_to_dense(int device, const float* whole_packed, int64_t n_whole, const int64_t* target_to_whole,
+                      const float* chr_packed, int64_t n_chr, const int64_t* target_to_chr, int64_t n_target,
+                      double denominator, double* out_colmajor);
 
 /* Phase timers (CUDA events on the handle's streams), milliseconds accumulated since create:
  * [0] H2D copies  [1] repack+count+stats  [2] expand  [3] SYRK  [4] pack+D2H  [5] SYRK launches  [6] all kernels launched

@@ -260,3 +260,87 @@ def test_grm_loader_large_roundtrip_from_engine_files(tmp_path):
         got = engine.load_grm(tmp_path / "o.add", chr_prefix=tmp_path / f"o.add.chr{c}")
         assert np.array_equal(got, want), c
         assert np.array_equal(got, got.T)
+
+
+def _write_grm(prefix, matrix, ids):
+    """GrmBinWriter + GrmIdWriter byte layouts (grm_bin_writer.cpp:54-61, grm_id_writer.cpp:41-54) for loader fixtures."""
+    m = np.asarray(matrix, dtype=np.float64)
+    n = m.shape[0]
+    m[np.tril_indices(n)].astype(np.float32).tofile(str(prefix) + ".bin")
+    with open(str(prefix) + ".id", "w") as f:
+        for fid, iid in ids:
+            f.write(f"{fid}\t{iid}\n")
+
+
+def _f32(v):
+    return np.float64(np.float32(v))
+
+
+@pytest.mark.gpu
+def test_grm_loader_known_answers_of_the_reference_tests(tmp_path):
+    # The hand-written vectors of the reference's own tests/test_grm_loader.cpp, restated against this loader.
+    ids3 = [(f"FAM{i}", f"IND{i}") for i in range(3)]
+    # :290-325  3 x 3, trace/n = 1: every element is float(original)
+    m3 = np.array([[1.0, 0.5, 0.3], [0.5, 1.0, 0.4], [0.3, 0.4, 1.0]])
+    _write_grm(tmp_path / "a", m3, ids3)
+    got = engine.load_grm(tmp_path / "a")
+    assert got.shape == (3, 3) and all(got[i, j] == _f32(m3[i, j]) for i in range(3) for j in range(3))
+    # :423-470  subset: samples 1 and 3 of 4 -> rows 0 and 1
+    m4 = np.array([[1.0, 0.1, 0.2, 0.3], [0.1, 2.0, 0.4, 0.5], [0.2, 0.4, 3.0, 0.6], [0.3, 0.5, 0.6, 4.0]])
+    ids4 = [(f"FAM{i}", f"IND{i}") for i in range(4)]
+    _write_grm(tmp_path / "b", m4, ids4)
+    got = engine.load_grm(tmp_path / "b", normalize=False, id_map={("FAM1", "IND1"): 0, ("FAM3", "IND3"): 1})
+    assert got.shape == (2, 2)
+    assert got[0, 0] == _f32(2.0) and got[1, 1] == _f32(4.0) and got[0, 1] == _f32(0.5) and got[1, 0] == _f32(0.5)
+    # :474-520  reversed order
+    got = engine.load_grm(tmp_path / "b", normalize=False, id_map={ids4[i]: 3 - i for i in range(4)})
+    assert all(got[3 - i, 3 - j] == _f32(m4[i, j]) for i in range(4) for j in range(4))
+    # :590-638  sparse target indices: 0 -> 0, 2 -> 5 gives a 6 x 6 matrix, unmapped rows zero
+    m3b = np.array([[1.0, 0.1, 0.2], [0.1, 2.0, 0.3], [0.2, 0.3, 3.0]])
+    _write_grm(tmp_path / "c", m3b, ids3)
+    got = engine.load_grm(tmp_path / "c", normalize=False, id_map={("FAM0", "IND0"): 0, ("FAM2", "IND2"): 5})
+    assert got.shape == (6, 6)
+    assert got[0, 0] == _f32(1.0) and got[5, 5] == _f32(3.0) and got[0, 5] == _f32(0.2) and got[5, 0] == _f32(0.2)
+    assert all(got[k, k] == 0.0 for k in (1, 2, 3, 4)) and np.count_nonzero(got) == 4
+    # :735-777  inf and NaN survive
+    _write_grm(tmp_path / "d", np.array([[np.inf, 0.5], [0.5, 1.0]]), ids3[:2])
+    got = engine.load_grm(tmp_path / "d", normalize=False)
+    assert np.isinf(got[0, 0]) and got[0, 0] > 0
+    _write_grm(tmp_path / "e", np.array([[np.nan, 0.5], [0.5, 1.0]]), ids3[:2])
+    assert np.isnan(engine.load_grm(tmp_path / "e", normalize=False)[0, 0])
+    # :780-812  trace-based normalisation: trace 12, n 3 -> denominator 4
+    _write_grm(tmp_path / "f", np.array([[2.0, 1.0, 0.6], [1.0, 4.0, 0.8], [0.6, 0.8, 6.0]]), ids3)
+    got = engine.load_grm(tmp_path / "f")
+    assert got[0, 0] == _f32(2.0 / 4.0) and got[1, 1] == _f32(4.0 / 4.0) and got[2, 2] == _f32(6.0 / 4.0)
+    assert got[1, 0] == _f32(1.0) / 4.0 and got[2, 1] == got[1, 2] == _f32(0.8) / 4.0
+    # :523-544  empty id_map -> empty matrix is an API property of the C++ class (IdMap{}); through this binding an empty map means
+    # "no filter", so it is covered in the C++ sources only.
+
+
+@pytest.mark.gpu
+def test_loco_grm_loader_known_answers_of_the_reference_tests(tmp_path):
+    # tests/test_loco_grm_loader.cpp:60-110 (basic) and :112-173 (filtered + reordered), tolerance 1e-5 relative as there;
+    # plus chromosome files whose .id order differs from the whole-genome file (each loader maps by ID)
+    rng = np.random.default_rng(12)
+    n = 3
+    ids = [("F1", "I1"), ("F1", "I2"), ("F1", "I3")]
+    xw, xi = rng.uniform(-1, 1, (n, 10)), rng.uniform(-1, 1, (n, 3))
+    gw, gi = xw @ xw.T, xi @ xi.T
+    _write_grm(tmp_path / "whole", gw, ids)
+    _write_grm(tmp_path / "chr1", gi, ids)
+    got = engine.load_grm(tmp_path / "whole", chr_prefix=tmp_path / "chr1", id_map={ids[i]: i for i in range(n)})
+    want = (gw - gi) / (np.trace(gw) / n - np.trace(gi) / n)
+    assert np.allclose(got, want, rtol=1e-5, atol=0)
+    got = engine.load_grm(tmp_path / "whole", chr_prefix=tmp_path / "chr1", id_map={("F1", "I3"): 0, ("F1", "I1"): 1})
+    sel = [2, 0]
+    gws, gis = gw[np.ix_(sel, sel)], gi[np.ix_(sel, sel)]
+    want = (gws - gis) / (np.trace(gws) / 2 - np.trace(gis) / 2)
+    assert got.shape == (2, 2) and np.allclose(got, want, rtol=1e-5, atol=0)
+    perm = [2, 0, 1]  # chromosome file lists the samples in another order
+    _write_grm(tmp_path / "chr2", gi[np.ix_(perm, perm)], [ids[p] for p in perm])
+    got2 = engine.load_grm(tmp_path / "whole", chr_prefix=tmp_path / "chr2", id_map={("F1", "I3"): 0, ("F1", "I1"): 1})
+    assert np.array_equal(got2, got)
+    # k_loco <= 0 (loco_grm_loader.cpp:62-70)
+    _write_grm(tmp_path / "big", gw * 2, ids)
+    with pytest.raises(engine.EngineError, match="LOCO error: Chromosome GRM denominator .* is greater than or equal to Whole GRM denominator"):
+        engine.load_grm(tmp_path / "whole", chr_prefix=tmp_path / "big")
