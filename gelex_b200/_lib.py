@@ -63,7 +63,7 @@ class Config(C.Structure):
 
 
 EXPORTS = [
-    "ggrm_create", "ggrm_destroy", "ggrm_last_error", "ggrm_push", "ggrm_push_device", "ggrm_finish", "ggrm_finish_async", "ggrm_reset", "ggrm_snp_stats",
+    "ggrm_create", "ggrm_destroy", "ggrm_last_error", "ggrm_push", "ggrm_push_device", "ggrm_finish", "ggrm_finish_async", "ggrm_set_push_end", "ggrm_reset", "ggrm_snp_stats",
     "ggrm_fetch", "ggrm_fetch_f64", "ggrm_release_group", "ggrm_accum_buffer", "ggrm_reduce_peer",
     "ggrm_fetch_normalized", "ggrm_fetch_loco", "ggrm_get_timers", "ggrm_decode_chunk", "ggrm_standardise_chunk",
     "ggrm_synth_bed_host", "ggrm_synth_bed_device", "ggrm_device_count", "ggrm_version", "ggrm_enable_peer_access",
@@ -92,6 +92,7 @@ def load() -> C.CDLL:
     lib.ggrm_push_device.argtypes = [vp, vp, i64, i64, i64]
     lib.ggrm_finish.argtypes = [vp]
     lib.ggrm_finish_async.argtypes = [vp]
+    lib.ggrm_set_push_end.argtypes = [vp, i64]
     lib.ggrm_reset.argtypes = [vp]
     lib.ggrm_snp_stats.argtypes = [vp, i64, i64, vp, vp, vp, vp, vp]
     lib.ggrm_fetch.argtypes = [vp, C.c_int, C.c_int, i64, i64, vp, C.POINTER(dbl)]
@@ -213,6 +214,9 @@ class Accumulator:
 
     def finish_async(self):
         self._check(self.lib.ggrm_finish_async(self.h))
+
+    def set_push_end(self, snp_end: int):
+        self._check(self.lib.ggrm_set_push_end(self.h, snp_end))
 
     def reset(self):
         self._check(self.lib.ggrm_reset(self.h))

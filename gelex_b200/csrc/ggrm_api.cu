@@ -194,7 +194,8 @@ static void free_handle(Handle* h) {
     fr(h->d_slot_of); fr(h->d_items_tc); fr(h->d_items_f64); fr(h->d_out_to_raw);
     fr(h->d_raw[0]); fr(h->d_raw[1]); fr(h->d_dense); fr(h->d_counts); fr(h->d_freq);
     for (int k = 0; k < 2; ++k) {
-        fr(h->d_tab16[k]); fr(h->d_tab64[k]); fr(h->d_Z[k][0]); fr(h->d_Z[k][1]); fr(h->whole[k]);
+        fr(h->d_tab16[k]); fr(h->d_tab64[k]); fr(h->whole[k]);
+        for (int b = 0; b < Handle::kMaxZBuf; ++b) fr(h->d_Z[k][b]);
         for (void* p : h->pool[k]) fr(p);
     }
     fr(h->d_stage); fr(h->d_trace); fr(h->d_fault); fr(h->d_wave_ctr);
@@ -202,8 +203,9 @@ static void free_handle(Handle* h) {
         if (h->ring[i] != nullptr) cudaFreeHost(h->ring[i]);
         if (h->ring_free[i] != nullptr) cudaEventDestroy(h->ring_free[i]);
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < 2; ++i)
         if (h->raw_free[i] != nullptr) cudaEventDestroy(h->raw_free[i]);
+    for (int i = 0; i < Handle::kMaxZBuf; ++i) {
         if (h->prep_done[i] != nullptr) cudaEventDestroy(h->prep_done[i]);
         if (h->z_free[i] != nullptr) cudaEventDestroy(h->z_free[i]);
     }
@@ -291,8 +293,8 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
     if (const char* e = std::getenv("GGRM_OVERLAP_PREP")) h->overlap_prep = std::atoi(e) != 0;
     GGRM_CUDA(cudaStreamCreateWithFlags(&h->s_fetch, cudaStreamNonBlocking));
     GGRM_CUDA(cudaEventCreateWithFlags(&h->h2d_done, cudaEventDisableTiming));
-    for (int i = 0; i < 2; ++i) {
-        GGRM_CUDA(cudaEventCreateWithFlags(&h->raw_free[i], cudaEventDisableTiming));
+    for (int i = 0; i < 2; ++i) GGRM_CUDA(cudaEventCreateWithFlags(&h->raw_free[i], cudaEventDisableTiming));
+    for (int i = 0; i < Handle::kMaxZBuf; ++i) {
         GGRM_CUDA(cudaEventCreateWithFlags(&h->prep_done[i], cudaEventDisableTiming));
         GGRM_CUDA(cudaEventCreateWithFlags(&h->z_free[i], cudaEventDisableTiming));
     }
@@ -332,6 +334,16 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
         k_cap = std::max<int64_t>(1024, std::min<int64_t>(target, budget / per_snp / 1024 * 1024));
     }
     k_cap = std::min<int64_t>(k_cap, round_up(cfg->m_total, 64));
+    // Extra operand slabs for the band-major tail (Handle::tail_slabs): as many of the wanted 4 as fit in a quarter of what is left
+    {
+        int want = h->fp64 ? 0 : 4;
+        if (const char* e = std::getenv("GGRM_TAIL_SLABS")) want = std::max(0, std::min(Handle::kMaxZBuf - 2, std::atoi(e)));
+        if (h->fp64) want = 0;
+        const int64_t slab_bytes = h->n_pad * k_cap * z_elem * kinds;
+        const int64_t spare = (avail - k_cap * per_snp) / 4;
+        h->tail_slabs = static_cast<int>(std::max<int64_t>(0, std::min<int64_t>(want, slab_bytes > 0 ? spare / slab_bytes : 0)));
+        h->n_zbuf = 2 + h->tail_slabs;
+    }
     if (k_cap * per_snp > avail)
         throw CudaError{GGRM_ERR_OUT_OF_MEMORY, "not enough device memory for accumulators plus one SNP chunk (need " +
                                                     std::to_string((k_cap * per_snp) >> 20) + " MiB more)"};
@@ -349,12 +361,12 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
             GGRM_CUDA(cudaMalloc(&h->whole[kind], static_cast<size_t>(accum_bytes)));
             GGRM_CUDA(cudaMemsetAsync(h->whole[kind], 0, static_cast<size_t>(accum_bytes), h->s_comp));
         }
-        for (int b = 0; b < 2; ++b) GGRM_CUDA(cudaMalloc(&h->d_Z[kind][b], static_cast<size_t>(h->n_pad * k_cap * z_elem)));
+        for (int b = 0; b < h->n_zbuf; ++b) GGRM_CUDA(cudaMalloc(&h->d_Z[kind][b], static_cast<size_t>(h->n_pad * k_cap * z_elem)));
         if (h->fp64) {
             GGRM_CUDA(cudaMalloc(&h->d_tab64[kind], static_cast<size_t>(k_cap) * sizeof(SnpTable)));
         } else {
             GGRM_CUDA(cudaMalloc(&h->d_tab16[kind], static_cast<size_t>(k_cap) * sizeof(uint2)));
-            for (int b = 0; b < 2; ++b) encode_tensor_map(&h->tmap[kind][b], h->d_Z[kind][b], k_cap, h->n_pad, cfg->precision == GGRM_PREC_FP16);
+            for (int b = 0; b < h->n_zbuf; ++b) encode_tensor_map(&h->tmap[kind][b], h->d_Z[kind][b], k_cap, h->n_pad, cfg->precision == GGRM_PREC_FP16);
         }
     }
     for (int i = 0; i < 2; ++i) GGRM_CUDA(cudaMalloc(&h->d_raw[i], static_cast<size_t>(k_cap * h->bpv_raw)));

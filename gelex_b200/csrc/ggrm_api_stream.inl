@@ -78,9 +78,12 @@ static void start_group(Handle& h, int g, bool zero) {
     gs.started = true;
 }
 
+static void accumulate_slabs(Handle& h, int g, bool banded);
+
 static void complete_group(Handle& h, int g) {
     GroupState& gs = h.groups[g];
     if (gs.complete) return;
+    if (!h.deferred.empty() && h.deferred_group == g) accumulate_slabs(h, g, false);
     if (gs.started && !gs.folded) {
         for (int kind = 0; kind < 2; ++kind) {
             if (h.whole[kind] == nullptr || gs.buffer[kind] < 0 || h.accum_elems == 0) continue;
@@ -154,6 +157,48 @@ static void launch_syrk(Handle& h, int kind, int g, int64_t c, int zb, float* fo
 }
 
 
+// K4 over the parked slabs of group g (Handle::deferred; normally exactly one).  banded: row band by row band - every slab of
+// band 0, event, every slab of band 1, event, ... - so that rows become final progressively (ggrm_finish_async + ggrm_fetch*).
+static void accumulate_slabs(Handle& h, int g, bool banded) {
+    if (h.deferred.empty()) return;
+    GroupState& gs = h.groups[g];
+    for (const auto& sl : h.deferred) GGRM_CUDA(cudaStreamWaitEvent(h.s_comp, h.prep_done[sl.zb], 0));
+    const size_t ti = phase_begin(h, h.s_comp, 3);
+    // last slab of a chromosome whose partial also feeds `whole`: fold inside that slab's SYRK epilogue (tcgen05 path)
+    const auto& last = h.deferred.back();
+    const bool fold_here = !h.fp64 && !gs.folded && last.first_snp + last.count == gs.end;
+    int accumulate[2];
+    for (int kind = 0; kind < 2; ++kind) {  // first slab of a group stores, later slabs add (see start_group)
+        accumulate[kind] = gs.touched[kind] ? 1 : 0;
+        gs.touched[kind] = true;
+    }
+    banded = banded && !h.fp64 && h.band_item_end.size() > 1;
+    const size_t nbands = banded ? h.band_item_end.size() : 1;
+    int item_begin = 0;
+    for (size_t b = 0; b < nbands; ++b) {
+        const int item_end = banded ? h.band_item_end[b] : h.num_items_tc;
+        for (size_t si = 0; si < h.deferred.size(); ++si) {
+            const auto& sl = h.deferred[si];
+            const bool is_last = si + 1 == h.deferred.size();
+            for (int kind = 0; kind < 2; ++kind) {
+                if (h.d_Z[kind][sl.zb] == nullptr) continue;
+                launch_syrk(h, kind, g, sl.count, sl.zb, fold_here && is_last ? static_cast<float*>(h.whole[kind]) : nullptr,
+                            si == 0 ? accumulate[kind] : 1, item_begin, item_end - item_begin);
+            }
+        }
+        if (banded) GGRM_CUDA(cudaEventRecord(h.band_done[b], h.s_comp));
+        item_begin = item_end;
+    }
+    if (banded) {
+        h.banded_group = g;
+        h.banded_whole = fold_here;
+    }
+    if (fold_here) gs.folded = true;
+    phase_end(h, h.s_comp, ti);
+    for (const auto& sl : h.deferred) GGRM_CUDA(cudaEventRecord(h.z_free[sl.zb], h.s_comp));
+    h.deferred.clear();
+}
+
 static void flush_chunk(Handle& h, bool final_flush = false) {
     if (h.cur_count == 0) return;
     const int b = h.cur_buf;
@@ -198,35 +243,25 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
     }
     phase_end(h, sp, ti);
     GGRM_CUDA(cudaEventRecord(h.prep_done[zb], sp));
-    GGRM_CUDA(cudaStreamWaitEvent(h.s_comp, h.prep_done[zb], 0));
-    ti = phase_begin(h, h.s_comp, 3);
-    // last slab of a chromosome whose partial also feeds `whole`: fold inside the SYRK epilogue (tcgen05 path)
-    const bool fold_here = !h.fp64 && !h.groups[g].folded && h.cur_first_snp + c == h.groups[g].end;
-    int accumulate[2];
-    for (int kind = 0; kind < 2; ++kind) {  // first slab of a group stores, later slabs add (see start_group)
-        accumulate[kind] = h.groups[g].touched[kind] ? 1 : 0;
-        h.groups[g].touched[kind] = true;
+
+    // K4.  A slab among the last tail_slabs of the pass is only parked here (its operands stay resident in their ring buffer);
+    // ggrm_finish / ggrm_finish_async accumulates all parked slabs band-major so the read-out can start after the first band.
+    const Handle::DeferredSlab slab{zb, c, h.cur_first_snp};
+    if (final_flush) {
+        if (!h.deferred.empty() && h.deferred_group != g) accumulate_slabs(h, h.deferred_group, true);
+        h.deferred_group = g;
+        h.deferred.push_back(slab);
+        accumulate_slabs(h, g, true);
+    } else if (h.cur_trailing && (h.deferred.empty() || h.deferred_group == g)) {
+        h.deferred_group = g;
+        h.deferred.push_back(slab);
+    } else {
+        if (!h.deferred.empty()) accumulate_slabs(h, h.deferred_group, false);
+        h.deferred_group = g;
+        h.deferred.push_back(slab);
+        accumulate_slabs(h, g, false);
     }
-    const bool banded = final_flush && !h.fp64 && h.band_item_end.size() > 1;
-    const size_t nbands = banded ? h.band_item_end.size() : 1;
-    int item_begin = 0;
-    for (size_t b = 0; b < nbands; ++b) {
-        const int item_end = banded ? h.band_item_end[b] : h.num_items_tc;
-        for (int kind = 0; kind < 2; ++kind) {
-            if (h.d_Z[kind][zb] == nullptr) continue;
-            launch_syrk(h, kind, g, c, zb, fold_here ? static_cast<float*>(h.whole[kind]) : nullptr, accumulate[kind], item_begin, item_end - item_begin);
-        }
-        if (banded) GGRM_CUDA(cudaEventRecord(h.band_done[b], h.s_comp));
-        item_begin = item_end;
-    }
-    if (banded) {
-        h.banded_group = g;
-        h.banded_whole = fold_here;
-    }
-    if (fold_here) h.groups[g].folded = true;
-    phase_end(h, h.s_comp, ti);
-    GGRM_CUDA(cudaEventRecord(h.z_free[zb], h.s_comp));
-    h.z_buf ^= 1;
+    h.z_buf = (h.z_buf + 1) % h.n_zbuf;
     h.cur_buf ^= 1;
     h.cur_count = 0;
     h.cur_first_snp = -1;
@@ -308,9 +343,13 @@ static void push_impl(Handle& h, const uint8_t* payload, bool is_device, int64_t
                 h.cur_first_snp = s;
                 // equal slabs: the rest of the group in ceil(rest / k_cap) pieces (every launch pays the same 2 x accumulator
                 // read-modify-write, so a short tail slab would be HBM-bound)
-                const int64_t rest = h.groups[g].end - s;
+                int64_t seg_end = h.groups[g].end;
+                if (h.push_end_hint > s) seg_end = std::min(seg_end, h.push_end_hint);  // SNP shard: the caller stops before the group does
+                const int64_t rest = seg_end - s;
                 const int64_t pieces = (rest + h.k_cap - 1) / h.k_cap;
                 h.cur_cap = std::min<int64_t>(h.k_cap, round_up((rest + pieces - 1) / pieces, 64));
+                // the last tail_slabs slabs of the pass are parked and accumulated band-major at finish
+                h.cur_trailing = h.tail_slabs > 0 && g + 1 == static_cast<int>(h.groups.size()) && pieces <= h.tail_slabs;
             }
             const int64_t take = std::min(run_end - s, h.cur_cap - h.cur_count);
             copy_rows(h, payload + (s - snp_begin) * h.bpv_raw, is_device, pinned, take, h.d_raw[h.cur_buf] + h.cur_count * h.bpv_raw);
@@ -326,6 +365,7 @@ static void push_impl(Handle& h, const uint8_t* payload, bool is_device, int64_t
 static void finish_enqueue(Handle& h) {
     if (h.finished) return;
     flush_chunk(h, true);
+    if (!h.deferred.empty()) accumulate_slabs(h, h.deferred_group, true);  // the pass ended exactly on a parked slab's boundary
     for (size_t g = 0; g < h.groups.size(); ++g)
         if (h.groups[g].started) complete_group(h, static_cast<int>(g));
     h.finished = true;
@@ -366,6 +406,8 @@ static void reset_impl(Handle& h) {
     finish_sync(h);  // also closes a pass that was finished with ggrm_finish_async and read out without a blocking finish
     h.banded_group = -1;
     h.banded_whole = false;
+    h.deferred.clear();  // (a finished pass has none; an abandoned one may)
+    h.cur_trailing = false;
     for (auto& g : h.groups) {
         g.buffer[0] = g.buffer[1] = -1;
         g.started = g.complete = g.folded = false;
@@ -411,6 +453,14 @@ extern "C" int ggrm_finish(ggrm_t* hh) {
     Handle* h = reinterpret_cast<Handle*>(hh);
     GGRM_API_BEGIN(h)
     finish_impl(*h);
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_set_push_end(ggrm_t* hh, int64_t snp_end) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    if (snp_end < -1 || snp_end > h->cfg.m_total) throw CudaError{GGRM_ERR_COLUMN_RANGE, "push end outside [0, m_total]"};
+    h->push_end_hint = snp_end;
     GGRM_API_END(h)
 }
 

@@ -87,10 +87,20 @@ struct Handle {
     uint2* d_tab16[2] = {nullptr, nullptr};
     SnpTable* d_tab64[2] = {nullptr, nullptr};
     // operand slabs are double buffered so that K1-K3 of slab i+1 (s_prep) overlap the SYRK of slab i (s_comp)
-    void* d_Z[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};   // [kind][z_buf]
-    CUtensorMap tmap[2][2];
-    cudaEvent_t prep_done[2] = {nullptr, nullptr};                 // recorded on s_prep after the expands into Z[.][b]
-    cudaEvent_t z_free[2] = {nullptr, nullptr};                    // recorded on s_comp after the SYRKs that read Z[.][b]
+    // plus `tail_slabs` more buffers: the last slabs of a pass stay resident so that they can be accumulated row band by row band
+    // (all deferred slabs of band 0, then of band 1, ...) and the read-out of the first bands overlaps ~tail_slabs slabs of SYRK
+    static constexpr int kMaxZBuf = 8;
+    void* d_Z[2][kMaxZBuf] = {};                                   // [kind][z_buf]
+    CUtensorMap tmap[2][kMaxZBuf];
+    cudaEvent_t prep_done[kMaxZBuf] = {};                          // recorded on s_prep after the expands into Z[.][b]
+    cudaEvent_t z_free[kMaxZBuf] = {};                             // recorded on s_comp after the SYRKs that read Z[.][b]
+    int n_zbuf = 2;
+    int tail_slabs = 0;                                            // GGRM_TAIL_SLABS (default 4 when memory allows; tcgen05 path only)
+    struct DeferredSlab { int zb; int64_t count; int64_t first_snp; };
+    std::vector<DeferredSlab> deferred;                            // prepared (Z resident) but not yet accumulated
+    int deferred_group = -1;
+    bool cur_trailing = false;                                     // the slab being filled is one of the last tail_slabs of the pass
+    int64_t push_end_hint = -1;                                    // ggrm_set_push_end: no SNP >= this will be pushed (-1: the last group's end)
     int z_buf = 0;
     bool overlap_prep = true;                                      // GGRM_OVERLAP_PREP=0: run K1-K3 on s_comp (serial)
     // pinned staging ring (pageable callers)

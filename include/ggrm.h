@@ -107,10 +107,15 @@ int ggrm_push_device(ggrm_t* h, const uint8_t* d_bed_payload, int64_t snp_begin,
 int ggrm_finish(ggrm_t* h);
 /* Same, but returns as soon as the rest of the pass is ENQUEUED.  The last slab is accumulated in row bands, so a read-out
  * that follows (ggrm_fetch / ggrm_fetch_f64 / ggrm_fetch_block, which wait on the device for exactly the rows they return)
- * starts with the first rows while the later bands are still on the tensor cores: the D2H of a 5 GB matrix overlaps the
+ * starts with the first rows while the later bands are still on the tensor cores (the last few slabs of a pass are kept
+ * resident and accumulated band-major for this, so the overlap window is several slabs long): the D2H of a 5 GB matrix overlaps the
  * tail of the accumulation instead of following it.  After it only ggrm_fetch*, ggrm_finish (blocks, reports device faults),
  * ggrm_reset, ggrm_get_timers and ggrm_destroy may be called; no further ggrm_push. */
 int ggrm_finish_async(ggrm_t* h);
+/* Optional hint for callers that push only part of a group (SNP shards): no SNP index >= snp_end will be pushed in this
+ * pass (-1 clears it).  Lets the library cut the shard into equal slabs and recognise its last slabs, which are accumulated
+ * row band by row band at finish (see ggrm_finish_async).  Purely a scheduling hint: results do not depend on it. */
+int ggrm_set_push_end(ggrm_t* h, int64_t snp_end);
 /* Re-arm the handle for another pass (e.g. the dominance pass of a second invocation, or a benchmark step): all
  * accumulators read as zero again, buffers / work lists / streams are reused. */
 int ggrm_reset(ggrm_t* h);

@@ -363,7 +363,9 @@ def test_finish_async_banded_readout_matches_blocking(monkeypatch):
     groups = [(0, 400), (400, 1500)]
 
     def build(async_finish, **kw):
-        acc = g.Accumulator(n, m, method=3, want_add=True, want_dom=True, precision=g.PREC_FP16, chunk_snps=512, **kw)
+        # 128-SNP slabs: 12 per pass (4 + 9 with the LOCO split) - the first ones accumulate as they arrive, the last four stay
+        # resident and are accumulated band-major at finish
+        acc = g.Accumulator(n, m, method=3, want_add=True, want_dom=True, precision=g.PREC_FP16, chunk_snps=128, **kw)
         for s in range(0, m, 300):
             acc.push(bed[s:min(m, s + 300)], s)
         (acc.finish_async if async_finish else acc.finish)()
@@ -395,6 +397,25 @@ def test_finish_async_banded_readout_matches_blocking(monkeypatch):
         acc2.finish()
         for a in (ref, acc, acc2):
             a.close()
+    # parking the last slabs is scheduling only: with it switched off the bits are the same
+    monkeypatch.setenv("GGRM_TAIL_SLABS", "0")
+    plain = build(False)
+    monkeypatch.delenv("GGRM_TAIL_SLABS")
+    parked = build(True)
+    for kind in (0, 1):
+        assert np.array_equal(plain.fetch(kind, g.GROUP_WHOLE)[0], parked.fetch(kind, g.GROUP_WHOLE)[0])
+    # an SNP shard that announces where it stops (ggrm_set_push_end) parks its own last slabs; same values as without the hint
+    hinted = g.Accumulator(n, m, method=3, want_add=True, want_dom=False, precision=g.PREC_FP16, chunk_snps=128)
+    hinted.set_push_end(900)
+    unhinted = g.Accumulator(n, m, method=3, want_add=True, want_dom=False, precision=g.PREC_FP16, chunk_snps=128)
+    for acc in (hinted, unhinted):
+        for s0 in range(0, 900, 300):
+            acc.push(bed[s0:s0 + 300], s0)
+    hinted.finish_async()
+    unhinted.finish()
+    assert np.array_equal(hinted.fetch(0, g.GROUP_WHOLE)[0], unhinted.fetch(0, g.GROUP_WHOLE)[0])
+    for a in (plain, parked, hinted, unhinted):
+        a.close()
 
 
 def test_error_codes_follow_reference_semantics():
