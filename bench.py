@@ -226,6 +226,8 @@ def gpu_arm(args):
     h_bed.copy_(d_bed)
     torch.cuda.synchronize()
     acc = g.Accumulator(n, m, method=METHOD, precision=prec, device=local)
+    if world > 1:
+        acc.set_push_end(s1)  # this rank stops at the end of its SNP shard: equal slabs inside the shard
     out_elems = g.tri(n)
     h_full = torch.empty(out_elems, dtype=torch.float32, pin_memory=True) if (world > 1 and args.reduce == "nccl" and rank == 0) else None
 

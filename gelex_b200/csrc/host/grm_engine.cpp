@@ -483,6 +483,7 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
 void run_shard_on_device(const RunContext& rc, int device, int64_t begin, int64_t end, ggrm_t** keep_handle, double* pass_ms, double* syrk_ms) {
     HandleGuard hg;
     hg.h = create_handle(rc, device, {0}, false);
+    check(hg.h, ggrm_set_push_end(hg.h, end));  // equal slabs inside the shard
     int64_t done = 0;
     push_range(rc, hg.h, begin, end, end - begin, &done);
     check(hg.h, ggrm_finish(hg.h));
