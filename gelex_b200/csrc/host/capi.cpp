@@ -149,3 +149,14 @@ extern "C" int64_t gelex_b200_grm_load(const char* prefix, const char* chr_prefi
     } catch (const std::bad_alloc&) { set_err(err, err_len, "std::bad_alloc"); return GGRM_ERR_OUT_OF_MEMORY;
     } catch (const std::exception& e) { set_err(err, err_len, std::string("std::exception: ") + e.what()); return -99; }
 }
+
+// Host-side sharding rule of the engine, for CPU tests: writes `parts` (begin, end) pairs; returns parts or -1.
+extern "C" int gelex_b200_row_slices(int64_t n, int parts, int64_t* begin_end) {
+    if (n <= 0 || parts <= 0 || begin_end == nullptr) return -1;
+    const auto sl = GrmEngine::row_slices_for(n, parts);
+    for (size_t r = 0; r < sl.size(); ++r) {
+        begin_end[2 * r] = sl[r].first;
+        begin_end[2 * r + 1] = sl[r].second;
+    }
+    return static_cast<int>(sl.size());
+}

@@ -665,6 +665,8 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
 
 }  // namespace
 
+std::vector<std::pair<int64_t, int64_t>> GrmEngine::row_slices_for(int64_t n, int parts) { return row_slices(n, parts); }
+
 void GrmEngine::compute(const GrmObserver& observer) {
     const auto t_start = Clock::now();
     summary_ = Summary{};

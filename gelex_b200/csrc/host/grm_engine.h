@@ -84,6 +84,9 @@ class GrmEngine {
     static std::vector<GrmWorkItem> build_plan(const std::vector<std::string>& chroms, GrmType mode, bool do_loco,
                                                std::string* output_pattern_suffix, size_t* num_groups);
 
+    // Row ranges the GPUs of an SNP-shard run reduce and write (cuts on 2 048-row super-rows, balanced on triangle area).
+    static std::vector<std::pair<int64_t, int64_t>> row_slices_for(int64_t n, int parts);
+
    private:
     Config config_;
     Summary summary_;

@@ -37,6 +37,7 @@ def load_host():
         h.gelex_b200_plan.restype = C.c_int64
         h.gelex_b200_grm_load.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_char_p, C.c_int]
         h.gelex_b200_grm_load.restype = C.c_int64
+        h.gelex_b200_row_slices.argtypes = [C.c_int64, C.c_int, C.c_void_p]
         _host = h
     return _host
 
@@ -100,3 +101,13 @@ def load_grm(prefix, chr_prefix=None, normalize=True, id_map=None):
         raise EngineError(int(got), err.value.decode())
     assert got == n, (got, n)
     return out
+
+
+def row_slices(n, parts):
+    """The C++ engine's row-slice rule (same contract as sharding.row_slices; compared in tests/test_sharding.py)."""
+    h = load_host()
+    out = np.zeros(2 * parts, dtype=np.int64)
+    got = h.gelex_b200_row_slices(int(n), int(parts), out.ctypes.data_as(C.c_void_p))
+    if got != parts:
+        raise EngineError(got, "row_slices failed")
+    return [(int(out[2 * r]), int(out[2 * r + 1])) for r in range(parts)]

@@ -83,3 +83,11 @@ def test_row_slices_cover_align_and_balance():
     assert max(areas) <= 1.25 * sum(areas) / 8   # coarse (25 super-rows over 8 ranks) but bounded
     areas = [(e * (e + 1) - b * (b + 1)) / 2 for b, e in sharding.row_slices(200000, 8)]
     assert max(areas) <= 1.10 * sum(areas) / 8
+
+
+def test_cpp_engine_uses_the_same_row_slice_rule():
+    from gelex_b200 import engine
+
+    for n in (1, 2047, 2048, 2049, 4500, 50000, 123457, 200000):
+        for w in (1, 2, 3, 4, 7, 8):
+            assert engine.row_slices(n, w) == sharding.row_slices(n, w), (n, w)
