@@ -279,11 +279,67 @@ def gpu_arm(args):
         state["reduce_n"] = state.get("reduce_n", 0) + 1
         dist.barrier()                      # peers have finished reading this rank's buffer before the next pass zeroes it
 
+    # ---- N > 1, default (--reduce pipe): the same reduce-scatter, pipelined band by band behind the accumulation.  The last
+    # slabs of every shard are accumulated row band by row band (ggrm_finish_async); each rank's CUDA host callbacks raise a
+    # flag per finished band in POSIX shared memory; band b belongs to rank b % N, which - as soon as all N flags of b are up -
+    # sums the peers' rows of b into its own over NVLink (ggrm_reduce_rows_async, on the read-out stream) and, in the e2e leg,
+    # reads them out, while every GPU is still on the tensor cores with the later bands.  No collective inside the pass.
+    pipe = {"ready": False, "pass_id": 0}
+
+    def setup_pipe():
+        from multiprocessing import shared_memory
+
+        name = [f"ggrm_bench_flags_{os.environ.get('MASTER_PORT', '0')}_{os.getpid()}"] if rank == 0 else [None]
+        dist.broadcast_object_list(name, src=0)
+        if rank == 0:
+            pipe["shm"] = shared_memory.SharedMemory(name=name[0], create=True, size=world * 64 * 4)
+            np.ndarray((world, 64), dtype=np.int32, buffer=pipe["shm"].buf)[:] = 0
+        dist.barrier()
+        if rank != 0:
+            pipe["shm"] = shared_memory.SharedMemory(name=name[0])
+        pipe["flags"] = np.ndarray((world, 64), dtype=np.int32, buffer=pipe["shm"].buf)
+        bands = acc.band_layout()
+        pipe["mine"] = [(b, lo, hi) for b, (lo, hi) in enumerate(bands) if b % world == rank and hi > lo]
+        pipe["n_bands"] = len(bands)
+        elems = sum(g.tri(hi) - g.tri(lo) for _, lo, hi in pipe["mine"])
+        pipe["h_out"] = torch.empty(max(1, elems), dtype=torch.float32, pin_memory=True)
+        pipe["nvlink_bytes"] = int(sum(acc.row_slice(lo, hi)[1] - acc.row_slice(lo, hi)[0] for _, lo, hi in pipe["mine"]) * 4 * (world - 1))
+        pipe["ready"] = True
+
+    def pipelined_pass(push, fetch):
+        pipe["pass_id"] += 1
+        pid = pipe["pass_id"]
+        acc.reset()
+        acc.set_band_flags(pipe["flags"][rank].ctypes.data, pid)
+        push()
+        acc.finish_async()
+        off = 0
+        for b, lo, hi in pipe["mine"]:
+            t_w = time.time()
+            col = pipe["flags"][:, b]
+            while not (col == pid).all():
+                if time.time() - t_w > 120:
+                    raise SystemExit(f"rank {rank}: band {b} flags {col.tolist()} never reached {pid}")
+                time.sleep(2e-5)
+            acc.reduce_rows_async(g.KIND_ADD, g.GROUP_WHOLE, peers, lo, hi)
+            if fetch:
+                acc.lib.ggrm_fetch(acc.h, g.KIND_ADD, g.GROUP_WHOLE, lo, hi - lo, ctypes.c_void_p(pipe["h_out"].data_ptr() + 4 * off), None)
+                off += g.tri(hi) - g.tri(lo)
+        acc.finish()      # waits for the accumulation and the read-out stream (the reduces), reports device faults
+        dist.barrier()    # peers have finished reading this rank's rows before the next pass overwrites them
+
+    use_pipe = world > 1 and args.reduce == "pipe"
+
     def step_resident():
+        if use_pipe and pipe["ready"]:
+            pipelined_pass(lambda: acc.push_device(d_bed.data_ptr(), s0, ms), fetch=False)
+            return
         acc.reset()
         acc.push_device(d_bed.data_ptr(), s0, ms)
         acc.finish()
         reduce_partials()
+        if use_pipe:      # first warm-up pass ran the blocking form (it maps the peers' accumulators); arm the pipeline now
+            setup_pipe()
 
     def fetch_mine():
         if world > 1 and args.reduce == "nccl":
@@ -293,6 +349,9 @@ def gpu_arm(args):
             acc.lib.ggrm_fetch(acc.h, g.KIND_ADD, g.GROUP_WHOLE, r0, r1 - r0, ctypes.c_void_p(h_out.data_ptr()), None)
 
     def step_e2e():
+        if use_pipe and pipe["ready"]:
+            pipelined_pass(lambda: acc.push_ptr(h_bed.data_ptr(), s0, ms), fetch=True)
+            return
         acc.reset()
         acc.push_ptr(h_bed.data_ptr(), s0, ms)
         if world == 1:
@@ -358,8 +417,13 @@ def gpu_arm(args):
             "data": "synthetic",
             "config": {"workload": f"configs[1]: Yang additive GRM (StandardizeHWE+Add), {n} samples x {m} SNPs, packed 2-bit PLINK BED "
                                    f"({m * bpv / 1e9:.2f} GB), 1 % missing, seed {SEED}",
-                       "partition": "single GPU" if world == 1 else (f"SNP-sharded over {world} GPUs + NCCL sum-reduce of FP32 partial GRMs to rank 0" if args.reduce == "nccl" else
-                                      f"SNP-sharded over {world} GPUs + reduce-scatter of FP32 partial GRMs by 2048-row slices over NVLink peer memory (CUDA IPC, P2P loads); each rank fetches its own rows"),
+                       "partition": "single GPU" if world == 1 else {
+                           "nccl": f"SNP-sharded over {world} GPUs + NCCL sum-reduce of FP32 partial GRMs to rank 0",
+                           "peer": f"SNP-sharded over {world} GPUs + reduce-scatter of FP32 partial GRMs by 2048-row slices over NVLink peer memory (CUDA IPC, P2P loads) "
+                                   "after a blocking finish; each rank fetches its own rows",
+                           "pipe": f"SNP-sharded over {world} GPUs + reduce-scatter of FP32 partial GRMs over NVLink peer memory (CUDA IPC, P2P loads), pipelined "
+                                   f"band by band behind the accumulation: {pipe.get('n_bands')} row bands, band b owned by rank b % {world}, per-band completion flags "
+                                   "raised by CUDA host callbacks in POSIX shared memory, no collective inside the pass; each rank fetches its own bands"}[args.reduce],
                        "l2": "inputs (packed BED 6.25 GB, 16-bit operand slabs 0.8 GB, accumulator 5 GB) are larger than the 126 MB L2; no flush needed",
                        "timing": "CUDA events around the K steps, barrier + cuda synchronize on both sides, max over ranks; kernel phases by CUDA events on the library's streams",
                        "chunk_snps": int(os.environ.get("GGRM_CHUNK_SNPS", 16384)), "host": numa_note},
@@ -367,12 +431,13 @@ def gpu_arm(args):
             "wall_clock_ms_per_step": wall_checks[0][1] / args.steps * 1e3,
             "phases_ms_per_step": {k: tm[k] / args.steps for k in ("h2d_ms", "prep_ms", "expand_ms", "syrk_ms")},
             "gpu_launches": int(tm["kernel_launches"]),
-            "reduce_ms_per_call_rank0": (state.get("reduce_s", 0.0) / max(1, state.get("reduce_n", 0)) * 1e3) if world > 1 else None,
-            "reduce_bytes_over_nvlink_rank0": int((state["slice"][1] - state["slice"][0]) * 4 * (world - 1)) if world > 1 and args.reduce == "peer" else None,
+            "reduce_ms_per_call_rank0": (state.get("reduce_s", 0.0) / max(1, state.get("reduce_n", 0)) * 1e3) if world > 1 and args.reduce != "pipe" else None,
+            "reduce_bytes_over_nvlink_rank0": (pipe.get("nvlink_bytes") if args.reduce == "pipe" else
+                                               int((state["slice"][1] - state["slice"][0]) * 4 * (world - 1)) if args.reduce == "peer" else None) if world > 1 else None,
             "clocks": clocks,
             "e2e": {"value": fl / (dt_e / args.steps) / 1e12, "unit": "TFLOP/s", "wall_s_per_grm": dt_e / args.steps,
                     "h2d_bytes_per_step": int(ms * bpv), "d2h_bytes_per_step": int(out_elems * 4),
-                    "path": "ggrm_reset -> ggrm_push(pinned host BED) -> ggrm_finish_async (N>1: ggrm_finish, then ggrm_reduce_peer on own row slice) -> ggrm_fetch(float32 lower-triangle rows to pinned host memory; N>1: each rank its own rows, bytes summed over ranks)",
+                    "path": "ggrm_reset -> ggrm_push(pinned host BED) -> ggrm_finish_async -> [N>1, per owned band: wait for all ranks' band flags -> ggrm_reduce_rows_async] -> ggrm_fetch(float32 lower-triangle rows to pinned host memory; N>1: each rank its own bands, bytes summed over ranks)",
                     "phases_ms_per_step": {k: tm_e[k] / args.steps for k in ("h2d_ms", "prep_ms", "expand_ms", "syrk_ms", "fetch_ms")}},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": sustained, "unit": "TFLOP/s", "frac": achieved / sustained,
                          "traffic": traffic, "kernel": "syrk_tc_kernel<2> (tcgen05 cta_group::2, UMMA 256x256x16)",
@@ -386,6 +451,13 @@ def gpu_arm(args):
     for p_ in peers:
         g.ipc_close(p_, device=local)
     acc.close()
+    if pipe.get("shm") is not None:
+        pipe["flags"] = None
+        pipe["shm"].close()
+        if world > 1:
+            dist.barrier()
+        if rank == 0:
+            pipe["shm"].unlink()
     if rank == 0 and world == 1 and not args.no_cpu:
         cb, _, _ = cpu_leg(1, 0, args.cpu_budget)
         line["cpu_baseline"] = cb
@@ -425,7 +497,9 @@ def main():
                          "(tests/test_gpu_parity.py::test_c2_snp_count_tolerance_16bit_device_resident), fp16 is the engine default for short inputs")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work per reference step")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--reduce", default="peer", choices=["peer", "nccl"], help="N>1: partial-GRM reduction (peer = own P2P kernel, nccl = dist.reduce)")
+    ap.add_argument("--reduce", default="pipe", choices=["pipe", "peer", "nccl"],
+                    help="N>1: partial-GRM reduction (pipe = own P2P kernel pipelined band by band behind the accumulation, "
+                         "peer = the same kernel after a blocking finish, nccl = dist.reduce to rank 0)")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)

@@ -69,6 +69,7 @@ EXPORTS = [
     "ggrm_synth_bed_host", "ggrm_synth_bed_device", "ggrm_device_count", "ggrm_version", "ggrm_enable_peer_access",
     "ggrm_ipc_export", "ggrm_ipc_open", "ggrm_ipc_close", "ggrm_row_slice",
     "ggrm_fetch_block", "ggrm_owned_supertiles", "ggrm_host_alloc", "ggrm_host_free", "ggrm_bin_to_dense", "ggrm_assoc_chunk",
+    "ggrm_band_layout", "ggrm_set_band_flags", "ggrm_reduce_rows_async",
 ]
 
 _lib = None
@@ -107,6 +108,9 @@ def load() -> C.CDLL:
     lib.ggrm_ipc_open.argtypes = [C.c_int, vp, C.POINTER(vp)]
     lib.ggrm_ipc_close.argtypes = [C.c_int, vp]
     lib.ggrm_row_slice.argtypes = [vp, i64, i64, C.POINTER(i64), C.POINTER(i64)]
+    lib.ggrm_band_layout.argtypes = [vp, C.POINTER(i64), C.c_int, C.POINTER(C.c_int)]
+    lib.ggrm_set_band_flags.argtypes = [vp, vp, i32]
+    lib.ggrm_reduce_rows_async.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int, i64, i64]
     lib.ggrm_fetch_block.argtypes = [vp, C.c_int, C.c_int, i64, i64, i64, i64, vp, i64]
     lib.ggrm_owned_supertiles.argtypes = [vp, C.POINTER(i64), C.POINTER(i64), i64, C.POINTER(i64)]
     lib.ggrm_bin_to_dense.argtypes = [C.c_int, vp, i64, vp, vp, i64, vp, i64, dbl, vp]
@@ -260,6 +264,24 @@ class Accumulator:
     def reduce_peer(self, kind, group, peer_ptrs, slice_begin, slice_end):
         arr = (C.c_void_p * max(1, len(peer_ptrs)))(*peer_ptrs)
         self._check(self.lib.ggrm_reduce_peer(self.h, kind, group, arr, len(peer_ptrs), slice_begin, slice_end))
+
+    def band_layout(self):
+        """[(row_begin, row_end)] of the bands the final accumulation completes in (see ggrm_band_layout)."""
+        ends = (C.c_int64 * 64)()
+        nb = C.c_int()
+        self._check(self.lib.ggrm_band_layout(self.h, ends, 64, C.byref(nb)))
+        out, prev = [], 0
+        for b in range(nb.value):
+            out.append((prev, ends[b]))
+            prev = ends[b]
+        return out
+
+    def set_band_flags(self, flags_addr: int, value: int):
+        self._check(self.lib.ggrm_set_band_flags(self.h, C.c_void_p(flags_addr), value))
+
+    def reduce_rows_async(self, kind, group, peer_ptrs, row_begin, row_end):
+        arr = (C.c_void_p * max(1, len(peer_ptrs)))(*peer_ptrs)
+        self._check(self.lib.ggrm_reduce_rows_async(self.h, kind, group, arr, len(peer_ptrs), row_begin, row_end))
 
     def ipc_export(self, kind=KIND_ADD, group=GROUP_WHOLE) -> bytes:
         buf = C.create_string_buffer(64)

@@ -293,6 +293,43 @@ extern "C" int ggrm_reduce_peer(ggrm_t* hh, int kind, int group, const void* con
     GGRM_API_END(h)
 }
 
+// Band-pipelined form of the reduce-scatter: sums the peers' rows [row_begin, row_end) (whole super-rows) into this handle's on
+// the READ-OUT stream, behind the band events that make this handle's own rows final, and returns without waiting.  A
+// ggrm_fetch of those rows that follows is ordered after it.  The caller guarantees the peers' rows are final (their band flags).
+extern "C" int ggrm_reduce_rows_async(ggrm_t* hh, int kind, int group, const void* const* peers, int n_peers, int64_t row_begin, int64_t row_end) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    if (n_peers < 0 || n_peers > kMaxPeers) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "n_peers must be 0..7"};
+    if (h->cfg.tile_world != 1) throw CudaError{GGRM_ERR_INVALID_OPERATION, "row slices are defined for handles that own every tile"};
+    if (row_begin < 0 || row_end < row_begin || row_end > h->n_out || ((row_begin % 2048) != 0 && row_begin != h->n_out) ||
+        ((row_end % 2048) != 0 && row_end != h->n_out))
+        throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "row range must be cut on multiples of 2048 rows (one super-row of tiles)"};
+    cudaEvent_t ev = nullptr;
+    bool banded = false;
+    void* mine = resolve_accum(*h, kind, group, &ev, &banded);
+    if (banded && row_end > row_begin) {
+        size_t b = 0;
+        while (h->band_row_end[b] < row_end) ++b;
+        ev = h->band_done[b];
+    }
+    if (ev != nullptr) GGRM_CUDA(cudaStreamWaitEvent(h->s_fetch, ev, 0));
+    const int64_t A = row_begin == h->n_out ? h->ntiles_side : row_begin / kTile;
+    const int64_t B = row_end == h->n_out ? h->ntiles_side : row_end / kTile;
+    const int64_t slice_begin = A * (A + 1) / 2 * 65536, slice_end = B * (B + 1) / 2 * 65536;
+    PeerPtrs pp{};
+    for (int i = 0; i < n_peers; ++i) pp.p[i] = peers[i];
+    const int64_t len = slice_end - slice_begin;
+    if (len > 0 && n_peers > 0) {
+        const int64_t span = 256 * (16 / h->elem_bytes) * 4;
+        const int blocks = static_cast<int>(std::min<int64_t>((len + span - 1) / span, h->sm_count * 8));
+        if (h->fp64) reduce_peers_kernel<double><<<blocks, 256, 0, h->s_fetch>>>(static_cast<double*>(mine), pp, n_peers, slice_begin, slice_end);
+        else reduce_peers_kernel<float><<<blocks, 256, 0, h->s_fetch>>>(static_cast<float*>(mine), pp, n_peers, slice_begin, slice_end);
+        GGRM_CUDA(cudaGetLastError());
+        ++h->kernel_launches;
+    }
+    GGRM_API_END(h)
+}
+
 extern "C" int ggrm_ipc_export(ggrm_t* hh, int kind, int group, void* handle64) {
     Handle* h = reinterpret_cast<Handle*>(hh);
     GGRM_API_BEGIN(h)

@@ -157,6 +157,18 @@ static void launch_syrk(Handle& h, int kind, int g, int64_t c, int zb, float* fo
 }
 
 
+static void CUDART_CB band_flag_callback(void* p) {
+    const auto* m = static_cast<const Handle::FlagMsg*>(p);
+    __atomic_store_n(m->addr, m->value, __ATOMIC_RELEASE);
+}
+
+// Enqueue "flags[band] = value" behind everything already on the compute stream.
+static void post_band_flag(Handle& h, size_t band) {
+    if (h.band_flags == nullptr) return;
+    h.flag_msgs.push_back({h.band_flags + band, h.band_flag_value});
+    GGRM_CUDA(cudaLaunchHostFunc(h.s_comp, band_flag_callback, &h.flag_msgs.back()));
+}
+
 // K4 over the parked slabs of group g (Handle::deferred; normally exactly one).  banded: row band by row band - every slab of
 // band 0, event, every slab of band 1, event, ... - so that rows become final progressively (ggrm_finish_async + ggrm_fetch*).
 static void accumulate_slabs(Handle& h, int g, bool banded) {
@@ -172,6 +184,7 @@ static void accumulate_slabs(Handle& h, int g, bool banded) {
         accumulate[kind] = gs.touched[kind] ? 1 : 0;
         gs.touched[kind] = true;
     }
+    const bool final_pass = banded;  // called from finish: completion flags are posted per band (or once, when there is one band)
     banded = banded && !h.fp64 && h.band_item_end.size() > 1;
     const size_t nbands = banded ? h.band_item_end.size() : 1;
     int item_begin = 0;
@@ -187,8 +200,10 @@ static void accumulate_slabs(Handle& h, int g, bool banded) {
             }
         }
         if (banded) GGRM_CUDA(cudaEventRecord(h.band_done[b], h.s_comp));
+        if (final_pass && g + 1 == static_cast<int>(h.groups.size())) post_band_flag(h, b);
         item_begin = item_end;
     }
+    if (final_pass && g + 1 == static_cast<int>(h.groups.size())) h.band_flags_posted = true;
     if (banded) {
         h.banded_group = g;
         h.banded_whole = fold_here;
@@ -370,6 +385,11 @@ static void finish_enqueue(Handle& h) {
         if (h.groups[g].started) complete_group(h, static_cast<int>(g));
     h.finished = true;
     if (h.pass_open) GGRM_CUDA(cudaEventRecord(h.pass_end, h.s_comp));
+    if (h.band_flags != nullptr && !h.band_flags_posted) {  // nothing was accumulated at finish: every band is final already
+        const size_t nb = std::max<size_t>(1, h.fp64 ? 1 : h.band_row_end.size());
+        for (size_t b = 0; b < nb; ++b) post_band_flag(h, b);
+        h.band_flags_posted = true;
+    }
 }
 
 // Wait for the device, surface faults, collect timers.
@@ -377,6 +397,8 @@ static void finish_sync(Handle& h) {
     cudaError_t e1 = cudaStreamSynchronize(h.s_copy);
     const cudaError_t e1b = cudaStreamSynchronize(h.s_prep);
     if (e1 == cudaSuccess) e1 = e1b;
+    const cudaError_t e1c = cudaStreamSynchronize(h.s_fetch);  // ggrm_reduce_rows_async runs there
+    if (e1 == cudaSuccess) e1 = e1c;
     const cudaError_t e2 = cudaStreamSynchronize(h.s_comp);
     if (e1 != cudaSuccess || e2 != cudaSuccess) {
         int where = 0;
@@ -406,6 +428,8 @@ static void reset_impl(Handle& h) {
     finish_sync(h);  // also closes a pass that was finished with ggrm_finish_async and read out without a blocking finish
     h.banded_group = -1;
     h.banded_whole = false;
+    h.flag_msgs.clear();  // every callback of the finished pass has run (streams are idle)
+    h.band_flags_posted = false;
     h.deferred.clear();  // (a finished pass has none; an abandoned one may)
     h.cur_trailing = false;
     for (auto& g : h.groups) {
@@ -461,6 +485,26 @@ extern "C" int ggrm_set_push_end(ggrm_t* hh, int64_t snp_end) {
     GGRM_API_BEGIN(h)
     if (snp_end < -1 || snp_end > h->cfg.m_total) throw CudaError{GGRM_ERR_COLUMN_RANGE, "push end outside [0, m_total]"};
     h->push_end_hint = snp_end;
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_set_band_flags(ggrm_t* hh, int32_t* flags, int32_t value) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    if (h->finished) throw CudaError{GGRM_ERR_INVALID_OPERATION, "ggrm_set_band_flags must precede ggrm_finish of the pass"};
+    h->band_flags = flags;
+    h->band_flag_value = value;
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_band_layout(ggrm_t* hh, int64_t* row_end, int capacity, int* n_bands) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    const bool banded = !h->fp64 && h->band_row_end.size() > 1;
+    const int nb = banded ? static_cast<int>(h->band_row_end.size()) : 1;
+    if (n_bands != nullptr) *n_bands = nb;
+    if (row_end != nullptr)
+        for (int b = 0; b < std::min(nb, capacity); ++b) row_end[b] = banded ? h->band_row_end[static_cast<size_t>(b)] : h->n_out;
     GGRM_API_END(h)
 }
 

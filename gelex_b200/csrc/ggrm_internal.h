@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <deque>
 #include <string>
 #include <vector>
 
@@ -71,6 +72,13 @@ struct Handle {
     std::vector<int> band_item_end;       // exclusive item index per band
     std::vector<int64_t> band_row_end;    // exclusive GRM row per band
     std::vector<cudaEvent_t> band_done;
+    // ggrm_set_band_flags: flags[b] = value is stored from a CUDA host callback once band b of the pass's final accumulation is
+    // complete (multi-process SNP shards pipeline their reduce-scatter + read-out band by band on these)
+    int32_t* band_flags = nullptr;
+    int32_t band_flag_value = 0;
+    bool band_flags_posted = false;
+    struct FlagMsg { int32_t* addr; int32_t value; };
+    std::deque<FlagMsg> flag_msgs;        // payloads of in-flight callbacks (stable addresses; cleared at reset)
     int banded_group = -1;                // group whose partial was finished band by band in the final flush (-1: none)
     bool banded_whole = false;            // ... and `whole` too (its last fold happened inside those launches)
     // projection

@@ -161,6 +161,19 @@ int ggrm_accum_buffer(ggrm_t* h, int kind, int group, void** d_ptr, int64_t* n_e
 int ggrm_reduce_peer(ggrm_t* h, int kind, int group, const void* const* peers, int n_peers, int64_t slice_begin,
                      int64_t slice_end);
 
+/* Band-pipelined reduce-scatter (SNP shards, one process per GPU).  The final accumulation of a pass completes row band by row
+ * band (ggrm_finish_async); ggrm_band_layout gives the bands (band b = rows [row_end[b-1], row_end[b]), whole 2 048-row
+ * super-rows, the same on every rank of equal n_out).  With ggrm_set_band_flags, `flags[b] = value` is stored by a CUDA host
+ * callback the moment band b is final on this device - put `flags` in memory every rank can see (POSIX shared memory) and the
+ * owner of band b knows when all its peers' rows are ready without a collective.  It then calls ggrm_reduce_rows_async (sums
+ * the peers' rows into its own on the read-out stream, behind its own band event, without blocking) followed by ggrm_fetch of
+ * those rows - while every GPU is still accumulating the later bands.  `flags` must stay valid until the pass is finished
+ * (ggrm_finish / ggrm_reset); NULL disables. */
+int ggrm_band_layout(ggrm_t* h, int64_t* row_end, int capacity, int* n_bands);
+int ggrm_set_band_flags(ggrm_t* h, int32_t* flags, int32_t value);
+int ggrm_reduce_rows_async(ggrm_t* h, int kind, int group, const void* const* peers, int n_peers, int64_t row_begin,
+                           int64_t row_end);
+
 /* Multi-PROCESS form of the same (one process per GPU, torch.distributed-style launch): export the accumulator of
  * (kind, group) as a CUDA IPC handle (64 bytes, cudaIpcMemHandle_t), ship it to the other ranks over any host channel,
  * open it there (maps the peer's memory over NVLink, enabling peer access lazily) and pass the mapped pointers to

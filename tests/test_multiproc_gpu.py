@@ -72,3 +72,92 @@ def test_snp_shard_reduce_scatter_over_ipc(tmp_path, world):
                 scale = float(np.max(np.abs(ref)))
                 assert np.max(np.abs(got - ref)) <= rel * scale, (tag, kind, float(np.max(np.abs(got - ref))), scale)
                 assert abs(tr - tr_ref) <= 2 * rel * abs(tr_ref) + 1e-9 * abs(tr_ref), (tag, kind)
+
+
+# ------------------------------------------------------------------------------------------------ band-pipelined reduce-scatter
+def _pipelined_worker(rank, world, port, tmpdir):
+    """finish_async -> per band: wait for every rank's completion flag (shared memory, set by CUDA host callbacks), then the
+    band's owner reduces the peers' rows over IPC-mapped memory and reads them out, while later bands are still accumulating."""
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__))))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      GGRM_BAND_MIN_TILES="4")  # 4500 rows = 3 strips: one band per strip
+    import time
+    from multiprocessing import shared_memory
+
+    import torch.distributed as dist
+
+    import gelex_b200 as g
+    from gelex_b200 import sharding
+
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    dev = rank % max(1, g.device_count())
+    name = f"ggrm_test_flags_{port}"
+    shm = shared_memory.SharedMemory(name=name, create=True, size=world * 64 * 4) if rank == 0 else None
+    dist.barrier()
+    if shm is None:
+        shm = shared_memory.SharedMemory(name=name)
+    flags = np.ndarray((world, 64), dtype=np.int32, buffer=shm.buf)
+    if rank == 0:
+        flags[:] = 0
+    dist.barrier()
+    bed = g.synth_bed_host(N, 0, M, SEED, 0.02)
+    s0, s1 = sharding.snp_shards(M, world)[rank]
+    acc = g.Accumulator(N, M, method=3, want_add=True, want_dom=False, precision=g.PREC_FP16, device=dev, chunk_snps=512)
+    peers = None
+    for pass_id in (1, 2):  # second pass: re-armed handle, same flags memory, new value
+        if pass_id > 1:
+            acc.reset()
+        acc.set_push_end(s1)
+        acc.set_band_flags(flags[rank].ctypes.data, pass_id)
+        acc.push(bed[s0:s1], s0)
+        acc.finish_async()
+        if peers is None:  # accumulator addresses are stable across ggrm_reset
+            handles = [None] * world
+            dist.all_gather_object(handles, acc.ipc_export(g.KIND_ADD, g.GROUP_WHOLE))
+            peers = [g.ipc_open(handles[r], device=dev) for r in range(world) if r != rank]
+        bands = acc.band_layout()
+        assert len(bands) == 3 and bands[-1][1] == N
+        got = {}
+        for b, (r0, r1) in enumerate(bands):
+            if b % world != rank:
+                continue
+            t0 = time.time()
+            while not np.all(flags[:, b] == pass_id):
+                assert time.time() - t0 < 60, "peer band flag never arrived"
+                time.sleep(0.0002)
+            acc.reduce_rows_async(g.KIND_ADD, g.GROUP_WHOLE, peers, r0, r1)
+            rows, tr = acc.fetch(g.KIND_ADD, g.GROUP_WHOLE, r0, r1 - r0, dtype=np.float64)
+            got[b] = (rows, tr)
+        acc.finish()
+        dist.barrier()  # nobody re-arms (first slab stores) while a peer may still read its rows
+        for b, (rows, tr) in got.items():
+            np.save(os.path.join(tmpdir, f"p{pass_id}_band{b}.npy"), rows)
+            np.save(os.path.join(tmpdir, f"p{pass_id}_band{b}_tr.npy"), np.array([tr]))
+    for p in peers:
+        g.ipc_close(p, device=dev)
+    acc.close()
+    dist.barrier()
+    shm.close()
+    if rank == 0:
+        shm.unlink()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_band_pipelined_reduce_scatter(tmp_path, world):
+    import gelex_b200 as g
+
+    port = 29700 + (os.getpid() % 2000) + world
+    mp.spawn(_pipelined_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    bed = g.synth_bed_host(N, 0, M, SEED, 0.02)
+    with g.Accumulator(N, M, method=3, want_add=True, want_dom=False, precision=g.PREC_FP16) as acc:
+        acc.push(bed, 0)
+        acc.finish()
+        ref, tr_ref = acc.fetch(g.KIND_ADD, g.GROUP_WHOLE, dtype=np.float64)
+    scale = float(np.max(np.abs(ref)))
+    for pass_id in (1, 2):
+        got = np.concatenate([np.load(tmp_path / f"p{pass_id}_band{b}.npy") for b in range(3)])
+        tr = sum(float(np.load(tmp_path / f"p{pass_id}_band{b}_tr.npy")[0]) for b in range(3))
+        assert got.shape == ref.shape
+        assert np.max(np.abs(got - ref)) <= 1e-4 * scale, (pass_id, float(np.max(np.abs(got - ref))), scale)
+        assert abs(tr - tr_ref) <= 3e-4 * abs(tr_ref)
