@@ -297,6 +297,12 @@ def gpu_arm(args):
         dist.barrier()
         if rank != 0:
             pipe["shm"] = shared_memory.SharedMemory(name=name[0])
+            try:  # only the creator unlinks; keep this process's resource tracker from trying again at exit (Python < 3.13)
+                from multiprocessing import resource_tracker
+
+                resource_tracker.unregister(pipe["shm"]._name, "shared_memory")
+            except Exception:  # noqa: BLE001
+                pass
         pipe["flags"] = np.ndarray((world, 64), dtype=np.int32, buffer=pipe["shm"].buf)
         bands = acc.band_layout()
         pipe["mine"] = [(b, lo, hi) for b, (lo, hi) in enumerate(bands) if b % world == rank and hi > lo]
