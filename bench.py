@@ -286,31 +286,51 @@ def gpu_arm(args):
     # reads them out, while every GPU is still on the tensor cores with the later bands.  No collective inside the pass.
     pipe = {"ready": False, "pass_id": 0}
 
+    def all_ok(flag):
+        t_ok = torch.tensor([1 if flag else 0], device="cuda", dtype=torch.int32)
+        dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
+        return int(t_ok.item()) == 1
+
     def setup_pipe():
+        """Collectives are unconditional; everything that can fail locally is guarded and agreed on afterwards."""
         from multiprocessing import shared_memory
 
         name = [f"ggrm_bench_flags_{os.environ.get('MASTER_PORT', '0')}_{os.getpid()}"] if rank == 0 else [None]
         dist.broadcast_object_list(name, src=0)
+        ok = True
         if rank == 0:
-            pipe["shm"] = shared_memory.SharedMemory(name=name[0], create=True, size=world * 64 * 4)
-            np.ndarray((world, 64), dtype=np.int32, buffer=pipe["shm"].buf)[:] = 0
-        dist.barrier()
+            try:
+                pipe["shm"] = shared_memory.SharedMemory(name=name[0], create=True, size=world * 64 * 4)
+                np.ndarray((world, 64), dtype=np.int32, buffer=pipe["shm"].buf)[:] = 0
+            except Exception as e:  # noqa: BLE001  (e.g. no POSIX shared memory in this container)
+                sys.stderr.write(f"[bench] band pipeline unavailable ({type(e).__name__}: {e}); using --reduce peer\n")
+                ok = False
+        if not all_ok(ok):
+            return False
         if rank != 0:
-            pipe["shm"] = shared_memory.SharedMemory(name=name[0])
-            try:  # only the creator unlinks; keep this process's resource tracker from trying again at exit (Python < 3.13)
-                from multiprocessing import resource_tracker
+            try:
+                pipe["shm"] = shared_memory.SharedMemory(name=name[0])
+                try:  # only the creator unlinks; keep this process's resource tracker from trying again at exit (Python < 3.13)
+                    from multiprocessing import resource_tracker
 
-                resource_tracker.unregister(pipe["shm"]._name, "shared_memory")
-            except Exception:  # noqa: BLE001
-                pass
-        pipe["flags"] = np.ndarray((world, 64), dtype=np.int32, buffer=pipe["shm"].buf)
-        bands = acc.band_layout()
-        pipe["mine"] = [(b, lo, hi) for b, (lo, hi) in enumerate(bands) if b % world == rank and hi > lo]
-        pipe["n_bands"] = len(bands)
-        elems = sum(g.tri(hi) - g.tri(lo) for _, lo, hi in pipe["mine"])
-        pipe["h_out"] = torch.empty(max(1, elems), dtype=torch.float32, pin_memory=True)
-        pipe["nvlink_bytes"] = int(sum(acc.row_slice(lo, hi)[1] - acc.row_slice(lo, hi)[0] for _, lo, hi in pipe["mine"]) * 4 * (world - 1))
+                    resource_tracker.unregister(pipe["shm"]._name, "shared_memory")
+                except Exception:  # noqa: BLE001
+                    pass
+            except Exception as e:  # noqa: BLE001
+                sys.stderr.write(f"[bench] rank {rank}: cannot attach band flags ({type(e).__name__}: {e}); using --reduce peer\n")
+                ok = False
+        if ok:
+            pipe["flags"] = np.ndarray((world, 64), dtype=np.int32, buffer=pipe["shm"].buf)
+            bands = acc.band_layout()
+            pipe["mine"] = [(b, lo, hi) for b, (lo, hi) in enumerate(bands) if b % world == rank and hi > lo]
+            pipe["n_bands"] = len(bands)
+            elems = sum(g.tri(hi) - g.tri(lo) for _, lo, hi in pipe["mine"])
+            pipe["h_out"] = torch.empty(max(1, elems), dtype=torch.float32, pin_memory=True)
+            pipe["nvlink_bytes"] = int(sum(acc.row_slice(lo, hi)[1] - acc.row_slice(lo, hi)[0] for _, lo, hi in pipe["mine"]) * 4 * (world - 1))
+        if not all_ok(ok):
+            return False
         pipe["ready"] = True
+        return True
 
     def pipelined_pass(push, fetch):
         pipe["pass_id"] += 1
@@ -344,8 +364,10 @@ def gpu_arm(args):
         acc.push_device(d_bed.data_ptr(), s0, ms)
         acc.finish()
         reduce_partials()
-        if use_pipe:      # first warm-up pass ran the blocking form (it maps the peers' accumulators); arm the pipeline now
-            setup_pipe()
+        if use_pipe and not pipe.get("failed"):  # first warm-up pass ran the blocking form (it maps the peers' accumulators); arm the pipeline now
+            if not setup_pipe():
+                pipe["failed"] = True
+                args.reduce = "peer"
 
     def fetch_mine():
         if world > 1 and args.reduce == "nccl":
