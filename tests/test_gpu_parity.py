@@ -418,6 +418,30 @@ def test_finish_async_banded_readout_matches_blocking(monkeypatch):
         a.close()
 
 
+@pytest.mark.parametrize("n,m", [(1, 5), (2, 1), (7, 1), (3, 64), (5, 65), (255, 3), (257, 130)])
+def test_minimal_and_ragged_shapes_vs_oracle(n, m):
+    # the reference's own edge cases (tests/test_bed_pipe.cpp:289-327: one sample, one SNP) plus sizes around the padding
+    # units of this implementation (4 samples per byte, 64-SNP operand blocks, 256-row tiles); center family so that a
+    # monomorphic or one-sample SNP stays finite (CenterHWE keeps sd out of the values)
+    bed = g.synth_bed_host(n, 0, m, 1000 + 17 * n + m, 0.1)
+    for method, kind in ((2, 0), (4, 1), (6, 0)):
+        G, den, freqs = o.grm_compute(bed, n, method, kind)
+        want = G[np.tril_indices(n)]
+        for prec, tol in ((g.PREC_FP64, 1e-12), (g.PREC_FP16, 2e-3)):
+            acc = run_gpu(bed, n, m, method, (kind,), prec, push=max(1, m // 2))
+            got, tr = acc.fetch(kind, g.GROUP_WHOLE, dtype=np.float64)
+            f = acc.snp_stats(0, m)[4]
+            acc.close()
+            assert got.shape == want.shape
+            assert np.array_equal(f, freqs)
+            assert same(np.isnan(got), np.isnan(want))
+            ok = ~np.isnan(want)
+            scale = max(1.0, float(np.max(np.abs(want[ok]))) if ok.any() else 1.0)
+            assert np.max(np.abs(got[ok] - want[ok]), initial=0.0) <= tol * scale, (n, m, method, kind, prec)
+            if np.isfinite(den):
+                assert abs(tr / n - den) <= tol * max(1.0, abs(den))
+
+
 def test_error_codes_follow_reference_semantics():
     acc = g.Accumulator(100, 50, method=1, precision=g.PREC_FP64)
     bed = g.synth_bed_host(100, 0, 50, 1, 0.0)
