@@ -472,7 +472,7 @@ def gpu_arm(args):
                          "traffic_launch": traffic_launch,
                          "flops_per_launch": fl_rank / launches, "avg_launch_ms": syrk_ms / launches, "launches_per_step": launches,
                          "launch_note": "achieved = this rank's credited flops of a step / its summed SYRK launch time (CUDA events on the library's compute "
-                                        "stream); a step is ceil(m_rank/16384) equal slabs, the last one launched as up to 8 row bands; traffic is the ncu "
+                                        "stream); a step is ceil(m_rank/16384) equal slabs, the last four accumulated band-major (up to 8 row bands x 4 slabs); traffic is the ncu "
                                         "--set full DRAM bytes of ONE steady-state 16384-SNP slab launch (traffic_launch)",
                          "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({how}); burst peak {burst} -> frac {achieved / burst:.3f}"},
         }
