@@ -512,9 +512,11 @@ def reference_arm(args):
 
 
 def main():
-    # keep stdout to the one JSON line: NCCL's "NCCL version ..." banner goes to stdout at NCCL_DEBUG=VERSION
-    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-        os.environ["NCCL_DEBUG"] = "WARN"
+    # keep stdout to the one JSON line: NCCL prints its "NCCL version ..." banner to stdout at NCCL_DEBUG=VERSION and above
+    # (WARN included), so drop the quiet levels and send whatever remains (INFO/TRACE asked for by the caller) to stderr
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION", "WARN"):
+        os.environ.pop("NCCL_DEBUG", None)
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
