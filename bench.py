@@ -281,9 +281,10 @@ def gpu_arm(args):
 
     # ---- N > 1, default (--reduce pipe): the same reduce-scatter, pipelined band by band behind the accumulation.  The last
     # slabs of every shard are accumulated row band by row band (ggrm_finish_async); each rank's CUDA host callbacks raise a
-    # flag per finished band in POSIX shared memory; band b belongs to rank b % N, which - as soon as all N flags of b are up -
-    # sums the peers' rows of b into its own over NVLink (ggrm_reduce_rows_async, on the read-out stream) and, in the e2e leg,
-    # reads them out, while every GPU is still on the tensor cores with the later bands.  No collective inside the pass.
+    # flag per finished band in POSIX shared memory; the 2048-row strips of the matrix are dealt to the ranks by LPT on their area
+    # (sharding.strip_owners), and the owner of a strip - as soon as all N flags of the strip's band are up - sums the peers'
+    # rows into its own over NVLink (ggrm_reduce_rows_async, on the read-out stream) and, in the e2e leg, reads them out,
+    # while every GPU is still on the tensor cores with the later bands.  No collective inside the pass.
     pipe = {"ready": False, "pass_id": 0}
 
     def all_ok(flag):
@@ -321,8 +322,10 @@ def gpu_arm(args):
                 ok = False
         if ok:
             pipe["flags"] = np.ndarray((world, 64), dtype=np.int32, buffer=pipe["shm"].buf)
+            from gelex_b200.sharding import strip_owners
+
             bands = acc.band_layout()
-            pipe["mine"] = [(b, lo, hi) for b, (lo, hi) in enumerate(bands) if b % world == rank and hi > lo]
+            pipe["mine"] = strip_owners(n, world, bands)[rank]   # 2048-row strips dealt by LPT; each waits for its band's flags
             pipe["n_bands"] = len(bands)
             elems = sum(g.tri(hi) - g.tri(lo) for _, lo, hi in pipe["mine"])
             pipe["h_out"] = torch.empty(max(1, elems), dtype=torch.float32, pin_memory=True)
@@ -450,8 +453,8 @@ def gpu_arm(args):
                            "peer": f"SNP-sharded over {world} GPUs + reduce-scatter of FP32 partial GRMs by 2048-row slices over NVLink peer memory (CUDA IPC, P2P loads) "
                                    "after a blocking finish; each rank fetches its own rows",
                            "pipe": f"SNP-sharded over {world} GPUs + reduce-scatter of FP32 partial GRMs over NVLink peer memory (CUDA IPC, P2P loads), pipelined "
-                                   f"band by band behind the accumulation: {pipe.get('n_bands')} row bands, band b owned by rank b % {world}, per-band completion flags "
-                                   "raised by CUDA host callbacks in POSIX shared memory, no collective inside the pass; each rank fetches its own bands"}[args.reduce],
+                                   f"band by band behind the accumulation: {pipe.get('n_bands')} row bands, 2048-row strips dealt to ranks by LPT on area, per-band completion flags "
+                                   "raised by CUDA host callbacks in POSIX shared memory, no collective inside the pass; each rank fetches its own strips"}[args.reduce],
                        "l2": "inputs (packed BED 6.25 GB, 16-bit operand slabs 0.8 GB, accumulator 5 GB) are larger than the 126 MB L2; no flush needed",
                        "timing": "CUDA events around the K steps, barrier + cuda synchronize on both sides, max over ranks; kernel phases by CUDA events on the library's streams",
                        "chunk_snps": int(os.environ.get("GGRM_CHUNK_SNPS", 16384)), "host": numa_note},

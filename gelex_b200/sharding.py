@@ -70,3 +70,19 @@ def row_slices(n: int, world: int, tile: int = 256, st: int = 8):
         cuts.append(max(cuts[-1], min(nsr, c)))
     cuts.append(nsr)
     return [(min(n, cuts[r] * tile * st), min(n, cuts[r + 1] * tile * st)) for r in range(world)]
+
+
+def strip_owners(n: int, world: int, bands, rows_per_strip: int = 2048):
+    """Band-pipelined reduce-scatter: who reduces and reads out which 2048-row strip.
+    `bands` = [(row_begin, row_end)] in completion order (ggrm_band_layout).  Strips are dealt by LPT on their triangle area
+    (largest first, to the least loaded rank), so every rank moves about the same bytes and the strips of the LAST band -
+    the only ones whose reduce + read-out cannot hide behind the accumulation - land on different ranks.
+    Returns per rank a list of (band_index, row_begin, row_end) in row order."""
+    strips = [(lo, min(n, lo + rows_per_strip)) for lo in range(0, n, rows_per_strip)]
+    area = [hi * (hi + 1) // 2 - lo * (lo + 1) // 2 for lo, hi in strips]
+    owner = lpt_assign(area, world) if world > 1 else [0] * len(strips)
+    out = [[] for _ in range(world)]
+    for (lo, hi), r in zip(strips, owner):
+        b = next(i for i, (_, be) in enumerate(bands) if hi <= be)
+        out[r].append((b, lo, hi))
+    return out

@@ -118,16 +118,14 @@ def _pipelined_worker(rank, world, port, tmpdir):
         bands = acc.band_layout()
         assert len(bands) == 3 and bands[-1][1] == N
         got = {}
-        for b, (r0, r1) in enumerate(bands):
-            if b % world != rank:
-                continue
+        for b, r0, r1 in sharding.strip_owners(N, world, bands)[rank]:
             t0 = time.time()
             while not np.all(flags[:, b] == pass_id):
                 assert time.time() - t0 < 60, "peer band flag never arrived"
                 time.sleep(0.0002)
             acc.reduce_rows_async(g.KIND_ADD, g.GROUP_WHOLE, peers, r0, r1)
             rows, tr = acc.fetch(g.KIND_ADD, g.GROUP_WHOLE, r0, r1 - r0, dtype=np.float64)
-            got[b] = (rows, tr)
+            got[r0 // 2048] = (rows, tr)
         acc.finish()
         dist.barrier()  # nobody re-arms (first slab stores) while a peer may still read its rows
         for b, (rows, tr) in got.items():

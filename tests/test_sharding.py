@@ -91,3 +91,30 @@ def test_cpp_engine_uses_the_same_row_slice_rule():
     for n in (1, 2047, 2048, 2049, 4500, 50000, 123457, 200000):
         for w in (1, 2, 3, 4, 7, 8):
             assert engine.row_slices(n, w) == sharding.row_slices(n, w), (n, w)
+
+
+def test_strip_owners_cover_balance_and_spread_the_last_band():
+    for n, nb in ((4500, 3), (50000, 8), (200000, 8)):
+        strips_total = (n + 2047) // 2048
+        # bands as the library cuts them: whole strips, about equal tile counts (here: equal strip-area shares are close enough)
+        area = [min(n, (s + 1) * 2048) * (min(n, (s + 1) * 2048) + 1) // 2 - (s * 2048) * (s * 2048 + 1) // 2 for s in range(strips_total)]
+        tot, acc, ends = sum(area), 0, []
+        for s_, a in enumerate(area):
+            acc += a
+            if len(ends) + 1 < nb and acc >= (len(ends) + 1) * tot / nb or s_ + 1 == strips_total:
+                ends.append(min(n, (s_ + 1) * 2048))
+        bands = [(0 if i == 0 else ends[i - 1], e) for i, e in enumerate(ends)]
+        for w in (1, 2, 3, 4, 8):
+            own = sharding.strip_owners(n, w, bands)
+            flat = sorted((lo, hi) for r in own for _, lo, hi in r)
+            assert flat == [(s * 2048, min(n, (s + 1) * 2048)) for s in range(strips_total)]       # every strip exactly once
+            assert all(bands[b][0] <= lo and hi <= bands[b][1] for r in own for b, lo, hi in r)    # tagged with its band
+            assert all(r == sorted(r, key=lambda t: t[1]) for r in own)                            # row (= completion) order
+            loads = [sum(hi * (hi + 1) // 2 - lo * (lo + 1) // 2 for _, lo, hi in r) for r in own]
+            if strips_total >= 3 * w:
+                assert max(loads) <= 1.15 * sum(loads) / w, (n, w, loads)
+            last = [r_i for r_i, r in enumerate(own) for b, _, _ in r if b == len(bands) - 1]
+            # the last band's strips (the exposed tail) are spread over the ranks, not piled on one (the small ragged strip may double up)
+            assert max(last.count(r_i) for r_i in set(last)) <= -(-len(last) // w) + 1, (n, w, last)
+            if w > 1 and len(last) > 1:
+                assert len(set(last)) >= min(len(last) - 1, w), (n, w, last)
