@@ -69,7 +69,7 @@ EXPORTS = [
     "ggrm_synth_bed_host", "ggrm_synth_bed_device", "ggrm_device_count", "ggrm_version", "ggrm_enable_peer_access",
     "ggrm_ipc_export", "ggrm_ipc_open", "ggrm_ipc_close", "ggrm_row_slice",
     "ggrm_fetch_block", "ggrm_owned_supertiles", "ggrm_host_alloc", "ggrm_host_free", "ggrm_bin_to_dense", "ggrm_assoc_chunk",
-    "ggrm_band_layout", "ggrm_set_band_flags", "ggrm_reduce_rows_async",
+    "ggrm_band_layout", "ggrm_set_band_flags", "ggrm_reduce_rows_async", "ggrm_genotype_chunk",
 ]
 
 _lib = None
@@ -119,6 +119,7 @@ def load() -> C.CDLL:
     lib.ggrm_decode_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, vp]
     lib.ggrm_standardise_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, C.c_int, C.c_int, C.c_int, vp, vp]
     lib.ggrm_assoc_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, C.c_int, C.c_int, vp, vp]
+    lib.ggrm_genotype_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp]
     lib.ggrm_synth_bed_host.argtypes = [vp, i64, i64, i64, u64, dbl]
     lib.ggrm_synth_bed_device.argtypes = [C.c_int, vp, i64, i64, i64, u64, dbl]
     lib.ggrm_device_count.argtypes = []
@@ -359,6 +360,26 @@ def assoc_chunk(payload, n_raw, method, kind, n_out=None, raw_to_out=None, devic
     if st != 0:
         raise GrmError(st, lib.ggrm_last_error(None).decode())
     return out.T, freq
+
+
+def genotype_chunk(payload, n_raw, method, kind, n_out=None, raw_to_out=None, device=0):
+    """GenotypeLoader/GenotypePipe::process_chunk (genotype_loader.cpp:51-79): standardised (n_out, c) chunk + per-SNP LocusStatistic
+    as a dict {freq, mean, stddev, mono}."""
+    lib = load()
+    n_out = n_raw if n_out is None else n_out
+    bpv = (n_raw + 3) // 4
+    payload = np.ascontiguousarray(payload, dtype=np.uint8)
+    c = payload.size // bpv
+    out = np.empty((c, n_out), dtype=np.float64)
+    freq, mean, sd = (np.empty(c, dtype=np.float64) for _ in range(3))
+    mono = np.empty(c, dtype=np.uint8)
+    r2o = None if raw_to_out is None else np.ascontiguousarray(raw_to_out, dtype=np.int32)
+    m = METHODS[method] if isinstance(method, str) else int(method)
+    st = lib.ggrm_genotype_chunk(device, _ptr(payload), c, bpv, n_raw, n_out, _ptr(r2o), m, kind, _ptr(out), _ptr(freq), _ptr(mean), _ptr(sd),
+                                 _ptr(mono))
+    if st != 0:
+        raise GrmError(st, lib.ggrm_last_error(None).decode())
+    return out.T, {"freq": freq, "mean": mean, "stddev": sd, "mono": mono.astype(bool)}
 
 
 def synth_bed_host(n, snp_begin, snp_count, seed, missing_rate=0.01):

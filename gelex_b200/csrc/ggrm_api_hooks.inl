@@ -15,7 +15,8 @@ struct ScratchFree {
 };
 
 static void decode_common(int device, const uint8_t* payload, int64_t snp_count, int64_t bpv, int64_t n_raw, int64_t n_out,
-                          const int32_t* raw_to_out, int method, int kind, int policy, bool standardise, double* out, double* freq) {
+                          const int32_t* raw_to_out, int method, int kind, int policy, bool standardise, double* out, double* freq,
+                          double* mean = nullptr, double* stddev = nullptr, uint8_t* monomorphic = nullptr) {
     check_device(device, nullptr);
     if (payload == nullptr || out == nullptr) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "null argument"};
     if (n_raw <= 0 || n_out <= 0 || snp_count <= 0 || snp_count > 65535) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "test hook limits: 0 < snp_count <= 65535"};
@@ -43,12 +44,16 @@ static void decode_common(int device, const uint8_t* payload, int64_t snp_count,
     GGRM_CUDA(cudaGetLastError());
     SnpTable* d_tab = nullptr;
     double* d_freq = nullptr;
+    SnpMoments* d_mom = nullptr;
+    const bool want_moments = mean != nullptr || stddev != nullptr || monomorphic != nullptr;
     if (standardise) {
         d_tab = sf.alloc<SnpTable>(static_cast<size_t>(snp_count));
         d_freq = sf.alloc<double>(static_cast<size_t>(snp_count));
+        if (want_moments) d_mom = sf.alloc<SnpMoments>(static_cast<size_t>(snp_count));
         StatsOut so{};
         so.freq = d_freq;
         so.tab64[kind] = d_tab;
+        so.moments[kind] = d_mom;
         count_stats_kernel<<<static_cast<unsigned>((snp_count + 7) / 8), 256>>>(d_dense, bpv_pad, n_out, n_pad, snp_count, method, policy, 0, so, 0);
         GGRM_CUDA(cudaGetLastError());
     }
@@ -57,6 +62,15 @@ static void decode_common(int device, const uint8_t* payload, int64_t snp_count,
     GGRM_CUDA(cudaGetLastError());
     GGRM_CUDA(cudaMemcpy(out, d_out, static_cast<size_t>(snp_count * n_out) * sizeof(double), cudaMemcpyDeviceToHost));
     if (standardise && freq != nullptr) GGRM_CUDA(cudaMemcpy(freq, d_freq, static_cast<size_t>(snp_count) * sizeof(double), cudaMemcpyDeviceToHost));
+    if (d_mom != nullptr) {
+        std::vector<SnpMoments> mo(static_cast<size_t>(snp_count));
+        GGRM_CUDA(cudaMemcpy(mo.data(), d_mom, mo.size() * sizeof(SnpMoments), cudaMemcpyDeviceToHost));
+        for (size_t j = 0; j < mo.size(); ++j) {
+            if (mean != nullptr) mean[j] = mo[j].mean;
+            if (stddev != nullptr) stddev[j] = mo[j].stddev;
+            if (monomorphic != nullptr) monomorphic[j] = static_cast<uint8_t>(mo[j].monomorphic);
+        }
+    }
 }
 
 }  // namespace ggrm
@@ -102,6 +116,18 @@ extern "C" int ggrm_assoc_chunk(int device, const uint8_t* bed_payload, int64_t 
     if (kind != GGRM_KIND_ADD && kind != GGRM_KIND_DOM) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "kind must be 0 (add) or 1 (dom)"};
     decode_common(device, bed_payload, snp_count, bytes_per_variant, n_raw, n_out, raw_to_out, method, kind, GGRM_ALLMISS_REFERENCE_NAN, true,
                   out_colmajor, freq);
+    GGRM_STATELESS_END
+}
+
+// GenotypeLoader::process_chunk / GenotypePipe::process_chunk (src/data/genotype/genotype_loader.cpp:51-79, genotype_pipe.cpp:28-49):
+// the standardised chunk itself is the product, with the LocusStatistic of every SNP beside it.
+extern "C" int ggrm_genotype_chunk(int device, const uint8_t* bed_payload, int64_t snp_count, int64_t bytes_per_variant, int64_t n_raw,
+                                   int64_t n_out, const int32_t* raw_to_out, int method, int kind, double* out_colmajor, double* freq,
+                                   double* mean, double* stddev, uint8_t* is_monomorphic) {
+    GGRM_STATELESS_BEGIN
+    if (kind != GGRM_KIND_ADD && kind != GGRM_KIND_DOM) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "kind must be 0 (add) or 1 (dom)"};
+    decode_common(device, bed_payload, snp_count, bytes_per_variant, n_raw, n_out, raw_to_out, method, kind, GGRM_ALLMISS_REFERENCE_NAN, true,
+                  out_colmajor, freq, mean, stddev, is_monomorphic);
     GGRM_STATELESS_END
 }
 

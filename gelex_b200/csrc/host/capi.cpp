@@ -4,6 +4,7 @@
 #include <string>
 
 #include "exceptions.h"
+#include "genotype_pipe.h"
 #include "grm_engine.h"
 #include "grm_loader.h"
 #include "plink_meta.h"
@@ -159,4 +160,84 @@ extern "C" int gelex_b200_row_slices(int64_t n, int parts, int64_t* begin_end) {
         begin_end[2 * r + 1] = sl[r].second;
     }
     return static_cast<int>(sl.size());
+}
+
+// Current exception -> (status, "Type: message"); call inside a catch (...) block.
+static int translate_exception(char* err, int err_len) {
+    try {
+        throw;
+    } catch (const FileNotFoundException& e) { set_err(err, err_len, std::string("FileNotFoundException: ") + e.what()); return -10;
+    } catch (const FileOpenException& e) { set_err(err, err_len, std::string("FileOpenException: ") + e.what()); return -11;
+    } catch (const FileWriteException& e) { set_err(err, err_len, std::string("FileWriteException: ") + e.what()); return -12;
+    } catch (const FileExistsException& e) { set_err(err, err_len, std::string("FileExistsException: ") + e.what()); return -13;
+    } catch (const FileFormatException& e) { set_err(err, err_len, std::string("FileFormatException: ") + e.what()); return GGRM_ERR_FILE_FORMAT;
+    } catch (const ColumnRangeException& e) { set_err(err, err_len, std::string("ColumnRangeException: ") + e.what()); return GGRM_ERR_COLUMN_RANGE;
+    } catch (const ArgumentValidationException& e) { set_err(err, err_len, std::string("ArgumentValidationException: ") + e.what()); return GGRM_ERR_INVALID_ARGUMENT;
+    } catch (const InvalidInputException& e) { set_err(err, err_len, std::string("InvalidInputException: ") + e.what()); return GGRM_ERR_INVALID_ARGUMENT;
+    } catch (const InvalidOperationException& e) { set_err(err, err_len, std::string("InvalidOperationException: ") + e.what()); return GGRM_ERR_INVALID_OPERATION;
+    } catch (const GelexException& e) { set_err(err, err_len, std::string("GelexException: ") + e.what()); return GGRM_ERR_CUDA;
+    } catch (const std::bad_alloc&) { set_err(err, err_len, "std::bad_alloc"); return GGRM_ERR_OUT_OF_MEMORY;
+    } catch (const std::exception& e) { set_err(err, err_len, std::string("std::exception: ") + e.what()); return -99; }
+}
+
+static void copy_stats(const GenotypeStats& st, int64_t* dims3, double* mean, double* stddev, double* freq, int64_t* mono, int64_t mono_cap) {
+    if (dims3 != nullptr) {
+        dims3[0] = st.num_samples;
+        dims3[1] = st.num_variants;
+        dims3[2] = static_cast<int64_t>(st.monomorphic_indices.size());
+    }
+    const size_t m = static_cast<size_t>(st.num_variants);
+    if (mean != nullptr) std::memcpy(mean, st.means.data(), m * sizeof(double));
+    if (stddev != nullptr) std::memcpy(stddev, st.stddevs.data(), m * sizeof(double));
+    if (freq != nullptr) std::memcpy(freq, st.freqs.data(), m * sizeof(double));
+    if (mono != nullptr)
+        for (size_t k = 0; k < st.monomorphic_indices.size() && static_cast<int64_t>(k) < mono_cap; ++k) mono[k] = st.monomorphic_indices[k];
+}
+
+// GenotypePipe(bed, prefix).process<GT>(method, chunk) through C: writes <prefix>.bmat + <prefix>.snpstats.  dims3 = {n, m, #mono};
+// mean/stddev/freq (m doubles each) and mono (mono_cap indices) may be NULL.  Returns 0 or a negative / GGRM_ERR_* status.
+extern "C" int gelex_b200_genotype_export(const char* bfile, const char* out_prefix, int method, int additive, int chunk_size, int device,
+                                          int64_t* dims3, double* mean, double* stddev, double* freq, int64_t* mono, int64_t mono_cap,
+                                          char* err, int err_len) {
+    try {
+        if (bfile == nullptr || out_prefix == nullptr) throw ArgumentValidationException("null argument");
+        if (method < 1 || method > 8) throw InvalidInputException("Invalid genotype process method.");
+        if (chunk_size <= 0) throw ArgumentValidationException("chunk_size must be positive");
+        GenotypePipe pipe(format_bed_path(bfile), out_prefix, device);
+        const GenotypeStats st = pipe.process(additive != 0, static_cast<GenotypeProcessMethod>(method), static_cast<size_t>(chunk_size));
+        copy_stats(st, dims3, mean, stddev, freq, mono, mono_cap);
+        set_err(err, err_len, "");
+        return 0;
+    } catch (...) {
+        return translate_exception(err, err_len);
+    }
+}
+
+// GenotypeLoader(bed).process<GT>(method, chunk) through C.  Call with out == NULL to query dims3 = {n, m, 0} (no GPU work); otherwise
+// out must hold n*m doubles (column-major).
+extern "C" int gelex_b200_genotype_load(const char* bfile, int method, int additive, int chunk_size, int device, double* out, int64_t out_cap,
+                                        int64_t* dims3, double* mean, double* stddev, double* freq, int64_t* mono, int64_t mono_cap, char* err,
+                                        int err_len) {
+    try {
+        if (bfile == nullptr) throw ArgumentValidationException("null argument");
+        if (method < 1 || method > 8) throw InvalidInputException("Invalid genotype process method.");
+        if (chunk_size <= 0) throw ArgumentValidationException("chunk_size must be positive");
+        GenotypeLoader loader(format_bed_path(bfile), device);
+        if (out == nullptr) {
+            if (dims3 != nullptr) {
+                dims3[0] = loader.num_samples();
+                dims3[1] = loader.num_variants();
+                dims3[2] = 0;
+            }
+            set_err(err, err_len, "");
+            return 0;
+        }
+        if (out_cap < loader.num_samples() * loader.num_variants()) throw ArgumentValidationException("output buffer too small");
+        const GenotypeStats st = loader.process(additive != 0, static_cast<GenotypeProcessMethod>(method), out, static_cast<size_t>(chunk_size));
+        copy_stats(st, dims3, mean, stddev, freq, mono, mono_cap);
+        set_err(err, err_len, "");
+        return 0;
+    } catch (...) {
+        return translate_exception(err, err_len);
+    }
 }

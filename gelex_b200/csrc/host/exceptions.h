@@ -21,6 +21,7 @@ class GelexException : public std::runtime_error {
 GGRM_DEFINE_EXC(FileNotFoundException);
 GGRM_DEFINE_EXC(FileOpenException);
 GGRM_DEFINE_EXC(FileWriteException);
+GGRM_DEFINE_EXC(FileExistsException);
 GGRM_DEFINE_EXC(FileFormatException);
 GGRM_DEFINE_EXC(DataParseException);
 GGRM_DEFINE_EXC(ArgumentValidationException);

@@ -76,9 +76,15 @@ __global__ void __launch_bounds__(256) repack_kernel(const uint8_t* __restrict__
 struct SnpTable {
     double z[4];
 };
+// LocusStatistic (include/gelex/types/genetic_effect_type.h:20-26) minus maf: what GenotypeLoader / GenotypePipe keep per SNP.
+struct SnpMoments {
+    double mean, stddev;
+    int monomorphic;
+};
 
 __device__ __forceinline__ void compute_snp_table(int method, int kind, int n0, int n1, int n2, int nmiss,
-                                                  int all_missing_policy, double* freq_out, SnpTable* tab) {
+                                                  int all_missing_policy, double* freq_out, SnpTable* tab,
+                                                  SnpMoments* mom = nullptr) {
     const double qnan = __longlong_as_double(0x7ff8000000000000ll);
     const int validi = n0 + n1 + n2;
     (void)nmiss;
@@ -87,6 +93,7 @@ __device__ __forceinline__ void compute_snp_table(int method, int kind, int n0, 
         const double v = (all_missing_policy == GGRM_ALLMISS_SKIP) ? 0.0 : qnan;
         tab->z[0] = tab->z[1] = tab->z[2] = tab->z[3] = v;
         *freq_out = 0.0;  // LocusStatistic{} default
+        if (mom != nullptr) *mom = SnpMoments{0.0, 0.0, 0};
         return;
     }
     const double valid = static_cast<double>(validi);
@@ -146,6 +153,7 @@ __device__ __forceinline__ void compute_snp_table(int method, int kind, int n0, 
     double z0 = __dsub_rn(e0, mean), z1 = __dsub_rn(e1, mean), z2 = __dsub_rn(e2, mean);
     double zm = __dsub_rn(mean, mean);  // missing -> mean -> centred (0, or NaN if mean is not finite)
     const bool mono = sd < 1e-10;       // MONOMORPHIC_TOL; NaN compares false exactly like the reference
+    if (mom != nullptr) *mom = SnpMoments{mean, sd, mono ? 1 : 0};
     if (scale && !mono) {
         z0 = __ddiv_rn(z0, sd);
         z1 = __ddiv_rn(z1, sd);
@@ -173,6 +181,7 @@ struct StatsOut {
     double* freq;       // may be nullptr
     uint2* tab16[2];    // [kind]; nullptr when that kind / precision is not wanted
     SnpTable* tab64[2];
+    SnpMoments* moments[2];  // [kind]; only the genotype-export hook asks for them (with tab64 of the same kind)
 };
 
 __global__ void __launch_bounds__(256) count_stats_kernel(const uint8_t* __restrict__ dense, int64_t bpv_pad,
@@ -215,7 +224,9 @@ __global__ void __launch_bounds__(256) count_stats_kernel(const uint8_t* __restr
         for (int kind = 0; kind < 2; ++kind) {
             if (out.tab16[kind] == nullptr && out.tab64[kind] == nullptr) continue;
             SnpTable t;
-            compute_snp_table(method, kind, n0, n1, n2, nmiss, all_missing_policy, &freq, &t);
+            SnpMoments mo;
+            compute_snp_table(method, kind, n0, n1, n2, nmiss, all_missing_policy, &freq, &t, &mo);
+            if (out.moments[kind] != nullptr) out.moments[kind][snp] = mo;
             if (out.tab64[kind] != nullptr) out.tab64[kind][snp] = t;
             if (out.tab16[kind] != nullptr) {
                 const uint32_t a = to_op16(t.z[0], fp16) | (static_cast<uint32_t>(to_op16(t.z[1], fp16)) << 16);

@@ -38,6 +38,11 @@ def load_host():
         h.gelex_b200_grm_load.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_char_p, C.c_int]
         h.gelex_b200_grm_load.restype = C.c_int64
         h.gelex_b200_row_slices.argtypes = [C.c_int64, C.c_int, C.c_void_p]
+        vp = C.c_void_p
+        h.gelex_b200_genotype_export.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, C.c_int64,
+                                                 C.c_char_p, C.c_int]
+        h.gelex_b200_genotype_load.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int64, vp, vp, vp, vp, vp, C.c_int64,
+                                               C.c_char_p, C.c_int]
         _host = h
     return _host
 
@@ -111,3 +116,68 @@ def row_slices(n, parts):
     if got != parts:
         raise EngineError(got, "row_slices failed")
     return [(int(out[2 * r]), int(out[2 * r + 1])) for r in range(parts)]
+
+
+def _genotype_dims(bfile):
+    h = load_host()
+    dims = np.zeros(3, dtype=np.int64)
+    err = C.create_string_buffer(2048)
+    st = h.gelex_b200_genotype_load(str(bfile).encode(), 1, 1, 1, 0, None, 0, dims.ctypes.data_as(C.c_void_p), None, None, None, None, 0, err, len(err))
+    if st != 0:
+        raise EngineError(int(st), err.value.decode())
+    return int(dims[0]), int(dims[1])
+
+
+def _stats_dict(dims, mean, sd, freq, mono):
+    return {"num_samples": int(dims[0]), "num_variants": int(dims[1]), "mean": mean, "stddev": sd, "freq": freq,
+            "monomorphic_indices": mono[: int(dims[2])].copy()}
+
+
+def genotype_export(bfile, out_prefix, method="OSH", additive=True, chunk_size=10000, device=0):
+    """GenotypePipe(bed, prefix).process<GT>(method, chunk) (genotype_pipe.h:55-89): writes <prefix>.bmat (column-major FP64 n x m) and
+    <prefix>.snpstats; returns the per-SNP statistics the .snpstats file holds (+ A1 frequencies)."""
+    h = load_host()
+    n, m = _genotype_dims(bfile)
+    mth = _lib.METHODS[method] if isinstance(method, str) else int(method)
+    dims = np.zeros(3, dtype=np.int64)
+    mean, sd, freq = (np.empty(m, dtype=np.float64) for _ in range(3))
+    mono = np.empty(max(1, m), dtype=np.int64)
+    err = C.create_string_buffer(2048)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    st = h.gelex_b200_genotype_export(str(bfile).encode(), str(out_prefix).encode(), mth, int(additive), int(chunk_size), int(device), p(dims),
+                                      p(mean), p(sd), p(freq), p(mono), m, err, len(err))
+    if st != 0:
+        raise EngineError(int(st), err.value.decode())
+    return _stats_dict(dims, mean, sd, freq, mono)
+
+
+def genotype_load(bfile, method="OSH", additive=True, chunk_size=10000, device=0):
+    """GenotypeLoader(bed).process<GT>(method, chunk) (genotype_loader.h:52-80): the standardised (n, m) matrix (Fortran order, as
+    Eigen holds it) + statistics."""
+    h = load_host()
+    n, m = _genotype_dims(bfile)
+    mth = _lib.METHODS[method] if isinstance(method, str) else int(method)
+    out = np.empty((n, m), dtype=np.float64, order="F")
+    dims = np.zeros(3, dtype=np.int64)
+    mean, sd, freq = (np.empty(m, dtype=np.float64) for _ in range(3))
+    mono = np.empty(max(1, m), dtype=np.int64)
+    err = C.create_string_buffer(2048)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    st = h.gelex_b200_genotype_load(str(bfile).encode(), mth, int(additive), int(chunk_size), int(device), p(out), n * m, p(dims), p(mean), p(sd),
+                                    p(freq), p(mono), m, err, len(err))
+    if st != 0:
+        raise EngineError(int(st), err.value.decode())
+    return out, _stats_dict(dims, mean, sd, freq, mono)
+
+
+def read_snp_stats(path):
+    """The .snpstats layout (snp_stats_writer.cpp:50-91) as GenotypeMap::load_metadata reads it (genotype_mmap.cpp:64-106)."""
+    raw = Path(path).read_bytes()
+    n, m, k = (int(v) for v in np.frombuffer(raw, dtype=np.int64, count=3))
+    off = 24
+    mono = np.frombuffer(raw, dtype=np.int64, count=k, offset=off).copy()
+    off += 8 * k
+    mean = np.frombuffer(raw, dtype=np.float64, count=m, offset=off).copy()
+    sd = np.frombuffer(raw, dtype=np.float64, count=m, offset=off + 8 * m).copy()
+    assert len(raw) == off + 16 * m, "trailing bytes in .snpstats"
+    return {"num_samples": n, "num_variants": m, "monomorphic_indices": mono, "mean": mean, "stddev": sd}

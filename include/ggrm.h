@@ -227,6 +227,17 @@ int ggrm_standardise_chunk(int device, const uint8_t* bed_payload, int64_t snp_c
 int ggrm_assoc_chunk(int device, const uint8_t* bed_payload, int64_t snp_count, int64_t bytes_per_variant, int64_t n_raw,
                      int64_t n_out, const int32_t* raw_to_out, int method, int kind, double* out_colmajor, double* freq);
 
+/* Whole-matrix standardised genotype export: the chunk body of GenotypeLoader::process
+ * (include/gelex/data/genotype/genotype_loader.h:52-80, src/data/genotype/genotype_loader.cpp:51-79) and GenotypePipe::process
+ * (genotype_pipe.h:55-89, genotype_pipe.cpp:28-49) = load_chunk + process_matrix<GT> for any of the 8 methods, the
+ * standardised column-major n_out x snp_count chunk being the product, with every SNP's LocusStatistic
+ * (include/gelex/types/genetic_effect_type.h:20-26) beside it: freq = maf, mean, stddev, is_monomorphic (stddev < 1e-10; an
+ * all-missing SNP returns the default {0, 0, 0, false} and a NaN column, genotype_processor.h:38-42).  Any of the four
+ * per-SNP outputs may be NULL. */
+int ggrm_genotype_chunk(int device, const uint8_t* bed_payload, int64_t snp_count, int64_t bytes_per_variant, int64_t n_raw,
+                        int64_t n_out, const int32_t* raw_to_out, int method, int kind, double* out_colmajor, double* freq,
+                        double* mean, double* stddev, uint8_t* is_monomorphic);
+
 /* ---- Synthetic PLINK BED payload: p_j~U(0.05,0.5), HWE genotypes, i.i.d. missing -------------------
  * Counter-based integer RNG, bit-identical on host and device.  Writes snp_count rows of ceil(n/4) bytes for SNPs
  * [snp_begin, snp_begin+snp_count); padding bits of the last byte are 0. */

@@ -119,6 +119,49 @@ def test_assoc_chunk_preprocessing_center_family_only(golden_dir):
         assert e.value.status == -1 and "supports only center-family methods" in e.value.message
 
 
+def test_genotype_chunk_locus_statistics(golden_dir):
+    # the standardised chunk as the product (GenotypeLoader / GenotypePipe::process_chunk) with every SNP's
+    # LocusStatistic.  (1) the columns of the reference's own unit tests, outputs of the unmodified reference
+    import json
+
+    vectors = json.load(open(golden_dir / "process_vectors.json"))
+    for v in vectors:
+        col = np.array([float("nan") if x == "nan" else float(x) for x in v["input"]], dtype=np.float64)
+        ref = np.array([float("nan") if x == "nan" else x for x in v["z"]], dtype=np.float64)
+        z, st = g.genotype_chunk(plink_io.encode_matrix(col[:, None]), col.size, v["method"], 0 if v["kind"] == "A" else 1)
+        assert st["freq"][0] == v["maf"], v
+        assert close(z[:, 0], ref, rtol=1e-12, atol=1e-13), v
+        assert bool(st["mono"][0]) == bool(v["mono"]), v
+        assert abs(st["mean"][0] - v["mean"]) <= 1e-14 * abs(v["mean"]), v
+        assert abs(st["stddev"][0] - v["stddev"]) <= 1e-12 * abs(v["stddev"]) + 1e-300, v
+    # (2) random SNPs through a shuffled projection + monomorphic / all-missing / single-valid columns, against the oracle
+    n = 777
+    fam = [(f"f{i % 4}", f"s{(i * 5011) % n}") for i in range(n)]
+    ids, r2o = plink_io.sample_order(fam)
+    bed = g.synth_bed_host(n, 0, 96, 17, 0.05)
+    special = np.full((n, 4), 2.0)
+    special[:, 1] = np.nan           # all missing: default LocusStatistic, NaN column
+    special[:, 2] = 0.0              # monomorphic
+    special[5:, 3] = np.nan          # five valid calls only
+    special[:5, 3] = [0, 1, 2, 1, 1]
+    bed = np.concatenate([bed, plink_io.encode_matrix(special)])
+    raw = o.decode_chunk(bed, n, len(ids), r2o)
+    for method in range(1, 9):
+        for kind in (0, 1):
+            z, st = g.genotype_chunk(bed, n, method, kind, n_out=len(ids), raw_to_out=r2o)
+            zr, fr = o.process_matrix(raw, method, kind)
+            assert np.array_equal(st["freq"], fr)
+            assert close(z, zr, rtol=1e-12, atol=1e-13)
+            for j in range(raw.shape[1]):
+                _, ls = o.process_column(raw[:, j], method, kind)
+                assert bool(st["mono"][j]) == bool(ls.is_monomorphic), (method, kind, j)
+                assert close(st["mean"][j], ls.mean, rtol=1e-13, atol=0), (method, kind, j)  # sample-policy means are sums over the column
+                assert close(st["stddev"][j], ls.stddev, rtol=1e-12, atol=1e-300), (method, kind, j)
+    with pytest.raises(g.GrmError) as e:
+        g.genotype_chunk(bed, n, 9, 0, n_out=len(ids), raw_to_out=r2o)
+    assert "Invalid genotype process method." in e.value.message
+
+
 def test_all_missing_snp_policy():
     n = 64
     geno = np.random.default_rng(2).integers(0, 3, size=(n, 6)).astype(np.float64)

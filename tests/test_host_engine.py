@@ -344,3 +344,82 @@ def test_loco_grm_loader_known_answers_of_the_reference_tests(tmp_path):
     _write_grm(tmp_path / "big", gw * 2, ids)
     with pytest.raises(engine.EngineError, match="LOCO error: Chromosome GRM denominator .* is greater than or equal to Whole GRM denominator"):
         engine.load_grm(tmp_path / "whole", chr_prefix=tmp_path / "big")
+
+
+# ------------------------------------------------------------------------------------------------ standardised genotype export
+def test_genotype_export_validation_needs_no_gpu(golden_dir, tmp_path):
+    # GenotypePipe::GenotypePipe (genotype_pipe.cpp:51-82): inputs are opened and existing outputs refused before any device work
+    assert engine._genotype_dims(golden_dir / "tiny") == (36, 96)   # sorted + de-duplicated samples, BIM lines
+    (tmp_path / "have.bmat").write_bytes(b"")
+    with pytest.raises(engine.EngineError, match="FileExistsException: .*have: existing files"):
+        engine.genotype_export(golden_dir / "tiny", tmp_path / "have")
+    (tmp_path / "have.bmat").unlink()
+    (tmp_path / "have.snpstats").write_bytes(b"")
+    with pytest.raises(engine.EngineError, match="FileExistsException"):
+        engine.genotype_export(golden_dir / "tiny", tmp_path / "have")
+    with pytest.raises(engine.EngineError, match="FileNotFoundException"):
+        engine.genotype_export(tmp_path / "nothing", tmp_path / "out")
+    h = engine.load_host()
+    import ctypes as C
+
+    err = C.create_string_buffer(512)
+    st = h.gelex_b200_genotype_export(str(golden_dir / "tiny").encode(), str(tmp_path / "o").encode(), 9, 1, 100, 0, None, None, None, None, None, 0,
+                                      err, len(err))
+    assert st == -1 and b"Invalid genotype process method." in err.value
+    assert not (tmp_path / "o.bmat").exists()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("method,additive,chunk", [("OSH", True, 10000), ("SH", False, 7), ("OC", False, 40), ("S", True, 33)])
+def test_genotype_export_files_match_reference_layout(golden_dir, tmp_path, method, additive, chunk):
+    # tiny fixture (37 FAM lines, one duplicated id, shuffled): the values are the unmodified reference's process_matrix outputs
+    # (tiny_chunks.npz); .bmat = column-major FP64 without header, .snpstats = {n, m, #mono} + indices + means + stddevs
+    import oracle_lib as o
+    from test_oracle_golden import close, load_tiny
+
+    payload, n_raw, ids, r2o, _ = load_tiny(golden_dir)
+    n, m = len(ids), payload.shape[0]
+    code, kind = g.METHODS[method], 0 if additive else 1
+    st = engine.genotype_export(golden_dir / "tiny", tmp_path / "t", method=method, additive=additive, chunk_size=chunk)
+    gold = np.load(golden_dir / "tiny_chunks.npz")
+    bmat = np.fromfile(tmp_path / "t.bmat", dtype=np.float64)
+    assert bmat.size == n * m                                      # GenotypeMap's exact-size check (genotype_mmap.cpp:44-53)
+    z = bmat.reshape(m, n).T
+    assert close(z, gold[f"z_{code}_{'A' if additive else 'D'}"], rtol=1e-12, atol=1e-13)
+    assert np.array_equal(st["freq"], gold[f"freq_{code}_{'A' if additive else 'D'}"])
+    meta = engine.read_snp_stats(tmp_path / "t.snpstats")
+    assert (meta["num_samples"], meta["num_variants"]) == (n, m)
+    raw = o.decode_chunk(payload, n_raw, n, r2o)
+    mono = []
+    for j in range(m):
+        _, ls = o.process_column(raw[:, j], code, kind)
+        # (a column with one valid call has stddev 0/0 = NaN under the sample policies, in the reference too)
+        assert close(meta["mean"][j], ls.mean, rtol=1e-13, atol=0) and close(meta["stddev"][j], ls.stddev, rtol=1e-12, atol=1e-300), j
+        if ls.is_monomorphic:
+            mono.append(j)
+    assert meta["monomorphic_indices"].tolist() == mono == st["monomorphic_indices"].tolist()
+    assert np.array_equal(meta["mean"], st["mean"], equal_nan=True) and np.array_equal(meta["stddev"], st["stddev"], equal_nan=True)
+    # GenotypeLoader: the same matrix in memory, bit for bit, whatever the chunking
+    mat, st2 = engine.genotype_load(golden_dir / "tiny", method=method, additive=additive, chunk_size=5)
+    assert mat.shape == (n, m) and np.array_equal(np.nan_to_num(mat, nan=-9.0), np.nan_to_num(z, nan=-9.0))
+    assert np.array_equal(st2["mean"], st["mean"], equal_nan=True) and st2["monomorphic_indices"].tolist() == mono
+
+
+@pytest.mark.gpu
+def test_genotype_export_larger_dense_with_monomorphic_snps(tmp_path):
+    import oracle_lib as o
+    from test_oracle_golden import close
+
+    n, m = 1003, 700
+    bed = g.synth_bed_host(n, 0, m, 23, 0.02).copy()
+    bed[[10, 400, 699]] = 0xFF                # code 11 everywhere: genotype 0 for every sample -> monomorphic
+    bed[[10, 400, 699], -1] = 0x3F            # padding bits of the tail byte stay 0 (n % 4 == 3)
+    plink_io.write_plink(tmp_path / "d", bed, [("F", f"s{i:05d}") for i in range(n)], ["1"] * m)
+    st = engine.genotype_export(tmp_path / "d", tmp_path / "d_out", method="OSH", additive=True, chunk_size=256)
+    assert st["monomorphic_indices"].tolist() == [10, 400, 699]
+    z = np.fromfile(tmp_path / "d_out.bmat", dtype=np.float64).reshape(m, n).T
+    zr, fr = o.process_matrix(o.decode_chunk(bed, n), 3, 0)
+    assert np.array_equal(st["freq"], fr) and close(z, zr, rtol=1e-12, atol=1e-13)
+    meta = engine.read_snp_stats(tmp_path / "d_out.snpstats")
+    assert meta["monomorphic_indices"].tolist() == [10, 400, 699] and meta["num_samples"] == n and meta["num_variants"] == m
+    assert np.all(z[:, 10] == 0.0)            # centred, not scaled (genotype_processor.h:49-52)

@@ -159,6 +159,9 @@ def test_process_vectors_match_reference(golden_dir):
         assert st.maf == v["maf"], v
         assert close(z, ref), v
         assert st.is_monomorphic == v["mono"], v
+        # LocusStatistic moments (what GenotypeLoader / GenotypePipe keep per SNP)
+        assert st.mean == v["mean"] or abs(st.mean - v["mean"]) <= 1e-15 * abs(v["mean"]), v
+        assert st.stddev == v["stddev"] or abs(st.stddev - v["stddev"]) <= 4e-16 * abs(v["stddev"]) + 1e-300, v
 
 
 @pytest.mark.parametrize("tag,method,kind,chunk", [("SH.add", 1, 0, 25), ("OSH.add", 3, 0, 10000), ("OSH.dom", 3, 1, 10000),
