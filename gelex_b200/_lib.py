@@ -58,7 +58,7 @@ class Config(C.Structure):
         ("keep_whole", C.c_int32), ("keep_stats", C.c_int32), ("all_missing_policy", C.c_int32),
         ("tile_rank", C.c_int32), ("tile_world", C.c_int32),
         ("chunk_snps", C.c_int64),
-        ("max_resident_groups", C.c_int32), ("reserved", C.c_int32),
+        ("max_resident_groups", C.c_int32), ("second_matrix", C.c_int32),
     ]
 
 
@@ -69,7 +69,7 @@ EXPORTS = [
     "ggrm_synth_bed_host", "ggrm_synth_bed_device", "ggrm_device_count", "ggrm_version", "ggrm_enable_peer_access",
     "ggrm_ipc_export", "ggrm_ipc_open", "ggrm_ipc_close", "ggrm_row_slice",
     "ggrm_fetch_block", "ggrm_owned_supertiles", "ggrm_host_alloc", "ggrm_host_free", "ggrm_bin_to_dense", "ggrm_assoc_chunk",
-    "ggrm_band_layout", "ggrm_set_band_flags", "ggrm_reduce_rows_async", "ggrm_genotype_chunk",
+    "ggrm_band_layout", "ggrm_set_band_flags", "ggrm_reduce_rows_async", "ggrm_genotype_chunk", "ggrm_fetch_gcta",
 ]
 
 _lib = None
@@ -119,6 +119,7 @@ def load() -> C.CDLL:
     lib.ggrm_decode_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, vp]
     lib.ggrm_standardise_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, C.c_int, C.c_int, C.c_int, vp, vp]
     lib.ggrm_assoc_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, C.c_int, C.c_int, vp, vp]
+    lib.ggrm_fetch_gcta.argtypes = [vp, C.c_int, C.c_int, i64, i64, vp]
     lib.ggrm_genotype_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp]
     lib.ggrm_synth_bed_host.argtypes = [vp, i64, i64, i64, u64, dbl]
     lib.ggrm_synth_bed_device.argtypes = [C.c_int, vp, i64, i64, i64, u64, dbl]
@@ -142,7 +143,7 @@ class Accumulator:
 
     def __init__(self, n_raw, m_total, method=3, want_add=True, want_dom=False, precision=PREC_BF16, raw_to_out=None,
                  n_out=None, groups=None, keep_whole=True, keep_stats=False, all_missing_policy=ALLMISS_REFERENCE_NAN,
-                 device=0, chunk_snps=0, tile_rank=0, tile_world=1, max_resident_groups=0):
+                 device=0, chunk_snps=0, tile_rank=0, tile_world=1, max_resident_groups=0, second_matrix=0):
         self.lib = load()
         self.n_raw = int(n_raw)
         self.n_out = int(n_out if n_out is not None else n_raw)
@@ -174,6 +175,7 @@ class Accumulator:
         cfg.tile_rank, cfg.tile_world = tile_rank, tile_world
         cfg.chunk_snps = chunk_snps
         cfg.max_resident_groups = max_resident_groups
+        cfg.second_matrix = second_matrix  # 1: the dom slot holds the non-missing pair counts (GCTA .grm.N.bin)
         self.precision = precision
         h = C.c_void_p()
         st = self.lib.ggrm_create(C.byref(cfg), C.byref(h))
@@ -293,6 +295,14 @@ class Accumulator:
         b, e = C.c_int64(), C.c_int64()
         self._check(self.lib.ggrm_row_slice(self.h, row_begin, row_end, C.byref(b), C.byref(e)))
         return b.value, e.value
+
+    def fetch_gcta(self, which, group=GROUP_WHOLE, row_begin=0, row_count=None):
+        """which = 0: A = G_add / N (GCTA .grm.bin values); 1: N (.grm.N.bin).  Needs second_matrix=1, want_add and want_dom."""
+        if row_count is None:
+            row_count = self.n_out - row_begin
+        out = np.empty(tri(row_begin + row_count) - tri(row_begin), dtype=np.float32)
+        self._check(self.lib.ggrm_fetch_gcta(self.h, which, group, row_begin, row_count, _ptr(out)))
+        return out
 
     def fetch_block(self, kind, group, row_begin, row_count, col_begin, col_count):
         out = np.empty((row_count, col_count), dtype=np.float32)

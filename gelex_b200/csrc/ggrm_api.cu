@@ -237,6 +237,10 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
     if (cfg->tile_world < 1 || cfg->tile_rank < 0 || cfg->tile_rank >= cfg->tile_world)
         throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "invalid tile partition"};
     if (cfg->n_out > (int64_t{1} << 30)) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "n_out too large"};
+    if (cfg->second_matrix != GGRM_SECOND_DOMINANCE && cfg->second_matrix != GGRM_SECOND_NONMISSING)
+        throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "invalid second_matrix"};
+    if (cfg->second_matrix == GGRM_SECOND_NONMISSING && cfg->precision != GGRM_PREC_FP64 && cfg->m_total >= (int64_t{1} << 24))
+        throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "non-missing pair counts are exact in FP32 only below 2^24 SNPs: use the FP64 precision"};
 
     h->cfg = *cfg;
     h->cfg.raw_to_out = nullptr;

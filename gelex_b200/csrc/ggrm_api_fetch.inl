@@ -68,6 +68,7 @@ static double full_trace(Handle& h, const TAcc* A) {
 }
 
 // mode 0: raw accumulator   mode 1: G/(trace/n)   mode 2: (G_whole - G_group)/(k_whole - k_group)
+// mode 3: G_add / N entrywise, N = the non-missing-pair counts in the second accumulator (GCTA .grm.bin values; kind must be add)
 template <typename TAcc, typename TOut>
 static void fetch_typed(Handle& h, int kind, int group, int64_t row_begin, int64_t row_count, TOut* out, double* trace_out, int mode) {
     if (row_begin < 0 || row_count < 0 || row_begin + row_count > h.n_out)
@@ -80,7 +81,13 @@ static void fetch_typed(Handle& h, int kind, int group, int64_t row_begin, int64
     if (ev != nullptr && !banded) GGRM_CUDA(cudaStreamWaitEvent(h.s_fetch, ev, 0));
     int band_waited = -1;
     const TAcc* B = nullptr;
+    const TAcc* D = nullptr;
     double scale = 1.0;
+    if (mode == 3) {
+        cudaEvent_t evn = nullptr;
+        D = static_cast<const TAcc*>(resolve_accum(h, GGRM_KIND_DOM, group, &evn));
+        if (evn != nullptr) GGRM_CUDA(cudaStreamWaitEvent(h.s_fetch, evn, 0));
+    }
     if (mode == 1) {
         const double tr = full_trace<TAcc>(h, A);
         scale = static_cast<double>(h.n_out) / tr;
@@ -127,7 +134,7 @@ static void fetch_typed(Handle& h, int kind, int group, int64_t row_begin, int64
             cnt = lo;
         }
         const int64_t elems = tri(r + cnt) - tri(r);
-        pack_rows_kernel<TAcc, TOut><<<static_cast<unsigned>(cnt), 256, 0, h.s_fetch>>>(A, B, h.d_slot_of, r, cnt, scale, static_cast<TOut*>(h.d_stage), h.d_trace);
+        pack_rows_kernel<TAcc, TOut><<<static_cast<unsigned>(cnt), 256, 0, h.s_fetch>>>(A, B, D, h.d_slot_of, r, cnt, scale, static_cast<TOut*>(h.d_stage), h.d_trace);
         GGRM_CUDA(cudaGetLastError());
         ++h.kernel_launches;
         GGRM_CUDA(cudaMemcpyAsync(out + written, h.d_stage, static_cast<size_t>(elems) * sizeof(TOut), cudaMemcpyDeviceToHost, h.s_fetch));
@@ -216,6 +223,17 @@ extern "C" int ggrm_fetch_loco(ggrm_t* hh, int kind, int group, int64_t row_begi
     GGRM_API_BEGIN(h)
     if (h->groups.size() < 2) throw CudaError{GGRM_ERR_INVALID_OPERATION, "LOCO read-out needs n_groups > 1 and keep_whole"};
     fetch_dispatch<double>(*h, kind, group, row_begin, row_count, out_lower_rows, nullptr, 2);
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_fetch_gcta(ggrm_t* hh, int which, int group, int64_t row_begin, int64_t row_count, float* out_lower_rows) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    if (h->cfg.second_matrix != GGRM_SECOND_NONMISSING || !h->cfg.want_add || !h->cfg.want_dom)
+        throw CudaError{GGRM_ERR_INVALID_OPERATION, "GCTA read-out needs want_add, want_dom and second_matrix = GGRM_SECOND_NONMISSING"};
+    if (which != 0 && which != 1) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "which must be 0 (A = G/N) or 1 (N)"};
+    if (which == 0) fetch_dispatch<float>(*h, GGRM_KIND_ADD, group, row_begin, row_count, out_lower_rows, nullptr, 3);
+    else fetch_dispatch<float>(*h, GGRM_KIND_DOM, group, row_begin, row_count, out_lower_rows, nullptr, 0);
     GGRM_API_END(h)
 }
 

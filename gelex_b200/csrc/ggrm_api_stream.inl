@@ -234,6 +234,7 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
     StatsOut so{};
     so.counts = h.d_counts;
     so.freq = h.d_freq;
+    so.second_nonmissing = h.cfg.second_matrix == GGRM_SECOND_NONMISSING ? 1 : 0;
     for (int kind = 0; kind < 2; ++kind) {
         so.tab16[kind] = h.d_tab16[kind];
         so.tab64[kind] = h.d_tab64[kind];

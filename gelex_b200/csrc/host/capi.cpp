@@ -241,3 +241,32 @@ extern "C" int gelex_b200_genotype_load(const char* bfile, int method, int addit
         return translate_exception(err, err_len);
     }
 }
+
+// GrmEngine with Config::gcta: <out>.grm.bin (A = G / N), <out>.grm.N.bin, <out>.grm.id.  Additive, whole genome; SNP shards when n_gpus > 1.
+extern "C" int gelex_b200_grm_run_gcta(const char* bfile, const char* out_prefix, int method, int chunk_size, int precision, int n_gpus,
+                                       int writer_threads, char* err, int err_len) {
+    try {
+        if (bfile == nullptr || out_prefix == nullptr) throw ArgumentValidationException("null argument");
+        if (method < 1 || method > 8) throw InvalidInputException("Invalid genotype process method.");
+        GrmEngine::Config cfg;
+        cfg.bed_path = format_bed_path(bfile);
+        cfg.mode = GrmType::A;
+        cfg.method = static_cast<GenotypeProcessMethod>(method);
+        cfg.out_prefix = out_prefix;
+        cfg.chunk_size = chunk_size;
+        cfg.precision = precision;
+        cfg.partition = Partition::SnpShard;
+        cfg.writer_threads = writer_threads;
+        cfg.gcta = true;
+        cfg.gpus.clear();
+        const char* over = std::getenv("GELEX_B200_OVERSUBSCRIBE");  // test aid, see gelex_b200_grm_run_ex
+        const int devs = ggrm_device_count();
+        for (int i = 0; i < (n_gpus > 0 ? n_gpus : 1); ++i) cfg.gpus.push_back(over != nullptr && over[0] == '1' && devs > 0 ? i % devs : i);
+        GrmEngine engine(cfg);
+        engine.compute();
+        set_err(err, err_len, "");
+        return 0;
+    } catch (...) {
+        return translate_exception(err, err_len);
+    }
+}

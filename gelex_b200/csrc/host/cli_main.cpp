@@ -1,7 +1,7 @@
 // `gelex-b200 grm ...` — drop-in for `gelex grm` (apps/cli/grm/grm_args.cpp:31-62): identical flags and defaults, the
 // same [Config] / [Dataset Summary] / progress / [File Summary] report (apps/cli/grm/grm_reporter.cpp:30-94), messages also
 // written to <out>.log, exit code 0 / 1 (apps/main.cpp:54-98).  Opt-in additions: --gpus, --precision, --with-whole,
-// --skip-all-missing.
+// --skip-all-missing, --partition, --writer-threads, --gcta.
 #include <unistd.h>
 
 #include <chrono>
@@ -37,7 +37,7 @@ const char* kUsage =
     "Usage: gelex-b200 grm [--help] --bfile <BFILE> [--out <OUT>] [--geno-method <STR>] [--chunk-size <SIZE>]\n"
     "                      [--threads <N>] [--add] [--dom] [--loco] [--gpus <N>] [--precision <fp16|bf16|fp64>]\n"
     "                      [--partition <auto|snp|tile>] [--writer-threads <N>]\n"
-    "                      [--with-whole] [--skip-all-missing]\n\n"
+    "                      [--with-whole] [--skip-all-missing] [--gcta]\n\n"
     "Compute genomic relationship matrix (GRM) from PLINK binary files and output in GCTA format\n\n"
     "Data Files:\n"
     "  -b, --bfile <BFILE>        PLINK binary file prefix (.bed/.bim/.fam) [required]\n"
@@ -56,7 +56,8 @@ const char* kUsage =
     "  --partition <auto|snp|tile> Multi-GPU split: SNP shards + one reduce-scatter, or 2D output tiles (auto: tile from 100k samples)\n"
     "  --writer-threads <N>       pwrite threads per GPU draining the read-out ring [default: 4]\n"
     "  --with-whole               With --loco also write the whole-genome matrix (sum of the partials, same pass)\n"
-    "  --skip-all-missing         Treat an all-missing SNP as contributing 0 (the reference lets it poison the GRM with NaN)\n";
+    "  --skip-all-missing         Treat an all-missing SNP as contributing 0 (the reference lets it poison the GRM with NaN)\n"
+    "  --gcta                     GCTA binary format: <out>.grm.bin (G_ij / N_ij), <out>.grm.N.bin, <out>.grm.id (with --add, no --loco)\n";
 
 std::string mode_name(GrmType m) { return m == GrmType::A ? "A" : (m == GrmType::D ? "D" : "AD"); }
 
@@ -64,7 +65,7 @@ int run_grm(int argc, char** argv, Logger& log) {
     std::string bfile, out = "grm", gm = "OSH", precision = "fp16", partition = "auto";
     int chunk = 10000, gpus = 1, writer_threads = 4;
     int threads = static_cast<int>(std::thread::hardware_concurrency() / 2);
-    bool add = false, dom = false, loco = false, with_whole = false, skip_missing = false;
+    bool add = false, dom = false, loco = false, with_whole = false, skip_missing = false, gcta = false;
     auto need = [&](int& i) -> std::string {
         if (i + 1 >= argc) throw ArgumentValidationException(std::string("Too few arguments for '") + argv[i] + "'.");
         return argv[++i];
@@ -96,6 +97,7 @@ int run_grm(int argc, char** argv, Logger& log) {
         else if (a == "--writer-threads") writer_threads = to_int(need(i), "--writer-threads");
         else if (a == "--with-whole") with_whole = true;
         else if (a == "--skip-all-missing") skip_missing = true;
+        else if (a == "--gcta") gcta = true;
         else throw ArgumentValidationException("Unknown argument: " + a);
     }
     (void)threads;
@@ -124,6 +126,7 @@ int run_grm(int argc, char** argv, Logger& log) {
     cfg.writer_threads = writer_threads;
     cfg.write_whole = with_whole;
     cfg.skip_all_missing = skip_missing;
+    cfg.gcta = gcta;
 
     log.info("gelex-b200 | GRM Computation (B200 tcgen05 engine)");
     log.info("");

@@ -173,7 +173,7 @@ class WriterPool {
 inline int64_t tri(int64_t i) { return i * (i + 1) / 2; }
 
 // Rows [r0, r1) of matrix (kind, group) -> their byte range of the file, in blocks of whole rows.
-void write_packed_rows(ggrm_t* h, int kind, int group, int64_t r0, int64_t r1, const BinFile& file, WriterPool& pool) {
+void write_packed_rows(ggrm_t* h, int kind, int group, int64_t r0, int64_t r1, const BinFile& file, WriterPool& pool, bool gcta = false) {
     int64_t r = r0;
     while (r < r1) {
         int64_t cnt = 1;
@@ -186,7 +186,8 @@ void write_packed_rows(ggrm_t* h, int kind, int group, int64_t r0, int64_t r1, c
             cnt = lo;
         }
         float* buf = pool.acquire();
-        const int st = ggrm_fetch(h, kind, group, r, cnt, buf, nullptr);
+        // gcta: kind 0 -> A = G / N, kind 1 -> N (ggrm_fetch_gcta's `which` is the kind index)
+        const int st = gcta ? ggrm_fetch_gcta(h, kind, group, r, cnt, buf) : ggrm_fetch(h, kind, group, r, cnt, buf, nullptr);
         if (st != GGRM_OK) {
             pool.submit(file, buf, {});
             throw_status(st, ggrm_last_error(h));
@@ -314,6 +315,7 @@ struct RunContext {
     std::vector<ChrRun> groups;  // one pseudo-group [0, m) when not LOCO
     bool loco;
     bool want_add, want_dom;
+    bool gcta;  // kind 1 is the non-missing pair count matrix; outputs are <out>.grm.bin / .grm.N.bin / .grm.id
     // progress (reference: per work item, counted in SNPs; grm.h:124-130)
     const GrmObserver* observer;
     std::mutex* mu;
@@ -352,6 +354,7 @@ ggrm_t* create_handle(const RunContext& rc, int device, const std::vector<int>& 
     c.all_missing_policy = rc.cfg->skip_all_missing ? GGRM_ALLMISS_SKIP : GGRM_ALLMISS_REFERENCE_NAN;
     c.tile_rank = tile_rank;
     c.tile_world = tile_world;
+    c.second_matrix = rc.gcta ? GGRM_SECOND_NONMISSING : GGRM_SECOND_DOMINANCE;
     ggrm_t* h = nullptr;
     const int st = ggrm_create(&c, &h);
     if (st != GGRM_OK) throw_status(st, ggrm_last_error(nullptr));
@@ -380,13 +383,16 @@ void push_range(const RunContext& rc, ggrm_t* h, int64_t begin, int64_t end, int
 }
 
 std::string output_base(const RunContext& rc, int kind, const std::string& suffix) {
+    if (rc.gcta) return rc.cfg->out_prefix + (kind == 0 ? ".grm" : ".grm.N");
     return rc.cfg->out_prefix + "." + (kind == 0 ? "add" : "dom") + suffix;
 }
 
-void register_files(const RunContext& rc, const std::string& base) {
+bool has_id_file(const RunContext& rc, int kind) { return !(rc.gcta && kind == 1); }  // GCTA: one .grm.id beside both .bin files
+
+void register_files(const RunContext& rc, const std::string& base, bool with_id = true) {
     std::lock_guard<std::mutex> lk(*rc.mu);
     rc.files->push_back(base + ".bin");
-    rc.files->push_back(base + ".id");
+    if (with_id) rc.files->push_back(base + ".id");
 }
 
 // Main-thread step of the multi-writer modes: size every .bin, write every .id, before any GPU thread opens them.
@@ -398,8 +404,8 @@ void precreate_outputs(const RunContext& rc, const std::vector<std::string>& suf
             BinFile f;
             f.open(base + ".bin", rc.n_out, true);
             f.close_checked();
-            write_id_file(base + ".id", rc.order->ids);
-            register_files(rc, base);
+            if (has_id_file(rc, kind)) write_id_file(base + ".id", rc.order->ids);
+            register_files(rc, base, has_id_file(rc, kind));
         }
 }
 
@@ -413,8 +419,8 @@ void write_outputs(const RunContext& rc, ggrm_t* h, int local_group, const std::
         f.open(base + ".bin", rc.n_out, part.create);
         try {
             switch (part.kind) {
-                case WritePart::AllRows: write_packed_rows(h, kind, local_group, 0, rc.n_out, f, pool); break;
-                case WritePart::RowSlice: write_packed_rows(h, kind, local_group, part.r0, part.r1, f, pool); break;
+                case WritePart::AllRows: write_packed_rows(h, kind, local_group, 0, rc.n_out, f, pool, rc.gcta); break;
+                case WritePart::RowSlice: write_packed_rows(h, kind, local_group, part.r0, part.r1, f, pool, rc.gcta); break;
                 case WritePart::OwnedTiles: write_owned_supertiles(h, kind, local_group, rc.n_out, f, pool); break;
             }
         } catch (...) {
@@ -424,8 +430,8 @@ void write_outputs(const RunContext& rc, ggrm_t* h, int local_group, const std::
         pool.drain();
         f.close_checked();
         if (part.create) {
-            write_id_file(base + ".id", rc.order->ids);
-            register_files(rc, base);
+            if (has_id_file(rc, kind)) write_id_file(base + ".id", rc.order->ids);
+            register_files(rc, base, has_id_file(rc, kind));
         }
     }
     std::lock_guard<std::mutex> lk(*rc.mu);
@@ -672,6 +678,8 @@ void GrmEngine::compute(const GrmObserver& observer) {
     summary_ = Summary{};
     if (config_.chunk_size <= 0) throw ArgumentValidationException("chunk_size must be positive");
     if (config_.gpus.empty()) throw ArgumentValidationException("at least one GPU is required (there is no CPU fallback)");
+    if (config_.gcta && (config_.mode != GrmType::A || config_.do_loco))
+        throw ArgumentValidationException("--gcta writes the additive matrix of the whole genome: use --add without --dom / --loco");
     fs::path fam = config_.bed_path, bim = config_.bed_path;
     fam.replace_extension(".fam");
     bim.replace_extension(".bim");
@@ -707,8 +715,9 @@ void GrmEngine::compute(const GrmObserver& observer) {
     rc.bpv = bpv;
     rc.loco = config_.do_loco;
     rc.groups = config_.do_loco ? chromosome_runs(chroms) : std::vector<ChrRun>{{"", 0, static_cast<int64_t>(chroms.size())}};
+    rc.gcta = config_.gcta;
     rc.want_add = config_.mode != GrmType::D;
-    rc.want_dom = config_.mode != GrmType::A;
+    rc.want_dom = config_.mode != GrmType::A || config_.gcta;
     rc.observer = &observer;
     rc.mu = &mu;
     rc.files = &files;
@@ -727,13 +736,14 @@ void GrmEngine::compute(const GrmObserver& observer) {
     } else {
         // SNP shards (+ one reduce) while the FP32 triangle fits comfortably per GPU, 2D output tiles from n >= 100 000
         const bool tile_mode = config_.partition == Partition::Tile || (config_.partition == Partition::Auto && rc.n_out >= 100000);
+        if (tile_mode && config_.gcta) throw ArgumentValidationException("--gcta is not available with the 2D-tile partition");
         run_multi_gpu(rc, tile_mode, &pass_ms, &syrk_ms);
     }
 
     if (observer) {
         observer(GrmProgressEvent{total_work, total_work, true});
         observer(GrmFilesWrittenEvent{items.size() * 2, fs::absolute(fs::path(config_.out_prefix)).parent_path().string(),
-                                      config_.out_prefix + pattern_suffix});
+                                      config_.out_prefix + (config_.gcta ? std::string(".grm.{bin|N.bin|id}") : pattern_suffix)});
     }
     summary_.num_samples = order.ids.size();
     summary_.num_snps = static_cast<size_t>(m);

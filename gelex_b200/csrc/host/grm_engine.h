@@ -67,6 +67,9 @@ class GrmEngine {
         bool skip_all_missing = false;   // GGRM_ALLMISS_SKIP instead of the reference's NaN poisoning
         Partition partition = Partition::Auto;
         int writer_threads = 4;          // pwrite threads per GPU draining the page-locked read-out ring
+        // GCTA binary format behind a flag (docs/source/data_formats.rst:188-208): instead of <out>.add.{bin,id} write
+        // <out>.grm.bin (A_ij = G_ij / N_ij), <out>.grm.N.bin (N_ij = SNPs called in both samples) and <out>.grm.id.  Mode A, no LOCO.
+        bool gcta = false;
     };
 
     explicit GrmEngine(Config config);
@@ -104,3 +107,6 @@ extern "C" int gelex_b200_grm_run_ex(const char* bfile, const char* out_prefix, 
                                      int precision, int n_gpus, int write_whole, int partition, int writer_threads, char* err, int err_len);
 extern "C" int gelex_b200_grm_run(const char* bfile, const char* out_prefix, int method, int mode, int do_loco, int chunk_size,
                                   int precision, int n_gpus, int write_whole, char* err, int err_len);
+// Config::gcta run (GCTA binary format out); see capi.cpp.
+extern "C" int gelex_b200_grm_run_gcta(const char* bfile, const char* out_prefix, int method, int chunk_size, int precision, int n_gpus,
+                                       int writer_threads, char* err, int err_len);

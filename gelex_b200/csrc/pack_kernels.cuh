@@ -30,6 +30,7 @@ __device__ __forceinline__ int64_t tile_elem_offset<double>(int r, int c) {
 
 template <typename TAcc, typename TOut>
 __global__ void __launch_bounds__(256) pack_rows_kernel(const TAcc* __restrict__ A, const TAcc* __restrict__ B,
+                                                        const TAcc* __restrict__ D,  // entrywise divisor (GCTA N matrix) or nullptr
                                                         const int32_t* __restrict__ slot_of, int64_t row_begin,
                                                         int64_t row_count, double scale, TOut* __restrict__ out,
                                                         double* __restrict__ trace) {
@@ -47,6 +48,10 @@ __global__ void __launch_bounds__(256) pack_rows_kernel(const TAcc* __restrict__
             v = static_cast<double>(A[off]);
             if (B != nullptr) v -= static_cast<double>(B[off]);
             v *= scale;
+            if (D != nullptr) {
+                const double d = static_cast<double>(D[off]);
+                v = d > 0.0 ? __ddiv_rn(v, d) : 0.0;
+            }
         }
         out[base + j] = static_cast<TOut>(v);
         if (j == i && trace != nullptr) atomicAdd(trace, v);

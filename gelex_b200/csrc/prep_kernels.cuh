@@ -182,6 +182,7 @@ struct StatsOut {
     uint2* tab16[2];    // [kind]; nullptr when that kind / precision is not wanted
     SnpTable* tab64[2];
     SnpMoments* moments[2];  // [kind]; only the genotype-export hook asks for them (with tab64 of the same kind)
+    int second_nonmissing;   // kind 1 = the 0/1 non-missing indicator instead of the dominance policy (GGRM_SECOND_NONMISSING)
 };
 
 __global__ void __launch_bounds__(256) count_stats_kernel(const uint8_t* __restrict__ dense, int64_t bpv_pad,
@@ -225,7 +226,13 @@ __global__ void __launch_bounds__(256) count_stats_kernel(const uint8_t* __restr
             if (out.tab16[kind] == nullptr && out.tab64[kind] == nullptr) continue;
             SnpTable t;
             SnpMoments mo;
-            compute_snp_table(method, kind, n0, n1, n2, nmiss, all_missing_policy, &freq, &t, &mo);
+            if (kind == GGRM_KIND_DOM && out.second_nonmissing) {
+                compute_snp_table(method, GGRM_KIND_ADD, n0, n1, n2, nmiss, all_missing_policy, &freq, &t, &mo);  // frequency only
+                t.z[0] = t.z[2] = t.z[3] = 1.0;  // called genotype (BED 00 / 10 / 11)
+                t.z[1] = 0.0;                    // BED 01 = missing (padding rows are encoded as missing too)
+            } else {
+                compute_snp_table(method, kind, n0, n1, n2, nmiss, all_missing_policy, &freq, &t, &mo);
+            }
             if (out.moments[kind] != nullptr) out.moments[kind][snp] = mo;
             if (out.tab64[kind] != nullptr) out.tab64[kind][snp] = t;
             if (out.tab16[kind] != nullptr) {

@@ -61,6 +61,10 @@ enum { GGRM_GROUP_WHOLE = -1 };
 /* What an all-missing SNP contributes.  The reference leaves the column NaN
  * (include/gelex/internal/genotype_processor/genotype_processor.h:38-42) and dsyrk then poisons the whole GRM. */
 enum { GGRM_ALLMISS_REFERENCE_NAN = 0, GGRM_ALLMISS_SKIP = 1 };
+/* What the second accumulator (the `want_dom` slot, kind 1) holds: the dominance matrix of `method`, or the number of SNPs
+ * non-missing in BOTH samples, N = M M^T with M = the 0/1 non-missing indicator (exact: integers < 2^24 in FP32) - the
+ * `.grm.N.bin` matrix of the GCTA format. */
+enum { GGRM_SECOND_DOMINANCE = 0, GGRM_SECOND_NONMISSING = 1 };
 
 typedef struct ggrm_handle ggrm_t;
 
@@ -86,7 +90,7 @@ typedef struct ggrm_config {
     int32_t tile_world;        /* 1 = own all tiles (single GPU or SNP-shard mode) */
     int64_t chunk_snps;        /* device K-chunk (SNPs expanded to 16-bit operands at once); 0 = auto */
     int32_t max_resident_groups; /* accumulator pool size per kind; 0 = as many as fit / n_groups */
-    int32_t reserved;
+    int32_t second_matrix;     /* GGRM_SECOND_*; 0 in every reference-compatible run */
 } ggrm_config_t;
 
 /* Create / destroy.  Fails with GGRM_ERR_NO_DEVICE when no sm_100 GPU is present (no CPU fallback). */
@@ -134,6 +138,13 @@ int ggrm_snp_stats(ggrm_t* h, int64_t snp_begin, int64_t snp_count, int32_t* n0,
  * this handle does not own are returned as 0 so per-rank results can be summed or written at their own offsets. */
 int ggrm_fetch(ggrm_t* h, int kind, int group, int64_t row_begin, int64_t row_count, float* out_lower_rows,
                double* trace_out);
+/* GCTA-format read-out (docs/source/data_formats.rst:188-208 names the format, the reference writes only its own
+ * .bin): needs want_add, want_dom and second_matrix = GGRM_SECOND_NONMISSING.  which = 0: rows of A_ij = G_ij / N_ij (0 where
+ * N_ij = 0), G the additive matrix of `method` (StandardizeHWE gives GCTA's sum of (x_i - 2p)(x_j - 2p) / 2pq over the SNPs
+ * called in both samples; the diagonal uses the same sum, not GCTA's inbreeding-based variant); which = 1: rows of N_ij.
+ * Same row-major packed lower-triangle float32 layout as ggrm_fetch = the byte order of .grm.bin / .grm.N.bin. */
+int ggrm_fetch_gcta(ggrm_t* h, int which, int group, int64_t row_begin, int64_t row_count, float* out_lower_rows);
+
 /* 2D-tile mode read-out: the dense block rows [row_begin, +row_count) x columns [col_begin, +col_count) of the lower
  * triangle as float32 into `out` (host, caller-owned, row-major with leading dimension `ld` >= col_count elements).
  * Entries above the diagonal, and entries of tiles this handle does not own, are written as 0.  The writer calls it once

@@ -564,3 +564,40 @@ def test_c2_snp_count_tolerance_16bit_device_resident():
         # raw (un-normalised) entries: the FP32 TMEM accumulation truncates, a uniform relative bias that grows with the slab
         # length (-8.6e-5 at the default 16 384-SNP slabs) and cancels in G/(trace/n)
         assert abs(tr / tr_ref - 1.0) < 1.5e-4, (prec, tr / tr_ref - 1.0)
+
+
+def test_gcta_ratio_and_pair_counts():
+    # the second accumulator holds N_ij = SNPs called in both samples (exact integers), ggrm_fetch_gcta returns
+    # A_ij = G_ij / N_ij and N in the .grm.bin / .grm.N.bin byte order
+    n, m = 515, 900
+    geno = plink_io.decode_payload(g.synth_bed_host(n, 0, m, 31, 0.08), n)   # (n, m) 0/1/2/NaN
+    geno[0, : m // 2] = np.nan      # samples 0 and 1 share no called SNP: N_10 = 0 -> A_10 = 0
+    geno[1, m // 2:] = np.nan
+    bed = plink_io.encode_matrix(geno)
+    called = (~np.isnan(geno)).astype(np.float64)
+    N = (called @ called.T)[np.tril_indices(n)]
+    G, _, _ = o.grm_compute(bed, n, 1, 0, chunk=256)
+    A = np.divide(G[np.tril_indices(n)], N, out=np.zeros_like(N), where=N > 0)
+    assert N[1] == 0.0                                                       # packed index of (1, 0)
+    for prec, tol in ((g.PREC_FP64, None), (g.PREC_FP16, 2e-3), (g.PREC_BF16, 8e-3)):
+        with g.Accumulator(n, m, method="SH", want_add=True, want_dom=True, precision=prec, chunk_snps=256, second_matrix=1) as acc:
+            for s in range(0, m, 333):
+                acc.push(bed[s:s + 333], s)
+            acc.finish()
+            got_n = acc.fetch_gcta(1)
+            got_a = acc.fetch_gcta(0)
+            part = acc.fetch_gcta(0, row_begin=200, row_count=57)
+        assert np.array_equal(got_n.astype(np.float64), N), prec               # counts: bit-exact in every precision
+        assert got_a[1] == 0.0 and np.all(np.isfinite(got_a))
+        assert np.array_equal(part, got_a[g.tri(200):g.tri(257)])
+        if tol is None:
+            ref32 = A.astype(np.float32)
+            assert np.all(np.abs(got_a - ref32) <= np.spacing(np.abs(ref32)) + 1e-12)   # float32(G64 / N) to one ulp
+        else:
+            assert np.max(np.abs(got_a.astype(np.float64) - A)) <= tol, prec
+    with g.Accumulator(n, m, method="SH", want_add=True, want_dom=True, precision=g.PREC_FP64) as acc:
+        acc.push(bed, 0)
+        acc.finish()
+        with pytest.raises(g.GrmError) as e:
+            acc.fetch_gcta(0)
+        assert "second_matrix" in e.value.message

@@ -423,3 +423,48 @@ def test_genotype_export_larger_dense_with_monomorphic_snps(tmp_path):
     meta = engine.read_snp_stats(tmp_path / "d_out.snpstats")
     assert meta["monomorphic_indices"].tolist() == [10, 400, 699] and meta["num_samples"] == n and meta["num_variants"] == m
     assert np.all(z[:, 10] == 0.0)            # centred, not scaled (genotype_processor.h:49-52)
+
+
+# ------------------------------------------------------------------------------------------------ GCTA binary format behind a flag
+def test_gcta_flag_validation_needs_no_gpu(golden_dir, tmp_path):
+    r = subprocess.run([str(engine.CLI_PATH), "grm", "-b", str(golden_dir / "tiny"), "--add", "--dom", "--gcta", "-o", str(tmp_path / "x")],
+                       capture_output=True, text=True)
+    assert r.returncode == 1 and "--gcta writes the additive matrix of the whole genome" in (r.stdout + r.stderr)
+    r = subprocess.run([str(engine.CLI_PATH), "grm", "-b", str(golden_dir / "tiny"), "--loco", "--gcta", "-o", str(tmp_path / "x")],
+                       capture_output=True, text=True)
+    assert r.returncode == 1 and not list(tmp_path.glob("x.grm*"))
+
+
+@pytest.mark.gpu
+def test_engine_gcta_files(tmp_path, monkeypatch):
+    import oracle_lib as o
+
+    monkeypatch.setenv("GELEX_B200_OVERSUBSCRIBE", "1")
+    n, m = 2301, 1500   # two super-rows: the two-GPU run reduces and writes two row slices
+    rng = np.random.default_rng(3)
+    perm = rng.permutation(n)
+    fam = [(f"fam{i % 7}", f"s{perm[i]:05d}") for i in range(n)]
+    ids, r2o = plink_io.sample_order(fam)
+    bed = g.synth_bed_host(n, 0, m, 41, 0.05)
+    plink_io.write_plink(tmp_path / "d", bed, fam, ["1"] * m)
+    engine.grm_run_gcta(tmp_path / "d", tmp_path / "g1", method="SH", precision=g.PREC_FP64, chunk_size=400)
+    assert sorted(p.name for p in tmp_path.glob("g1.*")) == ["g1.grm.N.bin", "g1.grm.bin", "g1.grm.id"]
+    raw = o.decode_chunk(bed, n, len(ids), r2o)
+    called = (~np.isnan(raw)).astype(np.float64)
+    N = (called @ called.T)[np.tril_indices(n)]
+    G, _, _ = o.grm_compute(bed, n, 1, 0, chunk=500, n_out=len(ids), raw_to_out=r2o)
+    ref = (G[np.tril_indices(n)] / N).astype(np.float32)
+    got_n, got_a = plink_io.read_bin(tmp_path / "g1.grm.N.bin", n), plink_io.read_bin(tmp_path / "g1.grm.bin", n)
+    assert np.array_equal(got_n.astype(np.float64), N)
+    assert np.all(np.abs(got_a - ref) <= np.spacing(np.abs(ref)) + 1e-12)
+    assert (tmp_path / "g1.grm.id").read_text() == "".join(f"{i.split(chr(31))[0]}\t{i.split(chr(31))[1]}\n" for i in ids)
+    # two SNP shards: both matrices reduce-scattered over peer memory, each GPU divides and writes its own rows
+    engine.grm_run_gcta(tmp_path / "d", tmp_path / "g2", method="SH", precision=g.PREC_FP64, chunk_size=400, n_gpus=2)
+    assert (tmp_path / "g2.grm.N.bin").read_bytes() == (tmp_path / "g1.grm.N.bin").read_bytes()
+    assert_bin_close(tmp_path / "g2.grm.bin", tmp_path / "g1.grm.bin", n, ulps=2)
+    assert (tmp_path / "g2.grm.id").read_bytes() == (tmp_path / "g1.grm.id").read_bytes()
+    # 16-bit operands: counts still exact
+    engine.grm_run_gcta(tmp_path / "d", tmp_path / "g3", method="SH", precision=g.PREC_BF16)
+    assert (tmp_path / "g3.grm.N.bin").read_bytes() == (tmp_path / "g1.grm.N.bin").read_bytes()
+    a3 = plink_io.read_bin(tmp_path / "g3.grm.bin", n).astype(np.float64)
+    assert np.max(np.abs(a3 - ref)) <= 8e-3
