@@ -7,7 +7,6 @@ GGRM_ERR_NO_DEVICE and GrmError is raised.
 from __future__ import annotations
 
 import ctypes as C
-import os
 from pathlib import Path
 
 import numpy as np

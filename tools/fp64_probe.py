@@ -3,7 +3,6 @@ measured the same way" as MEASURED_PEAKS.json: torch.matmul, 2*N^3 flops, best o
 import json
 import os
 import sys
-import time
 
 import torch
 
