@@ -167,6 +167,58 @@ void build_ownership_and_items(Handle& h) {
     }
 }
 
+// ---- device allocations, optionally between guard bands (Handle::guard) ----------------------------------------------------
+constexpr size_t kGuardBytes = size_t{64} << 10;
+
+static void dev_alloc(Handle& h, void** p, size_t bytes, const char* name) {
+    bytes = std::max<size_t>(bytes, 1);
+    if (!h.guard) {
+        GGRM_CUDA(cudaMalloc(p, bytes));
+        return;
+    }
+    const size_t tail = kGuardBytes + (256 - bytes % 256) % 256;  // the back band starts at the first byte past the buffer
+    char* base = nullptr;
+    GGRM_CUDA(cudaMalloc(&base, kGuardBytes + bytes + tail));
+    GGRM_CUDA(cudaMemset(base, 0xA5, kGuardBytes));
+    GGRM_CUDA(cudaMemset(base + kGuardBytes + bytes, 0xA5, tail));
+    h.guards.push_back({base, bytes, tail, name});
+    *p = base + kGuardBytes;
+}
+template <typename T>
+static void dev_alloc(Handle& h, T** p, size_t bytes, const char* name) { dev_alloc(h, reinterpret_cast<void**>(p), bytes, name); }
+
+static void dev_free(Handle& h, void* p) {
+    if (p == nullptr) return;
+    for (auto& g : h.guards)
+        if (g.base + kGuardBytes == p) {
+            cudaFree(g.base);
+            g.base = nullptr;
+            return;
+        }
+    cudaFree(p);
+}
+
+// Called with the device idle.  Throws on the first band that no longer reads 0xA5 everywhere.
+static void check_guards(Handle& h) {
+    if (!h.guard) return;
+    std::vector<unsigned char> host;
+    for (const auto& g : h.guards) {
+        if (g.base == nullptr) continue;
+        for (int side = 0; side < 2; ++side) {
+            const size_t len = side == 0 ? kGuardBytes : g.tail;
+            const char* src = side == 0 ? g.base : g.base + kGuardBytes + g.bytes;
+            host.resize(len);
+            GGRM_CUDA(cudaMemcpy(host.data(), src, len, cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < len; ++i)
+                if (host[i] != 0xA5) {
+                    const long long off = side == 0 ? static_cast<long long>(i) - static_cast<long long>(kGuardBytes) : static_cast<long long>(g.bytes + i);
+                    throw CudaError{GGRM_ERR_CUDA, std::string("guard band of device buffer '") + g.name + "' (" + std::to_string(g.bytes) +
+                                                       " bytes) overwritten at byte offset " + std::to_string(off)};
+                }
+        }
+    }
+}
+
 static void check_device(int device, int* sm_count) {
     int count = 0;
     const cudaError_t e = cudaGetDeviceCount(&count);
@@ -190,7 +242,7 @@ static void free_handle(Handle* h) {
     if (h == nullptr) return;
     cudaSetDevice(h->cfg.device);
     cudaDeviceSynchronize();
-    auto fr = [](void* p) { if (p != nullptr) cudaFree(p); };
+    auto fr = [h](void* p) { dev_free(*h, p); };
     fr(h->d_slot_of); fr(h->d_items_tc); fr(h->d_items_f64); fr(h->d_out_to_raw);
     fr(h->d_raw[0]); fr(h->d_raw[1]); fr(h->d_dense); fr(h->d_counts); fr(h->d_freq);
     for (int k = 0; k < 2; ++k) {
@@ -243,6 +295,7 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
         throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "non-missing pair counts are exact in FP32 only below 2^24 SNPs: use the FP64 precision"};
 
     h->cfg = *cfg;
+    if (const char* e = std::getenv("GGRM_GUARD")) h->guard = std::atoi(e) != 0;
     h->cfg.raw_to_out = nullptr;
     h->cfg.group_begin = h->cfg.group_end = nullptr;
     check_device(cfg->device, &h->sm_count);
@@ -357,27 +410,27 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
         if (!(kind == 0 ? cfg->want_add : cfg->want_dom)) continue;
         for (int p = 0; p < pool_n; ++p) {
             void* buf = nullptr;
-            GGRM_CUDA(cudaMalloc(&buf, static_cast<size_t>(accum_bytes)));
+            dev_alloc(*h, &buf, static_cast<size_t>(accum_bytes), kind == 0 ? "accumulator (kind 0)" : "accumulator (kind 1)");
             h->pool[kind].push_back(buf);
             h->pool_owner[kind].push_back(-1);
         }
         if (want_whole) {
-            GGRM_CUDA(cudaMalloc(&h->whole[kind], static_cast<size_t>(accum_bytes)));
+            dev_alloc(*h, &h->whole[kind], static_cast<size_t>(accum_bytes), "whole-genome accumulator");
             GGRM_CUDA(cudaMemsetAsync(h->whole[kind], 0, static_cast<size_t>(accum_bytes), h->s_comp));
         }
-        for (int b = 0; b < h->n_zbuf; ++b) GGRM_CUDA(cudaMalloc(&h->d_Z[kind][b], static_cast<size_t>(h->n_pad * k_cap * z_elem)));
+        for (int b = 0; b < h->n_zbuf; ++b) dev_alloc(*h, &h->d_Z[kind][b], static_cast<size_t>(h->n_pad * k_cap * z_elem), "operand slab Z");
         if (h->fp64) {
-            GGRM_CUDA(cudaMalloc(&h->d_tab64[kind], static_cast<size_t>(k_cap) * sizeof(SnpTable)));
+            dev_alloc(*h, &h->d_tab64[kind], static_cast<size_t>(k_cap) * sizeof(SnpTable), "value tables (f64)");
         } else {
-            GGRM_CUDA(cudaMalloc(&h->d_tab16[kind], static_cast<size_t>(k_cap) * sizeof(uint2)));
+            dev_alloc(*h, &h->d_tab16[kind], static_cast<size_t>(k_cap) * sizeof(uint2), "value tables (16-bit)");
             for (int b = 0; b < h->n_zbuf; ++b) encode_tensor_map(&h->tmap[kind][b], h->d_Z[kind][b], k_cap, h->n_pad, cfg->precision == GGRM_PREC_FP16);
         }
     }
-    for (int i = 0; i < 2; ++i) GGRM_CUDA(cudaMalloc(&h->d_raw[i], static_cast<size_t>(k_cap * h->bpv_raw)));
-    GGRM_CUDA(cudaMalloc(&h->d_dense, static_cast<size_t>(k_cap * h->bpv_pad)));
+    for (int i = 0; i < 2; ++i) dev_alloc(*h, &h->d_raw[i], static_cast<size_t>(k_cap * h->bpv_raw), "raw BED chunk");
+    dev_alloc(*h, &h->d_dense, static_cast<size_t>(k_cap * h->bpv_pad), "dense 2-bit chunk");
     if (cfg->keep_stats) {
-        GGRM_CUDA(cudaMalloc(&h->d_counts, static_cast<size_t>(cfg->m_total) * sizeof(int4)));
-        GGRM_CUDA(cudaMalloc(&h->d_freq, static_cast<size_t>(cfg->m_total) * sizeof(double)));
+        dev_alloc(*h, &h->d_counts, static_cast<size_t>(cfg->m_total) * sizeof(int4), "per-SNP counts");
+        dev_alloc(*h, &h->d_freq, static_cast<size_t>(cfg->m_total) * sizeof(double), "per-SNP frequencies");
         GGRM_CUDA(cudaMemsetAsync(h->d_counts, 0, static_cast<size_t>(cfg->m_total) * sizeof(int4), h->s_comp));
         GGRM_CUDA(cudaMemsetAsync(h->d_freq, 0, static_cast<size_t>(cfg->m_total) * sizeof(double), h->s_comp));
     }

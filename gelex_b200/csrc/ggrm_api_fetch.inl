@@ -104,7 +104,7 @@ static void fetch_typed(Handle& h, int kind, int group, int64_t row_begin, int64
     if (h.d_stage == nullptr) {
         const int64_t want = std::min<int64_t>(int64_t{256} << 20, std::max<int64_t>(tri(h.n_out) * 8, h.n_out * 8 + 1024));
         h.stage_bytes = std::max<int64_t>(want, h.n_out * 8);
-        GGRM_CUDA(cudaMalloc(&h.d_stage, static_cast<size_t>(h.stage_bytes)));
+        dev_alloc(h, &h.d_stage, static_cast<size_t>(h.stage_bytes), "read-out staging buffer");
     }
     const int64_t stage_elems = h.stage_bytes / static_cast<int64_t>(sizeof(TOut));
     const size_t tfetch = phase_begin(h, h.s_fetch, 4);
@@ -147,6 +147,10 @@ static void fetch_typed(Handle& h, int kind, int group, int64_t row_begin, int64
     GGRM_CUDA(cudaStreamSynchronize(h.s_fetch));
     if (trace_out != nullptr) *trace_out = tr;
     if (h.finished) collect_timers(h);
+    if (h.guard && h.finished) {  // debug mode only; skipped while a ggrm_finish_async tail is still running
+        if (cudaStreamQuery(h.s_comp) == cudaSuccess) check_guards(h);
+        else cudaGetLastError();
+    }
 }
 
 // Rectangular block of the lower triangle -> host buffer with leading dimension ld (elements).  Used by the 2D-tile
@@ -171,7 +175,7 @@ static void fetch_block_typed(Handle& h, int kind, int group, int64_t row_begin,
     if (h.d_stage == nullptr) {
         const int64_t want = std::min<int64_t>(int64_t{256} << 20, std::max<int64_t>(tri(h.n_out) * 8, h.n_out * 8 + 1024));
         h.stage_bytes = std::max<int64_t>(want, h.n_out * 8);
-        GGRM_CUDA(cudaMalloc(&h.d_stage, static_cast<size_t>(h.stage_bytes)));
+        dev_alloc(h, &h.d_stage, static_cast<size_t>(h.stage_bytes), "read-out staging buffer");
     }
     const int64_t rows_per_pass = std::max<int64_t>(1, h.stage_bytes / (col_count * static_cast<int64_t>(sizeof(float))));
     const size_t tfetch = phase_begin(h, h.s_fetch, 4);
@@ -351,6 +355,7 @@ extern "C" int ggrm_reduce_rows_async(ggrm_t* hh, int kind, int group, const voi
 extern "C" int ggrm_ipc_export(ggrm_t* hh, int kind, int group, void* handle64) {
     Handle* h = reinterpret_cast<Handle*>(hh);
     GGRM_API_BEGIN(h)
+    if (h->guard) throw CudaError{GGRM_ERR_INVALID_OPERATION, "GGRM_GUARD offsets device buffers inside their allocations: IPC export is not available"};
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ggrm.h documents a 64-byte handle");
     if (handle64 == nullptr) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "null handle buffer"};
     cudaEvent_t ev = nullptr;

@@ -407,6 +407,11 @@ static void finish_sync(Handle& h) {
         throw CudaError{GGRM_ERR_CUDA, std::string("CUDA: device fault during GRM accumulation: ") +
                                            cudaGetErrorString(e2 != cudaSuccess ? e2 : e1) + " (pipeline wait id " + std::to_string(where) + ")"};
     }
+    if (h.guard) {
+        const char* e = std::getenv("GGRM_GUARD_SELFTEST");  // proves the detector: one byte past the dense chunk buffer
+        if (e != nullptr && std::atoi(e) != 0) cudaMemset(reinterpret_cast<char*>(h.d_dense) + h.k_cap * h.bpv_pad, 0, 1);
+    }
+    check_guards(h);
     collect_timers(h);
     if (h.pass_open) {
         float ms = 0.f;

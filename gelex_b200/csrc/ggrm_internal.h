@@ -133,6 +133,12 @@ struct Handle {
     // fetch staging
     void* d_stage = nullptr;
     int64_t stage_bytes = 0;
+
+    // Debug aid (GGRM_GUARD=1): every device buffer the kernels write sits between two 64 KiB guard bands filled with 0xA5,
+    // verified at ggrm_finish - an out-of-bounds store next to a buffer becomes an error instead of silent corruption.
+    struct GuardRec { char* base; size_t bytes; size_t tail; const char* name; };
+    bool guard = false;
+    std::vector<GuardRec> guards;
     double* d_trace = nullptr;
     unsigned long long* d_wave_ctr = nullptr;  // SYRK wave pacing counter (monotonic; wave_base = value all earlier launches add up to)
     unsigned long long wave_base = 0;

@@ -601,3 +601,43 @@ def test_gcta_ratio_and_pair_counts():
         with pytest.raises(g.GrmError) as e:
             acc.fetch_gcta(0)
         assert "second_matrix" in e.value.message
+
+
+def test_guard_bands_stay_intact_over_ragged_shapes(monkeypatch):
+    # compute-sanitizer is not available on this pool, so the library carries its own bounds check: with GGRM_GUARD=1 every
+    # device buffer the kernels write sits between 64 KiB guard bands that ggrm_finish / ggrm_fetch verify.  Shapes are chosen
+    # so that every kernel works on ragged edges (n % 256, n % 4, m % 64, last slab shorter than the others, projection with
+    # dropped samples, LOCO groups with the fused fold, the band-major tail, the second matrix of the GCTA mode).
+    monkeypatch.setenv("GGRM_GUARD", "1")
+    monkeypatch.setenv("GGRM_BAND_MIN_TILES", "1")
+    rng = np.random.default_rng(9)
+    for n, m, chunk in ((257, 130, 64), (1001, 777, 200), (2307, 1000, 192), (515, 65, 0)):
+        bed = g.synth_bed_host(n, 0, m, 100 + n, 0.03)
+        r2o = rng.permutation(n).astype(np.int32)
+        r2o[::7] = -1
+        keep = r2o >= 0
+        r2o[keep] = np.argsort(np.argsort(r2o[keep])).astype(np.int32)
+        n_out = int(keep.sum())
+        cuts = sorted({0, m // 3, m // 3 + 1, (2 * m) // 3, m})
+        groups = [(cuts[i], cuts[i + 1]) for i in range(len(cuts) - 1)]
+        for prec in (g.PREC_BF16, g.PREC_FP16, g.PREC_FP64):
+            for kw in ({"want_dom": True}, {"groups": groups, "keep_whole": True}, {"want_dom": True, "second_matrix": 1},
+                       {"raw_to_out": r2o, "n_out": n_out, "keep_stats": True}):
+                with g.Accumulator(n, m, method="OSH", precision=prec, chunk_snps=chunk, **kw) as acc:
+                    for s in range(0, m, 97):
+                        acc.push(bed[s:s + 97], s)
+                    acc.finish_async()
+                    acc.fetch(g.KIND_ADD, g.GROUP_WHOLE, dtype=np.float64 if prec == g.PREC_FP64 else np.float32)
+                    acc.finish()                                  # verifies every guard band; raises GrmError on a stray store
+                    if kw.get("second_matrix"):
+                        acc.fetch_gcta(0)
+                    acc.reset()
+                    acc.push(bed, 0)
+                    acc.finish()
+    # the detector itself: a deliberate one-byte store past a buffer is reported
+    monkeypatch.setenv("GGRM_GUARD_SELFTEST", "1")
+    with g.Accumulator(300, 64, method="SH", precision=g.PREC_BF16) as acc:
+        acc.push(g.synth_bed_host(300, 0, 64, 1, 0.0), 0)
+        with pytest.raises(g.GrmError) as e:
+            acc.finish()
+        assert "guard band of device buffer 'dense 2-bit chunk'" in e.value.message and "overwritten at byte offset" in e.value.message
