@@ -68,7 +68,7 @@ EXPORTS = [
     "ggrm_synth_bed_host", "ggrm_synth_bed_device", "ggrm_device_count", "ggrm_version", "ggrm_enable_peer_access",
     "ggrm_ipc_export", "ggrm_ipc_open", "ggrm_ipc_close", "ggrm_row_slice",
     "ggrm_fetch_block", "ggrm_owned_supertiles", "ggrm_host_alloc", "ggrm_host_free", "ggrm_bin_to_dense", "ggrm_assoc_chunk",
-    "ggrm_band_layout", "ggrm_set_band_flags", "ggrm_reduce_rows_async", "ggrm_genotype_chunk", "ggrm_fetch_gcta",
+    "ggrm_band_layout", "ggrm_set_band_flags", "ggrm_reduce_rows_async", "ggrm_genotype_chunk", "ggrm_fetch_gcta", "ggrm_accum_address",
 ]
 
 _lib = None
@@ -118,6 +118,7 @@ def load() -> C.CDLL:
     lib.ggrm_decode_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, vp]
     lib.ggrm_standardise_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, C.c_int, C.c_int, C.c_int, vp, vp]
     lib.ggrm_assoc_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, C.c_int, C.c_int, vp, vp]
+    lib.ggrm_accum_address.argtypes = [vp, C.c_int, C.POINTER(vp)]
     lib.ggrm_fetch_gcta.argtypes = [vp, C.c_int, C.c_int, i64, i64, vp]
     lib.ggrm_genotype_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp]
     lib.ggrm_synth_bed_host.argtypes = [vp, i64, i64, i64, u64, dbl]
@@ -266,6 +267,11 @@ class Accumulator:
     def reduce_peer(self, kind, group, peer_ptrs, slice_begin, slice_end):
         arr = (C.c_void_p * max(1, len(peer_ptrs)))(*peer_ptrs)
         self._check(self.lib.ggrm_reduce_peer(self.h, kind, group, arr, len(peer_ptrs), slice_begin, slice_end))
+
+    def accum_address(self, kind=KIND_ADD):
+        p = C.c_void_p()
+        self._check(self.lib.ggrm_accum_address(self.h, kind, C.byref(p)))
+        return p.value
 
     def band_layout(self):
         """[(row_begin, row_end)] of the bands the final accumulation completes in (see ggrm_band_layout)."""

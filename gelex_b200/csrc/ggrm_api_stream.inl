@@ -514,6 +514,19 @@ extern "C" int ggrm_band_layout(ggrm_t* hh, int64_t* row_end, int capacity, int*
     GGRM_API_END(h)
 }
 
+extern "C" int ggrm_accum_address(ggrm_t* hh, int kind, void** d_ptr) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    if (kind != GGRM_KIND_ADD && kind != GGRM_KIND_DOM) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "kind must be 0 (add) or 1 (dom)"};
+    if (d_ptr == nullptr) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "null argument"};
+    if (h->groups.size() != 1) throw CudaError{GGRM_ERR_INVALID_OPERATION, "ggrm_accum_address is defined for handles with one group"};
+    if (h->pool[kind].empty()) throw CudaError{GGRM_ERR_INVALID_OPERATION, kind == 0 ? "additive matrix was not requested" : "dominance matrix was not requested"};
+    const int slot = h->groups[0].started ? h->groups[0].buffer[kind] : 0;  // start_group takes the first free slot: 0 on a fresh / reset handle
+    if (slot < 0) throw CudaError{GGRM_ERR_INVALID_OPERATION, "group accumulator was released"};
+    *d_ptr = h->pool[kind][static_cast<size_t>(slot)];
+    GGRM_API_END(h)
+}
+
 extern "C" int ggrm_finish_async(ggrm_t* hh) {
     Handle* h = reinterpret_cast<Handle*>(hh);
     GGRM_API_BEGIN(h)

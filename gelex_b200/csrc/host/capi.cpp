@@ -270,3 +270,15 @@ extern "C" int gelex_b200_grm_run_gcta(const char* bfile, const char* out_prefix
         return translate_exception(err, err_len);
     }
 }
+
+extern "C" int gelex_b200_strip_owners(int64_t n, int world, const int64_t* band_row_end, int n_bands, int64_t* out4, int cap) {
+    if (n <= 0 || world <= 0 || band_row_end == nullptr || n_bands <= 0 || out4 == nullptr) return -1;
+    const auto strips = GrmEngine::strip_owners_for(n, world, std::vector<int64_t>(band_row_end, band_row_end + n_bands));
+    for (size_t i = 0; i < strips.size() && static_cast<int>(i) < cap; ++i) {
+        out4[4 * i] = strips[i].rank;
+        out4[4 * i + 1] = strips[i].band;
+        out4[4 * i + 2] = strips[i].row_begin;
+        out4[4 * i + 3] = strips[i].row_end;
+    }
+    return static_cast<int>(strips.size());
+}

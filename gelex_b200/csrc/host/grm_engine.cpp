@@ -1,6 +1,7 @@
 #include "grm_engine.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cctype>
 #include <chrono>
 #include <cstdio>
@@ -485,17 +486,98 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
     }
 }
 
-// One GPU, one contiguous SNP shard of the whole-genome matrix (multi-GPU SNP-shard mode); the handle is kept for the reduce.
-void run_shard_on_device(const RunContext& rc, int device, int64_t begin, int64_t end, ggrm_t** keep_handle, double* pass_ms, double* syrk_ms) {
-    HandleGuard hg;
-    hg.h = create_handle(rc, device, {0}, false);
-    check(hg.h, ggrm_set_push_end(hg.h, end));  // equal slabs inside the shard
+// ---------------------------------------------------------------------------------------------------------------
+// SNP shards of the whole-genome matrix, band-pipelined (SURVEY 8e "fuse the reduce-scatter behind the last chunks' SYRK").
+// Every GPU accumulates its SNP range; the last slabs of a pass finish row band by row band (ggrm_finish_async) and a CUDA
+// host callback raises flags[rank][band] the moment a band is final on that GPU.  The 2 048-row strips of the matrix are dealt
+// to the GPUs by LPT on their triangle area; the owner of a strip waits for every rank's flag of the strip's band, sums the
+// peers' rows into its own over NVLink peer memory (ggrm_reduce_rows_async, read-out stream) and writes them - while all GPUs
+// are still accumulating the later bands.  No collective, no barrier inside the pass.
+struct Strip { int band; int64_t r0, r1; };
+
+// Same rule as gelex_b200/sharding.py::strip_owners (compared in tests/test_sharding.py).
+std::vector<std::vector<Strip>> strip_owners(int64_t n, int world, const std::vector<int64_t>& band_row_end) {
+    std::vector<Strip> strips;
+    for (int64_t lo = 0; lo < n; lo += kSuperRows) {
+        const int64_t hi = std::min(n, lo + kSuperRows);
+        int b = 0;
+        while (static_cast<size_t>(b) + 1 < band_row_end.size() && band_row_end[static_cast<size_t>(b)] < hi) ++b;
+        strips.push_back({b, lo, hi});
+    }
+    std::vector<size_t> order(strips.size());
+    std::iota(order.begin(), order.end(), size_t{0});
+    auto area = [&](size_t i) { return strips[i].r1 * (strips[i].r1 + 1) / 2 - strips[i].r0 * (strips[i].r0 + 1) / 2; };
+    std::stable_sort(order.begin(), order.end(), [&](size_t a, size_t b) { return area(a) > area(b); });
+    std::vector<int64_t> load(static_cast<size_t>(world), 0);
+    std::vector<int> owner(strips.size(), 0);
+    for (size_t i : order) {
+        const size_t r = static_cast<size_t>(std::min_element(load.begin(), load.end()) - load.begin());
+        owner[i] = static_cast<int>(r);
+        load[r] += area(i);
+    }
+    std::vector<std::vector<Strip>> out(static_cast<size_t>(world));
+    for (size_t i = 0; i < strips.size(); ++i) out[static_cast<size_t>(owner[i])].push_back(strips[i]);  // row order within a rank
+    return out;
+}
+
+struct ShardPipe {
+    std::vector<ggrm_t*> handles;                 // one per rank, created up front
+    std::vector<std::pair<int64_t, int64_t>> snps;  // SNP range of each rank
+    std::vector<std::vector<const void*>> accum;  // [kind][rank] device address of the accumulator
+    std::vector<std::vector<Strip>> mine;         // strips each rank reduces + writes
+    std::vector<int32_t> flags;                   // [rank][band], written by CUDA host callbacks
+    int n_bands = 1;
+    std::atomic<bool> failed{false};
+};
+
+void run_pipelined_rank(const RunContext& rc, ShardPipe& sp, size_t r, double* pass_ms, double* syrk_ms) {
+    ggrm_t* h = sp.handles[r];
+    const size_t ng = sp.handles.size();
+    const auto nb = static_cast<size_t>(sp.n_bands);
+    check(h, ggrm_set_band_flags(h, sp.flags.data() + r * nb, 1));
+    check(h, ggrm_set_push_end(h, sp.snps[r].second));  // equal slabs inside the shard
+    WriterPool pool(rc.cfg->writer_threads, rc.cfg->writer_threads + 2, std::max<int64_t>(kWriterBufferElems, rc.n_out));
+    BinFile files[2];
+    for (int kind = 0; kind < 2; ++kind)
+        if (kind == 0 ? rc.want_add : rc.want_dom) files[kind].open(output_base(rc, kind, "") + ".bin", rc.n_out, false);
     int64_t done = 0;
-    push_range(rc, hg.h, begin, end, end - begin, &done);
-    check(hg.h, ggrm_finish(hg.h));
-    note_timers(rc, hg.h, pass_ms, syrk_ms);
-    *keep_handle = hg.h;
-    hg.h = nullptr;
+    push_range(rc, h, sp.snps[r].first, sp.snps[r].second, sp.snps[r].second - sp.snps[r].first, &done);
+    check(h, ggrm_finish_async(h));
+    const auto t0 = Clock::now();
+    try {
+        for (const Strip& st : sp.mine[r]) {
+            const auto t_wait = Clock::now();
+            for (;;) {  // every rank's rows of this band are final
+                bool ready = true;
+                for (size_t p = 0; p < ng && ready; ++p)
+                    ready = __atomic_load_n(&sp.flags[p * nb + static_cast<size_t>(st.band)], __ATOMIC_ACQUIRE) == 1;
+                if (ready) break;
+                if (sp.failed.load()) throw GelexException("multi-GPU run aborted: another GPU failed");
+                if (since(t_wait) > 3600.0) throw GelexException("multi-GPU run: timed out waiting for a peer's row band");
+                std::this_thread::sleep_for(std::chrono::microseconds(20));
+            }
+            for (int kind = 0; kind < 2; ++kind) {
+                if (!(kind == 0 ? rc.want_add : rc.want_dom)) continue;
+                std::vector<const void*> peers;
+                for (size_t p = 0; p < ng; ++p)
+                    if (p != r) peers.push_back(sp.accum[static_cast<size_t>(kind)][p]);
+                for (size_t off = 0; off < peers.size(); off += 7)  // up to 7 peers per call
+                    check(h, ggrm_reduce_rows_async(h, kind, GGRM_GROUP_WHOLE, peers.data() + off, static_cast<int>(std::min<size_t>(7, peers.size() - off)),
+                                                    st.r0, st.r1));
+            }
+            for (int kind = 0; kind < 2; ++kind)  // after BOTH kinds are reduced: the GCTA ratio reads the two of them
+                if (kind == 0 ? rc.want_add : rc.want_dom) write_packed_rows(h, kind, GGRM_GROUP_WHOLE, st.r0, st.r1, files[kind], pool, rc.gcta);
+        }
+        check(h, ggrm_finish(h));  // accumulation + read-out stream drained, device faults surfaced
+    } catch (...) {
+        try { pool.drain(); } catch (...) {}
+        throw;
+    }
+    pool.drain();
+    for (auto& f : files) f.close_checked();
+    note_timers(rc, h, pass_ms, syrk_ms);
+    std::lock_guard<std::mutex> lk(*rc.mu);
+    *rc.write_s += since(t0);
 }
 
 // Rows cut on super-row (2048) boundaries into `parts` ranges of about equal lower-triangle area (the same rule as
@@ -597,6 +679,8 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
     // function scope: these outlive the worker threads (joined below), which read them by reference
     std::vector<std::vector<int>> mine(ng);
     std::vector<int> all;
+    ShardPipe pipe;
+    bool pipelined = false;
     if (tile_mode) {
         // 2D output tiles: every GPU streams ALL SNPs, owns disjoint 2048 x 2048 super-tiles of every matrix and writes them
         // straight to their file offsets.  No collective anywhere on the path.
@@ -643,21 +727,63 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
             });
         }
     } else {
+        // contiguous SNP ranges cut on multiples of 64; ranks whose range would be empty (tiny m) are left out
         for (size_t r = 0; r < ng; ++r) {
             const int64_t b = std::min<int64_t>(rc.m, (rc.m * static_cast<int64_t>(r) / static_cast<int64_t>(ng) + 63) / 64 * 64);
             const int64_t e = r + 1 == ng ? rc.m : std::min<int64_t>(rc.m, (rc.m * static_cast<int64_t>(r + 1) / static_cast<int64_t>(ng) + 63) / 64 * 64);
-            threads.emplace_back([&, r, b, e] {
+            if (e > b) pipe.snps.emplace_back(b, e);
+        }
+        const size_t world = pipe.snps.size();
+        pipe.handles.assign(world, nullptr);
+        for (size_t r = 0; r < world; ++r) {  // handles first (contexts, accumulators, rings), in parallel
+            threads.emplace_back([&, r] {
                 try {
-                    run_shard_on_device(rc, gpus[r], b, e, &handles[r], pass_ms, syrk_ms);
+                    pipe.handles[r] = create_handle(rc, gpus[r], {0}, false);
                 } catch (...) {
                     errors[r] = std::current_exception();
                 }
             });
         }
+        for (auto& t : threads) t.join();
+        threads.clear();
+        for (size_t r = 0; r < world; ++r) handles[r] = pipe.handles[r];  // owned by `cleanup` from here on
+        for (auto& e : errors) if (e) std::rethrow_exception(e);
+        for (size_t a = 0; a < world; ++a)
+            for (size_t b = 0; b < world; ++b)
+                if (a != b && gpus[a] != gpus[b]) {
+                    const int st = ggrm_enable_peer_access(gpus[a], gpus[b]);
+                    if (st != GGRM_OK) throw_status(st, ggrm_last_error(nullptr));
+                }
+        pipe.accum.assign(2, std::vector<const void*>(world, nullptr));
+        for (int kind = 0; kind < 2; ++kind) {
+            if (!(kind == 0 ? rc.want_add : rc.want_dom)) continue;
+            for (size_t r = 0; r < world; ++r) {
+                void* ptr = nullptr;
+                check(pipe.handles[r], ggrm_accum_address(pipe.handles[r], kind, &ptr));
+                pipe.accum[static_cast<size_t>(kind)][r] = ptr;
+            }
+        }
+        std::vector<int64_t> band_end(64, 0);
+        check(pipe.handles[0], ggrm_band_layout(pipe.handles[0], band_end.data(), 64, &pipe.n_bands));
+        band_end.resize(static_cast<size_t>(pipe.n_bands));
+        pipe.mine = strip_owners(rc.n_out, static_cast<int>(world), band_end);
+        pipe.flags.assign(world * static_cast<size_t>(pipe.n_bands), 0);
+        precreate_outputs(rc, {""});
+        for (size_t r = 0; r < world; ++r) {
+            threads.emplace_back([&, r] {
+                try {
+                    run_pipelined_rank(rc, pipe, r, pass_ms, syrk_ms);
+                } catch (...) {
+                    pipe.failed.store(true);
+                    errors[r] = std::current_exception();
+                }
+            });
+        }
+        pipelined = true;
     }
     for (auto& t : threads) t.join();
     for (auto& e : errors) if (e) std::rethrow_exception(e);
-    if (want_whole && !tile_mode) {
+    if (want_whole && !tile_mode && !pipelined) {
         std::vector<ggrm_t*> live;
         std::vector<int> devs;
         for (size_t r = 0; r < ng; ++r)
@@ -672,6 +798,14 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
 }  // namespace
 
 std::vector<std::pair<int64_t, int64_t>> GrmEngine::row_slices_for(int64_t n, int parts) { return row_slices(n, parts); }
+
+std::vector<GrmEngine::OwnedStrip> GrmEngine::strip_owners_for(int64_t n, int world, const std::vector<int64_t>& band_row_end) {
+    std::vector<OwnedStrip> out;
+    const auto per_rank = strip_owners(n, world, band_row_end);
+    for (size_t r = 0; r < per_rank.size(); ++r)
+        for (const Strip& st : per_rank[r]) out.push_back({static_cast<int>(r), st.band, st.r0, st.r1});
+    return out;
+}
 
 void GrmEngine::compute(const GrmObserver& observer) {
     const auto t_start = Clock::now();

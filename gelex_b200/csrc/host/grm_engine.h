@@ -89,6 +89,9 @@ class GrmEngine {
 
     // Row ranges the GPUs of an SNP-shard run reduce and write (cuts on 2 048-row super-rows, balanced on triangle area).
     static std::vector<std::pair<int64_t, int64_t>> row_slices_for(int64_t n, int parts);
+    // 2 048-row strips of the band-pipelined SNP-shard run, dealt by LPT: (rank, band, row range), rank-major, rows ascending.
+    struct OwnedStrip { int rank, band; int64_t row_begin, row_end; };
+    static std::vector<OwnedStrip> strip_owners_for(int64_t n, int world, const std::vector<int64_t>& band_row_end);
 
    private:
     Config config_;
@@ -110,3 +113,5 @@ extern "C" int gelex_b200_grm_run(const char* bfile, const char* out_prefix, int
 // Config::gcta run (GCTA binary format out); see capi.cpp.
 extern "C" int gelex_b200_grm_run_gcta(const char* bfile, const char* out_prefix, int method, int chunk_size, int precision, int n_gpus,
                                        int writer_threads, char* err, int err_len);
+// strip_owners_for through C (CPU tests): out4 receives (rank, band, row_begin, row_end) per strip, up to cap strips; returns the strip count.
+extern "C" int gelex_b200_strip_owners(int64_t n, int world, const int64_t* band_row_end, int n_bands, int64_t* out4, int cap);

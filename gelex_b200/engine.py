@@ -38,6 +38,7 @@ def load_host():
         h.gelex_b200_grm_load.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_char_p, C.c_int]
         h.gelex_b200_grm_load.restype = C.c_int64
         h.gelex_b200_row_slices.argtypes = [C.c_int64, C.c_int, C.c_void_p]
+        h.gelex_b200_strip_owners.argtypes = [C.c_int64, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
         h.gelex_b200_grm_run_gcta.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]
         vp = C.c_void_p
         h.gelex_b200_genotype_export.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, C.c_int64,
@@ -194,3 +195,20 @@ def grm_run_gcta(bfile, out_prefix, method="SH", chunk_size=10000, precision=_li
                                    int(writer_threads), err, len(err))
     if st != 0:
         raise EngineError(int(st), err.value.decode())
+
+
+def strip_owners(n, world, bands):
+    """The C++ engine's strip dealing for the band-pipelined SNP-shard run (same contract as sharding.strip_owners: per rank a list of
+    (band, row_begin, row_end)); `bands` = [(row_begin, row_end)] as ggrm_band_layout gives them."""
+    h = load_host()
+    ends = np.array([e for _, e in bands], dtype=np.int64)
+    cap = (int(n) + 2047) // 2048 + 1
+    out = np.zeros(4 * cap, dtype=np.int64)
+    cnt = h.gelex_b200_strip_owners(int(n), int(world), ends.ctypes.data_as(C.c_void_p), len(ends), out.ctypes.data_as(C.c_void_p), cap)
+    if cnt < 0 or cnt > cap:
+        raise EngineError(cnt, "strip_owners failed")
+    per = [[] for _ in range(world)]
+    for i in range(cnt):
+        r, b, lo, hi = (int(v) for v in out[4 * i:4 * i + 4])
+        per[r].append((b, lo, hi))
+    return per

@@ -181,6 +181,10 @@ int ggrm_reduce_peer(ggrm_t* h, int kind, int group, const void* const* peers, i
  * those rows - while every GPU is still accumulating the later bands.  `flags` must stay valid until the pass is finished
  * (ggrm_finish / ggrm_reset); NULL disables. */
 int ggrm_band_layout(ggrm_t* h, int64_t* row_end, int capacity, int* n_bands);
+/* Device address the accumulator of `kind` has for the whole pass on a handle with ONE group (SNP-shard mode), available
+ * before anything is pushed - so peers can be wired up ahead of a single pass (ggrm_accum_buffer answers only once the group
+ * is complete).  The contents are defined only after this handle's own band flags / ggrm_finish. */
+int ggrm_accum_address(ggrm_t* h, int kind, void** d_ptr);
 int ggrm_set_band_flags(ggrm_t* h, int32_t* flags, int32_t value);
 int ggrm_reduce_rows_async(ggrm_t* h, int kind, int group, const void* const* peers, int n_peers, int64_t row_begin,
                            int64_t row_end);

@@ -92,6 +92,20 @@ def test_cpp_engine_uses_the_same_row_slice_rule():
             assert engine.row_slices(n, w) == sharding.row_slices(n, w), (n, w)
 
 
+def test_cpp_engine_deals_strips_like_the_python_rule():
+    # the band-pipelined SNP-shard run of the C++ engine (host/grm_engine.cpp::strip_owners) and bench.py must agree on who owns what
+    from gelex_b200 import engine
+
+    for n in (1, 2048, 2049, 4500, 50000, 123457):
+        strips_total = (n + 2047) // 2048
+        for nb in (1, 2, 3, 8):
+            per = max(1, strips_total // nb)
+            ends = sorted({min(n, (i + 1) * per * 2048) for i in range(nb - 1)} | {n})
+            bands = [(0 if i == 0 else ends[i - 1], e) for i, e in enumerate(ends)]
+            for w in (1, 2, 3, 4, 8):
+                assert engine.strip_owners(n, w, bands) == sharding.strip_owners(n, w, bands), (n, nb, w)
+
+
 def test_strip_owners_cover_balance_and_spread_the_last_band():
     for n, nb in ((4500, 3), (50000, 8), (200000, 8)):
         strips_total = (n + 2047) // 2048
