@@ -17,6 +17,24 @@ static void set_err(char* err, int err_len, const std::string& m) {
     err[err_len - 1] = '\0';
 }
 
+// Current exception -> (status, "Type: message"); call inside a catch (...) block.
+static int translate_exception(char* err, int err_len) {
+    try {
+        throw;
+    } catch (const FileNotFoundException& e) { set_err(err, err_len, std::string("FileNotFoundException: ") + e.what()); return -10;
+    } catch (const FileOpenException& e) { set_err(err, err_len, std::string("FileOpenException: ") + e.what()); return -11;
+    } catch (const FileWriteException& e) { set_err(err, err_len, std::string("FileWriteException: ") + e.what()); return -12;
+    } catch (const FileExistsException& e) { set_err(err, err_len, std::string("FileExistsException: ") + e.what()); return -13;
+    } catch (const FileFormatException& e) { set_err(err, err_len, std::string("FileFormatException: ") + e.what()); return GGRM_ERR_FILE_FORMAT;
+    } catch (const ColumnRangeException& e) { set_err(err, err_len, std::string("ColumnRangeException: ") + e.what()); return GGRM_ERR_COLUMN_RANGE;
+    } catch (const ArgumentValidationException& e) { set_err(err, err_len, std::string("ArgumentValidationException: ") + e.what()); return GGRM_ERR_INVALID_ARGUMENT;
+    } catch (const InvalidInputException& e) { set_err(err, err_len, std::string("InvalidInputException: ") + e.what()); return GGRM_ERR_INVALID_ARGUMENT;
+    } catch (const InvalidOperationException& e) { set_err(err, err_len, std::string("InvalidOperationException: ") + e.what()); return GGRM_ERR_INVALID_OPERATION;
+    } catch (const GelexException& e) { set_err(err, err_len, std::string("GelexException: ") + e.what()); return GGRM_ERR_CUDA;
+    } catch (const std::bad_alloc&) { set_err(err, err_len, "std::bad_alloc"); return GGRM_ERR_OUT_OF_MEMORY;
+    } catch (const std::exception& e) { set_err(err, err_len, std::string("std::exception: ") + e.what()); return -99; }
+}
+
 extern "C" int gelex_b200_grm_run(const char* bfile, const char* out_prefix, int method, int mode, int do_loco, int chunk_size,
                                   int precision, int n_gpus, int write_whole, char* err, int err_len) {
     return gelex_b200_grm_run_ex(bfile, out_prefix, method, mode, do_loco, chunk_size, precision, n_gpus, write_whole, 0, 4, err, err_len);
@@ -50,17 +68,9 @@ extern "C" int gelex_b200_grm_run_ex(const char* bfile, const char* out_prefix, 
         engine.compute();
         set_err(err, err_len, "");
         return 0;
-    } catch (const FileNotFoundException& e) { set_err(err, err_len, std::string("FileNotFoundException: ") + e.what()); return -10;
-    } catch (const FileOpenException& e) { set_err(err, err_len, std::string("FileOpenException: ") + e.what()); return -11;
-    } catch (const FileFormatException& e) { set_err(err, err_len, std::string("FileFormatException: ") + e.what()); return GGRM_ERR_FILE_FORMAT;
-    } catch (const FileWriteException& e) { set_err(err, err_len, std::string("FileWriteException: ") + e.what()); return -12;
-    } catch (const ColumnRangeException& e) { set_err(err, err_len, std::string("ColumnRangeException: ") + e.what()); return GGRM_ERR_COLUMN_RANGE;
-    } catch (const ArgumentValidationException& e) { set_err(err, err_len, std::string("ArgumentValidationException: ") + e.what()); return GGRM_ERR_INVALID_ARGUMENT;
-    } catch (const InvalidInputException& e) { set_err(err, err_len, std::string("InvalidInputException: ") + e.what()); return GGRM_ERR_INVALID_ARGUMENT;
-    } catch (const InvalidOperationException& e) { set_err(err, err_len, std::string("InvalidOperationException: ") + e.what()); return GGRM_ERR_INVALID_OPERATION;
-    } catch (const GelexException& e) { set_err(err, err_len, std::string("GelexException: ") + e.what()); return GGRM_ERR_CUDA;
-    } catch (const std::bad_alloc&) { set_err(err, err_len, "std::bad_alloc"); return GGRM_ERR_OUT_OF_MEMORY;
-    } catch (const std::exception& e) { set_err(err, err_len, std::string("std::exception: ") + e.what()); return -99; }
+    } catch (...) {
+        return translate_exception(err, err_len);
+    }
 }
 
 // Metadata-only entry (no GPU needed): sample order, projection and chromosome runs as the engine will use them.
@@ -101,9 +111,8 @@ extern "C" int64_t gelex_b200_plan(const char* bfile, int mode, int do_loco, int
         if (n_items_out) *n_items_out = static_cast<int>(items.size());
         set_err(err, err_len, "");
         return static_cast<int64_t>(order.ids.size());
-    } catch (const std::exception& e) {
-        set_err(err, err_len, e.what());
-        return -1;
+    } catch (...) {
+        return translate_exception(err, err_len);  // "Type: message", status < 0
     }
 }
 
@@ -160,24 +169,6 @@ extern "C" int gelex_b200_row_slices(int64_t n, int parts, int64_t* begin_end) {
         begin_end[2 * r + 1] = sl[r].second;
     }
     return static_cast<int>(sl.size());
-}
-
-// Current exception -> (status, "Type: message"); call inside a catch (...) block.
-static int translate_exception(char* err, int err_len) {
-    try {
-        throw;
-    } catch (const FileNotFoundException& e) { set_err(err, err_len, std::string("FileNotFoundException: ") + e.what()); return -10;
-    } catch (const FileOpenException& e) { set_err(err, err_len, std::string("FileOpenException: ") + e.what()); return -11;
-    } catch (const FileWriteException& e) { set_err(err, err_len, std::string("FileWriteException: ") + e.what()); return -12;
-    } catch (const FileExistsException& e) { set_err(err, err_len, std::string("FileExistsException: ") + e.what()); return -13;
-    } catch (const FileFormatException& e) { set_err(err, err_len, std::string("FileFormatException: ") + e.what()); return GGRM_ERR_FILE_FORMAT;
-    } catch (const ColumnRangeException& e) { set_err(err, err_len, std::string("ColumnRangeException: ") + e.what()); return GGRM_ERR_COLUMN_RANGE;
-    } catch (const ArgumentValidationException& e) { set_err(err, err_len, std::string("ArgumentValidationException: ") + e.what()); return GGRM_ERR_INVALID_ARGUMENT;
-    } catch (const InvalidInputException& e) { set_err(err, err_len, std::string("InvalidInputException: ") + e.what()); return GGRM_ERR_INVALID_ARGUMENT;
-    } catch (const InvalidOperationException& e) { set_err(err, err_len, std::string("InvalidOperationException: ") + e.what()); return GGRM_ERR_INVALID_OPERATION;
-    } catch (const GelexException& e) { set_err(err, err_len, std::string("GelexException: ") + e.what()); return GGRM_ERR_CUDA;
-    } catch (const std::bad_alloc&) { set_err(err, err_len, "std::bad_alloc"); return GGRM_ERR_OUT_OF_MEMORY;
-    } catch (const std::exception& e) { set_err(err, err_len, std::string("std::exception: ") + e.what()); return -99; }
 }
 
 static void copy_stats(const GenotypeStats& st, int64_t* dims3, double* mean, double* stddev, double* freq, int64_t* mono, int64_t mono_cap) {

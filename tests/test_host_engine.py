@@ -46,6 +46,32 @@ def test_fam_delimiter_detection_and_errors(tmp_path):
     assert "file not found" in e.value.message  # bed_path.cpp:33-37
 
 
+def test_bim_and_fam_cases_of_the_reference_loader_tests(tmp_path):
+    # reference tests/test_bim_loader.cpp:110-152 (column count, non-numeric / empty position), :74-107 (space-delimited),
+    # tests/test_fam_loader.cpp:90-104 (missing IID), :139-165 (single line, space or tab delimited)
+    bed = bytes([0x6C, 0x1B, 0x01, 0])
+
+    def triple(name, fam, bim):
+        (tmp_path / f"{name}.fam").write_text(fam)
+        (tmp_path / f"{name}.bim").write_text(bim)
+        (tmp_path / f"{name}.bed").write_bytes(bed[:3] + bytes(max(1, bim.count("\n") + (0 if bim.endswith("\n") else 1))))
+        return tmp_path / name
+
+    for bim, msg in (("1\trs12345\t0\t1000\tA\tG\n1\trs67890\t0.001\t2000\tC", "2: has 5 columns, expected 6"),
+                     ("1\trs12345\t0\tinvalid\tA\tG", "failed to parse 'invalid' as number"),
+                     ("1\trs12345\t0\t\tA\tG", "has 5 columns, expected 6")):
+        with pytest.raises(engine.EngineError) as e:
+            engine.plan(triple("b", "1 sample1 0 0 1 2.5\n", bim))
+        assert e.value.message.startswith("FileFormatException") and e.value.message.endswith(msg), e.value.message
+    with pytest.raises(engine.EngineError) as e:
+        engine.plan(triple("f", "1\n2 sample2\n", "1\ts\t0\t1\tA\tG\n"))
+    assert e.value.message.startswith("FileFormatException") and e.value.message.endswith("failed to parse FID and IID (missing delimiter)")
+    for fam in ("1 sample1 0 0 1 2.5\n", "1\tsample1\t0\t0\t1\t2.5\n"):
+        p = engine.plan(triple("one", fam, "1 rs1 0 1000 A G\n1 rs2 0.001 2000 C T\n2 rs3 0.002 3000 T A\n"), loco=True)  # space-delimited BIM
+        assert p["n_raw"] == 1 and p["n_out"] == 1 and p["m"] == 3 and p["dense"]
+        assert p["items"] == [("add.chr1", 0, 2), ("add.chr2", 2, 3)]
+
+
 def test_bed_validation_errors_precede_any_gpu_work(tmp_path):
     # reference tests/test_bed_pipe.cpp:154-257: bad magic, truncated file -> FileFormatException
     payload = plink_io.encode_matrix(np.zeros((8, 5)))
