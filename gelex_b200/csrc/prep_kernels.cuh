@@ -34,10 +34,13 @@ __global__ void __launch_bounds__(256) repack_kernel(const uint8_t* __restrict__
     const uint8_t* src = raw + snp * bpv_raw;
     uint32_t* dst = reinterpret_cast<uint32_t*>(dense + snp * bpv_pad);
     const int64_t words = bpv_pad / 4;
+    const bool words_aligned = ((bpv_raw & 3) == 0) && ((reinterpret_cast<uintptr_t>(raw) & 3) == 0);
     for (int64_t w = threadIdx.x; w < words; w += blockDim.x) {
         uint32_t out = 0;
         const int64_t s0 = w * 16;
-        if (out_to_raw == nullptr) {
+        if (out_to_raw == nullptr && words_aligned && s0 + 16 <= n_out) {
+            out = __ldg(reinterpret_cast<const uint32_t*>(src) + w);  // identity projection, whole word of real samples
+        } else if (out_to_raw == nullptr) {
 #pragma unroll
             for (int b = 0; b < 4; ++b) {
                 const int64_t byte = w * 4 + b;
@@ -253,8 +256,8 @@ __global__ void __launch_bounds__(256) count_stats_kernel(const uint8_t* __restr
 // K3: expand to 16-bit operands.  dense [c][bpv_pad] + tab16[c] -> Z [n_pad][k_pad] (K-major: one GRM row = one
 // sample, SNPs contiguous), the layout the TMA/tcgen05 SYRK consumes.  Tile = 64 SNPs x 256 samples:
 //   load : 64 rows x 64 bytes, one 16-byte load per thread, transposed into smem as [byte][snp]
-//   emit : thread (sample, octet) reads 8 contiguous smem bytes (8 SNPs of one sample quad), looks the 8 values up in
-//          the per-SNP tables and writes one 16-byte store; 8 lanes cover one sample's 128 contiguous bytes.
+//   emit : thread (sample quad, octet) reads 8 contiguous smem bytes (8 SNPs of four samples), looks the 32 values up in
+//          the per-SNP tables with byte permutes and writes four 16-byte stores; 8 lanes cover one sample's 128 contiguous bytes.
 // SNPs in [snp_count, k_pad) are written as 0 so the SYRK can run whole 64-wide K blocks.
 __global__ void __launch_bounds__(256) expand16_kernel(const uint8_t* __restrict__ dense, int64_t bpv_pad,
                                                        const uint2* __restrict__ tab16, int64_t snp_count,
@@ -275,24 +278,42 @@ __global__ void __launch_bounds__(256) expand16_kernel(const uint8_t* __restrict
         if (tid < 64) s_tab[tid] = (k0 + tid < snp_count) ? __ldg(tab16 + k0 + tid) : make_uint2(0u, 0u);
     }
     __syncthreads();
+    // A SNP's table is 8 bytes {z(00), z(01) | z(10), z(11)}: one PRMT with selector nibbles (2c, 2c+1, 2c', 2c'+1) looks up the
+    // values of two samples' codes c, c' at once; a second PRMT pairs the values of two neighbouring SNPs of one sample.
     const int octet = tid & 7;
+    uint2 tab[8];
 #pragma unroll
-    for (int it = 0; it < 8; ++it) {
-        const int sample = it * 32 + (tid >> 3);  // 0..255 within the tile
-        const uint2 bytes = *reinterpret_cast<const uint2*>(&s_t[sample >> 2][octet * 8]);
-        const int shift = 2 * (sample & 3);
-        uint32_t o[4];
+    for (int u = 0; u < 8; ++u) tab[u] = s_tab[octet * 8 + u];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            const uint32_t byte = ((u < 4 ? bytes.x : bytes.y) >> (8 * (u & 3))) & 0xFFu;
-            const uint32_t code = (byte >> shift) & 3u;
-            const uint2 t = s_tab[octet * 8 + u];
-            const uint32_t pair = (code & 2u) ? t.y : t.x;
-            const uint32_t val = (code & 1u) ? (pair >> 16) : (pair & 0xFFFFu);
-            if (u & 1) o[u >> 1] |= val << 16; else o[u >> 1] = val;
+    for (int it = 0; it < 2; ++it) {
+        const int quad = it * 32 + (tid >> 3);  // byte column of the tile = samples 4*quad .. 4*quad + 3
+        const uint2 bytes = *reinterpret_cast<const uint2*>(&s_t[quad][octet * 8]);  // that quad's byte at 8 consecutive SNPs
+        uint32_t x01[8], x23[8];  // per SNP: {value of sample 0, sample 1}, {sample 2, sample 3}
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const uint32_t w = h == 0 ? bytes.x : bytes.y;
+            const uint32_t c0 = w & 0x03030303u, c1 = (w >> 2) & 0x03030303u, c2 = (w >> 4) & 0x03030303u, c3 = (w >> 6) & 0x03030303u;
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+                const uint32_t gather = static_cast<uint32_t>(v | ((4 + v) << 4));  // low 16 bits <- {byte v of a, byte v of b}
+                const uint32_t sel01 = __byte_perm(c0, c1, gather) * 0x22u + 0x1010u;  // PRMT reads the low 16 bits only
+                const uint32_t sel23 = __byte_perm(c2, c3, gather) * 0x22u + 0x1010u;
+                x01[h * 4 + v] = __byte_perm(tab[h * 4 + v].x, tab[h * 4 + v].y, sel01);
+                x23[h * 4 + v] = __byte_perm(tab[h * 4 + v].x, tab[h * 4 + v].y, sel23);
+            }
         }
-        const int64_t row = b0 * 4 + sample;
-        *reinterpret_cast<uint4*>(Z + row * k_pad + k0 + octet * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+        uint32_t o[4][4];
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            o[0][p] = __byte_perm(x01[2 * p], x01[2 * p + 1], 0x5410u);
+            o[1][p] = __byte_perm(x01[2 * p], x01[2 * p + 1], 0x7632u);
+            o[2][p] = __byte_perm(x23[2 * p], x23[2 * p + 1], 0x5410u);
+            o[3][p] = __byte_perm(x23[2 * p], x23[2 * p + 1], 0x7632u);
+        }
+        const int64_t row = (b0 + quad) * 4;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            *reinterpret_cast<uint4*>(Z + (row + j) * k_pad + k0 + octet * 8) = make_uint4(o[j][0], o[j][1], o[j][2], o[j][3]);
     }
 }
 
