@@ -1,7 +1,7 @@
 // `gelex-b200 grm ...` — drop-in for `gelex grm` (apps/cli/grm/grm_args.cpp:31-62): identical flags and defaults, the
 // same [Config] / [Dataset Summary] / progress / [File Summary] report (apps/cli/grm/grm_reporter.cpp:30-94), messages also
 // written to <out>.log, exit code 0 / 1 (apps/main.cpp:54-98).  Opt-in additions: --gpus, --precision, --with-whole,
-// --skip-all-missing, --partition, --writer-threads, --gcta.
+// --skip-all-missing, --partition, --writer-threads, --writer, --gcta.
 #include <unistd.h>
 
 #include <chrono>
@@ -36,7 +36,7 @@ struct Logger {
 const char* kUsage =
     "Usage: gelex-b200 grm [--help] --bfile <BFILE> [--out <OUT>] [--geno-method <STR>] [--chunk-size <SIZE>]\n"
     "                      [--threads <N>] [--add] [--dom] [--loco] [--gpus <N>] [--precision <fp16|bf16|fp64>]\n"
-    "                      [--partition <auto|snp|tile>] [--writer-threads <N>]\n"
+    "                      [--partition <auto|snp|tile>] [--writer-threads <N>] [--writer <auto|pwrite|mmap>]\n"
     "                      [--with-whole] [--skip-all-missing] [--gcta]\n\n"
     "Compute genomic relationship matrix (GRM) from PLINK binary files and output in GCTA format\n\n"
     "Data Files:\n"
@@ -54,7 +54,9 @@ const char* kUsage =
     "  --gpus <N>                 Number of GPUs of this node to use [default: 1]\n"
     "  --precision <P>            fp16 (default) | bf16 : 16-bit operands, FP32 accumulate on tcgen05; fp64 : DMMA\n"
     "  --partition <auto|snp|tile> Multi-GPU split: SNP shards + one reduce-scatter, or 2D output tiles (auto: tile from 100k samples)\n"
-    "  --writer-threads <N>       pwrite threads per GPU draining the read-out ring [default: 4]\n"
+    "  --writer-threads <N>       writer threads per GPU draining the read-out ring [default: 4]\n"
+    "  --writer <auto|pwrite|mmap> How blocks reach the .bin: pwrite, or memcpy into a shared mapping of the pre-sized file\n"
+    "                             (auto: mapping for scattered tile rows and on tmpfs, when the file system has room) [default: auto]\n"
     "  --with-whole               With --loco also write the whole-genome matrix (sum of the partials, same pass)\n"
     "  --skip-all-missing         Treat an all-missing SNP as contributing 0 (the reference lets it poison the GRM with NaN)\n"
     "  --gcta                     GCTA binary format: <out>.grm.bin (G_ij / N_ij), <out>.grm.N.bin, <out>.grm.id (with --add, no --loco)\n";
@@ -62,7 +64,7 @@ const char* kUsage =
 std::string mode_name(GrmType m) { return m == GrmType::A ? "A" : (m == GrmType::D ? "D" : "AD"); }
 
 int run_grm(int argc, char** argv, Logger& log) {
-    std::string bfile, out = "grm", gm = "OSH", precision = "fp16", partition = "auto";
+    std::string bfile, out = "grm", gm = "OSH", precision = "fp16", partition = "auto", writer = "auto";
     int chunk = 10000, gpus = 1, writer_threads = 4;
     int threads = static_cast<int>(std::thread::hardware_concurrency() / 2);
     bool add = false, dom = false, loco = false, with_whole = false, skip_missing = false, gcta = false;
@@ -95,6 +97,7 @@ int run_grm(int argc, char** argv, Logger& log) {
         else if (a == "--precision") precision = need(i);
         else if (a == "--partition") partition = need(i);
         else if (a == "--writer-threads") writer_threads = to_int(need(i), "--writer-threads");
+        else if (a == "--writer") writer = need(i);
         else if (a == "--with-whole") with_whole = true;
         else if (a == "--skip-all-missing") skip_missing = true;
         else if (a == "--gcta") gcta = true;
@@ -124,6 +127,10 @@ int run_grm(int argc, char** argv, Logger& log) {
     else throw ArgumentValidationException("--partition must be auto, snp or tile");
     if (writer_threads < 1) throw ArgumentValidationException("--writer-threads must be >= 1");
     cfg.writer_threads = writer_threads;
+    if (writer == "auto") cfg.writer = WriterMode::Auto;
+    else if (writer == "pwrite") cfg.writer = WriterMode::Pwrite;
+    else if (writer == "mmap") cfg.writer = WriterMode::Mmap;
+    else throw ArgumentValidationException("--writer must be auto, pwrite or mmap");
     cfg.write_whole = with_whole;
     cfg.skip_all_missing = skip_missing;
     cfg.gcta = gcta;

@@ -16,6 +16,9 @@
 #include <deque>
 
 #include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/statvfs.h>
+#include <sys/vfs.h>
 #include <unistd.h>
 
 #include "exceptions.h"
@@ -46,22 +49,54 @@ struct HandleGuard {
 // ggrm_fetch_block into a ring of page-locked buffers) and a small pool of threads pwrite()s each block at its file
 // offset while the next block is already crossing PCIe.  Several GPUs (row slices, or 2D tiles) write disjoint byte
 // ranges of the same pre-sized file concurrently.
+// Two ways to put a block at its offset (Config::writer / GELEX_B200_WRITER):
+//   pwrite  one system call per segment; buffered writes to ONE inode serialise on the inode lock, so several writer threads
+//           (and, in the multi-GPU modes, several GPUs' pools) queue behind each other, and the 8 KiB row segments of a 2D-tile
+//           run pay a system call each (80 GB at n = 200 000 = 10 M calls)
+//   mmap    the pre-sized file is mapped MAP_SHARED and segments are memcpy()d into the mapping: no system call, no inode lock,
+//           first-touch page faults run in parallel.  Measured on tmpfs with 4-8 threads: 3.1-3.8 GB/s against 1.3-2.0 GB/s
+//           (profiles/r01_summary.md, writer microbenchmark).  A store into a mapped hole of a FULL file system raises SIGBUS
+//           instead of returning ENOSPC, so a run only maps its outputs when the file system had room for ALL of them at the
+//           start (RunContext::allow_map); otherwise every write goes through pwrite and fails the reference's way.
+// Auto = mmap for segments below kMapSegmentBytes (scattered tile rows) and for every segment on tmpfs, pwrite otherwise.
+constexpr int64_t kMapSegmentBytes = int64_t{256} << 10;
+
 struct BinFile {
     int fd = -1;
     std::string path;
+    char* map = nullptr;       // whole file, MAP_SHARED (nullptr: pwrite only)
+    size_t map_bytes = 0;
+    bool map_all = false;      // every segment goes through the mapping (tmpfs, or WriterMode::Mmap)
     BinFile() = default;
     BinFile(const BinFile&) = delete;
     BinFile& operator=(const BinFile&) = delete;
-    ~BinFile() { if (fd >= 0) ::close(fd); }
+    ~BinFile() {
+        if (map != nullptr) ::munmap(map, map_bytes);
+        if (fd >= 0) ::close(fd);
+    }
     // create = truncate + size the file (one caller); otherwise open an existing, already sized file for writing
-    void open(const fs::path& p, int64_t n, bool create) {
+    void open(const fs::path& p, int64_t n, bool create, WriterMode mode = WriterMode::Pwrite) {
         path = p.string();
-        fd = ::open(path.c_str(), create ? (O_WRONLY | O_CREAT | O_TRUNC) : O_WRONLY, 0644);
+        fd = ::open(path.c_str(), create ? (O_RDWR | O_CREAT | O_TRUNC) : O_RDWR, 0644);
         if (fd < 0) throw FileOpenException(path + ": failed to open file");
-        if (create && ::ftruncate(fd, static_cast<off_t>(n * (n + 1) / 2 * static_cast<int64_t>(sizeof(float)))) != 0)
+        const int64_t bytes = n * (n + 1) / 2 * static_cast<int64_t>(sizeof(float));
+        if (create && ::ftruncate(fd, static_cast<off_t>(bytes)) != 0)
             throw FileWriteException(path + ": failed to write GRM data to binary file");
+        if (mode == WriterMode::Pwrite || bytes == 0) return;
+        void* m = ::mmap(nullptr, static_cast<size_t>(bytes), PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+        if (m == MAP_FAILED) return;  // e.g. a file system without mmap: pwrite still works
+        map = static_cast<char*>(m);
+        map_bytes = static_cast<size_t>(bytes);
+        struct statfs sf {};
+        const bool tmpfs = ::fstatfs(fd, &sf) == 0 && static_cast<unsigned long>(sf.f_type) == 0x01021994ul;  // TMPFS_MAGIC
+        map_all = mode == WriterMode::Mmap || tmpfs;
     }
     void close_checked() {
+        if (map != nullptr) {
+            const int rc = ::munmap(map, map_bytes);
+            map = nullptr;
+            if (rc != 0) throw FileWriteException(path + ": failed to write GRM data to binary file");
+        }
         if (fd >= 0 && ::close(fd) != 0) {
             fd = -1;
             throw FileWriteException(path + ": failed to write GRM data to binary file");
@@ -69,6 +104,15 @@ struct BinFile {
         fd = -1;
     }
 };
+
+// Room for `bytes` more (plus a margin) on the file system that will hold `path`?  Decides once per run whether outputs may be mapped.
+bool file_system_has_room(const fs::path& path, int64_t bytes) {
+    fs::path dir = fs::absolute(path).parent_path();
+    struct statvfs sv {};
+    if (::statvfs(dir.c_str(), &sv) != 0) return false;
+    const double avail = static_cast<double>(sv.f_bavail) * static_cast<double>(sv.f_frsize);
+    return avail >= static_cast<double>(bytes) * 1.02 + static_cast<double>(int64_t{256} << 20);
+}
 
 struct Segment { int64_t src_elem, file_byte, bytes; };  // buffer elements [src_elem, +bytes/4) -> file bytes [file_byte, +bytes)
 
@@ -108,7 +152,7 @@ class WriterPool {
     void submit(const BinFile& file, float* buf, std::vector<Segment> segs) {
         {
             std::lock_guard<std::mutex> lk(mu_);
-            jobs_.push_back({file.fd, &file.path, buf, std::move(segs)});
+            jobs_.push_back({file.fd, &file.path, buf, std::move(segs), file.map, file.map_all});
             ++inflight_;
         }
         cv_job_.notify_one();
@@ -121,7 +165,7 @@ class WriterPool {
     double busy_s() const { return busy_s_; }
 
    private:
-    struct Job { int fd; const std::string* path; float* buf; std::vector<Segment> segs; };
+    struct Job { int fd; const std::string* path; float* buf; std::vector<Segment> segs; char* map; bool map_all; };
     void run() {
         for (;;) {
             Job job;
@@ -136,6 +180,10 @@ class WriterPool {
             bool ok = true;
             for (const Segment& sg : job.segs) {
                 const char* src = reinterpret_cast<const char*>(job.buf + sg.src_elem);
+                if (job.map != nullptr && (job.map_all || sg.bytes < kMapSegmentBytes)) {
+                    std::memcpy(job.map + sg.file_byte, src, static_cast<size_t>(sg.bytes));
+                    continue;
+                }
                 int64_t done = 0;
                 while (ok && done < sg.bytes) {
                     const ssize_t w = ::pwrite(job.fd, src + done, static_cast<size_t>(sg.bytes - done), static_cast<off_t>(sg.file_byte + done));
@@ -173,19 +221,34 @@ class WriterPool {
 
 inline int64_t tri(int64_t i) { return i * (i + 1) / 2; }
 
+// Largest count of whole rows starting at r (not past r1) whose packed entries fit `cap` elements; a single row always fits
+// (buffers hold >= n floats).
+int64_t rows_fitting(int64_t r, int64_t r1, int64_t cap) {
+    int64_t lo = 1, hi = r1 - r;
+    while (lo < hi) {
+        const int64_t mid = (lo + hi + 1) / 2;
+        if (tri(r + mid) - tri(r) <= cap) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+// Row segments of the rows x cols block at (row0, col0), held row-major with pitch `cols`, that lie in the lower triangle.
+std::vector<Segment> supertile_segments(int64_t row0, int64_t col0, int64_t rows, int64_t cols) {
+    std::vector<Segment> segs;
+    segs.reserve(static_cast<size_t>(rows));
+    for (int64_t i = 0; i < rows; ++i) {
+        const int64_t gi = row0 + i;
+        const int64_t len = std::min(cols, gi + 1 - col0);
+        if (len > 0) segs.push_back(Segment{i * cols, (tri(gi) + col0) * 4, len * 4});
+    }
+    return segs;
+}
+
 // Rows [r0, r1) of matrix (kind, group) -> their byte range of the file, in blocks of whole rows.
 void write_packed_rows(ggrm_t* h, int kind, int group, int64_t r0, int64_t r1, const BinFile& file, WriterPool& pool, bool gcta = false) {
     int64_t r = r0;
     while (r < r1) {
-        int64_t cnt = 1;
-        {
-            int64_t lo = 1, hi = r1 - r;  // largest cnt whose rows fit one buffer (a single row always fits: buffers hold >= n floats)
-            while (lo < hi) {
-                const int64_t mid = (lo + hi + 1) / 2;
-                if (tri(r + mid) - tri(r) <= pool.buffer_elems()) lo = mid; else hi = mid - 1;
-            }
-            cnt = lo;
-        }
+        const int64_t cnt = rows_fitting(r, r1, pool.buffer_elems());
         float* buf = pool.acquire();
         // gcta: kind 0 -> A = G / N, kind 1 -> N (ggrm_fetch_gcta's `which` is the kind index)
         const int st = gcta ? ggrm_fetch_gcta(h, kind, group, r, cnt, buf) : ggrm_fetch(h, kind, group, r, cnt, buf, nullptr);
@@ -215,14 +278,7 @@ void write_owned_supertiles(ggrm_t* h, int kind, int group, int64_t n, const Bin
             pool.submit(file, buf, {});
             throw_status(st, ggrm_last_error(h));
         }
-        std::vector<Segment> segs;
-        segs.reserve(static_cast<size_t>(rows));
-        for (int64_t i = 0; i < rows; ++i) {
-            const int64_t gi = row0 + i;
-            const int64_t len = std::min(cols, gi + 1 - col0);
-            if (len > 0) segs.push_back(Segment{i * cols, (tri(gi) + col0) * 4, len * 4});
-        }
-        pool.submit(file, buf, std::move(segs));
+        pool.submit(file, buf, supertile_segments(row0, col0, rows, cols));
     }
 }
 
@@ -317,6 +373,7 @@ struct RunContext {
     bool loco;
     bool want_add, want_dom;
     bool gcta;  // kind 1 is the non-missing pair count matrix; outputs are <out>.grm.bin / .grm.N.bin / .grm.id
+    WriterMode writer;  // effective mode of this run: Pwrite when the file system could not hold every output (see BinFile)
     // progress (reference: per work item, counted in SNPs; grm.h:124-130)
     const GrmObserver* observer;
     std::mutex* mu;
@@ -417,7 +474,7 @@ void write_outputs(const RunContext& rc, ggrm_t* h, int local_group, const std::
         if (!(kind == 0 ? rc.want_add : rc.want_dom)) continue;
         const std::string base = output_base(rc, kind, suffix);
         BinFile f;
-        f.open(base + ".bin", rc.n_out, part.create);
+        f.open(base + ".bin", rc.n_out, part.create, rc.writer);
         try {
             switch (part.kind) {
                 case WritePart::AllRows: write_packed_rows(h, kind, local_group, 0, rc.n_out, f, pool, rc.gcta); break;
@@ -539,7 +596,7 @@ void run_pipelined_rank(const RunContext& rc, ShardPipe& sp, size_t r, double* p
     WriterPool pool(rc.cfg->writer_threads, rc.cfg->writer_threads + 2, std::max<int64_t>(kWriterBufferElems, rc.n_out));
     BinFile files[2];
     for (int kind = 0; kind < 2; ++kind)
-        if (kind == 0 ? rc.want_add : rc.want_dom) files[kind].open(output_base(rc, kind, "") + ".bin", rc.n_out, false);
+        if (kind == 0 ? rc.want_add : rc.want_dom) files[kind].open(output_base(rc, kind, "") + ".bin", rc.n_out, false, rc.writer);
     int64_t done = 0;
     push_range(rc, h, sp.snps[r].first, sp.snps[r].second, sp.snps[r].second - sp.snps[r].first, &done);
     check(h, ggrm_finish_async(h));
@@ -807,6 +864,99 @@ std::vector<GrmEngine::OwnedStrip> GrmEngine::strip_owners_for(int64_t n, int wo
     return out;
 }
 
+namespace {
+
+WriterMode resolve_writer_mode(WriterMode configured) {
+    if (configured != WriterMode::Auto) return configured;
+    const char* e = std::getenv("GELEX_B200_WRITER");
+    if (e == nullptr) return WriterMode::Auto;
+    const std::string v = lower(e);
+    if (v == "pwrite") return WriterMode::Pwrite;
+    if (v == "mmap") return WriterMode::Mmap;
+    if (v == "auto" || v.empty()) return WriterMode::Auto;
+    throw ArgumentValidationException("GELEX_B200_WRITER must be auto, pwrite or mmap");
+}
+
+// entries (i, j0 .. j0 + len) of the self-test matrix: float((31 i + j) mod 65521) + 0.5, copied from two periods of the pattern
+// (the producer must not be the bottleneck of a writer measurement)
+void selftest_fill(float* out, int64_t i, int64_t j0, int64_t len) {
+    constexpr int64_t kP = 65521;
+    static const std::vector<float> table = [] {
+        std::vector<float> t(static_cast<size_t>(2 * kP));
+        for (int64_t k = 0; k < 2 * kP; ++k) t[static_cast<size_t>(k)] = static_cast<float>(k % kP) + 0.5f;
+        return t;
+    }();
+    while (len > 0) {
+        const int64_t start = (i * 31 + j0) % kP;
+        const int64_t take = std::min(len, kP);
+        std::memcpy(out, table.data() + start, static_cast<size_t>(take) * sizeof(float));
+        out += take;
+        j0 += take;
+        len -= take;
+    }
+}
+
+}  // namespace
+
+double GrmEngine::writer_selftest(const fs::path& bin_path, int64_t n, bool tiles, int parts, int writer_threads, WriterMode mode, bool* mapped) {
+    if (n < 1 || parts < 1 || writer_threads < 1) throw ArgumentValidationException("writer_selftest: invalid argument");
+    mode = resolve_writer_mode(mode);
+    if (mode != WriterMode::Pwrite && !file_system_has_room(bin_path, tri(n) * 4)) mode = WriterMode::Pwrite;
+    {
+        BinFile f;
+        f.open(bin_path, n, true);
+        f.close_checked();
+    }
+    // the work of each part, as the engine deals it: row slices (SNP-shard writers) or super-tiles round-robin (2D tiles)
+    const auto slices = row_slices(n, parts);
+    std::vector<std::pair<int64_t, int64_t>> supers;
+    for (int64_t si = 0; si * kSuperRows < n; ++si)
+        for (int64_t sj = 0; sj <= si; ++sj) supers.emplace_back(si, sj);
+    std::vector<std::exception_ptr> errors(static_cast<size_t>(parts));
+    std::vector<int> any_map(static_cast<size_t>(parts), 0);
+    std::vector<std::thread> threads;
+    const auto t0 = Clock::now();
+    for (int r = 0; r < parts; ++r) {
+        threads.emplace_back([&, r] {
+            try {
+                WriterPool pool(writer_threads, writer_threads + 2, std::max<int64_t>(kWriterBufferElems, n));
+                BinFile f;
+                f.open(bin_path, n, false, mode);
+                any_map[static_cast<size_t>(r)] = f.map != nullptr ? 1 : 0;
+                if (!tiles) {
+                    int64_t row = slices[static_cast<size_t>(r)].first;
+                    const int64_t r1 = slices[static_cast<size_t>(r)].second;
+                    while (row < r1) {
+                        const int64_t cnt = rows_fitting(row, r1, pool.buffer_elems());
+                        float* buf = pool.acquire();
+                        float* o = buf;
+                        for (int64_t i = row; i < row + cnt; o += i + 1, ++i) selftest_fill(o, i, 0, i + 1);
+                        pool.submit(f, buf, {Segment{0, tri(row) * 4, (tri(row + cnt) - tri(row)) * 4}});
+                        row += cnt;
+                    }
+                } else {
+                    for (size_t t = static_cast<size_t>(r); t < supers.size(); t += static_cast<size_t>(parts)) {
+                        const int64_t row0 = supers[t].first * kSuperRows, col0 = supers[t].second * kSuperRows;
+                        const int64_t rows = std::min(kSuperRows, n - row0), cols = std::min(kSuperRows, n - col0);
+                        float* buf = pool.acquire();
+                        for (int64_t i = 0; i < rows; ++i) selftest_fill(buf + i * cols, row0 + i, col0, cols);
+                        pool.submit(f, buf, supertile_segments(row0, col0, rows, cols));
+                    }
+                }
+                pool.drain();
+                f.close_checked();
+            } catch (...) {
+                errors[static_cast<size_t>(r)] = std::current_exception();
+            }
+        });
+    }
+    for (auto& t : threads) t.join();
+    const double dt = since(t0);
+    for (auto& e : errors) if (e) std::rethrow_exception(e);
+    if (mapped != nullptr) *mapped = std::any_of(any_map.begin(), any_map.end(), [](int v) { return v != 0; });
+    return dt;
+}
+
 void GrmEngine::compute(const GrmObserver& observer) {
     const auto t_start = Clock::now();
     summary_ = Summary{};
@@ -859,6 +1009,15 @@ void GrmEngine::compute(const GrmObserver& observer) {
 
     const int n_gpus = static_cast<int>(config_.gpus.size());
     if (config_.writer_threads < 1) throw ArgumentValidationException("writer_threads must be >= 1");
+    rc.writer = resolve_writer_mode(config_.writer);
+    if (rc.writer != WriterMode::Pwrite) {
+        // every .bin of the run: one per work item, plus the whole-genome sums of a LOCO run, or the GCTA pair
+        int64_t bins = static_cast<int64_t>(items.size());
+        if (config_.do_loco && config_.write_whole) bins += (rc.want_add ? 1 : 0) + (rc.want_dom ? 1 : 0);
+        if (config_.gcta) bins = 2;
+        if (!file_system_has_room(config_.out_prefix, bins * tri(rc.n_out) * 4)) rc.writer = WriterMode::Pwrite;
+    }
+    summary_.outputs_mapped = rc.writer != WriterMode::Pwrite;
     if (items.empty() || rc.groups.empty() || chroms.empty()) {
         // nothing to accumulate (empty BIM is rejected earlier as "is empty")
     } else if (n_gpus == 1) {

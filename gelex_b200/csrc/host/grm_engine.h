@@ -50,6 +50,12 @@ struct GrmWorkItem {  // src/pipeline/grm_work_plan.h:34-39
 // tiles from there on.
 enum class Partition : uint8_t { Auto, SnpShard, Tile };
 
+// How blocks reach the .bin files (grm_engine.cpp, BinFile): Auto = memcpy into a shared mapping of the pre-sized file for
+// scattered segments (2D-tile rows) and on tmpfs, pwrite otherwise; Pwrite / Mmap force one of them.  A mapping is only used
+// when the output file system had room for every output at the start of the run (a full disk must fail with
+// FileWriteException, not SIGBUS).  GELEX_B200_WRITER=auto|pwrite|mmap overrides Auto.
+enum class WriterMode : uint8_t { Auto, Pwrite, Mmap };
+
 class GrmEngine {
    public:
     struct Config {
@@ -66,7 +72,8 @@ class GrmEngine {
         bool write_whole = false;        // with do_loco: also write <out>.<add|dom>.{bin,id} from the sum of partials
         bool skip_all_missing = false;   // GGRM_ALLMISS_SKIP instead of the reference's NaN poisoning
         Partition partition = Partition::Auto;
-        int writer_threads = 4;          // pwrite threads per GPU draining the page-locked read-out ring
+        int writer_threads = 4;          // writer threads per GPU draining the page-locked read-out ring
+        WriterMode writer = WriterMode::Auto;
         // GCTA binary format behind a flag (docs/source/data_formats.rst:188-208): instead of <out>.add.{bin,id} write
         // <out>.grm.bin (A_ij = G_ij / N_ij), <out>.grm.N.bin (N_ij = SNPs called in both samples) and <out>.grm.id.  Mode A, no LOCO.
         bool gcta = false;
@@ -80,6 +87,7 @@ class GrmEngine {
         size_t num_samples = 0, num_snps = 0, num_files = 0;
         double wall_s = 0, device_pass_ms = 0, syrk_ms = 0, write_s = 0;
         std::vector<std::string> files;
+        bool outputs_mapped = false;  // the run was allowed to write through shared mappings (WriterMode, free-space check)
     };
     const Summary& summary() const { return summary_; }
 
@@ -92,6 +100,13 @@ class GrmEngine {
     // 2 048-row strips of the band-pipelined SNP-shard run, dealt by LPT: (rank, band, row range), rank-major, rows ascending.
     struct OwnedStrip { int rank, band; int64_t row_begin, row_end; };
     static std::vector<OwnedStrip> strip_owners_for(int64_t n, int world, const std::vector<int64_t>& band_row_end);
+
+    // CPU-only check of the writer pool (no GPU involved): writes the packed lower triangle of an n x n matrix with entry
+    // (i, j) = float((31 i + j) mod 65521) + 0.5 through the same jobs the engine submits - whole-row blocks of `parts` row
+    // slices (tiles = false), or 2 048 x 2 048 super-tile row segments dealt round-robin to `parts` concurrent pools (tiles = true) -
+    // and returns the seconds spent.  tests/test_host_engine.py compares the file with numpy.
+    static double writer_selftest(const std::filesystem::path& bin_path, int64_t n, bool tiles, int parts, int writer_threads, WriterMode mode,
+                                  bool* mapped);
 
    private:
     Config config_;
@@ -115,3 +130,6 @@ extern "C" int gelex_b200_grm_run_gcta(const char* bfile, const char* out_prefix
                                        int writer_threads, char* err, int err_len);
 // strip_owners_for through C (CPU tests): out4 receives (rank, band, row_begin, row_end) per strip, up to cap strips; returns the strip count.
 extern "C" int gelex_b200_strip_owners(int64_t n, int world, const int64_t* band_row_end, int n_bands, int64_t* out4, int cap);
+// GrmEngine::writer_selftest through C (CPU tests): writer 0 = auto, 1 = pwrite, 2 = mmap.
+extern "C" int gelex_b200_writer_selftest(const char* bin_path, int64_t n, int tiles, int parts, int writer_threads, int writer,
+                                          double* seconds_out, int* mapped_out, char* err, int err_len);

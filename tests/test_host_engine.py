@@ -191,6 +191,51 @@ def test_engine_16bit_tile_mode_large_rows(tmp_path, monkeypatch):
     assert np.max(np.abs(a3 - a1)) <= 1e-4 * np.max(np.abs(a1))
 
 
+@pytest.mark.parametrize("writer", ["pwrite", "mmap", "auto"])
+@pytest.mark.parametrize("tiles,parts", [(False, 1), (False, 3), (True, 1), (True, 3)])
+def test_writer_pool_bytes_need_no_gpu(tmp_path, writer, tiles, parts):
+    # The .bin writer of the engine (BinFile + WriterPool, grm_engine.cpp) on a synthetic matrix: whole-row blocks of `parts` row
+    # slices (single GPU / SNP-shard read-out) and super-tile row segments dealt to `parts` concurrent pools (2D-tile read-out),
+    # through pwrite and through the shared mapping: the reference's layout (grm_bin_writer.cpp:54-61: row-major lower triangle,
+    # float32, no header), byte for byte.  n = 4500: three super-rows, ragged last super-tile; n = 1 and 5: a single block.
+    for n in (1, 5, 4500):
+        path = tmp_path / f"w{n}.bin"
+        _, mapped = engine.writer_selftest(path, n, tiles=tiles, parts=parts, writer_threads=2, writer=writer)
+        assert mapped == (writer != "pwrite")
+        got = np.fromfile(path, dtype=np.float32)
+        assert path.stat().st_size == n * (n + 1) // 2 * 4  # exactly n(n+1)/2 floats (test_grm_bin_writer.cpp:40-43)
+        assert np.array_equal(got, engine.writer_selftest_expected(n))
+
+
+def test_writer_mode_env_and_validation_need_no_gpu(tmp_path, monkeypatch):
+    monkeypatch.setenv("GELEX_B200_WRITER", "pwrite")  # the environment overrides Auto only
+    assert engine.writer_selftest(tmp_path / "a.bin", 300, writer="auto")[1] is False
+    assert engine.writer_selftest(tmp_path / "a.bin", 300, writer="mmap")[1] is True
+    monkeypatch.setenv("GELEX_B200_WRITER", "floppy")
+    with pytest.raises(engine.EngineError, match="ArgumentValidationException: GELEX_B200_WRITER must be auto, pwrite or mmap"):
+        engine.writer_selftest(tmp_path / "a.bin", 300, writer="auto")
+    monkeypatch.delenv("GELEX_B200_WRITER")
+    with pytest.raises(engine.EngineError, match="FileOpenException"):
+        engine.writer_selftest(tmp_path / "no_such_dir" / "a.bin", 300)
+    with pytest.raises(engine.EngineError, match="ArgumentValidationException"):
+        engine.writer_selftest(tmp_path / "a.bin", 0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("partition", ["snp", "tile"])
+def test_engine_writer_modes_give_identical_files(tmp_path, monkeypatch, partition):
+    # same run through pwrite and through the shared mapping: identical bytes (two ranks on one device when the box has one GPU)
+    monkeypatch.setenv("GELEX_B200_OVERSUBSCRIBE", "1")
+    n, m = 4100, 1024
+    payload = g.synth_bed_host(n, 0, m, 29, 0.01)
+    plink_io.write_plink(tmp_path / "d", payload, [("F", f"s{i:05d}") for i in range(n)], ["1"] * m)
+    for w in ("pwrite", "mmap"):
+        monkeypatch.setenv("GELEX_B200_WRITER", w)
+        engine.grm_run(tmp_path / "d", tmp_path / w, method="SH", precision=g.PREC_FP64, n_gpus=2, partition=partition)
+    assert (tmp_path / "mmap.add.bin").read_bytes() == (tmp_path / "pwrite.add.bin").read_bytes()
+    assert (tmp_path / "mmap.add.id").read_bytes() == (tmp_path / "pwrite.add.id").read_bytes()
+
+
 @pytest.mark.gpu
 def test_cli_is_a_drop_in(golden_dir, tmp_path):
     r = subprocess.run([str(engine.CLI_PATH), "grm", "-b", str(golden_dir / "tiny"), "--gm", "SH", "--add", "-c", "25", "--precision", "fp64",
