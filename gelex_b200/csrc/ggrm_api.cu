@@ -25,16 +25,17 @@ void encode_tensor_map(CUtensorMap* map, void* base, int64_t k_cap, int64_t n_pa
     typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-    static EncodeFn encode = nullptr;
-    if (encode == nullptr) {
+    // resolved once; a function-local static is initialised under the compiler's guard, so handles created concurrently from
+    // several host threads (the multi-GPU engine does that) do not race on it, and a failed lookup is retried by the next call
+    static const EncodeFn encode = [] {
         void* fn = nullptr;
         cudaDriverEntryPointQueryResult qres;
         GGRM_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
         if (fn == nullptr || qres != cudaDriverEntryPointSuccess) {
             throw CudaError{GGRM_ERR_CUDA, "CUDA: cuTensorMapEncodeTiled entry point not available"};
         }
-        encode = reinterpret_cast<EncodeFn>(fn);
-    }
+        return reinterpret_cast<EncodeFn>(fn);
+    }();
     const cuuint64_t dims[2] = {static_cast<cuuint64_t>(k_cap), static_cast<cuuint64_t>(n_pad)};
     const cuuint64_t strides[1] = {static_cast<cuuint64_t>(k_cap) * 2};
     const cuuint32_t box[2] = {64, 128};
@@ -495,6 +496,10 @@ extern "C" int ggrm_create(const ggrm_config_t* cfg, ggrm_t** out) {
         g_create_error = "host allocation failed";
         free_handle(h);
         return GGRM_ERR_OUT_OF_MEMORY;
+    } catch (const std::exception& e) {  // nothing may unwind through the C ABI
+        g_create_error = e.what();
+        free_handle(h);
+        return GGRM_ERR_INVALID_OPERATION;
     }
     *out = reinterpret_cast<ggrm_t*>(h);
     return GGRM_OK;

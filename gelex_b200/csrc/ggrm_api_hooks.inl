@@ -86,6 +86,10 @@ static void decode_common(int device, const uint8_t* payload, int64_t snp_count,
         g_create_error = "host allocation failed"; \
         return GGRM_ERR_OUT_OF_MEMORY;        \
     }                                         \
+    catch (const std::exception& e) {         \
+        g_create_error = e.what();            \
+        return GGRM_ERR_INVALID_OPERATION;    \
+    }                                         \
     return GGRM_OK;
 
 extern "C" int ggrm_decode_chunk(int device, const uint8_t* bed_payload, int64_t snp_count, int64_t bytes_per_variant, int64_t n_raw,
