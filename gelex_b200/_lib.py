@@ -69,6 +69,7 @@ EXPORTS = [
     "ggrm_ipc_export", "ggrm_ipc_open", "ggrm_ipc_close", "ggrm_row_slice",
     "ggrm_fetch_block", "ggrm_owned_supertiles", "ggrm_host_alloc", "ggrm_host_free", "ggrm_bin_to_dense", "ggrm_assoc_chunk",
     "ggrm_band_layout", "ggrm_set_band_flags", "ggrm_reduce_rows_async", "ggrm_genotype_chunk", "ggrm_fetch_gcta", "ggrm_accum_address",
+    "ggrm_stage_create", "ggrm_stage_destroy", "ggrm_stage_upload", "ggrm_stage_slot", "ggrm_wait_copies",
 ]
 
 _lib = None
@@ -123,6 +124,12 @@ def load() -> C.CDLL:
     lib.ggrm_genotype_chunk.argtypes = [C.c_int, vp, i64, i64, i64, i64, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp]
     lib.ggrm_synth_bed_host.argtypes = [vp, i64, i64, i64, u64, dbl]
     lib.ggrm_synth_bed_device.argtypes = [C.c_int, vp, i64, i64, i64, u64, dbl]
+    lib.ggrm_stage_create.argtypes = [C.c_int, i64, C.c_int, C.POINTER(vp)]
+    lib.ggrm_stage_destroy.argtypes = [vp]
+    lib.ggrm_stage_destroy.restype = None
+    lib.ggrm_stage_upload.argtypes = [vp, C.c_int, vp, i64]
+    lib.ggrm_stage_slot.argtypes = [vp, C.c_int, C.POINTER(vp)]
+    lib.ggrm_wait_copies.argtypes = [vp]
     lib.ggrm_device_count.argtypes = []
     lib.ggrm_version.argtypes = []
     lib.ggrm_version.restype = C.c_char_p

@@ -523,3 +523,4 @@ extern "C" const char* ggrm_version(void) { return "gelex-grm-b200 0.1 (sm_100a;
 #include "ggrm_api_stream.inl"
 #include "ggrm_api_fetch.inl"
 #include "ggrm_api_hooks.inl"
+#include "ggrm_api_stage.inl"

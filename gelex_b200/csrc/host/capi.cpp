@@ -290,3 +290,13 @@ extern "C" int gelex_b200_writer_selftest(const char* bin_path, int64_t n, int t
         return translate_exception(err, err_len);
     }
 }
+
+extern "C" int64_t gelex_b200_relay_selftest(int n_chunks, int world, int slots, int chunk_bytes, int fail_at_chunk, char* err, int err_len) {
+    try {
+        const int64_t bad = GrmEngine::relay_selftest(n_chunks, world, slots, chunk_bytes, fail_at_chunk);
+        set_err(err, err_len, "");
+        return bad;
+    } catch (...) {
+        return translate_exception(err, err_len);
+    }
+}

@@ -8,6 +8,7 @@
 #include <cstring>
 #include <exception>
 #include <fstream>
+#include <memory>
 #include <mutex>
 #include <numeric>
 #include <thread>
@@ -374,6 +375,7 @@ struct RunContext {
     bool want_add, want_dom;
     bool gcta;  // kind 1 is the non-missing pair count matrix; outputs are <out>.grm.bin / .grm.N.bin / .grm.id
     WriterMode writer;  // effective mode of this run: Pwrite when the file system could not hold every output (see BinFile)
+    bool bed_relay;     // 2D-tile mode: one upload per host chunk, peers copy it over NVLink (BedRelay)
     // progress (reference: per work item, counted in SNPs; grm.h:124-130)
     const GrmObserver* observer;
     std::mutex* mu;
@@ -426,15 +428,157 @@ void emit_progress(const RunContext& rc, size_t current, size_t total) {
     for (int k = 0; k < kinds; ++k) (*rc.observer)(GrmProgressEvent{current, total, false});
 }
 
-// Push SNPs [begin, end) in host chunks of cfg.chunk_size (the reference's load_chunk granularity).
-void push_range(const RunContext& rc, ggrm_t* h, int64_t begin, int64_t end, int64_t item_total, int64_t* item_done, bool report = true) {
+// ---------------------------------------------------------------------------------------------------------------
+// One host read of the BED for every GPU of a 2D-tile run (Config::bed_relay; SURVEY 8e, input side of the tile partition).
+// All GPUs need all SNPs.  Without the relay each GPU thread pushes the whole mapped file through its own pinned ring and PCIe
+// link (C5: 30 GB per GPU, 5.1 s of accumulate for 1.85 s of SYRK, profiles/r01_summary.md §5).  With it, host chunk j is uploaded
+// ONCE - by an uploader thread of rank j % N into one of that GPU's staging slots (ggrm_stage_upload) - and every rank takes it
+// from there with ggrm_push_device: a copy over NVLink peer memory for the N - 1 others.  All ranks walk the same chunk list in
+// the same order (run_groups_on_device cuts every chromosome run from its first SNP in steps of chunk_size), so a chunk is its
+// index; slot (j / N) % slots of rank j % N is reused once all N ranks have consumed chunk j - N * slots.  No collective: flags
+// in process memory, as in the band-pipelined reduce.
+// The protocol, free of any device call (GrmEngine::relay_selftest drives it with host buffers): `world` uploader threads fill
+// slots, `world` consumers take every chunk in order.
+class ChunkRelay {
+   public:
+    using Upload = std::function<void(size_t owner, int slot, size_t chunk)>;  // blocking: on return the slot holds the chunk
+    ChunkRelay(size_t n_chunks, size_t world, size_t slots, Upload upload)
+        : n_(n_chunks), world_(world), slots_(slots), upload_(std::move(upload)), ready_(n_chunks), consumed_(n_chunks), errors_(world) {
+        for (size_t r = 0; r < world_; ++r) uploaders_.emplace_back([this, r] { upload_loop(r); });
+    }
+    ChunkRelay(const ChunkRelay&) = delete;
+    ChunkRelay& operator=(const ChunkRelay&) = delete;
+    ~ChunkRelay() { stop(); }
+    size_t owner_of(size_t j) const { return j % world_; }
+    int slot_of(size_t j) const { return static_cast<int>((j / world_) % slots_); }
+    // Consumer side: block until chunk j sits in slot_of(j) of owner_of(j) ...
+    void acquire(size_t j) {
+        wait_for([&] { return ready_[j].load(std::memory_order_acquire) != 0; }, "BED relay: timed out waiting for a chunk");
+    }
+    // ... and, once this consumer has copied it out, let the slot go (it is refilled when all `world` consumers have).
+    void release(size_t j) { consumed_[j].fetch_add(1, std::memory_order_release); }
+    void fail() { failed_.store(true); }
+    // Joins the uploaders (after the consumers have finished or failed) and rethrows the first uploader error, if any.
+    void stop_and_rethrow() {
+        stop();
+        for (auto& e : errors_) if (e) std::rethrow_exception(e);
+    }
+
+   private:
+    void stop() {
+        failed_.store(true);  // a no-op after a complete run: every uploader has left its loop
+        for (auto& t : uploaders_) t.join();
+        uploaders_.clear();
+    }
+    template <typename Pred>
+    void wait_for(Pred ok, const char* what) {
+        const auto t0 = Clock::now();
+        while (!ok()) {
+            if (failed_.load()) throw GelexException("multi-GPU run aborted: another GPU failed");
+            if (since(t0) > 3600.0) throw GelexException(what);
+            std::this_thread::sleep_for(std::chrono::microseconds(20));
+        }
+    }
+    void upload_loop(size_t r) {
+        try {
+            const size_t lap = world_ * slots_;
+            for (size_t j = r; j < n_; j += world_) {
+                if (j >= lap)  // the chunk that last used this slot has been taken by every consumer
+                    wait_for([&] { return consumed_[j - lap].load(std::memory_order_acquire) == static_cast<int>(world_); },
+                             "BED relay: timed out waiting for a free slot");
+                upload_(r, slot_of(j), j);
+                ready_[j].store(1, std::memory_order_release);
+            }
+        } catch (...) {
+            if (!failed_.exchange(true)) errors_[r] = std::current_exception();  // only a first failure is a cause
+        }
+    }
+    size_t n_, world_, slots_;
+    Upload upload_;
+    std::vector<std::atomic<int>> ready_, consumed_;
+    std::vector<std::exception_ptr> errors_;
+    std::vector<std::thread> uploaders_;
+    std::atomic<bool> failed_{false};
+};
+
+class BedRelay {
+   public:
+    BedRelay(const RunContext& rc, const std::vector<int>& gpus, int slots_per_gpu) : rc_(rc) {
+        for (const ChrRun& g : rc.groups)
+            for (int64_t s = g.begin; s < g.end; s += rc.cfg->chunk_size) {
+                index_of_[s] = chunks_.size();
+                chunks_.push_back({s, std::min<int64_t>(rc.cfg->chunk_size, g.end - s)});
+            }
+        const size_t world = gpus.size();
+        for (size_t a = 0; a < world; ++a)
+            for (size_t b = 0; b < world; ++b)
+                if (gpus[a] != gpus[b]) {
+                    const int st = ggrm_enable_peer_access(gpus[a], gpus[b]);
+                    if (st != GGRM_OK) throw_status(st, ggrm_last_error(nullptr));
+                }
+        stages_.assign(world, nullptr);
+        try {
+            for (size_t r = 0; r < world; ++r) {
+                const int st = ggrm_stage_create(gpus[r], std::max<int64_t>(1, static_cast<int64_t>(rc.cfg->chunk_size) * rc.bpv), slots_per_gpu, &stages_[r]);
+                if (st != GGRM_OK) throw_status(st, ggrm_last_error(nullptr));
+            }
+            relay_ = std::make_unique<ChunkRelay>(chunks_.size(), world, static_cast<size_t>(slots_per_gpu), [this](size_t owner, int slot, size_t j) {
+                const Chunk& ck = chunks_[j];
+                const uint8_t* p = rc_.bed->chunk_ptr(ck.s, ck.c);
+                if (p == nullptr) throw FileFormatException("BedPipe::load_chunk: mapped BED payload is truncated");
+                const int st = ggrm_stage_upload(stages_[owner], slot, p, ck.c * rc_.bpv);
+                if (st != GGRM_OK) throw_status(st, ggrm_last_error(nullptr));
+            });
+        } catch (...) {
+            for (ggrm_stage_t* st : stages_) if (st != nullptr) ggrm_stage_destroy(st);
+            throw;
+        }
+    }
+    BedRelay(const BedRelay&) = delete;
+    BedRelay& operator=(const BedRelay&) = delete;
+    ~BedRelay() {
+        relay_.reset();  // joins the uploaders before their slots go away
+        for (ggrm_stage_t* st : stages_) if (st != nullptr) ggrm_stage_destroy(st);
+    }
+    void fail() { relay_->fail(); }
+    void stop_and_rethrow() { relay_->stop_and_rethrow(); }
+    // The handle of one rank takes the host chunk that starts at SNP s (one of the relay's chunks, c SNPs).
+    void push(ggrm_t* h, int64_t s, int64_t c) {
+        const auto it = index_of_.find(s);
+        if (it == index_of_.end() || chunks_[it->second].c != c) throw GelexException("BED relay: chunk list out of step");
+        const size_t j = it->second;
+        relay_->acquire(j);
+        const uint8_t* d = nullptr;
+        const int st = ggrm_stage_slot(stages_[relay_->owner_of(j)], relay_->slot_of(j), &d);
+        if (st != GGRM_OK) throw_status(st, ggrm_last_error(nullptr));
+        check(h, ggrm_push_device(h, d, s, c, rc_.bpv));
+        check(h, ggrm_wait_copies(h));  // the slot has been read by this rank
+        relay_->release(j);
+    }
+
+   private:
+    struct Chunk { int64_t s, c; };
+    const RunContext& rc_;
+    std::vector<Chunk> chunks_;
+    std::unordered_map<int64_t, size_t> index_of_;
+    std::vector<ggrm_stage_t*> stages_;
+    std::unique_ptr<ChunkRelay> relay_;
+};
+
+// Push SNPs [begin, end) in host chunks of cfg.chunk_size (the reference's load_chunk granularity); through the relay when there is one.
+void push_range(const RunContext& rc, ggrm_t* h, int64_t begin, int64_t end, int64_t item_total, int64_t* item_done, bool report = true,
+                BedRelay* relay = nullptr) {
     for (int64_t s = begin; s < end; s += rc.cfg->chunk_size) {
         const int64_t c = std::min<int64_t>(rc.cfg->chunk_size, end - s);
         if (s < 0 || s + c > rc.m || c <= 0)  // validate_chunk_range, bed_pipe.cpp:38-52
             throw ColumnRangeException("invalid chunk range: [" + std::to_string(s) + ", " + std::to_string(s + c) + "). Total SNPs: " + std::to_string(rc.m));
-        const uint8_t* p = rc.bed->chunk_ptr(s, c);
-        if (p == nullptr) throw FileFormatException("BedPipe::load_chunk: mapped BED payload is truncated");
-        check(h, ggrm_push(h, p, s, c, rc.bpv));
+        if (relay != nullptr) {
+            relay->push(h, s, c);
+        } else {
+            const uint8_t* p = rc.bed->chunk_ptr(s, c);
+            if (p == nullptr) throw FileFormatException("BedPipe::load_chunk: mapped BED payload is truncated");
+            check(h, ggrm_push(h, p, s, c, rc.bpv));
+        }
         *item_done += c;
         if (report) emit_progress(rc, static_cast<size_t>(*item_done), static_cast<size_t>(item_total));
     }
@@ -507,7 +651,8 @@ void note_timers(const RunContext& rc, ggrm_t* h, double* pass_ms, double* syrk_
 // One GPU, a list of groups (chromosome runs) in SNP order.  Group g is written while the GPU already works on g+1.
 // `part` says which piece of every group's file this handle writes (all rows, or the tiles it owns in 2D-tile mode).
 void run_groups_on_device(const RunContext& rc, int device, const std::vector<int>& my_groups, bool keep_whole, ggrm_t** keep_handle,
-                          double* pass_ms, double* syrk_ms, const WritePart& part, int tile_rank, int tile_world, bool report, bool write_whole_here) {
+                          double* pass_ms, double* syrk_ms, const WritePart& part, int tile_rank, int tile_world, bool report, bool write_whole_here,
+                          BedRelay* relay = nullptr) {
     HandleGuard hg;
     hg.h = create_handle(rc, device, my_groups, keep_whole, tile_rank, tile_world);
     WriterPool pool(rc.cfg->writer_threads, rc.cfg->writer_threads + 2, std::max<int64_t>(kWriterBufferElems, rc.n_out));
@@ -518,14 +663,14 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
         int64_t done = 0;
         // first chunk of this group makes the previous group fetchable
         const int64_t first_end = std::min<int64_t>(run.end, run.begin + rc.cfg->chunk_size);
-        push_range(rc, hg.h, run.begin, first_end, run.end - run.begin, &done, report);
+        push_range(rc, hg.h, run.begin, first_end, run.end - run.begin, &done, report, relay);
         if (pending >= 0) {
             write_outputs(rc, hg.h, pending, group_name(pending), part, pool);
             for (int kind = 0; kind < 2; ++kind)
                 if (kind == 0 ? rc.want_add : rc.want_dom) check(hg.h, ggrm_release_group(hg.h, kind, pending));
             pending = -1;
         }
-        push_range(rc, hg.h, first_end, run.end, run.end - run.begin, &done, report);
+        push_range(rc, hg.h, first_end, run.end, run.end - run.begin, &done, report, relay);
         if (rc.loco) pending = static_cast<int>(li);
     }
     // The matrix still accumulating when the last SNP is pushed (the whole-genome one, or the last chromosome) is read out
@@ -737,6 +882,7 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
     std::vector<std::vector<int>> mine(ng);
     std::vector<int> all;
     ShardPipe pipe;
+    std::unique_ptr<BedRelay> relay;  // function scope: outlives the worker threads
     bool pipelined = false;
     if (tile_mode) {
         // 2D output tiles: every GPU streams ALL SNPs, owns disjoint 2048 x 2048 super-tiles of every matrix and writes them
@@ -747,14 +893,17 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
         precreate_outputs(rc, suffixes);
         all.resize(rc.groups.size());
         std::iota(all.begin(), all.end(), 0);
+        if (rc.bed_relay) relay = std::make_unique<BedRelay>(rc, gpus, 2);
         for (size_t r = 0; r < ng; ++r) {
             threads.emplace_back([&, r] {
                 try {
                     WritePart part;
                     part.kind = WritePart::OwnedTiles;
                     part.create = false;
-                    run_groups_on_device(rc, gpus[r], all, rc.loco && want_whole, nullptr, pass_ms, syrk_ms, part, static_cast<int>(r), static_cast<int>(ng), r == 0, false);
+                    run_groups_on_device(rc, gpus[r], all, rc.loco && want_whole, nullptr, pass_ms, syrk_ms, part, static_cast<int>(r), static_cast<int>(ng), r == 0, false,
+                                         relay.get());
                 } catch (...) {
+                    if (relay) relay->fail();
                     errors[r] = std::current_exception();
                 }
             });
@@ -839,6 +988,16 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
         pipelined = true;
     }
     for (auto& t : threads) t.join();
+    if (relay) {
+        // an uploader's own failure (unreadable BED, device error) is the cause; the ranks it starved only report "aborted"
+        try {
+            relay->stop_and_rethrow();
+        } catch (...) {
+            relay.reset();
+            throw;
+        }
+        relay.reset();
+    }
     for (auto& e : errors) if (e) std::rethrow_exception(e);
     if (want_whole && !tile_mode && !pipelined) {
         std::vector<ggrm_t*> live;
@@ -957,6 +1116,44 @@ double GrmEngine::writer_selftest(const fs::path& bin_path, int64_t n, bool tile
     return dt;
 }
 
+int64_t GrmEngine::relay_selftest(int n_chunks, int world, int slots, int chunk_bytes, int fail_at_chunk) {
+    if (n_chunks < 0 || world < 1 || slots < 1 || chunk_bytes < 1) throw ArgumentValidationException("relay_selftest: invalid argument");
+    const auto pattern = [](size_t j, size_t k) { return static_cast<uint8_t>((j * 131 + k * 7 + (j >> 3)) & 0xff); };
+    std::vector<std::vector<uint8_t>> store(static_cast<size_t>(world) * static_cast<size_t>(slots), std::vector<uint8_t>(static_cast<size_t>(chunk_bytes)));
+    auto slot_mem = [&](size_t owner, int slot) -> std::vector<uint8_t>& { return store[owner * static_cast<size_t>(slots) + static_cast<size_t>(slot)]; };
+    ChunkRelay relay(static_cast<size_t>(n_chunks), static_cast<size_t>(world), static_cast<size_t>(slots), [&](size_t owner, int slot, size_t j) {
+        if (fail_at_chunk >= 0 && j == static_cast<size_t>(fail_at_chunk)) throw FileFormatException("relay_selftest: injected upload failure");
+        auto& m = slot_mem(owner, slot);
+        if ((j * 2654435761u >> 7) % 5 == 0) std::this_thread::sleep_for(std::chrono::microseconds(200));  // uneven uploaders
+        for (size_t k = 0; k < m.size(); ++k) m[k] = pattern(j, k);
+    });
+    std::atomic<int64_t> bad{0};
+    std::vector<std::exception_ptr> errors(static_cast<size_t>(world));
+    std::vector<std::thread> consumers;
+    for (int r = 0; r < world; ++r) {
+        consumers.emplace_back([&, r] {
+            try {
+                for (size_t j = 0; j < static_cast<size_t>(n_chunks); ++j) {
+                    relay.acquire(j);
+                    const auto& m = slot_mem(relay.owner_of(j), relay.slot_of(j));
+                    if ((j + static_cast<size_t>(r)) % 7 == 0) std::this_thread::sleep_for(std::chrono::microseconds(150));  // uneven consumers
+                    int64_t wrong = 0;
+                    for (size_t k = 0; k < m.size(); ++k) wrong += m[k] != pattern(j, k);
+                    if (wrong != 0) bad.fetch_add(1);
+                    relay.release(j);
+                }
+            } catch (...) {
+                relay.fail();
+                errors[static_cast<size_t>(r)] = std::current_exception();
+            }
+        });
+    }
+    for (auto& t : consumers) t.join();
+    relay.stop_and_rethrow();  // an uploader's failure is the cause ...
+    for (auto& e : errors) if (e) std::rethrow_exception(e);  // ... otherwise a consumer's
+    return bad.load();
+}
+
 void GrmEngine::compute(const GrmObserver& observer) {
     const auto t_start = Clock::now();
     summary_ = Summary{};
@@ -1010,6 +1207,10 @@ void GrmEngine::compute(const GrmObserver& observer) {
     const int n_gpus = static_cast<int>(config_.gpus.size());
     if (config_.writer_threads < 1) throw ArgumentValidationException("writer_threads must be >= 1");
     rc.writer = resolve_writer_mode(config_.writer);
+    {
+        const char* e = std::getenv("GELEX_B200_BED_RELAY");
+        rc.bed_relay = config_.bed_relay || (e != nullptr && e[0] == '1');
+    }
     if (rc.writer != WriterMode::Pwrite) {
         // every .bin of the run: one per work item, plus the whole-genome sums of a LOCO run, or the GCTA pair
         int64_t bins = static_cast<int64_t>(items.size());

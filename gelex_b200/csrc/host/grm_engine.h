@@ -74,6 +74,10 @@ class GrmEngine {
         Partition partition = Partition::Auto;
         int writer_threads = 4;          // writer threads per GPU draining the page-locked read-out ring
         WriterMode writer = WriterMode::Auto;
+        // 2D-tile partition only: upload every host chunk of the BED once (to GPU chunk % N) and let the other GPUs take it over
+        // NVLink peer memory, instead of every GPU reading the whole file over its own PCIe link (grm_engine.cpp, BedRelay).
+        // GELEX_B200_BED_RELAY=1 turns it on as well.  Off by default until it has been measured on an 8-GPU box.
+        bool bed_relay = false;
         // GCTA binary format behind a flag (docs/source/data_formats.rst:188-208): instead of <out>.add.{bin,id} write
         // <out>.grm.bin (A_ij = G_ij / N_ij), <out>.grm.N.bin (N_ij = SNPs called in both samples) and <out>.grm.id.  Mode A, no LOCO.
         bool gcta = false;
@@ -108,6 +112,12 @@ class GrmEngine {
     static double writer_selftest(const std::filesystem::path& bin_path, int64_t n, bool tiles, int parts, int writer_threads, WriterMode mode,
                                   bool* mapped);
 
+    // CPU-only check of the BED relay's protocol (ChunkRelay in grm_engine.cpp: `world` uploader threads filling `slots` slots
+    // each, `world` consumers taking every chunk in order) with host buffers in place of device staging slots.  Returns the number
+    // of (consumer, chunk) pairs that did not read the chunk's own bytes (0 = no slot was refilled early); fail_at_chunk >= 0
+    // injects an upload failure, which must surface as that FileFormatException and not as a hang.
+    static int64_t relay_selftest(int n_chunks, int world, int slots, int chunk_bytes, int fail_at_chunk = -1);
+
    private:
     Config config_;
     Summary summary_;
@@ -133,3 +143,5 @@ extern "C" int gelex_b200_strip_owners(int64_t n, int world, const int64_t* band
 // GrmEngine::writer_selftest through C (CPU tests): writer 0 = auto, 1 = pwrite, 2 = mmap.
 extern "C" int gelex_b200_writer_selftest(const char* bin_path, int64_t n, int tiles, int parts, int writer_threads, int writer,
                                           double* seconds_out, int* mapped_out, char* err, int err_len);
+// GrmEngine::relay_selftest through C (CPU tests): returns the mismatch count (>= 0) or a negative status with err set.
+extern "C" int64_t gelex_b200_relay_selftest(int n_chunks, int world, int slots, int chunk_bytes, int fail_at_chunk, char* err, int err_len);

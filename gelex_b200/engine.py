@@ -47,6 +47,8 @@ def load_host():
                                                C.c_char_p, C.c_int]
         h.gelex_b200_writer_selftest.argtypes = [C.c_char_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int),
                                                  C.c_char_p, C.c_int]
+        h.gelex_b200_relay_selftest.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]
+        h.gelex_b200_relay_selftest.restype = C.c_int64
         _host = h
     return _host
 
@@ -238,3 +240,14 @@ def strip_owners(n, world, bands):
         r, b, lo, hi = (int(v) for v in out[4 * i:4 * i + 4])
         per[r].append((b, lo, hi))
     return per
+
+
+def relay_selftest(n_chunks, world, slots, chunk_bytes=4096, fail_at_chunk=-1):
+    """Protocol of the 2D-tile BED relay on host buffers (GrmEngine::relay_selftest): number of (consumer, chunk) pairs that read
+    anything but the chunk's own bytes."""
+    h = load_host()
+    err = C.create_string_buffer(2048)
+    r = h.gelex_b200_relay_selftest(int(n_chunks), int(world), int(slots), int(chunk_bytes), int(fail_at_chunk), err, len(err))
+    if r < 0:
+        raise EngineError(int(r), err.value.decode())
+    return int(r)

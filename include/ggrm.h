@@ -272,6 +272,25 @@ int ggrm_enable_peer_access(int device, int peer_device);
 int ggrm_host_alloc(int64_t bytes, void** out);
 int ggrm_host_free(void* p);
 
+/* ---- One host read of the BED feeding several handles (2D-tile multi-GPU mode, SURVEY 8e input side) ------------------
+ * Every GPU of a 2D-tile run accumulates every SNP.  Rather than each GPU pulling the whole file over its own PCIe link
+ * (what BedPipe::load_chunk per GPU would amount to, bed_pipe.cpp:107-158), the host uploads chunk j ONCE, into a staging
+ * slot on GPU j % N, and every handle takes it from there with ggrm_push_device (a peer copy over NVLink when the slot is
+ * on another GPU; ggrm_enable_peer_access first).
+ *   ggrm_stage_create   n_slots device buffers of slot_bytes on `device`
+ *   ggrm_stage_upload   host bytes -> slot; pageable sources are staged through two pinned 32 MiB bounce buffers; returns
+ *                       when the bytes are in device memory
+ *   ggrm_stage_slot     device address of a slot
+ *   ggrm_wait_copies    (on a handle) every copy enqueued by earlier ggrm_push* calls has read its source, so the slot
+ *                       may be overwritten
+ * Errors of the stage calls are reported through ggrm_last_error(NULL) on the calling thread. */
+typedef struct ggrm_stage ggrm_stage_t;
+int ggrm_stage_create(int device, int64_t slot_bytes, int n_slots, ggrm_stage_t** out);
+void ggrm_stage_destroy(ggrm_stage_t* s);
+int ggrm_stage_upload(ggrm_stage_t* s, int slot, const uint8_t* host_src, int64_t bytes);
+int ggrm_stage_slot(ggrm_stage_t* s, int slot, const uint8_t** d_ptr);
+int ggrm_wait_copies(ggrm_t* h);
+
 /* Library / device facts for the harness. */
 int ggrm_device_count(void);
 const char* ggrm_version(void);

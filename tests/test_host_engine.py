@@ -1,5 +1,6 @@
 """Host-side logic of the C++ engine (FAM/BIM parsing, row order, work plan, file validation, error behaviour).
 CPU-only parts run everywhere; the end-to-end file parity tests need a B200 and are marked gpu."""
+import os
 import shutil
 import subprocess
 
@@ -234,6 +235,45 @@ def test_engine_writer_modes_give_identical_files(tmp_path, monkeypatch, partiti
         engine.grm_run(tmp_path / "d", tmp_path / w, method="SH", precision=g.PREC_FP64, n_gpus=2, partition=partition)
     assert (tmp_path / "mmap.add.bin").read_bytes() == (tmp_path / "pwrite.add.bin").read_bytes()
     assert (tmp_path / "mmap.add.id").read_bytes() == (tmp_path / "pwrite.add.id").read_bytes()
+
+
+@pytest.mark.parametrize("n_chunks,world,slots", [(0, 2, 2), (1, 3, 2), (37, 1, 1), (200, 2, 1), (333, 3, 2), (600, 8, 2)])
+def test_bed_relay_protocol_needs_no_gpu(n_chunks, world, slots):
+    # 2D-tile BED relay (grm_engine.cpp, ChunkRelay): `world` uploaders fill `slots` slots each, `world` consumers take every chunk
+    # in order; a slot may only be refilled once every consumer has read it.  Host buffers stand in for the device staging slots;
+    # uploaders and consumers are slowed unevenly.  0 = every consumer read every chunk's own bytes.
+    assert engine.relay_selftest(n_chunks, world, slots, chunk_bytes=8192) == 0
+
+
+def test_bed_relay_upload_failure_surfaces_instead_of_hanging():
+    for at in (0, 5, 99):
+        with pytest.raises(engine.EngineError, match="FileFormatException: relay_selftest: injected upload failure"):
+            engine.relay_selftest(100, 4, 2, chunk_bytes=512, fail_at_chunk=at)
+    with pytest.raises(engine.EngineError, match="ArgumentValidationException"):
+        engine.relay_selftest(10, 0, 2)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(os.environ.get("GELEX_B200_TEST_UNVERIFIED") != "1",
+                    reason="BED relay device path was written after the round's GPU minutes were spent: opt in with GELEX_B200_TEST_UNVERIFIED=1")
+@pytest.mark.parametrize("loco", [False, True])
+def test_engine_tile_mode_bed_relay_matches_direct_push(tmp_path, monkeypatch, loco):
+    # same 2D-tile run with every GPU reading the whole BED itself, and with one upload per chunk shared through staging slots
+    # (ggrm_stage_* + ggrm_push_device + ggrm_wait_copies): identical bytes
+    monkeypatch.setenv("GELEX_B200_OVERSUBSCRIBE", "1")
+    n, m = 4100, 3000
+    payload = g.synth_bed_host(n, 0, m, 31, 0.01)
+    bounds = [round(m * i / 3) for i in range(4)]
+    chroms = [str(c + 1) for c in range(3) for _ in range(bounds[c + 1] - bounds[c])]
+    plink_io.write_plink(tmp_path / "d", payload, [("F", f"s{i:05d}") for i in range(n)], chroms)
+    kw = dict(method="SH", precision=g.PREC_FP64, n_gpus=3, partition="tile", loco=loco, write_whole=loco, chunk_size=250)
+    engine.grm_run(tmp_path / "d", tmp_path / "direct", **kw)
+    monkeypatch.setenv("GELEX_B200_BED_RELAY", "1")
+    engine.grm_run(tmp_path / "d", tmp_path / "relay", **kw)
+    names = sorted(p.name for p in tmp_path.iterdir() if p.name.startswith("direct."))
+    assert len(names) == (8 if loco else 2)
+    for name in names:
+        assert (tmp_path / name.replace("direct.", "relay.")).read_bytes() == (tmp_path / name).read_bytes(), name
 
 
 @pytest.mark.gpu
