@@ -29,6 +29,27 @@ def test_library_exports_every_declared_symbol():
     assert set(_lib.EXPORTS) == set(syms)
 
 
+def test_header_is_plain_c_and_stage_calls_fail_loudly_without_gpu(tmp_path):
+    # the boundary is a C header: a C99 compiler takes it as is (what a cgo / ctypes / JNI binding would include)
+    import shutil
+    import subprocess
+
+    if shutil.which("gcc") is None:
+        pytest.skip("no C compiler")
+    src = tmp_path / "use.c"
+    src.write_text('#include "ggrm.h"\nint main(void) { ggrm_config_t c; (void)c; return sizeof(ggrm_config_t) == 120 ? 0 : 1; }\n')
+    r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", f"-I{ROOT / 'include'}", str(src), "-o", str(tmp_path / "use")],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert subprocess.run([str(tmp_path / "use")]).returncode == 0
+    if g.device_count() == 0:  # staging slots live in device memory: no device, no stage (and no host-memory stand-in)
+        lib = _lib.load()
+        st = ctypes.c_void_p()
+        assert lib.ggrm_stage_create(0, 1 << 20, 2, ctypes.byref(st)) == -6 and not st.value
+        assert b"no CPU fallback" in lib.ggrm_last_error(None)
+        assert lib.ggrm_stage_create(0, 0, 2, ctypes.byref(st)) == -1  # GGRM_ERR_INVALID_ARGUMENT before any device work
+
+
 def test_config_struct_layout_matches_header():
     # 8-byte aligned C layout of ggrm_config_t: 2*4 + 2*8 + 8 + 8 + 4*4 + 4(+4 pad) + 2*8 + 5*4(+4 pad) + 8 + 2*4
     assert ctypes.sizeof(_lib.Config) == 120
