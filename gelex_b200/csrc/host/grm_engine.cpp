@@ -78,7 +78,12 @@ struct BinFile {
     // create = truncate + size the file (one caller); otherwise open an existing, already sized file for writing
     void open(const fs::path& p, int64_t n, bool create, WriterMode mode = WriterMode::Pwrite) {
         path = p.string();
-        fd = ::open(path.c_str(), create ? (O_RDWR | O_CREAT | O_TRUNC) : O_RDWR, 0644);
+        const int extra = create ? (O_CREAT | O_TRUNC) : 0;
+        if (mode != WriterMode::Pwrite) fd = ::open(path.c_str(), O_RDWR | extra, 0644);  // a shared writable mapping needs read access too
+        if (fd < 0) {
+            mode = WriterMode::Pwrite;  // e.g. an existing write-only file: the reference only needs to write it, so do we
+            fd = ::open(path.c_str(), O_WRONLY | extra, 0644);
+        }
         if (fd < 0) throw FileOpenException(path + ": failed to open file");
         const int64_t bytes = n * (n + 1) / 2 * static_cast<int64_t>(sizeof(float));
         if (create && ::ftruncate(fd, static_cast<off_t>(bytes)) != 0)
