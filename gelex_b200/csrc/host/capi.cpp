@@ -2,6 +2,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <vector>
 
 #include "exceptions.h"
 #include "genotype_pipe.h"
@@ -296,6 +297,39 @@ extern "C" int64_t gelex_b200_relay_selftest(int n_chunks, int world, int slots,
         const int64_t bad = GrmEngine::relay_selftest(n_chunks, world, slots, chunk_bytes, fail_at_chunk);
         set_err(err, err_len, "");
         return bad;
+    } catch (...) {
+        return translate_exception(err, err_len);
+    }
+}
+
+// write_id_file (GrmIdWriter::write, grm_id_writer.cpp:41-54) through C: ids = n_ids canonical "FID<US>IID" strings, each NUL-terminated,
+// back to back.  For the reference's id-writer test cases (tests/test_grm_id_writer.cpp).
+extern "C" int gelex_b200_write_id_file(const char* path, const char* ids, int64_t n_ids, char* err, int err_len) {
+    try {
+        if (path == nullptr || (ids == nullptr && n_ids > 0) || n_ids < 0) throw ArgumentValidationException("null argument");
+        std::vector<std::string> v;
+        const char* p = ids;
+        for (int64_t i = 0; i < n_ids; ++i) {
+            v.emplace_back(p);
+            p += v.back().size() + 1;
+        }
+        write_id_file(path, v);
+        set_err(err, err_len, "");
+        return 0;
+    } catch (...) {
+        return translate_exception(err, err_len);
+    }
+}
+
+// format_bed_path (src/data/genotype/bed_path.cpp:26-40) through C: out receives the .bed path.
+extern "C" int gelex_b200_format_bed_path(const char* bfile, char* out, int out_len, char* err, int err_len) {
+    try {
+        if (bfile == nullptr || out == nullptr || out_len <= 0) throw ArgumentValidationException("null argument");
+        const std::string r = format_bed_path(bfile).string();
+        if (static_cast<int>(r.size()) >= out_len) throw ArgumentValidationException("output buffer too small");
+        std::memcpy(out, r.c_str(), r.size() + 1);
+        set_err(err, err_len, "");
+        return 0;
     } catch (...) {
         return translate_exception(err, err_len);
     }

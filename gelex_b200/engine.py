@@ -47,6 +47,8 @@ def load_host():
                                                C.c_char_p, C.c_int]
         h.gelex_b200_writer_selftest.argtypes = [C.c_char_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int),
                                                  C.c_char_p, C.c_int]
+        h.gelex_b200_write_id_file.argtypes = [C.c_char_p, C.c_char_p, C.c_int64, C.c_char_p, C.c_int]
+        h.gelex_b200_format_bed_path.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_int]
         h.gelex_b200_relay_selftest.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]
         h.gelex_b200_relay_selftest.restype = C.c_int64
         _host = h
@@ -251,3 +253,22 @@ def relay_selftest(n_chunks, world, slots, chunk_bytes=4096, fail_at_chunk=-1):
     if r < 0:
         raise EngineError(int(r), err.value.decode())
     return int(r)
+
+
+def write_id_file(path, ids):
+    """GrmIdWriter::write mirror: canonical 'FID\x1fIID' strings -> 'FID\tIID\n' lines."""
+    h = load_host()
+    err = C.create_string_buffer(2048)
+    blob = b"".join(i.encode() + b"\0" for i in ids)
+    st = h.gelex_b200_write_id_file(str(path).encode(), blob, len(ids), err, len(err))
+    if st != 0:
+        raise EngineError(st, err.value.decode())
+
+
+def format_bed_path(bfile):
+    h = load_host()
+    err, out = C.create_string_buffer(2048), C.create_string_buffer(4096)
+    st = h.gelex_b200_format_bed_path(str(bfile).encode(), out, len(out), err, len(err))
+    if st != 0:
+        raise EngineError(st, err.value.decode())
+    return out.value.decode()

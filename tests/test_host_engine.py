@@ -73,6 +73,42 @@ def test_bim_and_fam_cases_of_the_reference_loader_tests(tmp_path):
         assert p["items"] == [("add.chr1", 0, 2), ("add.chr2", 2, 3)]
 
 
+def test_id_writer_cases_of_the_reference_tests(tmp_path):
+    US = "\x1f"
+    p = tmp_path / "t.grm.id"
+    engine.write_id_file(p, [])  # test_grm_id_writer.cpp:118-133: empty list -> the file exists and is empty
+    assert p.exists() and p.stat().st_size == 0
+    engine.write_id_file(p, [f"FAM1{US}IND1"])  # :139-150
+    assert p.read_bytes() == b"FAM1\tIND1\n"
+    engine.write_id_file(p, [f"FAM1{US}IND1", f"FAM2{US}IND2", f"FAM3{US}IND3"])  # :152-168 (and: an existing file is truncated, :100-115)
+    assert p.read_bytes() == b"FAM1\tIND1\nFAM2\tIND2\nFAM3\tIND3\n"
+    engine.write_id_file(p, [f"FAM_A{US}IND_1", f"F.1-x y{US}I 2"])  # :170-186, :390-406: underscores, dots, dashes, spaces pass through
+    assert p.read_bytes() == b"FAM_A\tIND_1\nF.1-x y\tI 2\n"
+    for ids, msg in (([ "FAM1_IND1"], "canonical FID<US>IID format"), (["NOSPLIT"], "canonical FID<US>IID format"), ([""], "cannot be empty"),
+                     ([f"{US}IND1"], "non-empty FID and IID"), ([f"FAM1{US}"], "non-empty FID and IID")):  # :188-253
+        with pytest.raises(engine.EngineError, match="ArgumentValidationException: .*" + msg):
+            engine.write_id_file(p, ids)
+    ids = [f"FAM{i}{US}IND{i}" for i in range(10000)]  # :339-365
+    engine.write_id_file(p, ids)
+    lines = p.read_text().split("\n")
+    assert lines[-1] == "" and len(lines) == 10001 and lines[0] == "FAM0\tIND0" and lines[9999] == "FAM9999\tIND9999"
+    with pytest.raises(engine.EngineError, match="FileOpenException"):
+        engine.write_id_file(tmp_path / "missing_dir" / "x.id", ids[:1])
+
+
+def test_format_bed_path_cases_of_the_reference_tests(tmp_path):
+    bed = tmp_path / "cohort.bed"  # test_bed_path.cpp:37-78
+    bed.write_bytes(b"")
+    assert engine.format_bed_path(bed) == str(bed)
+    assert engine.format_bed_path(tmp_path / "cohort") == str(bed)
+    tricky = tmp_path / "my.bedsets"
+    tricky.mkdir()
+    (tricky / "cohort1.bed").write_bytes(b"")
+    assert engine.format_bed_path(tricky / "cohort1") == str(tricky / "cohort1.bed")
+    with pytest.raises(engine.EngineError, match=r"FileNotFoundException: .*missing_prefix\.bed: file not found$"):
+        engine.format_bed_path(tmp_path / "missing_prefix")
+
+
 def test_bed_validation_errors_precede_any_gpu_work(tmp_path):
     # reference tests/test_bed_pipe.cpp:154-257: bad magic, truncated file -> FileFormatException
     payload = plink_io.encode_matrix(np.zeros((8, 5)))
