@@ -1,0 +1,127 @@
+"""Differential test of the host side against the UNMODIFIED reference (oracle/_ref/gelex_ref, built by oracle/Makefile from
+/root/reference; skipped where that binary does not exist): random small PLINK triples with the quirks real files have - tab / space /
+repeated-space FAM delimiters, duplicate and unsorted sample IDs, short and long lines, blank lines, CRLF, missing final newline,
+chromosomes that re-appear, non-numeric positions, wrong BED magic, truncated or over-long payloads, empty files - go through
+`gelex grm` of the reference and through this repo's GrmEngine front half (everything up to the first device call; there is no
+GPU here, so a run that passes validation ends in the engine's "no CUDA device" error).
+
+Checked per case: the same inputs are accepted or rejected; a rejection carries the reference's exception message verbatim
+(so validation happens in the reference's ORDER: FAM, BIM line count, BED, BIM records - grm.cpp:36-40, bed_pipe.cpp:69-98,
+grm_engine.cpp:52-70); an accepted case plans the files the reference wrote (names incl. `chr<NAME>` of re-appearing chromosomes),
+the same matrix size n(n+1)/2 (sort + de-duplicate of the IDs), and the same `.id` rows in the same order."""
+import random
+import shutil
+import subprocess
+from pathlib import Path
+
+import pytest
+
+from gelex_b200 import engine
+
+REF = Path(__file__).resolve().parent.parent / "oracle" / "_ref" / "gelex_ref"
+pytestmark = pytest.mark.skipif(not REF.exists(), reason="oracle/_ref/gelex_ref not built (needs /root/reference)")
+
+
+def make_case(rng, d: Path):
+    n, m = rng.randint(1, 9), rng.randint(1, 14)
+    fam_delim = rng.choice(["\t", " ", " ", "  "])
+    lines = []
+    for _ in range(n):
+        cols = [rng.choice(["f1", "f2", "F", "fam_a", "a.b", "10", "9"]), rng.choice(["i1", "i2", "s01", "s1", "x_y", "2", "11"]), "0", "0",
+                str(rng.randint(0, 2)), "-9"]
+        q = rng.random()
+        if q < 0.04:
+            cols = cols[:rng.randint(0, 1)]
+        elif q < 0.08:
+            cols = cols[:rng.randint(2, 5)]
+        elif q < 0.12:
+            cols += ["extra"]
+        line = fam_delim.join(cols)
+        if rng.random() < 0.05:
+            line = " " + line
+        if rng.random() < 0.05:
+            line += fam_delim
+        lines.append(line)
+    if rng.random() < 0.06:
+        lines.insert(rng.randint(0, len(lines)), "")
+    eol = "\r\n" if rng.random() < 0.06 else "\n"
+    fam = eol.join(lines) + (eol if rng.random() < 0.85 else "")
+    if rng.random() < 0.03:
+        fam = ""
+    bim_delim = rng.choice(["\t", "\t", " "])
+    c, bl = rng.choice(["1", "2", "X", "chr1", "23"]), []
+    for j in range(m):
+        if rng.random() < 0.3:
+            c = rng.choice(["1", "2", "3", "X", "chr1", "23", "MT"])
+        cols = [c, f"rs{j}", "0", str(100 + j), "A", "G"]
+        q = rng.random()
+        if q < 0.03:
+            cols = cols[:rng.randint(1, 5)]
+        elif q < 0.05:
+            cols += ["x"]
+        elif q < 0.07:
+            cols[3] = "notint"
+        bl.append(bim_delim.join(cols))
+    if rng.random() < 0.04:
+        bl.insert(rng.randint(0, len(bl)), "")
+    bim = "\n".join(bl) + ("\n" if rng.random() < 0.9 else "")
+    if rng.random() < 0.03:
+        bim = ""
+    payload = bytes(rng.randrange(256) for _ in range(m * ((n + 3) // 4)))
+    magic = bytes([0x6C, 0x1B, 0x01])
+    q = rng.random()
+    if q < 0.03:
+        magic = bytes([0x6C, 0x1B, 0x00])  # sample-major
+    elif q < 0.05:
+        magic = bytes([0x6C, 0x1A, 0x01])
+    elif q < 0.08:
+        payload = payload[:-1]
+    elif q < 0.10:
+        payload += b"\0\0"
+    (d / "t.fam").write_text(fam, newline="")
+    (d / "t.bim").write_text(bim, newline="")
+    (d / "t.bed").write_bytes(magic + payload)
+    return fam
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_front_half_agrees_with_the_reference_on_quirky_inputs(tmp_path, seed):
+    rng = random.Random(seed)
+    accepted = rejected = 0
+    for k in range(70):
+        d = tmp_path / f"c{k}"
+        d.mkdir()
+        fam = make_case(rng, d)
+        loco, mode = rng.random() < 0.5, rng.choice(["A", "D", "AD"])
+        r = subprocess.run([str(REF), "grm", str(d / "t"), str(d / "ref"), "1", mode, "1" if loco else "0", "5", "1"], capture_output=True, text=True)
+        ref_files = sorted(p.name for p in d.iterdir() if p.name.startswith("ref."))
+        try:
+            engine.grm_run(d / "t", d / "mine", method="SH", mode=mode, loco=loco, chunk_size=5)
+            mine_err = None  # (a GPU is present and the run went through)
+        except engine.EngineError as e:
+            mine_err = None if "no CUDA device" in e.message else e.message
+        ctx = f"seed {seed} case {k}: fam={fam!r} bim={(d / 't.bim').read_text()!r} loco={loco} mode={mode}"
+        assert (r.returncode != 0) == (mine_err is not None), f"{ctx}\nreference: rc={r.returncode} {r.stderr!r}\nhere: {mine_err!r}"
+        if r.returncode != 0:
+            rejected += 1
+            assert mine_err.split(": ", 1)[1] == r.stderr.strip().replace("error: ", "", 1), ctx  # "<ExceptionName>: <reference message>"
+            shutil.rmtree(d)
+            continue
+        accepted += 1
+        p = engine.plan(d / "t", mode=mode, loco=loco)
+        assert sorted({f"ref.{name}.{ext}" for name, _, _ in p["items"] for ext in ("bin", "id")}) == ref_files, ctx
+        for f in ref_files:
+            if f.endswith(".bin"):
+                assert (d / f).stat().st_size == p["n_out"] * (p["n_out"] + 1) // 2 * 4, ctx
+        # .id rows: row t = the FAM line i with raw_to_out[i] == t
+        delim = "\t" if "\t" in fam.split("\n")[0] else " "
+        raw = [ln for ln in fam.split("\n") if ln != ""]
+        assert len(raw) == p["n_raw"], ctx
+        rows = {}
+        for i, ln in enumerate(raw):
+            toks = [t for t in ln.rstrip("\r").split(delim) if t != ""]
+            if p["raw_to_out"][i] >= 0:
+                rows[int(p["raw_to_out"][i])] = toks[0] + "\t" + toks[1] + "\n"
+        assert "".join(rows[t] for t in range(p["n_out"])) == (d / [f for f in ref_files if f.endswith(".id")][0]).read_text(), ctx
+        shutil.rmtree(d)
+    assert accepted >= 15 and rejected >= 10  # the generator exercises both sides
