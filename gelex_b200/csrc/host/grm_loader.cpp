@@ -12,6 +12,8 @@
 #include "exceptions.h"
 #include "plink_meta.h"
 
+#include <format>
+
 namespace fs = std::filesystem;
 
 namespace gelex::b200 {
@@ -30,14 +32,15 @@ GrmLoader::GrmLoader(const fs::path& prefix, int device)
     : bin_path_(prefix.string() + ".bin"), id_path_(prefix.string() + ".id"), type_(type_of(prefix.string())), device_(device) {
     // load_sample_ids, grm_loader.cpp:58-95: "FID\tIID" per line, empty lines skipped
     {
-        if (!fs::exists(id_path_)) throw FileNotFoundException(id_path_.string() + ": not found");
-        std::ifstream f(id_path_);
-        if (!f.is_open()) throw FileOpenException(id_path_.string() + ": failed to open file");
+        std::ifstream f = open_text(id_path_);
         std::string line;
         while (std::getline(f, line)) {
             if (line.empty()) continue;
             const size_t tab = line.find('\t');
             if (tab == std::string::npos) throw FileFormatException(id_path_.string() + ": invalid ID line '" + line + "' (expected FID and IID)");
+            // make_sample_id, include/gelex/types/sample_id.h:32-45
+            if (tab == 0) throw ArgumentValidationException("FID cannot be empty");
+            if (tab + 1 == line.size()) throw ArgumentValidationException("IID cannot be empty");
             sample_ids_.push_back(line.substr(0, tab) + kSampleIdSeparator + line.substr(tab + 1));
         }
         if (sample_ids_.empty()) throw FileFormatException(id_path_.string() + ": no sample IDs found");
@@ -52,6 +55,10 @@ GrmLoader::GrmLoader(const fs::path& prefix, int device)
         throw FileOpenException(bin_path_.string() + ": failed to mmap file");
     }
     map_size_ = static_cast<size_t>(st.st_size);
+    if (map_size_ == 0) {  // mio cannot map an empty file: the reference reports that before it compares sizes
+        ::close(fd);
+        throw FileOpenException(bin_path_.string() + ": failed to mmap file");
+    }
     const size_t expected = static_cast<size_t>(num_samples_) * (static_cast<size_t>(num_samples_) + 1) / 2 * sizeof(float);
     if (map_size_ != expected) {
         ::close(fd);
@@ -141,8 +148,8 @@ DenseMatrix LocoGRMLoader::load_loco_grm(const fs::path& chr_grm_prefix, const I
     const double k_i = n_chr > 0 ? chr.filtered_trace(chr_map) / static_cast<double>(n_chr) : 0.0;
     const double k_loco = k_whole_ - k_i;
     if (k_loco <= 0)
-        throw InvalidInputException("LOCO error: Chromosome GRM denominator (" + std::to_string(k_i) + ") is greater than or equal to Whole GRM denominator (" +
-                                    std::to_string(k_whole_) + ")");
+        throw InvalidInputException(std::format("LOCO error: Chromosome GRM denominator ({}) is greater than or equal to Whole GRM denominator ({})", k_i,
+                                                k_whole_));  // "{}" of a double: shortest round-trip digits, as the reference prints them
     // the two files are aligned through the SAME id_map (each by its own .id list), as in the reference
     if (n_chr != n_target_) throw InvalidInputException("LOCO error: " + bin_path.string() + " maps to a different matrix size than the whole-genome GRM");
     DenseMatrix out;

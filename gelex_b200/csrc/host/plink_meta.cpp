@@ -16,8 +16,6 @@ namespace fs = std::filesystem;
 
 namespace gelex::b200 {
 
-namespace {
-
 // Same checks, in the same order, with the same messages as the reference's open_file (include/gelex/io/parser.h:48-93).
 std::ifstream open_text(const fs::path& path) {
     if (fs::is_directory(path)) throw FileOpenException(path.string() + ": is a directory, not a regular file");
@@ -32,6 +30,8 @@ std::ifstream open_text(const fs::path& path) {
     }
     return f;
 }
+
+namespace {
 
 char detect_delimiter(std::ifstream& f) {
     std::string probe;

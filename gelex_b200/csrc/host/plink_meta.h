@@ -4,6 +4,7 @@
 #pragma once
 #include <cstdint>
 #include <filesystem>
+#include <fstream>
 #include <string>
 #include <utility>
 #include <vector>
@@ -14,6 +15,10 @@ constexpr char kSampleIdSeparator = '\x1F';  // include/gelex/types/sample_id.h:
 
 // "<prefix>" or "<prefix>.bed" -> existing .bed path (src/data/genotype/bed_path.cpp:25-39; FileNotFoundException).
 std::filesystem::path format_bed_path(const std::string& bfile);
+
+// open_file<std::ifstream>(path, std::ios::in) of the reference (include/gelex/io/parser.h:48-93): directory, missing, unreadable and
+// EMPTY files are rejected here, with the reference's exception types and messages.
+std::ifstream open_text(const std::filesystem::path& path);
 
 // Number of lines, a trailing line without '\n' counts (src/io/parser.cpp:30-61).
 size_t count_total_lines(const std::filesystem::path& path);

@@ -9,11 +9,13 @@ Checked per case: the same inputs are accepted or rejected; a rejection carries 
 (so validation happens in the reference's ORDER: FAM, BIM line count, BED, BIM records - grm.cpp:36-40, bed_pipe.cpp:69-98,
 grm_engine.cpp:52-70); an accepted case plans the files the reference wrote (names incl. `chr<NAME>` of re-appearing chromosomes),
 the same matrix size n(n+1)/2 (sort + de-duplicate of the IDs), and the same `.id` rows in the same order."""
+import os
 import random
 import shutil
 import subprocess
 from pathlib import Path
 
+import numpy as np
 import pytest
 
 from gelex_b200 import engine
@@ -125,3 +127,111 @@ def test_front_half_agrees_with_the_reference_on_quirky_inputs(tmp_path, seed):
         assert "".join(rows[t] for t in range(p["n_out"])) == (d / [f for f in ref_files if f.endswith(".id")][0]).read_text(), ctx
         shutil.rmtree(d)
     assert accepted >= 15 and rejected >= 10  # the generator exercises both sides
+
+
+def _reference(cmd):
+    r = subprocess.run([str(REF)] + [str(c) for c in cmd], capture_output=True)  # bytes: '\r' inside a message must survive
+    return r.returncode, r.stderr.decode().rstrip("\n").replace("error: ", "", 1)
+
+
+def _here(call):
+    """None when validation passed (the call then needs a GPU, or ran on one), else '<ExceptionName>: message'."""
+    try:
+        call()
+        return None
+    except engine.EngineError as e:
+        return None if "no CUDA device" in e.message else e.message
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_grm_loader_rejects_what_the_reference_rejects(tmp_path, seed):
+    # GrmLoader(prefix) on damaged .id / .bin pairs (grm_loader.cpp:48-123): lines without a tab, empty FID or IID, three columns,
+    # blank lines, CRLF, empty and missing files, payloads one sample too long / short or cut mid-float
+    rng = random.Random(seed)
+    rejected = 0
+    for k in range(150):
+        d = tmp_path / f"l{k}"
+        d.mkdir()
+        n = rng.randint(0, 6)
+        lines = []
+        for i in range(n):
+            cols = [rng.choice(["F1", "F2", "a b", "F3"] * 3 + [""]), rng.choice(["s1", "s2", "s3", "x"]) + str(i if rng.random() < 0.8 else 0)]
+            q = rng.random()
+            if q < 0.06:
+                cols = cols[:1]
+            elif q < 0.12:
+                cols += ["z"]
+            lines.append(("\t" if rng.random() < 0.9 else " ").join(cols))
+        if rng.random() < 0.08:
+            lines.insert(rng.randint(0, len(lines)), "")
+        ids = "\n".join(lines) + ("\n" if rng.random() < 0.9 else "")
+        if rng.random() < 0.05 and lines:
+            ids = ids.replace("\n", "\r\n")
+        nn = n + 1 if rng.random() < 0.1 else (max(0, n - 1) if rng.random() < 0.1 else n)
+        b = np.array([rng.uniform(0.5, 2.0) for _ in range(nn * (nn + 1) // 2)], dtype=np.float32).tobytes()
+        q = rng.random()
+        if q < 0.06:
+            b = b[:-1]
+        elif q < 0.1:
+            b += b"\0\0\0"
+        if rng.random() < 0.95:
+            (d / "g.bin").write_bytes(b)
+        if rng.random() < 0.95:
+            (d / "g.id").write_text(ids, newline="")
+        rc, ref_msg = _reference(["load", d / "g", d / "ref.out"])
+        mine = _here(lambda: engine.load_grm(d / "g"))
+        ctx = f"seed {seed} case {k}: ids={ids!r} bin bytes={len(b)}"
+        assert (rc != 0) == (mine is not None), f"{ctx}\nreference: {ref_msg!r}\nhere: {mine!r}"
+        if rc != 0:
+            rejected += 1
+            assert mine.split(": ", 1)[1] == ref_msg, ctx
+        shutil.rmtree(d)
+    assert rejected >= 30
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_loco_loader_rejects_what_the_reference_rejects(tmp_path, seed):
+    # LocoGRMLoader(whole, id_map).load_loco_grm(chr, id_map) (loco_grm_loader.cpp:27-77): chromosome file with other / fewer / more /
+    # reordered samples, damaged payloads, missing files, and k_chr >= k_whole - the denominators in that message are the
+    # reference's own digits, so trace / n is computed the same way on the host
+    rng = random.Random(seed)
+    rejected = 0
+
+    def write(prefix, ids, scale, n_bin=None, corrupt=False):
+        n = len(ids) if n_bin is None else n_bin
+        v = [(scale if i == j else 0.1 * scale) * rng.uniform(0.9, 1.1) for i in range(n) for j in range(i + 1)]
+        b = np.array(v, dtype=np.float32).tobytes()
+        Path(str(prefix) + ".bin").write_bytes(b[:-2] if corrupt else b)
+        Path(str(prefix) + ".id").write_text("".join(f"{f}\t{i}\n" for f, i in ids))
+
+    for k in range(150):
+        d = tmp_path / f"o{k}"
+        d.mkdir()
+        ids = [(rng.choice(["F1", "F2"]), f"s{i}") for i in range(rng.randint(1, 6))]
+        cids = list(ids)
+        q = rng.random()
+        if q < 0.15:
+            rng.shuffle(cids)
+        elif q < 0.3:
+            cids = cids[:-1] if len(cids) > 1 else cids
+        elif q < 0.4:
+            cids = cids + [("F9", "new")]
+        elif q < 0.5:
+            cids[0] = ("F9", "other")
+        if rng.random() < 0.05:
+            cids = cids + [cids[0]]
+        write(d / "w", ids, 10.0, corrupt=rng.random() < 0.05)
+        write(d / "c", cids, rng.choice([1.0, 1.0, 1.0, 10.0, 12.0]), n_bin=(len(cids) + 1 if rng.random() < 0.05 else None), corrupt=rng.random() < 0.05)
+        if rng.random() < 0.04:
+            os.unlink(d / "c.bin")
+        if rng.random() < 0.04:
+            os.unlink(d / "c.id")
+        rc, ref_msg = _reference(["loco", d / "w", d / "c", d / "ref.out"])
+        mine = _here(lambda: engine.load_grm(d / "w", chr_prefix=d / "c", id_map={fi: t for t, fi in enumerate(ids)}))
+        ctx = f"seed {seed} case {k}: ids={ids} chr ids={cids}"
+        assert (rc != 0) == (mine is not None), f"{ctx}\nreference: {ref_msg!r}\nhere: {mine!r}"
+        if rc != 0:
+            rejected += 1
+            assert mine.split(": ", 1)[1] == ref_msg, ctx
+        shutil.rmtree(d)
+    assert rejected >= 30
