@@ -235,3 +235,48 @@ def test_loco_loader_rejects_what_the_reference_rejects(tmp_path, seed):
             assert mine.split(": ", 1)[1] == ref_msg, ctx
         shutil.rmtree(d)
     assert rejected >= 30
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_oracle_agrees_with_the_reference_on_random_small_inputs(tmp_path, seed):
+    # The CPU oracle (oracle/grm_oracle.c, what the GPU parity tests compare against) beside `gelex grm` of the unmodified reference:
+    # random small matrices with the cases the reference's own GRM tests leave out (missing data through GRM::compute,
+    # n not a multiple of 4, duplicate and unsorted FAM ids) plus monomorphic, all-heterozygous and all-missing SNPs (the last one
+    # poisons the matrix with NaN in the reference, and must here too), every code policy, additive and dominance, ragged chunks.
+    import oracle_lib as o
+    import plink_io
+
+    rng = np.random.default_rng(seed)
+    for k in range(24):
+        n_raw, m = int(rng.integers(1, 24)), int(rng.integers(1, 40))
+        p = rng.uniform(0.02, 0.98, size=m)
+        geno = rng.binomial(2, p, size=(n_raw, m)).astype(np.float64)
+        geno[rng.random((n_raw, m)) < rng.choice([0.0, 0.05, 0.4])] = np.nan
+        for j in range(m):
+            q = rng.random()
+            if q < 0.06:
+                geno[:, j] = rng.integers(0, 3)  # monomorphic
+            elif q < 0.09:
+                geno[:, j] = 1.0                 # all heterozygous
+            elif q < 0.11:
+                geno[:, j] = np.nan              # all missing
+        fam = [(f"f{int(rng.integers(0, 3))}", f"s{int(rng.integers(0, max(2, n_raw)))}" if rng.random() < 0.3 else f"s{i:03d}") for i in range(n_raw)]
+        order = rng.permutation(n_raw)
+        fam = [fam[i] for i in order]
+        payload = plink_io.encode_matrix(geno)
+        plink_io.write_plink(tmp_path / f"t{k}", payload, fam, ["1"] * m, fam_delim=str(rng.choice(["\t", " "])))
+        ids, r2o = plink_io.sample_order(fam)
+        method, kind, chunk = int(rng.integers(1, 9)), int(rng.integers(0, 2)), int(rng.choice([1, 3, 7, 10000]))
+        rc, msg = _reference(["grm", tmp_path / f"t{k}", tmp_path / f"r{k}", method, "AD"[kind], 0, chunk, 1])
+        assert rc == 0, msg
+        ref = plink_io.read_bin(tmp_path / f"r{k}.{('add', 'dom')[kind]}.bin", len(ids))
+        G, _, _ = o.grm_compute(payload, n_raw, method, kind, chunk=chunk, n_out=len(ids), raw_to_out=r2o)
+        got = o.pack_lower_f32(G)
+        ctx = f"seed {seed} case {k}: n_raw={n_raw} n={len(ids)} m={m} method={method} kind={kind} chunk={chunk}"
+        assert np.array_equal(np.isnan(got), np.isnan(ref)), ctx
+        ok = ~np.isnan(ref)
+        # float32 file values: identical after rounding, or one float32 ulp apart (BLAS summation order); entries that cancel to zero
+        # carry the FP64 rounding noise of the sum (|x| ~ 1e-17 against 0 exactly), hence the floor relative to the largest entry
+        floor = 1e-14 * float(np.max(np.abs(ref[ok]))) if ok.any() else 0.0
+        assert np.all(np.abs(got[ok].astype(np.float64) - ref[ok]) <= np.spacing(np.abs(ref[ok])) + floor), ctx
+        assert (tmp_path / f"r{k}.{('add', 'dom')[kind]}.id").read_text() == "".join(s.replace("\x1f", "\t") + "\n" for s in ids), ctx
