@@ -5,6 +5,8 @@ Tolerances (north star): decode, counts, allele frequencies bit-exact; GRM entri
   FP64 path <= 1e-10;  16-bit/FP32 path <= 1e-4 at the named shapes (m >= 50 000).  The rounding error of 16-bit
   operands averages out as 1/sqrt(m), so for the small m used here the bound is scaled: tol16(m) = 1e-4*sqrt(5e4/m).
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -641,3 +643,44 @@ def test_guard_bands_stay_intact_over_ragged_shapes(monkeypatch):
         with pytest.raises(g.GrmError) as e:
             acc.finish()
         assert "guard band of device buffer 'dense 2-bit chunk'" in e.value.message and "overwritten at byte offset" in e.value.message
+
+
+@pytest.mark.skipif(os.environ.get("GELEX_B200_TEST_UNVERIFIED") != "1",
+                    reason="added after the round's GPU minutes were spent: opt in with GELEX_B200_TEST_UNVERIFIED=1 (tools/r02_first_run.sh)")
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_fp64_path_agrees_with_oracle_on_random_small_inputs(seed):
+    # the generator of tests/test_reference_differential.py::test_oracle_agrees_with_the_reference_on_random_small_inputs (where the
+    # oracle is compared with the unmodified reference on the same cases): tiny ragged shapes, heavy missingness, duplicate and
+    # unsorted ids, monomorphic / all-heterozygous / all-missing SNPs, every policy, ragged device slabs
+    rng = np.random.default_rng(seed)
+    for k in range(24):
+        n_raw, m = int(rng.integers(1, 24)), int(rng.integers(1, 40))
+        p = rng.uniform(0.02, 0.98, size=m)
+        geno = rng.binomial(2, p, size=(n_raw, m)).astype(np.float64)
+        geno[rng.random((n_raw, m)) < rng.choice([0.0, 0.05, 0.4])] = np.nan
+        for j in range(m):
+            q = rng.random()
+            if q < 0.06:
+                geno[:, j] = rng.integers(0, 3)
+            elif q < 0.09:
+                geno[:, j] = 1.0
+            elif q < 0.11:
+                geno[:, j] = np.nan
+        fam = [(f"f{int(rng.integers(0, 3))}", f"s{int(rng.integers(0, max(2, n_raw)))}" if rng.random() < 0.3 else f"s{i:03d}") for i in range(n_raw)]
+        fam = [fam[i] for i in rng.permutation(n_raw)]
+        rng.choice(["\t", " "])  # (keeps the stream in step with the CPU test's generator)
+        payload = plink_io.encode_matrix(geno)
+        ids, r2o = plink_io.sample_order(fam)
+        method, kind, chunk = int(rng.integers(1, 9)), int(rng.integers(0, 2)), int(rng.choice([1, 3, 7, 10000]))
+        G, _, freqs = o.grm_compute(payload, n_raw, method, kind, chunk=chunk, n_out=len(ids), raw_to_out=r2o)
+        want = o.pack_lower_f64(G)
+        acc = run_gpu(payload, n_raw, m, method, (kind,), g.PREC_FP64, chunk=64, push=max(1, chunk if chunk < 100 else 13), n_out=len(ids), raw_to_out=r2o)
+        got, _ = acc.fetch(kind, g.GROUP_WHOLE, dtype=np.float64)
+        f = acc.snp_stats(0, m)[4]
+        acc.close()
+        ctx = f"seed {seed} case {k}: n_raw={n_raw} n={len(ids)} m={m} method={method} kind={kind}"
+        assert np.array_equal(f, freqs), ctx  # allele frequencies: bit-exact
+        assert np.array_equal(np.isnan(got), np.isnan(want)), ctx
+        ok = ~np.isnan(want)
+        if ok.any():
+            assert np.max(np.abs(got[ok] - want[ok])) <= 1e-10 * max(1.0, float(np.max(np.abs(want[ok])))), ctx
