@@ -1,6 +1,7 @@
 """Differential test of the host side against the UNMODIFIED reference (oracle/_ref/gelex_ref, built by oracle/Makefile from
 /root/reference; skipped where that binary does not exist): random small PLINK triples with the quirks real files have - tab / space /
-repeated-space FAM delimiters, duplicate and unsorted sample IDs, short and long lines, blank lines, CRLF, missing final newline,
+repeated-space / mixed FAM delimiters, duplicate and unsorted sample IDs, short and long lines, blank and whitespace-only lines, '#'
+lines, non-ASCII ids, CRLF, missing final newline,
 chromosomes that re-appear, non-numeric positions, wrong BED magic, truncated or over-long payloads, empty files - go through
 `gelex grm` of the reference and through this repo's GrmEngine front half (everything up to the first device call; there is no
 GPU here, so a run that passes validation ends in the engine's "no CUDA device" error).
@@ -43,6 +44,14 @@ def make_case(rng, d: Path):
             line = " " + line
         if rng.random() < 0.05:
             line += fam_delim
+        if rng.random() < 0.04:
+            line = line.replace(fam_delim, "\t" if fam_delim != "\t" else " ", 1)  # the other delimiter inside a line
+        if rng.random() < 0.03:
+            line = "   "
+        if rng.random() < 0.03:
+            line = "# " + line
+        if rng.random() < 0.03:
+            line = line.replace("s", "\u00e9", 1)
         lines.append(line)
     if rng.random() < 0.06:
         lines.insert(rng.randint(0, len(lines)), "")
@@ -66,7 +75,10 @@ def make_case(rng, d: Path):
         bl.append(bim_delim.join(cols))
     if rng.random() < 0.04:
         bl.insert(rng.randint(0, len(bl)), "")
-    bim = "\n".join(bl) + ("\n" if rng.random() < 0.9 else "")
+    beol = "\r\n" if rng.random() < 0.08 else "\n"
+    if rng.random() < 0.05 and bl:
+        bl[rng.randrange(len(bl))] = "  "
+    bim = beol.join(bl) + (beol if rng.random() < 0.9 else "")
     if rng.random() < 0.03:
         bim = ""
     payload = bytes(rng.randrange(256) for _ in range(m * ((n + 3) // 4)))
@@ -90,12 +102,13 @@ def make_case(rng, d: Path):
 def test_front_half_agrees_with_the_reference_on_quirky_inputs(tmp_path, seed):
     rng = random.Random(seed)
     accepted = rejected = 0
-    for k in range(70):
+    for k in range(90):
         d = tmp_path / f"c{k}"
         d.mkdir()
         fam = make_case(rng, d)
         loco, mode = rng.random() < 0.5, rng.choice(["A", "D", "AD"])
-        r = subprocess.run([str(REF), "grm", str(d / "t"), str(d / "ref"), "1", mode, "1" if loco else "0", "5", "1"], capture_output=True, text=True)
+        r = subprocess.run([str(REF), "grm", str(d / "t"), str(d / "ref"), "1", mode, "1" if loco else "0", "5", "1"], capture_output=True)
+        ref_msg = r.stderr.decode().rstrip("\n").replace("error: ", "", 1)  # bytes: a '\r' inside a message must survive
         ref_files = sorted(p.name for p in d.iterdir() if p.name.startswith("ref."))
         try:
             engine.grm_run(d / "t", d / "mine", method="SH", mode=mode, loco=loco, chunk_size=5)
@@ -103,10 +116,10 @@ def test_front_half_agrees_with_the_reference_on_quirky_inputs(tmp_path, seed):
         except engine.EngineError as e:
             mine_err = None if "no CUDA device" in e.message else e.message
         ctx = f"seed {seed} case {k}: fam={fam!r} bim={(d / 't.bim').read_text()!r} loco={loco} mode={mode}"
-        assert (r.returncode != 0) == (mine_err is not None), f"{ctx}\nreference: rc={r.returncode} {r.stderr!r}\nhere: {mine_err!r}"
+        assert (r.returncode != 0) == (mine_err is not None), f"{ctx}\nreference: rc={r.returncode} {ref_msg!r}\nhere: {mine_err!r}"
         if r.returncode != 0:
             rejected += 1
-            assert mine_err.split(": ", 1)[1] == r.stderr.strip().replace("error: ", "", 1), ctx  # "<ExceptionName>: <reference message>"
+            assert mine_err.split(": ", 1)[1] == ref_msg, ctx  # "<ExceptionName>: <reference message>"
             shutil.rmtree(d)
             continue
         accepted += 1
@@ -126,7 +139,7 @@ def test_front_half_agrees_with_the_reference_on_quirky_inputs(tmp_path, seed):
                 rows[int(p["raw_to_out"][i])] = toks[0] + "\t" + toks[1] + "\n"
         assert "".join(rows[t] for t in range(p["n_out"])) == (d / [f for f in ref_files if f.endswith(".id")][0]).read_text(), ctx
         shutil.rmtree(d)
-    assert accepted >= 15 and rejected >= 10  # the generator exercises both sides
+    assert accepted >= 8 and rejected >= 10  # the generator exercises both sides
 
 
 def _reference(cmd):
