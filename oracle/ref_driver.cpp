@@ -14,6 +14,9 @@
 //   loco    <whole_prefix> <chr_prefix> <out.bin>
 //           -> LocoGRMLoader arithmetic (src/data/grm/loco_grm_loader.cpp:62-76) dumped as doubles
 //   load    <prefix> <out.bin>  -> GrmLoader::load (normalised, src/data/grm/grm_loader.cpp:125-165)
+//   pipe    <bfile> <out_prefix> <method> <A|D> <chunk>
+//           -> GenotypePipe(bed, SampleManager::create_finalized(bed), out_prefix).process<GT>(method, chunk)
+//              (include/gelex/data/genotype/genotype_pipe.h:55-89): writes <out_prefix>.bmat and <out_prefix>.snpstats
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -30,6 +33,8 @@
 #include "ref_shim/cblas.h"
 
 #include "gelex/data/genotype/bed_pipe.h"
+#include "gelex/data/genotype/genotype_pipe.h"
+#include "gelex/infra/logger.h"
 #include "gelex/data/genotype/genotype_processor.h"
 #include "gelex/data/genotype/sample_manager.h"
 #include "gelex/data/grm/grm.h"
@@ -41,6 +46,16 @@ extern "C" void scipy_openblas_set_num_threads(int) __attribute__((weak));
 extern "C" char* scipy_openblas_get_config(void) __attribute__((weak));
 extern "C" void openblas_set_num_threads(int) __attribute__((weak));
 extern "C" char* openblas_get_config(void) __attribute__((weak));
+
+// gelex::logging::get() without spdlog (oracle/ref_shim/spdlog/logger.h): the genotype sinks log an error line before they throw.
+namespace gelex::logging
+{
+std::shared_ptr<spdlog::logger>& get()
+{
+    static std::shared_ptr<spdlog::logger> l = std::make_shared<spdlog::logger>();
+    return l;
+}
+}  // namespace gelex::logging
 
 namespace
 {
@@ -234,6 +249,34 @@ int cmd_loco(int argc, char** argv)
     return f.good() ? 0 : 1;
 }
 
+int cmd_pipe(int argc, char** argv)
+{
+    if (argc < 7) { return 2; }
+    std::string bed_path = std::string(argv[2]) + ".bed";
+    auto method = method_of(argv[4]);
+    bool add = std::string(argv[5]) != "D";
+    size_t chunk = static_cast<size_t>(std::atol(argv[6]));
+    // process() ends in finalize(), which maps the files it has just written through GenotypeMap while the two writers are still
+    // open: with outputs smaller than the stream buffers nothing has reached the file yet and the unmodified reference throws
+    // "Failed to read scalar: rows" there.  Both files are complete once the pipe is destroyed (the writers flush), so that
+    // exception is reported, not fatal; constructor errors (existing outputs, bad inputs) propagate as they are.
+    std::string finalize_error;
+    {
+        gelex::GenotypePipe pipe(bed_path, gelex::SampleManager::create_finalized(bed_path), argv[3]);
+        try
+        {
+            if (add) { pipe.process<gelex::GeneticEffectType::Add>(method, chunk); }
+            else { pipe.process<gelex::GeneticEffectType::Dom>(method, chunk); }
+        }
+        catch (const std::exception& e)
+        {
+            finalize_error = e.what();
+        }
+    }
+    std::printf("{\"cmd\":\"pipe\",\"finalize_error\":\"%s\"}\n", finalize_error.c_str());
+    return 0;
+}
+
 int cmd_load(int argc, char** argv)
 {
     if (argc < 4) { return 2; }
@@ -251,7 +294,7 @@ int main(int argc, char** argv)
 {
     if (argc < 2)
     {
-        std::fprintf(stderr, "usage: gelex_ref grm|stages|chunk|process|loco|load ...\n");
+        std::fprintf(stderr, "usage: gelex_ref grm|stages|chunk|process|loco|load|pipe ...\n");
         return 2;
     }
     try
@@ -263,6 +306,7 @@ int main(int argc, char** argv)
         if (c == "process") { return cmd_process(argc, argv); }
         if (c == "loco") { return cmd_loco(argc, argv); }
         if (c == "load") { return cmd_load(argc, argv); }
+        if (c == "pipe") { return cmd_pipe(argc, argv); }
         std::fprintf(stderr, "unknown command %s\n", c.c_str());
         return 2;
     }

@@ -11,6 +11,8 @@ Fixtures (all small):
   tiny_loaders.npz        GrmLoader::load and LocoGRMLoader::load_loco_grm outputs
   dense.bed/.bim/.fam     40 samples already in sorted order (dense decode path), 50 SNPs; dense_chunks.npz, dense_SH_add.bin
   process_vectors.json    per-column process() outputs for the columns used in the reference's own unit tests
+  tiny_pipe_<tag>.bmat/.snpstats   GenotypePipe::process<GT> outputs on the tiny fixture (`python tests/golden/make_golden.py pipe`
+                          regenerates only these): OSH add chunk 25, SH dom chunk 7, OC dom chunk 40, S add chunk 33
 """
 import json
 import subprocess
@@ -141,5 +143,24 @@ def main():
     print("golden fixtures written to", HERE)
 
 
+PIPE_CASES = [("OSH", 3, "A", 25), ("SH", 1, "D", 7), ("OC", 8, "D", 40), ("S", 5, "A", 33)]
+
+
+def make_pipe():
+    """GenotypePipe outputs of the unmodified reference (ref_driver `pipe`).  Its process() ends by mapping the files it has just
+    written while the writers are still open, which throws on outputs this small ("Failed to read scalar: rows"); the files are
+    complete once the pipe is destroyed, and the driver reports that exception instead of failing."""
+    for tag, method, kind, chunk in PIPE_CASES:
+        prefix = HERE / f"tiny_pipe_{tag}.{'add' if kind == 'A' else 'dom'}"
+        for ext in (".bmat", ".snpstats"):
+            Path(str(prefix) + ext).unlink(missing_ok=True)
+        info = json.loads(run("pipe", HERE / "tiny", prefix, method, kind, chunk).strip().splitlines()[-1])
+        print(prefix.name, info)
+
+
 if __name__ == "__main__":
-    main()
+    if sys.argv[1:] == ["pipe"]:
+        make_pipe()
+    else:
+        main()
+        make_pipe()

@@ -3,6 +3,7 @@ CPU-only parts run everywhere; the end-to-end file parity tests need a B200 and 
 import os
 import shutil
 import subprocess
+from pathlib import Path
 
 import numpy as np
 import pytest
@@ -550,6 +551,29 @@ def test_genotype_export_files_match_reference_layout(golden_dir, tmp_path, meth
     mat, st2 = engine.genotype_load(golden_dir / "tiny", method=method, additive=additive, chunk_size=5)
     assert mat.shape == (n, m) and np.array_equal(np.nan_to_num(mat, nan=-9.0), np.nan_to_num(z, nan=-9.0))
     assert np.array_equal(st2["mean"], st["mean"], equal_nan=True) and st2["monomorphic_indices"].tolist() == mono
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(os.environ.get("GELEX_B200_TEST_UNVERIFIED") != "1",
+                    reason="added after the round's GPU minutes were spent: opt in with GELEX_B200_TEST_UNVERIFIED=1 (tools/r02_first_run.sh)")
+@pytest.mark.parametrize("method,additive,chunk", [("OSH", True, 25), ("SH", False, 7), ("OC", False, 40), ("S", True, 33)])
+def test_genotype_export_files_against_the_reference_pipe_files(golden_dir, tmp_path, method, additive, chunk):
+    # our .bmat / .snpstats beside the files the unmodified reference's GenotypePipe wrote for the same input (tests/golden/tiny_pipe_*):
+    # identical sizes, header and monomorphic indices; values to 2 ulp (FP64 on the device, explicit _rn arithmetic)
+    engine.genotype_export(golden_dir / "tiny", tmp_path / "t", method=method, additive=additive, chunk_size=chunk)
+    base = golden_dir / f"tiny_pipe_{method}.{'add' if additive else 'dom'}"
+    ref, got = np.fromfile(str(base) + ".bmat", dtype=np.float64), np.fromfile(tmp_path / "t.bmat", dtype=np.float64)
+    assert got.shape == ref.shape and np.array_equal(np.isnan(got), np.isnan(ref))
+    ok = ~np.isnan(ref)
+    assert np.all(np.abs(got[ok] - ref[ok]) <= 2 * np.spacing(np.abs(ref[ok])) + 1e-15)
+    rm, gm = engine.read_snp_stats(str(base) + ".snpstats"), engine.read_snp_stats(tmp_path / "t.snpstats")
+    assert (tmp_path / "t.snpstats").stat().st_size == Path(str(base) + ".snpstats").stat().st_size
+    assert (gm["num_samples"], gm["num_variants"]) == (rm["num_samples"], rm["num_variants"])
+    assert gm["monomorphic_indices"].tolist() == rm["monomorphic_indices"].tolist()
+    for key in ("mean", "stddev"):
+        assert np.array_equal(np.isnan(gm[key]), np.isnan(rm[key]))
+        ok = ~np.isnan(rm[key])
+        assert np.all(np.abs(gm[key][ok] - rm[key][ok]) <= 2 * np.spacing(np.abs(rm[key][ok])) + 1e-300), key
 
 
 @pytest.mark.gpu

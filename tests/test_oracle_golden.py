@@ -212,3 +212,34 @@ def test_whole_equals_sum_of_chromosome_partials(golden_dir):
     w = plink_io.read_bin(golden_dir / "tiny_OCH.add.bin", n).astype(np.float64)
     s = sum(plink_io.read_bin(golden_dir / f"tiny_OCH.add.chr{c}.bin", n).astype(np.float64) for c in ("1", "2", "X", "7"))
     assert np.allclose(w, s, rtol=1e-5, atol=1e-5)
+
+
+PIPE_CASES = [("OSH", 3, True, 25), ("SH", 1, False, 7), ("OC", 8, False, 40), ("S", 5, True, 33)]
+
+
+@pytest.mark.parametrize("tag,code,additive,chunk", PIPE_CASES)
+def test_genotype_pipe_files_of_the_reference(golden_dir, tag, code, additive, chunk):
+    # .bmat / .snpstats written by the unmodified reference's GenotypePipe::process<GT> (tests/golden/make_golden.py pipe): pins the
+    # layout this repo's GenotypePipe mirror writes - .bmat = column-major FP64 without header, .snpstats =
+    # {int64 n, int64 m, int64 #mono} + int64 indices + m means + m stddevs - and the oracle's LocusStatistic beside it.
+    from gelex_b200 import engine
+
+    payload, n_raw, ids, r2o, _ = load_tiny(golden_dir)
+    n, m = len(ids), payload.shape[0]
+    kind = 0 if additive else 1
+    base = golden_dir / f"tiny_pipe_{tag}.{'add' if additive else 'dom'}"
+    bmat = np.fromfile(str(base) + ".bmat", dtype=np.float64)
+    assert bmat.size == n * m
+    gold = np.load(golden_dir / "tiny_chunks.npz")
+    z = bmat.reshape(m, n).T
+    assert same(z, gold[f"z_{code}_{'A' if additive else 'D'}"])  # the file holds process_matrix's output, bit for bit, whatever the chunking
+    meta = engine.read_snp_stats(str(base) + ".snpstats")
+    assert (meta["num_samples"], meta["num_variants"]) == (n, m)
+    raw = o.decode_chunk(payload, n_raw, n, r2o)
+    mono = []
+    for j in range(m):
+        _, ls = o.process_column(raw[:, j], code, kind)
+        assert close(meta["mean"][j], ls.mean, rtol=1e-15, atol=0) and close(meta["stddev"][j], ls.stddev, rtol=1e-15, atol=1e-300), j  # sample policies: Eigen sums the centred column in another order
+        if ls.is_monomorphic:
+            mono.append(j)
+    assert meta["monomorphic_indices"].tolist() == mono
