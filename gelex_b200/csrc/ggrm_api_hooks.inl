@@ -212,7 +212,12 @@ extern "C" int ggrm_host_alloc(int64_t bytes, void** out) {
     GGRM_STATELESS_BEGIN
     if (out == nullptr || bytes <= 0) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "invalid pinned allocation request"};
     *out = nullptr;
-    GGRM_CUDA(cudaHostAlloc(out, static_cast<size_t>(bytes), cudaHostAllocPortable));
+    const cudaError_t e = cudaHostAlloc(out, static_cast<size_t>(bytes), cudaHostAllocPortable);
+    if (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) {  // a box without a GPU: say so the way ggrm_create does
+        cudaGetLastError();
+        throw CudaError{GGRM_ERR_NO_DEVICE, "no CUDA device visible; the B200 GRM engine has no CPU fallback"};
+    }
+    GGRM_CUDA(e);
     GGRM_STATELESS_END
 }
 
