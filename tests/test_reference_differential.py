@@ -328,3 +328,45 @@ def test_genotype_pipe_front_half_agrees_with_the_reference(tmp_path, seed):
             accepted += 1
         shutil.rmtree(d)
     assert accepted >= 5 and rejected >= 10
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_oracle_loco_partials_agree_with_the_reference(tmp_path, seed):
+    # `gelex grm --loco` of the reference on random small inputs whose chromosomes re-appear (a later run of the same name
+    # overwrites the earlier file, grm_work_plan.cpp:54-81 + grm_engine.cpp:88-110) beside the oracle run over the same SNP
+    # ranges; AD mode writes both matrices per run
+    import oracle_lib as o
+    import plink_io
+
+    rng = np.random.default_rng(100 + seed)
+    for k in range(10):
+        n_raw, m = int(rng.integers(2, 20)), int(rng.integers(3, 40))
+        geno = rng.binomial(2, rng.uniform(0.05, 0.95, size=m), size=(n_raw, m)).astype(np.float64)
+        geno[rng.random((n_raw, m)) < 0.1] = np.nan
+        chroms, c = [], "1"
+        for _ in range(m):
+            if rng.random() < 0.25:
+                c = str(rng.choice(["1", "2", "X", "7"]))
+            chroms.append(c)
+        fam = [("F", f"s{i:03d}") for i in rng.permutation(n_raw)]
+        payload = plink_io.encode_matrix(geno)
+        plink_io.write_plink(tmp_path / f"t{k}", payload, fam, chroms)
+        ids, r2o = plink_io.sample_order(fam)
+        method, chunk = int(rng.integers(1, 9)), int(rng.choice([2, 5, 10000]))
+        rc, msg = _reference(["grm", tmp_path / f"t{k}", tmp_path / f"r{k}", method, "AD", 1, chunk, 1])
+        assert rc == 0, msg
+        last = {}
+        for name, b, e in plink_io.chrom_runs(chroms):
+            last[name] = (b, e)  # the file that survives is the last run of that name
+        written = sorted(p.name for p in tmp_path.iterdir() if p.name.startswith(f"r{k}.") and p.name.endswith(".bin"))
+        assert written == sorted(f"r{k}.{kd}.chr{name}.bin" for name in last for kd in ("add", "dom"))
+        for name, (b, e) in last.items():
+            for kind, kd in ((0, "add"), (1, "dom")):
+                ref = plink_io.read_bin(tmp_path / f"r{k}.{kd}.chr{name}.bin", len(ids))
+                G, _, _ = o.grm_compute(payload, n_raw, method, kind, ranges=[(b, e)], chunk=chunk, n_out=len(ids), raw_to_out=r2o)
+                got = o.pack_lower_f32(G)
+                ctx = f"seed {seed} case {k} chr {name} [{b},{e}) {kd}: n={len(ids)} m={m} method={method}"
+                assert np.array_equal(np.isnan(got), np.isnan(ref)), ctx
+                ok = ~np.isnan(ref)
+                floor = 1e-14 * float(np.max(np.abs(ref[ok]))) if ok.any() else 0.0
+                assert np.all(np.abs(got[ok].astype(np.float64) - ref[ok]) <= np.spacing(np.abs(ref[ok])) + floor), ctx
