@@ -663,6 +663,15 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
     WriterPool pool(rc.cfg->writer_threads, rc.cfg->writer_threads + 2, std::max<int64_t>(kWriterBufferElems, rc.n_out));
     int pending = -1;  // local index of a group that is complete on the device but not yet written
     auto group_name = [&](int li) { return ".chr" + rc.groups[static_cast<size_t>(my_groups[static_cast<size_t>(li)])].name; };
+    // A chromosome that re-appears later in the BIM gives a second run with the same output name; the reference writes both, the
+    // later one over the earlier (grm_work_plan.cpp:54-81, grm_engine.cpp:88-110).  The earlier file is therefore never written
+    // here (its partial still feeds the whole-genome sum): same final files, and two GPUs never write one file in chromosome-shard mode.
+    auto superseded = [&](int li) {
+        const size_t gi = static_cast<size_t>(my_groups[static_cast<size_t>(li)]);
+        for (size_t later = gi + 1; later < rc.groups.size(); ++later)
+            if (rc.groups[later].name == rc.groups[gi].name) return true;
+        return false;
+    };
     for (size_t li = 0; li < my_groups.size(); ++li) {
         const ChrRun& run = rc.groups[static_cast<size_t>(my_groups[li])];
         int64_t done = 0;
@@ -670,7 +679,7 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
         const int64_t first_end = std::min<int64_t>(run.end, run.begin + rc.cfg->chunk_size);
         push_range(rc, hg.h, run.begin, first_end, run.end - run.begin, &done, report, relay);
         if (pending >= 0) {
-            write_outputs(rc, hg.h, pending, group_name(pending), part, pool);
+            if (!superseded(pending)) write_outputs(rc, hg.h, pending, group_name(pending), part, pool);
             for (int kind = 0; kind < 2; ++kind)
                 if (kind == 0 ? rc.want_add : rc.want_dom) check(hg.h, ggrm_release_group(hg.h, kind, pending));
             pending = -1;
@@ -682,7 +691,7 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
     // through ggrm_finish_async: its first row bands cross PCIe while the last slab is still on the tensor cores.
     const bool whole_here = !rc.loco && (write_whole_here || part.kind == WritePart::OwnedTiles);
     check(hg.h, ggrm_finish_async(hg.h));
-    if (rc.loco && pending >= 0) write_outputs(rc, hg.h, pending, group_name(pending), part, pool);
+    if (rc.loco && pending >= 0 && !superseded(pending)) write_outputs(rc, hg.h, pending, group_name(pending), part, pool);
     if (whole_here) write_outputs(rc, hg.h, GGRM_GROUP_WHOLE, "", part, pool);
     check(hg.h, ggrm_finish(hg.h));
     note_timers(rc, hg.h, pass_ms, syrk_ms);

@@ -314,6 +314,31 @@ def test_engine_tile_mode_bed_relay_matches_direct_push(tmp_path, monkeypatch, l
 
 
 @pytest.mark.gpu
+@pytest.mark.skipif(os.environ.get("GELEX_B200_TEST_UNVERIFIED") != "1",
+                    reason="added after the round's GPU minutes were spent: opt in with GELEX_B200_TEST_UNVERIFIED=1 (tools/r02_first_run.sh)")
+@pytest.mark.parametrize("n_gpus", [1, 3])
+def test_engine_loco_reappearing_chromosome_last_run_wins(tmp_path, monkeypatch, n_gpus):
+    # BIM order 1,2,1,X: the reference writes add.chr1 twice, the second run over the first (pinned against the reference binary in
+    # tests/test_reference_differential.py::test_oracle_loco_partials_agree_with_the_reference); here the first is never written
+    import oracle_lib as o
+
+    monkeypatch.setenv("GELEX_B200_OVERSUBSCRIBE", "1")
+    n, m = 300, 400
+    payload = g.synth_bed_host(n, 0, m, 37, 0.02)
+    chroms = ["1"] * 100 + ["2"] * 120 + ["1"] * 80 + ["X"] * 100
+    plink_io.write_plink(tmp_path / "d", payload, [("F", f"s{i:05d}") for i in range(n)], chroms)
+    engine.grm_run(tmp_path / "d", tmp_path / "g", method="SH", loco=True, precision=g.PREC_FP64, n_gpus=n_gpus, write_whole=True, chunk_size=64,
+                   partition="snp")
+    assert sorted(p.name for p in tmp_path.iterdir() if p.name.startswith("g.") and p.name.endswith(".bin")) == \
+        ["g.add.bin", "g.add.chr1.bin", "g.add.chr2.bin", "g.add.chrX.bin"]
+    for name, (b, e) in {"1": (220, 300), "2": (100, 220), "X": (300, 400), None: (0, 400)}.items():
+        G, _, _ = o.grm_compute(payload, n, 1, 0, ranges=[(b, e)], chunk=64)
+        ref = o.pack_lower_f32(G)
+        got = plink_io.read_bin(tmp_path / ("g.add.bin" if name is None else f"g.add.chr{name}.bin"), n)
+        assert np.all(np.abs(got - ref) <= 2 * np.spacing(np.abs(ref)) + 1e-12), name
+
+
+@pytest.mark.gpu
 def test_cli_is_a_drop_in(golden_dir, tmp_path):
     r = subprocess.run([str(engine.CLI_PATH), "grm", "-b", str(golden_dir / "tiny"), "--gm", "SH", "--add", "-c", "25", "--precision", "fp64",
                         "-o", str(tmp_path / "cli")], capture_output=True, text=True)
