@@ -1171,7 +1171,6 @@ int64_t GrmEngine::relay_selftest(int n_chunks, int world, int slots, int chunk_
 void GrmEngine::compute(const GrmObserver& observer) {
     const auto t_start = Clock::now();
     summary_ = Summary{};
-    if (config_.chunk_size <= 0) throw ArgumentValidationException("chunk_size must be positive");
     if (config_.gpus.empty()) throw ArgumentValidationException("at least one GPU is required (there is no CPU fallback)");
     if (config_.gcta && (config_.mode != GrmType::A || config_.do_loco))
         throw ArgumentValidationException("--gcta writes the additive matrix of the whole genome: use --add without --dom / --loco");
@@ -1220,6 +1219,14 @@ void GrmEngine::compute(const GrmObserver& observer) {
 
     const int n_gpus = static_cast<int>(config_.gpus.size());
     if (config_.writer_threads < 1) throw ArgumentValidationException("writer_threads must be >= 1");
+    // The CLI refuses chunk_size <= 0 (grm_config.cpp:42-46).  The reference ENGINE does not look at it until the first
+    // BedPipe::load_chunk(start, start + chunk_size), whose range check fails (bed_pipe.cpp:38-52) - after every input has been
+    // validated.  Same here, before any loop steps by it.
+    if (config_.chunk_size <= 0 && !rc.groups.empty() && !chroms.empty()) {
+        const int64_t s0 = rc.groups.front().begin;
+        throw ColumnRangeException("invalid chunk range: [" + std::to_string(s0) + ", " + std::to_string(s0 + config_.chunk_size) +
+                                   "). Total SNPs: " + std::to_string(m));
+    }
     rc.writer = resolve_writer_mode(config_.writer);
     {
         const char* e = std::getenv("GELEX_B200_BED_RELAY");
