@@ -77,16 +77,16 @@ def main():
         expect_bytes = n * (n + 1) // 2 * 4
         seen, stop = {}, threading.Event()
 
-        def reaper():  # LOCO only: keep the newest two .bin files, delete older finished ones after recording their size
+        def reaper():  # LOCO only: keep the newest 1 + gpus .bin files, delete older finished ones after recording their size
             while not stop.is_set():
                 bins = sorted(d.glob(name + "_out.*.chr*.bin"), key=lambda p: p.stat().st_mtime)
-                for p in bins[:-2]:
+                for p in bins[:-(1 + args.gpus)]:  # every GPU may have one file in progress (those have the newest mtimes)
                     seen[p.name] = p.stat().st_size
                     p.unlink()
                 time.sleep(0.2)
 
         th = threading.Thread(target=reaper, daemon=True)
-        if c["loco"] and args.gpus == 1:
+        if c["loco"]:
             th.start()
         t0 = time.time()
         r = subprocess.run(cmd, capture_output=True, text=True)
