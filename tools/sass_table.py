@@ -25,11 +25,20 @@ def main():
     print("Static instruction counts (loops are not unrolled into them). `syrk_tc_kernel<2>` is the kernel `bench.py` runs: its four `UTCHMMA` are")
     print("the K = 16 steps of one 64-element K block (`tcgen05.mma.cta_group::2.kind::f16`, 256 x 256 x 16), `UTMALDG` the two TMA box")
     print("loads per stage, `LDTM` the `tcgen05.ld.32x32b.x32` of the epilogue; no `HMMA` anywhere (no legacy tensor path).\n")
+    res = {}
+    usage = subprocess.run(["cuobjdump", "-res-usage", str(LIB)], capture_output=True, text=True, check=True).stdout
+    for mname, body in re.findall(r"Function ([^:\s]+):\s*\n\s*(REG:[^\n]*)", usage):
+        d = subprocess.run(["c++filt", mname], capture_output=True, text=True).stdout.strip()
+        d = re.sub(r"\(.*", "", d).replace("void ", "").replace("ggrm::", "")
+        res[d] = (re.search(r"REG:(\d+)", body).group(1), re.search(r"STACK:(\d+)", body).group(1), re.search(r"SHARED:(\d+)", body).group(1))
     keys = list(PAT)
-    print("| kernel | SASS lines | " + " | ".join(keys) + " |")
-    print("|---|---:|" + "---:|" * len(keys))
+    print("Registers / stack bytes / static shared bytes per thread block are `cuobjdump -res-usage` (the SYRK ring is dynamic shared memory, 194 KB,")
+    print("and does not show here); no kernel spills.\n")
+    print("| kernel | regs | stack | static smem | SASS lines | " + " | ".join(keys) + " |")
+    print("|---|---:|---:|---:|---:|" + "---:|" * len(keys))
     for dem, n, c in sorted(rows):
-        print(f"| `{dem}` | {n} | " + " | ".join(str(c[k]) if c[k] else "" for k in keys) + " |")
+        r = res.get(dem, ("", "", ""))
+        print(f"| `{dem}` | {r[0]} | {r[1]} | {r[2]} | {n} | " + " | ".join(str(c[k]) if c[k] else "" for k in keys) + " |")
 
 
 if __name__ == "__main__":
