@@ -89,3 +89,24 @@ def test_plink_helpers_follow_reference_conventions():
     # BED encoding (tests/bed_fixture.cpp:72-95)
     geno = np.array([[0.0], [1.0], [2.0], [np.nan], [2.0]])
     assert plink_io.encode_matrix(geno).tolist() == [[0b01001011, 0b00000000]]
+
+
+def test_built_library_holds_blackwell_tensor_and_tma_instructions():
+    # what proves a Blackwell-native kernel is in the SASS, not in the PTX names (profiles/r01_sass_mnemonics.md): the SYRK that
+    # bench.py runs must hold UTCHMMA (tcgen05.mma), UTCBAR (tcgen05.commit), LDTM (tcgen05.ld) and UTMALDG (TMA loads), the FP64
+    # mode DMMA, and nothing may fall back to the legacy HMMA path
+    import shutil
+    import subprocess
+
+    if shutil.which("cuobjdump") is None:
+        pytest.skip("no cuobjdump")
+    sass = subprocess.run(["cuobjdump", "-sass", str(_lib.LIB_PATH)], capture_output=True, text=True, check=True).stdout
+    assert "arch = sm_100a" in sass
+    funcs = {f.split("\n", 1)[0].strip(): f for f in re.split(r"\n\s*Function : ", sass)[1:]}
+    tc2 = [body for name, body in funcs.items() if "syrk_tc_kernelILi2" in name]
+    assert len(tc2) == 1
+    for mnemonic in ("UTCHMMA.2CTA", "UTCBAR", "LDTM", "UTMALDG", "SYNCS"):
+        assert mnemonic in tc2[0], mnemonic
+    f64 = [body for name, body in funcs.items() if "syrk_f64_kernel" in name]
+    assert len(f64) == 1 and "DMMA" in f64[0]
+    assert not any(re.search(r"\bHMMA\b", body) for body in funcs.values())
