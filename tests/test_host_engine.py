@@ -338,6 +338,28 @@ def test_engine_loco_reappearing_chromosome_last_run_wins(tmp_path, monkeypatch,
         assert np.all(np.abs(got - ref) <= 2 * np.spacing(np.abs(ref)) + 1e-12), name
 
 
+REF_BINDING = Path(__file__).resolve().parent.parent / "oracle" / "_ref" / "gelex_ref_b200"
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(os.environ.get("GELEX_B200_TEST_UNVERIFIED") != "1" or not REF_BINDING.exists(),
+                    reason="oracle/_ref/gelex_ref_b200 (built where /root/reference exists) was added after the round's GPU minutes were spent: "
+                           "opt in with GELEX_B200_TEST_UNVERIFIED=1")
+def test_reference_host_code_over_the_c_abi_writes_the_reference_files(golden_dir, tmp_path):
+    # INTEGRATION.md section 2 as a program (oracle/ref_binding.cpp): the UNMODIFIED reference's SampleManager, BedPipe projection + mmap,
+    # work plans and GrmBinWriter / GrmIdWriter, with only the chunk loop of GRM::compute<GT> replaced by ggrm_create / push / finish /
+    # fetch_f64.  Its files against the plain reference's (tests/golden): .id identical, .bin within one float32 ulp (FP64 mode).
+    r = subprocess.run([str(REF_BINDING), str(golden_dir / "tiny"), str(tmp_path / "sh"), "1", "A", "0", "25", "fp64"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([str(REF_BINDING), str(golden_dir / "tiny"), str(tmp_path / "och"), "4", "AD", "1", "7", "fp64"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    pairs = [("sh.add", "tiny_SH.add")] + [(f"och.{k}.chr{c}", f"tiny_OCH.{k}.chr{c}") for k in ("add", "dom") for c in ("1", "2", "X", "7")]
+    for mine, gold in pairs:
+        assert (tmp_path / f"{mine}.id").read_bytes() == (golden_dir / f"{gold}.id").read_bytes(), mine
+        got, ref = plink_io.read_bin(tmp_path / f"{mine}.bin", 36), plink_io.read_bin(golden_dir / f"{gold}.bin", 36)
+        assert np.all(np.abs(got.astype(np.float64) - ref) <= np.spacing(np.abs(ref)) + 1e-12), mine
+
+
 @pytest.mark.gpu
 def test_cli_is_a_drop_in(golden_dir, tmp_path):
     r = subprocess.run([str(engine.CLI_PATH), "grm", "-b", str(golden_dir / "tiny"), "--gm", "SH", "--add", "-c", "25", "--precision", "fp64",

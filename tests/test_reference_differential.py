@@ -371,3 +371,20 @@ def test_oracle_loco_partials_agree_with_the_reference(tmp_path, seed):
                 ok = ~np.isnan(ref)
                 floor = 1e-14 * float(np.max(np.abs(ref[ok]))) if ok.any() else 0.0
                 assert np.all(np.abs(got[ok].astype(np.float64) - ref[ok]) <= np.spacing(np.abs(ref[ok])) + floor), ctx
+
+
+def test_reference_side_binding_builds_and_reaches_the_c_abi(tmp_path):
+    # oracle/ref_binding.cpp = INTEGRATION.md section 2 compiled against the unmodified reference headers and linked with its own
+    # loaders / planners / writers plus libggrm_b200.so.  Without a GPU the reference's front half still runs (and rejects what it
+    # rejects) and the first ABI call fails loudly; with one, tests/test_host_engine.py compares its files with the reference's.
+    exe = REF.parent / "gelex_ref_b200"
+    if not exe.exists():
+        pytest.skip("oracle/_ref/gelex_ref_b200 not built")
+    golden = Path(__file__).resolve().parent / "golden"
+    r = subprocess.run([str(exe), str(golden / "tiny"), str(tmp_path / "o"), "1", "A", "0", "25", "fp64"], capture_output=True, text=True)
+    if r.returncode == 0:  # a GPU is present
+        assert (tmp_path / "o.add.id").read_bytes() == (golden / "tiny_SH.add.id").read_bytes()
+    else:
+        assert "no CUDA device visible; the B200 GRM engine has no CPU fallback" in r.stderr
+    r = subprocess.run([str(exe), str(tmp_path / "missing"), str(tmp_path / "o"), "1", "A", "0", "25", "fp64"], capture_output=True, text=True)
+    assert r.returncode == 1 and "not found" in r.stderr  # the reference's own FileNotFoundException, before any ABI call
