@@ -277,12 +277,16 @@ extern "C" int gelex_b200_strip_owners(int64_t n, int world, const int64_t* band
 
 // GrmEngine::writer_selftest through C (CPU tests, no GPU): writer 0 = auto, 1 = pwrite, 2 = mmap; seconds_out / mapped_out optional.
 extern "C" int gelex_b200_writer_selftest(const char* bin_path, int64_t n, int tiles, int parts, int writer_threads, int writer,
-                                          double* seconds_out, int* mapped_out, char* err, int err_len) {
+                                          int prefault_threads, double* seconds_out, double* prefault_seconds_out, int* mapped_out, char* err,
+                                          int err_len) {
     try {
         if (bin_path == nullptr) throw ArgumentValidationException("null argument");
         if (writer < 0 || writer > 2) throw ArgumentValidationException("writer must be 0 (auto), 1 (pwrite) or 2 (mmap)");
         bool mapped = false;
-        const double s = GrmEngine::writer_selftest(bin_path, n, tiles != 0, parts, writer_threads, static_cast<WriterMode>(writer), &mapped);
+        double pf = 0.0;
+        const double s = GrmEngine::writer_selftest(bin_path, n, tiles != 0, parts, writer_threads, static_cast<WriterMode>(writer), &mapped,
+                                                    prefault_threads, &pf);
+        if (prefault_seconds_out != nullptr) *prefault_seconds_out = pf;
         if (seconds_out != nullptr) *seconds_out = s;
         if (mapped_out != nullptr) *mapped_out = mapped ? 1 : 0;
         set_err(err, err_len, "");

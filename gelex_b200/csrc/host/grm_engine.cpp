@@ -15,9 +15,11 @@
 #include <unordered_map>
 #include <condition_variable>
 #include <deque>
+#include <map>
 
 #include <fcntl.h>
 #include <sys/mman.h>
+#include <sys/stat.h>
 #include <sys/statvfs.h>
 #include <sys/vfs.h>
 #include <unistd.h>
@@ -62,17 +64,37 @@ struct HandleGuard {
 // Auto = mmap for segments below kMapSegmentBytes (scattered tile rows) and for every segment on tmpfs, pwrite otherwise.
 constexpr int64_t kMapSegmentBytes = int64_t{256} << 10;
 
+// Mappings that a Prefaulter has populated, by inode.  A BinFile opened for the same file writes through THAT mapping instead of a
+// fresh one of its own: the pages are already in this process's page tables (measured: 23 GB/s, against 5.6 GB/s through a second
+// mapping of the same populated file, which still takes a minor fault per page).  A Prefaulter outlives every BinFile of its run.
+struct SharedMappings {
+    std::mutex mu;
+    std::map<std::pair<uint64_t, uint64_t>, std::pair<char*, size_t>> by_inode;
+    static SharedMappings& get() {
+        static SharedMappings s;
+        return s;
+    }
+    char* find(int fd, size_t bytes) {
+        struct stat st {};
+        if (::fstat(fd, &st) != 0) return nullptr;
+        std::lock_guard<std::mutex> lk(mu);
+        const auto it = by_inode.find({static_cast<uint64_t>(st.st_dev), static_cast<uint64_t>(st.st_ino)});
+        return it != by_inode.end() && it->second.second == bytes ? it->second.first : nullptr;
+    }
+};
+
 struct BinFile {
     int fd = -1;
     std::string path;
     char* map = nullptr;       // whole file, MAP_SHARED (nullptr: pwrite only)
     size_t map_bytes = 0;
+    bool owns_map = true;      // false: the mapping belongs to a Prefaulter (SharedMappings)
     bool map_all = false;      // every segment goes through the mapping (tmpfs, or WriterMode::Mmap)
     BinFile() = default;
     BinFile(const BinFile&) = delete;
     BinFile& operator=(const BinFile&) = delete;
     ~BinFile() {
-        if (map != nullptr) ::munmap(map, map_bytes);
+        if (map != nullptr && owns_map) ::munmap(map, map_bytes);
         if (fd >= 0) ::close(fd);
     }
     // create = truncate + size the file (one caller); otherwise open an existing, already sized file for writing
@@ -89,17 +111,22 @@ struct BinFile {
         if (create && ::ftruncate(fd, static_cast<off_t>(bytes)) != 0)
             throw FileWriteException(path + ": failed to write GRM data to binary file");
         if (mode == WriterMode::Pwrite || bytes == 0) return;
-        void* m = ::mmap(nullptr, static_cast<size_t>(bytes), PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
-        if (m == MAP_FAILED) return;  // e.g. a file system without mmap: pwrite still works
-        map = static_cast<char*>(m);
+        if (char* shared = create ? nullptr : SharedMappings::get().find(fd, static_cast<size_t>(bytes))) {
+            map = shared;
+            owns_map = false;
+        } else {
+            void* m = ::mmap(nullptr, static_cast<size_t>(bytes), PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+            if (m == MAP_FAILED) return;  // e.g. a file system without mmap: pwrite still works
+            map = static_cast<char*>(m);
+        }
         map_bytes = static_cast<size_t>(bytes);
         struct statfs sf {};
         const bool tmpfs = ::fstatfs(fd, &sf) == 0 && static_cast<unsigned long>(sf.f_type) == 0x01021994ul;  // TMPFS_MAGIC
-        map_all = mode == WriterMode::Mmap || tmpfs;
+        map_all = mode == WriterMode::Mmap || tmpfs || !owns_map;  // a populated mapping takes every segment
     }
     void close_checked() {
         if (map != nullptr) {
-            const int rc = ::munmap(map, map_bytes);
+            const int rc = owns_map ? ::munmap(map, map_bytes) : 0;
             map = nullptr;
             if (rc != 0) throw FileWriteException(path + ": failed to write GRM data to binary file");
         }
@@ -119,6 +146,74 @@ bool file_system_has_room(const fs::path& path, int64_t bytes) {
     const double avail = static_cast<double>(sv.f_bavail) * static_cast<double>(sv.f_frsize);
     return avail >= static_cast<double>(bytes) * 1.02 + static_cast<double>(int64_t{256} << 20);
 }
+
+// Page allocation, not copying, is what a fresh output file costs (tmpfs on the build host: 2.5 GB/s into untouched pages, 29 GB/s
+// into populated ones; profiles/r01_summary.md §11).  The matrix of a non-LOCO run is only final when the last SNP has been
+// accumulated, so the file sits idle for the whole pass: a Prefaulter populates the pages of the pre-sized file meanwhile
+// (MADV_POPULATE_WRITE on its own shared mapping, a few threads, 64 MiB at a time; contents untouched, so it may still be running
+// when the writers start).  A file system without room makes the call fail instead of raising SIGBUS; the threads then simply stop.
+class Prefaulter {
+   public:
+    Prefaulter(const std::string& path, int threads) {
+        fd_ = ::open(path.c_str(), O_RDWR);
+        if (fd_ < 0) return;
+        struct stat st {};
+        if (::fstat(fd_, &st) != 0 || st.st_size <= 0) return;
+        bytes_ = static_cast<size_t>(st.st_size);
+        void* m = ::mmap(nullptr, bytes_, PROT_READ | PROT_WRITE, MAP_SHARED, fd_, 0);
+        if (m == MAP_FAILED) return;
+        map_ = static_cast<char*>(m);
+        {
+            auto& reg = SharedMappings::get();
+            std::lock_guard<std::mutex> lk(reg.mu);
+            key_ = {static_cast<uint64_t>(st.st_dev), static_cast<uint64_t>(st.st_ino)};
+            registered_ = reg.by_inode.emplace(key_, std::make_pair(map_, bytes_)).second;
+        }
+        for (int t = 0; t < std::max(1, threads); ++t) workers_.emplace_back([this] { run(); });
+    }
+    Prefaulter(const Prefaulter&) = delete;
+    Prefaulter& operator=(const Prefaulter&) = delete;
+    ~Prefaulter() {
+        stop_.store(true);
+        for (auto& w : workers_) w.join();
+        if (registered_) {
+            auto& reg = SharedMappings::get();
+            std::lock_guard<std::mutex> lk(reg.mu);
+            reg.by_inode.erase(key_);
+        }
+        if (map_ != nullptr) ::munmap(map_, bytes_);
+        if (fd_ >= 0) ::close(fd_);
+    }
+    void wait() {  // (self-test) until every piece has been tried
+        for (auto& w : workers_) w.join();
+        workers_.clear();
+    }
+    size_t populated_bytes() const { return populated_.load(); }
+
+   private:
+    static constexpr size_t kPiece = size_t{64} << 20;
+    void run() {
+        for (;;) {
+            const size_t off = next_.fetch_add(kPiece);
+            if (off >= bytes_ || stop_.load()) return;
+            const size_t len = std::min(kPiece, bytes_ - off);
+#ifdef MADV_POPULATE_WRITE
+            if (::madvise(map_ + off, len, MADV_POPULATE_WRITE) != 0) return;  // old kernel, or no room: leave the rest to the writers
+            populated_.fetch_add(len);
+#else
+            return;
+#endif
+        }
+    }
+    int fd_ = -1;
+    char* map_ = nullptr;
+    size_t bytes_ = 0;
+    std::atomic<size_t> next_{0}, populated_{0};
+    std::atomic<bool> stop_{false};
+    std::vector<std::thread> workers_;
+    std::pair<uint64_t, uint64_t> key_{0, 0};
+    bool registered_ = false;
+};
 
 struct Segment { int64_t src_elem, file_byte, bytes; };  // buffer elements [src_elem, +bytes/4) -> file bytes [file_byte, +bytes)
 
@@ -381,6 +476,7 @@ struct RunContext {
     bool gcta;  // kind 1 is the non-missing pair count matrix; outputs are <out>.grm.bin / .grm.N.bin / .grm.id
     WriterMode writer;  // effective mode of this run: Pwrite when the file system could not hold every output (see BinFile)
     bool bed_relay;     // 2D-tile mode: one upload per host chunk, peers copy it over NVLink (BedRelay)
+    bool prefault;      // non-LOCO runs with mapped outputs: populate the output pages while the GPUs accumulate (Prefaulter)
     // progress (reference: per work item, counted in SNPs; grm.h:124-130)
     const GrmObserver* observer;
     std::mutex* mu;
@@ -614,6 +710,17 @@ void precreate_outputs(const RunContext& rc, const std::vector<std::string>& suf
             if (has_id_file(rc, kind)) write_id_file(base + ".id", rc.order->ids);
             register_files(rc, base, has_id_file(rc, kind));
         }
+}
+
+// Prefaulters for the whole-genome .bin of every requested kind (files must exist, pre-sized).  Empty unless the run maps its
+// outputs, asked for it, and is not a LOCO run (whose files are written one after another while the GPU is already ahead).
+std::vector<std::unique_ptr<Prefaulter>> start_prefault(const RunContext& rc) {
+    std::vector<std::unique_ptr<Prefaulter>> out;
+    if (!rc.prefault || rc.loco || rc.writer == WriterMode::Pwrite) return out;
+    for (int kind = 0; kind < 2; ++kind)
+        if (kind == 0 ? rc.want_add : rc.want_dom)
+            out.push_back(std::make_unique<Prefaulter>(output_base(rc, kind, "") + ".bin", std::max(2, rc.cfg->writer_threads)));
+    return out;
 }
 
 void write_outputs(const RunContext& rc, ggrm_t* h, int local_group, const std::string& suffix /* "" or ".chrNAME" */, const WritePart& part,
@@ -897,6 +1004,7 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
     std::vector<int> all;
     ShardPipe pipe;
     std::unique_ptr<BedRelay> relay;  // function scope: outlives the worker threads
+    std::vector<std::unique_ptr<Prefaulter>> prefaulters;  // stopped when this function returns
     bool pipelined = false;
     if (tile_mode) {
         // 2D output tiles: every GPU streams ALL SNPs, owns disjoint 2048 x 2048 super-tiles of every matrix and writes them
@@ -905,6 +1013,7 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
         if (rc.loco) for (const ChrRun& g : rc.groups) suffixes.push_back(".chr" + g.name);
         if (want_whole) suffixes.emplace_back("");
         precreate_outputs(rc, suffixes);
+        prefaulters = start_prefault(rc);
         all.resize(rc.groups.size());
         std::iota(all.begin(), all.end(), 0);
         if (rc.bed_relay) relay = std::make_unique<BedRelay>(rc, gpus, 2);
@@ -989,6 +1098,7 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
         pipe.mine = strip_owners(rc.n_out, static_cast<int>(world), band_end);
         pipe.flags.assign(world * static_cast<size_t>(pipe.n_bands), 0);
         precreate_outputs(rc, {""});
+        prefaulters = start_prefault(rc);
         for (size_t r = 0; r < world; ++r) {
             threads.emplace_back([&, r] {
                 try {
@@ -1071,7 +1181,8 @@ void selftest_fill(float* out, int64_t i, int64_t j0, int64_t len) {
 
 }  // namespace
 
-double GrmEngine::writer_selftest(const fs::path& bin_path, int64_t n, bool tiles, int parts, int writer_threads, WriterMode mode, bool* mapped) {
+double GrmEngine::writer_selftest(const fs::path& bin_path, int64_t n, bool tiles, int parts, int writer_threads, WriterMode mode, bool* mapped,
+                                  int prefault_threads, double* prefault_seconds) {
     if (n < 1 || parts < 1 || writer_threads < 1) throw ArgumentValidationException("writer_selftest: invalid argument");
     mode = resolve_writer_mode(mode);
     if (mode != WriterMode::Pwrite && !file_system_has_room(bin_path, tri(n) * 4)) mode = WriterMode::Pwrite;
@@ -1079,6 +1190,15 @@ double GrmEngine::writer_selftest(const fs::path& bin_path, int64_t n, bool tile
         BinFile f;
         f.open(bin_path, n, true);
         f.close_checked();
+    }
+    // what the engine does while the GPUs accumulate (Config::prefault): here it runs to completion first and is timed on its own
+    if (prefault_seconds != nullptr) *prefault_seconds = 0.0;
+    std::unique_ptr<Prefaulter> prefaulter;
+    if (prefault_threads > 0 && mode != WriterMode::Pwrite) {
+        const auto tp = Clock::now();
+        prefaulter = std::make_unique<Prefaulter>(bin_path.string(), prefault_threads);
+        prefaulter->wait();
+        if (prefault_seconds != nullptr) *prefault_seconds = since(tp);
     }
     // the work of each part, as the engine deals it: row slices (SNP-shard writers) or super-tiles round-robin (2D tiles)
     const auto slices = row_slices(n, parts);
@@ -1231,6 +1351,8 @@ void GrmEngine::compute(const GrmObserver& observer) {
     {
         const char* e = std::getenv("GELEX_B200_BED_RELAY");
         rc.bed_relay = config_.bed_relay || (e != nullptr && e[0] == '1');
+        const char* pf = std::getenv("GELEX_B200_PREFAULT");
+        rc.prefault = config_.prefault || (pf != nullptr && pf[0] == '1');
     }
     if (rc.writer != WriterMode::Pwrite) {
         // every .bin of the run: one per work item, plus the whole-genome sums of a LOCO run, or the GCTA pair
@@ -1246,7 +1368,14 @@ void GrmEngine::compute(const GrmObserver& observer) {
         std::vector<int> all(rc.groups.size());
         std::iota(all.begin(), all.end(), 0);
         // one GPU writes everything itself, the whole-genome matrix included (non-LOCO: the only output; LOCO: with write_whole)
-        run_groups_on_device(rc, config_.gpus[0], all, config_.do_loco && config_.write_whole, nullptr, &pass_ms, &syrk_ms, WritePart{}, 0, 1, true,
+        WritePart part;
+        std::vector<std::unique_ptr<Prefaulter>> prefaulters;
+        if (rc.prefault && !rc.loco && rc.writer != WriterMode::Pwrite) {
+            precreate_outputs(rc, {""});  // the file exists from the start so that its pages can be populated during the pass
+            prefaulters = start_prefault(rc);
+            part.create = false;
+        }
+        run_groups_on_device(rc, config_.gpus[0], all, config_.do_loco && config_.write_whole, nullptr, &pass_ms, &syrk_ms, part, 0, 1, true,
                              !config_.do_loco || config_.write_whole);
     } else {
         // SNP shards (+ one reduce) while the FP32 triangle fits comfortably per GPU, 2D output tiles from n >= 100 000

@@ -78,6 +78,10 @@ class GrmEngine {
         // NVLink peer memory, instead of every GPU reading the whole file over its own PCIe link (grm_engine.cpp, BedRelay).
         // GELEX_B200_BED_RELAY=1 turns it on as well.  Off by default until it has been measured on an 8-GPU box.
         bool bed_relay = false;
+        // Non-LOCO runs whose outputs are mapped: create the .bin up front and populate its pages (MADV_POPULATE_WRITE, a few host
+        // threads) while the GPUs accumulate, so that the read-out copies into allocated pages (grm_engine.cpp, Prefaulter).
+        // GELEX_B200_PREFAULT=1 turns it on as well.  Off by default until measured through the CLI on the GPU box.
+        bool prefault = false;
         // GCTA binary format behind a flag (docs/source/data_formats.rst:188-208): instead of <out>.add.{bin,id} write
         // <out>.grm.bin (A_ij = G_ij / N_ij), <out>.grm.N.bin (N_ij = SNPs called in both samples) and <out>.grm.id.  Mode A, no LOCO.
         bool gcta = false;
@@ -109,8 +113,10 @@ class GrmEngine {
     // (i, j) = float((31 i + j) mod 65521) + 0.5 through the same jobs the engine submits - whole-row blocks of `parts` row
     // slices (tiles = false), or 2 048 x 2 048 super-tile row segments dealt round-robin to `parts` concurrent pools (tiles = true) -
     // and returns the seconds spent.  tests/test_host_engine.py compares the file with numpy.
+    // prefault_threads > 0 (and a mapped mode): the file's pages are populated first, as Config::prefault does during the pass;
+    // that phase is timed separately (prefault_seconds) and the returned seconds are the writers' alone.
     static double writer_selftest(const std::filesystem::path& bin_path, int64_t n, bool tiles, int parts, int writer_threads, WriterMode mode,
-                                  bool* mapped);
+                                  bool* mapped, int prefault_threads = 0, double* prefault_seconds = nullptr);
 
     // CPU-only check of the BED relay's protocol (ChunkRelay in grm_engine.cpp: `world` uploader threads filling `slots` slots
     // each, `world` consumers taking every chunk in order) with host buffers in place of device staging slots.  Returns the number
@@ -142,6 +148,7 @@ extern "C" int gelex_b200_grm_run_gcta(const char* bfile, const char* out_prefix
 extern "C" int gelex_b200_strip_owners(int64_t n, int world, const int64_t* band_row_end, int n_bands, int64_t* out4, int cap);
 // GrmEngine::writer_selftest through C (CPU tests): writer 0 = auto, 1 = pwrite, 2 = mmap.
 extern "C" int gelex_b200_writer_selftest(const char* bin_path, int64_t n, int tiles, int parts, int writer_threads, int writer,
-                                          double* seconds_out, int* mapped_out, char* err, int err_len);
+                                          int prefault_threads, double* seconds_out, double* prefault_seconds_out, int* mapped_out, char* err,
+                                          int err_len);
 // GrmEngine::relay_selftest through C (CPU tests): returns the mismatch count (>= 0) or a negative status with err set.
 extern "C" int64_t gelex_b200_relay_selftest(int n_chunks, int world, int slots, int chunk_bytes, int fail_at_chunk, char* err, int err_len);

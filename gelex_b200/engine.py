@@ -45,8 +45,8 @@ def load_host():
                                                  C.c_char_p, C.c_int]
         h.gelex_b200_genotype_load.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int64, vp, vp, vp, vp, vp, C.c_int64,
                                                C.c_char_p, C.c_int]
-        h.gelex_b200_writer_selftest.argtypes = [C.c_char_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int),
-                                                 C.c_char_p, C.c_int]
+        h.gelex_b200_writer_selftest.argtypes = [C.c_char_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double),
+                                                 C.POINTER(C.c_double), C.POINTER(C.c_int), C.c_char_p, C.c_int]
         h.gelex_b200_write_id_file.argtypes = [C.c_char_p, C.c_char_p, C.c_int64, C.c_char_p, C.c_int]
         h.gelex_b200_format_bed_path.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_int]
         h.gelex_b200_relay_selftest.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]
@@ -58,18 +58,21 @@ def load_host():
 WRITERS = {"auto": 0, "pwrite": 1, "mmap": 2}
 
 
-def writer_selftest(bin_path, n, tiles=False, parts=1, writer_threads=4, writer="auto"):
+def writer_selftest(bin_path, n, tiles=False, parts=1, writer_threads=4, writer="auto", prefault_threads=0, with_prefault_seconds=False):
     """The engine's .bin writer pool on a synthetic n x n matrix, no GPU involved (GrmEngine::writer_selftest): entry (i, j) of
     the packed lower triangle is float32((31 i + j) mod 65521 + 0.5).  tiles=False: `parts` row-slice writers of whole-row
     blocks (SNP-shard read-out); tiles=True: 2048 x 2048 super-tiles dealt round-robin to `parts` pools as row segments (2D-tile
-    read-out).  Returns (seconds, outputs_mapped)."""
+    read-out).  prefault_threads > 0: the file's pages are populated first (what Config::prefault does during the pass), timed on its own.
+    Returns (writer seconds, outputs_mapped), plus the prefault seconds with with_prefault_seconds."""
     h = load_host()
     err = C.create_string_buffer(2048)
-    sec, mapped = C.c_double(0), C.c_int(0)
+    sec, pf, mapped = C.c_double(0), C.c_double(0), C.c_int(0)
     st = h.gelex_b200_writer_selftest(str(bin_path).encode(), int(n), int(bool(tiles)), int(parts), int(writer_threads), WRITERS[writer],
-                                      C.byref(sec), C.byref(mapped), err, len(err))
+                                      int(prefault_threads), C.byref(sec), C.byref(pf), C.byref(mapped), err, len(err))
     if st != 0:
         raise EngineError(st, err.value.decode())
+    if with_prefault_seconds:
+        return sec.value, bool(mapped.value), pf.value
     return sec.value, bool(mapped.value)
 
 

@@ -245,6 +245,19 @@ def test_writer_pool_bytes_need_no_gpu(tmp_path, writer, tiles, parts):
         assert np.array_equal(got, engine.writer_selftest_expected(n))
 
 
+@pytest.mark.parametrize("tiles,parts", [(False, 1), (False, 3), (True, 3)])
+def test_writer_pool_after_prefault_needs_no_gpu(tmp_path, tiles, parts):
+    # Config::prefault: the pages of the pre-sized file are populated (MADV_POPULATE_WRITE on a shared mapping, contents untouched)
+    # and the writers then copy through THAT mapping (SharedMappings) - same bytes; with pwrite forced nothing is mapped or populated
+    for n in (5, 4500):
+        for writer in ("mmap", "auto", "pwrite"):
+            path = tmp_path / f"p{n}.bin"
+            _, mapped, pf_s = engine.writer_selftest(path, n, tiles=tiles, parts=parts, writer_threads=2, writer=writer, prefault_threads=3,
+                                                     with_prefault_seconds=True)
+            assert mapped == (writer != "pwrite") and (pf_s > 0) == (writer != "pwrite")
+            assert np.array_equal(np.fromfile(path, dtype=np.float32), engine.writer_selftest_expected(n))
+
+
 def test_writer_mode_env_and_validation_need_no_gpu(tmp_path, monkeypatch):
     monkeypatch.setenv("GELEX_B200_WRITER", "pwrite")  # the environment overrides Auto only
     assert engine.writer_selftest(tmp_path / "a.bin", 300, writer="auto")[1] is False
@@ -336,6 +349,27 @@ def test_engine_loco_reappearing_chromosome_last_run_wins(tmp_path, monkeypatch,
         ref = o.pack_lower_f32(G)
         got = plink_io.read_bin(tmp_path / ("g.add.bin" if name is None else f"g.add.chr{name}.bin"), n)
         assert np.all(np.abs(got - ref) <= 2 * np.spacing(np.abs(ref)) + 1e-12), name
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(os.environ.get("GELEX_B200_TEST_UNVERIFIED") != "1",
+                    reason="added after the round's GPU minutes were spent: opt in with GELEX_B200_TEST_UNVERIFIED=1 (tools/r02_first_run.sh)")
+@pytest.mark.parametrize("n_gpus,partition", [(1, "auto"), (2, "snp"), (2, "tile")])
+def test_engine_prefault_gives_identical_files(tmp_path, monkeypatch, n_gpus, partition):
+    # Config::prefault (here through GELEX_B200_PREFAULT): the .bin exists from the start of the pass and its pages are populated while the
+    # GPU accumulates; AD mode = two files, two prefaulters.  Same bytes as the plain run.
+    monkeypatch.setenv("GELEX_B200_OVERSUBSCRIBE", "1")
+    n, m = 4100, 1024
+    payload = g.synth_bed_host(n, 0, m, 43, 0.01)
+    plink_io.write_plink(tmp_path / "d", payload, [("F", f"s{i:05d}") for i in range(n)], ["1"] * m)
+    kw = dict(method="OCH", mode="AD", precision=g.PREC_FP64, n_gpus=n_gpus, partition=partition)
+    engine.grm_run(tmp_path / "d", tmp_path / "plain", **kw)
+    monkeypatch.setenv("GELEX_B200_PREFAULT", "1")
+    monkeypatch.setenv("GELEX_B200_WRITER", "mmap")
+    engine.grm_run(tmp_path / "d", tmp_path / "pf", **kw)
+    for k in ("add", "dom"):
+        assert (tmp_path / f"pf.{k}.bin").read_bytes() == (tmp_path / f"plain.{k}.bin").read_bytes(), k
+        assert (tmp_path / f"pf.{k}.id").read_bytes() == (tmp_path / f"plain.{k}.id").read_bytes(), k
 
 
 REF_BINDING = Path(__file__).resolve().parent.parent / "oracle" / "_ref" / "gelex_ref_b200"

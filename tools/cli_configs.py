@@ -101,7 +101,7 @@ def main():
                "cli_wall_s": wall, "effective_tflops_wall": flops / wall / 1e12, "bed_bytes": m * ((n + 3) // 4),
                "out_files": len(seen), "out_bytes": int(sum(seen.values())), "all_sizes_ok": all(v == expect_bytes for v in seen.values()),
                "device_line": dev_line[0].strip() if dev_line else None, "input_gen_s": gen_s, "dir": str(d),
-               "writer": os.environ.get("GELEX_B200_WRITER", "auto"), "bed_relay": os.environ.get("GELEX_B200_BED_RELAY", "0")}
+               "writer": os.environ.get("GELEX_B200_WRITER", "auto"), "bed_relay": os.environ.get("GELEX_B200_BED_RELAY", "0"), "prefault": os.environ.get("GELEX_B200_PREFAULT", "0")}
         if r.returncode != 0:
             rec["stderr"] = r.stderr[-800:]
             rec["stdout"] = r.stdout[-800:]

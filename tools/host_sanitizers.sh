@@ -22,7 +22,8 @@ int main() {
     try { GrmEngine::relay_selftest(200, 4, 2, 512, 37); } catch (const std::exception& e) { std::printf("expected: %s\n", e.what()); }
     bool mapped = false;
     for (int tiles = 0; tiles < 2; ++tiles)
-        for (auto mode : {WriterMode::Pwrite, WriterMode::Mmap}) GrmEngine::writer_selftest("/dev/shm/tsan_w.bin", 4500, tiles != 0, 3, 2, mode, &mapped);
+        for (auto mode : {WriterMode::Pwrite, WriterMode::Mmap})
+            for (int prefault : {0, 3}) GrmEngine::writer_selftest("/dev/shm/tsan_w.bin", 4500, tiles != 0, 3, 2, mode, &mapped, prefault);
     std::printf("bad=%ld\n", bad);
     return bad != 0;
 }

@@ -10,7 +10,8 @@ timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --mast
 for w in pwrite mmap; do
   GELEX_B200_WRITER=$w timeout 200 python tools/cli_configs.py C2 --gpus 8 > gpurun_out/r02n8_c2_$w.jsonl 2> gpurun_out/r02n8_c2_$w.err; echo rc=$?; cat gpurun_out/r02n8_c2_$w.jsonl
 done
+GELEX_B200_WRITER=mmap GELEX_B200_PREFAULT=1 timeout 200 python tools/cli_configs.py C2 --gpus 8 > gpurun_out/r02n8_c2_prefault.jsonl 2> gpurun_out/r02n8_c2_prefault.err; echo rc=$?; cat gpurun_out/r02n8_c2_prefault.jsonl
 GELEX_B200_WRITER=pwrite timeout 300 python tools/cli_configs.py C5 --gpus 8 > gpurun_out/r02n8_c5_pwrite.jsonl 2> gpurun_out/r02n8_c5_pwrite.err; echo rc=$?; cat gpurun_out/r02n8_c5_pwrite.jsonl
 GELEX_B200_WRITER=mmap timeout 300 python tools/cli_configs.py C5 --gpus 8 > gpurun_out/r02n8_c5_mmap.jsonl 2> gpurun_out/r02n8_c5_mmap.err; echo rc=$?; cat gpurun_out/r02n8_c5_mmap.jsonl
-GELEX_B200_WRITER=mmap GELEX_B200_BED_RELAY=1 timeout 300 python tools/cli_configs.py C5 --gpus 8 > gpurun_out/r02n8_c5_relay.jsonl 2> gpurun_out/r02n8_c5_relay.err; echo rc=$?; cat gpurun_out/r02n8_c5_relay.jsonl
+GELEX_B200_WRITER=mmap GELEX_B200_PREFAULT=1 GELEX_B200_BED_RELAY=1 timeout 300 python tools/cli_configs.py C5 --gpus 8 > gpurun_out/r02n8_c5_relay.jsonl 2> gpurun_out/r02n8_c5_relay.err; echo rc=$?; cat gpurun_out/r02n8_c5_relay.jsonl
 timeout 400 python tools/cli_configs.py C4 --gpus 8 > gpurun_out/r02n8_c4.jsonl 2> gpurun_out/r02n8_c4.err; echo rc=$?; cat gpurun_out/r02n8_c4.jsonl
