@@ -107,7 +107,8 @@ int cmd_grm(int argc, char** argv)
     cfg.chunk_size = std::atoi(argv[7]);
     int threads = std::atoi(argv[8]);
     set_threads(threads);
-    size_t n = 0, m = 0;
+    size_t n = 0, m = 0, total_snps = 0, num_files = 0, progress_events = 0, progress_sum = 0;
+    std::string file_pattern;
     auto t0 = Clock::now();
     gelex::GrmEngine engine(cfg);
     engine.compute(
@@ -118,11 +119,29 @@ int cmd_grm(int argc, char** argv)
                 n = d->num_samples;
                 m = d->num_snps;
             }
+            else if (const auto* s = std::get_if<gelex::GrmComputeStartedEvent>(&ev)) { total_snps = s->total_snps; }
+            else if (const auto* p = std::get_if<gelex::GrmProgressEvent>(&ev))
+            {
+                if (!p->done)
+                {
+                    ++progress_events;
+                    progress_sum += p->current;
+                }
+            }
+            else if (const auto* f = std::get_if<gelex::GrmFilesWrittenEvent>(&ev))
+            {
+                num_files = f->num_files;
+                file_pattern = f->file_pattern;
+            }
         });
     auto t1 = Clock::now();
+    // events as the CLI reporter receives them (grm_event.h:28-67): totals, the files-written summary, and the per-chunk progress
+    // stream reduced to its count and the sum of `current`
     std::printf(
-        "{\"cmd\":\"grm\",\"n\":%zu,\"m\":%zu,\"wall_s\":%.6f,\"threads\":%d,\"blas\":\"%s\"}\n",
-        n, m, secs(t0, t1), omp_get_max_threads(), blas_name().c_str());
+        "{\"cmd\":\"grm\",\"n\":%zu,\"m\":%zu,\"wall_s\":%.6f,\"threads\":%d,\"blas\":\"%s\",\"total_snps\":%zu,\"num_files\":%zu,"
+        "\"file_pattern\":\"%s\",\"progress_events\":%zu,\"progress_sum\":%zu}\n",
+        n, m, secs(t0, t1), omp_get_max_threads(), blas_name().c_str(), total_snps, num_files, file_pattern.c_str(), progress_events,
+        progress_sum);
     return 0;
 }
 

@@ -10,6 +10,7 @@ Checked per case: the same inputs are accepted or rejected; a rejection carries 
 (so validation happens in the reference's ORDER: FAM, BIM line count, BED, BIM records - grm.cpp:36-40, bed_pipe.cpp:69-98,
 grm_engine.cpp:52-70); an accepted case plans the files the reference wrote (names incl. `chr<NAME>` of re-appearing chromosomes),
 the same matrix size n(n+1)/2 (sort + de-duplicate of the IDs), and the same `.id` rows in the same order."""
+import json
 import os
 import random
 import shutil
@@ -126,6 +127,16 @@ def test_front_half_agrees_with_the_reference_on_quirky_inputs(tmp_path, seed):
         accepted += 1
         p = engine.plan(d / "t", mode=mode, loco=loco)
         assert sorted({f"ref.{name}.{ext}" for name, _, _ in p["items"] for ext in ("bin", "id")}) == ref_files, ctx
+        # the events the reference's reporter received (grm_event.h:28-67) against what this engine's plan emits: dataset summary,
+        # total work, files-written summary, and the per-chunk progress stream (one event per work item and chunk, `current` counted
+        # inside the item - grm.h:124-130; the one-pass engine emits the same events, add and dom interleaved)
+        ev = json.loads(r.stdout.decode().strip().splitlines()[-1])
+        assert (ev["n"], ev["m"]) == (p["n_out"], p["m"]), ctx
+        assert ev["total_snps"] == sum(e - b for _, b, e in p["items"]), ctx
+        assert ev["num_files"] == 2 * len(p["items"]), ctx
+        assert ev["file_pattern"] == str(d / "ref") + p["pattern_suffix"], ctx
+        currents = [min(s + chunk, e) - b for _, b, e in p["items"] for s in range(b, e, chunk)]
+        assert (ev["progress_events"], ev["progress_sum"]) == (len(currents), sum(currents)), ctx
         for f in ref_files:
             if f.endswith(".bin"):
                 assert (d / f).stat().st_size == p["n_out"] * (p["n_out"] + 1) // 2 * 4, ctx
