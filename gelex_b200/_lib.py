@@ -223,6 +223,10 @@ class Accumulator:
     def push_device(self, dev_ptr: int, snp_begin: int, snp_count: int):
         self._check(self.lib.ggrm_push_device(self.h, C.c_void_p(dev_ptr), snp_begin, snp_count, self.bpv))
 
+    def wait_copies(self):
+        """Every copy enqueued by earlier push calls has read its source (a staging slot may be overwritten)."""
+        self._check(self.lib.ggrm_wait_copies(self.h))
+
     def finish(self):
         self._check(self.lib.ggrm_finish(self.h))
 
@@ -438,3 +442,38 @@ def ipc_close(ptr: int, device=0):
 
 def device_count() -> int:
     return load().ggrm_device_count()
+
+
+class Stage:
+    """Device staging slots (ggrm_stage_*): one host upload of a BED chunk that several handles take with push_device."""
+
+    def __init__(self, slot_bytes: int, n_slots: int = 2, device: int = 0):
+        self.lib = load()
+        self.h = C.c_void_p()
+        st = self.lib.ggrm_stage_create(device, int(slot_bytes), int(n_slots), C.byref(self.h))
+        if st != 0:
+            raise GrmError(st, self.lib.ggrm_last_error(None).decode())
+
+    def upload(self, slot: int, payload: np.ndarray):
+        payload = np.ascontiguousarray(payload, dtype=np.uint8)
+        st = self.lib.ggrm_stage_upload(self.h, int(slot), _ptr(payload), payload.size)
+        if st != 0:
+            raise GrmError(st, self.lib.ggrm_last_error(None).decode())
+
+    def slot(self, slot: int) -> int:
+        p = C.c_void_p()
+        st = self.lib.ggrm_stage_slot(self.h, int(slot), C.byref(p))
+        if st != 0:
+            raise GrmError(st, self.lib.ggrm_last_error(None).decode())
+        return p.value
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.ggrm_stage_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()

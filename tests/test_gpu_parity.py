@@ -684,3 +684,36 @@ def test_fp64_path_agrees_with_oracle_on_random_small_inputs(seed):
         ok = ~np.isnan(want)
         if ok.any():
             assert np.max(np.abs(got[ok] - want[ok])) <= 1e-10 * max(1.0, float(np.max(np.abs(want[ok])))), ctx
+
+
+@pytest.mark.skipif(os.environ.get("GELEX_B200_TEST_UNVERIFIED") != "1",
+                    reason="added after the round's GPU minutes were spent: opt in with GELEX_B200_TEST_UNVERIFIED=1 (tools/r02_first_run.sh)")
+def test_stage_slots_feed_two_handles_like_host_pushes():
+    # ggrm_stage_* + ggrm_push_device + ggrm_wait_copies (the 2D-tile BED relay at the ABI level): every chunk is uploaded once into one
+    # of two staging slots, two handles take it from there, and a slot is only refilled after both have waited for their copies -
+    # bit-identical to two handles fed by ggrm_push from host memory
+    from gelex_b200._lib import Stage
+
+    n, m, chunk = 1500, 1200, 100
+    bed = g.synth_bed_host(n, 0, m, 47, 0.02)
+    kw = dict(method=1, precision=g.PREC_FP64, chunk_snps=256)
+    ref = g.Accumulator(n, m, **kw)
+    a, b = g.Accumulator(n, m, **kw), g.Accumulator(n, m, **kw)
+    with Stage(chunk * bed.shape[1], n_slots=2) as st:
+        for j, s in enumerate(range(0, m, chunk)):
+            ref.push(bed[s:s + chunk], s)
+            st.upload(j % 2, bed[s:s + chunk])
+            for acc in (a, b):
+                acc.push_device(st.slot(j % 2), s, min(chunk, m - s))
+            for acc in (a, b):
+                acc.wait_copies()
+        for acc in (ref, a, b):
+            acc.finish()
+    want, _ = ref.fetch(g.KIND_ADD, g.GROUP_WHOLE, dtype=np.float64)
+    for acc in (a, b):
+        got, _ = acc.fetch(g.KIND_ADD, g.GROUP_WHOLE, dtype=np.float64)
+        assert np.array_equal(got, want)
+    with pytest.raises(g.GrmError):
+        Stage(0)
+    for acc in (ref, a, b):
+        acc.close()

@@ -5,7 +5,7 @@
 set -x
 mkdir -p gpurun_out
 timeout 420 python -m pytest tests -m gpu -x -q > gpurun_out/r02a_pytest.log 2>&1; echo rc=$?; tail -5 gpurun_out/r02a_pytest.log
-GELEX_B200_TEST_UNVERIFIED=1 timeout 300 python -m pytest tests -m gpu -q -k "bed_relay or writer_modes or random_small_inputs or reference_pipe_files or reappearing or reference_host_code or prefault" > gpurun_out/r02a_unverified.log 2>&1; echo rc=$?; tail -8 gpurun_out/r02a_unverified.log
+GELEX_B200_TEST_UNVERIFIED=1 timeout 300 python -m pytest tests -m gpu -q -k "bed_relay or writer_modes or random_small_inputs or reference_pipe_files or reappearing or reference_host_code or prefault or stage_slots" > gpurun_out/r02a_unverified.log 2>&1; echo rc=$?; tail -8 gpurun_out/r02a_unverified.log
 timeout 60 python -c "import __graft_entry__ as e; e.smoke()" > gpurun_out/r02a_smoke.log 2>&1; echo rc=$?; cat gpurun_out/r02a_smoke.log
 timeout 300 python bench.py --gpus 1 --steps 3 --warmup 3 > gpurun_out/r02a_bench.json 2> gpurun_out/r02a_bench.err; echo rc=$?; cat gpurun_out/r02a_bench.json
 timeout 300 python bench.py --impl reference --gpus 1 --steps 3 --warmup 3 > gpurun_out/r02a_reference.json 2> gpurun_out/r02a_reference.err; echo rc=$?; cat gpurun_out/r02a_reference.json
