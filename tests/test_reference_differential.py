@@ -146,10 +146,14 @@ def test_front_half_agrees_with_the_reference_on_quirky_inputs(tmp_path, seed):
         assert len(raw) == p["n_raw"], ctx
         rows = {}
         for i, ln in enumerate(raw):
-            toks = [t for t in ln.rstrip("\r").split(delim) if t != ""]
+            # parse_id (src/io/parser.cpp:63-82): FID = up to the first delimiter, IID = up to the next one; nothing is trimmed
+            # (the '\r' of a CRLF file stays in a last column, "a.b\t\r" is FID "a.b" with IID "\r")
+            p1 = ln.find(delim)
+            p2 = ln.find(delim, p1 + 1)
             if p["raw_to_out"][i] >= 0:
-                rows[int(p["raw_to_out"][i])] = toks[0] + "\t" + toks[1] + "\n"
-        assert "".join(rows[t] for t in range(p["n_out"])) == (d / [f for f in ref_files if f.endswith(".id")][0]).read_text(), ctx
+                rows[int(p["raw_to_out"][i])] = ln[:p1] + "\t" + (ln[p1 + 1:p2] if p2 >= 0 else ln[p1 + 1:]) + "\n"
+        ref_id = (d / [f for f in ref_files if f.endswith(".id")][0]).read_bytes().decode()
+        assert "".join(rows[t] for t in range(p["n_out"])) == ref_id, ctx
         shutil.rmtree(d)
     assert accepted >= 8 and rejected >= 10  # the generator exercises both sides
 
