@@ -1,16 +1,22 @@
 #!/usr/bin/env python
-"""bench.py — headline benchmark of the `gelex grm` hot path (BASELINE.json): Yang additive GRM (StandardizeHWE + Add),
-50 000 samples x 500 000 SNPs, synthetic PLINK BED payload (p~U(0.05,0.5), HWE, 1 % missing).
+"""bench.py — headline benchmark of the `gelex grm` hot path (BASELINE.json).
 
-  python bench.py --gpus N --steps K --warmup W            # this repo: B200 engine through the C ABI
-  python bench.py --impl reference --gpus N --steps K ...  # the reference's own CPU path (oracle/_ref) on the host cores
+  python bench.py --gpus N --steps K --warmup W                 # this repo: B200 engine through the C ABI, config C2
+  python bench.py --config c4 --gpus N ...                      # C4: 22 LOCO chromosome partials + whole, 50 000 x 600 000
+  python bench.py --impl reference --gpus N --steps K ...       # the reference's own CPU path (oracle/_ref) on the host cores
 
-A "step" = one full GRM build (one pass of decode -> counts/frequencies -> standardise -> SYRK over every SNP).
-  value : effective TFLOP/s = n(n+1)m / t with the packed BED already resident in HBM (6.25 GB > L2, so no L2 flush needed)
-  e2e   : same metric through ggrm_push (pinned HOST payload -> H2D inside the timed region) .. ggrm_finish .. ggrm_fetch
-          (full float32 lower triangle, the .bin payload, D2H into host memory)
-N > 1   : SNP-sharded ("strong" scaling: total work fixed), one process per GPU, partial GRMs summed over NVLink
-          (NCCL reduce via torch.distributed) inside the timed region.
+Workloads (synthetic packed PLINK BED, p~U(0.05,0.5), HWE, 1 % missing, counter-based generator):
+  c2 (default)  configs[1]: Yang additive GRM (StandardizeHWE + Add), 50 000 samples x 500 000 SNPs.
+                N > 1: SNP shards ("strong" scaling), partial GRMs reduce-scattered over NVLink peer memory, band-pipelined.
+  c4            configs[3]: 22 per-chromosome partial GRMs + the whole-genome GRM (= their sum), 50 000 x 600 000, one pass.
+                N > 1: whole chromosomes dealt to ranks by LPT (no reduce for the partials), one reduce-scatter for the whole.
+A "step" = one full build (decode -> counts / frequencies -> standardise -> SYRK over every SNP).
+  value : effective TFLOP/s = n(n+1)m / t with the packed BED already resident in HBM (6-7.5 GB > L2: no flush needed)
+  e2e   : the same through ggrm_push from pinned HOST memory (H2D inside the timed region) .. ggrm_fetch of every output matrix's
+          float32 lower triangle (the .bin payload) into pinned host memory
+  wall  : `gelex-b200 grm` on real files, process start -> files closed (SURVEY 8d t_wall), with its phase split
+  cpu_baseline / --impl reference : oracle/_ref/gelex_ref = the UNMODIFIED reference (GrmEngine::compute, OpenBLAS dsyrk) on the host
+          cores, on a FIXED bounded sample of the workload, plus one like-for-like pair on configs[0] (C1), wall seconds both arms.
 One JSON line on stdout (rank 0)."""
 import argparse
 import ctypes
@@ -28,17 +34,36 @@ ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 sys.path.insert(0, str(ROOT / "tests"))
 
-N_SAMPLES = int(os.environ.get("GGRM_BENCH_N", 50000))
-M_SNPS = int(os.environ.get("GGRM_BENCH_M", 500000))
-SEED = 20261104 + 2
 MISSING = 0.01
 METHOD = 1  # StandardizeHWE ("Yang" additive)
-METRIC = "GRM build effective TFLOP/s (n(n+1)m FLOPs / wall-s), Yang additive GRM, 50k samples x 500k SNPs"
 REF_BIN = ROOT / "oracle" / "_ref" / "gelex_ref"
+CLI_BIN = ROOT / "gelex_b200" / "gelex-b200"
+CHR_MB = [248, 242, 198, 190, 182, 171, 159, 145, 138, 134, 135, 133, 114, 107, 102, 90, 83, 80, 59, 64, 47, 51]  # GRCh38 autosomes
+
+CONFIGS = {
+    "c2": dict(tag="configs[1]", n=int(os.environ.get("GGRM_BENCH_N", 50000)), m=int(os.environ.get("GGRM_BENCH_M", 500000)), loco=False, seed=20261104 + 2,
+               metric="GRM build effective TFLOP/s (n(n+1)m FLOPs / wall-s), Yang additive GRM, 50k samples x 500k SNPs",
+               what="Yang additive GRM (StandardizeHWE+Add)"),
+    "c4": dict(tag="configs[3]", n=int(os.environ.get("GGRM_BENCH_N", 50000)), m=int(os.environ.get("GGRM_BENCH_M", 600000)), loco=True, seed=20261104 + 4,
+               metric="GRM build effective TFLOP/s (n(n+1)m FLOPs / wall-s), 22 LOCO chromosome partial GRMs + whole-genome Yang additive GRM, 50k samples x 600k SNPs",
+               what="22 per-chromosome partial GRMs + whole-genome GRM (StandardizeHWE+Add), one pass"),
+}
+C1 = dict(n=2000, m=50000, seed=20261104 + 1)       # configs[0]: the like-for-like pair
+CPU_SAMPLE = (8000, 30000)                          # fixed bounded sample of the workload for the CPU arm (about 2-3 s per step)
 
 
 def flops(n, m):
     return float(n) * (n + 1.0) * m
+
+
+def chromosome_runs(m):
+    """22 contiguous runs, lengths proportional to the human autosomes."""
+    cuts, acc = [0], 0
+    for mb in CHR_MB:
+        acc += mb
+        cuts.append(round(m * acc / sum(CHR_MB)))
+    cuts[-1] = m
+    return [(cuts[i], cuts[i + 1]) for i in range(22)]
 
 
 # ---------------------------------------------------------------------------------------------------------------- clocks
@@ -83,8 +108,8 @@ class ClockSampler:
 
 
 def bind_to_gpu_numa_node(local_rank):
-    """Multi-rank runs: keep this rank's threads (and, by first touch, its pinned buffers) on the NUMA node its GPU hangs off, so
-    the eight ranks' H2D/D2H streams do not all cross the socket interconnect.  Best effort; returns a note for the JSON line."""
+    """Multi-rank runs: keep this rank's threads (and, by first touch, its pinned buffers) on the NUMA node its GPU hangs off.
+    Best effort; returns a note for the JSON line."""
     try:
         bus = subprocess.run(["nvidia-smi", f"--id={local_rank}", "--query-gpu=pci.bus_id", "--format=csv,noheader"], capture_output=True,
                              text=True, timeout=20).stdout.strip().lower()
@@ -106,76 +131,215 @@ def bind_to_gpu_numa_node(local_rank):
         return f"numa: not bound ({type(e).__name__})"
 
 
-# ---------------------------------------------------------------------------------------------------------------- CPU reference arm
-def cpu_threads():
+# ---------------------------------------------------------------------------------------------------------------- host facts
+def logical_cpus():
     return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
 
 
-def write_sample_plink(prefix, n, m):
-    """Synthetic PLINK triple for the CPU legs (same generator, same seed as the GPU run; FAM in sorted order = dense path)."""
+def physical_cores():
+    """Distinct cores among the CPUs this process may run on (SMT siblings counted once), from the kernel's topology files."""
+    cpus = sorted(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else list(range(os.cpu_count() or 1))
+    seen = set()
+    for c in cpus:
+        try:
+            sib = (Path(f"/sys/devices/system/cpu/cpu{c}/topology") / "thread_siblings_list").read_text().strip()
+        except OSError:
+            sib = str(c)
+        seen.add(sib)
+    return max(1, len(seen))
+
+
+def cpu_model():
+    try:
+        for line in Path("/proc/cpuinfo").read_text().splitlines():
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
+def fs_of(path):
+    try:
+        out = subprocess.run(["stat", "-f", "-c", "%T", str(path)], capture_output=True, text=True, timeout=10).stdout.strip()
+        return out or "unknown"
+    except Exception:  # noqa: BLE001
+        return "unknown"
+
+
+# ---------------------------------------------------------------------------------------------------------------- PLINK triples
+def write_triple(prefix, n, m, payload_rows, chrom_ranges):
+    """payload_rows: iterable of uint8 arrays (row blocks of the packed BED).  FAM in sorted order (the reference's dense path)."""
+    prefix = Path(prefix)
+    prefix.parent.mkdir(parents=True, exist_ok=True)
+    with open(str(prefix) + ".bed", "wb") as f:
+        f.write(bytes([0x6C, 0x1B, 0x01]))
+        import numpy as np
+
+        for block in payload_rows:
+            f.write(np.ascontiguousarray(block, dtype=np.uint8))
+    with open(str(prefix) + ".fam", "w") as f:
+        f.write("".join(f"F\ts{i:07d}\t0\t0\t1\t-9\n" for i in range(n)))
+    with open(str(prefix) + ".bim", "w") as f:
+        for ci, (b, e) in enumerate(chrom_ranges):
+            f.write("".join(f"{ci + 1}\tsnp{j + 1}\t0\t{1000 + j}\tA\tG\n" for j in range(b, e)))
+
+
+def synth_rows_numpy(n, m, seed):
+    """CPU arm: the generator restated in numpy (tests/synth_np.py), so this arm never maps the product library."""
+    import synth_np
+
+    step = 4096
+    for s in range(0, m, step):
+        yield synth_np.synth_bed(n, s, min(step, m - s), seed, MISSING, threads=min(16, logical_cpus()))
+
+
+def synth_rows_device(n, m, seed, device=0):
+    """GPU arm: the same bytes from the device generator (csrc/synth.h), 1 GiB at a time."""
+    import torch
+
     import gelex_b200 as g
-    import plink_io
 
-    payload = g.synth_bed_host(n, 0, m, SEED, MISSING)
-    bounds = [round(m * i / 22) for i in range(23)]
-    chroms = [str(c + 1) for c in range(22) for _ in range(bounds[c + 1] - bounds[c])]
-    plink_io.write_plink(prefix, payload, [("F", f"s{i:07d}") for i in range(n)], chroms)
-    return payload
+    bpv = (n + 3) // 4
+    step = max(1, (1 << 30) // bpv)
+    d = torch.empty(min(step, m) * bpv, dtype=torch.uint8, device=f"cuda:{device}")
+    for s in range(0, m, step):
+        c = min(step, m - s)
+        g.synth_bed_device(d.data_ptr(), n, s, c, seed, MISSING, device=device)
+        yield d[: c * bpv].cpu().numpy()
+    del d
+    torch.cuda.empty_cache()
 
 
-def run_ref_once(prefix, out, threads, chunk=10000):
-    r = subprocess.run([str(REF_BIN), "grm", str(prefix), str(out), str(METHOD), "A", "0", str(chunk), str(threads)],
-                       capture_output=True, text=True, check=True)
+# ---------------------------------------------------------------------------------------------------------------- CPU reference arm
+def run_ref(args_list):
+    r = subprocess.run([str(REF_BIN)] + [str(a) for a in args_list], capture_output=True, text=True, check=True)
     return json.loads(r.stdout.strip().splitlines()[-1])
 
 
-def run_port_once(payload, n, threads):
+def run_port_once(prefix, n, threads):
+    """Fallback when oracle/_ref is absent: the plain-C oracle port (kind "port")."""
+    import numpy as np
+
     import oracle_lib as o
 
+    payload = np.fromfile(str(prefix) + ".bed", dtype=np.uint8)[3:]
     os.environ["OMP_NUM_THREADS"] = str(threads)
     t0 = time.time()
     o.grm_compute(payload, n, METHOD, 0, chunk=2000)
     return {"wall_s": time.time() - t0, "blas": "none (plain C oracle port)"}
 
 
-def cpu_sample_shape(budget_s, threads):
-    """Pick a bounded sample (n_s, m_s) of the workload that costs about budget_s seconds on this host."""
-    n_s = int(os.environ.get("GGRM_BENCH_CPU_N", 8000))
-    tmp = Path(tempfile.mkdtemp(prefix="ggrm_probe_"))
-    try:
-        have_ref = REF_BIN.exists()
-        pn, pm = (2000, 4000) if have_ref else (600, 1500)
-        payload = write_sample_plink(tmp / "probe", pn, pm)
-        t = run_ref_once(tmp / "probe", tmp / "o", threads)["wall_s"] if have_ref else run_port_once(payload, pn, threads)["wall_s"]
-        rate = flops(pn, pm) / max(t, 1e-3)
-    finally:
-        shutil.rmtree(tmp, ignore_errors=True)
-    if not have_ref:
-        n_s = 1500
-    m_s = int(min(50000, max(2000, budget_s * rate * 1.5 / (n_s * (n_s + 1.0)))))  # larger problems run closer to BLAS peak
-    return n_s, m_s
-
-
-def cpu_leg(steps, warmup, budget_s):
-    """Times the reference's own CPU implementation (oracle/_ref, else the oracle port) on a bounded sample."""
-    threads = cpu_threads()
-    n_s, m_s = cpu_sample_shape(budget_s, threads)
+def cpu_leg(steps, warmup, cfg, payload_rows_fn):
+    """Times the reference's own CPU implementation (oracle/_ref, else the oracle port) on the fixed bounded sample, with the
+    stage split, one run at gelex's default -t hw/2 (apps/cli/grm/grm_args.cpp:54-59) and the C1 like-for-like run."""
+    have_ref = REF_BIN.exists()
+    kind = "reference" if have_ref else "port"
+    phys, logical = physical_cores(), logical_cpus()
+    n_s, m_s = CPU_SAMPLE if have_ref else (1500, 3000)
     tmp = Path(tempfile.mkdtemp(prefix="ggrm_cpu_"))
+    out = {}
     try:
-        payload = write_sample_plink(tmp / "sample", n_s, m_s)
-        kind = "reference" if REF_BIN.exists() else "port"
+        write_triple(tmp / "sample", n_s, m_s, payload_rows_fn(n_s, m_s, cfg["seed"]), [(round(m_s * i / 22), round(m_s * (i + 1) / 22)) for i in range(22)])
         walls, info = [], {}
         for i in range(warmup + steps):
-            info = run_ref_once(tmp / "sample", tmp / "out", threads) if kind == "reference" else run_port_once(payload, n_s, threads)
+            info = run_ref(["grm", tmp / "sample", tmp / "out", METHOD, "A", 0, 10000, phys]) if have_ref else run_port_once(tmp / "sample", n_s, phys)
             if i >= warmup:
                 walls.append(info["wall_s"])
-    finally:
+        wall = sum(walls) / len(walls)
+        out = {"value": flops(n_s, m_s) / wall / 1e12, "unit": "TFLOP/s", "cores": phys, "kind": kind,
+               "sample": f"{n_s} samples x {m_s} SNPs of the same synthetic workload (fixed shape, same generator and seed), GrmEngine::compute incl. "
+                         f".bin/.id write, chunk 10000, {phys} threads = physical cores",
+               "wall_s": wall, "steps_timed": len(walls), "physical_cores": phys, "logical_cpus": logical, "cpu_model": cpu_model(),
+               "blas": info.get("blas", ""), "same_config": False}
+        if have_ref:
+            st = run_ref(["stages", tmp / "sample", METHOD, "A", 10000, phys])
+            out["stages_s"] = {k: st[k] for k in ("decode_s", "standardise_s", "dsyrk_s", "wall_s")}
+            out["stages_s"]["write_and_setup_s"] = max(0.0, wall - st["wall_s"])
+            half = max(1, logical // 2)  # gelex's own default: -t hardware_concurrency / 2
+            hw = run_ref(["grm", tmp / "sample", tmp / "out_half", METHOD, "A", 0, 10000, half])
+            out["gelex_default_threads"] = {"threads": half, "wall_s": hw["wall_s"], "value": flops(n_s, m_s) / hw["wall_s"] / 1e12}
+            # like for like: configs[0] (C1) is small enough for both arms; wall seconds of the whole command
+            write_triple(tmp / "c1", C1["n"], C1["m"], payload_rows_fn(C1["n"], C1["m"], C1["seed"]), chromosome_runs(C1["m"]))
+            t0 = time.time()
+            c1 = run_ref(["grm", tmp / "c1", tmp / "c1_ref", METHOD, "A", 0, 10000, phys])
+            out["like_for_like"] = {"config": f"configs[0] C1: Yang additive GRM, {C1['n']} samples x {C1['m']} SNPs, real files in and out", "same_config": True,
+                                    "reference_cli_wall_s": time.time() - t0, "reference_compute_wall_s": c1["wall_s"], "reference_threads": phys,
+                                    "fs": fs_of(tmp)}
+            out["_c1_prefix"] = str(tmp / "c1")
+        return out, tmp
+    except Exception:
         shutil.rmtree(tmp, ignore_errors=True)
-    wall = sum(walls) / len(walls)
-    return {"value": flops(n_s, m_s) / wall / 1e12, "unit": "TFLOP/s", "cores": threads, "kind": kind,
-            "sample": f"{n_s} samples x {m_s} SNPs of the same synthetic workload, GrmEngine::compute incl. .bin/.id write, chunk 10000, "
-                      f"{threads} threads, {info.get('blas', '')}".strip(),
-            "wall_s": wall}, n_s, m_s
+        raise
+
+
+def parse_cli_report(stdout):
+    """The CLI's closing lines: '  Device      : accumulate A ms (SYRK S ms), read-out + file write W s, engine wall E s' and
+    '  Host phases : name a-b s | ...'."""
+    import re
+
+    rep = {}
+    for ln in stdout.splitlines():
+        if "Device      :" in ln:
+            mm = re.search(r"accumulate ([\d.]+) ms \(SYRK ([\d.]+) ms\), read-out \+ file write ([\d.]+) s, engine wall ([\d.]+) s", ln)
+            if mm:
+                rep.update(accumulate_s=float(mm.group(1)) / 1e3, syrk_s=float(mm.group(2)) / 1e3, write_s=float(mm.group(3)), engine_wall_s=float(mm.group(4)))
+        elif "Host phases :" in ln:
+            ph = {}
+            for part in ln.split(":", 1)[1].split("|"):
+                mm = re.match(r"\s*(.+?) ([\d.]+)-([\d.]+) s\s*$", part)
+                if mm:
+                    ph[mm.group(1)] = [float(mm.group(2)), float(mm.group(3))]
+            rep["phases_s"] = ph
+    return rep
+
+
+def run_cli(prefix, out_prefix, gpus, precision, loco=False):
+    cmd = [str(CLI_BIN), "grm", "-b", str(prefix), "-o", str(out_prefix), "--gm", "SH", "--add", "--precision", precision, "--gpus", str(gpus)]
+    if loco:
+        cmd += ["--loco", "--with-whole"]
+    t0 = time.time()
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    wall = time.time() - t0
+    rep = parse_cli_report(r.stdout)
+    rep.update(cli_wall_s=wall, rc=r.returncode)
+    if r.returncode != 0:
+        rep["stderr"] = (r.stderr or r.stdout)[-600:]
+    return rep
+
+
+def cli_wall_leg(cfg, gpus, precision, device=0):
+    """t_wall of SURVEY 8d: `gelex-b200 grm` on real files (tmpfs when it has room), process start -> files closed."""
+    n, m = cfg["n"], cfg["m"]
+    bed_bytes = m * ((n + 3) // 4)
+    out_bytes = n * (n + 1) // 2 * 4 * (23 if cfg["loco"] else 1)
+    base = None
+    for cand in ("/dev/shm", tempfile.gettempdir()):
+        try:
+            st = os.statvfs(cand)
+            if st.f_bavail * st.f_frsize > (bed_bytes + out_bytes) * 1.05 + (1 << 30):
+                base = cand
+                break
+        except OSError:
+            continue
+    if base is None:
+        return {"unavailable": f"no file system with {(bed_bytes + out_bytes) / 1e9:.0f} GB free for real files"}
+    d = Path(tempfile.mkdtemp(prefix="ggrm_wall_", dir=base))
+    try:
+        t0 = time.time()
+        write_triple(d / "in", n, m, synth_rows_device(n, m, cfg["seed"], device), chromosome_runs(m))
+        gen_s = time.time() - t0
+        rep = run_cli(d / "in", d / "out", gpus, precision, loco=cfg["loco"])
+        sizes = [p.stat().st_size for p in d.glob("out.*.bin")]
+        ph = rep.get("phases_s", {})
+        rep.update({"fs": fs_of(d), "dir": base, "input_gen_s": gen_s, "bed_bytes": bed_bytes, "out_files": len(sizes), "out_bytes": int(sum(sizes)),
+                    "all_sizes_ok": bool(sizes) and all(s == n * (n + 1) // 2 * 4 for s in sizes),
+                    "startup_s": ph.get("push", [None])[0],
+                    "effective_tflops_wall": flops(n, m) / rep["cli_wall_s"] / 1e12,
+                    "command": f"gelex-b200 grm -b in -o out --gm SH --add --precision {precision} --gpus {gpus}" + (" --loco --with-whole" if cfg["loco"] else "")})
+        return rep
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
 
 
 # ---------------------------------------------------------------------------------------------------------------- GPU arm
@@ -194,13 +358,18 @@ def peaks():
     return 1400.0, 1590.0, "fallback"
 
 
+DTYPE_NOTE = {"fp16": "f16 operands, f32 accumulate (tcgen05 kind::f16)", "bf16": "bf16 operands, f32 accumulate (tcgen05 kind::f16)", "fp64": "f64 (DMMA)"}
+
+
 def gpu_arm(args):
     import numpy as np
     import torch
     import torch.distributed as dist
 
     import gelex_b200 as g
+    from gelex_b200.sharding import chromosome_shards, row_slices, snp_shards
 
+    cfg = CONFIGS[args.config]
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -210,26 +379,36 @@ def gpu_arm(args):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    n, m = N_SAMPLES, M_SNPS
+    n, m = cfg["n"], cfg["m"]
     bpv = (n + 3) // 4
     prec = {"fp16": g.PREC_FP16, "bf16": g.PREC_BF16, "fp64": g.PREC_FP64}[args.precision]
-    # SNP shard of this rank (contiguous, cut on 64-SNP boundaries)
-    from gelex_b200.sharding import snp_shards
+    loco = cfg["loco"]
+    out_elems = g.tri(n)
 
-    s0, s1 = snp_shards(m, world)[rank]
-    ms = s1 - s0
-    d_bed = torch.empty(ms * bpv, dtype=torch.uint8, device="cuda")
-    for s in range(0, ms, 32768):
-        c = min(32768, ms - s)
-        g.synth_bed_device(d_bed.data_ptr() + s * bpv, n, s0 + s, c, SEED, MISSING, device=local)
-    h_bed = torch.empty(ms * bpv, dtype=torch.uint8, pin_memory=True)
+    # ---- what this rank accumulates: SNP ranges [(begin, end)] in ascending order, and (LOCO) the groups they form
+    if loco:
+        chrom = chromosome_runs(m)
+        my_groups = chromosome_shards(chrom, world)[rank]
+        ranges = [chrom[gi] for gi in my_groups]
+        per_rank_snps = [sum(chrom[gi][1] - chrom[gi][0] for gi in grp) for grp in chromosome_shards(chrom, world)]
+    else:
+        s0, s1 = snp_shards(m, world)[rank]
+        ranges = [(s0, s1)]
+        per_rank_snps = [e - b for b, e in snp_shards(m, world)]
+    ms = sum(e - b for b, e in ranges)
+    offs = np.cumsum([0] + [e - b for b, e in ranges])           # row offset of each range inside this rank's payload buffers
+    d_bed = torch.empty(max(1, ms) * bpv, dtype=torch.uint8, device="cuda")
+    for (b, e), o0 in zip(ranges, offs):
+        for s in range(b, e, 32768):
+            c = min(32768, e - s)
+            g.synth_bed_device(d_bed.data_ptr() + int(o0 + s - b) * bpv, n, s, c, cfg["seed"], MISSING, device=local)
+    h_bed = torch.empty(max(1, ms) * bpv, dtype=torch.uint8, pin_memory=True)
     h_bed.copy_(d_bed)
     torch.cuda.synchronize()
-    acc = g.Accumulator(n, m, method=METHOD, precision=prec, device=local)
-    if world > 1:
-        acc.set_push_end(s1)  # this rank stops at the end of its SNP shard: equal slabs inside the shard
-    out_elems = g.tri(n)
-    h_full = torch.empty(out_elems, dtype=torch.float32, pin_memory=True) if (world > 1 and args.reduce == "nccl" and rank == 0) else None
+    acc = g.Accumulator(n, m, method=METHOD, precision=prec, device=local, groups=ranges if loco else None, keep_whole=True)
+    if world > 1 and not loco:
+        acc.set_push_end(ranges[0][1])  # this rank stops at the end of its SNP shard: equal slabs inside the shard
+    h_full = torch.empty(out_elems, dtype=torch.float32, pin_memory=True) if (world > 1 and args.reduce == "nccl" and rank == 0 and not loco) else None
 
     def barrier():
         torch.cuda.synchronize()
@@ -237,14 +416,20 @@ def gpu_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- N > 1: SNP-sharded partial GRMs, then a reduce-scatter by row slices over NVLink peer memory: rank r sums ITS rows
-    # from every peer's accumulator with one kernel of plain P2P loads (ggrm_reduce_peer on CUDA-IPC mapped pointers), and in
-    # the e2e leg fetches only those rows, so the D2H of the 5 GB result is spread over all ranks' PCIe links.
-    from gelex_b200.sharding import row_slices
+    def push_all(dev):
+        for (b, e), o0 in zip(ranges, offs):
+            if dev:
+                acc.push_device(d_bed.data_ptr() + int(o0) * bpv, b, e - b)
+            else:
+                acc.push_ptr(h_bed.data_ptr() + int(o0) * bpv, b, e - b)
 
+    # ---- N > 1: reduce-scatter by row slices over NVLink peer memory: rank r sums ITS rows from every peer's accumulator with one
+    # kernel of plain P2P loads (ggrm_reduce_peer on CUDA-IPC mapped pointers) and, in the e2e leg, fetches only those rows, so the
+    # D2H of the 5 GB result is spread over all ranks' PCIe links.  c2: the blocking form of the first warm-up pass (and of
+    # --reduce peer); c4: how the whole-genome sum of the per-rank chromosome partials is formed.
     r0, r1 = row_slices(n, world)[rank]
     my_out_elems = g.tri(r1) - g.tri(r0)
-    h_out = torch.empty(max(1, my_out_elems), dtype=torch.float32, pin_memory=True)
+    h_out = torch.empty(max(1, out_elems if loco else my_out_elems), dtype=torch.float32, pin_memory=True)
     peers = []
     state = {"ready": False, "slice": (0, 0)}
 
@@ -262,7 +447,7 @@ def gpu_arm(args):
     def reduce_partials():
         if world == 1:
             return
-        if args.reduce == "nccl":
+        if args.reduce == "nccl" and not loco:
             dptr, n_el, eb = acc.accum_buffer(g.KIND_ADD, g.GROUP_WHOLE)
             t = torch.as_tensor(DevPtr(dptr, n_el, "<f4" if eb == 4 else "<f8"), device="cuda")
             dist.reduce(t, dst=0, op=dist.ReduceOp.SUM)
@@ -279,7 +464,7 @@ def gpu_arm(args):
         state["reduce_n"] = state.get("reduce_n", 0) + 1
         dist.barrier()                      # peers have finished reading this rank's buffer before the next pass zeroes it
 
-    # ---- N > 1, default (--reduce pipe): the same reduce-scatter, pipelined band by band behind the accumulation.  The last
+    # ---- c2, N > 1, default (--reduce pipe): the same reduce-scatter, pipelined band by band behind the accumulation.  The last
     # slabs of every shard are accumulated row band by row band (ggrm_finish_async); each rank's CUDA host callbacks raise a
     # flag per finished band in POSIX shared memory; the 2048-row strips of the matrix are dealt to the ranks by LPT on their area
     # (sharding.strip_owners), and the owner of a strip - as soon as all N flags of the strip's band are up - sums the peers'
@@ -335,12 +520,12 @@ def gpu_arm(args):
         pipe["ready"] = True
         return True
 
-    def pipelined_pass(push, fetch):
+    def pipelined_pass(dev, fetch):
         pipe["pass_id"] += 1
         pid = pipe["pass_id"]
         acc.reset()
         acc.set_band_flags(pipe["flags"][rank].ctypes.data, pid)
-        push()
+        push_all(dev)
         acc.finish_async()
         off = 0
         for b, lo, hi in pipe["mine"]:
@@ -357,14 +542,17 @@ def gpu_arm(args):
         acc.finish()      # waits for the accumulation and the read-out stream (the reduces), reports device faults
         dist.barrier()    # peers have finished reading this rank's rows before the next pass overwrites them
 
-    use_pipe = world > 1 and args.reduce == "pipe"
+    use_pipe = world > 1 and args.reduce == "pipe" and not loco
+
+    def fetch_rows(group, lo, hi, dst_off_elems=0):
+        acc.lib.ggrm_fetch(acc.h, g.KIND_ADD, group, lo, hi - lo, ctypes.c_void_p(h_out.data_ptr() + 4 * dst_off_elems), None)
 
     def step_resident():
         if use_pipe and pipe["ready"]:
-            pipelined_pass(lambda: acc.push_device(d_bed.data_ptr(), s0, ms), fetch=False)
+            pipelined_pass(True, fetch=False)
             return
         acc.reset()
-        acc.push_device(d_bed.data_ptr(), s0, ms)
+        push_all(True)
         acc.finish()
         reduce_partials()
         if use_pipe and not pipe.get("failed"):  # first warm-up pass ran the blocking form (it maps the peers' accumulators); arm the pipeline now
@@ -372,19 +560,27 @@ def gpu_arm(args):
                 pipe["failed"] = True
                 args.reduce = "peer"
 
-    def fetch_mine():
-        if world > 1 and args.reduce == "nccl":
-            if rank == 0:
-                acc.lib.ggrm_fetch(acc.h, g.KIND_ADD, g.GROUP_WHOLE, 0, n, ctypes.c_void_p(h_full.data_ptr()), None)
-        elif r1 > r0:
-            acc.lib.ggrm_fetch(acc.h, g.KIND_ADD, g.GROUP_WHOLE, r0, r1 - r0, ctypes.c_void_p(h_out.data_ptr()), None)
-
     def step_e2e():
         if use_pipe and pipe["ready"]:
-            pipelined_pass(lambda: acc.push_ptr(h_bed.data_ptr(), s0, ms), fetch=True)
+            pipelined_pass(False, fetch=True)
             return
         acc.reset()
-        acc.push_ptr(h_bed.data_ptr(), s0, ms)
+        if loco:
+            # a chromosome's partial is read out (5 GB over PCIe) while the next chromosome is on the tensor cores: pushes from pinned
+            # memory only enqueue, ggrm_fetch blocks this thread for the finished group alone
+            for li, ((b, e), o0) in enumerate(zip(ranges, offs)):
+                acc.push_ptr(h_bed.data_ptr() + int(o0) * bpv, b, e - b)
+                if li > 0:
+                    fetch_rows(li - 1, 0, n)
+            acc.finish_async()
+            if ranges:
+                fetch_rows(len(ranges) - 1, 0, n)
+            acc.finish()
+            reduce_partials()               # whole = sum over ranks of their chromosomes' partial sums (N = 1: already folded)
+            if r1 > r0:
+                fetch_rows(g.GROUP_WHOLE, r0, r1)
+            return
+        push_all(False)
         if world == 1:
             # ggrm_finish_async: the last slab runs in row bands and ggrm_fetch (which blocks until the requested rows are on
             # the host) starts reading the first bands out while the later ones are still accumulating
@@ -392,7 +588,11 @@ def gpu_arm(args):
         else:
             acc.finish()
         reduce_partials()
-        fetch_mine()
+        if world > 1 and args.reduce == "nccl":
+            if rank == 0:
+                acc.lib.ggrm_fetch(acc.h, g.KIND_ADD, g.GROUP_WHOLE, 0, n, ctypes.c_void_p(h_full.data_ptr()), None)
+        elif r1 > r0:
+            fetch_rows(g.GROUP_WHOLE, r0, r1)
 
     wall_checks = []
 
@@ -427,6 +627,13 @@ def gpu_arm(args):
     clocks = sampler.stop(*win) if rank == 0 else None
     dt_e, tm_e, _ = timed(step_e2e, args.steps, max(1, args.warmup // 2))
     fl = flops(n, m)
+    # per-rank SYRK time of the resident leg (LPT balance / per-GPU roofline of the multi-GPU runs)
+    syrk_all = [tm["syrk_ms"] / args.steps]
+    if world > 1:
+        t = torch.zeros(world, device="cuda", dtype=torch.float64)
+        t[rank] = tm["syrk_ms"] / args.steps
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        syrk_all = [float(x) for x in t.tolist()]
     line = None
     if rank == 0:
         sustained, burst, how = peaks()
@@ -439,49 +646,63 @@ def gpu_arm(args):
         if tp.exists():
             tj = json.loads(tp.read_text())
             traffic, traffic_launch = tj.get("syrk_dram_bytes_per_launch"), tj.get("launch")
+        if world == 1:
+            partition = "single GPU" + (": 22 partial accumulators + whole resident (23 x 5.06 GB), whole folded in the SYRK epilogue of each chromosome's last slab" if loco else "")
+        elif loco:
+            partition = (f"chromosome shards over {world} GPUs (whole chromosome runs dealt by LPT on SNP counts; SNPs per rank {per_rank_snps}, "
+                         f"max/mean {max(per_rank_snps) / (sum(per_rank_snps) / world):.3f}): no reduce for the 22 partials; whole = reduce-scatter of the per-rank "
+                         "sums by 2048-row slices over NVLink peer memory (CUDA IPC, P2P loads)")
+        else:
+            partition = {
+                "nccl": f"SNP-sharded over {world} GPUs + NCCL sum-reduce of FP32 partial GRMs to rank 0",
+                "peer": f"SNP-sharded over {world} GPUs + reduce-scatter of FP32 partial GRMs by 2048-row slices over NVLink peer memory (CUDA IPC, P2P loads) "
+                        "after a blocking finish; each rank fetches its own rows",
+                "pipe": f"SNP-sharded over {world} GPUs + reduce-scatter of FP32 partial GRMs over NVLink peer memory (CUDA IPC, P2P loads), pipelined "
+                        f"band by band behind the accumulation: {pipe.get('n_bands')} row bands, 2048-row strips dealt to ranks by LPT on area, per-band completion flags "
+                        "raised by CUDA host callbacks in POSIX shared memory, no collective inside the pass; each rank fetches its own strips"}[args.reduce]
+        d2h = int(out_elems * 4) * (23 if loco else 1)
         line = {
-            "metric": METRIC, "value": fl / (dt / args.steps) / 1e12, "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps,
+            "metric": cfg["metric"], "value": fl / (dt / args.steps) / 1e12, "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "wall_s_per_grm": dt / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": {"fp16": "f16 operands, f32 accumulate (tcgen05 kind::f16)", "bf16": "bf16 operands, f32 accumulate (tcgen05 kind::f16)",
-                      "fp64": "f64 (DMMA)"}[args.precision],
-            "data": "synthetic",
-            "config": {"workload": f"configs[1]: Yang additive GRM (StandardizeHWE+Add), {n} samples x {m} SNPs, packed 2-bit PLINK BED "
-                                   f"({m * bpv / 1e9:.2f} GB), 1 % missing, seed {SEED}",
-                       "partition": "single GPU" if world == 1 else {
-                           "nccl": f"SNP-sharded over {world} GPUs + NCCL sum-reduce of FP32 partial GRMs to rank 0",
-                           "peer": f"SNP-sharded over {world} GPUs + reduce-scatter of FP32 partial GRMs by 2048-row slices over NVLink peer memory (CUDA IPC, P2P loads) "
-                                   "after a blocking finish; each rank fetches its own rows",
-                           "pipe": f"SNP-sharded over {world} GPUs + reduce-scatter of FP32 partial GRMs over NVLink peer memory (CUDA IPC, P2P loads), pipelined "
-                                   f"band by band behind the accumulation: {pipe.get('n_bands')} row bands, 2048-row strips dealt to ranks by LPT on area, per-band completion flags "
-                                   "raised by CUDA host callbacks in POSIX shared memory, no collective inside the pass; each rank fetches its own strips"}[args.reduce],
-                       "l2": "inputs (packed BED 6.25 GB, 16-bit operand slabs 0.8 GB, accumulator 5 GB) are larger than the 126 MB L2; no flush needed",
+            "dtype": DTYPE_NOTE[args.precision], "data": "synthetic",
+            "config": {"workload": f"{cfg['tag']}: {cfg['what']}, {n} samples x {m} SNPs, packed 2-bit PLINK BED "
+                                   f"({m * bpv / 1e9:.2f} GB), 1 % missing, seed {cfg['seed']}",
+                       "partition": partition,
+                       "l2": "inputs (packed BED 6-7.5 GB, 16-bit operand slabs 0.8 GB, accumulator 5 GB) are larger than the 126 MB L2; no flush needed",
                        "timing": "CUDA events around the K steps, barrier + cuda synchronize on both sides, max over ranks; kernel phases by CUDA events on the library's streams",
                        "chunk_snps": int(os.environ.get("GGRM_CHUNK_SNPS", 16384)), "host": numa_note},
             "device_pass_ms_per_step": tm["pass_ms"] / args.steps,
             "wall_clock_ms_per_step": wall_checks[0][1] / args.steps * 1e3,
             "phases_ms_per_step": {k: tm[k] / args.steps for k in ("h2d_ms", "prep_ms", "expand_ms", "syrk_ms")},
+            "syrk_ms_per_rank": syrk_all, "snps_per_rank": per_rank_snps,
             "gpu_launches": int(tm["kernel_launches"]),
-            "reduce_ms_per_call_rank0": (state.get("reduce_s", 0.0) / max(1, state.get("reduce_n", 0)) * 1e3) if world > 1 and args.reduce != "pipe" else None,
-            "reduce_bytes_over_nvlink_rank0": (pipe.get("nvlink_bytes") if args.reduce == "pipe" else
-                                               int((state["slice"][1] - state["slice"][0]) * 4 * (world - 1)) if args.reduce == "peer" else None) if world > 1 else None,
+            "reduce_ms_per_call_rank0": (state.get("reduce_s", 0.0) / max(1, state.get("reduce_n", 0)) * 1e3) if world > 1 and not use_pipe else None,
+            "reduce_bytes_over_nvlink_rank0": (pipe.get("nvlink_bytes") if use_pipe else
+                                               int((state["slice"][1] - state["slice"][0]) * 4 * (world - 1)) if state["ready"] else None) if world > 1 else None,
             "clocks": clocks,
             "e2e": {"value": fl / (dt_e / args.steps) / 1e12, "unit": "TFLOP/s", "wall_s_per_grm": dt_e / args.steps,
-                    "h2d_bytes_per_step": int(ms * bpv), "d2h_bytes_per_step": int(out_elems * 4),
-                    "path": "ggrm_reset -> ggrm_push(pinned host BED) -> ggrm_finish_async -> [N>1, per owned band: wait for all ranks' band flags -> ggrm_reduce_rows_async] -> ggrm_fetch(float32 lower-triangle rows to pinned host memory; N>1: each rank its own bands, bytes summed over ranks)",
+                    "h2d_bytes_per_step": int(m * bpv), "d2h_bytes_per_step": d2h,
+                    "path": ("ggrm_reset -> per chromosome: ggrm_push(pinned host BED) then ggrm_fetch of the previous chromosome's partial (float32 lower triangle to "
+                             "pinned host memory, overlapping the next chromosome's accumulation) -> ggrm_finish -> [N>1: reduce-scatter of the whole over NVLink] -> "
+                             "ggrm_fetch(whole; N>1: each rank its row slice); bytes summed over ranks") if loco else
+                            "ggrm_reset -> ggrm_push(pinned host BED) -> ggrm_finish_async -> [N>1, per owned band: wait for all ranks' band flags -> ggrm_reduce_rows_async] -> ggrm_fetch(float32 lower-triangle rows to pinned host memory; N>1: each rank its own bands, bytes summed over ranks)",
                     "phases_ms_per_step": {k: tm_e[k] / args.steps for k in ("h2d_ms", "prep_ms", "expand_ms", "syrk_ms", "fetch_ms")}},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": sustained, "unit": "TFLOP/s", "frac": achieved / sustained,
                          "traffic": traffic, "kernel": "syrk_tc_kernel<2> (tcgen05 cta_group::2, UMMA 256x256x16)",
                          "traffic_launch": traffic_launch,
                          "flops_per_launch": fl_rank / launches, "avg_launch_ms": syrk_ms / launches, "launches_per_step": launches,
+                         "whole_job_frac_of_n_x_burst": fl / (dt / args.steps) / 1e12 / (burst * world),
                          "launch_note": "achieved = this rank's credited flops of a step / its summed SYRK launch time (CUDA events on the library's compute "
-                                        "stream); a step is ceil(m_rank/16384) equal slabs, the last four accumulated band-major (up to 8 row bands x 4 slabs); traffic is the ncu "
+                                        "stream); a step is ceil(m_group/16384) equal slabs per group, the last four accumulated band-major (up to 8 row bands x 4 slabs); traffic is the ncu "
                                         "--set full DRAM bytes of ONE steady-state 16384-SNP slab launch (traffic_launch)",
                          "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({how}); burst peak {burst} -> frac {achieved / burst:.3f}"},
         }
     for p_ in peers:
         g.ipc_close(p_, device=local)
     acc.close()
+    del d_bed, h_bed, h_out
+    torch.cuda.empty_cache()
     if pipe.get("shm") is not None:
         pipe["flags"] = None
         pipe["shm"].close()
@@ -489,8 +710,24 @@ def gpu_arm(args):
             dist.barrier()
         if rank == 0:
             pipe["shm"].unlink()
+    if world > 1:
+        dist.barrier()  # every rank has released its accumulators: the CLI below gets the GPUs to itself
+    if rank == 0 and (not args.no_wall) and (not loco or args.wall) and CLI_BIN.exists():
+        try:
+            line["wall"] = cli_wall_leg(cfg, world, args.precision, device=local)
+        except Exception as e:  # noqa: BLE001
+            line["wall"] = {"unavailable": f"{type(e).__name__}: {e}"}
     if rank == 0 and world == 1 and not args.no_cpu:
-        cb, _, _ = cpu_leg(1, 0, args.cpu_budget)
+        cb, tmp = cpu_leg(1, 0, cfg, lambda n_, m_, seed: [g.synth_bed_host(n_, 0, m_, seed, MISSING)])
+        try:
+            c1p = cb.pop("_c1_prefix", None)
+            if c1p is not None and CLI_BIN.exists():
+                ours = run_cli(c1p, str(tmp / "c1_ours"), 1, args.precision)
+                cb["like_for_like"].update({"ours_cli_wall_s": ours["cli_wall_s"], "ours_engine_wall_s": ours.get("engine_wall_s"),
+                                            "ours_phases_s": ours.get("phases_s"), "ours_rc": ours["rc"]})
+                line["like_for_like"] = cb.pop("like_for_like")
+        finally:
+            shutil.rmtree(tmp, ignore_errors=True)
         line["cpu_baseline"] = cb
     if world > 1:
         dist.barrier()
@@ -503,12 +740,17 @@ def reference_arm(args):
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
         return
-    cb, n_s, m_s = cpu_leg(args.steps, args.warmup, args.cpu_budget)
-    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "TFLOP/s", "n_gpus": args.gpus, "steps": args.steps,
+    cfg = CONFIGS[args.config]
+    cb, tmp = cpu_leg(args.steps, args.warmup, cfg, synth_rows_numpy)
+    shutil.rmtree(tmp, ignore_errors=True)
+    cb.pop("_c1_prefix", None)
+    n_s, m_s = CPU_SAMPLE if REF_BIN.exists() else (1500, 3000)
+    line = {"impl": "reference", "metric": cfg["metric"], "value": cb["value"], "unit": "TFLOP/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": cb["wall_s"] * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"configs[1]: Yang additive GRM (StandardizeHWE+Add), {N_SAMPLES} samples x {M_SNPS} SNPs; each step = bounded sample "
+            "config": {"workload": f"{cfg['tag']}: {cfg['what']}, {cfg['n']} samples x {cfg['m']} SNPs; each step = the fixed bounded sample "
                                    f"{n_s} x {m_s} of it (the CPU path needs hours and 40 GB for the full shape)"},
+            "like_for_like": cb.pop("like_for_like", None),
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
@@ -525,13 +767,16 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default=os.environ.get("GGRM_BENCH_CONFIG", "c2"), choices=sorted(CONFIGS),
+                    help="c2 = configs[1] (the headline shape), c4 = configs[3] (22 LOCO partials + whole)")
     ap.add_argument("--precision", default=os.environ.get("GGRM_BENCH_PRECISION", "bf16"), choices=["fp16", "bf16", "fp64"],
-                    help="operand type of the tcgen05 path; bf16 meets the 1e-4 bound at this workload's 500k SNPs "
-                         "(tests/test_gpu_parity.py::test_c2_snp_count_tolerance_16bit_device_resident), fp16 is the engine default for short inputs")
-    ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work per reference step")
-    ap.add_argument("--no-cpu", action="store_true")
+                    help="operand type of the tcgen05 path; bf16 meets the 1e-4 bound at these workloads' 500-600k SNPs "
+                         "(tests/test_named_configs_gpu.py), fp16 is the engine default")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg (N = 1)")
+    ap.add_argument("--no-wall", action="store_true", help="skip the CLI wall-clock leg")
+    ap.add_argument("--wall", action="store_true", help="c4: run the CLI wall-clock leg too (writes 23 x 5 GB)")
     ap.add_argument("--reduce", default="pipe", choices=["pipe", "peer", "nccl"],
-                    help="N>1: partial-GRM reduction (pipe = own P2P kernel pipelined band by band behind the accumulation, "
+                    help="c2, N>1: partial-GRM reduction (pipe = own P2P kernel pipelined band by band behind the accumulation, "
                          "peer = the same kernel after a blocking finish, nccl = dist.reduce to rank 0)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -70,6 +70,7 @@ EXPORTS = [
     "ggrm_fetch_block", "ggrm_owned_supertiles", "ggrm_host_alloc", "ggrm_host_free", "ggrm_bin_to_dense", "ggrm_assoc_chunk",
     "ggrm_band_layout", "ggrm_set_band_flags", "ggrm_reduce_rows_async", "ggrm_genotype_chunk", "ggrm_fetch_gcta", "ggrm_accum_address",
     "ggrm_stage_create", "ggrm_stage_destroy", "ggrm_stage_upload", "ggrm_stage_slot", "ggrm_wait_copies",
+    "ggrm_warm_device",
 ]
 
 _lib = None
@@ -130,6 +131,7 @@ def load() -> C.CDLL:
     lib.ggrm_stage_upload.argtypes = [vp, C.c_int, vp, i64]
     lib.ggrm_stage_slot.argtypes = [vp, C.c_int, C.POINTER(vp)]
     lib.ggrm_wait_copies.argtypes = [vp]
+    lib.ggrm_warm_device.argtypes = [C.c_int]
     lib.ggrm_device_count.argtypes = []
     lib.ggrm_version.argtypes = []
     lib.ggrm_version.restype = C.c_char_p
@@ -257,14 +259,16 @@ class Accumulator:
         self._check(fn(self.h, kind, group, row_begin, row_count, _ptr(out), C.byref(tr)))
         return out, tr.value
 
-    def fetch_normalized(self, kind=KIND_ADD, group=GROUP_WHOLE):
-        out = np.empty(tri(self.n_out), dtype=np.float64)
-        self._check(self.lib.ggrm_fetch_normalized(self.h, kind, group, 0, self.n_out, _ptr(out)))
+    def fetch_normalized(self, kind=KIND_ADD, group=GROUP_WHOLE, row_begin=0, row_count=None):
+        row_count = self.n_out - row_begin if row_count is None else row_count
+        out = np.empty(tri(row_begin + row_count) - tri(row_begin), dtype=np.float64)
+        self._check(self.lib.ggrm_fetch_normalized(self.h, kind, group, row_begin, row_count, _ptr(out)))
         return out
 
-    def fetch_loco(self, kind, group):
-        out = np.empty(tri(self.n_out), dtype=np.float64)
-        self._check(self.lib.ggrm_fetch_loco(self.h, kind, group, 0, self.n_out, _ptr(out)))
+    def fetch_loco(self, kind, group, row_begin=0, row_count=None):
+        row_count = self.n_out - row_begin if row_count is None else row_count
+        out = np.empty(tri(row_begin + row_count) - tri(row_begin), dtype=np.float64)
+        self._check(self.lib.ggrm_fetch_loco(self.h, kind, group, row_begin, row_count, _ptr(out)))
         return out
 
     def release_group(self, kind, group):

@@ -21,7 +21,7 @@ static inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * 
 // ---------------------------------------------------------------------------------------------------------------
 // TMA descriptor for a K-major 16-bit operand matrix Z[n_pad][k_cap]: box = 64 elements (128 B) x 128 rows,
 // 128-byte swizzle — the smem image tcgen05 descriptors (make_smem_desc_sw128) expect.
-void encode_tensor_map(CUtensorMap* map, void* base, int64_t k_cap, int64_t n_pad, bool fp16) {
+void encode_tensor_map(CUtensorMap* map, void* base, int64_t k_cap, int64_t n_pad, bool fp16) {  // k_cap = columns of the matrix
     typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -146,14 +146,28 @@ void build_ownership_and_items(Handle& h) {
                                    off + static_cast<int64_t>(bi) * 64 * 256 + bj * 64});
                 }
         } else if (h.tc_mode == 2) {
-            tc.push_back({static_cast<int32_t>(I * 256), static_cast<int32_t>(J * 256), off});
+            tc.push_back({static_cast<int32_t>(I * 256), static_cast<int32_t>(J * 256), off, 0, 0});
         } else {
-            tc.push_back({static_cast<int32_t>(I * 256), static_cast<int32_t>(J * 256), off});
-            tc.push_back({static_cast<int32_t>(I * 256 + 128), static_cast<int32_t>(J * 256), off + kHalfTileElems});
+            tc.push_back({static_cast<int32_t>(I * 256), static_cast<int32_t>(J * 256), off, 0, 0});
+            tc.push_back({static_cast<int32_t>(I * 256 + 128), static_cast<int32_t>(J * 256), off + kHalfTileElems, 0, 0});
         }
     }
     h.owned_tiles = slot;
     h.accum_elems = static_cast<int64_t>(slot) * 65536;
+    // Split-K list (Handle::ksplit): as many K parts as whole waves of CTA pairs the tiles leave empty, at most 8; part-major, so
+    // that the parts of one tile run in the same wave and share its operand panels in L2.
+    h.ksplit = 1;
+    std::vector<TcItem> split;
+    if (!h.fp64 && h.tc_mode == 2 && slot > 0) {
+        int want = std::min<int>(8, (h.sm_count / 2) / static_cast<int>(slot));
+        if (const char* e = std::getenv("GGRM_KSPLIT")) want = std::max(1, std::min(8, std::atoi(e)));
+        const bool keeps_whole = h.cfg.n_groups > 1 && h.cfg.keep_whole;  // the in-epilogue fold into `whole` assumes one copy
+        if (want > 1 && !keeps_whole && h.band_item_end.size() <= 1) {
+            h.ksplit = want;
+            for (const TcItem& t : tc)
+                for (int p = 0; p < want; ++p) split.push_back({t.a_row0, t.b_row0, t.out_off + static_cast<int64_t>(p) * h.accum_elems, p, 0});
+        }
+    }
     GGRM_CUDA(cudaMalloc(&h.d_slot_of, std::max<size_t>(1, h.slot_of_host.size()) * sizeof(int32_t)));
     GGRM_CUDA(cudaMemcpy(h.d_slot_of, h.slot_of_host.data(), h.slot_of_host.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
     h.num_items_tc = static_cast<int>(tc.size());
@@ -161,6 +175,11 @@ void build_ownership_and_items(Handle& h) {
     if (!tc.empty()) {
         GGRM_CUDA(cudaMalloc(&h.d_items_tc, tc.size() * sizeof(TcItem)));
         GGRM_CUDA(cudaMemcpy(h.d_items_tc, tc.data(), tc.size() * sizeof(TcItem), cudaMemcpyHostToDevice));
+    }
+    h.num_items_split = static_cast<int>(split.size());
+    if (!split.empty()) {
+        GGRM_CUDA(cudaMalloc(&h.d_items_split, split.size() * sizeof(TcItem)));
+        GGRM_CUDA(cudaMemcpy(h.d_items_split, split.data(), split.size() * sizeof(TcItem), cudaMemcpyHostToDevice));
     }
     if (!f64.empty()) {
         GGRM_CUDA(cudaMalloc(&h.d_items_f64, f64.size() * sizeof(F64Item)));
@@ -244,14 +263,14 @@ static void free_handle(Handle* h) {
     cudaSetDevice(h->cfg.device);
     cudaDeviceSynchronize();
     auto fr = [h](void* p) { dev_free(*h, p); };
-    fr(h->d_slot_of); fr(h->d_items_tc); fr(h->d_items_f64); fr(h->d_out_to_raw);
+    fr(h->d_slot_of); fr(h->d_items_tc); fr(h->d_items_split); fr(h->d_items_f64); fr(h->d_out_to_raw);
     fr(h->d_raw[0]); fr(h->d_raw[1]); fr(h->d_dense); fr(h->d_counts); fr(h->d_freq);
     for (int k = 0; k < 2; ++k) {
         fr(h->d_tab16[k]); fr(h->d_tab64[k]); fr(h->whole[k]);
         for (int b = 0; b < Handle::kMaxZBuf; ++b) fr(h->d_Z[k][b]);
         for (void* p : h->pool[k]) fr(p);
     }
-    fr(h->d_stage); fr(h->d_trace); fr(h->d_fault); fr(h->d_wave_ctr);
+    fr(h->d_stage); fr(h->d_trace); fr(h->d_fault); fr(h->d_wave_ctr); fr(h->d_range_flag);
     for (int i = 0; i < Handle::kRingSlots; ++i) {
         if (h->ring[i] != nullptr) cudaFreeHost(h->ring[i]);
         if (h->ring_free[i] != nullptr) cudaEventDestroy(h->ring_free[i]);
@@ -357,6 +376,13 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
         GGRM_CUDA(cudaEventCreateWithFlags(&h->z_free[i], cudaEventDisableTiming));
     }
 
+    // BF16 operands carry 8 mantissa bits: the rounding error of G/(trace/n) shrinks as 1/sqrt(m) and measures ~0.018/sqrt(m)
+    // (4.0e-4 at m = 2 048, ~8e-5 at the 50 000 SNPs of config C1, ~2.5e-5 at C2's 500 000).  Below 2^18 SNPs - where a
+    // plain BF16 product would not keep 1e-4 with a 2x margin - the operands are split into hi + lo (3 MMAs per K block, error
+    // of an ~16-bit mantissa), so GGRM_PREC_BF16 meets the bound at every size.  GGRM_BF16_SPLIT=0/1 forces it off/on.
+    h->bf16_split = cfg->precision == GGRM_PREC_BF16 && cfg->m_total < (int64_t{1} << 18);
+    if (const char* e = std::getenv("GGRM_BF16_SPLIT")) h->bf16_split = cfg->precision == GGRM_PREC_BF16 && std::atoi(e) != 0;
+
     build_ownership_and_items(*h);
 
     // ---- memory plan -------------------------------------------------------------------------------------------
@@ -365,17 +391,18 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
     const int kinds = (cfg->want_add ? 1 : 0) + (cfg->want_dom ? 1 : 0);
     const int64_t accum_bytes = std::max<int64_t>(h->accum_elems, 4) * h->elem_bytes;
     const bool want_whole = cfg->n_groups > 1 && cfg->keep_whole;
-    const int64_t z_elem = h->fp64 ? 8 : 2;
+    const int64_t z_elem = h->fp64 ? 8 : (h->bf16_split ? 4 : 2);  // bytes per sample per SNP of one operand slab (hi + lo when split)
+    const int64_t z_cols_per_k = h->bf16_split ? 2 : 1;
     const int64_t per_snp = 2 * h->n_pad * z_elem * kinds + 2 * h->bpv_raw + h->bpv_pad + 128;
     int64_t avail = static_cast<int64_t>(free_b) - (int64_t{1} << 30) - (want_whole ? accum_bytes * kinds : 0);
     const int64_t min_chunk = std::min<int64_t>(round_up(cfg->m_total, 64), 4096) * per_snp;
     int pool_n = 1;
     if (cfg->n_groups > 1) {
-        int64_t fit = (avail - min_chunk) / (accum_bytes * kinds);
+        int64_t fit = (avail - min_chunk) / (accum_bytes * h->ksplit * kinds);
         if (cfg->max_resident_groups > 0) fit = std::min<int64_t>(fit, cfg->max_resident_groups);
         pool_n = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(fit, cfg->n_groups)));
     }
-    avail -= static_cast<int64_t>(pool_n) * accum_bytes * kinds;
+    avail -= static_cast<int64_t>(pool_n) * accum_bytes * h->ksplit * kinds;
     int64_t k_cap;
     if (cfg->chunk_snps > 0) {
         k_cap = round_up(cfg->chunk_snps, 64);
@@ -411,7 +438,7 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
         if (!(kind == 0 ? cfg->want_add : cfg->want_dom)) continue;
         for (int p = 0; p < pool_n; ++p) {
             void* buf = nullptr;
-            dev_alloc(*h, &buf, static_cast<size_t>(accum_bytes), kind == 0 ? "accumulator (kind 0)" : "accumulator (kind 1)");
+            dev_alloc(*h, &buf, static_cast<size_t>(accum_bytes * h->ksplit), kind == 0 ? "accumulator (kind 0)" : "accumulator (kind 1)");
             h->pool[kind].push_back(buf);
             h->pool_owner[kind].push_back(-1);
         }
@@ -423,8 +450,9 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
         if (h->fp64) {
             dev_alloc(*h, &h->d_tab64[kind], static_cast<size_t>(k_cap) * sizeof(SnpTable), "value tables (f64)");
         } else {
-            dev_alloc(*h, &h->d_tab16[kind], static_cast<size_t>(k_cap) * sizeof(uint2), "value tables (16-bit)");
-            for (int b = 0; b < h->n_zbuf; ++b) encode_tensor_map(&h->tmap[kind][b], h->d_Z[kind][b], k_cap, h->n_pad, cfg->precision == GGRM_PREC_FP16);
+            dev_alloc(*h, &h->d_tab16[kind], static_cast<size_t>(k_cap * z_cols_per_k) * sizeof(uint2), "value tables (16-bit)");
+            for (int b = 0; b < h->n_zbuf; ++b)
+                encode_tensor_map(&h->tmap[kind][b], h->d_Z[kind][b], k_cap * z_cols_per_k, h->n_pad, cfg->precision == GGRM_PREC_FP16);
         }
     }
     for (int i = 0; i < 2; ++i) dev_alloc(*h, &h->d_raw[i], static_cast<size_t>(k_cap * h->bpv_raw), "raw BED chunk");
@@ -441,6 +469,8 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
     if (const char* e = std::getenv("GGRM_WAVE_SYNC")) h->sync_every = std::max(0, std::atoi(e));
     GGRM_CUDA(cudaMalloc(&h->d_fault, sizeof(int)));
     GGRM_CUDA(cudaMemsetAsync(h->d_fault, 0, sizeof(int), h->s_comp));
+    GGRM_CUDA(cudaMalloc(&h->d_range_flag, sizeof(unsigned long long)));
+    GGRM_CUDA(cudaMemsetAsync(h->d_range_flag, 0, sizeof(unsigned long long), h->s_comp));
 
     if (!h->fp64) {
         GGRM_CUDA(cudaFuncSetAttribute(syrk_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcConfig<1>::kSmemBytes));
@@ -516,6 +546,24 @@ extern "C" int ggrm_device_count(void) {
     int c = 0;
     if (cudaGetDeviceCount(&c) != cudaSuccess) return 0;
     return c;
+}
+
+extern "C" int ggrm_warm_device(int device) {
+    try {
+        check_device(device, nullptr);
+        GGRM_CUDA(cudaFree(nullptr));  // primary context
+        cudaFuncAttributes fa{};       // module load (lazy loading would otherwise pay it at the first launch)
+        GGRM_CUDA(cudaFuncGetAttributes(&fa, syrk_tc_kernel<2>));
+        GGRM_CUDA(cudaFuncGetAttributes(&fa, expand16_kernel));
+        GGRM_CUDA(cudaFuncGetAttributes(&fa, count_stats_kernel));
+    } catch (const CudaError& e) {
+        g_create_error = e.msg;
+        return e.status;
+    } catch (const std::exception& e) {
+        g_create_error = e.what();
+        return GGRM_ERR_INVALID_OPERATION;
+    }
+    return GGRM_OK;
 }
 
 extern "C" const char* ggrm_version(void) { return "gelex-grm-b200 0.1 (sm_100a; tcgen05 SYRK)"; }

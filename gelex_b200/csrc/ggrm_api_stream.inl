@@ -70,6 +70,7 @@ static void start_group(Handle& h, int g, bool zero) {
         h.pool_owner[kind][slot] = g;
         gs.buffer[kind] = slot;
         gs.touched[kind] = false;
+        gs.split_touched[kind] = false;
         if (zero) {
             GGRM_CUDA(cudaMemsetAsync(h.pool[kind][slot], 0, static_cast<size_t>(std::max<int64_t>(h.accum_elems, 4)) * h.elem_bytes, h.s_comp));
             gs.touched[kind] = true;
@@ -84,6 +85,18 @@ static void complete_group(Handle& h, int g) {
     GroupState& gs = h.groups[g];
     if (gs.complete) return;
     if (!h.deferred.empty() && h.deferred_group == g) accumulate_slabs(h, g, false);
+    // split-K launches (Handle::ksplit): copies 1 .. ksplit-1 of the tiles are summed into copy 0, in a fixed order
+    for (int kind = 0; kind < 2 && gs.started; ++kind) {
+        if (!gs.split_touched[kind] || gs.buffer[kind] < 0) continue;
+        float* base = static_cast<float*>(h.pool[kind][gs.buffer[kind]]);
+        const int blocks = static_cast<int>(std::min<int64_t>((h.accum_elems / 4 + 255) / 256, h.sm_count * 8));
+        for (int p = 1; p < h.ksplit; ++p) {
+            axpy_accum_kernel<float><<<blocks, 256, 0, h.s_comp>>>(base, base + static_cast<int64_t>(p) * h.accum_elems, h.accum_elems);
+            GGRM_CUDA(cudaGetLastError());
+            ++h.kernel_launches;
+        }
+        gs.split_touched[kind] = false;
+    }
     if (gs.started && !gs.folded) {
         for (int kind = 0; kind < 2; ++kind) {
             if (h.whole[kind] == nullptr || gs.buffer[kind] < 0 || h.accum_elems == 0) continue;
@@ -118,6 +131,16 @@ static void launch_syrk(Handle& h, int kind, int g, int64_t c, int zb, float* fo
         const TcItem* items = h.d_items_tc + item_begin;
         const int nkb = static_cast<int>(round_up(c, 64) / 64);
         const uint32_t fmt = h.cfg.precision == GGRM_PREC_FP16 ? 0u : 1u;
+        const int lo_blk = h.bf16_split ? static_cast<int>(h.k_cap / 64) : 0;
+        // few tiles: cut this slab along K as well (whole list only; never combined with bands or the in-epilogue fold)
+        int ksplit = 1, accumulate_split = 0;
+        if (h.ksplit > 1 && nkb >= h.ksplit && item_begin == 0 && item_count == h.num_items_tc && fold == nullptr) {
+            ksplit = h.ksplit;
+            items = h.d_items_split;
+            item_count = h.num_items_split;
+            accumulate_split = gs.split_touched[kind] ? 1 : 0;
+            gs.split_touched[kind] = true;
+        }
         int grid_ctas = 0, n_clusters = 1;
         if (h.tc_mode == 2) {
             const int clusters = std::min(item_count, h.sm_count / 2);
@@ -134,14 +157,14 @@ static void launch_syrk(Handle& h, int kind, int g, int64_t c, int zb, float* fo
             lc.attrs = attr;
             lc.numAttrs = 1;
             GGRM_CUDA(cudaLaunchKernelEx(&lc, syrk_tc_kernel<2>, h.tmap[kind][zb], static_cast<float*>(accum),
-                                         items, item_count, nkb, 0, accumulate, fmt, h.cache_hints, h.d_fault,
+                                         items, item_count, nkb, ksplit, lo_blk, accumulate, accumulate_split, fmt, h.cache_hints, h.d_fault,
                                          h.d_wave_ctr, h.wave_base, h.sync_every, fold));
             grid_ctas = 2 * clusters;
             n_clusters = clusters;
         } else {
             const int grid = std::min(item_count, h.sm_count);
             syrk_tc_kernel<1><<<grid, 256, TcConfig<1>::kSmemBytes, h.s_comp>>>(h.tmap[kind][zb], static_cast<float*>(accum), items,
-                                                                                item_count, nkb, 0, accumulate, fmt, h.cache_hints, h.d_fault,
+                                                                                item_count, nkb, 1, lo_blk, accumulate, 0, fmt, h.cache_hints, h.d_fault,
                                                                                 h.d_wave_ctr, h.wave_base, h.sync_every, fold);
             GGRM_CUDA(cudaGetLastError());
             grid_ctas = grid;
@@ -235,8 +258,10 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
     so.counts = h.d_counts;
     so.freq = h.d_freq;
     so.second_nonmissing = h.cfg.second_matrix == GGRM_SECOND_NONMISSING ? 1 : 0;
+    so.range_flag = h.cfg.precision == GGRM_PREC_FP16 ? h.d_range_flag : nullptr;
     for (int kind = 0; kind < 2; ++kind) {
         so.tab16[kind] = h.d_tab16[kind];
+        so.tab16_lo[kind] = h.bf16_split && h.d_tab16[kind] != nullptr ? h.d_tab16[kind] + h.k_cap : nullptr;
         so.tab64[kind] = h.d_tab64[kind];
     }
     count_stats_kernel<<<static_cast<unsigned>((c + 7) / 8), 256, 0, sp>>>(
@@ -252,8 +277,16 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
         if (h.d_Z[kind][zb] == nullptr) continue;
         if (h.fp64)
             expand64_kernel<<<egrid, 256, 0, sp>>>(h.d_dense, h.bpv_pad, h.d_tab64[kind], c, static_cast<double*>(h.d_Z[kind][zb]), h.k_cap);
-        else
-            expand16_kernel<<<egrid, 256, 0, sp>>>(h.d_dense, h.bpv_pad, h.d_tab16[kind], c, static_cast<uint16_t*>(h.d_Z[kind][zb]), h.k_cap);
+        else {
+            const int64_t z_pitch = h.bf16_split ? 2 * h.k_cap : h.k_cap;  // hi in columns [0, k_cap), lo in [k_cap, 2 k_cap)
+            expand16_kernel<<<egrid, 256, 0, sp>>>(h.d_dense, h.bpv_pad, h.d_tab16[kind], c, static_cast<uint16_t*>(h.d_Z[kind][zb]), z_pitch);
+            if (h.bf16_split) {
+                GGRM_CUDA(cudaGetLastError());
+                ++h.kernel_launches;
+                expand16_kernel<<<egrid, 256, 0, sp>>>(h.d_dense, h.bpv_pad, h.d_tab16[kind] + h.k_cap, c,
+                                                       static_cast<uint16_t*>(h.d_Z[kind][zb]) + h.k_cap, z_pitch);
+            }
+        }
         GGRM_CUDA(cudaGetLastError());
         ++h.kernel_launches;
     }
@@ -269,6 +302,9 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
         h.deferred.push_back(slab);
         accumulate_slabs(h, g, true);
     } else if (h.cur_trailing && (h.deferred.empty() || h.deferred_group == g)) {
+        // never park more slabs than there are spare operand buffers: pushes that skip SNPs inside the tail cut it into more
+        // than tail_slabs pieces, and the ring would otherwise wrap onto a parked slab that has not been accumulated yet
+        if (static_cast<int>(h.deferred.size()) + 1 > h.n_zbuf - 2) accumulate_slabs(h, h.deferred_group, false);
         h.deferred_group = g;
         h.deferred.push_back(slab);
     } else {
@@ -413,6 +449,17 @@ static void finish_sync(Handle& h) {
     }
     check_guards(h);
     collect_timers(h);
+    if (h.cfg.precision == GGRM_PREC_FP16) {
+        unsigned long long bad = 0;
+        GGRM_CUDA(cudaMemcpy(&bad, h.d_range_flag, sizeof(bad), cudaMemcpyDeviceToHost));
+        if (bad != 0) {
+            GGRM_CUDA(cudaMemset(h.d_range_flag, 0, sizeof(bad)));
+            throw CudaError{GGRM_ERR_INVALID_OPERATION,
+                            "FP16 operand overflow: a standardised genotype value of SNP " + std::to_string(bad - 1) +
+                                " exceeds the binary16 range (65504); the matrix would hold inf/NaN where the FP64 reference is finite. "
+                                "Use GGRM_PREC_BF16 (FP32 exponent range) or GGRM_PREC_FP64 for this input"};
+        }
+    }
     if (h.pass_open) {
         float ms = 0.f;
         if (cudaEventElapsedTime(&ms, h.pass_begin, h.pass_end) == cudaSuccess) h.pass_ms += ms;
@@ -442,6 +489,7 @@ static void reset_impl(Handle& h) {
         g.buffer[0] = g.buffer[1] = -1;
         g.started = g.complete = g.folded = false;
         g.touched[0] = g.touched[1] = false;
+        g.split_touched[0] = g.split_touched[1] = false;
     }
     for (int kind = 0; kind < 2; ++kind) {
         std::fill(h.pool_owner[kind].begin(), h.pool_owner[kind].end(), -1);

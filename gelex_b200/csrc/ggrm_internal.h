@@ -34,6 +34,7 @@ struct GroupState {
     int buffer[2] = {-1, -1};     // accumulator pool slot per kind (-1 = none yet / released)
     bool started = false;
     bool touched[2] = {false, false};  // a SYRK has written this group's accumulator of that kind (first slab stores, later slabs add)
+    bool split_touched[2] = {false, false};  // ... and its split-K copies 1 .. ksplit-1 (Handle::ksplit); summed into copy 0 when the group completes
     bool complete = false;        // all SNPs accumulated (+ folded into whole); `done` event recorded
     bool folded = false;
     cudaEvent_t done = nullptr;
@@ -64,6 +65,16 @@ struct Handle {
     int32_t* d_slot_of = nullptr;
     TcItem* d_items_tc = nullptr;
     int num_items_tc = 0;
+    // Split-K work list for few-tile problems (fewer tiles than CTA pairs, e.g. config C1: 36 tiles for 74 pairs): every tile
+    // appears ksplit times, part p accumulating K blocks [p nkb / ksplit, (p + 1) nkb / ksplit) into copy p of the accumulator
+    // (copy p at element offset p * accum_elems; pool buffers hold ksplit copies).  Copies are summed in a fixed order when the
+    // group completes, so results stay deterministic.  ksplit == 1: not used.
+    TcItem* d_items_split = nullptr;
+    int num_items_split = 0;
+    int ksplit = 1;
+    // GGRM_PREC_BF16 on short inputs: operands are kept as hi = bf16(z) and lo = bf16(z - hi) (Z slabs and value tables hold both,
+    // lo at K offset k_cap) and every K block is accumulated as hi hi^T + hi lo^T + lo hi^T (syrk_tc.cuh, lo_blk)
+    bool bf16_split = false;
     F64Item* d_items_f64 = nullptr;
     int num_items_f64 = 0;
     // Row bands of the tcgen05 work list (whole strips of strip_h tile rows, ~equal tile counts).  The LAST slab of a pass is
@@ -144,6 +155,7 @@ struct Handle {
     unsigned long long wave_base = 0;
     int sync_every = 1;                   // waves between pacing points, 0 = off (GGRM_WAVE_SYNC)
     int* d_fault = nullptr;               // mbarrier-timeout location written by a stuck SYRK before it traps
+    unsigned long long* d_range_flag = nullptr;  // FP16 operands: 1 + index of a SNP whose standardised value overflows binary16 (0 = none)
     // timers
     std::vector<Timer> timers;
     double phase_ms[7] = {0, 0, 0, 0, 0, 0, 0};

@@ -185,6 +185,15 @@ int run_grm(int argc, char** argv, Logger& log) {
     std::snprintf(line, sizeof(line), "  Device      : accumulate %.1f ms (SYRK %.1f ms), read-out + file write %.2f s, engine wall %.2f s", sm.device_pass_ms,
                   sm.syrk_ms, sm.write_s, sm.wall_s);
     log.info(line);
+    std::string ph = "  Host phases :";
+    for (const auto& p : sm.phases) {
+        std::snprintf(line, sizeof(line), " %s %.2f-%.2f s |", p.name.c_str(), p.begin, p.end);
+        ph += line;
+    }
+    if (!sm.phases.empty()) {
+        ph.pop_back();
+        log.info(ph);
+    }
     return 0;
 }
 

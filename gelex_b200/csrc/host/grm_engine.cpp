@@ -482,7 +482,22 @@ struct RunContext {
     std::mutex* mu;
     std::vector<std::string>* files;
     double* write_s;
+    Clock::time_point t_start;
+    std::vector<GrmEngine::Summary::Phase>* phases;
 };
+
+// Record a host-side phase (seconds since compute() began); per name the earliest begin and the latest end over the GPU threads.
+void note_phase(const RunContext& rc, const char* name, Clock::time_point a, Clock::time_point b) {
+    const double ta = std::chrono::duration<double>(a - rc.t_start).count(), tb = std::chrono::duration<double>(b - rc.t_start).count();
+    std::lock_guard<std::mutex> lk(*rc.mu);
+    for (auto& p : *rc.phases)
+        if (p.name == name) {
+            p.begin = std::min(p.begin, ta);
+            p.end = std::max(p.end, tb);
+            return;
+        }
+    rc.phases->push_back({name, ta, tb});
+}
 
 // Which part of an output file a handle contributes.
 struct WritePart {
@@ -766,8 +781,11 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
                           double* pass_ms, double* syrk_ms, const WritePart& part, int tile_rank, int tile_world, bool report, bool write_whole_here,
                           BedRelay* relay = nullptr) {
     HandleGuard hg;
+    const auto t_setup = Clock::now();
     hg.h = create_handle(rc, device, my_groups, keep_whole, tile_rank, tile_world);
     WriterPool pool(rc.cfg->writer_threads, rc.cfg->writer_threads + 2, std::max<int64_t>(kWriterBufferElems, rc.n_out));
+    const auto t_push = Clock::now();
+    note_phase(rc, "device setup", t_setup, t_push);
     int pending = -1;  // local index of a group that is complete on the device but not yet written
     auto group_name = [&](int li) { return ".chr" + rc.groups[static_cast<size_t>(my_groups[static_cast<size_t>(li)])].name; };
     // A chromosome that re-appears later in the BIM gives a second run with the same output name; the reference writes both, the
@@ -798,14 +816,22 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
     // through ggrm_finish_async: its first row bands cross PCIe while the last slab is still on the tensor cores.
     const bool whole_here = !rc.loco && (write_whole_here || part.kind == WritePart::OwnedTiles);
     check(hg.h, ggrm_finish_async(hg.h));
+    const auto t_readout = Clock::now();
+    note_phase(rc, "push", t_push, t_readout);
     if (rc.loco && pending >= 0 && !superseded(pending)) write_outputs(rc, hg.h, pending, group_name(pending), part, pool);
     if (whole_here) write_outputs(rc, hg.h, GGRM_GROUP_WHOLE, "", part, pool);
     check(hg.h, ggrm_finish(hg.h));
     note_timers(rc, hg.h, pass_ms, syrk_ms);
     if (rc.loco && keep_whole && (write_whole_here || part.kind == WritePart::OwnedTiles)) write_outputs(rc, hg.h, GGRM_GROUP_WHOLE, "", part, pool);
+    const auto t_teardown = Clock::now();
+    note_phase(rc, "read-out", t_readout, t_teardown);
     if (keep_handle != nullptr) {
         *keep_handle = hg.h;
         hg.h = nullptr;
+    } else {
+        ggrm_destroy(hg.h);
+        hg.h = nullptr;
+        note_phase(rc, "teardown", t_teardown, Clock::now());
     }
 }
 
@@ -864,9 +890,11 @@ void run_pipelined_rank(const RunContext& rc, ShardPipe& sp, size_t r, double* p
     for (int kind = 0; kind < 2; ++kind)
         if (kind == 0 ? rc.want_add : rc.want_dom) files[kind].open(output_base(rc, kind, "") + ".bin", rc.n_out, false, rc.writer);
     int64_t done = 0;
+    const auto t_push = Clock::now();
     push_range(rc, h, sp.snps[r].first, sp.snps[r].second, sp.snps[r].second - sp.snps[r].first, &done);
     check(h, ggrm_finish_async(h));
     const auto t0 = Clock::now();
+    note_phase(rc, "push", t_push, t0);
     try {
         for (const Strip& st : sp.mine[r]) {
             const auto t_wait = Clock::now();
@@ -899,6 +927,7 @@ void run_pipelined_rank(const RunContext& rc, ShardPipe& sp, size_t r, double* p
     pool.drain();
     for (auto& f : files) f.close_checked();
     note_timers(rc, h, pass_ms, syrk_ms);
+    note_phase(rc, "read-out", t0, Clock::now());
     std::lock_guard<std::mutex> lk(*rc.mu);
     *rc.write_s += since(t0);
 }
@@ -1064,6 +1093,7 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
         }
         const size_t world = pipe.snps.size();
         pipe.handles.assign(world, nullptr);
+        const auto t_setup = Clock::now();
         for (size_t r = 0; r < world; ++r) {  // handles first (contexts, accumulators, rings), in parallel
             threads.emplace_back([&, r] {
                 try {
@@ -1099,6 +1129,7 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
         pipe.flags.assign(world * static_cast<size_t>(pipe.n_bands), 0);
         precreate_outputs(rc, {""});
         prefaulters = start_prefault(rc);
+        note_phase(rc, "device setup", t_setup, Clock::now());
         for (size_t r = 0; r < world; ++r) {
             threads.emplace_back([&, r] {
                 try {
@@ -1298,6 +1329,15 @@ void GrmEngine::compute(const GrmObserver& observer) {
     fam.replace_extension(".fam");
     bim.replace_extension(".bim");
 
+    // CUDA contexts and kernel images come up on helper threads while this thread parses the metadata (0.3-0.5 s per cold
+    // process otherwise in front of the first push).  Failures are not reported here: ggrm_create repeats the checks and owns the
+    // error, after every input has been validated in the reference's order.
+    struct Warmers {
+        std::vector<std::thread> t;
+        ~Warmers() { for (auto& x : t) if (x.joinable()) x.join(); }
+    } warmers;
+    for (int dev : config_.gpus) warmers.t.emplace_back([dev] { (void)ggrm_warm_device(dev); });
+
     // GRM::GRM(bed_path): SampleManager::create_finalized + BedPipe (grm.cpp:36-40, bed_pipe.cpp:69-98)
     const std::vector<std::string> raw_ids = load_fam_ids(fam);
     const SampleOrder order = make_sample_order(raw_ids);
@@ -1306,6 +1346,7 @@ void GrmEngine::compute(const GrmObserver& observer) {
     const int64_t bpv = (n_raw + 3) / 4;
     const BedMapping bed(config_.bed_path, m, bpv);
     if (observer) observer(GrmDataLoadedEvent{order.ids.size(), static_cast<size_t>(m)});
+    const auto t_meta1 = Clock::now();
 
     const std::vector<std::string> chroms = load_bim_chromosomes(bim);
     std::string pattern_suffix;
@@ -1336,6 +1377,10 @@ void GrmEngine::compute(const GrmObserver& observer) {
     rc.mu = &mu;
     rc.files = &files;
     rc.write_s = &write_s;
+    rc.t_start = t_start;
+    rc.phases = &summary_.phases;
+    note_phase(rc, "metadata", t_start, t_meta1);
+    note_phase(rc, "work plan", t_meta1, Clock::now());
 
     const int n_gpus = static_cast<int>(config_.gpus.size());
     if (config_.writer_threads < 1) throw ArgumentValidationException("writer_threads must be >= 1");

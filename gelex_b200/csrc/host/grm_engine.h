@@ -96,6 +96,11 @@ class GrmEngine {
         double wall_s = 0, device_pass_ms = 0, syrk_ms = 0, write_s = 0;
         std::vector<std::string> files;
         bool outputs_mapped = false;  // the run was allowed to write through shared mappings (WriterMode, free-space check)
+        // Host-side phases of the run in seconds since compute() began, (name, begin, end); slowest GPU thread per phase.
+        // "metadata" FAM / BIM / BED mapping, "device setup" context + buffers, "push" first SNP pushed .. pass enqueued,
+        // "read-out" waiting for / fetching / writing the matrices still pending when the pass is enqueued, "teardown".
+        struct Phase { std::string name; double begin, end; };
+        std::vector<Phase> phases;
     };
     const Summary& summary() const { return summary_; }
 

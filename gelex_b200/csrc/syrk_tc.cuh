@@ -26,8 +26,18 @@ namespace ggrm {
 struct TcItem {
     int32_t a_row0;   // first GRM row of the item (128 rows for kCtaGroup 1, 256 for kCtaGroup 2)
     int32_t b_row0;   // first GRM column (= Z row) of the 256-column block
-    int64_t out_off;  // element offset of the item's first half tile in the accumulator
+    int64_t out_off;  // element offset of the item's first half tile in the accumulator (of copy `kpart` in split-K launches)
+    int32_t kpart;    // split-K: this item covers K blocks [kpart * nkb / ksplit, (kpart + 1) * nkb / ksplit) of the slab
+    int32_t pad_;
 };
+
+// K range of one work item.  ksplit == 1: the whole slab.  Few-tile problems (n <= ~2 300: fewer tiles than CTA pairs) are cut along
+// K instead, every part accumulating into its own copy of the tile (summed once per group by axpy_accum_kernel), so that one launch
+// still fills the machine - config C1 has 36 tiles for 74 CTA pairs.
+__device__ __forceinline__ void tc_k_range(const TcItem& item, int num_k_blocks, int ksplit, int* kb0, int* kb1) {
+    *kb0 = static_cast<int>(static_cast<int64_t>(item.kpart) * num_k_blocks / ksplit);
+    *kb1 = static_cast<int>(static_cast<int64_t>(item.kpart + 1) * num_k_blocks / ksplit);
+}
 
 constexpr int kTcBlockK = 64;                 // 64 x 16-bit = 128 B = one swizzle row
 constexpr int kTcABytes = 128 * 128;          // 128 rows x 128 B
@@ -47,8 +57,13 @@ struct TcConfig {
 template <int kCtaGroup>
 __global__ void __launch_bounds__(256, 1)
 syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ accum, const TcItem* __restrict__ items,
-               int num_items, int num_k_blocks, int k_block0, int accumulate, uint32_t ab_format, int cache_hints, int* fault_flag,
-               unsigned long long* wave_ctr, unsigned long long wave_base, int sync_every, float* __restrict__ fold) {
+               int num_items, int num_k_blocks, int ksplit, int lo_blk, int accumulate, int accumulate_split, uint32_t ab_format,
+               int cache_hints, int* fault_flag, unsigned long long* wave_ctr, unsigned long long wave_base, int sync_every,
+               float* __restrict__ fold) {
+    // lo_blk > 0: BF16 hi + lo operands (GGRM_PREC_BF16 on short inputs).  The operand matrix holds hi = bf16(z) in K blocks
+    // [0, lo_blk) and lo = bf16(z - hi) in [lo_blk, 2 lo_blk); every K block is accumulated three times - hi hi^T, hi lo^T,
+    // lo hi^T - which restores ~16 mantissa bits for 3x the tensor time (lo lo^T ~ 2^-18 relative is dropped).
+    const int nsub = lo_blk > 0 ? 3 : 1;
     using Cfg = TcConfig<kCtaGroup>;
     constexpr int kStages = Cfg::kStages;
     extern __shared__ uint8_t smem_raw[];
@@ -115,27 +130,32 @@ syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ a
             const TcItem item = items[it];
             const int32_t a_row = item.a_row0 + static_cast<int32_t>(cta_rank) * 128;
             const int32_t b_row = item.b_row0 + static_cast<int32_t>(cta_rank) * Cfg::kBRows;
-            for (int kb = 0; kb < num_k_blocks; ++kb) {
-                ptx::mbar_wait(&empty_bar[stage], phase ^ 1, fault_flag, 1);
-                if (ptx::elect_one()) {
-                    const int32_t kc = (k_block0 + kb) * kTcBlockK;
-                    uint8_t* sa = smem_a + stage * kTcABytes;
-                    uint8_t* sb = smem_b + stage * Cfg::kBBytes;
-                    if constexpr (kCtaGroup == 1) {
-                        ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-                        ptx::tma_load_2d(&tmap_z, &full_bar[stage], sa, kc, a_row, z_hint);
-                        ptx::tma_load_2d(&tmap_z, &full_bar[stage], sb, kc, b_row, b_hint);
-                        ptx::tma_load_2d(&tmap_z, &full_bar[stage], sb + kTcABytes, kc, b_row + 128, b_hint);
-                    } else {
-                        // both CTAs' bytes are counted on the leader's barrier
-                        if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
-                        else ptx::mbar_arrive_cluster(&full_bar[stage], 0);
-                        ptx::tma_load_2d_pair(&tmap_z, &full_bar[stage], sa, kc, a_row, z_hint);
-                        ptx::tma_load_2d_pair(&tmap_z, &full_bar[stage], sb, kc, b_row, b_hint);
+            int kb0, kb1;
+            tc_k_range(item, num_k_blocks, ksplit, &kb0, &kb1);
+            for (int kb = kb0; kb < kb1; ++kb) {
+                for (int sub = 0; sub < nsub; ++sub) {
+                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1, fault_flag, 1);
+                    if (ptx::elect_one()) {
+                        const int32_t kc_a = (kb + (sub == 2 ? lo_blk : 0)) * kTcBlockK;  // hi, hi, lo
+                        const int32_t kc_b = (kb + (sub == 1 ? lo_blk : 0)) * kTcBlockK;  // hi, lo, hi
+                        uint8_t* sa = smem_a + stage * kTcABytes;
+                        uint8_t* sb = smem_b + stage * Cfg::kBBytes;
+                        if constexpr (kCtaGroup == 1) {
+                            ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+                            ptx::tma_load_2d(&tmap_z, &full_bar[stage], sa, kc_a, a_row, z_hint);
+                            ptx::tma_load_2d(&tmap_z, &full_bar[stage], sb, kc_b, b_row, b_hint);
+                            ptx::tma_load_2d(&tmap_z, &full_bar[stage], sb + kTcABytes, kc_b, b_row + 128, b_hint);
+                        } else {
+                            // both CTAs' bytes are counted on the leader's barrier
+                            if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
+                            else ptx::mbar_arrive_cluster(&full_bar[stage], 0);
+                            ptx::tma_load_2d_pair(&tmap_z, &full_bar[stage], sa, kc_a, a_row, z_hint);
+                            ptx::tma_load_2d_pair(&tmap_z, &full_bar[stage], sb, kc_b, b_row, b_hint);
+                        }
                     }
+                    __syncwarp();
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
-                __syncwarp();
-                if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
         }
         if (sync_every > 0) {  // check in for the sync points of waves this CTA had no tile in
@@ -152,7 +172,10 @@ syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ a
             ptx::mbar_wait(&tmem_empty_bar[as], aphase ^ 1, fault_flag, 2);
             ptx::tc_fence_after();
             const uint32_t tmem_d = tmem_base + as * Cfg::kUmmaN;
-            for (int kb = 0; kb < num_k_blocks; ++kb) {
+            int kb0, kb1;
+            tc_k_range(items[it], num_k_blocks, ksplit, &kb0, &kb1);
+            const int n_steps = (kb1 - kb0) * nsub;  // >= 1: the host never launches a split with more parts than K blocks
+            for (int kb = 0; kb < n_steps; ++kb) {
                 ptx::mbar_wait(&full_bar[stage], phase, fault_flag, 3);
                 ptx::tc_fence_after();
                 if (ptx::elect_one()) {
@@ -166,7 +189,7 @@ syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ a
                     // frees the smem slot (both CTAs in pair mode) once the MMAs above have read it
                     if constexpr (kCtaGroup == 1) ptx::umma_commit(&empty_bar[stage]);
                     else ptx::umma_commit_pair(&empty_bar[stage], 0x3);
-                    if (kb == num_k_blocks - 1) {
+                    if (kb == n_steps - 1) {
                         if constexpr (kCtaGroup == 1) ptx::umma_commit(&tmem_full_bar[as]);
                         else ptx::umma_commit_pair(&tmem_full_bar[as], 0x3);
                     }
@@ -193,6 +216,7 @@ syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ a
             // LOCO: on the last slab of a chromosome the finished partial is also added into the whole-genome accumulator here,
             // while the tile is in registers (replaces a separate 3-access whole += partial pass over 5 GB per chromosome)
             float* out2 = fold != nullptr ? fold + tile_off : nullptr;
+            const int acc_item = item.kpart == 0 ? accumulate : accumulate_split;
 #pragma unroll 1
             for (int chunk = 0; chunk < 8; ++chunk) {
                 uint32_t v[32];
@@ -203,7 +227,7 @@ syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ a
                     float4* dst = reinterpret_cast<float4*>(out + (chunk * 8 + q) * (128 * 4));
                     float4 r = make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]),
                                            __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3]));
-                    if (accumulate) {
+                    if (acc_item) {
                         const float4 o = stream ? ptx::ld_stream_f4(dst, stream_policy) : *dst;
                         r.x += o.x; r.y += o.y; r.z += o.z; r.w += o.w;
                     }

@@ -291,6 +291,12 @@ int ggrm_stage_upload(ggrm_stage_t* s, int slot, const uint8_t* host_src, int64_
 int ggrm_stage_slot(ggrm_stage_t* s, int slot, const uint8_t** d_ptr);
 int ggrm_wait_copies(ggrm_t* h);
 
+/* Start-up overlap for hosts: creates the CUDA context of `device` and loads this library's kernels (0.3-0.5 s on a cold
+ * process) so that a host can do it on a helper thread while it parses FAM / BIM metadata, as the C++ GrmEngine does
+ * (the reference has nothing comparable: its start-up is the BedPipe / SampleManager construction, grm.cpp:36-40).
+ * Idempotent; errors are reported like those of ggrm_create (ggrm_last_error(NULL) on the calling thread). */
+int ggrm_warm_device(int device);
+
 /* Library / device facts for the harness. */
 int ggrm_device_count(void);
 const char* ggrm_version(void);

@@ -237,3 +237,32 @@ ORACLE_API void oracle_counts(const double* col, int64_t n, int32_t* out4) {
         else out4[2]++;
     }
 }
+
+/* Checker for the full-size configs (C2-C4), where the n x n FP64 matrix of oracle_grm_compute (20 GB at n = 50 000) and its
+ * n^2 m flops are out of reach on the host: the same per-column arithmetic (oracle_decode_chunk + oracle_process_column, i.e.
+ * bed_pipe.cpp:121-158 and genotype_processor.h:35-58) for `c` SNPs in parallel over columns, leaving the standardised chunk Z
+ * (column-major n_out x c) for the caller - tests form selected ROWS of Z Z^T from it with an FP64 GEMM - and adding every
+ * sample's z^2 into diag_accum[n_out] (the diagonal of Z Z^T, whose sum is the trace in GrmResult::denominator, grm.h:134). */
+ORACLE_API void oracle_standardise_chunk(const uint8_t* payload, int64_t c, int64_t bpv, int64_t n_raw, int64_t n_out,
+                                         const int32_t* raw_to_out, int method, int kind, double* Z, double* diag_accum,
+                                         double* freqs) {
+#pragma omp parallel
+    {
+        double* local = diag_accum != NULL ? (double*)calloc((size_t)n_out, sizeof(double)) : NULL;
+#pragma omp for schedule(static)
+        for (int64_t j = 0; j < c; ++j) {
+            double* col = Z + j * n_out;
+            oracle_locus_stat st;
+            oracle_decode_chunk(payload + j * bpv, 1, bpv, n_raw, n_out, raw_to_out, col);
+            oracle_process_column(col, n_out, method, kind, &st);
+            if (freqs != NULL) freqs[j] = st.maf;
+            if (local != NULL)
+                for (int64_t i = 0; i < n_out; ++i) local[i] += col[i] * col[i];
+        }
+        if (local != NULL) {
+#pragma omp critical
+            for (int64_t i = 0; i < n_out; ++i) diag_accum[i] += local[i];
+            free(local);
+        }
+    }
+}

@@ -8,6 +8,9 @@
 //           -> GrmEngine::compute (src/pipeline/grm_engine.cpp:52-124), prints one JSON line with wall s
 //   stages  <bfile> <method> <A|D> <chunk> <threads>
 //           -> the chunk loop of grm.h:111-132 re-timed stage by stage (decode / standardise / dsyrk)
+//   dense   <bfile> <method> <A|D> <chunk> <threads> <out.f64>
+//           -> GRM::compute<GT> (include/gelex/data/grm/grm.h:94-137), the FP64 result BEFORE the float32 cast of the writer:
+//              dumps n (int64), denominator (double), then the packed lower triangle row-major as doubles
 //   chunk   <bfile> <start> <end> <method> <A|D> <out.bin>
 //           -> BedPipe::load_chunk + process_matrix; dumps n, c, raw doubles, freqs, processed doubles
 //   process <method> <A|D> v0 v1 ...   (values 0,1,2 or nan) -> prints processed column, maf, mean, sd
@@ -196,6 +199,34 @@ int cmd_stages(int argc, char** argv)
     return 0;
 }
 
+int cmd_dense(int argc, char** argv)
+{
+    if (argc < 8) { return 2; }
+    std::string bed_path = std::string(argv[2]) + ".bed";
+    auto method = method_of(argv[3]);
+    bool add = std::string(argv[4]) != "D";
+    Eigen::Index chunk = std::atol(argv[5]);
+    set_threads(std::atoi(argv[6]));
+    gelex::GRM grm(bed_path);
+    auto t0 = Clock::now();
+    gelex::GrmResult res = add ? grm.compute<gelex::GeneticEffectType::Add>(method, chunk)
+                               : grm.compute<gelex::GeneticEffectType::Dom>(method, chunk);
+    auto t1 = Clock::now();
+    std::ofstream f(argv[7], std::ios::binary | std::ios::trunc);
+    const int64_t n = res.grm.rows();
+    f.write(reinterpret_cast<const char*>(&n), sizeof(n));
+    f.write(reinterpret_cast<const char*>(&res.denominator), sizeof(double));
+    std::vector<double> row(static_cast<size_t>(n));
+    for (int64_t i = 0; i < n; ++i)
+    {
+        for (int64_t j = 0; j <= i; ++j) { row[static_cast<size_t>(j)] = res.grm(i, j); }
+        write_doubles(f, row.data(), static_cast<size_t>(i + 1));
+    }
+    std::printf("{\"cmd\":\"dense\",\"n\":%lld,\"wall_s\":%.6f,\"denominator\":%.17g}\n", static_cast<long long>(n), secs(t0, t1),
+                res.denominator);
+    return f.good() ? 0 : 1;
+}
+
 int cmd_chunk(int argc, char** argv)
 {
     if (argc < 8) { return 2; }
@@ -313,7 +344,7 @@ int main(int argc, char** argv)
 {
     if (argc < 2)
     {
-        std::fprintf(stderr, "usage: gelex_ref grm|stages|chunk|process|loco|load|pipe ...\n");
+        std::fprintf(stderr, "usage: gelex_ref grm|stages|dense|chunk|process|loco|load|pipe ...\n");
         return 2;
     }
     try
@@ -321,6 +352,7 @@ int main(int argc, char** argv)
         std::string c = argv[1];
         if (c == "grm") { return cmd_grm(argc, argv); }
         if (c == "stages") { return cmd_stages(argc, argv); }
+        if (c == "dense") { return cmd_dense(argc, argv); }
         if (c == "chunk") { return cmd_chunk(argc, argv); }
         if (c == "process") { return cmd_process(argc, argv); }
         if (c == "loco") { return cmd_loco(argc, argv); }

@@ -42,6 +42,8 @@ def lib():
         l.oracle_loco.restype = None
         l.oracle_counts.argtypes = [vp, i64, vp]
         l.oracle_counts.restype = None
+        l.oracle_standardise_chunk.argtypes = [vp, i64, i64, i64, i64, vp, C.c_int, C.c_int, vp, vp, vp]
+        l.oracle_standardise_chunk.restype = None
         _lib = l
     return _lib
 
@@ -125,3 +127,28 @@ def loco(whole_packed, chr_packed, n):
     c = np.ascontiguousarray(chr_packed, dtype=np.float32)
     lib().oracle_loco(_p(w), _p(c), n, _p(out))
     return out
+
+
+def row_spot(payload, n_raw, method, kind, rows, groups=None, chunk=4096, n_out=None, raw_to_out=None):
+    """Checker for full-size configs: selected ROWS of the FP64 matrix Z Z^T and its full diagonal, per SNP group, without
+    ever forming the n x n matrix.  The standardised chunk comes from the oracle's own per-column arithmetic
+    (oracle_standardise_chunk = oracle_decode_chunk + oracle_process_column); the rows are an FP64 GEMM of it (numpy / BLAS).
+    groups: list of (begin, end) SNP ranges (default one group = all SNPs).
+    Returns (R, D): R[g] is (len(rows), n_out) with R[g][k, j] = G_g(rows[k], j); D[g] is the diagonal of G_g (n_out)."""
+    n_out = n_raw if n_out is None else n_out
+    bpv = (n_raw + 3) // 4
+    payload = np.ascontiguousarray(payload, dtype=np.uint8).reshape(-1, bpv)
+    m = payload.shape[0]
+    groups = [(0, m)] if groups is None else list(groups)
+    rows = np.asarray(rows, dtype=np.int64)
+    r2o = None if raw_to_out is None else np.ascontiguousarray(raw_to_out, dtype=np.int32)
+    R = [np.zeros((rows.size, n_out), dtype=np.float64) for _ in groups]
+    D = [np.zeros(n_out, dtype=np.float64) for _ in groups]
+    buf = np.empty((min(chunk, m), n_out), dtype=np.float64)  # (c, n) C-order == column-major n x c
+    for gi, (b, e) in enumerate(groups):
+        for s in range(b, e, chunk):
+            c = min(chunk, e - s)
+            z = buf[:c]
+            lib().oracle_standardise_chunk(_p(payload[s:s + c]), c, bpv, n_raw, n_out, _p(r2o), method, kind, _p(z), _p(D[gi]), None)
+            R[gi] += z[:, rows].T @ z
+    return R, D

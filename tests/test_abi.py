@@ -110,3 +110,12 @@ def test_built_library_holds_blackwell_tensor_and_tma_instructions():
     f64 = [body for name, body in funcs.items() if "syrk_f64_kernel" in name]
     assert len(f64) == 1 and "DMMA" in f64[0]
     assert not any(re.search(r"\bHMMA\b", body) for body in funcs.values())
+
+
+def test_numpy_synth_matches_library():
+    # bench.py's reference arm builds its PLINK triple with tests/synth_np.py so that it never maps libggrm_b200.so;
+    # the bytes must be the ones the GPU arm's generator (csrc/synth.h) produces
+    import synth_np
+
+    for n, m, s0, seed, miss in ((1001, 300, 0, 7, 0.01), (4000, 130, 1234, 20261106, 0.03), (257, 70, 5, 1, 0.0), (64, 9, 0, 3, 1.0)):
+        assert np.array_equal(synth_np.synth_bed(n, s0, m, seed, miss, threads=2, block=64), g.synth_bed_host(n, s0, m, seed, miss))

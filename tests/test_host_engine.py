@@ -304,8 +304,6 @@ def test_bed_relay_upload_failure_surfaces_instead_of_hanging():
 
 
 @pytest.mark.gpu
-@pytest.mark.skipif(os.environ.get("GELEX_B200_TEST_UNVERIFIED") != "1",
-                    reason="BED relay device path was written after the round's GPU minutes were spent: opt in with GELEX_B200_TEST_UNVERIFIED=1")
 @pytest.mark.parametrize("loco", [False, True])
 def test_engine_tile_mode_bed_relay_matches_direct_push(tmp_path, monkeypatch, loco):
     # same 2D-tile run with every GPU reading the whole BED itself, and with one upload per chunk shared through staging slots
@@ -327,8 +325,6 @@ def test_engine_tile_mode_bed_relay_matches_direct_push(tmp_path, monkeypatch, l
 
 
 @pytest.mark.gpu
-@pytest.mark.skipif(os.environ.get("GELEX_B200_TEST_UNVERIFIED") != "1",
-                    reason="added after the round's GPU minutes were spent: opt in with GELEX_B200_TEST_UNVERIFIED=1 (tools/r02_first_run.sh)")
 @pytest.mark.parametrize("n_gpus", [1, 3])
 def test_engine_loco_reappearing_chromosome_last_run_wins(tmp_path, monkeypatch, n_gpus):
     # BIM order 1,2,1,X: the reference writes add.chr1 twice, the second run over the first (pinned against the reference binary in
@@ -352,8 +348,6 @@ def test_engine_loco_reappearing_chromosome_last_run_wins(tmp_path, monkeypatch,
 
 
 @pytest.mark.gpu
-@pytest.mark.skipif(os.environ.get("GELEX_B200_TEST_UNVERIFIED") != "1",
-                    reason="added after the round's GPU minutes were spent: opt in with GELEX_B200_TEST_UNVERIFIED=1 (tools/r02_first_run.sh)")
 @pytest.mark.parametrize("n_gpus,partition", [(1, "auto"), (2, "snp"), (2, "tile")])
 def test_engine_prefault_gives_identical_files(tmp_path, monkeypatch, n_gpus, partition):
     # Config::prefault (here through GELEX_B200_PREFAULT): the .bin exists from the start of the pass and its pages are populated while the
@@ -376,9 +370,7 @@ REF_BINDING = Path(__file__).resolve().parent.parent / "oracle" / "_ref" / "gele
 
 
 @pytest.mark.gpu
-@pytest.mark.skipif(os.environ.get("GELEX_B200_TEST_UNVERIFIED") != "1" or not REF_BINDING.exists(),
-                    reason="oracle/_ref/gelex_ref_b200 (built where /root/reference exists) was added after the round's GPU minutes were spent: "
-                           "opt in with GELEX_B200_TEST_UNVERIFIED=1")
+@pytest.mark.skipif(not REF_BINDING.exists(), reason="oracle/_ref/gelex_ref_b200 (the reference-side binding program) is not built")
 def test_reference_host_code_over_the_c_abi_writes_the_reference_files(golden_dir, tmp_path):
     # INTEGRATION.md section 2 as a program (oracle/ref_binding.cpp): the UNMODIFIED reference's SampleManager, BedPipe projection + mmap,
     # work plans and GrmBinWriter / GrmIdWriter, with only the chunk loop of GRM::compute<GT> replaced by ggrm_create / push / finish /
@@ -635,8 +627,6 @@ def test_genotype_export_files_match_reference_layout(golden_dir, tmp_path, meth
 
 
 @pytest.mark.gpu
-@pytest.mark.skipif(os.environ.get("GELEX_B200_TEST_UNVERIFIED") != "1",
-                    reason="added after the round's GPU minutes were spent: opt in with GELEX_B200_TEST_UNVERIFIED=1 (tools/r02_first_run.sh)")
 @pytest.mark.parametrize("method,additive,chunk", [("OSH", True, 25), ("SH", False, 7), ("OC", False, 40), ("S", True, 33)])
 def test_genotype_export_files_against_the_reference_pipe_files(golden_dir, tmp_path, method, additive, chunk):
     # our .bmat / .snpstats beside the files the unmodified reference's GenotypePipe wrote for the same input (tests/golden/tiny_pipe_*):
@@ -651,10 +641,17 @@ def test_genotype_export_files_against_the_reference_pipe_files(golden_dir, tmp_
     assert (tmp_path / "t.snpstats").stat().st_size == Path(str(base) + ".snpstats").stat().st_size
     assert (gm["num_samples"], gm["num_variants"]) == (rm["num_samples"], rm["num_variants"])
     assert gm["monomorphic_indices"].tolist() == rm["monomorphic_indices"].tolist()
+    # mean / stddev: 2 ulp where they are closed forms of the allele frequency (HWE policies, additive sample mean).  The sample
+    # policy's dominance mean and every sample stddev are SUMS over the column in the reference (statistic_policy.h:61-65, 70-78):
+    # Eigen adds n rounded terms in its own (vectorised) order, the device evaluates n1*e1 + n2*e2 and the three-term sum of
+    # squares from the integer counts, so the two differ by the reference's own summation rounding - a few ulp on the tiny fixture (measured
+    # 4), bounded here by 16.
+    sums = method in ("S", "C", "OS", "OC")
+    ulps = {"mean": 16 if (sums and not additive) else 2, "stddev": 16 if sums else 2}
     for key in ("mean", "stddev"):
         assert np.array_equal(np.isnan(gm[key]), np.isnan(rm[key]))
         ok = ~np.isnan(rm[key])
-        assert np.all(np.abs(gm[key][ok] - rm[key][ok]) <= 2 * np.spacing(np.abs(rm[key][ok])) + 1e-300), key
+        assert np.all(np.abs(gm[key][ok] - rm[key][ok]) <= ulps[key] * np.spacing(np.abs(rm[key][ok])) + 1e-300), key
 
 
 @pytest.mark.gpu
