@@ -37,7 +37,7 @@ const char* kUsage =
     "Usage: gelex-b200 grm [--help] --bfile <BFILE> [--out <OUT>] [--geno-method <STR>] [--chunk-size <SIZE>]\n"
     "                      [--threads <N>] [--add] [--dom] [--loco] [--gpus <N>] [--precision <fp16|bf16|fp64>]\n"
     "                      [--partition <auto|snp|tile>] [--writer-threads <N>] [--writer <auto|pwrite|mmap>]\n"
-    "                      [--prefault] [--bed-relay] [--with-whole] [--skip-all-missing] [--gcta]\n\n"
+    "                      [--no-prefault] [--bed-relay] [--with-whole] [--skip-all-missing] [--gcta]\n\n"
     "Compute genomic relationship matrix (GRM) from PLINK binary files and output in GCTA format\n\n"
     "Data Files:\n"
     "  -b, --bfile <BFILE>        PLINK binary file prefix (.bed/.bim/.fam) [required]\n"
@@ -57,7 +57,7 @@ const char* kUsage =
     "  --writer-threads <N>       writer threads per GPU draining the read-out ring [default: 4]\n"
     "  --writer <auto|pwrite|mmap> How blocks reach the .bin: pwrite, or memcpy into a shared mapping of the pre-sized file\n"
     "                             (auto: mapping for scattered tile rows and on tmpfs, when the file system has room) [default: auto]\n"
-    "  --prefault                 Without --loco: create the .bin first and populate its pages while the GPUs accumulate\n"
+    "  --no-prefault              Do not create the .bin files ahead of the writers and populate their pages meanwhile (default: do)\n"
     "  --bed-relay                2D-tile partition: upload each BED chunk once and share it between the GPUs over NVLink\n"
     "  --with-whole               With --loco also write the whole-genome matrix (sum of the partials, same pass)\n"
     "  --skip-all-missing         Treat an all-missing SNP as contributing 0 (the reference lets it poison the GRM with NaN)\n"
@@ -69,7 +69,7 @@ int run_grm(int argc, char** argv, Logger& log) {
     std::string bfile, out = "grm", gm = "OSH", precision = "fp16", partition = "auto", writer = "auto";
     int chunk = 10000, gpus = 1, writer_threads = 4;
     int threads = static_cast<int>(std::thread::hardware_concurrency() / 2);
-    bool add = false, dom = false, loco = false, with_whole = false, skip_missing = false, gcta = false, bed_relay = false, prefault = false;
+    bool add = false, dom = false, loco = false, with_whole = false, skip_missing = false, gcta = false, bed_relay = false, prefault = true;
     auto need = [&](int& i) -> std::string {
         if (i + 1 >= argc) throw ArgumentValidationException(std::string("Too few arguments for '") + argv[i] + "'.");
         return argv[++i];
@@ -103,6 +103,7 @@ int run_grm(int argc, char** argv, Logger& log) {
         else if (a == "--with-whole") with_whole = true;
         else if (a == "--bed-relay") bed_relay = true;
         else if (a == "--prefault") prefault = true;
+        else if (a == "--no-prefault") prefault = false;
         else if (a == "--skip-all-missing") skip_missing = true;
         else if (a == "--gcta") gcta = true;
         else throw ArgumentValidationException("Unknown argument: " + a);

@@ -67,21 +67,28 @@ constexpr int64_t kMapSegmentBytes = int64_t{256} << 10;
 // Mappings that a Prefaulter has populated, by inode.  A BinFile opened for the same file writes through THAT mapping instead of a
 // fresh one of its own: the pages are already in this process's page tables (measured: 23 GB/s, against 5.6 GB/s through a second
 // mapping of the same populated file, which still takes a minor fault per page).  A Prefaulter outlives every BinFile of its run.
+class Prefaulter;
 struct SharedMappings {
+    struct Entry { char* map; size_t bytes; Prefaulter* owner; };
     std::mutex mu;
-    std::map<std::pair<uint64_t, uint64_t>, std::pair<char*, size_t>> by_inode;
+    std::map<std::pair<uint64_t, uint64_t>, Entry> by_inode;
     static SharedMappings& get() {
         static SharedMappings s;
         return s;
     }
-    char* find(int fd, size_t bytes) {
+    bool find(int fd, size_t bytes, Entry* out) {
         struct stat st {};
-        if (::fstat(fd, &st) != 0) return nullptr;
+        if (::fstat(fd, &st) != 0) return false;
         std::lock_guard<std::mutex> lk(mu);
         const auto it = by_inode.find({static_cast<uint64_t>(st.st_dev), static_cast<uint64_t>(st.st_ino)});
-        return it != by_inode.end() && it->second.second == bytes ? it->second.first : nullptr;
+        if (it == by_inode.end() || it->second.bytes != bytes) return false;
+        *out = it->second;
+        return true;
     }
 };
+// Blocks until the prefaulter has tried every piece; false = it could not populate the file (no room, old kernel): a store into
+// the mapping might then raise SIGBUS, so the caller must write with pwrite, whose ENOSPC becomes FileWriteException.
+bool prefault_completed_ok(Prefaulter* p);
 
 struct BinFile {
     int fd = -1;
@@ -90,6 +97,7 @@ struct BinFile {
     size_t map_bytes = 0;
     bool owns_map = true;      // false: the mapping belongs to a Prefaulter (SharedMappings)
     bool map_all = false;      // every segment goes through the mapping (tmpfs, or WriterMode::Mmap)
+    bool on_tmpfs = false;
     BinFile() = default;
     BinFile(const BinFile&) = delete;
     BinFile& operator=(const BinFile&) = delete;
@@ -98,7 +106,9 @@ struct BinFile {
         if (fd >= 0) ::close(fd);
     }
     // create = truncate + size the file (one caller); otherwise open an existing, already sized file for writing
-    void open(const fs::path& p, int64_t n, bool create, WriterMode mode = WriterMode::Pwrite) {
+    // use_prepared: a mapping of this very file that a Prefaulter of this process has fully populated is written through even in
+    // Pwrite mode (its pages exist, so no store can fault for lack of space); the caller passes false when the user forced pwrite
+    void open(const fs::path& p, int64_t n, bool create, WriterMode mode = WriterMode::Pwrite, bool use_prepared = true) {
         path = p.string();
         const int extra = create ? (O_CREAT | O_TRUNC) : 0;
         if (mode != WriterMode::Pwrite) fd = ::open(path.c_str(), O_RDWR | extra, 0644);  // a shared writable mapping needs read access too
@@ -110,23 +120,28 @@ struct BinFile {
         const int64_t bytes = n * (n + 1) / 2 * static_cast<int64_t>(sizeof(float));
         if (create && ::ftruncate(fd, static_cast<off_t>(bytes)) != 0)
             throw FileWriteException(path + ": failed to write GRM data to binary file");
-        if (mode == WriterMode::Pwrite || bytes == 0) return;
-        if (char* shared = create ? nullptr : SharedMappings::get().find(fd, static_cast<size_t>(bytes))) {
-            map = shared;
+        if (bytes == 0) return;
+        SharedMappings::Entry shared{};
+        if (!create && use_prepared && SharedMappings::get().find(fd, static_cast<size_t>(bytes), &shared)) {
+            if (!prefault_completed_ok(shared.owner)) return;  // not populated: pwrite only (see prefault_completed_ok)
+            map = shared.map;
             owns_map = false;
         } else {
+            if (mode == WriterMode::Pwrite) return;
             void* m = ::mmap(nullptr, static_cast<size_t>(bytes), PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
             if (m == MAP_FAILED) return;  // e.g. a file system without mmap: pwrite still works
             map = static_cast<char*>(m);
         }
         map_bytes = static_cast<size_t>(bytes);
         struct statfs sf {};
-        const bool tmpfs = ::fstatfs(fd, &sf) == 0 && static_cast<unsigned long>(sf.f_type) == 0x01021994ul;  // TMPFS_MAGIC
-        map_all = mode == WriterMode::Mmap || tmpfs || !owns_map;  // a populated mapping takes every segment
+        on_tmpfs = ::fstatfs(fd, &sf) == 0 && static_cast<unsigned long>(sf.f_type) == 0x01021994ul;  // TMPFS_MAGIC
+        map_all = mode == WriterMode::Mmap || on_tmpfs || !owns_map;  // a populated mapping takes every segment
     }
     void close_checked() {
         if (map != nullptr) {
-            const int rc = owns_map ? ::munmap(map, map_bytes) : 0;
+            // stores into a mapping of a disk file reach the disk by write-back, whose errors only msync reports (tmpfs has none)
+            int rc = on_tmpfs ? 0 : ::msync(map, map_bytes, MS_SYNC);
+            if (owns_map && ::munmap(map, map_bytes) != 0) rc = -1;
             map = nullptr;
             if (rc != 0) throw FileWriteException(path + ": failed to write GRM data to binary file");
         }
@@ -167,9 +182,10 @@ class Prefaulter {
             auto& reg = SharedMappings::get();
             std::lock_guard<std::mutex> lk(reg.mu);
             key_ = {static_cast<uint64_t>(st.st_dev), static_cast<uint64_t>(st.st_ino)};
-            registered_ = reg.by_inode.emplace(key_, std::make_pair(map_, bytes_)).second;
+            registered_ = reg.by_inode.emplace(key_, SharedMappings::Entry{map_, bytes_, this}).second;
         }
-        for (int t = 0; t < std::max(1, threads); ++t) workers_.emplace_back([this] { run(); });
+        running_.store(std::max(1, threads));
+        for (int t = 0; t < std::max(1, threads); ++t) workers_.emplace_back([this] { run(); running_.fetch_sub(1); });
     }
     Prefaulter(const Prefaulter&) = delete;
     Prefaulter& operator=(const Prefaulter&) = delete;
@@ -189,6 +205,9 @@ class Prefaulter {
         workers_.clear();
     }
     size_t populated_bytes() const { return populated_.load(); }
+    // every piece tried (any thread may ask; does not join) / every piece populated
+    bool finished() const { return running_.load() == 0; }
+    bool ok() const { return finished() && !failed_.load() && populated_.load() == bytes_; }
 
    private:
     static constexpr size_t kPiece = size_t{64} << 20;
@@ -198,9 +217,13 @@ class Prefaulter {
             if (off >= bytes_ || stop_.load()) return;
             const size_t len = std::min(kPiece, bytes_ - off);
 #ifdef MADV_POPULATE_WRITE
-            if (::madvise(map_ + off, len, MADV_POPULATE_WRITE) != 0) return;  // old kernel, or no room: leave the rest to the writers
+            if (::madvise(map_ + off, len, MADV_POPULATE_WRITE) != 0) {  // old kernel, or no room: the writers fall back to pwrite
+                failed_.store(true);
+                return;
+            }
             populated_.fetch_add(len);
 #else
+            failed_.store(true);
             return;
 #endif
         }
@@ -209,11 +232,18 @@ class Prefaulter {
     char* map_ = nullptr;
     size_t bytes_ = 0;
     std::atomic<size_t> next_{0}, populated_{0};
-    std::atomic<bool> stop_{false};
+    std::atomic<bool> stop_{false}, failed_{false};
+    std::atomic<int> running_{0};
     std::vector<std::thread> workers_;
     std::pair<uint64_t, uint64_t> key_{0, 0};
     bool registered_ = false;
 };
+
+bool prefault_completed_ok(Prefaulter* p) {
+    if (p == nullptr) return false;
+    while (!p->finished()) std::this_thread::sleep_for(std::chrono::microseconds(100));
+    return p->ok();
+}
 
 struct Segment { int64_t src_elem, file_byte, bytes; };  // buffer elements [src_elem, +bytes/4) -> file bytes [file_byte, +bytes)
 
@@ -476,7 +506,8 @@ struct RunContext {
     bool gcta;  // kind 1 is the non-missing pair count matrix; outputs are <out>.grm.bin / .grm.N.bin / .grm.id
     WriterMode writer;  // effective mode of this run: Pwrite when the file system could not hold every output (see BinFile)
     bool bed_relay;     // 2D-tile mode: one upload per host chunk, peers copy it over NVLink (BedRelay)
-    bool prefault;      // non-LOCO runs with mapped outputs: populate the output pages while the GPUs accumulate (Prefaulter)
+    bool prefault;      // create output files ahead of the writers and populate their pages meanwhile (Prefaulter / OutputPreparer);
+                        // false when the user forced pwrite.  Independent of `writer`: a populated mapping cannot fault for lack of space
     // progress (reference: per work item, counted in SNPs; grm.h:124-130)
     const GrmObserver* observer;
     std::mutex* mu;
@@ -504,6 +535,7 @@ struct WritePart {
     enum Kind { AllRows, RowSlice, OwnedTiles } kind = AllRows;
     int64_t r0 = 0, r1 = 0;   // RowSlice
     bool create = true;        // this caller creates + sizes the .bin and writes the .id (otherwise the main thread did)
+    bool precreated = false;   // with create: the .bin already exists, sized (and populated) by an OutputPreparer; .id / registration still ours
 };
 
 ggrm_t* create_handle(const RunContext& rc, int device, const std::vector<int>& my_groups, bool keep_whole, int tile_rank = 0, int tile_world = 1) {
@@ -540,8 +572,18 @@ ggrm_t* create_handle(const RunContext& rc, int device, const std::vector<int>& 
 void emit_progress(const RunContext& rc, size_t current, size_t total) {
     if (rc.observer == nullptr || !*rc.observer) return;
     std::lock_guard<std::mutex> lk(*rc.mu);
-    const int kinds = (rc.want_add ? 1 : 0) + (rc.want_dom ? 1 : 0);
+    const int kinds = (rc.want_add ? 1 : 0) + (rc.want_dom && !rc.gcta ? 1 : 0);
     for (int k = 0; k < kinds; ++k) (*rc.observer)(GrmProgressEvent{current, total, false});
+}
+
+// SNP shards of ONE work item on several GPUs: the observer was told the item has `total` SNPs (GrmComputeStartedEvent), so the
+// ranks report against one shared counter - (sum over ranks, total), monotone because the counter moves under the observer's lock.
+void emit_progress_shared(const RunContext& rc, int64_t* shared_done, int64_t step, size_t total) {
+    std::lock_guard<std::mutex> lk(*rc.mu);
+    *shared_done += step;
+    if (rc.observer == nullptr || !*rc.observer) return;
+    const int kinds = (rc.want_add ? 1 : 0) + (rc.want_dom && !rc.gcta ? 1 : 0);
+    for (int k = 0; k < kinds; ++k) (*rc.observer)(GrmProgressEvent{static_cast<size_t>(*shared_done), total, false});
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -683,7 +725,7 @@ class BedRelay {
 
 // Push SNPs [begin, end) in host chunks of cfg.chunk_size (the reference's load_chunk granularity); through the relay when there is one.
 void push_range(const RunContext& rc, ggrm_t* h, int64_t begin, int64_t end, int64_t item_total, int64_t* item_done, bool report = true,
-                BedRelay* relay = nullptr) {
+                BedRelay* relay = nullptr, int64_t* shared_done = nullptr) {
     for (int64_t s = begin; s < end; s += rc.cfg->chunk_size) {
         const int64_t c = std::min<int64_t>(rc.cfg->chunk_size, end - s);
         if (s < 0 || s + c > rc.m || c <= 0)  // validate_chunk_range, bed_pipe.cpp:38-52
@@ -696,7 +738,8 @@ void push_range(const RunContext& rc, ggrm_t* h, int64_t begin, int64_t end, int
             check(h, ggrm_push(h, p, s, c, rc.bpv));
         }
         *item_done += c;
-        if (report) emit_progress(rc, static_cast<size_t>(*item_done), static_cast<size_t>(item_total));
+        if (report && shared_done != nullptr) emit_progress_shared(rc, shared_done, c, static_cast<size_t>(item_total));
+        else if (report) emit_progress(rc, static_cast<size_t>(*item_done), static_cast<size_t>(item_total));
     }
 }
 
@@ -729,14 +772,90 @@ void precreate_outputs(const RunContext& rc, const std::vector<std::string>& suf
 
 // Prefaulters for the whole-genome .bin of every requested kind (files must exist, pre-sized).  Empty unless the run maps its
 // outputs, asked for it, and is not a LOCO run (whose files are written one after another while the GPU is already ahead).
-std::vector<std::unique_ptr<Prefaulter>> start_prefault(const RunContext& rc) {
+std::vector<std::unique_ptr<Prefaulter>> start_prefault(const RunContext& rc, bool whole_of_loco_run = false) {
     std::vector<std::unique_ptr<Prefaulter>> out;
-    if (!rc.prefault || rc.loco || rc.writer == WriterMode::Pwrite) return out;
+    if (!rc.prefault || (rc.loco && !whole_of_loco_run)) return out;
     for (int kind = 0; kind < 2; ++kind)
         if (kind == 0 ? rc.want_add : rc.want_dom)
             out.push_back(std::make_unique<Prefaulter>(output_base(rc, kind, "") + ".bin", std::max(2, rc.cfg->writer_threads)));
     return out;
 }
+
+// LOCO runs write one 5 GB file per chromosome, one after another, and page allocation - not copying - is what a fresh file
+// costs (see Prefaulter).  An OutputPreparer walks the run's output list a few files ahead of the writer: it creates and sizes
+// file i + 1 .. i + ahead and populates their pages on its own threads while the writers copy file i into pages that are
+// already there.  The populated mapping stays registered (SharedMappings) until the writer reports the file done, so the
+// BinFile of that file writes through it.  A preparation that fails (no room, old kernel) leaves the file to the writer, which
+// then creates it itself and fails the reference's way.
+class OutputPreparer {
+   public:
+    OutputPreparer(std::vector<std::vector<std::string>> bins /* per entry: the .bin paths written together */, int64_t n, int threads, int ahead)
+        : bins_(std::move(bins)), n_(n), threads_(std::max(1, threads)), ahead_(std::max(1, ahead)), ready_(bins_.size()), ok_(bins_.size()), slots_(bins_.size()) {
+        for (auto& r : ready_) r.store(0);
+        worker_ = std::thread([this] { run(); });
+    }
+    OutputPreparer(const OutputPreparer&) = delete;
+    OutputPreparer& operator=(const OutputPreparer&) = delete;
+    ~OutputPreparer() {
+        stop_.store(true);
+        if (worker_.joinable()) worker_.join();
+    }
+    // Blocks until entry i has been prepared (or given up on); true = the files exist, sized, pages populated.
+    bool wait_ready(size_t i) {
+        while (ready_[i].load(std::memory_order_acquire) == 0) std::this_thread::sleep_for(std::chrono::microseconds(50));
+        return ok_[i] != 0;
+    }
+    // The writer has closed entry i's files: drop their populated mappings and let the preparer move on.
+    void done(size_t i) {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            slots_[i].clear();
+        }
+        done_.fetch_add(1);
+    }
+
+   private:
+    void run() {
+        for (size_t i = 0; i < bins_.size() && !stop_.load(); ++i) {
+            while (i >= done_.load() + static_cast<size_t>(ahead_) && !stop_.load()) std::this_thread::sleep_for(std::chrono::microseconds(200));
+            if (stop_.load()) break;
+            bool ok = true;
+            std::vector<std::unique_ptr<Prefaulter>> made;
+            try {
+                for (const std::string& path : bins_[i]) {
+                    BinFile f;
+                    f.open(path, n_, true);
+                    f.close_checked();
+                    made.push_back(std::make_unique<Prefaulter>(path, threads_));
+                    made.back()->wait();
+                }
+            } catch (...) {
+                ok = false;  // the writer creates the file itself and reports the error the reference would
+                made.clear();
+            }
+            {
+                std::lock_guard<std::mutex> lk(mu_);
+                slots_[i] = std::move(made);
+            }
+            ok_[i] = ok ? 1 : 0;
+            ready_[i].store(1, std::memory_order_release);
+        }
+        for (auto& r : ready_) {  // stopped early: nobody may wait forever
+            int z = 0;
+            r.compare_exchange_strong(z, 1);
+        }
+    }
+    std::vector<std::vector<std::string>> bins_;
+    int64_t n_;
+    int threads_, ahead_;
+    std::vector<std::atomic<int>> ready_;
+    std::vector<char> ok_;
+    std::vector<std::vector<std::unique_ptr<Prefaulter>>> slots_;
+    std::atomic<size_t> done_{0};
+    std::atomic<bool> stop_{false};
+    std::mutex mu_;
+    std::thread worker_;
+};
 
 void write_outputs(const RunContext& rc, ggrm_t* h, int local_group, const std::string& suffix /* "" or ".chrNAME" */, const WritePart& part,
                    WriterPool& pool) {
@@ -745,7 +864,7 @@ void write_outputs(const RunContext& rc, ggrm_t* h, int local_group, const std::
         if (!(kind == 0 ? rc.want_add : rc.want_dom)) continue;
         const std::string base = output_base(rc, kind, suffix);
         BinFile f;
-        f.open(base + ".bin", rc.n_out, part.create, rc.writer);
+        f.open(base + ".bin", rc.n_out, part.create && !part.precreated, rc.writer, rc.prefault);
         try {
             switch (part.kind) {
                 case WritePart::AllRows: write_packed_rows(h, kind, local_group, 0, rc.n_out, f, pool, rc.gcta); break;
@@ -797,6 +916,37 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
             if (rc.groups[later].name == rc.groups[gi].name) return true;
         return false;
     };
+    // LOCO, this handle writes whole files: prepare the chromosome files (and the whole-genome one, written last) ahead of the writer
+    std::unique_ptr<OutputPreparer> preparer;
+    std::vector<int> prep_index(my_groups.size() + 1, -1);  // local group (last slot: the whole-genome file) -> preparer entry
+    const bool whole_last = rc.loco && keep_whole && write_whole_here;
+    if (rc.loco && rc.prefault && part.kind == WritePart::AllRows && part.create) {
+        std::vector<std::vector<std::string>> bins;
+        auto entry = [&](const std::string& suffix) {
+            std::vector<std::string> v;
+            for (int kind = 0; kind < 2; ++kind)
+                if (kind == 0 ? rc.want_add : rc.want_dom) v.push_back(output_base(rc, kind, suffix) + ".bin");
+            bins.push_back(std::move(v));
+            return static_cast<int>(bins.size()) - 1;
+        };
+        for (size_t li = 0; li < my_groups.size(); ++li)
+            if (!superseded(static_cast<int>(li))) prep_index[li] = entry(group_name(static_cast<int>(li)));
+        if (whole_last) prep_index[my_groups.size()] = entry("");
+        if (!bins.empty()) preparer = std::make_unique<OutputPreparer>(std::move(bins), rc.n_out, std::max(2, rc.cfg->writer_threads), 2);
+    }
+    // write one prepared (or not) output entry
+    auto write_entry = [&](int local_group, const std::string& suffix, size_t slot) {
+        WritePart p = part;
+        const int pi = prep_index[slot];
+        if (preparer && pi >= 0) p.precreated = preparer->wait_ready(static_cast<size_t>(pi));
+        try {
+            write_outputs(rc, hg.h, local_group, suffix, p, pool);
+        } catch (...) {
+            if (preparer && pi >= 0) preparer->done(static_cast<size_t>(pi));
+            throw;
+        }
+        if (preparer && pi >= 0) preparer->done(static_cast<size_t>(pi));
+    };
     for (size_t li = 0; li < my_groups.size(); ++li) {
         const ChrRun& run = rc.groups[static_cast<size_t>(my_groups[li])];
         int64_t done = 0;
@@ -804,7 +954,7 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
         const int64_t first_end = std::min<int64_t>(run.end, run.begin + rc.cfg->chunk_size);
         push_range(rc, hg.h, run.begin, first_end, run.end - run.begin, &done, report, relay);
         if (pending >= 0) {
-            if (!superseded(pending)) write_outputs(rc, hg.h, pending, group_name(pending), part, pool);
+            if (!superseded(pending)) write_entry(pending, group_name(pending), static_cast<size_t>(pending));
             for (int kind = 0; kind < 2; ++kind)
                 if (kind == 0 ? rc.want_add : rc.want_dom) check(hg.h, ggrm_release_group(hg.h, kind, pending));
             pending = -1;
@@ -818,11 +968,12 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
     check(hg.h, ggrm_finish_async(hg.h));
     const auto t_readout = Clock::now();
     note_phase(rc, "push", t_push, t_readout);
-    if (rc.loco && pending >= 0 && !superseded(pending)) write_outputs(rc, hg.h, pending, group_name(pending), part, pool);
+    if (rc.loco && pending >= 0 && !superseded(pending)) write_entry(pending, group_name(pending), static_cast<size_t>(pending));
     if (whole_here) write_outputs(rc, hg.h, GGRM_GROUP_WHOLE, "", part, pool);
     check(hg.h, ggrm_finish(hg.h));
     note_timers(rc, hg.h, pass_ms, syrk_ms);
-    if (rc.loco && keep_whole && (write_whole_here || part.kind == WritePart::OwnedTiles)) write_outputs(rc, hg.h, GGRM_GROUP_WHOLE, "", part, pool);
+    if (rc.loco && keep_whole && (write_whole_here || part.kind == WritePart::OwnedTiles)) write_entry(GGRM_GROUP_WHOLE, "", my_groups.size());
+    preparer.reset();
     const auto t_teardown = Clock::now();
     note_phase(rc, "read-out", t_readout, t_teardown);
     if (keep_handle != nullptr) {
@@ -877,6 +1028,7 @@ struct ShardPipe {
     std::vector<int32_t> flags;                   // [rank][band], written by CUDA host callbacks
     int n_bands = 1;
     std::atomic<bool> failed{false};
+    int64_t snps_done = 0;                        // over all ranks (progress events; guarded by the observer's mutex)
 };
 
 void run_pipelined_rank(const RunContext& rc, ShardPipe& sp, size_t r, double* pass_ms, double* syrk_ms) {
@@ -888,10 +1040,10 @@ void run_pipelined_rank(const RunContext& rc, ShardPipe& sp, size_t r, double* p
     WriterPool pool(rc.cfg->writer_threads, rc.cfg->writer_threads + 2, std::max<int64_t>(kWriterBufferElems, rc.n_out));
     BinFile files[2];
     for (int kind = 0; kind < 2; ++kind)
-        if (kind == 0 ? rc.want_add : rc.want_dom) files[kind].open(output_base(rc, kind, "") + ".bin", rc.n_out, false, rc.writer);
+        if (kind == 0 ? rc.want_add : rc.want_dom) files[kind].open(output_base(rc, kind, "") + ".bin", rc.n_out, false, rc.writer, rc.prefault);
     int64_t done = 0;
     const auto t_push = Clock::now();
-    push_range(rc, h, sp.snps[r].first, sp.snps[r].second, sp.snps[r].second - sp.snps[r].first, &done);
+    push_range(rc, h, sp.snps[r].first, sp.snps[r].second, rc.m, &done, true, nullptr, &sp.snps_done);
     check(h, ggrm_finish_async(h));
     const auto t0 = Clock::now();
     note_phase(rc, "push", t_push, t0);
@@ -963,7 +1115,7 @@ std::vector<std::pair<int64_t, int64_t>> row_slices(int64_t n, int parts) {
 // (one process owns every GPU, so peers' device pointers are addressable once peer access is on; no NCCL): GPU r sums ITS
 // rows from every peer's accumulator and then writes only those rows, so the read-out uses every GPU's PCIe link and the
 // file is written by several threads at once.
-void reduce_scatter_and_write(const RunContext& rc, const std::vector<ggrm_t*>& handles, const std::vector<int>& devices) {
+void reduce_scatter_and_write(const RunContext& rc, const std::vector<ggrm_t*>& handles, const std::vector<int>& devices, bool precreated) {
     const size_t ng = handles.size();
     for (size_t a = 0; a < ng; ++a)
         for (size_t b = 0; b < ng; ++b)
@@ -980,7 +1132,7 @@ void reduce_scatter_and_write(const RunContext& rc, const std::vector<ggrm_t*>& 
             accum[static_cast<size_t>(kind)][p] = ptr;
         }
     }
-    precreate_outputs(rc, {""});
+    if (!precreated) precreate_outputs(rc, {""});
     const auto slices = row_slices(rc.n_out, static_cast<int>(ng));
     std::vector<std::exception_ptr> errors(ng);
     std::vector<std::thread> threads;
@@ -1034,7 +1186,7 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
     ShardPipe pipe;
     std::unique_ptr<BedRelay> relay;  // function scope: outlives the worker threads
     std::vector<std::unique_ptr<Prefaulter>> prefaulters;  // stopped when this function returns
-    bool pipelined = false;
+    bool pipelined = false, whole_precreated = false;
     if (tile_mode) {
         // 2D output tiles: every GPU streams ALL SNPs, owns disjoint 2048 x 2048 super-tiles of every matrix and writes them
         // straight to their file offsets.  No collective anywhere on the path.
@@ -1072,6 +1224,12 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
             const size_t r = static_cast<size_t>(std::min_element(load.begin(), load.end()) - load.begin());
             mine[r].push_back(static_cast<int>(g));
             load[r] += rc.groups[g].end - rc.groups[g].begin;
+        }
+        if (want_whole && rc.prefault) {
+            // the whole-genome file is written last (reduce-scatter of the per-GPU sums): size it now, populate it during the pass
+            precreate_outputs(rc, {""});
+            prefaulters = start_prefault(rc, true);
+            whole_precreated = true;
         }
         for (size_t r = 0; r < ng; ++r) {
             std::sort(mine[r].begin(), mine[r].end());
@@ -1162,7 +1320,7 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
                 live.push_back(handles[r]);
                 devs.push_back(gpus[r]);
             }
-        if (!live.empty()) reduce_scatter_and_write(rc, live, devs);
+        if (!live.empty()) reduce_scatter_and_write(rc, live, devs, whole_precreated);
     }
 }
 
@@ -1396,8 +1554,10 @@ void GrmEngine::compute(const GrmObserver& observer) {
     {
         const char* e = std::getenv("GELEX_B200_BED_RELAY");
         rc.bed_relay = config_.bed_relay || (e != nullptr && e[0] == '1');
+        // populate output pages ahead of the writers: on by default (measured on the GPU box: C2 read-out + write 1.12 -> 0.42 s,
+        // profiles/r02a_cli_writers.jsonl); GELEX_B200_PREFAULT=0 turns it off
         const char* pf = std::getenv("GELEX_B200_PREFAULT");
-        rc.prefault = config_.prefault || (pf != nullptr && pf[0] == '1');
+        rc.prefault = (pf != nullptr ? pf[0] != '0' : config_.prefault) && rc.writer != WriterMode::Pwrite;  // a forced pwrite stays pwrite
     }
     if (rc.writer != WriterMode::Pwrite) {
         // every .bin of the run: one per work item, plus the whole-genome sums of a LOCO run, or the GCTA pair
@@ -1415,7 +1575,7 @@ void GrmEngine::compute(const GrmObserver& observer) {
         // one GPU writes everything itself, the whole-genome matrix included (non-LOCO: the only output; LOCO: with write_whole)
         WritePart part;
         std::vector<std::unique_ptr<Prefaulter>> prefaulters;
-        if (rc.prefault && !rc.loco && rc.writer != WriterMode::Pwrite) {
+        if (rc.prefault && !rc.loco) {
             precreate_outputs(rc, {""});  // the file exists from the start so that its pages can be populated during the pass
             prefaulters = start_prefault(rc);
             part.create = false;
@@ -1431,7 +1591,7 @@ void GrmEngine::compute(const GrmObserver& observer) {
 
     if (observer) {
         observer(GrmProgressEvent{total_work, total_work, true});
-        observer(GrmFilesWrittenEvent{items.size() * 2, fs::absolute(fs::path(config_.out_prefix)).parent_path().string(),
+        observer(GrmFilesWrittenEvent{config_.gcta ? files.size() : items.size() * 2, fs::absolute(fs::path(config_.out_prefix)).parent_path().string(),
                                       config_.out_prefix + (config_.gcta ? std::string(".grm.{bin|N.bin|id}") : pattern_suffix)});
     }
     summary_.num_samples = order.ids.size();

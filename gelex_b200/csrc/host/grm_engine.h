@@ -80,8 +80,9 @@ class GrmEngine {
         bool bed_relay = false;
         // Non-LOCO runs whose outputs are mapped: create the .bin up front and populate its pages (MADV_POPULATE_WRITE, a few host
         // threads) while the GPUs accumulate, so that the read-out copies into allocated pages (grm_engine.cpp, Prefaulter).
-        // GELEX_B200_PREFAULT=1 turns it on as well.  Off by default until measured through the CLI on the GPU box.
-        bool prefault = false;
+        // LOCO runs prepare the per-chromosome files two ahead of the writer the same way (OutputPreparer).  On by default
+        // (measured on the GPU box, profiles/r02a_cli_writers.jsonl); GELEX_B200_PREFAULT=0/1 overrides.
+        bool prefault = true;
         // GCTA binary format behind a flag (docs/source/data_formats.rst:188-208): instead of <out>.add.{bin,id} write
         // <out>.grm.bin (A_ij = G_ij / N_ij), <out>.grm.N.bin (N_ij = SNPs called in both samples) and <out>.grm.id.  Mode A, no LOCO.
         bool gcta = false;

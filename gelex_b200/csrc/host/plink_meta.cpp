@@ -195,12 +195,17 @@ BedMapping::BedMapping(const fs::path& bed_path, int64_t num_snps, int64_t bytes
         base_ = nullptr;
         throw FileOpenException(bed_path.string() + ": failed to mmap bed file");
     }
+    // a constructor that throws never runs the destructor: release the mapping first
+    auto reject = [this](const std::string& msg) {
+        ::munmap(base_, size_);
+        base_ = nullptr;
+        throw FileFormatException(msg);
+    };
     const auto* b = static_cast<const uint8_t*>(base_);
-    if (!(b[0] == 0x6C && b[1] == 0x1B && b[2] == 0x01)) throw FileFormatException(bed_path.string() + ": invalid BED magic number");
+    if (!(b[0] == 0x6C && b[1] == 0x1B && b[2] == 0x01)) reject(bed_path.string() + ": invalid BED magic number");
     const size_t expected = 3 + static_cast<size_t>(num_snps) * static_cast<size_t>(bpv_);
     if (size_ < expected)
-        throw FileFormatException(bed_path.string() + ": bed file truncated. Expected " + std::to_string(expected) + " bytes, got " +
-                                  std::to_string(size_));
+        reject(bed_path.string() + ": bed file truncated. Expected " + std::to_string(expected) + " bytes, got " + std::to_string(size_));
     payload_snps_ = (size_ - 3) / static_cast<size_t>(bpv_);
     ::madvise(base_, size_, MADV_SEQUENTIAL);
 }
