@@ -507,14 +507,29 @@ def gpu_arm(args):
                 ok = False
         if ok:
             pipe["flags"] = np.ndarray((world, 64), dtype=np.int32, buffer=pipe["shm"].buf)
-            from gelex_b200.sharding import strip_owners
+            from gelex_b200.sharding import piece_owners
 
             bands = acc.band_layout()
-            pipe["mine"] = strip_owners(n, world, bands)[rank]   # 2048-row strips dealt by LPT; each waits for its band's flags
+            # strips cut along their columns into ~64 MB pieces of whole 2048 x 2048 super-tile columns; every band's pieces are dealt
+            # over all ranks, so the last band's reduce + read-out (the exposed tail) is ~70 MB per rank instead of 393 MB on one
+            owners = piece_owners(n, world, bands)
             pipe["n_bands"] = len(bands)
-            elems = sum(g.tri(hi) - g.tri(lo) for _, lo, hi in pipe["mine"])
+
+            def geom(si, c0, c1):
+                row0, col0 = si * 2048, c0 * 2048
+                return row0, min(n, row0 + 2048) - row0, col0, min(n, c1 * 2048) - col0
+
+            pipe["mine"] = [(b, si, c0, c1) + geom(si, c0, c1) for b, si, c0, c1 in owners[rank]]
+            elems = sum(rows * cols for *_, rows, _, cols in pipe["mine"])
             pipe["h_out"] = torch.empty(max(1, elems), dtype=torch.float32, pin_memory=True)
-            pipe["nvlink_bytes"] = int(sum(acc.row_slice(lo, hi)[1] - acc.row_slice(lo, hi)[0] for _, lo, hi in pipe["mine"]) * 4 * (world - 1))
+            pipe["d2h_bytes_all_ranks"] = int(sum(geom(si, c0, c1)[1] * geom(si, c0, c1)[3] for lst in owners for _, si, c0, c1 in lst) * 4)
+            T = (n + 255) // 256
+
+            def stored_elems(si, c0, c1):  # accumulator elements of the piece (whole 256 x 256 tiles)
+                ri = min(T, si * 8 + 8) - si * 8
+                return sum(ri * 8 if c < si else ri * (ri + 1) // 2 for c in range(c0, c1)) * 65536
+
+            pipe["nvlink_bytes"] = int(sum(stored_elems(si, c0, c1) for _, si, c0, c1, *_ in pipe["mine"]) * 4 * (world - 1))
         if not all_ok(ok):
             return False
         pipe["ready"] = True
@@ -528,17 +543,18 @@ def gpu_arm(args):
         push_all(dev)
         acc.finish_async()
         off = 0
-        for b, lo, hi in pipe["mine"]:
+        for b, si, c0, c1, row0, rows, col0, cols in pipe["mine"]:
             t_w = time.time()
             col = pipe["flags"][:, b]
             while not (col == pid).all():
                 if time.time() - t_w > 120:
                     raise SystemExit(f"rank {rank}: band {b} flags {col.tolist()} never reached {pid}")
                 time.sleep(2e-5)
-            acc.reduce_rows_async(g.KIND_ADD, g.GROUP_WHOLE, peers, lo, hi)
-            if fetch:
-                acc.lib.ggrm_fetch(acc.h, g.KIND_ADD, g.GROUP_WHOLE, lo, hi - lo, ctypes.c_void_p(pipe["h_out"].data_ptr() + 4 * off), None)
-                off += g.tri(hi) - g.tri(lo)
+            acc.reduce_block_async(g.KIND_ADD, g.GROUP_WHOLE, peers, si, c0, c1)
+            if fetch:  # the piece as a dense rows x cols block (entries above the diagonal read 0); a writer stores its row segments at their .bin offsets
+                acc._check(acc.lib.ggrm_fetch_block(acc.h, g.KIND_ADD, g.GROUP_WHOLE, row0, rows, col0, cols,
+                                                    ctypes.c_void_p(pipe["h_out"].data_ptr() + 4 * off), cols))
+                off += rows * cols
         acc.finish()      # waits for the accumulation and the read-out stream (the reduces), reports device faults
         dist.barrier()    # peers have finished reading this rank's rows before the next pass overwrites them
 
@@ -658,9 +674,12 @@ def gpu_arm(args):
                 "peer": f"SNP-sharded over {world} GPUs + reduce-scatter of FP32 partial GRMs by 2048-row slices over NVLink peer memory (CUDA IPC, P2P loads) "
                         "after a blocking finish; each rank fetches its own rows",
                 "pipe": f"SNP-sharded over {world} GPUs + reduce-scatter of FP32 partial GRMs over NVLink peer memory (CUDA IPC, P2P loads), pipelined "
-                        f"band by band behind the accumulation: {pipe.get('n_bands')} row bands, 2048-row strips dealt to ranks by LPT on area, per-band completion flags "
-                        "raised by CUDA host callbacks in POSIX shared memory, no collective inside the pass; each rank fetches its own strips"}[args.reduce]
+                        f"band by band behind the accumulation: {pipe.get('n_bands')} row bands, 2048-row strips cut along their columns into ~64 MB pieces (whole super-tile "
+                        "columns), every band's pieces dealt over all ranks, per-band completion flags raised by CUDA host callbacks in POSIX shared memory, no collective "
+                        "inside the pass; each rank fetches its own pieces (ggrm_fetch_block)"}[args.reduce]
         d2h = int(out_elems * 4) * (23 if loco else 1)
+        if use_pipe and pipe.get("ready"):
+            d2h = pipe["d2h_bytes_all_ranks"]  # dense blocks: the diagonal super-tiles carry their zero upper halves too
         line = {
             "metric": cfg["metric"], "value": fl / (dt / args.steps) / 1e12, "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "wall_s_per_grm": dt / args.steps,
@@ -686,7 +705,7 @@ def gpu_arm(args):
                     "path": ("ggrm_reset -> per chromosome: ggrm_push(pinned host BED) then ggrm_fetch of the previous chromosome's partial (float32 lower triangle to "
                              "pinned host memory, overlapping the next chromosome's accumulation) -> ggrm_finish -> [N>1: reduce-scatter of the whole over NVLink] -> "
                              "ggrm_fetch(whole; N>1: each rank its row slice); bytes summed over ranks") if loco else
-                            "ggrm_reset -> ggrm_push(pinned host BED) -> ggrm_finish_async -> [N>1, per owned band: wait for all ranks' band flags -> ggrm_reduce_rows_async] -> ggrm_fetch(float32 lower-triangle rows to pinned host memory; N>1: each rank its own bands, bytes summed over ranks)",
+                            "ggrm_reset -> ggrm_push(pinned host BED) -> ggrm_finish_async -> [N>1, per owned piece: wait for all ranks' band flags -> ggrm_reduce_block_async -> ggrm_fetch_block] / [N=1: ggrm_fetch(float32 lower-triangle rows)] to pinned host memory; bytes summed over ranks",
                     "phases_ms_per_step": {k: tm_e[k] / args.steps for k in ("h2d_ms", "prep_ms", "expand_ms", "syrk_ms", "fetch_ms")}},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": sustained, "unit": "TFLOP/s", "frac": achieved / sustained,
                          "traffic": traffic, "kernel": "syrk_tc_kernel<2> (tcgen05 cta_group::2, UMMA 256x256x16)",

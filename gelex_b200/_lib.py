@@ -70,7 +70,7 @@ EXPORTS = [
     "ggrm_fetch_block", "ggrm_owned_supertiles", "ggrm_host_alloc", "ggrm_host_free", "ggrm_bin_to_dense", "ggrm_assoc_chunk",
     "ggrm_band_layout", "ggrm_set_band_flags", "ggrm_reduce_rows_async", "ggrm_genotype_chunk", "ggrm_fetch_gcta", "ggrm_accum_address",
     "ggrm_stage_create", "ggrm_stage_destroy", "ggrm_stage_upload", "ggrm_stage_slot", "ggrm_wait_copies",
-    "ggrm_warm_device",
+    "ggrm_warm_device", "ggrm_reduce_block_async",
 ]
 
 _lib = None
@@ -132,6 +132,7 @@ def load() -> C.CDLL:
     lib.ggrm_stage_slot.argtypes = [vp, C.c_int, C.POINTER(vp)]
     lib.ggrm_wait_copies.argtypes = [vp]
     lib.ggrm_warm_device.argtypes = [C.c_int]
+    lib.ggrm_reduce_block_async.argtypes = [vp, C.c_int, C.c_int, C.POINTER(vp), C.c_int, i64, i64, i64]
     lib.ggrm_device_count.argtypes = []
     lib.ggrm_version.argtypes = []
     lib.ggrm_version.restype = C.c_char_p
@@ -305,6 +306,10 @@ class Accumulator:
     def reduce_rows_async(self, kind, group, peer_ptrs, row_begin, row_end):
         arr = (C.c_void_p * max(1, len(peer_ptrs)))(*peer_ptrs)
         self._check(self.lib.ggrm_reduce_rows_async(self.h, kind, group, arr, len(peer_ptrs), row_begin, row_end))
+
+    def reduce_block_async(self, kind, group, peer_ptrs, super_row, super_col_begin, super_col_end):
+        arr = (C.c_void_p * max(1, len(peer_ptrs)))(*peer_ptrs)
+        self._check(self.lib.ggrm_reduce_block_async(self.h, kind, group, arr, len(peer_ptrs), super_row, super_col_begin, super_col_end))
 
     def ipc_export(self, kind=KIND_ADD, group=GROUP_WHOLE) -> bytes:
         buf = C.create_string_buffer(64)

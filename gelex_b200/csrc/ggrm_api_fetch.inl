@@ -352,6 +352,44 @@ extern "C" int ggrm_reduce_rows_async(ggrm_t* hh, int kind, int group, const voi
     GGRM_API_END(h)
 }
 
+extern "C" int ggrm_reduce_block_async(ggrm_t* hh, int kind, int group, const void* const* peers, int n_peers, int64_t super_row,
+                                       int64_t super_col_begin, int64_t super_col_end) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    if (n_peers < 0 || n_peers > kMaxPeers) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "n_peers must be 0..7"};
+    if (h->cfg.tile_world != 1) throw CudaError{GGRM_ERR_INVALID_OPERATION, "super-tile ranges are defined for handles that own every tile"};
+    const int64_t T = h->ntiles_side, nsr = (T + 7) / 8;
+    if (super_row < 0 || super_row >= nsr || super_col_begin < 0 || super_col_end < super_col_begin || super_col_end > super_row + 1)
+        throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "super-tile range outside the lower triangle"};
+    // storage slots: super-row by super-row, inside one super-tile by super-tile (build_ownership_and_items); a super-tile left of
+    // the diagonal holds Ri x 8 tiles, the diagonal one Ri (Ri + 1) / 2 (Ri = tile rows of this super-row: 8, or fewer in the last)
+    const int64_t A = super_row * 8, Ri = std::min<int64_t>(T, A + 8) - A;
+    auto slot_at = [&](int64_t sc) { return A * (A + 1) / 2 + (sc <= super_row ? sc * Ri * 8 : super_row * Ri * 8 + Ri * (Ri + 1) / 2); };
+    const int64_t slice_begin = slot_at(super_col_begin) * 65536, slice_end = slot_at(super_col_end) * 65536;
+    cudaEvent_t ev = nullptr;
+    bool banded = false;
+    void* mine = resolve_accum(*h, kind, group, &ev, &banded);
+    if (banded) {
+        const int64_t row_end = std::min<int64_t>(h->n_out, (super_row + 1) * 2048);
+        size_t b = 0;
+        while (h->band_row_end[b] < row_end) ++b;
+        ev = h->band_done[b];
+    }
+    if (ev != nullptr) GGRM_CUDA(cudaStreamWaitEvent(h->s_fetch, ev, 0));
+    PeerPtrs pp{};
+    for (int i = 0; i < n_peers; ++i) pp.p[i] = peers[i];
+    const int64_t len = slice_end - slice_begin;
+    if (len > 0 && n_peers > 0) {
+        const int64_t span = 256 * (16 / h->elem_bytes) * 4;
+        const int blocks = static_cast<int>(std::min<int64_t>((len + span - 1) / span, h->sm_count * 8));
+        if (h->fp64) reduce_peers_kernel<double><<<blocks, 256, 0, h->s_fetch>>>(static_cast<double*>(mine), pp, n_peers, slice_begin, slice_end);
+        else reduce_peers_kernel<float><<<blocks, 256, 0, h->s_fetch>>>(static_cast<float*>(mine), pp, n_peers, slice_begin, slice_end);
+        GGRM_CUDA(cudaGetLastError());
+        ++h->kernel_launches;
+    }
+    GGRM_API_END(h)
+}
+
 extern "C" int ggrm_ipc_export(ggrm_t* hh, int kind, int group, void* handle64) {
     Handle* h = reinterpret_cast<Handle*>(hh);
     GGRM_API_BEGIN(h)

@@ -275,6 +275,19 @@ extern "C" int gelex_b200_strip_owners(int64_t n, int world, const int64_t* band
     return static_cast<int>(strips.size());
 }
 
+extern "C" int gelex_b200_piece_owners(int64_t n, int world, const int64_t* band_row_end, int n_bands, int64_t* out5, int cap) {
+    if (n <= 0 || world <= 0 || band_row_end == nullptr || n_bands <= 0 || out5 == nullptr) return -1;
+    const auto pieces = GrmEngine::piece_owners_for(n, world, std::vector<int64_t>(band_row_end, band_row_end + n_bands));
+    for (size_t i = 0; i < pieces.size() && static_cast<int>(i) < cap; ++i) {
+        out5[5 * i] = pieces[i].rank;
+        out5[5 * i + 1] = pieces[i].band;
+        out5[5 * i + 2] = pieces[i].super_row;
+        out5[5 * i + 3] = pieces[i].super_col_begin;
+        out5[5 * i + 4] = pieces[i].super_col_end;
+    }
+    return static_cast<int>(pieces.size());
+}
+
 // GrmEngine::writer_selftest through C (CPU tests, no GPU): writer 0 = auto, 1 = pwrite, 2 = mmap; seconds_out / mapped_out optional.
 extern "C" int gelex_b200_writer_selftest(const char* bin_path, int64_t n, int tiles, int parts, int writer_threads, int writer,
                                           int prefault_threads, double* seconds_out, double* prefault_seconds_out, int* mapped_out, char* err,

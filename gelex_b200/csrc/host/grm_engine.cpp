@@ -12,6 +12,7 @@
 #include <mutex>
 #include <numeric>
 #include <thread>
+#include <tuple>
 #include <unordered_map>
 #include <condition_variable>
 #include <deque>
@@ -1020,11 +1021,60 @@ std::vector<std::vector<Strip>> strip_owners(int64_t n, int world, const std::ve
     return out;
 }
 
+// The same reduce-scatter at the grain that keeps every band's tail short (same rule as gelex_b200/sharding.py::piece_owners,
+// compared in tests/test_sharding.py): every 2 048-row strip is cut along its columns into pieces of whole super-tile columns,
+// about 64 MB of FP32 each, and the pieces of every band are dealt over ALL ranks - largest first, to the rank with the least
+// work in this band, ties to the least loaded overall, then the lower rank.
+struct Piece { int band; int64_t si, c0, c1; };
+
+std::vector<std::vector<Piece>> piece_owners(int64_t n, int world, const std::vector<int64_t>& band_row_end, int64_t target_elems = int64_t{16} << 20) {
+    struct P { Piece p; int64_t area; };
+    std::vector<P> pieces;
+    int64_t si = 0;
+    for (int64_t lo = 0; lo < n; lo += kSuperRows, ++si) {
+        const int64_t hi = std::min(n, lo + kSuperRows), rows = hi - lo;
+        int b = 0;
+        while (static_cast<size_t>(b) + 1 < band_row_end.size() && band_row_end[static_cast<size_t>(b)] < hi) ++b;
+        const int64_t ncol = si + 1;
+        const int64_t diag_area = hi * (hi + 1) / 2 - lo * (lo + 1) / 2 - rows * lo;
+        const int64_t w = std::max<int64_t>(1, target_elems / (rows * kSuperRows));
+        for (int64_t c0 = 0; c0 < ncol; c0 += w) {
+            const int64_t c1 = std::min(ncol, c0 + w);
+            int64_t area = 0;
+            for (int64_t c = c0; c < c1; ++c) area += c < si ? rows * kSuperRows : diag_area;
+            pieces.push_back({{b, si, c0, c1}, area});
+        }
+    }
+    std::vector<int64_t> total(static_cast<size_t>(world), 0);
+    std::vector<std::vector<Piece>> out(static_cast<size_t>(world));
+    for (size_t b = 0; b < band_row_end.size(); ++b) {
+        std::vector<size_t> idx;
+        for (size_t i = 0; i < pieces.size(); ++i)
+            if (pieces[i].p.band == static_cast<int>(b)) idx.push_back(i);
+        std::stable_sort(idx.begin(), idx.end(), [&](size_t x, size_t y) { return pieces[x].area > pieces[y].area; });
+        std::vector<int64_t> band(static_cast<size_t>(world), 0);
+        for (size_t i : idx) {
+            size_t best = 0;
+            for (size_t q = 1; q < static_cast<size_t>(world); ++q)
+                if (band[q] < band[best] || (band[q] == band[best] && total[q] < total[best])) best = q;
+            band[best] += pieces[i].area;
+            total[best] += pieces[i].area;
+            out[best].push_back(pieces[i].p);
+        }
+    }
+    for (auto& v : out)
+        std::sort(v.begin(), v.end(), [](const Piece& a, const Piece& b) {
+            return std::tie(a.band, a.si, a.c0) < std::tie(b.band, b.si, b.c0);
+        });
+    return out;
+}
+
 struct ShardPipe {
     std::vector<ggrm_t*> handles;                 // one per rank, created up front
     std::vector<std::pair<int64_t, int64_t>> snps;  // SNP range of each rank
     std::vector<std::vector<const void*>> accum;  // [kind][rank] device address of the accumulator
-    std::vector<std::vector<Strip>> mine;         // strips each rank reduces + writes
+    std::vector<std::vector<Strip>> mine;         // strips each rank reduces + writes (GCTA runs: the ratio is read out by rows)
+    std::vector<std::vector<Piece>> pieces;       // column pieces of strips each rank reduces + writes (every other run)
     std::vector<int32_t> flags;                   // [rank][band], written by CUDA host callbacks
     int n_bands = 1;
     std::atomic<bool> failed{false};
@@ -1047,18 +1097,53 @@ void run_pipelined_rank(const RunContext& rc, ShardPipe& sp, size_t r, double* p
     check(h, ggrm_finish_async(h));
     const auto t0 = Clock::now();
     note_phase(rc, "push", t_push, t0);
+    auto wait_band = [&](int band) {  // every rank's rows of this band are final
+        const auto t_wait = Clock::now();
+        for (;;) {
+            bool ready = true;
+            for (size_t p = 0; p < ng && ready; ++p)
+                ready = __atomic_load_n(&sp.flags[p * nb + static_cast<size_t>(band)], __ATOMIC_ACQUIRE) == 1;
+            if (ready) return;
+            if (sp.failed.load()) throw GelexException("multi-GPU run aborted: another GPU failed");
+            if (since(t_wait) > 3600.0) throw GelexException("multi-GPU run: timed out waiting for a peer's row band");
+            std::this_thread::sleep_for(std::chrono::microseconds(20));
+        }
+    };
+    auto peers_of = [&](int kind) {
+        std::vector<const void*> peers;
+        for (size_t p = 0; p < ng; ++p)
+            if (p != r) peers.push_back(sp.accum[static_cast<size_t>(kind)][p]);
+        return peers;
+    };
     try {
-        for (const Strip& st : sp.mine[r]) {
-            const auto t_wait = Clock::now();
-            for (;;) {  // every rank's rows of this band are final
-                bool ready = true;
-                for (size_t p = 0; p < ng && ready; ++p)
-                    ready = __atomic_load_n(&sp.flags[p * nb + static_cast<size_t>(st.band)], __ATOMIC_ACQUIRE) == 1;
-                if (ready) break;
-                if (sp.failed.load()) throw GelexException("multi-GPU run aborted: another GPU failed");
-                if (since(t_wait) > 3600.0) throw GelexException("multi-GPU run: timed out waiting for a peer's row band");
-                std::this_thread::sleep_for(std::chrono::microseconds(20));
+        // column pieces: reduce the piece's super-tiles over NVLink, then read them out one 2 048 x 2 048 super-tile at a time and
+        // write their row segments at their own file offsets (as the 2D-tile writer does)
+        for (const Piece& pc : rc.gcta ? std::vector<Piece>{} : sp.pieces[r]) {
+            wait_band(pc.band);
+            for (int kind = 0; kind < 2; ++kind) {
+                if (!(kind == 0 ? rc.want_add : rc.want_dom)) continue;
+                const auto peers = peers_of(kind);
+                for (size_t off = 0; off < peers.size(); off += 7)
+                    check(h, ggrm_reduce_block_async(h, kind, GGRM_GROUP_WHOLE, peers.data() + off, static_cast<int>(std::min<size_t>(7, peers.size() - off)),
+                                                     pc.si, pc.c0, pc.c1));
             }
+            const int64_t row0 = pc.si * kSuperRows, rows = std::min(kSuperRows, rc.n_out - row0);
+            for (int kind = 0; kind < 2; ++kind) {
+                if (!(kind == 0 ? rc.want_add : rc.want_dom)) continue;
+                for (int64_t sc = pc.c0; sc < pc.c1; ++sc) {
+                    const int64_t col0 = sc * kSuperRows, cols = std::min(kSuperRows, rc.n_out - col0);
+                    float* buf = pool.acquire();
+                    const int st = ggrm_fetch_block(h, kind, GGRM_GROUP_WHOLE, row0, rows, col0, cols, buf, cols);
+                    if (st != GGRM_OK) {
+                        pool.submit(files[kind], buf, {});
+                        throw_status(st, ggrm_last_error(h));
+                    }
+                    pool.submit(files[kind], buf, supertile_segments(row0, col0, rows, cols));
+                }
+            }
+        }
+        for (const Strip& st : rc.gcta ? sp.mine[r] : std::vector<Strip>{}) {
+            wait_band(st.band);
             for (int kind = 0; kind < 2; ++kind) {
                 if (!(kind == 0 ? rc.want_add : rc.want_dom)) continue;
                 std::vector<const void*> peers;
@@ -1284,6 +1369,7 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
         check(pipe.handles[0], ggrm_band_layout(pipe.handles[0], band_end.data(), 64, &pipe.n_bands));
         band_end.resize(static_cast<size_t>(pipe.n_bands));
         pipe.mine = strip_owners(rc.n_out, static_cast<int>(world), band_end);
+        pipe.pieces = piece_owners(rc.n_out, static_cast<int>(world), band_end);
         pipe.flags.assign(world * static_cast<size_t>(pipe.n_bands), 0);
         precreate_outputs(rc, {""});
         prefaulters = start_prefault(rc);
@@ -1327,6 +1413,14 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
 }  // namespace
 
 std::vector<std::pair<int64_t, int64_t>> GrmEngine::row_slices_for(int64_t n, int parts) { return row_slices(n, parts); }
+
+std::vector<GrmEngine::OwnedPiece> GrmEngine::piece_owners_for(int64_t n, int world, const std::vector<int64_t>& band_row_end) {
+    std::vector<OwnedPiece> out;
+    const auto per_rank = piece_owners(n, world, band_row_end);
+    for (size_t r = 0; r < per_rank.size(); ++r)
+        for (const Piece& pc : per_rank[r]) out.push_back({static_cast<int>(r), pc.band, pc.si, pc.c0, pc.c1});
+    return out;
+}
 
 std::vector<GrmEngine::OwnedStrip> GrmEngine::strip_owners_for(int64_t n, int world, const std::vector<int64_t>& band_row_end) {
     std::vector<OwnedStrip> out;

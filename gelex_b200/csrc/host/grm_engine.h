@@ -114,6 +114,10 @@ class GrmEngine {
     // 2 048-row strips of the band-pipelined SNP-shard run, dealt by LPT: (rank, band, row range), rank-major, rows ascending.
     struct OwnedStrip { int rank, band; int64_t row_begin, row_end; };
     static std::vector<OwnedStrip> strip_owners_for(int64_t n, int world, const std::vector<int64_t>& band_row_end);
+    // ... and the finer dealing the run actually uses: column pieces of the strips (whole 2 048 x 2 048 super-tile columns, ~64 MB
+    // each), every band spread over all ranks: (rank, band, super-row, super-column range), rank-major, (band, super-row, column) order.
+    struct OwnedPiece { int rank, band; int64_t super_row, super_col_begin, super_col_end; };
+    static std::vector<OwnedPiece> piece_owners_for(int64_t n, int world, const std::vector<int64_t>& band_row_end);
 
     // CPU-only check of the writer pool (no GPU involved): writes the packed lower triangle of an n x n matrix with entry
     // (i, j) = float((31 i + j) mod 65521) + 0.5 through the same jobs the engine submits - whole-row blocks of `parts` row
@@ -152,6 +156,8 @@ extern "C" int gelex_b200_grm_run_gcta(const char* bfile, const char* out_prefix
                                        int writer_threads, char* err, int err_len);
 // strip_owners_for through C (CPU tests): out4 receives (rank, band, row_begin, row_end) per strip, up to cap strips; returns the strip count.
 extern "C" int gelex_b200_strip_owners(int64_t n, int world, const int64_t* band_row_end, int n_bands, int64_t* out4, int cap);
+// piece_owners_for through C: out5 receives (rank, band, super_row, super_col_begin, super_col_end) per piece; returns the piece count.
+extern "C" int gelex_b200_piece_owners(int64_t n, int world, const int64_t* band_row_end, int n_bands, int64_t* out5, int cap);
 // GrmEngine::writer_selftest through C (CPU tests): writer 0 = auto, 1 = pwrite, 2 = mmap.
 extern "C" int gelex_b200_writer_selftest(const char* bin_path, int64_t n, int tiles, int parts, int writer_threads, int writer,
                                           int prefault_threads, double* seconds_out, double* prefault_seconds_out, int* mapped_out, char* err,

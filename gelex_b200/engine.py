@@ -39,6 +39,7 @@ def load_host():
         h.gelex_b200_grm_load.restype = C.c_int64
         h.gelex_b200_row_slices.argtypes = [C.c_int64, C.c_int, C.c_void_p]
         h.gelex_b200_strip_owners.argtypes = [C.c_int64, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        h.gelex_b200_piece_owners.argtypes = [C.c_int64, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
         h.gelex_b200_grm_run_gcta.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]
         vp = C.c_void_p
         h.gelex_b200_genotype_export.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, C.c_int64,
@@ -244,6 +245,24 @@ def strip_owners(n, world, bands):
     for i in range(cnt):
         r, b, lo, hi = (int(v) for v in out[4 * i:4 * i + 4])
         per[r].append((b, lo, hi))
+    return per
+
+
+def piece_owners(n, world, bands):
+    """The C++ engine's dealing of strip column pieces (same contract as sharding.piece_owners: per rank a list of
+    (band, super_row, super_col_begin, super_col_end))."""
+    h = load_host()
+    ends = np.array([e for _, e in bands], dtype=np.int64)
+    ns = (int(n) + 2047) // 2048
+    cap = ns * (ns + 1) // 2 + 1
+    out = np.zeros(5 * cap, dtype=np.int64)
+    cnt = h.gelex_b200_piece_owners(int(n), int(world), ends.ctypes.data_as(C.c_void_p), len(ends), out.ctypes.data_as(C.c_void_p), cap)
+    if cnt < 0 or cnt > cap:
+        raise EngineError(cnt, "piece_owners failed")
+    per = [[] for _ in range(world)]
+    for i in range(cnt):
+        r, b, si, c0, c1 = (int(v) for v in out[5 * i:5 * i + 5])
+        per[r].append((b, si, c0, c1))
     return per
 
 

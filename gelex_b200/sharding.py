@@ -86,3 +86,43 @@ def strip_owners(n: int, world: int, bands, rows_per_strip: int = 2048):
         b = next(i for i, (_, be) in enumerate(bands) if hi <= be)
         out[r].append((b, lo, hi))
     return out
+
+
+def piece_owners(n: int, world: int, bands, rows_per_strip: int = 2048, target_elems: int = 16 << 20):
+    """Band-pipelined reduce-scatter at the grain that keeps every band's tail short: each 2048-row strip (one super-row of
+    2048 x 2048 super-tiles) is cut along its COLUMNS into pieces of `target_elems // (rows * 2048)` whole super-tile columns
+    (about `target_elems` entries = 64 MB of FP32 each), and the pieces of every band are dealt over ALL ranks (largest first, to the rank with the least
+    work in this band, ties to the least loaded overall).  With whole strips (strip_owners) the last band of a 50 000-sample
+    matrix is two strips - 393 MB and 168 MB on two ranks - and their reduce + read-out is the exposed tail of the pass;
+    with pieces it is ~70 MB on each of eight ranks.
+    `bands` = [(row_begin, row_end)] in completion order (ggrm_band_layout).
+    Returns per rank a list of (band, super_row, super_col_begin, super_col_end) in (band, super_row, column) order; the
+    piece covers rows [super_row * 2048, min(n, (super_row + 1) * 2048)) x columns [super_col_begin * 2048, min(n, super_col_end * 2048)),
+    lower triangle only."""
+    def tri(x):
+        return x * (x + 1) // 2
+
+    pieces = []  # (band, si, c0, c1, area)
+    for si, lo in enumerate(range(0, n, rows_per_strip)):
+        hi = min(n, lo + rows_per_strip)
+        b = next(i for i, (_, be) in enumerate(bands) if hi <= be)
+        rows = hi - lo
+        ncol = si + 1                                         # super-tile columns of this super-row
+        col_area = [rows * rows_per_strip] * si + [tri(hi) - tri(lo) - rows * lo]  # left of the diagonal: full blocks; diagonal block: its triangle part
+        w = max(1, target_elems // (rows * rows_per_strip))   # whole super-tile columns per piece (4 at 2048 rows and 64 MB)
+        for c0 in range(0, ncol, w):
+            c1 = min(ncol, c0 + w)
+            pieces.append((b, si, c0, c1, sum(col_area[c0:c1])))
+    total_load = [0] * world
+    out = [[] for _ in range(world)]
+    for b in range(len(bands)):
+        band_load = [0] * world
+        mine = sorted((p for p in pieces if p[0] == b), key=lambda p: -p[4])  # stable: equal areas keep (si, c0) order
+        for p in mine:
+            r = min(range(world), key=lambda q: (band_load[q], total_load[q], q))
+            band_load[r] += p[4]
+            total_load[r] += p[4]
+            out[r].append(p[:4])
+    for r in range(world):
+        out[r].sort()
+    return out

@@ -189,6 +189,15 @@ int ggrm_set_band_flags(ggrm_t* h, int32_t* flags, int32_t value);
 int ggrm_reduce_rows_async(ggrm_t* h, int kind, int group, const void* const* peers, int n_peers, int64_t row_begin,
                            int64_t row_end);
 
+/* The same at a finer grain, for the bands that finish last: sums the peers' 2 048 x 2 048 super-tiles
+ * [super_col_begin, super_col_end) of super-row `super_row` (rows super_row * 2048 ..; super_col <= super_row; the super-tiles of
+ * a super-row are contiguous in the accumulator) into this handle's, on the read-out stream, behind the band event of those rows.
+ * A strip of the LAST band is hundreds of MB at n = 50 000; cut along its columns and dealt to all ranks, its reduce + read-out
+ * (ggrm_fetch_block of the same rows x columns) is spread over every GPU's NVLink and PCIe link instead of one.  Needs
+ * tile_world == 1. */
+int ggrm_reduce_block_async(ggrm_t* h, int kind, int group, const void* const* peers, int n_peers, int64_t super_row,
+                            int64_t super_col_begin, int64_t super_col_end);
+
 /* Multi-PROCESS form of the same (one process per GPU, torch.distributed-style launch): export the accumulator of
  * (kind, group) as a CUDA IPC handle (64 bytes, cudaIpcMemHandle_t), ship it to the other ranks over any host channel,
  * open it there (maps the peer's memory over NVLink, enabling peer access lazily) and pass the mapped pointers to

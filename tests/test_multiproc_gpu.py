@@ -117,20 +117,32 @@ def _pipelined_worker(rank, world, port, tmpdir):
             peers = [g.ipc_open(handles[r], device=dev) for r in range(world) if r != rank]
         bands = acc.band_layout()
         assert len(bands) == 3 and bands[-1][1] == N
-        got = {}
-        for b, r0, r1 in sharding.strip_owners(N, world, bands)[rank]:
-            t0 = time.time()
-            while not np.all(flags[:, b] == pass_id):
-                assert time.time() - t0 < 60, "peer band flag never arrived"
-                time.sleep(0.0002)
-            acc.reduce_rows_async(g.KIND_ADD, g.GROUP_WHOLE, peers, r0, r1)
-            rows, tr = acc.fetch(g.KIND_ADD, g.GROUP_WHOLE, r0, r1 - r0, dtype=np.float64)
-            got[r0 // 2048] = (rows, tr)
+        got, blocks = {}, {}
+        if pass_id == 1:  # whole strips, read out as packed rows
+            for b, r0, r1 in sharding.strip_owners(N, world, bands)[rank]:
+                t0 = time.time()
+                while not np.all(flags[:, b] == pass_id):
+                    assert time.time() - t0 < 60, "peer band flag never arrived"
+                    time.sleep(0.0002)
+                acc.reduce_rows_async(g.KIND_ADD, g.GROUP_WHOLE, peers, r0, r1)
+                rows, tr = acc.fetch(g.KIND_ADD, g.GROUP_WHOLE, r0, r1 - r0, dtype=np.float64)
+                got[r0 // 2048] = (rows, tr)
+        else:  # column pieces of the strips (what bench.py and the C++ engine run), read out as dense blocks; tiny target -> one super-tile each
+            for b, si, c0, c1 in sharding.piece_owners(N, world, bands, target_elems=1 << 20)[rank]:
+                t0 = time.time()
+                while not np.all(flags[:, b] == pass_id):
+                    assert time.time() - t0 < 60, "peer band flag never arrived"
+                    time.sleep(0.0002)
+                acc.reduce_block_async(g.KIND_ADD, g.GROUP_WHOLE, peers, si, c0, c1)
+                row0, col0 = si * 2048, c0 * 2048
+                blocks[(si, c0, c1)] = acc.fetch_block(g.KIND_ADD, g.GROUP_WHOLE, row0, min(N, row0 + 2048) - row0, col0, min(N, c1 * 2048) - col0)
         acc.finish()
         dist.barrier()  # nobody re-arms (first slab stores) while a peer may still read its rows
         for b, (rows, tr) in got.items():
             np.save(os.path.join(tmpdir, f"p{pass_id}_band{b}.npy"), rows)
             np.save(os.path.join(tmpdir, f"p{pass_id}_band{b}_tr.npy"), np.array([tr]))
+        for (si, c0, c1), blk in blocks.items():
+            np.save(os.path.join(tmpdir, f"p{pass_id}_piece_{si}_{c0}_{c1}.npy"), blk)
     for p in peers:
         g.ipc_close(p, device=dev)
     acc.close()
@@ -153,9 +165,20 @@ def test_band_pipelined_reduce_scatter(tmp_path, world):
         acc.finish()
         ref, tr_ref = acc.fetch(g.KIND_ADD, g.GROUP_WHOLE, dtype=np.float64)
     scale = float(np.max(np.abs(ref)))
-    for pass_id in (1, 2):
-        got = np.concatenate([np.load(tmp_path / f"p{pass_id}_band{b}.npy") for b in range(3)])
-        tr = sum(float(np.load(tmp_path / f"p{pass_id}_band{b}_tr.npy")[0]) for b in range(3))
-        assert got.shape == ref.shape
-        assert np.max(np.abs(got - ref)) <= 1e-4 * scale, (pass_id, float(np.max(np.abs(got - ref))), scale)
-        assert abs(tr - tr_ref) <= 3e-4 * abs(tr_ref)
+    got = np.concatenate([np.load(tmp_path / f"p1_band{b}.npy") for b in range(3)])
+    tr = sum(float(np.load(tmp_path / f"p1_band{b}_tr.npy")[0]) for b in range(3))
+    assert got.shape == ref.shape
+    assert np.max(np.abs(got - ref)) <= 1e-4 * scale, (float(np.max(np.abs(got - ref))), scale)
+    assert abs(tr - tr_ref) <= 3e-4 * abs(tr_ref)
+    # second pass (re-armed handle): the pieces tile the lower triangle exactly once and hold the same values
+    full = np.zeros((N, N))
+    full[np.tril_indices(N)] = ref
+    count = np.zeros((3, 3), dtype=int)
+    for f in sorted(tmp_path.glob("p2_piece_*.npy")):
+        si, c0, c1 = (int(x) for x in f.stem.split("_")[2:])
+        count[si, c0:c1] += 1
+        blk = np.load(f)
+        row0, col0 = si * 2048, c0 * 2048
+        want = full[row0:row0 + blk.shape[0], col0:col0 + blk.shape[1]]
+        assert np.max(np.abs(blk - want)) <= 1e-4 * scale, f.name
+    assert count.tolist() == [[1, 0, 0], [1, 1, 0], [1, 1, 1]]

@@ -131,3 +131,53 @@ def test_strip_owners_cover_balance_and_spread_the_last_band():
             assert max(last.count(r_i) for r_i in set(last)) <= -(-len(last) // w) + 1, (n, w, last)
             if w > 1 and len(last) > 1:
                 assert len(set(last)) >= min(len(last) - 1, w), (n, w, last)
+
+
+def _bands_for(n, nb):
+    strips_total = (n + 2047) // 2048
+    area = [min(n, (s + 1) * 2048) * (min(n, (s + 1) * 2048) + 1) // 2 - (s * 2048) * (s * 2048 + 1) // 2 for s in range(strips_total)]
+    tot, acc, ends = sum(area), 0, []
+    for s_, a in enumerate(area):
+        acc += a
+        if len(ends) + 1 < nb and acc >= (len(ends) + 1) * tot / nb or s_ + 1 == strips_total:
+            ends.append(min(n, (s_ + 1) * 2048))
+    return [(0 if i == 0 else ends[i - 1], e) for i, e in enumerate(ends)]
+
+
+def test_piece_owners_cover_every_supertile_once_and_spread_every_band():
+    # the finer dealing of the band-pipelined reduce-scatter: column pieces of strips, every band over all ranks
+    for n, nb in ((4500, 3), (50000, 8), (200000, 8), (2049, 1)):
+        ns = (n + 2047) // 2048
+        bands = _bands_for(n, nb)
+        for w in (1, 2, 3, 4, 8):
+            own = sharding.piece_owners(n, w, bands)
+            seen = {}
+            for r, lst in enumerate(own):
+                assert lst == sorted(lst)
+                for b, si, c0, c1 in lst:
+                    assert 0 <= c0 < c1 <= si + 1 and bands[b][0] <= si * 2048 and min(n, (si + 1) * 2048) <= bands[b][1]
+                    for c in range(c0, c1):
+                        assert (si, c) not in seen
+                        seen[(si, c)] = r
+            assert len(seen) == ns * (ns + 1) // 2
+            if n == 50000 and w == 8:
+                # the exposed tail: bytes of the LAST band per rank (strip_owners put 393 MB on one rank)
+                def area(si, c):
+                    lo, hi = si * 2048, min(n, (si + 1) * 2048)
+                    return (hi - lo) * 2048 if c < si else hi * (hi + 1) // 2 - lo * (lo + 1) // 2 - (hi - lo) * lo
+                last = [0] * w
+                for r, lst in enumerate(own):
+                    for b, si, c0, c1 in lst:
+                        if b == len(bands) - 1:
+                            last[r] += sum(area(si, c) for c in range(c0, c1)) * 4
+                assert max(last) < 120e6 and min(last) > 40e6, last
+
+
+def test_cpp_engine_deals_pieces_like_the_python_rule():
+    from gelex_b200 import engine
+
+    for n in (1, 2048, 2049, 4500, 50000, 123457):
+        for nb in (1, 3, 8):
+            bands = _bands_for(n, nb)
+            for w in (1, 2, 3, 8):
+                assert engine.piece_owners(n, w, bands) == sharding.piece_owners(n, w, bands), (n, nb, w)
