@@ -788,9 +788,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default=os.environ.get("GGRM_BENCH_CONFIG", "c2"), choices=sorted(CONFIGS),
                     help="c2 = configs[1] (the headline shape), c4 = configs[3] (22 LOCO partials + whole)")
-    ap.add_argument("--precision", default=os.environ.get("GGRM_BENCH_PRECISION", "bf16"), choices=["fp16", "bf16", "fp64"],
-                    help="operand type of the tcgen05 path; bf16 meets the 1e-4 bound at these workloads' 500-600k SNPs "
-                         "(tests/test_named_configs_gpu.py), fp16 is the engine default")
+    ap.add_argument("--precision", default=os.environ.get("GGRM_BENCH_PRECISION"), choices=["fp16", "bf16", "fp64"],
+                    help="operand type of the tcgen05 path (same pipe and throughput for both 16-bit types).  Default: bf16 for c2 - inside the "
+                         "1e-4 bound at 500k SNPs; fp16 (the engine default) for c4, whose chromosome partials are 9.8k-52k SNPs each: plain bf16 "
+                         "misses the bound on those and the library would split its operands (3x the tensor time).  tests/test_named_configs_gpu.py")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg (N = 1)")
     ap.add_argument("--no-wall", action="store_true", help="skip the CLI wall-clock leg")
     ap.add_argument("--wall", action="store_true", help="c4: run the CLI wall-clock leg too (writes 23 x 5 GB)")
@@ -798,6 +799,8 @@ def main():
                     help="c2, N>1: partial-GRM reduction (pipe = own P2P kernel pipelined band by band behind the accumulation, "
                          "peer = the same kernel after a blocking finish, nccl = dist.reduce to rank 0)")
     args = ap.parse_args()
+    if args.precision is None:
+        args.precision = "fp16" if args.config == "c4" else "bf16"
     if args.impl == "reference":
         reference_arm(args)
     else:

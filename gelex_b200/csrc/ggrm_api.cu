@@ -2,6 +2,7 @@
 // Host-side orchestration only; all arithmetic happens in the kernels of prep_kernels.cuh, syrk_tc.cuh,
 // syrk_f64.cuh and pack_kernels.cuh.  There is deliberately no CPU fallback anywhere in this file.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -315,10 +316,16 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
         throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "non-missing pair counts are exact in FP32 only below 2^24 SNPs: use the FP64 precision"};
 
     h->cfg = *cfg;
+    const bool dbg_time = std::getenv("GGRM_DEBUG_TIMING") != nullptr;
+    const auto t_create0 = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (dbg_time) std::fprintf(stderr, "[ggrm] create: %-28s at %.3f s\n", what, std::chrono::duration<double>(std::chrono::steady_clock::now() - t_create0).count());
+    };
     if (const char* e = std::getenv("GGRM_GUARD")) h->guard = std::atoi(e) != 0;
     h->cfg.raw_to_out = nullptr;
     h->cfg.group_begin = h->cfg.group_end = nullptr;
     check_device(cfg->device, &h->sm_count);
+    lap("device checked");
     h->n_raw = cfg->n_raw;
     h->n_out = cfg->n_out;
     h->n_pad = round_up(cfg->n_out, kTile);
@@ -376,23 +383,40 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
         GGRM_CUDA(cudaEventCreateWithFlags(&h->z_free[i], cudaEventDisableTiming));
     }
 
-    // BF16 operands carry 8 mantissa bits: the rounding error of G/(trace/n) shrinks as 1/sqrt(m) and measures ~0.018/sqrt(m)
-    // (4.0e-4 at m = 2 048, ~8e-5 at the 50 000 SNPs of config C1, ~2.5e-5 at C2's 500 000).  Below 2^18 SNPs - where a
-    // plain BF16 product would not keep 1e-4 with a 2x margin - the operands are split into hi + lo (3 MMAs per K block, error
-    // of an ~16-bit mantissa), so GGRM_PREC_BF16 meets the bound at every size.  GGRM_BF16_SPLIT=0/1 forces it off/on.
-    h->bf16_split = cfg->precision == GGRM_PREC_BF16 && cfg->m_total < (int64_t{1} << 18);
-    if (const char* e = std::getenv("GGRM_BF16_SPLIT")) h->bf16_split = cfg->precision == GGRM_PREC_BF16 && std::atoi(e) != 0;
+    // 16-bit operands and the 1e-4 bound on G/(trace/n).  The rounding error of an output matrix accumulated over m SNPs measures
+    // c / sqrt(m) (independent per-SNP rounding of the four table values): c ~ 0.018 for BF16 (8 mantissa bits; 4.0e-4 at
+    // m = 2 048, 2.3e-5 at C2's 500 000) and ~ 0.0023 for FP16 (11 bits; 1.1e-5 at C1's 50 000).  The scaled orthogonal dominance
+    // codes (OrthStandardizeHWE / OrthStandardize: homozygote = -q/p, heavy-tailed) measure 3.5x that (FP16: 1.0e-4 at m = 6 000).
+    // Below the SNP count where a plain 16-bit product keeps the bound with a ~3x margin, operands are split into hi + lo (3 MMAs
+    // per K block, ~2^-17 relative error per product), so both 16-bit precisions meet 1e-4 at every size.  What counts is the
+    // SHORTEST group: each chromosome partial of a LOCO run is an output matrix of its own (C4's smallest has 9 800 SNPs - the
+    // reason the engine's default is FP16, whose threshold those partials clear).  GGRM_OPERAND_SPLIT=0/1 forces it off / on.
+    {
+        int64_t m_short = cfg->m_total;
+        for (const auto& gr : h->groups)
+            if (gr.end > gr.begin) m_short = std::min(m_short, gr.end - gr.begin);
+        const bool heavy = cfg->want_dom && cfg->second_matrix == GGRM_SECOND_DOMINANCE &&
+                           (cfg->method == GGRM_ORTH_STANDARDIZE_HWE || cfg->method == GGRM_ORTH_STANDARDIZE);
+        int64_t below = 0;
+        if (cfg->precision == GGRM_PREC_BF16) below = heavy ? (int64_t{1} << 22) : (int64_t{1} << 18);
+        if (cfg->precision == GGRM_PREC_FP16) below = heavy ? (int64_t{1} << 16) : (int64_t{1} << 13);
+        h->op_split = m_short < below;
+        const char* e = std::getenv("GGRM_OPERAND_SPLIT");
+        if (e == nullptr) e = std::getenv("GGRM_BF16_SPLIT");
+        if (e != nullptr) h->op_split = cfg->precision != GGRM_PREC_FP64 && std::atoi(e) != 0;
+    }
 
     build_ownership_and_items(*h);
 
     // ---- memory plan -------------------------------------------------------------------------------------------
+    lap("streams + work lists");
     size_t free_b = 0, total_b = 0;
     GGRM_CUDA(cudaMemGetInfo(&free_b, &total_b));
     const int kinds = (cfg->want_add ? 1 : 0) + (cfg->want_dom ? 1 : 0);
     const int64_t accum_bytes = std::max<int64_t>(h->accum_elems, 4) * h->elem_bytes;
     const bool want_whole = cfg->n_groups > 1 && cfg->keep_whole;
-    const int64_t z_elem = h->fp64 ? 8 : (h->bf16_split ? 4 : 2);  // bytes per sample per SNP of one operand slab (hi + lo when split)
-    const int64_t z_cols_per_k = h->bf16_split ? 2 : 1;
+    const int64_t z_elem = h->fp64 ? 8 : (h->op_split ? 4 : 2);  // bytes per sample per SNP of one operand slab (hi + lo when split)
+    const int64_t z_cols_per_k = h->op_split ? 2 : 1;
     const int64_t per_snp = 2 * h->n_pad * z_elem * kinds + 2 * h->bpv_raw + h->bpv_pad + 128;
     int64_t avail = static_cast<int64_t>(free_b) - (int64_t{1} << 30) - (want_whole ? accum_bytes * kinds : 0);
     const int64_t min_chunk = std::min<int64_t>(round_up(cfg->m_total, 64), 4096) * per_snp;
@@ -413,7 +437,9 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
         // 16k to 32k).  Accuracy caps it: the tensor core truncates when it adds into the FP32 TMEM accumulator, which biases
         // large positive sums (the diagonal, ~1 per SNP) by about -5.4e-9 x K relative: 16k SNPs keeps that under 1e-4
         // (tools/precision_probe.py; the bias is uniform, so G/(trace/n) is unaffected either way).
-        int64_t target = 16384;
+        // split-K launches (few tiles) accumulate only 1 / ksplit of a slab per TMEM chain, so the slab may be ksplit times longer
+        // for the same bias - and a small-n problem is launch-bound: fewer, longer slabs
+        int64_t target = std::min<int64_t>(int64_t{16384} * h->ksplit, 65536);
         if (const char* e = std::getenv("GGRM_CHUNK_SNPS")) target = std::max<int64_t>(64, std::atoll(e));
         const int64_t budget = std::min<int64_t>(int64_t{24} << 30, avail / 2);
         k_cap = std::max<int64_t>(1024, std::min<int64_t>(target, budget / per_snp / 1024 * 1024));
@@ -463,6 +489,7 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
         GGRM_CUDA(cudaMemsetAsync(h->d_counts, 0, static_cast<size_t>(cfg->m_total) * sizeof(int4), h->s_comp));
         GGRM_CUDA(cudaMemsetAsync(h->d_freq, 0, static_cast<size_t>(cfg->m_total) * sizeof(double), h->s_comp));
     }
+    lap("device buffers allocated");
     GGRM_CUDA(cudaMalloc(&h->d_trace, sizeof(double)));
     GGRM_CUDA(cudaMalloc(&h->d_wave_ctr, sizeof(unsigned long long)));
     GGRM_CUDA(cudaMemsetAsync(h->d_wave_ctr, 0, sizeof(unsigned long long), h->s_comp));
@@ -482,6 +509,7 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
         GGRM_CUDA(cudaFuncSetAttribute(syrk_tc_kernel<2>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     }
     GGRM_CUDA(cudaStreamSynchronize(h->s_comp));
+    lap("kernel attributes + sync");
 }
 
 }  // namespace ggrm

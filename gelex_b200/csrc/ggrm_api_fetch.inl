@@ -1,6 +1,8 @@
 // Part of ggrm_api.cu: read-out (packed lower rows, trace, normalised / LOCO forms), accumulator access for the
 // multi-GPU reduce, peer reduce.
 
+#include <type_traits>
+
 namespace ggrm {
 
 static inline int64_t tri(int64_t i) { return i * (i + 1) / 2; }
@@ -134,7 +136,10 @@ static void fetch_typed(Handle& h, int kind, int group, int64_t row_begin, int64
             cnt = lo;
         }
         const int64_t elems = tri(r + cnt) - tri(r);
-        pack_rows_kernel<TAcc, TOut><<<static_cast<unsigned>(cnt), 256, 0, h.s_fetch>>>(A, B, D, h.d_slot_of, r, cnt, scale, static_cast<TOut*>(h.d_stage), h.d_trace);
+        if constexpr (std::is_same<TAcc, float>::value)  // one warp per row, eight consecutive rows per block (see pack_rows8_kernel)
+            pack_rows8_kernel<TOut><<<static_cast<unsigned>((cnt + 7) / 8), 256, 0, h.s_fetch>>>(A, B, D, h.d_slot_of, r, cnt, scale, static_cast<TOut*>(h.d_stage), h.d_trace);
+        else
+            pack_rows_kernel<TAcc, TOut><<<static_cast<unsigned>(cnt), 256, 0, h.s_fetch>>>(A, B, D, h.d_slot_of, r, cnt, scale, static_cast<TOut*>(h.d_stage), h.d_trace);
         GGRM_CUDA(cudaGetLastError());
         ++h.kernel_launches;
         GGRM_CUDA(cudaMemcpyAsync(out + written, h.d_stage, static_cast<size_t>(elems) * sizeof(TOut), cudaMemcpyDeviceToHost, h.s_fetch));

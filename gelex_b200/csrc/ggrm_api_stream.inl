@@ -131,7 +131,10 @@ static void launch_syrk(Handle& h, int kind, int g, int64_t c, int zb, float* fo
         const TcItem* items = h.d_items_tc + item_begin;
         const int nkb = static_cast<int>(round_up(c, 64) / 64);
         const uint32_t fmt = h.cfg.precision == GGRM_PREC_FP16 ? 0u : 1u;
-        const int lo_blk = h.bf16_split ? static_cast<int>(h.k_cap / 64) : 0;
+        const int lo_blk = h.op_split ? static_cast<int>(h.k_cap / 64) : 0;
+        // operand slab small enough to live in L2 (few-tile problems): every CTA pair walks its K range from a different starting
+        // block, so that the pairs sharing a panel do not all ask one L2 slice for the same line at the same moment
+        const int k_rotate = h.n_pad * round_up(c, 64) * 2 * (h.op_split ? 2 : 1) <= (int64_t{48} << 20) ? 13 : 0;
         // few tiles: cut this slab along K as well (whole list only; never combined with bands or the in-epilogue fold)
         int ksplit = 1, accumulate_split = 0;
         if (h.ksplit > 1 && nkb >= h.ksplit && item_begin == 0 && item_count == h.num_items_tc && fold == nullptr) {
@@ -157,14 +160,14 @@ static void launch_syrk(Handle& h, int kind, int g, int64_t c, int zb, float* fo
             lc.attrs = attr;
             lc.numAttrs = 1;
             GGRM_CUDA(cudaLaunchKernelEx(&lc, syrk_tc_kernel<2>, h.tmap[kind][zb], static_cast<float*>(accum),
-                                         items, item_count, nkb, ksplit, lo_blk, accumulate, accumulate_split, fmt, h.cache_hints, h.d_fault,
+                                         items, item_count, nkb, ksplit, lo_blk, k_rotate, accumulate, accumulate_split, fmt, h.cache_hints, h.d_fault,
                                          h.d_wave_ctr, h.wave_base, h.sync_every, fold));
             grid_ctas = 2 * clusters;
             n_clusters = clusters;
         } else {
             const int grid = std::min(item_count, h.sm_count);
             syrk_tc_kernel<1><<<grid, 256, TcConfig<1>::kSmemBytes, h.s_comp>>>(h.tmap[kind][zb], static_cast<float*>(accum), items,
-                                                                                item_count, nkb, 1, lo_blk, accumulate, 0, fmt, h.cache_hints, h.d_fault,
+                                                                                item_count, nkb, 1, lo_blk, k_rotate, accumulate, 0, fmt, h.cache_hints, h.d_fault,
                                                                                 h.d_wave_ctr, h.wave_base, h.sync_every, fold);
             GGRM_CUDA(cudaGetLastError());
             grid_ctas = grid;
@@ -261,7 +264,7 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
     so.range_flag = h.cfg.precision == GGRM_PREC_FP16 ? h.d_range_flag : nullptr;
     for (int kind = 0; kind < 2; ++kind) {
         so.tab16[kind] = h.d_tab16[kind];
-        so.tab16_lo[kind] = h.bf16_split && h.d_tab16[kind] != nullptr ? h.d_tab16[kind] + h.k_cap : nullptr;
+        so.tab16_lo[kind] = h.op_split && h.d_tab16[kind] != nullptr ? h.d_tab16[kind] + h.k_cap : nullptr;
         so.tab64[kind] = h.d_tab64[kind];
     }
     count_stats_kernel<<<static_cast<unsigned>((c + 7) / 8), 256, 0, sp>>>(
@@ -278,9 +281,9 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
         if (h.fp64)
             expand64_kernel<<<egrid, 256, 0, sp>>>(h.d_dense, h.bpv_pad, h.d_tab64[kind], c, static_cast<double*>(h.d_Z[kind][zb]), h.k_cap);
         else {
-            const int64_t z_pitch = h.bf16_split ? 2 * h.k_cap : h.k_cap;  // hi in columns [0, k_cap), lo in [k_cap, 2 k_cap)
+            const int64_t z_pitch = h.op_split ? 2 * h.k_cap : h.k_cap;  // hi in columns [0, k_cap), lo in [k_cap, 2 k_cap)
             expand16_kernel<<<egrid, 256, 0, sp>>>(h.d_dense, h.bpv_pad, h.d_tab16[kind], c, static_cast<uint16_t*>(h.d_Z[kind][zb]), z_pitch);
-            if (h.bf16_split) {
+            if (h.op_split) {
                 GGRM_CUDA(cudaGetLastError());
                 ++h.kernel_launches;
                 expand16_kernel<<<egrid, 256, 0, sp>>>(h.d_dense, h.bpv_pad, h.d_tab16[kind] + h.k_cap, c,

@@ -72,9 +72,10 @@ struct Handle {
     TcItem* d_items_split = nullptr;
     int num_items_split = 0;
     int ksplit = 1;
-    // GGRM_PREC_BF16 on short inputs: operands are kept as hi = bf16(z) and lo = bf16(z - hi) (Z slabs and value tables hold both,
-    // lo at K offset k_cap) and every K block is accumulated as hi hi^T + hi lo^T + lo hi^T (syrk_tc.cuh, lo_blk)
-    bool bf16_split = false;
+    // 16-bit operands on short inputs: operands are kept as hi = op16(z) and lo = op16(z - hi) (Z slabs and value tables hold
+    // both, lo at K offset k_cap) and every K block is accumulated as hi hi^T + hi lo^T + lo hi^T (syrk_tc.cuh, lo_blk).  Decided
+    // in create_impl from the precision, the code policy and the SHORTEST group (every LOCO partial is an output of its own).
+    bool op_split = false;
     F64Item* d_items_f64 = nullptr;
     int num_items_f64 = 0;
     // Row bands of the tcgen05 work list (whole strips of strip_h tile rows, ~equal tile counts).  The LAST slab of a pass is

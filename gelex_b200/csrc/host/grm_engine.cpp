@@ -42,9 +42,12 @@ void check(ggrm_t* h, int status) {
 }
 inline void check_status(ggrm_t* h, int status) { check(h, status); }
 
+// Config::process_exits_after: release nothing that the operating system reclaims at exit anyway
+std::atomic<bool> g_leave_to_os{false};
+
 struct HandleGuard {
     ggrm_t* h = nullptr;
-    ~HandleGuard() { if (h != nullptr) ggrm_destroy(h); }
+    ~HandleGuard() { if (h != nullptr && !g_leave_to_os.load()) ggrm_destroy(h); }
 };
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -198,7 +201,7 @@ class Prefaulter {
             std::lock_guard<std::mutex> lk(reg.mu);
             reg.by_inode.erase(key_);
         }
-        if (map_ != nullptr) ::munmap(map_, bytes_);
+        if (map_ != nullptr && !g_leave_to_os.load()) ::munmap(map_, bytes_);
         if (fd_ >= 0) ::close(fd_);
     }
     void wait() {  // (self-test) until every piece has been tried
@@ -270,7 +273,8 @@ class WriterPool {
         }
         cv_job_.notify_all();
         for (auto& w : workers_) w.join();
-        for (void* p : pinned_) ggrm_host_free(p);
+        if (!g_leave_to_os.load())
+            for (void* p : pinned_) ggrm_host_free(p);
     }
     int64_t buffer_elems() const { return elems_; }
     float* acquire() {
@@ -505,6 +509,7 @@ struct RunContext {
     bool loco;
     bool want_add, want_dom;
     bool gcta;  // kind 1 is the non-missing pair count matrix; outputs are <out>.grm.bin / .grm.N.bin / .grm.id
+    int precision;  // operand precision of this run (Config::precision unless FP16 cannot represent the code values, see compute())
     WriterMode writer;  // effective mode of this run: Pwrite when the file system could not hold every output (see BinFile)
     bool bed_relay;     // 2D-tile mode: one upload per host chunk, peers copy it over NVLink (BedRelay)
     bool prefault;      // create output files ahead of the writers and populate their pages meanwhile (Prefaulter / OutputPreparer);
@@ -550,7 +555,7 @@ ggrm_t* create_handle(const RunContext& rc, int device, const std::vector<int>& 
     c.method = static_cast<int>(rc.cfg->method);
     c.want_add = rc.want_add;
     c.want_dom = rc.want_dom;
-    c.precision = rc.cfg->precision;
+    c.precision = rc.precision;
     std::vector<int64_t> gb, ge;
     for (int g : my_groups) {
         gb.push_back(rc.groups[static_cast<size_t>(g)].begin);
@@ -980,7 +985,7 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
     if (keep_handle != nullptr) {
         *keep_handle = hg.h;
         hg.h = nullptr;
-    } else {
+    } else if (!g_leave_to_os.load()) {
         ggrm_destroy(hg.h);
         hg.h = nullptr;
         note_phase(rc, "teardown", t_teardown, Clock::now());
@@ -1262,7 +1267,7 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
     std::vector<std::thread> threads;
     struct Cleanup {
         std::vector<ggrm_t*>* hs;
-        ~Cleanup() { for (ggrm_t* h : *hs) if (h != nullptr) ggrm_destroy(h); }
+        ~Cleanup() { for (ggrm_t* h : *hs) if (h != nullptr && !g_leave_to_os.load()) ggrm_destroy(h); }
     } cleanup{&handles};
     const bool want_whole = !rc.loco || rc.cfg->write_whole;
     // function scope: these outlive the worker threads (joined below), which read them by reference
@@ -1574,6 +1579,7 @@ int64_t GrmEngine::relay_selftest(int n_chunks, int world, int slots, int chunk_
 void GrmEngine::compute(const GrmObserver& observer) {
     const auto t_start = Clock::now();
     summary_ = Summary{};
+    g_leave_to_os.store(config_.process_exits_after);
     if (config_.gpus.empty()) throw ArgumentValidationException("at least one GPU is required (there is no CPU fallback)");
     if (config_.gcta && (config_.mode != GrmType::A || config_.do_loco))
         throw ArgumentValidationException("--gcta writes the additive matrix of the whole genome: use --add without --dom / --loco");
@@ -1625,6 +1631,14 @@ void GrmEngine::compute(const GrmObserver& observer) {
     rc.gcta = config_.gcta;
     rc.want_add = config_.mode != GrmType::D;
     rc.want_dom = config_.mode != GrmType::A || config_.gcta;
+    // FP16 operands overflow when a standardised value exceeds 65 504.  The scaled orthogonal dominance codes reach |z| ~ n (a
+    // homozygote of an allele seen once: -q/p = -(n - 1)), so from 65 505 samples on such a run takes BF16 operands (FP32 exponent
+    // range) instead; anything else that overflows is caught on the device (ggrm_finish fails with "FP16 operand overflow").
+    rc.precision = config_.precision;
+    if (config_.precision == GGRM_PREC_FP16 && rc.want_dom && !config_.gcta && rc.n_out > 65504 &&
+        (config_.method == GenotypeProcessMethod::OrthStandardizeHWE || config_.method == GenotypeProcessMethod::OrthStandardize))
+        rc.precision = GGRM_PREC_BF16;
+    summary_.precision_used = rc.precision;
     rc.observer = &observer;
     rc.mu = &mu;
     rc.files = &files;

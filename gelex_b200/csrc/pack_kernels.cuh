@@ -58,6 +58,73 @@ __global__ void __launch_bounds__(256) pack_rows_kernel(const TAcc* __restrict__
     }
 }
 
+// FP32 accumulators (the tcgen05 path): the same read-out with one WARP per row and eight consecutive rows per block.  In the
+// tile layout ([float4-column][row][4]) a row's float4s are 2 KB apart, so a block that packs a single row uses 16 bytes of
+// every 32-byte sector it pulls (measured: 0.35 of the HBM peak, 1.19x the useful bytes from DRAM).  Rows r and r + 1 share the
+// sector and eight rows share the 128-byte line: with the eight rows in one block the line is fetched once and served to the
+// other seven warps from L1.  A lane reads one float4 (four columns) per step and writes 16 contiguous bytes; a warp writes 512
+// contiguous bytes of its row.  Arithmetic is the per-element FP64 form of pack_rows_kernel, so results are bit-identical.
+template <typename TOut>
+__global__ void __launch_bounds__(256) pack_rows8_kernel(const float* __restrict__ A, const float* __restrict__ B,
+                                                         const float* __restrict__ D, const int32_t* __restrict__ slot_of,
+                                                         int64_t row_begin, int64_t row_count, double scale,
+                                                         TOut* __restrict__ out, double* __restrict__ trace) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t local = static_cast<int64_t>(blockIdx.x) * 8 + warp;
+    if (local >= row_count) return;
+    const int64_t i = row_begin + local;
+    TOut* dst_row = out + (i * (i + 1) / 2 - row_begin * (row_begin + 1) / 2);
+    const int64_t I = i >> 8;
+    const int r = static_cast<int>(i & 255);
+    const int64_t row_off = static_cast<int64_t>(r >> 7) * 32768 + static_cast<int64_t>(r & 127) * 4;  // + float4-column * 512
+    for (int64_t J = 0; J <= I; ++J) {
+        const int32_t slot = slot_of[I * (I + 1) / 2 + J];
+        const int64_t tile = static_cast<int64_t>(slot) * 65536 + row_off;
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int c4 = lane + 32 * k;
+            const int64_t j0 = J * 256 + 4 * c4;
+            if (j0 > i) continue;
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a, d = a;
+            if (slot >= 0) {
+                a = __ldg(reinterpret_cast<const float4*>(A + tile + c4 * 512));
+                if (B != nullptr) b = __ldg(reinterpret_cast<const float4*>(B + tile + c4 * 512));
+                if (D != nullptr) d = __ldg(reinterpret_cast<const float4*>(D + tile + c4 * 512));
+            }
+            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w}, dv[4] = {d.x, d.y, d.z, d.w};
+            TOut o[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                double v = 0.0;
+                if (slot >= 0) {
+                    v = static_cast<double>(av[e]);
+                    if (B != nullptr) v -= static_cast<double>(bv[e]);
+                    v *= scale;
+                    if (D != nullptr) {
+                        const double dd = static_cast<double>(dv[e]);
+                        v = dd > 0.0 ? __ddiv_rn(v, dd) : 0.0;
+                    }
+                }
+                o[e] = static_cast<TOut>(v);
+                if (j0 + e == i && trace != nullptr) atomicAdd(trace, v);
+            }
+            TOut* dst = dst_row + j0;
+            if (j0 + 3 <= i && (reinterpret_cast<uintptr_t>(dst) & (4 * sizeof(TOut) - 1)) == 0) {
+                if constexpr (sizeof(TOut) == 4) {
+                    *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+                } else {
+                    *reinterpret_cast<double2*>(dst) = make_double2(o[0], o[1]);
+                    *reinterpret_cast<double2*>(dst + 2) = make_double2(o[2], o[3]);
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                    if (j0 + e <= i) dst[e] = o[e];
+            }
+        }
+    }
+}
+
 // Rectangular read-out for the 2D-tile multi-GPU mode: rows [row_begin, +row_count) x columns [col_begin, +col_count) of
 // the lower triangle as a dense row-major [row_count][col_count] block (entries above the diagonal or in tiles this
 // handle does not own read as 0), so a rank can ship exactly the super-tiles it owns to their offsets in the .bin file.

@@ -175,13 +175,14 @@ __device__ __forceinline__ uint16_t to_op16(double v, int fp16) {
     return __bfloat16_as_ushort(__float2bfloat16_rn(f));
 }
 
-// lo half of a BF16 hi + lo operand: bf16(z - hi), hi = bf16(z).  NaN / inf (all-missing SNP under the reference's NaN policy)
-// keep lo = 0 so that hi alone carries the non-finite value.
-__device__ __forceinline__ uint16_t bf16_residual(double v) {
-    const float hi = __bfloat162float(__float2bfloat16_rn(__double2float_rn(v)));
+// lo half of a hi + lo 16-bit operand: op16(z - hi), hi = op16(z).  NaN / inf (all-missing SNP under the reference's NaN policy,
+// FP16 overflow) keep lo = 0 so that hi alone carries the non-finite value.
+__device__ __forceinline__ uint16_t op16_residual(double v, int fp16) {
+    const uint16_t hb = to_op16(v, fp16);
+    const float hi = fp16 ? __half2float(__ushort_as_half(hb)) : __bfloat162float(__ushort_as_bfloat16(hb));
     const double r = v - static_cast<double>(hi);
     if (!(fabs(r) <= 3.0e38)) return 0;
-    return __bfloat16_as_ushort(__float2bfloat16_rn(__double2float_rn(r)));
+    return to_op16(r, fp16);
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -192,7 +193,7 @@ struct StatsOut {
     int4* counts;       // may be nullptr
     double* freq;       // may be nullptr
     uint2* tab16[2];    // [kind]; nullptr when that kind / precision is not wanted
-    uint2* tab16_lo[2]; // [kind]; BF16 hi + lo operands: the table of lo = bf16(z - hi) (nullptr: single 16-bit operand)
+    uint2* tab16_lo[2]; // [kind]; hi + lo operands: the table of lo = op16(z - hi) (nullptr: single 16-bit operand)
     unsigned long long* range_flag;  // FP16 operands: receives 1 + SNP index when a value that occurs in the data overflows binary16
     SnpTable* tab64[2];
     SnpMoments* moments[2];  // [kind]; only the genotype-export hook asks for them (with tab64 of the same kind)
@@ -253,9 +254,9 @@ __global__ void __launch_bounds__(256) count_stats_kernel(const uint8_t* __restr
                 const uint32_t a = to_op16(t.z[0], fp16) | (static_cast<uint32_t>(to_op16(t.z[1], fp16)) << 16);
                 const uint32_t b = to_op16(t.z[2], fp16) | (static_cast<uint32_t>(to_op16(t.z[3], fp16)) << 16);
                 out.tab16[kind][snp] = make_uint2(a, b);
-                if (out.tab16_lo[kind] != nullptr) {  // lo = bf16(z - float(hi)); exact subtraction in FP64, one rounding
-                    const uint32_t la = bf16_residual(t.z[0]) | (static_cast<uint32_t>(bf16_residual(t.z[1])) << 16);
-                    const uint32_t lb = bf16_residual(t.z[2]) | (static_cast<uint32_t>(bf16_residual(t.z[3])) << 16);
+                if (out.tab16_lo[kind] != nullptr) {  // lo = op16(z - float(hi)); exact subtraction in FP64, one rounding
+                    const uint32_t la = op16_residual(t.z[0], fp16) | (static_cast<uint32_t>(op16_residual(t.z[1], fp16)) << 16);
+                    const uint32_t lb = op16_residual(t.z[2], fp16) | (static_cast<uint32_t>(op16_residual(t.z[3], fp16)) << 16);
                     out.tab16_lo[kind][snp] = make_uint2(la, lb);
                 }
                 if (fp16 && out.range_flag != nullptr) {

@@ -57,7 +57,7 @@ struct TcConfig {
 template <int kCtaGroup>
 __global__ void __launch_bounds__(256, 1)
 syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ accum, const TcItem* __restrict__ items,
-               int num_items, int num_k_blocks, int ksplit, int lo_blk, int accumulate, int accumulate_split, uint32_t ab_format,
+               int num_items, int num_k_blocks, int ksplit, int lo_blk, int k_rotate, int accumulate, int accumulate_split, uint32_t ab_format,
                int cache_hints, int* fault_flag, unsigned long long* wave_ctr, unsigned long long wave_base, int sync_every,
                float* __restrict__ fold) {
     // lo_blk > 0: BF16 hi + lo operands (GGRM_PREC_BF16 on short inputs).  The operand matrix holds hi = bf16(z) in K blocks
@@ -132,7 +132,12 @@ syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ a
             const int32_t b_row = item.b_row0 + static_cast<int32_t>(cta_rank) * Cfg::kBRows;
             int kb0, kb1;
             tc_k_range(item, num_k_blocks, ksplit, &kb0, &kb1);
-            for (int kb = kb0; kb < kb1; ++kb) {
+            // k_rotate != 0 (operand slab resident in L2): item `it` starts its K range at block (it * k_rotate) mod length and
+            // wraps around - the sum over K blocks is the same set in another, still deterministic, order
+            const int klen = kb1 - kb0;
+            const int rot = k_rotate != 0 && klen > 1 ? static_cast<int>((static_cast<unsigned>(it) * static_cast<unsigned>(k_rotate)) % static_cast<unsigned>(klen)) : 0;
+            for (int kk = 0; kk < klen; ++kk) {
+                const int kb = kb0 + (kk + rot < klen ? kk + rot : kk + rot - klen);
                 for (int sub = 0; sub < nsub; ++sub) {
                     ptx::mbar_wait(&empty_bar[stage], phase ^ 1, fault_flag, 1);
                     if (ptx::elect_one()) {

@@ -786,6 +786,30 @@ def test_split_k_few_tiles_agrees_with_unsplit_and_oracle(monkeypatch):
         assert np.max(np.abs(got - R[a, : r + 1] / kd)) <= TOL16
 
 
+@pytest.mark.parametrize("precision,method,kinds,m,n", [
+    (g.PREC_FP16, 1, (0,), 8192, 1024),          # FP16, additive: first unsplit size
+    (g.PREC_FP16, 3, (0, 1), 65536, 512),        # FP16, OrthStandardizeHWE add + dom (heavy-tailed dominance codes): first unsplit size
+    (g.PREC_BF16, 1, (0,), 1 << 18, 512),        # BF16, additive: first unsplit size
+    (g.PREC_BF16, 3, (0, 1), 1 << 22, 256),      # BF16, OrthStandardizeHWE add + dom: first unsplit size
+], ids=["fp16-add-8k", "fp16-osh-dom-64k", "bf16-add-256k", "bf16-osh-dom-4M"])
+def test_first_unsplit_sizes_keep_the_bound(precision, method, kinds, m, n):
+    # create_impl splits 16-bit operands into hi + lo below a SNP count that depends on the precision and on the code policy.
+    # Right AT each threshold the plain 16-bit product runs: the bound must hold there with room to spare (the margin is the point
+    # of the thresholds), against every row of the FP64 host matrix.
+    bed = g.synth_bed_host(n, 0, m, 101 + m % 97, 0.01)
+    rows = np.arange(n)
+    with g.Accumulator(n, m, method=method, want_add=0 in kinds, want_dom=1 in kinds, precision=precision) as acc:
+        for s in range(0, m, 65536):
+            acc.push(bed[s:s + 65536], s)
+        acc.finish()
+        for kind in kinds:
+            (R,), (D,) = o.row_spot(bed, n, method, kind, rows, chunk=8192)
+            got = acc.fetch_normalized(kind, g.GROUP_WHOLE)
+            err = float(np.max(np.abs(got - (R / (D.sum() / n))[np.tril_indices(n)])))
+            print(f"unsplit precision={precision} method={method} kind={kind} m={m}: max abs err {err:.3e}  (err * sqrt(m) = {err * m ** 0.5:.4f})")
+            assert err <= 0.6 * TOL16, (precision, method, kind, m, err)
+
+
 def test_bf16_hi_lo_split_keeps_the_bound_on_short_inputs(monkeypatch):
     # GGRM_PREC_BF16 below 2^18 SNPs runs hi + lo operands (3 MMAs per K block): inside 1e-4 where plain BF16 is not
     n, m = 600, 2048

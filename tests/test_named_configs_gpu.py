@@ -106,7 +106,7 @@ def check_rows(acc, kind, group, rows, R, D, n, tol, label, loco_of=None):
 def test_c2_full_shape_rows_match_the_oracle():
     n, m = 50_000, 500_000
     d_bed = device_payload(n, m, 20261104 + 2)
-    bed = d_bed.cpu().numpy()
+    bed = d_bed.cpu().numpy().reshape(m, -1)
     rows = spot_rows(n, 48, 2)
     (R,), (D,) = o.row_spot(bed, n, 1, g.KIND_ADD, rows, chunk=2048)
     for precision, name in ((g.PREC_BF16, "bf16"), (g.PREC_FP16, "fp16")):
@@ -130,7 +130,7 @@ def test_c2_full_shape_rows_match_the_oracle():
 def test_c3_full_shape_add_and_dom_rows_match_the_oracle():
     n, m = 20_000, 300_000
     d_bed = device_payload(n, m, 20261104 + 3)
-    bed = d_bed.cpu().numpy()
+    bed = d_bed.cpu().numpy().reshape(m, -1)
     rows = spot_rows(n, 48, 3)
     host = {kind: o.row_spot(bed, n, 4, kind, rows, chunk=4096) for kind in (g.KIND_ADD, g.KIND_DOM)}
     for precision, name in ((g.PREC_FP16, "fp16"), (g.PREC_BF16, "bf16")):
@@ -143,22 +143,26 @@ def test_c3_full_shape_add_and_dom_rows_match_the_oracle():
 
 
 def test_c4_full_shape_loco_readout_16bit():
+    # 22 chromosome partials + whole in one pass.  FP16 operands are what the engine and `bench.py --config c4` run: every partial
+    # (the shortest has 9 800 SNPs) clears FP16's 8 192-SNP threshold unsplit.  BF16 on the same input splits its operands (hi + lo)
+    # because those partials are far below BF16's 2^18 - checked as well, on fewer partials (it costs 3x the tensor time).
     n, m = 50_000, 600_000
     groups = chromosome_runs(m)
     d_bed = device_payload(n, m, 20261104 + 4)
-    bed = d_bed.cpu().numpy()
+    bed = d_bed.cpu().numpy().reshape(m, -1)
     rows = spot_rows(n, 32, 4)
     R, D = o.row_spot(bed, n, 1, g.KIND_ADD, rows, groups=groups, chunk=2048)
     Rw, Dw = sum(R), sum(D)
-    with g.Accumulator(n, m, method=1, precision=g.PREC_BF16, groups=groups, keep_whole=True) as acc:
-        acc.push_device(d_bed.data_ptr(), 0, m)
-        acc.finish()
-        check_rows(acc, g.KIND_ADD, g.GROUP_WHOLE, rows, Rw, Dw, n, TOL16, "C4 whole = sum of 22 partials")
-        for c in (0, 7, 20, 21):  # largest, middle, smallest chromosomes
-            check_rows(acc, g.KIND_ADD, c, rows, R[c], D[c], n, TOL16, f"C4 partial chr{c + 1} normalised")
-            check_rows(acc, g.KIND_ADD, c, rows, R[c], D[c], n, TOL16, f"C4 LOCO read-out without chr{c + 1}", loco_of=(Rw, Dw))
-        # the whole-genome matrix is the device-side sum of the 22 partials: raw rows add up to FP32 rounding
-        for r in rows[::8]:
-            whole, _ = acc.fetch(g.KIND_ADD, g.GROUP_WHOLE, row_begin=int(r), row_count=1)
-            parts = sum(acc.fetch(g.KIND_ADD, c, row_begin=int(r), row_count=1)[0].astype(np.float64) for c in range(22))
-            assert np.max(np.abs(whole - parts)) <= 22 * 2.0 ** -23 * np.max(np.abs(parts)) + 1e-3, r
+    for precision, name, partials in ((g.PREC_FP16, "fp16", (0, 7, 20, 21)), (g.PREC_BF16, "bf16 hi+lo", (21,))):
+        with g.Accumulator(n, m, method=1, precision=precision, groups=groups, keep_whole=True) as acc:
+            acc.push_device(d_bed.data_ptr(), 0, m)
+            acc.finish()
+            check_rows(acc, g.KIND_ADD, g.GROUP_WHOLE, rows, Rw, Dw, n, TOL16, f"C4 {name} whole = sum of 22 partials")
+            for c in partials:  # largest, middle, smallest chromosomes
+                check_rows(acc, g.KIND_ADD, c, rows, R[c], D[c], n, TOL16, f"C4 {name} partial chr{c + 1} normalised")
+                check_rows(acc, g.KIND_ADD, c, rows, R[c], D[c], n, TOL16, f"C4 {name} LOCO read-out without chr{c + 1}", loco_of=(Rw, Dw))
+            # the whole-genome matrix is the device-side sum of the 22 partials: raw rows add up to FP32 rounding
+            for r in rows[::8]:
+                whole, _ = acc.fetch(g.KIND_ADD, g.GROUP_WHOLE, row_begin=int(r), row_count=1)
+                parts = sum(acc.fetch(g.KIND_ADD, c, row_begin=int(r), row_count=1)[0].astype(np.float64) for c in range(22))
+                assert np.max(np.abs(whole - parts)) <= 22 * 2.0 ** -23 * np.max(np.abs(parts)) + 1e-3, r

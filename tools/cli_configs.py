@@ -105,6 +105,10 @@ def main():
         if r.returncode != 0:
             rec["stderr"] = r.stderr[-800:]
             rec["stdout"] = r.stdout[-800:]
+        ph = [ln for ln in r.stdout.splitlines() if "Host phases" in ln]
+        rec["host_phases"] = ph[0].strip() if ph else None
+        if os.environ.get("GGRM_DEBUG_TIMING"):
+            rec["create_timing"] = [ln.strip() for ln in r.stderr.splitlines() if "[ggrm] create" in ln][:40]
         # spot check: diagonal mean of the whole-genome additive file ~ non-missing SNP count (StandardizeHWE)
         whole = d / (name + "_out.add.bin")
         if whole.exists() and c["method"] == "SH":

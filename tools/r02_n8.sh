@@ -1,17 +1,14 @@
-# 8-GPU call of the next round (gpurun --gpus 8 --timeout 1500 -- 'bash tools/r02_n8.sh'): what round 1 left unmeasured on a full box.
-#   1. bench at N = 8 under torchrun (as the driver launches it)
-#   2. C2 through the CLI on 8 GPUs (SNP shards) with both writers: round 1 had 7.4 s through pwrite (eight writers on one tmpfs inode)
-#   3. C5 through the CLI (2D tiles) with pwrite / mapping, then with the BED relay (accumulate 5.1 s -> ~2.3 s expected)
-#   4. C4 (22 LOCO partials + whole) on 8 GPUs, chromosome shards: the north star's "plus 22 LOCO GRMs" on a full box
+# 8-GPU call of round 2 (gpurun --gpus 8 --timeout 900 -- 'bash tools/r02_n8.sh'): what has never been measured on a full box.
+#   1. multi-process / multi-GPU tests on real peers (NVLink P2P instead of two ranks sharing one device)
+#   2. bench C2 at N = 8 under torchrun, as the driver launches it (piece-grain band-pipelined reduce-scatter; CLI wall leg at 8 GPUs)
+#   3. bench C4 at N = 8: 22 LOCO partials + whole, chromosome shards; CLI wall leg writes 23 x 5 GB
+#   4. C5 (200k x 600k) through the CLI in 2D-tile mode with the BED relay
 set -x
 mkdir -p gpurun_out
+nvidia-smi topo -m > gpurun_out/r02n8_topo.txt 2>&1; df -h /dev/shm /tmp > gpurun_out/r02n8_df.txt 2>&1; nproc >> gpurun_out/r02n8_df.txt; free -g >> gpurun_out/r02n8_df.txt
+timeout 240 python -m pytest tests/test_multiproc_gpu.py tests/test_host_engine.py -m gpu -q -x -k "multi or shard or tile or relay or pipelined or reduce" > gpurun_out/r02n8_tests.log 2>&1; echo rc=$?; tail -4 gpurun_out/r02n8_tests.log
 timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 8 --steps 3 --warmup 3 \
-  > gpurun_out/r02n8_bench.json 2> gpurun_out/r02n8_bench.err; echo rc=$?; cat gpurun_out/r02n8_bench.json
-for w in pwrite mmap; do
-  GELEX_B200_WRITER=$w timeout 200 python tools/cli_configs.py C2 --gpus 8 > gpurun_out/r02n8_c2_$w.jsonl 2> gpurun_out/r02n8_c2_$w.err; echo rc=$?; cat gpurun_out/r02n8_c2_$w.jsonl
-done
-GELEX_B200_WRITER=mmap GELEX_B200_PREFAULT=1 timeout 200 python tools/cli_configs.py C2 --gpus 8 > gpurun_out/r02n8_c2_prefault.jsonl 2> gpurun_out/r02n8_c2_prefault.err; echo rc=$?; cat gpurun_out/r02n8_c2_prefault.jsonl
-GELEX_B200_WRITER=pwrite timeout 300 python tools/cli_configs.py C5 --gpus 8 > gpurun_out/r02n8_c5_pwrite.jsonl 2> gpurun_out/r02n8_c5_pwrite.err; echo rc=$?; cat gpurun_out/r02n8_c5_pwrite.jsonl
-GELEX_B200_WRITER=mmap timeout 300 python tools/cli_configs.py C5 --gpus 8 > gpurun_out/r02n8_c5_mmap.jsonl 2> gpurun_out/r02n8_c5_mmap.err; echo rc=$?; cat gpurun_out/r02n8_c5_mmap.jsonl
-GELEX_B200_WRITER=mmap GELEX_B200_PREFAULT=1 GELEX_B200_BED_RELAY=1 timeout 300 python tools/cli_configs.py C5 --gpus 8 > gpurun_out/r02n8_c5_relay.jsonl 2> gpurun_out/r02n8_c5_relay.err; echo rc=$?; cat gpurun_out/r02n8_c5_relay.jsonl
-timeout 400 python tools/cli_configs.py C4 --gpus 8 > gpurun_out/r02n8_c4.jsonl 2> gpurun_out/r02n8_c4.err; echo rc=$?; cat gpurun_out/r02n8_c4.jsonl
+  > gpurun_out/r02n8_bench_c2.json 2> gpurun_out/r02n8_bench_c2.err; echo rc=$?; cat gpurun_out/r02n8_bench_c2.json; tail -3 gpurun_out/r02n8_bench_c2.err
+timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29512 bench.py --config c4 --wall --gpus 8 --steps 2 --warmup 2 \
+  > gpurun_out/r02n8_bench_c4.json 2> gpurun_out/r02n8_bench_c4.err; echo rc=$?; cat gpurun_out/r02n8_bench_c4.json; tail -3 gpurun_out/r02n8_bench_c4.err
+GELEX_B200_BED_RELAY=1 timeout 300 python tools/cli_configs.py C5 --gpus 8 > gpurun_out/r02n8_c5_relay.jsonl 2> gpurun_out/r02n8_c5_relay.err; echo rc=$?; cat gpurun_out/r02n8_c5_relay.jsonl; tail -3 gpurun_out/r02n8_c5_relay.err
