@@ -137,7 +137,8 @@ static void fetch_typed(Handle& h, int kind, int group, int64_t row_begin, int64
         }
         const int64_t elems = tri(r + cnt) - tri(r);
         if constexpr (std::is_same<TAcc, float>::value)  // one warp per row, eight consecutive rows per block (see pack_rows8_kernel)
-            pack_rows8_kernel<TOut><<<static_cast<unsigned>((cnt + 7) / 8), 256, 0, h.s_fetch>>>(A, B, D, h.d_slot_of, r, cnt, scale, static_cast<TOut*>(h.d_stage), h.d_trace);
+            pack_rows8_kernel<TOut><<<dim3(static_cast<unsigned>((cnt + 7) / 8), static_cast<unsigned>(((r + cnt - 1) / kTile) / kPackTilesPerBlock + 1)), 256, 0, h.s_fetch>>>(
+                A, B, D, h.d_slot_of, r, cnt, scale, static_cast<TOut*>(h.d_stage), h.d_trace);
         else
             pack_rows_kernel<TAcc, TOut><<<static_cast<unsigned>(cnt), 256, 0, h.s_fetch>>>(A, B, D, h.d_slot_of, r, cnt, scale, static_cast<TOut*>(h.d_stage), h.d_trace);
         GGRM_CUDA(cudaGetLastError());

@@ -141,7 +141,6 @@ int run_grm(int argc, char** argv, Logger& log) {
     cfg.gcta = gcta;
     cfg.bed_relay = bed_relay;
     cfg.prefault = prefault;
-    cfg.process_exits_after = true;  // main() leaves through _exit once the report is flushed
 
     log.info("gelex-b200 | GRM Computation (B200 tcgen05 engine)");
     log.info("");
@@ -220,12 +219,7 @@ int main(int argc, char** argv) {
         std::snprintf(line, sizeof(line), "Done in %.2f s", el);
         log.info("");
         log.info(line);
-        // every output is closed; what is left (device memory, page-locked buffers, the mapped .bed, the CUDA context) goes back to
-        // the operating system with the process, without the library's and the runtime's orderly tear-down
-        std::cout.flush();
-        std::cerr.flush();
-        if (log.file.is_open()) log.file.close();
-        ::_exit(rc);
+        return rc;
     } catch (const std::exception& e) {
         log.error(e.what());
         return 1;

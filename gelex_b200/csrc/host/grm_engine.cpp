@@ -42,12 +42,9 @@ void check(ggrm_t* h, int status) {
 }
 inline void check_status(ggrm_t* h, int status) { check(h, status); }
 
-// Config::process_exits_after: release nothing that the operating system reclaims at exit anyway
-std::atomic<bool> g_leave_to_os{false};
-
 struct HandleGuard {
     ggrm_t* h = nullptr;
-    ~HandleGuard() { if (h != nullptr && !g_leave_to_os.load()) ggrm_destroy(h); }
+    ~HandleGuard() { if (h != nullptr) ggrm_destroy(h); }
 };
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -201,7 +198,7 @@ class Prefaulter {
             std::lock_guard<std::mutex> lk(reg.mu);
             reg.by_inode.erase(key_);
         }
-        if (map_ != nullptr && !g_leave_to_os.load()) ::munmap(map_, bytes_);
+        if (map_ != nullptr) ::munmap(map_, bytes_);
         if (fd_ >= 0) ::close(fd_);
     }
     void wait() {  // (self-test) until every piece has been tried
@@ -273,8 +270,7 @@ class WriterPool {
         }
         cv_job_.notify_all();
         for (auto& w : workers_) w.join();
-        if (!g_leave_to_os.load())
-            for (void* p : pinned_) ggrm_host_free(p);
+        for (void* p : pinned_) ggrm_host_free(p);
     }
     int64_t buffer_elems() const { return elems_; }
     float* acquire() {
@@ -811,19 +807,32 @@ class OutputPreparer {
         while (ready_[i].load(std::memory_order_acquire) == 0) std::this_thread::sleep_for(std::chrono::microseconds(50));
         return ok_[i] != 0;
     }
-    // The writer has closed entry i's files: drop their populated mappings and let the preparer move on.
+    // The writer has closed entry i's files: the preparer may move on; it also unmaps the populated mappings of finished entries
+    // on its own thread (tearing down the page tables of a 5 GB mapping takes ~0.1 s that the pushing thread should not pay).
     void done(size_t i) {
         {
             std::lock_guard<std::mutex> lk(mu_);
-            slots_[i].clear();
+            finished_.push_back(i);
         }
         done_.fetch_add(1);
     }
 
    private:
+    void release_finished() {
+        std::vector<std::vector<std::unique_ptr<Prefaulter>>> drop;
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            for (size_t i : finished_) drop.push_back(std::move(slots_[i]));
+            finished_.clear();
+        }
+    }
     void run() {
         for (size_t i = 0; i < bins_.size() && !stop_.load(); ++i) {
-            while (i >= done_.load() + static_cast<size_t>(ahead_) && !stop_.load()) std::this_thread::sleep_for(std::chrono::microseconds(200));
+            while (i >= done_.load() + static_cast<size_t>(ahead_) && !stop_.load()) {
+                release_finished();
+                std::this_thread::sleep_for(std::chrono::microseconds(200));
+            }
+            release_finished();
             if (stop_.load()) break;
             bool ok = true;
             std::vector<std::unique_ptr<Prefaulter>> made;
@@ -850,6 +859,11 @@ class OutputPreparer {
             int z = 0;
             r.compare_exchange_strong(z, 1);
         }
+        while (!stop_.load()) {  // the last entries are finished after the last one was prepared
+            release_finished();
+            std::this_thread::sleep_for(std::chrono::microseconds(500));
+        }
+        release_finished();
     }
     std::vector<std::vector<std::string>> bins_;
     int64_t n_;
@@ -857,6 +871,7 @@ class OutputPreparer {
     std::vector<std::atomic<int>> ready_;
     std::vector<char> ok_;
     std::vector<std::vector<std::unique_ptr<Prefaulter>>> slots_;
+    std::vector<size_t> finished_;
     std::atomic<size_t> done_{0};
     std::atomic<bool> stop_{false};
     std::mutex mu_;
@@ -985,7 +1000,7 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
     if (keep_handle != nullptr) {
         *keep_handle = hg.h;
         hg.h = nullptr;
-    } else if (!g_leave_to_os.load()) {
+    } else {
         ggrm_destroy(hg.h);
         hg.h = nullptr;
         note_phase(rc, "teardown", t_teardown, Clock::now());
@@ -1267,7 +1282,7 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
     std::vector<std::thread> threads;
     struct Cleanup {
         std::vector<ggrm_t*>* hs;
-        ~Cleanup() { for (ggrm_t* h : *hs) if (h != nullptr && !g_leave_to_os.load()) ggrm_destroy(h); }
+        ~Cleanup() { for (ggrm_t* h : *hs) if (h != nullptr) ggrm_destroy(h); }
     } cleanup{&handles};
     const bool want_whole = !rc.loco || rc.cfg->write_whole;
     // function scope: these outlive the worker threads (joined below), which read them by reference
@@ -1579,7 +1594,6 @@ int64_t GrmEngine::relay_selftest(int n_chunks, int world, int slots, int chunk_
 void GrmEngine::compute(const GrmObserver& observer) {
     const auto t_start = Clock::now();
     summary_ = Summary{};
-    g_leave_to_os.store(config_.process_exits_after);
     if (config_.gpus.empty()) throw ArgumentValidationException("at least one GPU is required (there is no CPU fallback)");
     if (config_.gcta && (config_.mode != GrmType::A || config_.do_loco))
         throw ArgumentValidationException("--gcta writes the additive matrix of the whole genome: use --add without --dom / --loco");

@@ -83,10 +83,6 @@ class GrmEngine {
         // LOCO runs prepare the per-chromosome files two ahead of the writer the same way (OutputPreparer).  On by default
         // (measured on the GPU box, profiles/r02a_cli_writers.jsonl); GELEX_B200_PREFAULT=0/1 overrides.
         bool prefault = true;
-        // The process ends right after compute() (the CLI): device handles, page-locked buffers and file mappings are left to the
-        // operating system instead of being released one by one (0.2-0.4 s of cudaFree / cudaFreeHost / munmap per run).  Every
-        // output file is complete and closed when compute() returns either way.
-        bool process_exits_after = false;
         // GCTA binary format behind a flag (docs/source/data_formats.rst:188-208): instead of <out>.add.{bin,id} write
         // <out>.grm.bin (A_ij = G_ij / N_ij), <out>.grm.N.bin (N_ij = SNPs called in both samples) and <out>.grm.id.  Mode A, no LOCO.
         bool gcta = false;

@@ -63,7 +63,9 @@ __global__ void __launch_bounds__(256) pack_rows_kernel(const TAcc* __restrict__
 // every 32-byte sector it pulls (measured: 0.35 of the HBM peak, 1.19x the useful bytes from DRAM).  Rows r and r + 1 share the
 // sector and eight rows share the 128-byte line: with the eight rows in one block the line is fetched once and served to the
 // other seven warps from L1.  A lane reads one float4 (four columns) per step and writes 16 contiguous bytes; a warp writes 512
-// contiguous bytes of its row.  Arithmetic is the per-element FP64 form of pack_rows_kernel, so results are bit-identical.
+// contiguous bytes of its row; blockIdx.y walks the row in chunks of kPackTilesPerBlock tile columns so that a read-out of a few
+// hundred rows still fills the machine.  Arithmetic is the per-element FP64 form of pack_rows_kernel, so results are bit-identical.
+constexpr int kPackTilesPerBlock = 8;
 template <typename TOut>
 __global__ void __launch_bounds__(256) pack_rows8_kernel(const float* __restrict__ A, const float* __restrict__ B,
                                                          const float* __restrict__ D, const int32_t* __restrict__ slot_of,
@@ -77,7 +79,9 @@ __global__ void __launch_bounds__(256) pack_rows8_kernel(const float* __restrict
     const int64_t I = i >> 8;
     const int r = static_cast<int>(i & 255);
     const int64_t row_off = static_cast<int64_t>(r >> 7) * 32768 + static_cast<int64_t>(r & 127) * 4;  // + float4-column * 512
-    for (int64_t J = 0; J <= I; ++J) {
+    const int64_t J_begin = static_cast<int64_t>(blockIdx.y) * kPackTilesPerBlock;
+    const int64_t J_end = J_begin + kPackTilesPerBlock < I + 1 ? J_begin + kPackTilesPerBlock : I + 1;
+    for (int64_t J = J_begin; J < J_end; ++J) {
         const int32_t slot = slot_of[I * (I + 1) / 2 + J];
         const int64_t tile = static_cast<int64_t>(slot) * 65536 + row_off;
 #pragma unroll

