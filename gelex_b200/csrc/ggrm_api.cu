@@ -160,7 +160,9 @@ void build_ownership_and_items(Handle& h) {
     h.ksplit = 1;
     std::vector<TcItem> split;
     if (!h.fp64 && h.tc_mode == 2 && slot > 0) {
-        int want = std::min<int>(8, (h.sm_count / 2) / static_cast<int>(slot));
+        // from the tile count of the WHOLE triangle, not of this handle's share: every 2D-tile rank then cuts K exactly like the
+        // single-GPU run does, and a tile's bits do not depend on who owns it
+        int want = static_cast<int>(std::min<int64_t>(8, (h.sm_count / 2) / std::max<int64_t>(1, T * (T + 1) / 2)));
         if (const char* e = std::getenv("GGRM_KSPLIT")) want = std::max(1, std::min(8, std::atoi(e)));
         const bool keeps_whole = h.cfg.n_groups > 1 && h.cfg.keep_whole;  // the in-epilogue fold into `whole` assumes one copy
         if (want > 1 && !keeps_whole && h.band_item_end.size() <= 1) {

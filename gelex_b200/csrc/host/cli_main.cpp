@@ -142,6 +142,14 @@ int run_grm(int argc, char** argv, Logger& log) {
     cfg.bed_relay = bed_relay;
     cfg.prefault = prefault;
 
+    // CUDA initialises every visible device when the first context is created (several hundred ms each on an 8-GPU box): a run
+    // that uses the first `gpus` devices hides the others, unless the caller has already chosen what is visible
+    if (std::getenv("CUDA_VISIBLE_DEVICES") == nullptr) {
+        std::string vis;
+        for (int g = 0; g < gpus; ++g) vis += (g ? "," : "") + std::to_string(g);
+        ::setenv("CUDA_VISIBLE_DEVICES", vis.c_str(), 0);
+    }
+
     log.info("gelex-b200 | GRM Computation (B200 tcgen05 engine)");
     log.info("");
     log.info("[Config]");

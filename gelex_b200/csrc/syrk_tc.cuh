@@ -132,10 +132,12 @@ syrk_tc_kernel(const __grid_constant__ CUtensorMap tmap_z, float* __restrict__ a
             const int32_t b_row = item.b_row0 + static_cast<int32_t>(cta_rank) * Cfg::kBRows;
             int kb0, kb1;
             tc_k_range(item, num_k_blocks, ksplit, &kb0, &kb1);
-            // k_rotate != 0 (operand slab resident in L2): item `it` starts its K range at block (it * k_rotate) mod length and
-            // wraps around - the sum over K blocks is the same set in another, still deterministic, order
+            // k_rotate != 0 (operand slab resident in L2): a tile starts its K range at a block derived from its own coordinates and
+            // wraps around - the sum over K blocks is the same set in another order that depends on the TILE only, so a tile gives
+            // the same bits whichever handle owns it (2D-tile ranks reproduce the single-GPU file byte for byte)
             const int klen = kb1 - kb0;
-            const int rot = k_rotate != 0 && klen > 1 ? static_cast<int>((static_cast<unsigned>(it) * static_cast<unsigned>(k_rotate)) % static_cast<unsigned>(klen)) : 0;
+            const unsigned tile_key = static_cast<unsigned>(item.a_row0 >> 7) * 7u + static_cast<unsigned>(item.b_row0 >> 8) * static_cast<unsigned>(k_rotate);
+            const int rot = k_rotate != 0 && klen > 1 ? static_cast<int>(tile_key % static_cast<unsigned>(klen)) : 0;
             for (int kk = 0; kk < klen; ++kk) {
                 const int kb = kb0 + (kk + rot < klen ? kk + rot : kk + rot - klen);
                 for (int sub = 0; sub < nsub; ++sub) {
