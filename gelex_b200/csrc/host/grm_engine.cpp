@@ -1109,14 +1109,16 @@ void run_pipelined_rank(const RunContext& rc, ShardPipe& sp, size_t r, double* p
     check(h, ggrm_set_push_end(h, sp.snps[r].second));  // equal slabs inside the shard
     WriterPool pool(rc.cfg->writer_threads, rc.cfg->writer_threads + 2, std::max<int64_t>(kWriterBufferElems, rc.n_out));
     BinFile files[2];
-    for (int kind = 0; kind < 2; ++kind)
-        if (kind == 0 ? rc.want_add : rc.want_dom) files[kind].open(output_base(rc, kind, "") + ".bin", rc.n_out, false, rc.writer, rc.prefault);
     int64_t done = 0;
     const auto t_push = Clock::now();
     push_range(rc, h, sp.snps[r].first, sp.snps[r].second, rc.m, &done, true, nullptr, &sp.snps_done);
     check(h, ggrm_finish_async(h));
     const auto t0 = Clock::now();
     note_phase(rc, "push", t_push, t0);
+    // opened only now: a file whose pages are being populated (Prefaulter) is opened when that has finished, which must not hold
+    // up the pushes - the whole pass is in front of the first write
+    for (int kind = 0; kind < 2; ++kind)
+        if (kind == 0 ? rc.want_add : rc.want_dom) files[kind].open(output_base(rc, kind, "") + ".bin", rc.n_out, false, rc.writer, rc.prefault);
     auto wait_band = [&](int band) {  // every rank's rows of this band are final
         const auto t_wait = Clock::now();
         for (;;) {
@@ -1280,9 +1282,14 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
     std::vector<ggrm_t*> handles(ng, nullptr);
     std::vector<std::exception_ptr> errors(ng);
     std::vector<std::thread> threads;
-    struct Cleanup {
+    struct Cleanup {  // handles go down side by side: releasing a 17 GB handle whose memory peers have mapped takes ~0.3 s
         std::vector<ggrm_t*>* hs;
-        ~Cleanup() { for (ggrm_t* h : *hs) if (h != nullptr) ggrm_destroy(h); }
+        ~Cleanup() {
+            std::vector<std::thread> ts;
+            for (ggrm_t* h : *hs)
+                if (h != nullptr) ts.emplace_back([h] { ggrm_destroy(h); });
+            for (auto& t : ts) t.join();
+        }
     } cleanup{&handles};
     const bool want_whole = !rc.loco || rc.cfg->write_whole;
     // function scope: these outlive the worker threads (joined below), which read them by reference
