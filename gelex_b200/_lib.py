@@ -70,7 +70,7 @@ EXPORTS = [
     "ggrm_fetch_block", "ggrm_owned_supertiles", "ggrm_host_alloc", "ggrm_host_free", "ggrm_bin_to_dense", "ggrm_assoc_chunk",
     "ggrm_band_layout", "ggrm_set_band_flags", "ggrm_reduce_rows_async", "ggrm_genotype_chunk", "ggrm_fetch_gcta", "ggrm_accum_address",
     "ggrm_stage_create", "ggrm_stage_destroy", "ggrm_stage_upload", "ggrm_stage_slot", "ggrm_wait_copies",
-    "ggrm_warm_device", "ggrm_reduce_block_async",
+    "ggrm_warm_device", "ggrm_reduce_block_async", "ggrm_host_register", "ggrm_host_unregister",
 ]
 
 _lib = None
@@ -132,6 +132,8 @@ def load() -> C.CDLL:
     lib.ggrm_stage_slot.argtypes = [vp, C.c_int, C.POINTER(vp)]
     lib.ggrm_wait_copies.argtypes = [vp]
     lib.ggrm_warm_device.argtypes = [C.c_int]
+    lib.ggrm_host_register.argtypes = [vp, i64]
+    lib.ggrm_host_unregister.argtypes = [vp]
     lib.ggrm_reduce_block_async.argtypes = [vp, C.c_int, C.c_int, C.POINTER(vp), C.c_int, i64, i64, i64]
     lib.ggrm_device_count.argtypes = []
     lib.ggrm_version.argtypes = []

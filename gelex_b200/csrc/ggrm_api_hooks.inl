@@ -227,6 +227,31 @@ extern "C" int ggrm_host_free(void* p) {
     GGRM_STATELESS_END
 }
 
+extern "C" int ggrm_host_register(void* p, int64_t bytes) {
+    if (p == nullptr || bytes <= 0) {
+        g_create_error = "null argument";
+        return GGRM_ERR_INVALID_ARGUMENT;
+    }
+    const cudaError_t e = cudaHostRegister(p, static_cast<size_t>(bytes), cudaHostRegisterPortable);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        g_create_error = std::string("CUDA: ") + cudaGetErrorString(e) + " at cudaHostRegister";
+        return GGRM_ERR_CUDA;
+    }
+    return GGRM_OK;
+}
+
+extern "C" int ggrm_host_unregister(void* p) {
+    if (p == nullptr) return GGRM_OK;
+    const cudaError_t e = cudaHostUnregister(p);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        g_create_error = std::string("CUDA: ") + cudaGetErrorString(e) + " at cudaHostUnregister";
+        return GGRM_ERR_CUDA;
+    }
+    return GGRM_OK;
+}
+
 static uint32_t miss_threshold(double missing_rate) {
     if (!(missing_rate > 0.0)) return 0u;
     if (missing_rate >= 1.0) return 1u << 24;

@@ -89,7 +89,7 @@ struct SharedMappings {
 };
 // Blocks until the prefaulter has tried every piece; false = it could not populate the file (no room, old kernel): a store into
 // the mapping might then raise SIGBUS, so the caller must write with pwrite, whose ENOSPC becomes FileWriteException.
-bool prefault_completed_ok(Prefaulter* p);
+bool prefault_completed_ok(Prefaulter* p, bool* pinned);
 
 struct BinFile {
     int fd = -1;
@@ -99,6 +99,7 @@ struct BinFile {
     bool owns_map = true;      // false: the mapping belongs to a Prefaulter (SharedMappings)
     bool map_all = false;      // every segment goes through the mapping (tmpfs, or WriterMode::Mmap)
     bool on_tmpfs = false;
+    bool pinned = false;       // the (prepared) mapping is page-locked: ggrm_fetch* may DMA rows straight into it
     BinFile() = default;
     BinFile(const BinFile&) = delete;
     BinFile& operator=(const BinFile&) = delete;
@@ -124,7 +125,7 @@ struct BinFile {
         if (bytes == 0) return;
         SharedMappings::Entry shared{};
         if (!create && use_prepared && SharedMappings::get().find(fd, static_cast<size_t>(bytes), &shared)) {
-            if (!prefault_completed_ok(shared.owner)) return;  // not populated: pwrite only (see prefault_completed_ok)
+            if (!prefault_completed_ok(shared.owner, &pinned)) return;  // not populated: pwrite only (see prefault_completed_ok)
             map = shared.map;
             owns_map = false;
         } else {
@@ -170,7 +171,7 @@ bool file_system_has_room(const fs::path& path, int64_t bytes) {
 // when the writers start).  A file system without room makes the call fail instead of raising SIGBUS; the threads then simply stop.
 class Prefaulter {
    public:
-    Prefaulter(const std::string& path, int threads) {
+    Prefaulter(const std::string& path, int threads, bool pin = false) : pin_(pin) {
         fd_ = ::open(path.c_str(), O_RDWR);
         if (fd_ < 0) return;
         struct stat st {};
@@ -185,8 +186,18 @@ class Prefaulter {
             key_ = {static_cast<uint64_t>(st.st_dev), static_cast<uint64_t>(st.st_ino)};
             registered_ = reg.by_inode.emplace(key_, SharedMappings::Entry{map_, bytes_, this}).second;
         }
+        populating_.store(std::max(1, threads));
         running_.store(std::max(1, threads));
-        for (int t = 0; t < std::max(1, threads); ++t) workers_.emplace_back([this] { run(); running_.fetch_sub(1); });
+        for (int t = 0; t < std::max(1, threads); ++t)
+            workers_.emplace_back([this] {
+                run();
+                // the last worker out page-locks the populated mapping (tmpfs only; ~11 GB/s on the GPU box, a disk file's pages
+                // cannot be pinned and the call fails): the read-out then DMAs rows straight into the file's pages - no staging
+                // buffer, no host copy (measured 56 GB/s against ~10 GB/s through writer threads, profiles/r02_summary.md)
+                if (populating_.fetch_sub(1) == 1 && pin_ && !failed_.load() && !stop_.load() && populated_.load() == bytes_)
+                    pinned_.store(ggrm_host_register(map_, static_cast<int64_t>(bytes_)) == GGRM_OK);
+                running_.fetch_sub(1);
+            });
     }
     Prefaulter(const Prefaulter&) = delete;
     Prefaulter& operator=(const Prefaulter&) = delete;
@@ -198,9 +209,15 @@ class Prefaulter {
             std::lock_guard<std::mutex> lk(reg.mu);
             reg.by_inode.erase(key_);
         }
+        if (pinned_.load()) ggrm_host_unregister(map_);
         if (map_ != nullptr) ::munmap(map_, bytes_);
         if (fd_ >= 0) ::close(fd_);
     }
+    // until every page has been tried (the page-locking of a pinned prefaulter may still be running: see finished())
+    void wait_populated() {
+        while (populating_.load() != 0) std::this_thread::sleep_for(std::chrono::microseconds(100));
+    }
+    bool pinned() const { return pinned_.load(); }
     void wait() {  // (self-test) until every piece has been tried
         for (auto& w : workers_) w.join();
         workers_.clear();
@@ -233,16 +250,18 @@ class Prefaulter {
     char* map_ = nullptr;
     size_t bytes_ = 0;
     std::atomic<size_t> next_{0}, populated_{0};
-    std::atomic<bool> stop_{false}, failed_{false};
-    std::atomic<int> running_{0};
+    std::atomic<bool> stop_{false}, failed_{false}, pinned_{false};
+    std::atomic<int> running_{0}, populating_{0};
+    bool pin_ = false;
     std::vector<std::thread> workers_;
     std::pair<uint64_t, uint64_t> key_{0, 0};
     bool registered_ = false;
 };
 
-bool prefault_completed_ok(Prefaulter* p) {
+bool prefault_completed_ok(Prefaulter* p, bool* pinned) {
     if (p == nullptr) return false;
     while (!p->finished()) std::this_thread::sleep_for(std::chrono::microseconds(100));
+    if (pinned != nullptr) *pinned = p->pinned();
     return p->ok();
 }
 
@@ -379,6 +398,18 @@ std::vector<Segment> supertile_segments(int64_t row0, int64_t col0, int64_t rows
 // Rows [r0, r1) of matrix (kind, group) -> their byte range of the file, in blocks of whole rows.
 void write_packed_rows(ggrm_t* h, int kind, int group, int64_t r0, int64_t r1, const BinFile& file, WriterPool& pool, bool gcta = false) {
     int64_t r = r0;
+    if (file.map != nullptr && file.pinned) {
+        // the file's pages are populated and page-locked: the device copies the packed rows to their place in the file
+        constexpr int64_t kDirectElems = int64_t{1} << 28;  // 1 GiB per call keeps the progress of a failing run observable
+        while (r < r1) {
+            const int64_t cnt = rows_fitting(r, r1, kDirectElems);
+            float* dst = reinterpret_cast<float*>(file.map + tri(r) * 4);
+            const int st = gcta ? ggrm_fetch_gcta(h, kind, group, r, cnt, dst) : ggrm_fetch(h, kind, group, r, cnt, dst, nullptr);
+            if (st != GGRM_OK) throw_status(st, ggrm_last_error(h));
+            r += cnt;
+        }
+        return;
+    }
     while (r < r1) {
         const int64_t cnt = rows_fitting(r, r1, pool.buffer_elems());
         float* buf = pool.acquire();
@@ -510,6 +541,7 @@ struct RunContext {
     bool bed_relay;     // 2D-tile mode: one upload per host chunk, peers copy it over NVLink (BedRelay)
     bool prefault;      // create output files ahead of the writers and populate their pages meanwhile (Prefaulter / OutputPreparer);
                         // false when the user forced pwrite.  Independent of `writer`: a populated mapping cannot fault for lack of space
+    bool direct_dma;    // prepared mappings are page-locked and whole-row read-outs DMA straight into them (GELEX_B200_DIRECT_DMA=0: off)
     // progress (reference: per work item, counted in SNPs; grm.h:124-130)
     const GrmObserver* observer;
     std::mutex* mu;
@@ -779,7 +811,7 @@ std::vector<std::unique_ptr<Prefaulter>> start_prefault(const RunContext& rc, bo
     if (!rc.prefault || (rc.loco && !whole_of_loco_run)) return out;
     for (int kind = 0; kind < 2; ++kind)
         if (kind == 0 ? rc.want_add : rc.want_dom)
-            out.push_back(std::make_unique<Prefaulter>(output_base(rc, kind, "") + ".bin", std::max(2, rc.cfg->writer_threads)));
+            out.push_back(std::make_unique<Prefaulter>(output_base(rc, kind, "") + ".bin", std::max(2, rc.cfg->writer_threads), rc.direct_dma));
     return out;
 }
 
@@ -791,8 +823,8 @@ std::vector<std::unique_ptr<Prefaulter>> start_prefault(const RunContext& rc, bo
 // then creates it itself and fails the reference's way.
 class OutputPreparer {
    public:
-    OutputPreparer(std::vector<std::vector<std::string>> bins /* per entry: the .bin paths written together */, int64_t n, int threads, int ahead)
-        : bins_(std::move(bins)), n_(n), threads_(std::max(1, threads)), ahead_(std::max(1, ahead)), ready_(bins_.size()), ok_(bins_.size()), slots_(bins_.size()) {
+    OutputPreparer(std::vector<std::vector<std::string>> bins /* per entry: the .bin paths written together */, int64_t n, int threads, int ahead, bool pin)
+        : bins_(std::move(bins)), n_(n), threads_(std::max(1, threads)), ahead_(std::max(1, ahead)), pin_(pin), ready_(bins_.size()), ok_(bins_.size()), slots_(bins_.size()) {
         for (auto& r : ready_) r.store(0);
         worker_ = std::thread([this] { run(); });
     }
@@ -841,8 +873,8 @@ class OutputPreparer {
                     BinFile f;
                     f.open(path, n_, true);
                     f.close_checked();
-                    made.push_back(std::make_unique<Prefaulter>(path, threads_));
-                    made.back()->wait();
+                    made.push_back(std::make_unique<Prefaulter>(path, threads_, pin_));
+                    made.back()->wait_populated();  // its page-locking (pin_) runs on while the next file is populated
                 }
             } catch (...) {
                 ok = false;  // the writer creates the file itself and reports the error the reference would
@@ -868,6 +900,7 @@ class OutputPreparer {
     std::vector<std::vector<std::string>> bins_;
     int64_t n_;
     int threads_, ahead_;
+    bool pin_;
     std::vector<std::atomic<int>> ready_;
     std::vector<char> ok_;
     std::vector<std::vector<std::unique_ptr<Prefaulter>>> slots_;
@@ -953,7 +986,9 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
         for (size_t li = 0; li < my_groups.size(); ++li)
             if (!superseded(static_cast<int>(li))) prep_index[li] = entry(group_name(static_cast<int>(li)));
         if (whole_last) prep_index[my_groups.size()] = entry("");
-        if (!bins.empty()) preparer = std::make_unique<OutputPreparer>(std::move(bins), rc.n_out, std::max(2, rc.cfg->writer_threads), 2);
+        // with direct DMA the writer threads idle, so the page population gets their share of the cores too
+        if (!bins.empty())
+            preparer = std::make_unique<OutputPreparer>(std::move(bins), rc.n_out, std::max(2, rc.cfg->writer_threads) * (rc.direct_dma ? 2 : 1), 2, rc.direct_dma);
     }
     // write one prepared (or not) output entry
     auto write_entry = [&](int local_group, const std::string& suffix, size_t slot) {
@@ -1687,6 +1722,8 @@ void GrmEngine::compute(const GrmObserver& observer) {
         // profiles/r02a_cli_writers.jsonl); GELEX_B200_PREFAULT=0 turns it off
         const char* pf = std::getenv("GELEX_B200_PREFAULT");
         rc.prefault = (pf != nullptr ? pf[0] != '0' : config_.prefault) && rc.writer != WriterMode::Pwrite;  // a forced pwrite stays pwrite
+        const char* dd = std::getenv("GELEX_B200_DIRECT_DMA");
+        rc.direct_dma = rc.prefault && !(dd != nullptr && dd[0] == '0');
     }
     if (rc.writer != WriterMode::Pwrite) {
         // every .bin of the run: one per work item, plus the whole-genome sums of a LOCO run, or the GCTA pair

@@ -280,6 +280,12 @@ int ggrm_enable_peer_access(int device, int peer_device);
  * headers of its own. */
 int ggrm_host_alloc(int64_t bytes, void** out);
 int ggrm_host_free(void* p);
+/* Page-lock memory the caller already owns (cudaHostRegister, portable) - e.g. a populated shared mapping of an output file on
+ * tmpfs - so that ggrm_fetch* can DMA rows straight into it instead of through a staging buffer and a host copy
+ * (grm_bin_writer.cpp:54-61 is the step this replaces).  Fails (GGRM_ERR_CUDA) for memory the driver cannot pin, such as the
+ * mapping of a file on a disk file system; the caller then keeps staging.  Unregister before unmapping. */
+int ggrm_host_register(void* p, int64_t bytes);
+int ggrm_host_unregister(void* p);
 
 /* ---- One host read of the BED feeding several handles (2D-tile multi-GPU mode, SURVEY 8e input side) ------------------
  * Every GPU of a 2D-tile run accumulates every SNP.  Rather than each GPU pulling the whole file over its own PCIe link

@@ -717,3 +717,35 @@ def test_engine_gcta_files(tmp_path, monkeypatch):
     assert (tmp_path / "g3.grm.N.bin").read_bytes() == (tmp_path / "g1.grm.N.bin").read_bytes()
     a3 = plink_io.read_bin(tmp_path / "g3.grm.bin", n).astype(np.float64)
     assert np.max(np.abs(a3 - ref)) <= 8e-3
+
+
+@pytest.mark.gpu
+def test_engine_direct_dma_into_the_output_mapping_matches_the_staged_writer(tmp_path, monkeypatch):
+    # On tmpfs the populated mapping of an output file is page-locked and whole-row read-outs DMA straight into it (no staging buffer,
+    # no host copy); elsewhere - and with GELEX_B200_DIRECT_DMA=0 - rows go through the writer pool.  Same bytes either way:
+    # whole-genome file, every chromosome file of a LOCO run and its whole (one GPU; two ranks' row slices of the LOCO whole).
+    import shutil
+    import tempfile
+
+    if not Path("/dev/shm").is_dir():
+        pytest.skip("no tmpfs at /dev/shm")
+    shm = Path(tempfile.mkdtemp(prefix="ggrm_dma_", dir="/dev/shm"))
+    try:
+        monkeypatch.setenv("GELEX_B200_OVERSUBSCRIBE", "1")
+        n, m = 4500, 3000
+        payload = g.synth_bed_host(n, 0, m, 29, 0.01)
+        bounds = [round(m * i / 5) for i in range(6)]
+        chroms = [str(c + 1) for c in range(5) for _ in range(bounds[c + 1] - bounds[c])]
+        plink_io.write_plink(shm / "d", payload, [("F", f"s{i:05d}") for i in range(n)], chroms)
+        runs = {}
+        for tag, dma in (("dma", "1"), ("staged", "0")):
+            monkeypatch.setenv("GELEX_B200_DIRECT_DMA", dma)
+            engine.grm_run(shm / "d", shm / f"{tag}_w", method="SH", precision=g.PREC_FP16)
+            engine.grm_run(shm / "d", shm / f"{tag}_l", method="OCH", mode="AD", loco=True, precision=g.PREC_FP16, write_whole=True)
+            engine.grm_run(shm / "d", shm / f"{tag}_l2", method="SH", loco=True, precision=g.PREC_FP16, write_whole=True, n_gpus=2, partition="snp")
+            runs[tag] = sorted(p.name[len(tag):] for p in shm.glob(f"{tag}_*.bin"))
+        assert runs["dma"] == runs["staged"] and len(runs["dma"]) == 1 + 12 + 6
+        for suffix in runs["dma"]:
+            assert (shm / f"dma{suffix}").read_bytes() == (shm / f"staged{suffix}").read_bytes(), suffix
+    finally:
+        shutil.rmtree(shm, ignore_errors=True)
