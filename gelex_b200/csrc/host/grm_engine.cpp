@@ -541,7 +541,7 @@ struct RunContext {
     bool bed_relay;     // 2D-tile mode: one upload per host chunk, peers copy it over NVLink (BedRelay)
     bool prefault;      // create output files ahead of the writers and populate their pages meanwhile (Prefaulter / OutputPreparer);
                         // false when the user forced pwrite.  Independent of `writer`: a populated mapping cannot fault for lack of space
-    bool direct_dma;    // prepared mappings are page-locked and whole-row read-outs DMA straight into them (GELEX_B200_DIRECT_DMA=0: off)
+    bool direct_dma;    // prepared mappings are page-locked and whole-row read-outs DMA straight into them (GELEX_B200_DIRECT_DMA=1; off by default)
     // progress (reference: per work item, counted in SNPs; grm.h:124-130)
     const GrmObserver* observer;
     std::mutex* mu;
@@ -1722,8 +1722,11 @@ void GrmEngine::compute(const GrmObserver& observer) {
         // profiles/r02a_cli_writers.jsonl); GELEX_B200_PREFAULT=0 turns it off
         const char* pf = std::getenv("GELEX_B200_PREFAULT");
         rc.prefault = (pf != nullptr ? pf[0] != '0' : config_.prefault) && rc.writer != WriterMode::Pwrite;  // a forced pwrite stays pwrite
+        // Opt-in (GELEX_B200_DIRECT_DMA=1): measured on the GPU box, page-locking a 5 GB mapping (0.4 s) holds the driver lock
+        // the pushing thread needs - C2 read-out 0.42 -> 0.35 s but accumulate 1.05 -> 1.42 s, C4 17.7 -> 34.9 s
+        // (profiles/r02_summary.md) - so the staged writer stays the default
         const char* dd = std::getenv("GELEX_B200_DIRECT_DMA");
-        rc.direct_dma = rc.prefault && !(dd != nullptr && dd[0] == '0');
+        rc.direct_dma = rc.prefault && dd != nullptr && dd[0] == '1';
     }
     if (rc.writer != WriterMode::Pwrite) {
         // every .bin of the run: one per work item, plus the whole-genome sums of a LOCO run, or the GCTA pair

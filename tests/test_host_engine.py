@@ -721,8 +721,9 @@ def test_engine_gcta_files(tmp_path, monkeypatch):
 
 @pytest.mark.gpu
 def test_engine_direct_dma_into_the_output_mapping_matches_the_staged_writer(tmp_path, monkeypatch):
-    # On tmpfs the populated mapping of an output file is page-locked and whole-row read-outs DMA straight into it (no staging buffer,
-    # no host copy); elsewhere - and with GELEX_B200_DIRECT_DMA=0 - rows go through the writer pool.  Same bytes either way:
+    # With GELEX_B200_DIRECT_DMA=1 (opt-in: measured slower end to end, the page-locking holds the driver lock) the populated mapping
+    # of an output file on tmpfs is page-locked and whole-row read-outs DMA straight into it (no staging buffer, no host copy);
+    # otherwise rows go through the writer pool.  Same bytes either way:
     # whole-genome file, every chromosome file of a LOCO run and its whole (one GPU; two ranks' row slices of the LOCO whole).
     import shutil
     import tempfile
