@@ -120,13 +120,23 @@ void build_ownership_and_items(Handle& h) {
         if (const char* e = std::getenv("GGRM_BAND_MIN_TILES")) min_tiles = std::max<int64_t>(1, std::atoll(e));
         const int bands = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(nb, total / min_tiles)));
         const int items_per_tile = h.tc_mode == 2 ? 1 : 2;
+        int64_t prev_strip_end = 0;  // tile index where the strip before the current one ended
         for (int64_t i = 0; i < total; ++i) {
             const bool strip_ends = i + 1 == total || owned[static_cast<size_t>(i + 1)].I / h.strip_h != owned[static_cast<size_t>(i)].I / h.strip_h;
+            if (!strip_ends) continue;
             const int64_t b = static_cast<int64_t>(h.band_item_end.size());
-            if (strip_ends && (i + 1 == total || (b + 1 < bands && i + 1 >= (b + 1) * total / bands))) {
-                h.band_item_end.push_back(static_cast<int>((i + 1) * items_per_tile));
-                h.band_row_end.push_back(i + 1 == total ? h.n_out : std::min<int64_t>(h.n_out, (owned[static_cast<size_t>(i)].I / h.strip_h + 1) * h.strip_h * kTile));
+            const bool last_strip = i + 1 == total;
+            // the LAST band is what a pipelined read-out cannot hide: when it would hold several strips, the final strip becomes a
+            // band of its own (168 MB instead of 560 MB at n = 50 000)
+            if (last_strip && bands > 1 && prev_strip_end > 0 && (h.band_item_end.empty() || h.band_item_end.back() < prev_strip_end * items_per_tile)) {
+                h.band_item_end.push_back(static_cast<int>(prev_strip_end * items_per_tile));
+                h.band_row_end.push_back(std::min<int64_t>(h.n_out, (owned[static_cast<size_t>(prev_strip_end - 1)].I / h.strip_h + 1) * h.strip_h * kTile));
             }
+            if (last_strip || (b + 1 < bands && i + 1 >= (b + 1) * total / bands)) {
+                h.band_item_end.push_back(static_cast<int>((i + 1) * items_per_tile));
+                h.band_row_end.push_back(last_strip ? h.n_out : std::min<int64_t>(h.n_out, (owned[static_cast<size_t>(i)].I / h.strip_h + 1) * h.strip_h * kTile));
+            }
+            prev_strip_end = i + 1;
         }
         for (size_t b = h.band_done.size(); b < h.band_item_end.size(); ++b) {
             cudaEvent_t ev = nullptr;
@@ -340,6 +350,7 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
     if (const char* e = std::getenv("GGRM_CACHE_HINTS")) h->cache_hints = std::atoi(e) & 7;
     if (const char* e = std::getenv("GGRM_TC_MODE")) h->tc_mode = std::atoi(e) == 1 ? 1 : 2;
     if (const char* e = std::getenv("GGRM_STRIP_H")) h->strip_h = std::max(0, std::atoi(e));
+    if (const char* e = std::getenv("GGRM_FIRST_SLAB")) h->first_slab_snps = std::max<int64_t>(0, std::atoll(e));
 
     // groups
     h->groups.resize(static_cast<size_t>(cfg->n_groups));

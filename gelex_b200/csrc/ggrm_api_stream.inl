@@ -334,7 +334,9 @@ static void copy_rows(Handle& h, const uint8_t* src, bool src_is_device, bool sr
         return;
     }
     if (h.ring[0] == nullptr) {
-        h.ring_bytes = std::max<int64_t>(int64_t{32} << 20, h.bpv_raw);
+        // 4 x 8 MiB: page-locking host memory costs ~0.5 ms per MiB and the driver serialises it across the handles of a multi-GPU
+        // run; the pushing thread's memcpy (~8 GB/s) is the pace setter, so a deeper ring buys nothing
+        h.ring_bytes = std::max<int64_t>(int64_t{8} << 20, h.bpv_raw);
         for (int i = 0; i < Handle::kRingSlots; ++i) {
             GGRM_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&h.ring[i]), static_cast<size_t>(h.ring_bytes), cudaHostAllocDefault));
             GGRM_CUDA(cudaEventCreateWithFlags(&h.ring_free[i], cudaEventDisableTiming));
@@ -401,8 +403,16 @@ static void push_impl(Handle& h, const uint8_t* payload, bool is_device, int64_t
                 int64_t seg_end = h.groups[g].end;
                 if (h.push_end_hint > s) seg_end = std::min(seg_end, h.push_end_hint);  // SNP shard: the caller stops before the group does
                 const int64_t rest = seg_end - s;
-                const int64_t pieces = (rest + h.k_cap - 1) / h.k_cap;
+                int64_t pieces = (rest + h.k_cap - 1) / h.k_cap;
                 h.cur_cap = std::min<int64_t>(h.k_cap, round_up((rest + pieces - 1) / pieces, 64));
+                // The first slab of a pass is short: the tensor cores wait for its upload and its K1-K3 (8.5 + 0.5 ms for a
+                // 15 600-SNP slab at 23 GB/s per rank on the 8-GPU box), so they get 4 096 SNPs to start on while the first
+                // full slab is still arriving.  It stores instead of accumulating, so it costs one launch and no extra accumulator read.
+                if (!h.first_slab_done && !h.fp64 && h.ksplit == 1 && h.first_slab_snps > 0 && rest > h.k_cap) {  // (few-tile problems are launch-bound: no extra slab)
+                    h.cur_cap = std::min<int64_t>(h.cur_cap, round_up(h.first_slab_snps, 64));
+                    pieces = 1 + (rest - h.cur_cap + h.k_cap - 1) / h.k_cap;
+                }
+                h.first_slab_done = true;
                 // the last tail_slabs slabs of the pass are parked and accumulated band-major at finish
                 h.cur_trailing = h.tail_slabs > 0 && g + 1 == static_cast<int>(h.groups.size()) && pieces <= h.tail_slabs;
             }
@@ -505,6 +515,7 @@ static void reset_impl(Handle& h) {
     h.last_snp_pushed = -1;
     h.finished = false;
     h.pass_open = false;
+    h.first_slab_done = false;
 }
 
 }  // namespace ggrm

@@ -267,6 +267,21 @@ bool prefault_completed_ok(Prefaulter* p, bool* pinned) {
 
 struct Segment { int64_t src_elem, file_byte, bytes; };  // buffer elements [src_elem, +bytes/4) -> file bytes [file_byte, +bytes)
 
+class WriterPool;
+// A pool that comes into being at its first use: its page-locked buffers (6 x 16 MB; ~0.5 ms per MB, serialised by the driver across
+// the GPU threads of one process) are then allocated while the GPUs accumulate, not in front of the first push.
+class LazyPool {
+   public:
+    LazyPool(int threads, int buffers, int64_t buffer_elems) : threads_(threads), buffers_(buffers), elems_(buffer_elems) {}
+    WriterPool& get();
+    WriterPool* peek() { return pool_.get(); }
+
+   private:
+    int threads_, buffers_;
+    int64_t elems_;
+    std::unique_ptr<WriterPool> pool_;
+};
+
 class WriterPool {
    public:
     WriterPool(int threads, int buffers, int64_t buffer_elems) : elems_(buffer_elems) {
@@ -369,6 +384,11 @@ class WriterPool {
     bool stop_ = false, failed_ = false;
     double busy_s_ = 0;
 };
+
+WriterPool& LazyPool::get() {
+    if (!pool_) pool_ = std::make_unique<WriterPool>(threads_, buffers_, elems_);
+    return *pool_;
+}
 
 inline int64_t tri(int64_t i) { return i * (i + 1) / 2; }
 
@@ -956,7 +976,7 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
     HandleGuard hg;
     const auto t_setup = Clock::now();
     hg.h = create_handle(rc, device, my_groups, keep_whole, tile_rank, tile_world);
-    WriterPool pool(rc.cfg->writer_threads, rc.cfg->writer_threads + 2, std::max<int64_t>(kWriterBufferElems, rc.n_out));
+    LazyPool lazy_pool(rc.cfg->writer_threads, rc.cfg->writer_threads + 2, std::max<int64_t>(kWriterBufferElems, rc.n_out));
     const auto t_push = Clock::now();
     note_phase(rc, "device setup", t_setup, t_push);
     int pending = -1;  // local index of a group that is complete on the device but not yet written
@@ -996,7 +1016,7 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
         const int pi = prep_index[slot];
         if (preparer && pi >= 0) p.precreated = preparer->wait_ready(static_cast<size_t>(pi));
         try {
-            write_outputs(rc, hg.h, local_group, suffix, p, pool);
+            write_outputs(rc, hg.h, local_group, suffix, p, lazy_pool.get());
         } catch (...) {
             if (preparer && pi >= 0) preparer->done(static_cast<size_t>(pi));
             throw;
@@ -1025,7 +1045,7 @@ void run_groups_on_device(const RunContext& rc, int device, const std::vector<in
     const auto t_readout = Clock::now();
     note_phase(rc, "push", t_push, t_readout);
     if (rc.loco && pending >= 0 && !superseded(pending)) write_entry(pending, group_name(pending), static_cast<size_t>(pending));
-    if (whole_here) write_outputs(rc, hg.h, GGRM_GROUP_WHOLE, "", part, pool);
+    if (whole_here) write_outputs(rc, hg.h, GGRM_GROUP_WHOLE, "", part, lazy_pool.get());
     check(hg.h, ggrm_finish(hg.h));
     note_timers(rc, hg.h, pass_ms, syrk_ms);
     if (rc.loco && keep_whole && (write_whole_here || part.kind == WritePart::OwnedTiles)) write_entry(GGRM_GROUP_WHOLE, "", my_groups.size());
@@ -1142,7 +1162,7 @@ void run_pipelined_rank(const RunContext& rc, ShardPipe& sp, size_t r, double* p
     const auto nb = static_cast<size_t>(sp.n_bands);
     check(h, ggrm_set_band_flags(h, sp.flags.data() + r * nb, 1));
     check(h, ggrm_set_push_end(h, sp.snps[r].second));  // equal slabs inside the shard
-    WriterPool pool(rc.cfg->writer_threads, rc.cfg->writer_threads + 2, std::max<int64_t>(kWriterBufferElems, rc.n_out));
+    LazyPool lazy_pool(rc.cfg->writer_threads, rc.cfg->writer_threads + 2, std::max<int64_t>(kWriterBufferElems, rc.n_out));
     BinFile files[2];
     int64_t done = 0;
     const auto t_push = Clock::now();
@@ -1150,6 +1170,7 @@ void run_pipelined_rank(const RunContext& rc, ShardPipe& sp, size_t r, double* p
     check(h, ggrm_finish_async(h));
     const auto t0 = Clock::now();
     note_phase(rc, "push", t_push, t0);
+    WriterPool& pool = lazy_pool.get();  // page-locked buffers allocated now, under the accumulation
     // opened only now: a file whose pages are being populated (Prefaulter) is opened when that has finished, which must not hold
     // up the pushes - the whole pass is in front of the first write
     for (int kind = 0; kind < 2; ++kind)
