@@ -413,8 +413,14 @@ static void push_impl(Handle& h, const uint8_t* payload, bool is_device, int64_t
                     pieces = 1 + (rest - h.cur_cap + h.k_cap - 1) / h.k_cap;
                 }
                 h.first_slab_done = true;
+                ++h.slabs_started;
                 // the last tail_slabs slabs of the pass are parked and accumulated band-major at finish
-                h.cur_trailing = h.tail_slabs > 0 && g + 1 == static_cast<int>(h.groups.size()) && pieces <= h.tail_slabs;
+                // ... but never more than half of the pass: parked slabs are not accumulated before the last push, and a short pass
+                // (an SNP shard of 8 GPUs is 5 slabs) would leave the tensor cores idle for its whole upload - 34 ms of H2D in front
+                // of 112 ms of SYRK at N = 8
+                const int64_t pass_slabs = h.slabs_started - 1 + pieces;
+                const int64_t tail = std::min<int64_t>(h.tail_slabs, std::max<int64_t>(1, pass_slabs / 2));
+                h.cur_trailing = h.tail_slabs > 0 && g + 1 == static_cast<int>(h.groups.size()) && pieces <= tail;
             }
             const int64_t take = std::min(run_end - s, h.cur_cap - h.cur_count);
             copy_rows(h, payload + (s - snp_begin) * h.bpv_raw, is_device, pinned, take, h.d_raw[h.cur_buf] + h.cur_count * h.bpv_raw);
@@ -516,6 +522,7 @@ static void reset_impl(Handle& h) {
     h.finished = false;
     h.pass_open = false;
     h.first_slab_done = false;
+    h.slabs_started = 0;
 }
 
 }  // namespace ggrm
