@@ -2,7 +2,7 @@
 # (shortened SNP axis, operand split forced off so that the launches are the ones the 500 000-SNP bench makes).
 set -x
 mkdir -p gpurun_out
-timeout 1200 python -m pytest tests -m gpu -q > gpurun_out/r02z_pytest.log 2>&1; echo rc=$?; tail -4 gpurun_out/r02z_pytest.log
+timeout 1200 python -m pytest tests -m gpu -q -x > gpurun_out/r02z_pytest.log 2>&1; echo rc=$?; tail -4 gpurun_out/r02z_pytest.log
 timeout 60 python -c "import __graft_entry__ as e; e.smoke()" > gpurun_out/r02z_smoke.log 2>&1; echo rc=$?; cat gpurun_out/r02z_smoke.log
 timeout 400 python bench.py --gpus 1 --steps 3 --warmup 3 > gpurun_out/r02z_bench_n1.json 2> gpurun_out/r02z_bench_n1.err; echo rc=$?; cat gpurun_out/r02z_bench_n1.json
 timeout 300 python bench.py --impl reference --gpus 1 --steps 3 --warmup 1 > gpurun_out/r02z_reference_arm.json 2> gpurun_out/r02z_reference_arm.err; echo rc=$?; cat gpurun_out/r02z_reference_arm.json
