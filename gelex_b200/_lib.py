@@ -71,6 +71,7 @@ EXPORTS = [
     "ggrm_band_layout", "ggrm_set_band_flags", "ggrm_reduce_rows_async", "ggrm_genotype_chunk", "ggrm_fetch_gcta", "ggrm_accum_address",
     "ggrm_stage_create", "ggrm_stage_destroy", "ggrm_stage_upload", "ggrm_stage_slot", "ggrm_wait_copies",
     "ggrm_warm_device", "ggrm_reduce_block_async", "ggrm_host_register", "ggrm_host_unregister",
+    "ggrm_snp_stats_noalloc",
 ]
 
 _lib = None
@@ -134,6 +135,7 @@ def load() -> C.CDLL:
     lib.ggrm_warm_device.argtypes = [C.c_int]
     lib.ggrm_host_register.argtypes = [vp, i64]
     lib.ggrm_host_unregister.argtypes = [vp]
+    lib.ggrm_snp_stats_noalloc.argtypes = [C.c_int, vp, i64, i64, i64, vp, vp, vp]
     lib.ggrm_reduce_block_async.argtypes = [vp, C.c_int, C.c_int, C.POINTER(vp), C.c_int, i64, i64, i64]
     lib.ggrm_device_count.argtypes = []
     lib.ggrm_version.argtypes = []
@@ -417,6 +419,19 @@ def genotype_chunk(payload, n_raw, method, kind, n_out=None, raw_to_out=None, de
     if st != 0:
         raise GrmError(st, lib.ggrm_last_error(None).decode())
     return out.T, {"freq": freq, "mean": mean, "stddev": sd, "mono": mono.astype(bool)}
+
+
+NOALLOC_SCRATCH_BYTES = 8 * 1024 * 1024  # GGRM_NOALLOC_SCRATCH_BYTES
+
+
+def snp_stats_noalloc(dev_bed_ptr: int, snp_count: int, n_raw: int, dev_counts4_ptr: int | None, dev_freq_ptr: int | None, device=0, stream=None):
+    """ggrm_snp_stats_noalloc: device pointers in and out, kernels only enqueued on `stream` (None = default); allocates nothing."""
+    lib = load()
+    st = lib.ggrm_snp_stats_noalloc(device, C.c_void_p(dev_bed_ptr), snp_count, (n_raw + 3) // 4, n_raw,
+                                    C.c_void_p(dev_counts4_ptr) if dev_counts4_ptr else None, C.c_void_p(dev_freq_ptr) if dev_freq_ptr else None,
+                                    C.c_void_p(stream) if stream else None)
+    if st != 0:
+        raise GrmError(st, lib.ggrm_last_error(None).decode())
 
 
 def synth_bed_host(n, snp_begin, snp_count, seed, missing_rate=0.01):

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <numeric>
 
@@ -613,3 +614,4 @@ extern "C" const char* ggrm_version(void) { return "gelex-grm-b200 0.1 (sm_100a;
 #include "ggrm_api_fetch.inl"
 #include "ggrm_api_hooks.inl"
 #include "ggrm_api_stage.inl"
+#include "ggrm_api_noalloc.inl"

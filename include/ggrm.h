@@ -306,6 +306,25 @@ int ggrm_stage_upload(ggrm_stage_t* s, int slot, const uint8_t* host_src, int64_
 int ggrm_stage_slot(ggrm_stage_t* s, int slot, const uint8_t** d_ptr);
 int ggrm_wait_copies(ggrm_t* h);
 
+/* ---- An entry point that allocates nothing ------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Per-SNP genotype counts and A1 allele frequency - the values of ggrm_snp_stats, bit for bit - for `snp_count` packed BED rows
+ * that are ALREADY in device memory of `device`, identity projection (n_out == n_raw), written to DEVICE memory:
+ *   d_counts4  [snp_count][4] int32 = {n0, n1, n2 (= #A1A1), nmiss} per SNP, 16-byte aligned; may be NULL
+ *   d_freq     [snp_count] double; may be NULL (not both)
+ *   stream     a cudaStream_t passed as a plain pointer, NULL = the default stream.  The two kernels are only ENQUEUED: the
+ *              caller synchronises the stream before reading the outputs.
+ * It calls no cudaMalloc / cudaFree or any other allocating routine.  The one intermediate of the computation (the chunk
+ * repacked to 256-sample padding) lives in a static device array of GGRM_NOALLOC_SCRATCH_BYTES that every GPU loading this
+ * library holds until the process exits; a call that needs more - snp_count * (round_up(n_raw, 256) / 4) bytes - is rejected
+ * with GGRM_ERR_INVALID_ARGUMENT and a message naming the limit (ggrm_last_error(NULL)): split the chunk.  At 50 000 samples
+ * that is 668 SNPs per call.  All calls on one device share that array: calls that overlap on the GPU (different streams or
+ * host threads) race on it - issue them on one stream, or serialise them.  Nothing in it has to be cleared between calls. */
+#define GGRM_NOALLOC_SCRATCH_BYTES (8 * 1024 * 1024)
+int ggrm_snp_stats_noalloc(int device, const uint8_t* d_bed_payload, int64_t snp_count, int64_t bytes_per_variant, int64_t n_raw,
+                           int32_t* d_counts4, double* d_freq, void* stream);
+
 /* Start-up overlap for hosts: creates the CUDA context of `device` and loads this library's kernels (0.3-0.5 s on a cold
  * process) so that a host can do it on a helper thread while it parses FAM / BIM metadata, as the C++ GrmEngine does
  * (the reference has nothing comparable: its start-up is the BedPipe / SampleManager construction, grm.cpp:36-40).
