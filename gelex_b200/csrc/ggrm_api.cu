@@ -174,6 +174,10 @@ void build_ownership_and_items(Handle& h) {
         // from the tile count of the WHOLE triangle, not of this handle's share: every 2D-tile rank then cuts K exactly like the
         // single-GPU run does, and a tile's bits do not depend on who owns it
         int want = static_cast<int>(std::min<int64_t>(8, (h.sm_count / 2) / std::max<int64_t>(1, T * (T + 1) / 2)));
+        // Few-tile problems are launch-bound (measured at C1: every extra slab costs a ~40 us gap, profiles/r02_summary.md section 3), so
+        // they take slabs of up to 65 536 SNPs - C1 is ONE launch - and enough K parts that one TMEM accumulation chain stays within
+        // 16 384 SNPs (the FP32 truncation bias of a chain grows with its length, see create_impl)
+        if (want > 1) want = static_cast<int>(std::min<int64_t>(8, std::max<int64_t>(want, (std::min<int64_t>(round_up(h.cfg.m_total, 64), 65536) + 16383) / 16384)));
         if (const char* e = std::getenv("GGRM_KSPLIT")) want = std::max(1, std::min(8, std::atoi(e)));
         const bool keeps_whole = h.cfg.n_groups > 1 && h.cfg.keep_whole;  // the in-epilogue fold into `whole` assumes one copy
         if (want > 1 && !keeps_whole && h.band_item_end.size() <= 1) {
@@ -352,6 +356,7 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
     if (const char* e = std::getenv("GGRM_TC_MODE")) h->tc_mode = std::atoi(e) == 1 ? 1 : 2;
     if (const char* e = std::getenv("GGRM_STRIP_H")) h->strip_h = std::max(0, std::atoi(e));
     if (const char* e = std::getenv("GGRM_FIRST_SLAB")) h->first_slab_snps = std::max<int64_t>(0, std::atoll(e));
+    if (const char* e = std::getenv("GGRM_FIRST_SLAB_SPLIT")) h->first_slab_with_split = std::atoi(e) != 0;
 
     // groups
     h->groups.resize(static_cast<size_t>(cfg->n_groups));

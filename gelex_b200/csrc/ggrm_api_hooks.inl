@@ -40,7 +40,7 @@ static void decode_common(int device, const uint8_t* payload, int64_t snp_count,
         GGRM_CUDA(cudaMemcpy(d_inv, inv.data(), inv.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
     }
     GGRM_CUDA(cudaMemcpy(d_raw, payload, static_cast<size_t>(snp_count * bpv), cudaMemcpyHostToDevice));
-    repack_kernel<<<static_cast<unsigned>(snp_count), 256>>>(d_raw, bpv, d_dense, bpv_pad, n_out, d_inv, snp_count);
+    repack_kernel<<<repack_grid(snp_count, bpv_pad), 256>>>(d_raw, bpv, d_dense, bpv_pad, n_out, d_inv, snp_count);
     GGRM_CUDA(cudaGetLastError());
     SnpTable* d_tab = nullptr;
     double* d_freq = nullptr;

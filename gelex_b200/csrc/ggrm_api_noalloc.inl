@@ -58,7 +58,7 @@ extern "C" int ggrm_snp_stats_noalloc(int device, const uint8_t* d_bed_payload, 
                             " SNPs per call at this sample count"};
     uint8_t* scratch = noalloc_scratch_for(device);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    repack_kernel<<<static_cast<unsigned>(snp_count), 256, 0, s>>>(d_bed_payload, bytes_per_variant, scratch, bpv_pad, n_raw, nullptr, snp_count);
+    repack_kernel<<<repack_grid(snp_count, bpv_pad), 256, 0, s>>>(d_bed_payload, bytes_per_variant, scratch, bpv_pad, n_raw, nullptr, snp_count);
     GGRM_CUDA(cudaGetLastError());
     StatsOut so{};  // no value tables: counts and frequency only
     so.counts = reinterpret_cast<int4*>(d_counts4);

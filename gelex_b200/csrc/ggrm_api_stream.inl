@@ -90,11 +90,9 @@ static void complete_group(Handle& h, int g) {
         if (!gs.split_touched[kind] || gs.buffer[kind] < 0) continue;
         float* base = static_cast<float*>(h.pool[kind][gs.buffer[kind]]);
         const int blocks = static_cast<int>(std::min<int64_t>((h.accum_elems / 4 + 255) / 256, h.sm_count * 8));
-        for (int p = 1; p < h.ksplit; ++p) {
-            axpy_accum_kernel<float><<<blocks, 256, 0, h.s_comp>>>(base, base + static_cast<int64_t>(p) * h.accum_elems, h.accum_elems);
-            GGRM_CUDA(cudaGetLastError());
-            ++h.kernel_launches;
-        }
+        sum_copies_kernel<<<blocks, 256, 0, h.s_comp>>>(base, h.accum_elems, h.ksplit);
+        GGRM_CUDA(cudaGetLastError());
+        ++h.kernel_launches;
         gs.split_touched[kind] = false;
     }
     if (gs.started && !gs.folded) {
@@ -254,7 +252,7 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
     start_group(h, g, h.fp64);
 
     size_t ti = phase_begin(h, sp, 1);
-    repack_kernel<<<static_cast<unsigned>(c), 256, 0, sp>>>(h.d_raw[b], h.bpv_raw, h.d_dense, h.bpv_pad, h.n_out, h.d_out_to_raw, c);
+    repack_kernel<<<repack_grid(c, h.bpv_pad), 256, 0, sp>>>(h.d_raw[b], h.bpv_raw, h.d_dense, h.bpv_pad, h.n_out, h.d_out_to_raw, c);
     GGRM_CUDA(cudaGetLastError());
     GGRM_CUDA(cudaEventRecord(h.raw_free[b], sp));
     StatsOut so{};
@@ -408,7 +406,7 @@ static void push_impl(Handle& h, const uint8_t* payload, bool is_device, int64_t
                 // The first slab of a pass is short: the tensor cores wait for its upload and its K1-K3 (8.5 + 0.5 ms for a
                 // 15 600-SNP slab at 23 GB/s per rank on the 8-GPU box), so they get 4 096 SNPs to start on while the first
                 // full slab is still arriving.  It stores instead of accumulating, so it costs one launch and no extra accumulator read.
-                if (!h.first_slab_done && !h.fp64 && h.ksplit == 1 && h.first_slab_snps > 0 && rest > h.k_cap) {  // (few-tile problems are launch-bound: no extra slab)
+                if (!h.first_slab_done && !h.fp64 && (h.ksplit == 1 || h.first_slab_with_split) && h.first_slab_snps > 0 && rest > h.k_cap) {  // (few-tile problems are launch-bound: no extra slab unless asked, GGRM_FIRST_SLAB_SPLIT)
                     h.cur_cap = std::min<int64_t>(h.cur_cap, round_up(h.first_slab_snps, 64));
                     pieces = 1 + (rest - h.cur_cap + h.k_cap - 1) / h.k_cap;
                 }

@@ -122,6 +122,7 @@ struct Handle {
     bool cur_trailing = false;                                     // the slab being filled is one of the last tail_slabs of the pass
     bool first_slab_done = false;                                  // this pass has started its first slab (see push_impl)
     int64_t slabs_started = 0;                                     // slabs begun in this pass (bounds the parked tail, see push_impl)
+    bool first_slab_with_split = false;                            // GGRM_FIRST_SLAB_SPLIT=1: short first slab for few-tile (split-K) problems too
     int64_t first_slab_snps = 4096;                                // GGRM_FIRST_SLAB (0 = off)
     int64_t push_end_hint = -1;                                    // ggrm_set_push_end: no SNP >= this will be pushed (-1: the last group's end)
     int z_buf = 0;

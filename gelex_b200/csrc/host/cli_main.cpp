@@ -35,7 +35,7 @@ struct Logger {
 
 const char* kUsage =
     "Usage: gelex-b200 grm [--help] --bfile <BFILE> [--out <OUT>] [--geno-method <STR>] [--chunk-size <SIZE>]\n"
-    "                      [--threads <N>] [--add] [--dom] [--loco] [--gpus <N>] [--precision <fp16|bf16|fp64>]\n"
+    "                      [--threads <N>] [--add] [--dom] [--loco] [--gpus <N>] [--gpus-exact] [--precision <fp16|bf16|fp64>]\n"
     "                      [--partition <auto|snp|tile>] [--writer-threads <N>] [--writer <auto|pwrite|mmap>]\n"
     "                      [--no-prefault] [--bed-relay] [--with-whole] [--skip-all-missing] [--gcta]\n\n"
     "Compute genomic relationship matrix (GRM) from PLINK binary files and output in GCTA format\n\n"
@@ -51,7 +51,8 @@ const char* kUsage =
     "  --dom                      Compute dominance GRM\n"
     "  --loco                     Compute GRM for each chromosome\n\n"
     "B200 engine options:\n"
-    "  --gpus <N>                 Number of GPUs of this node to use [default: 1]\n"
+    "  --gpus <N>                 Use up to N GPUs of this node: as many as the problem size pays for [default: 1]\n"
+    "  --gpus-exact               Use exactly the N GPUs of --gpus\n"
     "  --precision <P>            fp16 (default) | bf16 : 16-bit operands, FP32 accumulate on tcgen05; fp64 : DMMA\n"
     "  --partition <auto|snp|tile> Multi-GPU split: SNP shards + one reduce-scatter, or 2D output tiles (auto: tile from 100k samples)\n"
     "  --writer-threads <N>       writer threads per GPU draining the read-out ring [default: 4]\n"
@@ -69,7 +70,7 @@ int run_grm(int argc, char** argv, Logger& log) {
     std::string bfile, out = "grm", gm = "OSH", precision = "fp16", partition = "auto", writer = "auto";
     int chunk = 10000, gpus = 1, writer_threads = 4;
     int threads = static_cast<int>(std::thread::hardware_concurrency() / 2);
-    bool add = false, dom = false, loco = false, with_whole = false, skip_missing = false, gcta = false, bed_relay = false, prefault = true;
+    bool add = false, dom = false, loco = false, with_whole = false, skip_missing = false, gcta = false, bed_relay = false, prefault = true, gpus_exact = false;
     auto need = [&](int& i) -> std::string {
         if (i + 1 >= argc) throw ArgumentValidationException(std::string("Too few arguments for '") + argv[i] + "'.");
         return argv[++i];
@@ -96,6 +97,7 @@ int run_grm(int argc, char** argv, Logger& log) {
         else if (a == "--dom") dom = true;
         else if (a == "--loco") loco = true;
         else if (a == "--gpus") gpus = to_int(need(i), "--gpus");
+        else if (a == "--gpus-exact") gpus_exact = true;
         else if (a == "--precision") precision = need(i);
         else if (a == "--partition") partition = need(i);
         else if (a == "--writer-threads") writer_threads = to_int(need(i), "--writer-threads");
@@ -124,6 +126,19 @@ int run_grm(int argc, char** argv, Logger& log) {
     else if (precision == "fp64") cfg.precision = GGRM_PREC_FP64;
     else throw ArgumentValidationException("--precision must be fp16, bf16 or fp64");
     if (gpus < 1) throw ArgumentValidationException("--gpus must be >= 1");
+    // --gpus is an upper bound: a one-shot process pays ~0.3 s of context creation per GPU, which a small problem never earns back
+    // (GrmEngine::gpus_worth_using).  Metadata errors are left to the engine, which reports them in the reference's order.
+    const int gpus_offered = gpus;
+    if (gpus > 1 && !gpus_exact) {
+        try {
+            std::filesystem::path fam = cfg.bed_path, bim = cfg.bed_path;
+            fam.replace_extension(".fam");
+            bim.replace_extension(".bim");
+            const auto n = static_cast<int64_t>(count_total_lines(fam)), m = static_cast<int64_t>(count_total_lines(bim));
+            gpus = GrmEngine::gpus_worth_using(n, m, cfg.mode == GrmType::AD ? 2 : 1, cfg.precision, gpus);
+        } catch (const std::exception&) {
+        }
+    }
     cfg.gpus.clear();
     for (int g = 0; g < gpus; ++g) cfg.gpus.push_back(g);
     if (partition == "auto") cfg.partition = Partition::Auto;
@@ -156,7 +171,9 @@ int run_grm(int argc, char** argv, Logger& log) {
     log.info(std::string("  Method      : ") + method_name(cfg.method));
     log.info("  Mode        : " + mode_name(cfg.mode));
     log.info(std::string("  LOCO        : ") + (loco ? "yes" : "no"));
-    log.info("  Engine      : " + std::to_string(gpus) + " GPU(s), " + precision + " operands");
+    log.info("  Engine      : " + std::to_string(gpus) + " GPU(s)" +
+             (gpus < gpus_offered ? " of the " + std::to_string(gpus_offered) + " offered (more would cost more start-up than they save; --gpus-exact overrides)" : std::string()) +
+             ", " + precision + " operands");
     log.info("");
 
     const bool tty = ::isatty(fileno(stderr)) != 0;

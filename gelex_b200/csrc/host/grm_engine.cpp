@@ -4,6 +4,7 @@
 #include <atomic>
 #include <cctype>
 #include <chrono>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <exception>
@@ -1494,6 +1495,19 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
 }
 
 }  // namespace
+
+int GrmEngine::gpus_worth_using(int64_t n, int64_t m, int kinds, int precision, int offered) {
+    if (offered <= 1 || n <= 0 || m <= 0) return std::max(1, offered);
+    constexpr double kContextSeconds = 0.30;
+    const double rate = precision == GGRM_PREC_FP64 ? 3.0e13 : 1.3e15;
+    const double t1 = static_cast<double>(n) * (static_cast<double>(n) + 1.0) * static_cast<double>(m) * std::max(1, kinds) / rate;
+    int k = 1;
+    while (k < offered && t1 / (static_cast<double>(k + 1) * k) >= kContextSeconds) ++k;
+    // ... and never fewer than the FP32 (FP64: double) triangle needs: n^2 / 2 entries per matrix, ~120 GB of a B200 for accumulators
+    const double acc_bytes = 0.5 * static_cast<double>(n) * static_cast<double>(n) * (precision == GGRM_PREC_FP64 ? 8.0 : 4.0) * std::max(1, kinds);
+    const int floor_k = static_cast<int>(std::ceil(acc_bytes / 120e9));
+    return std::min(offered, std::max(k, floor_k));
+}
 
 std::vector<std::pair<int64_t, int64_t>> GrmEngine::row_slices_for(int64_t n, int parts) { return row_slices(n, parts); }
 

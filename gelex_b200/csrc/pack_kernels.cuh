@@ -171,6 +171,20 @@ __global__ void __launch_bounds__(256) axpy_accum_kernel(T* __restrict__ dst, co
     }
 }
 
+// Split-K launches (few-tile problems, Handle::ksplit): copy 0 += copy 1 + ... + copy (parts - 1), summed in that fixed order, in
+// ONE pass (parts reads + one write per element; separate axpy launches cost ~8 us each, which shows at C1's 0.3 ms pass).
+__global__ void __launch_bounds__(256) sum_copies_kernel(float* __restrict__ base, int64_t copy_elems, int parts) {
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x * 4;
+    for (int64_t i = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 4; i < copy_elems; i += stride) {
+        float4 a = *reinterpret_cast<const float4*>(base + i);
+        for (int p = 1; p < parts; ++p) {
+            const float4 b = *reinterpret_cast<const float4*>(base + static_cast<int64_t>(p) * copy_elems + i);
+            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+        }
+        *reinterpret_cast<float4*>(base + i) = a;
+    }
+}
+
 // Consumer side of the .bin format: packed float32 lower rows of one or two files already on the device ->
 // the dense symmetric FP64 matrix GrmLoader / LocoGRMLoader hand to the solvers (src/data/grm/grm_loader.cpp:125-243,
 // loco_grm_loader.cpp:62-76):  out(i, j) = (W(fw(i), fw(j)) - C(fc(i), fc(j))) / denom, fw / fc = target row -> row of that file

@@ -25,17 +25,18 @@ constexpr uint8_t kAllMissingByte = 0x55;  // four BED "01" codes
 // K1a: repack.  raw [c][bpv_raw] -> dense [c][bpv_pad] in GRM row order; rows >= n_out are BED 01 (missing) so that
 // every later kernel can treat padding exactly like a missing call (contributes 0 after mean imputation).
 // out_to_raw == nullptr means identity (the reference's dense path, sample_projection.cpp:51-54).
-// One block per SNP row; a thread produces 4 output bytes (16 samples) per iteration.
+// A thread produces 4 output bytes (16 samples) per iteration; threads walk the chunk's output words (snp, word) in one flat
+// grid-stride sequence, so short rows (n = 2 000: 128 words) fill their blocks as well as long ones.
 __global__ void __launch_bounds__(256) repack_kernel(const uint8_t* __restrict__ raw, int64_t bpv_raw,
                                                      uint8_t* __restrict__ dense, int64_t bpv_pad, int64_t n_out,
                                                      const int32_t* __restrict__ out_to_raw, int64_t snp_count) {
-    const int64_t snp = blockIdx.x;
-    if (snp >= snp_count) return;
-    const uint8_t* src = raw + snp * bpv_raw;
-    uint32_t* dst = reinterpret_cast<uint32_t*>(dense + snp * bpv_pad);
     const int64_t words = bpv_pad / 4;
     const bool words_aligned = ((bpv_raw & 3) == 0) && ((reinterpret_cast<uintptr_t>(raw) & 3) == 0);
-    for (int64_t w = threadIdx.x; w < words; w += blockDim.x) {
+    const int64_t total = snp_count * words;
+    for (int64_t idx = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total; idx += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int64_t snp = idx / words, w = idx - snp * words;
+        const uint8_t* src = raw + snp * bpv_raw;
+        uint32_t* dst = reinterpret_cast<uint32_t*>(dense + snp * bpv_pad);
         uint32_t out = 0;
         const int64_t s0 = w * 16;
         if (out_to_raw == nullptr && words_aligned && s0 + 16 <= n_out) {
@@ -70,6 +71,13 @@ __global__ void __launch_bounds__(256) repack_kernel(const uint8_t* __restrict__
         }
         dst[w] = out;
     }
+}
+
+// blocks for a chunk of snp_count rows: enough 256-thread blocks to cover every output word once, capped (grid-stride beyond)
+inline unsigned repack_grid(int64_t snp_count, int64_t bpv_pad) {
+    const int64_t total = snp_count * (bpv_pad / 4);
+    const int64_t blocks = (total + 255) / 256;
+    return static_cast<unsigned>(blocks < 1 ? 1 : (blocks > 148 * 64 ? 148 * 64 : blocks));
 }
 
 // ------------------------------------------------------------------------------------------------------------------

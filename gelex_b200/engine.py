@@ -39,6 +39,7 @@ def load_host():
         h.gelex_b200_grm_load.restype = C.c_int64
         h.gelex_b200_row_slices.argtypes = [C.c_int64, C.c_int, C.c_void_p]
         h.gelex_b200_strip_owners.argtypes = [C.c_int64, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        h.gelex_b200_gpus_worth_using.argtypes = [C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int]
         h.gelex_b200_piece_owners.argtypes = [C.c_int64, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
         h.gelex_b200_grm_run_gcta.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]
         vp = C.c_void_p
@@ -246,6 +247,11 @@ def strip_owners(n, world, bands):
         r, b, lo, hi = (int(v) for v in out[4 * i:4 * i + 4])
         per[r].append((b, lo, hi))
     return per
+
+
+def gpus_worth_using(n, m, kinds=1, precision=_lib.PREC_FP16, offered=8):
+    """How many of `offered` GPUs the CLI uses for an n x m problem (GrmEngine::gpus_worth_using)."""
+    return int(load_host().gelex_b200_gpus_worth_using(int(n), int(m), int(kinds), int(precision), int(offered)))
 
 
 def piece_owners(n, world, bands):
