@@ -284,6 +284,10 @@ def parse_cli_report(stdout):
             mm = re.search(r"accumulate ([\d.]+) ms \(SYRK ([\d.]+) ms\), read-out \+ file write ([\d.]+) s, engine wall ([\d.]+) s", ln)
             if mm:
                 rep.update(accumulate_s=float(mm.group(1)) / 1e3, syrk_s=float(mm.group(2)) / 1e3, write_s=float(mm.group(3)), engine_wall_s=float(mm.group(4)))
+        elif "Engine      :" in ln:
+            mm = re.search(r"Engine      : (\d+) GPU\(s\)(?: of the (\d+) offered)?", ln)
+            if mm:
+                rep.update(gpus_used=int(mm.group(1)), gpus_offered=int(mm.group(2) or mm.group(1)))
         elif "Host phases :" in ln:
             ph = {}
             for part in ln.split(":", 1)[1].split("|"):
