@@ -275,8 +275,8 @@ extern "C" int gelex_b200_strip_owners(int64_t n, int world, const int64_t* band
     return static_cast<int>(strips.size());
 }
 
-extern "C" int gelex_b200_gpus_worth_using(int64_t n, int64_t m, int kinds, int precision, int offered) {
-    return GrmEngine::gpus_worth_using(n, m, kinds, precision, offered);
+extern "C" int gelex_b200_gpus_worth_using(int64_t n, int64_t m, int kinds, int precision, int offered, int n_outputs) {
+    return GrmEngine::gpus_worth_using(n, m, kinds, precision, offered, n_outputs);
 }
 
 extern "C" int gelex_b200_piece_owners(int64_t n, int world, const int64_t* band_row_end, int n_bands, int64_t* out5, int cap) {

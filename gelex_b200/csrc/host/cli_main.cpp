@@ -126,7 +126,7 @@ int run_grm(int argc, char** argv, Logger& log) {
     else if (precision == "fp64") cfg.precision = GGRM_PREC_FP64;
     else throw ArgumentValidationException("--precision must be fp16, bf16 or fp64");
     if (gpus < 1) throw ArgumentValidationException("--gpus must be >= 1");
-    // --gpus is an upper bound: a one-shot process pays ~0.3 s of context creation per GPU, which a small problem never earns back
+    // --gpus is an upper bound: a one-shot process pays ~0.3 s of context creation per GPU and ~0.4 s for going multi-GPU at all, which a small problem never earns back
     // (GrmEngine::gpus_worth_using).  Metadata errors are left to the engine, which reports them in the reference's order.
     const int gpus_offered = gpus;
     if (gpus > 1 && !gpus_exact) {
@@ -135,7 +135,8 @@ int run_grm(int argc, char** argv, Logger& log) {
             fam.replace_extension(".fam");
             bim.replace_extension(".bim");
             const auto n = static_cast<int64_t>(count_total_lines(fam)), m = static_cast<int64_t>(count_total_lines(bim));
-            gpus = GrmEngine::gpus_worth_using(n, m, cfg.mode == GrmType::AD ? 2 : 1, cfg.precision, gpus);
+            const int kinds = cfg.mode == GrmType::AD ? 2 : 1;
+            gpus = GrmEngine::gpus_worth_using(n, m, kinds, cfg.precision, gpus, kinds * (loco ? 22 : 1));  // (22: an estimate; the BIM is parsed later)
         } catch (const std::exception&) {
         }
     }

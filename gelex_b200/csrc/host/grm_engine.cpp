@@ -1496,17 +1496,29 @@ void run_multi_gpu(const RunContext& rc, bool tile_mode, double* pass_ms, double
 
 }  // namespace
 
-int GrmEngine::gpus_worth_using(int64_t n, int64_t m, int kinds, int precision, int offered) {
+int GrmEngine::gpus_worth_using(int64_t n, int64_t m, int kinds, int precision, int offered, int n_outputs) {
     if (offered <= 1 || n <= 0 || m <= 0) return std::max(1, offered);
-    constexpr double kContextSeconds = 0.30;
+    // measured on the 2- and 8-GPU boxes (profiles/r02_summary.md sections 6 and 9)
+    constexpr double kContextSeconds = 0.30;    // per GPU, serialised by the driver: 2.3 s for eight
+    constexpr double kMultiGpuSeconds = 0.40;   // reduce-scatter + piece-grain read-out of a run on more than one GPU
     const double rate = precision == GGRM_PREC_FP64 ? 3.0e13 : 1.3e15;
     const double t1 = static_cast<double>(n) * (static_cast<double>(n) + 1.0) * static_cast<double>(m) * std::max(1, kinds) / rate;
-    int k = 1;
-    while (k < offered && t1 / (static_cast<double>(k + 1) * k) >= kContextSeconds) ++k;
+    int best = 1;
+    double best_cost = kContextSeconds + t1;
+    for (int k = 2; k <= offered; ++k) {
+        const double cost = kContextSeconds * k + t1 / k + kMultiGpuSeconds;
+        if (cost < best_cost) {
+            best_cost = cost;
+            best = k;
+        }
+    }
+    // write-bound runs (a LOCO run's 23 x 5 GB): a second GPU brings a second PCIe link and writer pool (C4: 17.7 -> 14.9 s), more do not
+    const double out_bytes = 2.0 * static_cast<double>(n) * static_cast<double>(n) * std::max(1, n_outputs);
+    if (best == 1 && out_bytes >= 32e9) best = 2;
     // ... and never fewer than the FP32 (FP64: double) triangle needs: n^2 / 2 entries per matrix, ~120 GB of a B200 for accumulators
     const double acc_bytes = 0.5 * static_cast<double>(n) * static_cast<double>(n) * (precision == GGRM_PREC_FP64 ? 8.0 : 4.0) * std::max(1, kinds);
     const int floor_k = static_cast<int>(std::ceil(acc_bytes / 120e9));
-    return std::min(offered, std::max(k, floor_k));
+    return std::min(offered, std::max(best, floor_k));
 }
 
 std::vector<std::pair<int64_t, int64_t>> GrmEngine::row_slices_for(int64_t n, int parts) { return row_slices(n, parts); }

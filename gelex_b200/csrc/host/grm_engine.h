@@ -110,12 +110,13 @@ class GrmEngine {
     static std::vector<GrmWorkItem> build_plan(const std::vector<std::string>& chroms, GrmType mode, bool do_loco,
                                                std::string* output_pattern_suffix, size_t* num_groups);
 
-    // How many of `offered` GPUs a one-shot run should use.  Every further GPU costs c ~ 0.3 s before the first push (CUDA context
-    // creation, which the driver serialises across the devices of a process: 2.3 s for eight, profiles/r02_summary.md section 6) and
-    // saves T1 / (k (k - 1)) s of device time when going from k - 1 to k GPUs (T1 = n(n+1) m kinds / rate, rate = 1.3e15 flop/s
-    // for 16-bit operands, 3.0e13 for FP64): the largest k <= offered for which that saving still covers c.  C2 -> 2, C4 -> 2,
-    // C5 -> 8, C1 / C3 -> 1.  The CLI applies it to --gpus (an upper bound) unless --gpus-exact; Config::gpus is always taken as is.
-    static int gpus_worth_using(int64_t n, int64_t m, int kinds, int precision, int offered);
+    // How many of `offered` GPUs a one-shot run should use: the k that minimises 0.3 k (CUDA context creation, which the driver
+    // serialises across the devices of a process: 2.3 s for eight) + T1 / k (T1 = n(n+1) m kinds / rate, rate = 1.3e15 flop/s for
+    // 16-bit operands, 3.0e13 for FP64) + 0.4 s for k > 1 (reduce-scatter and piece-grain read-out); a run that writes more than
+    // 32 GB (n_outputs matrices of 2 n^2 bytes: a LOCO run) takes at least two - the second PCIe link and writer pool are what it
+    // is short of - and never fewer than hold the accumulators.  C1 / C2 / C3 -> 1, C4 -> 2, C5 -> 8; all measured
+    // (profiles/r02_summary.md).  The CLI applies it to --gpus (an upper bound) unless --gpus-exact; Config::gpus is always taken as is.
+    static int gpus_worth_using(int64_t n, int64_t m, int kinds, int precision, int offered, int n_outputs = 1);
 
     // Row ranges the GPUs of an SNP-shard run reduce and write (cuts on 2 048-row super-rows, balanced on triangle area).
     static std::vector<std::pair<int64_t, int64_t>> row_slices_for(int64_t n, int parts);
@@ -165,7 +166,7 @@ extern "C" int gelex_b200_grm_run_gcta(const char* bfile, const char* out_prefix
 // strip_owners_for through C (CPU tests): out4 receives (rank, band, row_begin, row_end) per strip, up to cap strips; returns the strip count.
 extern "C" int gelex_b200_strip_owners(int64_t n, int world, const int64_t* band_row_end, int n_bands, int64_t* out4, int cap);
 // GrmEngine::gpus_worth_using through C (CPU tests).
-extern "C" int gelex_b200_gpus_worth_using(int64_t n, int64_t m, int kinds, int precision, int offered);
+extern "C" int gelex_b200_gpus_worth_using(int64_t n, int64_t m, int kinds, int precision, int offered, int n_outputs);
 // piece_owners_for through C: out5 receives (rank, band, super_row, super_col_begin, super_col_end) per piece; returns the piece count.
 extern "C" int gelex_b200_piece_owners(int64_t n, int world, const int64_t* band_row_end, int n_bands, int64_t* out5, int cap);
 // GrmEngine::writer_selftest through C (CPU tests): writer 0 = auto, 1 = pwrite, 2 = mmap.

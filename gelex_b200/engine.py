@@ -39,7 +39,7 @@ def load_host():
         h.gelex_b200_grm_load.restype = C.c_int64
         h.gelex_b200_row_slices.argtypes = [C.c_int64, C.c_int, C.c_void_p]
         h.gelex_b200_strip_owners.argtypes = [C.c_int64, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
-        h.gelex_b200_gpus_worth_using.argtypes = [C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int]
+        h.gelex_b200_gpus_worth_using.argtypes = [C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int]
         h.gelex_b200_piece_owners.argtypes = [C.c_int64, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
         h.gelex_b200_grm_run_gcta.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]
         vp = C.c_void_p
@@ -249,9 +249,9 @@ def strip_owners(n, world, bands):
     return per
 
 
-def gpus_worth_using(n, m, kinds=1, precision=_lib.PREC_FP16, offered=8):
-    """How many of `offered` GPUs the CLI uses for an n x m problem (GrmEngine::gpus_worth_using)."""
-    return int(load_host().gelex_b200_gpus_worth_using(int(n), int(m), int(kinds), int(precision), int(offered)))
+def gpus_worth_using(n, m, kinds=1, precision=_lib.PREC_FP16, offered=8, n_outputs=1):
+    """How many of `offered` GPUs the CLI uses for an n x m problem writing n_outputs matrices (GrmEngine::gpus_worth_using)."""
+    return int(load_host().gelex_b200_gpus_worth_using(int(n), int(m), int(kinds), int(precision), int(offered), int(n_outputs)))
 
 
 def piece_owners(n, world, bands):

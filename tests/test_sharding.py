@@ -184,15 +184,16 @@ def test_cpp_engine_deals_pieces_like_the_python_rule():
 
 
 def test_cli_gpu_count_rule_on_the_named_configs():
-    # --gpus is an upper bound in the CLI: a further GPU must save more device time than its ~0.3 s of context creation costs
+    # --gpus is an upper bound in the CLI: the GPU count that minimises context creation (0.3 s each, serialised) + device time +
+    # the fixed cost of a multi-GPU read-out; write-bound LOCO runs take a second GPU for its PCIe link and writer pool
     from gelex_b200 import _lib, engine
 
-    assert engine.gpus_worth_using(2_000, 50_000) == 1                      # C1
-    assert engine.gpus_worth_using(20_000, 300_000, kinds=2) == 1           # C3: 0.18 s of device time
-    assert engine.gpus_worth_using(50_000, 500_000) == 2                    # C2: 0.96 s on one GPU
-    assert engine.gpus_worth_using(50_000, 600_000) == 2                    # C4
-    assert engine.gpus_worth_using(200_000, 600_000) == 8                   # C5: 18 s on one GPU
+    assert engine.gpus_worth_using(2_000, 50_000) == 1                                   # C1
+    assert engine.gpus_worth_using(20_000, 300_000, kinds=2) == 1                        # C3: 0.18 s of device time
+    assert engine.gpus_worth_using(50_000, 500_000) == 1                                 # C2: measured 2.0 s on one GPU, 3.0 on two, 5.4 on eight
+    assert engine.gpus_worth_using(50_000, 600_000, n_outputs=22) == 2                   # C4: measured 17.7 / 14.9 / 15.1 s on 1 / 2 / 8
+    assert engine.gpus_worth_using(200_000, 600_000) == 8                                # C5: 18 s of device time on one GPU
     assert engine.gpus_worth_using(200_000, 600_000, offered=4) == 4
     assert engine.gpus_worth_using(50_000, 500_000, offered=1) == 1
-    assert engine.gpus_worth_using(20_000, 300_000, precision=_lib.PREC_FP64) == 4   # the DMMA path is 40x slower (4 s on one GPU): more GPUs pay
-    assert engine.gpus_worth_using(400_000, 1_000, offered=8) >= 3          # 320 GB of FP32 triangle: never fewer GPUs than hold it
+    assert engine.gpus_worth_using(20_000, 300_000, precision=_lib.PREC_FP64) == 4       # the DMMA path is 40x slower (4 s on one GPU)
+    assert engine.gpus_worth_using(400_000, 1_000, offered=8) >= 3                       # 320 GB of FP32 triangle: never fewer GPUs than hold it
