@@ -49,6 +49,8 @@ CONFIGS = {
                what="22 per-chromosome partial GRMs + whole-genome GRM (StandardizeHWE+Add), one pass"),
 }
 C1 = dict(n=2000, m=50000, seed=20261104 + 1)       # configs[0]: the like-for-like pair
+MID = dict(n=20000, m=30000, seed=20261104 + 6)     # a second like-for-like pair in the regime the engine is for: C3's sample count, a tenth
+                                                    # of its SNPs, ~17 s on the reference's CPU path with 16 cores (not a BASELINE.json config)
 CPU_SAMPLE = (8000, 30000)                          # fixed bounded sample of the workload for the CPU arm (about 2-3 s per step)
 
 
@@ -267,6 +269,15 @@ def cpu_leg(steps, warmup, cfg, payload_rows_fn):
                                     "reference_cli_wall_s": time.time() - t0, "reference_compute_wall_s": c1["wall_s"], "reference_threads": phys,
                                     "fs": fs_of(tmp)}
             out["_c1_prefix"] = str(tmp / "c1")
+            write_triple(tmp / "mid", MID["n"], MID["m"], payload_rows_fn(MID["n"], MID["m"], MID["seed"]), chromosome_runs(MID["m"]))
+            t0 = time.time()
+            mid = run_ref(["grm", tmp / "mid", tmp / "mid_ref", METHOD, "A", 0, 10000, phys])
+            out["like_for_like_mid"] = {"config": f"Yang additive GRM, {MID['n']} samples x {MID['m']} SNPs (C3's sample count, a tenth of its SNPs), real files in and out",
+                                        "same_config": True, "reference_cli_wall_s": time.time() - t0, "reference_compute_wall_s": mid["wall_s"],
+                                        "reference_threads": phys, "fs": fs_of(tmp)}
+            out["_mid_prefix"] = str(tmp / "mid")
+            for junk in tmp.glob("*_ref.*"):  # the reference's 1.6 GB output is not needed beside ours
+                junk.unlink()
         return out, tmp
     except Exception:
         shutil.rmtree(tmp, ignore_errors=True)
@@ -749,6 +760,12 @@ def gpu_arm(args):
                 cb["like_for_like"].update({"ours_cli_wall_s": ours["cli_wall_s"], "ours_engine_wall_s": ours.get("engine_wall_s"),
                                             "ours_phases_s": ours.get("phases_s"), "ours_rc": ours["rc"]})
                 line["like_for_like"] = cb.pop("like_for_like")
+            midp = cb.pop("_mid_prefix", None)
+            if midp is not None and CLI_BIN.exists():
+                ours = run_cli(midp, str(tmp / "mid_ours"), 1, args.precision)
+                cb["like_for_like_mid"].update({"ours_cli_wall_s": ours["cli_wall_s"], "ours_engine_wall_s": ours.get("engine_wall_s"),
+                                                "ours_phases_s": ours.get("phases_s"), "ours_rc": ours["rc"]})
+                line["like_for_like_mid"] = cb.pop("like_for_like_mid")
         finally:
             shutil.rmtree(tmp, ignore_errors=True)
         line["cpu_baseline"] = cb
@@ -767,6 +784,7 @@ def reference_arm(args):
     cb, tmp = cpu_leg(args.steps, args.warmup, cfg, synth_rows_numpy)
     shutil.rmtree(tmp, ignore_errors=True)
     cb.pop("_c1_prefix", None)
+    cb.pop("_mid_prefix", None)
     n_s, m_s = CPU_SAMPLE if REF_BIN.exists() else (1500, 3000)
     line = {"impl": "reference", "metric": cfg["metric"], "value": cb["value"], "unit": "TFLOP/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": cb["wall_s"] * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -774,6 +792,7 @@ def reference_arm(args):
             "config": {"workload": f"{cfg['tag']}: {cfg['what']}, {cfg['n']} samples x {cfg['m']} SNPs; each step = the fixed bounded sample "
                                    f"{n_s} x {m_s} of it (the CPU path needs hours and 40 GB for the full shape)"},
             "like_for_like": cb.pop("like_for_like", None),
+            "like_for_like_mid": cb.pop("like_for_like_mid", None),
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
