@@ -18,6 +18,7 @@ ABI_VERSION = 1
 KIND_ADD, KIND_DOM = 0, 1
 GROUP_WHOLE = -1
 PREC_BF16, PREC_FP64, PREC_FP16 = 0, 1, 2
+SECOND_DOMINANCE, SECOND_NONMISSING, SECOND_NONMISSING_GCTA_DIAG = 0, 1, 2
 ALLMISS_REFERENCE_NAN, ALLMISS_SKIP = 0, 1
 
 # GenotypeProcessMethod (reference include/gelex/data/genotype/genotype_processor.h:38-48)
@@ -71,7 +72,7 @@ EXPORTS = [
     "ggrm_band_layout", "ggrm_set_band_flags", "ggrm_reduce_rows_async", "ggrm_genotype_chunk", "ggrm_fetch_gcta", "ggrm_accum_address",
     "ggrm_stage_create", "ggrm_stage_destroy", "ggrm_stage_upload", "ggrm_stage_slot", "ggrm_wait_copies",
     "ggrm_warm_device", "ggrm_reduce_block_async", "ggrm_host_register", "ggrm_host_unregister",
-    "ggrm_snp_stats_noalloc",
+    "ggrm_snp_stats_noalloc", "ggrm_fetch_block_gcta", "ggrm_gcta_diag_address", "ggrm_gcta_diag_reduce_async",
 ]
 
 _lib = None
@@ -136,6 +137,9 @@ def load() -> C.CDLL:
     lib.ggrm_host_register.argtypes = [vp, i64]
     lib.ggrm_host_unregister.argtypes = [vp]
     lib.ggrm_snp_stats_noalloc.argtypes = [C.c_int, vp, i64, i64, i64, vp, vp, vp]
+    lib.ggrm_fetch_block_gcta.argtypes = [vp, C.c_int, C.c_int, i64, i64, i64, i64, vp, i64]
+    lib.ggrm_gcta_diag_address.argtypes = [vp, C.POINTER(vp)]
+    lib.ggrm_gcta_diag_reduce_async.argtypes = [vp, C.POINTER(vp), C.c_int]
     lib.ggrm_reduce_block_async.argtypes = [vp, C.c_int, C.c_int, C.POINTER(vp), C.c_int, i64, i64, i64]
     lib.ggrm_device_count.argtypes = []
     lib.ggrm_version.argtypes = []
@@ -189,7 +193,7 @@ class Accumulator:
         cfg.tile_rank, cfg.tile_world = tile_rank, tile_world
         cfg.chunk_snps = chunk_snps
         cfg.max_resident_groups = max_resident_groups
-        cfg.second_matrix = second_matrix  # 1: the dom slot holds the non-missing pair counts (GCTA .grm.N.bin)
+        cfg.second_matrix = second_matrix  # 1: the dom slot holds the non-missing pair counts (GCTA .grm.N.bin); 2: + GCTA's default diagonal
         self.precision = precision
         h = C.c_void_p()
         st = self.lib.ggrm_create(C.byref(cfg), C.byref(h))
@@ -332,6 +336,22 @@ class Accumulator:
         out = np.empty(tri(row_begin + row_count) - tri(row_begin), dtype=np.float32)
         self._check(self.lib.ggrm_fetch_gcta(self.h, which, group, row_begin, row_count, _ptr(out)))
         return out
+
+    def fetch_block_gcta(self, which, group, row_begin, row_count, col_begin, col_count):
+        """fetch_gcta as a rectangular block (the 2D-tile writer's unit)."""
+        out = np.empty((row_count, col_count), dtype=np.float32)
+        self._check(self.lib.ggrm_fetch_block_gcta(self.h, which, group, row_begin, row_count, col_begin, col_count, _ptr(out), col_count))
+        return out
+
+    def gcta_diag_address(self) -> int:
+        p = C.c_void_p()
+        self._check(self.lib.ggrm_gcta_diag_address(self.h, C.byref(p)))
+        return p.value
+
+    def gcta_diag_reduce_async(self, peer_ptrs):
+        """SNP shards with second_matrix=2: total diagonal sums = own + the peers' (gcta_diag_address of their handles)."""
+        arr = (C.c_void_p * max(1, len(peer_ptrs)))(*peer_ptrs)
+        self._check(self.lib.ggrm_gcta_diag_reduce_async(self.h, arr, len(peer_ptrs)))
 
     def fetch_block(self, kind, group, row_begin, row_count, col_begin, col_count):
         out = np.empty((row_count, col_count), dtype=np.float32)

@@ -289,6 +289,7 @@ static void free_handle(Handle* h) {
         for (void* p : h->pool[k]) fr(p);
     }
     fr(h->d_stage); fr(h->d_trace); fr(h->d_fault); fr(h->d_wave_ctr); fr(h->d_range_flag);
+    fr(h->d_gcta_w); fr(h->d_gcta_lanes); fr(h->d_gcta_diag); fr(h->d_gcta_total);
     for (int i = 0; i < Handle::kRingSlots; ++i) {
         if (h->ring[i] != nullptr) cudaFreeHost(h->ring[i]);
         if (h->ring_free[i] != nullptr) cudaEventDestroy(h->ring_free[i]);
@@ -327,9 +328,11 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
     if (cfg->tile_world < 1 || cfg->tile_rank < 0 || cfg->tile_rank >= cfg->tile_world)
         throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "invalid tile partition"};
     if (cfg->n_out > (int64_t{1} << 30)) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "n_out too large"};
-    if (cfg->second_matrix != GGRM_SECOND_DOMINANCE && cfg->second_matrix != GGRM_SECOND_NONMISSING)
+    if (cfg->second_matrix != GGRM_SECOND_DOMINANCE && cfg->second_matrix != GGRM_SECOND_NONMISSING && cfg->second_matrix != GGRM_SECOND_NONMISSING_GCTA_DIAG)
         throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "invalid second_matrix"};
-    if (cfg->second_matrix == GGRM_SECOND_NONMISSING && cfg->precision != GGRM_PREC_FP64 && cfg->m_total >= (int64_t{1} << 24))
+    if (cfg->second_matrix == GGRM_SECOND_NONMISSING_GCTA_DIAG && (cfg->method != GGRM_STANDARDIZE_HWE || cfg->n_groups != 1 || !cfg->want_add || !cfg->want_dom))
+        throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "GCTA's diagonal is defined for the standardize-HWE additive matrix of one group: needs method SH, n_groups = 1, want_add and want_dom"};
+    if (cfg->second_matrix != GGRM_SECOND_DOMINANCE && cfg->precision != GGRM_PREC_FP64 && cfg->m_total >= (int64_t{1} << 24))
         throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "non-missing pair counts are exact in FP32 only below 2^24 SNPs: use the FP64 precision"};
 
     h->cfg = *cfg;
@@ -507,6 +510,15 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
         dev_alloc(*h, &h->d_freq, static_cast<size_t>(cfg->m_total) * sizeof(double), "per-SNP frequencies");
         GGRM_CUDA(cudaMemsetAsync(h->d_counts, 0, static_cast<size_t>(cfg->m_total) * sizeof(int4), h->s_comp));
         GGRM_CUDA(cudaMemsetAsync(h->d_freq, 0, static_cast<size_t>(cfg->m_total) * sizeof(double), h->s_comp));
+    }
+    if (cfg->second_matrix == GGRM_SECOND_NONMISSING_GCTA_DIAG) {
+        dev_alloc(*h, &h->d_gcta_w, static_cast<size_t>(k_cap) * sizeof(double4), "GCTA diagonal terms of a chunk");
+        dev_alloc(*h, &h->d_gcta_lanes, static_cast<size_t>(kGctaLanes * h->n_pad) * sizeof(double), "GCTA diagonal lane sums");
+        GGRM_CUDA(cudaMemsetAsync(h->d_gcta_lanes, 0, static_cast<size_t>(kGctaLanes * h->n_pad) * sizeof(double), h->s_comp));
+        dev_alloc(*h, &h->d_gcta_diag, static_cast<size_t>(h->n_pad) * sizeof(double), "GCTA diagonal sums");
+        dev_alloc(*h, &h->d_gcta_total, static_cast<size_t>(h->n_pad) * sizeof(double), "GCTA diagonal sums over all shards");
+        GGRM_CUDA(cudaMemsetAsync(h->d_gcta_diag, 0, static_cast<size_t>(h->n_pad) * sizeof(double), h->s_comp));
+        GGRM_CUDA(cudaMemsetAsync(h->d_gcta_total, 0, static_cast<size_t>(h->n_pad) * sizeof(double), h->s_comp));
     }
     lap("device buffers allocated");
     GGRM_CUDA(cudaMalloc(&h->d_trace, sizeof(double)));

@@ -57,6 +57,23 @@ __global__ void __launch_bounds__(256) trace_kernel(const TAcc* __restrict__ A, 
     if ((threadIdx.x & 31) == 0) atomicAdd(trace, local);
 }
 
+// GCTA diagonal sums the ratio read-outs use: the all-shard total once ggrm_gcta_diag_reduce_async has produced it in this
+// pass, else this handle's own sums (complete when the handle saw every SNP: one GPU, or a 2D-tile rank); nullptr without the option.
+static const double* gcta_diag_for_readout(Handle& h) {
+    if (h.d_gcta_diag == nullptr) return nullptr;
+    return h.gcta_total_valid ? h.d_gcta_total : h.d_gcta_diag;
+}
+
+// total[i] = own[i] + sum_p peers[p][i], in peer order: every rank passes its peers in rank order around itself, so the
+// totals of two ranks may differ in the last bit; each rank only ever writes the diagonal entries of rows it owns.
+__global__ void __launch_bounds__(256) gcta_diag_total_kernel(const double* __restrict__ own, PeerPtrs peers, int n_peers, int64_t n, double* __restrict__ total) {
+    const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double v = own[i];
+    for (int p = 0; p < n_peers; ++p) v += static_cast<const double*>(peers.p[p])[i];
+    total[i] = v;
+}
+
 template <typename TAcc>
 static double full_trace(Handle& h, const TAcc* A) {
     GGRM_CUDA(cudaMemsetAsync(h.d_trace, 0, sizeof(double), h.s_fetch));
@@ -84,11 +101,13 @@ static void fetch_typed(Handle& h, int kind, int group, int64_t row_begin, int64
     int band_waited = -1;
     const TAcc* B = nullptr;
     const TAcc* D = nullptr;
+    const double* gdiag = nullptr;
     double scale = 1.0;
     if (mode == 3) {
         cudaEvent_t evn = nullptr;
         D = static_cast<const TAcc*>(resolve_accum(h, GGRM_KIND_DOM, group, &evn));
         if (evn != nullptr) GGRM_CUDA(cudaStreamWaitEvent(h.s_fetch, evn, 0));
+        gdiag = gcta_diag_for_readout(h);
     }
     if (mode == 1) {
         const double tr = full_trace<TAcc>(h, A);
@@ -138,9 +157,9 @@ static void fetch_typed(Handle& h, int kind, int group, int64_t row_begin, int64
         const int64_t elems = tri(r + cnt) - tri(r);
         if constexpr (std::is_same<TAcc, float>::value)  // one warp per row, eight consecutive rows per block (see pack_rows8_kernel)
             pack_rows8_kernel<TOut><<<dim3(static_cast<unsigned>((cnt + 7) / 8), static_cast<unsigned>(((r + cnt - 1) / kTile) / kPackTilesPerBlock + 1)), 256, 0, h.s_fetch>>>(
-                A, B, D, h.d_slot_of, r, cnt, scale, static_cast<TOut*>(h.d_stage), h.d_trace);
+                A, B, D, h.d_slot_of, r, cnt, scale, static_cast<TOut*>(h.d_stage), h.d_trace, gdiag);
         else
-            pack_rows_kernel<TAcc, TOut><<<static_cast<unsigned>(cnt), 256, 0, h.s_fetch>>>(A, B, D, h.d_slot_of, r, cnt, scale, static_cast<TOut*>(h.d_stage), h.d_trace);
+            pack_rows_kernel<TAcc, TOut><<<static_cast<unsigned>(cnt), 256, 0, h.s_fetch>>>(A, B, D, h.d_slot_of, r, cnt, scale, static_cast<TOut*>(h.d_stage), h.d_trace, gdiag);
         GGRM_CUDA(cudaGetLastError());
         ++h.kernel_launches;
         GGRM_CUDA(cudaMemcpyAsync(out + written, h.d_stage, static_cast<size_t>(elems) * sizeof(TOut), cudaMemcpyDeviceToHost, h.s_fetch));
@@ -163,7 +182,7 @@ static void fetch_typed(Handle& h, int kind, int group, int64_t row_begin, int64
 // writer: one call per owned 2048x2048 super-tile, rows then pwrite()n at their .bin offsets.
 template <typename TAcc>
 static void fetch_block_typed(Handle& h, int kind, int group, int64_t row_begin, int64_t row_count, int64_t col_begin, int64_t col_count,
-                              float* out, int64_t ld) {
+                              float* out, int64_t ld, bool gcta_ratio = false) {
     if (row_begin < 0 || row_count < 0 || row_begin + row_count > h.n_out || col_begin < 0 || col_count < 0 || col_begin + col_count > h.n_out)
         throw CudaError{GGRM_ERR_COLUMN_RANGE, "block outside [0, n_out) x [0, n_out)"};
     if (row_count == 0 || col_count == 0) return;
@@ -178,6 +197,16 @@ static void fetch_block_typed(Handle& h, int kind, int group, int64_t row_begin,
         ev = h.band_done[b];
     }
     if (ev != nullptr) GGRM_CUDA(cudaStreamWaitEvent(h.s_fetch, ev, 0));
+    const TAcc* D = nullptr;
+    const double* gdiag = nullptr;
+    if (gcta_ratio) {  // the pair counts of the same rows: same band, on the same stream
+        cudaEvent_t evn = nullptr;
+        bool bandedn = false;
+        D = static_cast<const TAcc*>(resolve_accum(h, GGRM_KIND_DOM, group, &evn, &bandedn));
+        if (bandedn) evn = ev;
+        if (evn != nullptr && evn != ev) GGRM_CUDA(cudaStreamWaitEvent(h.s_fetch, evn, 0));
+        gdiag = gcta_diag_for_readout(h);
+    }
     if (h.d_stage == nullptr) {
         const int64_t want = std::min<int64_t>(int64_t{256} << 20, std::max<int64_t>(tri(h.n_out) * 8, h.n_out * 8 + 1024));
         h.stage_bytes = std::max<int64_t>(want, h.n_out * 8);
@@ -188,7 +217,7 @@ static void fetch_block_typed(Handle& h, int kind, int group, int64_t row_begin,
     for (int64_t r = 0; r < row_count; r += rows_per_pass) {
         const int64_t cnt = std::min(rows_per_pass, row_count - r);
         pack_block_kernel<TAcc, float><<<static_cast<unsigned>(cnt), 256, 0, h.s_fetch>>>(A, h.d_slot_of, row_begin + r, cnt, col_begin, col_count,
-                                                                                         static_cast<float*>(h.d_stage));
+                                                                                         static_cast<float*>(h.d_stage), D, gdiag);
         GGRM_CUDA(cudaGetLastError());
         ++h.kernel_launches;
         GGRM_CUDA(cudaMemcpy2DAsync(out + r * ld, static_cast<size_t>(ld) * sizeof(float), h.d_stage, static_cast<size_t>(col_count) * sizeof(float),
@@ -239,11 +268,54 @@ extern "C" int ggrm_fetch_loco(ggrm_t* hh, int kind, int group, int64_t row_begi
 extern "C" int ggrm_fetch_gcta(ggrm_t* hh, int which, int group, int64_t row_begin, int64_t row_count, float* out_lower_rows) {
     Handle* h = reinterpret_cast<Handle*>(hh);
     GGRM_API_BEGIN(h)
-    if (h->cfg.second_matrix != GGRM_SECOND_NONMISSING || !h->cfg.want_add || !h->cfg.want_dom)
+    if (h->cfg.second_matrix == GGRM_SECOND_DOMINANCE || !h->cfg.want_add || !h->cfg.want_dom)
         throw CudaError{GGRM_ERR_INVALID_OPERATION, "GCTA read-out needs want_add, want_dom and second_matrix = GGRM_SECOND_NONMISSING"};
     if (which != 0 && which != 1) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "which must be 0 (A = G/N) or 1 (N)"};
     if (which == 0) fetch_dispatch<float>(*h, GGRM_KIND_ADD, group, row_begin, row_count, out_lower_rows, nullptr, 3);
     else fetch_dispatch<float>(*h, GGRM_KIND_DOM, group, row_begin, row_count, out_lower_rows, nullptr, 0);
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_fetch_block_gcta(ggrm_t* hh, int which, int group, int64_t row_begin, int64_t row_count, int64_t col_begin, int64_t col_count,
+                                     float* out, int64_t ld) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    if (h->cfg.second_matrix == GGRM_SECOND_DOMINANCE || !h->cfg.want_add || !h->cfg.want_dom)
+        throw CudaError{GGRM_ERR_INVALID_OPERATION, "GCTA read-out needs want_add, want_dom and second_matrix = GGRM_SECOND_NONMISSING"};
+    if (which != 0 && which != 1) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "which must be 0 (A = G/N) or 1 (N)"};
+    const int kind = which == 0 ? GGRM_KIND_ADD : GGRM_KIND_DOM;
+    if (h->fp64) fetch_block_typed<double>(*h, kind, group, row_begin, row_count, col_begin, col_count, out, ld, which == 0);
+    else fetch_block_typed<float>(*h, kind, group, row_begin, row_count, col_begin, col_count, out, ld, which == 0);
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_gcta_diag_address(ggrm_t* hh, void** d_ptr) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    if (h->d_gcta_diag == nullptr) throw CudaError{GGRM_ERR_INVALID_OPERATION, "the handle was not created with second_matrix = GGRM_SECOND_NONMISSING_GCTA_DIAG"};
+    if (d_ptr == nullptr) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "null argument"};
+    *d_ptr = h->d_gcta_diag;
+    GGRM_API_END(h)
+}
+
+extern "C" int ggrm_gcta_diag_reduce_async(ggrm_t* hh, const void* const* peers, int n_peers) {
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    GGRM_API_BEGIN(h)
+    if (h->d_gcta_diag == nullptr) throw CudaError{GGRM_ERR_INVALID_OPERATION, "the handle was not created with second_matrix = GGRM_SECOND_NONMISSING_GCTA_DIAG"};
+    if (n_peers < 0 || n_peers > kMaxPeers || (n_peers > 0 && peers == nullptr)) throw CudaError{GGRM_ERR_INVALID_ARGUMENT, "n_peers must be 0..7"};
+    // this handle's own sums are final once its pass is: behind the group's completion (band 0 of a banded pass follows every
+    // prepared slab of the pass, see accumulate_slabs)
+    cudaEvent_t ev = nullptr;
+    bool banded = false;
+    resolve_accum(*h, GGRM_KIND_ADD, GGRM_GROUP_WHOLE, &ev, &banded);
+    if (banded) ev = h->band_done.front();
+    if (ev != nullptr) GGRM_CUDA(cudaStreamWaitEvent(h->s_fetch, ev, 0));
+    PeerPtrs pp{};
+    for (int i = 0; i < n_peers; ++i) pp.p[i] = peers[i];
+    gcta_diag_total_kernel<<<static_cast<unsigned>((h->n_out + 255) / 256), 256, 0, h->s_fetch>>>(h->d_gcta_diag, pp, n_peers, h->n_out, h->d_gcta_total);
+    GGRM_CUDA(cudaGetLastError());
+    ++h->kernel_launches;
+    h->gcta_total_valid = true;
     GGRM_API_END(h)
 }
 

@@ -258,7 +258,8 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
     StatsOut so{};
     so.counts = h.d_counts;
     so.freq = h.d_freq;
-    so.second_nonmissing = h.cfg.second_matrix == GGRM_SECOND_NONMISSING ? 1 : 0;
+    so.second_nonmissing = h.cfg.second_matrix != GGRM_SECOND_DOMINANCE ? 1 : 0;
+    so.gcta_w = h.d_gcta_w;
     so.range_flag = h.cfg.precision == GGRM_PREC_FP16 ? h.d_range_flag : nullptr;
     for (int kind = 0; kind < 2; ++kind) {
         so.tab16[kind] = h.d_tab16[kind];
@@ -269,6 +270,12 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
         h.d_dense, h.bpv_pad, h.n_out, h.n_pad, c, h.cfg.method, h.cfg.all_missing_policy,
         h.cfg.precision == GGRM_PREC_FP16 ? 1 : 0, so, h.cur_first_snp);
     GGRM_CUDA(cudaGetLastError());
+    if (h.d_gcta_w != nullptr) {  // GGRM_SECOND_NONMISSING_GCTA_DIAG: this chunk's share of the per-sample diagonal sums
+        gcta_diag_kernel<<<static_cast<unsigned>(h.n_pad / kGctaSamplesPerBlock), 256, 0, sp>>>(h.d_dense, h.bpv_pad, h.d_gcta_w, c, h.cur_first_snp, h.n_pad, h.d_gcta_lanes,
+                                                                                 h.d_gcta_diag);
+        GGRM_CUDA(cudaGetLastError());
+        ++h.kernel_launches;
+    }
     phase_end(h, sp, ti);
     h.kernel_launches += 2;
 
@@ -512,6 +519,12 @@ static void reset_impl(Handle& h) {
         std::fill(h.pool_owner[kind].begin(), h.pool_owner[kind].end(), -1);
         if (h.whole[kind] != nullptr)
             GGRM_CUDA(cudaMemsetAsync(h.whole[kind], 0, static_cast<size_t>(std::max<int64_t>(h.accum_elems, 4)) * h.elem_bytes, h.s_comp));
+    }
+    if (h.d_gcta_diag != nullptr) {  // the streams are idle (finish_sync); the next pass's first chunk adds to it on the prep stream
+        cudaStream_t sp = h.overlap_prep ? h.s_prep : h.s_comp;
+        GGRM_CUDA(cudaMemsetAsync(h.d_gcta_lanes, 0, static_cast<size_t>(kGctaLanes * h.n_pad) * sizeof(double), sp));
+        GGRM_CUDA(cudaMemsetAsync(h.d_gcta_diag, 0, static_cast<size_t>(h.n_pad) * sizeof(double), sp));
+        h.gcta_total_valid = false;
     }
     h.cur_count = 0;
     h.cur_first_snp = -1;

@@ -160,6 +160,13 @@ struct Handle {
     unsigned long long wave_base = 0;
     int sync_every = 1;                   // waves between pacing points, 0 = off (GGRM_WAVE_SYNC)
     int* d_fault = nullptr;               // mbarrier-timeout location written by a stuck SYRK before it traps
+    // GGRM_SECOND_NONMISSING_GCTA_DIAG: per-SNP diagonal terms of the chunk being prepared, this handle's per-sample sums, and the
+    // sum over all SNP shards (ggrm_gcta_diag_reduce_async; the read-out uses it once it has been produced in this pass)
+    double4* d_gcta_w = nullptr;          // [k_cap]
+    double* d_gcta_lanes = nullptr;       // [16][n_pad] running sums by SNP index mod 16 (gcta_diag_kernel)
+    double* d_gcta_diag = nullptr;        // [n_pad] their sum, refreshed after every chunk
+    double* d_gcta_total = nullptr;       // [n_pad]
+    bool gcta_total_valid = false;
     unsigned long long* d_range_flag = nullptr;  // FP16 operands: 1 + index of a SNP whose standardised value overflows binary16 (0 = none)
     // timers
     std::vector<Timer> timers;

@@ -235,11 +235,12 @@ extern "C" int gelex_b200_genotype_load(const char* bfile, int method, int addit
 }
 
 // GrmEngine with Config::gcta: <out>.grm.bin (A = G / N), <out>.grm.N.bin, <out>.grm.id.  Additive, whole genome; SNP shards when n_gpus > 1.
-extern "C" int gelex_b200_grm_run_gcta(const char* bfile, const char* out_prefix, int method, int chunk_size, int precision, int n_gpus,
-                                       int writer_threads, char* err, int err_len) {
+extern "C" int gelex_b200_grm_run_gcta_ex(const char* bfile, const char* out_prefix, int method, int chunk_size, int precision, int n_gpus,
+                                          int writer_threads, int gcta_diag, int partition, char* err, int err_len) {
     try {
         if (bfile == nullptr || out_prefix == nullptr) throw ArgumentValidationException("null argument");
         if (method < 1 || method > 8) throw InvalidInputException("Invalid genotype process method.");
+        if (partition < 0 || partition > 2) throw ArgumentValidationException("partition must be 0 (auto), 1 (snp) or 2 (tile)");
         GrmEngine::Config cfg;
         cfg.bed_path = format_bed_path(bfile);
         cfg.mode = GrmType::A;
@@ -247,9 +248,10 @@ extern "C" int gelex_b200_grm_run_gcta(const char* bfile, const char* out_prefix
         cfg.out_prefix = out_prefix;
         cfg.chunk_size = chunk_size;
         cfg.precision = precision;
-        cfg.partition = Partition::SnpShard;
+        cfg.partition = partition == 2 ? Partition::Tile : (partition == 1 ? Partition::SnpShard : Partition::Auto);
         cfg.writer_threads = writer_threads;
         cfg.gcta = true;
+        cfg.gcta_diag = gcta_diag != 0;
         cfg.gpus.clear();
         const char* over = std::getenv("GELEX_B200_OVERSUBSCRIBE");  // test aid, see gelex_b200_grm_run_ex
         const int devs = ggrm_device_count();
@@ -261,6 +263,11 @@ extern "C" int gelex_b200_grm_run_gcta(const char* bfile, const char* out_prefix
     } catch (...) {
         return translate_exception(err, err_len);
     }
+}
+
+extern "C" int gelex_b200_grm_run_gcta(const char* bfile, const char* out_prefix, int method, int chunk_size, int precision, int n_gpus,
+                                       int writer_threads, char* err, int err_len) {
+    return gelex_b200_grm_run_gcta_ex(bfile, out_prefix, method, chunk_size, precision, n_gpus, writer_threads, 0, 1, err, err_len);
 }
 
 extern "C" int gelex_b200_strip_owners(int64_t n, int world, const int64_t* band_row_end, int n_bands, int64_t* out4, int cap) {

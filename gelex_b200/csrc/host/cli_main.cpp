@@ -1,7 +1,7 @@
 // `gelex-b200 grm ...` — drop-in for `gelex grm` (apps/cli/grm/grm_args.cpp:31-62): identical flags and defaults, the
 // same [Config] / [Dataset Summary] / progress / [File Summary] report (apps/cli/grm/grm_reporter.cpp:30-94), messages also
 // written to <out>.log, exit code 0 / 1 (apps/main.cpp:54-98).  Opt-in additions: --gpus, --precision, --with-whole,
-// --skip-all-missing, --partition, --writer-threads, --writer, --prefault, --bed-relay, --gcta.
+// --skip-all-missing, --partition, --writer-threads, --writer, --prefault, --bed-relay, --gcta, --gcta-diag.
 #include <unistd.h>
 
 #include <chrono>
@@ -37,7 +37,7 @@ const char* kUsage =
     "Usage: gelex-b200 grm [--help] --bfile <BFILE> [--out <OUT>] [--geno-method <STR>] [--chunk-size <SIZE>]\n"
     "                      [--threads <N>] [--add] [--dom] [--loco] [--gpus <N>] [--gpus-exact] [--precision <fp16|bf16|fp64>]\n"
     "                      [--partition <auto|snp|tile>] [--writer-threads <N>] [--writer <auto|pwrite|mmap>]\n"
-    "                      [--no-prefault] [--bed-relay] [--with-whole] [--skip-all-missing] [--gcta]\n\n"
+    "                      [--no-prefault] [--bed-relay] [--with-whole] [--skip-all-missing] [--gcta [--gcta-diag]]\n\n"
     "Compute genomic relationship matrix (GRM) from PLINK binary files and output in GCTA format\n\n"
     "Data Files:\n"
     "  -b, --bfile <BFILE>        PLINK binary file prefix (.bed/.bim/.fam) [required]\n"
@@ -62,7 +62,8 @@ const char* kUsage =
     "  --bed-relay                2D-tile partition: upload each BED chunk once and share it between the GPUs over NVLink\n"
     "  --with-whole               With --loco also write the whole-genome matrix (sum of the partials, same pass)\n"
     "  --skip-all-missing         Treat an all-missing SNP as contributing 0 (the reference lets it poison the GRM with NaN)\n"
-    "  --gcta                     GCTA binary format: <out>.grm.bin (G_ij / N_ij), <out>.grm.N.bin, <out>.grm.id (with --add, no --loco)\n";
+    "  --gcta                     GCTA binary format: <out>.grm.bin (G_ij / N_ij), <out>.grm.N.bin, <out>.grm.id (with --add, no --loco)\n"
+    "  --gcta-diag                with --gcta and --method SH: GCTA's default diagonal, 1 + (1/N) sum (x^2 - (1+2p)x + 2p^2) / (2p(1-p))\n";
 
 std::string mode_name(GrmType m) { return m == GrmType::A ? "A" : (m == GrmType::D ? "D" : "AD"); }
 
@@ -70,7 +71,7 @@ int run_grm(int argc, char** argv, Logger& log) {
     std::string bfile, out = "grm", gm = "OSH", precision = "fp16", partition = "auto", writer = "auto";
     int chunk = 10000, gpus = 1, writer_threads = 4;
     int threads = static_cast<int>(std::thread::hardware_concurrency() / 2);
-    bool add = false, dom = false, loco = false, with_whole = false, skip_missing = false, gcta = false, bed_relay = false, prefault = true, gpus_exact = false;
+    bool add = false, dom = false, loco = false, with_whole = false, skip_missing = false, gcta = false, gcta_diag = false, bed_relay = false, prefault = true, gpus_exact = false;
     auto need = [&](int& i) -> std::string {
         if (i + 1 >= argc) throw ArgumentValidationException(std::string("Too few arguments for '") + argv[i] + "'.");
         return argv[++i];
@@ -108,6 +109,7 @@ int run_grm(int argc, char** argv, Logger& log) {
         else if (a == "--no-prefault") prefault = false;
         else if (a == "--skip-all-missing") skip_missing = true;
         else if (a == "--gcta") gcta = true;
+        else if (a == "--gcta-diag") gcta_diag = true;
         else throw ArgumentValidationException("Unknown argument: " + a);
     }
     (void)threads;
@@ -155,6 +157,7 @@ int run_grm(int argc, char** argv, Logger& log) {
     cfg.write_whole = with_whole;
     cfg.skip_all_missing = skip_missing;
     cfg.gcta = gcta;
+    cfg.gcta_diag = gcta_diag;
     cfg.bed_relay = bed_relay;
     cfg.prefault = prefault;
 

@@ -446,7 +446,7 @@ void write_packed_rows(ggrm_t* h, int kind, int group, int64_t r0, int64_t r1, c
 }
 
 // 2D-tile mode: every 2048 x 2048 super-tile this handle owns -> row segments at their own offsets.
-void write_owned_supertiles(ggrm_t* h, int kind, int group, int64_t n, const BinFile& file, WriterPool& pool) {
+void write_owned_supertiles(ggrm_t* h, int kind, int group, int64_t n, const BinFile& file, WriterPool& pool, bool gcta = false) {
     constexpr int64_t kSuper = 2048;
     int64_t count = 0;
     check_status(h, ggrm_owned_supertiles(h, nullptr, nullptr, 0, &count));
@@ -457,13 +457,27 @@ void write_owned_supertiles(ggrm_t* h, int kind, int group, int64_t n, const Bin
         const int64_t rows = std::min(kSuper, n - row0), cols = std::min(kSuper, n - col0);
         if (rows <= 0 || cols <= 0) continue;
         float* buf = pool.acquire();
-        const int st = ggrm_fetch_block(h, kind, group, row0, rows, col0, cols, buf, cols);
+        const int st = gcta ? ggrm_fetch_block_gcta(h, kind, group, row0, rows, col0, cols, buf, cols) : ggrm_fetch_block(h, kind, group, row0, rows, col0, cols, buf, cols);
         if (st != GGRM_OK) {
             pool.submit(file, buf, {});
             throw_status(st, ggrm_last_error(h));
         }
         pool.submit(file, buf, supertile_segments(row0, col0, rows, cols));
     }
+}
+
+// SNP shards of a GCTA run with the default diagonal: total diagonal sums of handle r = its own + every peer's (the peers'
+// passes must be complete - a band flag of theirs is up, or they were finished).
+void reduce_gcta_diag(const std::vector<ggrm_t*>& handles, size_t r) {
+    std::vector<const void*> peers;
+    for (size_t p = 0; p < handles.size(); ++p) {
+        if (p == r) continue;
+        void* ptr = nullptr;
+        check(handles[p], ggrm_gcta_diag_address(handles[p], &ptr));
+        peers.push_back(ptr);
+    }
+    if (peers.size() > 7) throw GelexException("GCTA diagonal: more than 8 GPUs in one SNP-shard run");
+    check(handles[r], ggrm_gcta_diag_reduce_async(handles[r], peers.data(), static_cast<int>(peers.size())));
 }
 
 std::string lower(std::string s) {
@@ -557,6 +571,7 @@ struct RunContext {
     bool loco;
     bool want_add, want_dom;
     bool gcta;  // kind 1 is the non-missing pair count matrix; outputs are <out>.grm.bin / .grm.N.bin / .grm.id
+    bool gcta_diag = false;  // ... and the diagonal of .grm.bin is GCTA's default one (GGRM_SECOND_NONMISSING_GCTA_DIAG)
     int precision;  // operand precision of this run (Config::precision unless FP16 cannot represent the code values, see compute())
     WriterMode writer;  // effective mode of this run: Pwrite when the file system could not hold every output (see BinFile)
     bool bed_relay;     // 2D-tile mode: one upload per host chunk, peers copy it over NVLink (BedRelay)
@@ -617,7 +632,7 @@ ggrm_t* create_handle(const RunContext& rc, int device, const std::vector<int>& 
     c.all_missing_policy = rc.cfg->skip_all_missing ? GGRM_ALLMISS_SKIP : GGRM_ALLMISS_REFERENCE_NAN;
     c.tile_rank = tile_rank;
     c.tile_world = tile_world;
-    c.second_matrix = rc.gcta ? GGRM_SECOND_NONMISSING : GGRM_SECOND_DOMINANCE;
+    c.second_matrix = rc.gcta ? (rc.gcta_diag ? GGRM_SECOND_NONMISSING_GCTA_DIAG : GGRM_SECOND_NONMISSING) : GGRM_SECOND_DOMINANCE;
     ggrm_t* h = nullptr;
     const int st = ggrm_create(&c, &h);
     if (st != GGRM_OK) throw_status(st, ggrm_last_error(nullptr));
@@ -944,7 +959,7 @@ void write_outputs(const RunContext& rc, ggrm_t* h, int local_group, const std::
             switch (part.kind) {
                 case WritePart::AllRows: write_packed_rows(h, kind, local_group, 0, rc.n_out, f, pool, rc.gcta); break;
                 case WritePart::RowSlice: write_packed_rows(h, kind, local_group, part.r0, part.r1, f, pool, rc.gcta); break;
-                case WritePart::OwnedTiles: write_owned_supertiles(h, kind, local_group, rc.n_out, f, pool); break;
+                case WritePart::OwnedTiles: write_owned_supertiles(h, kind, local_group, rc.n_out, f, pool, rc.gcta); break;
             }
         } catch (...) {
             try { pool.drain(); } catch (...) {}  // no writer may still hold the descriptor when it closes
@@ -1221,8 +1236,13 @@ void run_pipelined_rank(const RunContext& rc, ShardPipe& sp, size_t r, double* p
                 }
             }
         }
+        bool diag_reduced = !rc.gcta_diag;
         for (const Strip& st : rc.gcta ? sp.mine[r] : std::vector<Strip>{}) {
             wait_band(st.band);
+            if (!diag_reduced) {  // any band flag of a peer means its pass - and with it its diagonal sums - is complete
+                reduce_gcta_diag(sp.handles, r);
+                diag_reduced = true;
+            }
             for (int kind = 0; kind < 2; ++kind) {
                 if (!(kind == 0 ? rc.want_add : rc.want_dom)) continue;
                 std::vector<const void*> peers;
@@ -1317,6 +1337,7 @@ void reduce_scatter_and_write(const RunContext& rc, const std::vector<ggrm_t*>& 
                         check(handles[r], ggrm_reduce_peer(handles[r], kind, GGRM_GROUP_WHOLE, peers.data() + off, cnt, eb, ee));
                     }
                 }
+                if (rc.gcta_diag) reduce_gcta_diag(handles, r);
                 WriterPool pool(rc.cfg->writer_threads, rc.cfg->writer_threads + 2, std::max<int64_t>(kWriterBufferElems, rc.n_out));
                 WritePart part;
                 part.kind = WritePart::RowSlice;
@@ -1686,6 +1707,8 @@ void GrmEngine::compute(const GrmObserver& observer) {
     if (config_.gpus.empty()) throw ArgumentValidationException("at least one GPU is required (there is no CPU fallback)");
     if (config_.gcta && (config_.mode != GrmType::A || config_.do_loco))
         throw ArgumentValidationException("--gcta writes the additive matrix of the whole genome: use --add without --dom / --loco");
+    if (config_.gcta_diag && (!config_.gcta || config_.method != GenotypeProcessMethod::StandardizeHWE))
+        throw ArgumentValidationException("--gcta-diag is GCTA's diagonal for its own standardisation: use it with --gcta and --method StandardizeHWE");
     fs::path fam = config_.bed_path, bim = config_.bed_path;
     fam.replace_extension(".fam");
     bim.replace_extension(".bim");
@@ -1732,6 +1755,7 @@ void GrmEngine::compute(const GrmObserver& observer) {
     rc.loco = config_.do_loco;
     rc.groups = config_.do_loco ? chromosome_runs(chroms) : std::vector<ChrRun>{{"", 0, static_cast<int64_t>(chroms.size())}};
     rc.gcta = config_.gcta;
+    rc.gcta_diag = config_.gcta && config_.gcta_diag;
     rc.want_add = config_.mode != GrmType::D;
     rc.want_dom = config_.mode != GrmType::A || config_.gcta;
     // FP16 operands overflow when a standardised value exceeds 65 504.  The scaled orthogonal dominance codes reach |z| ~ n (a
@@ -1801,7 +1825,6 @@ void GrmEngine::compute(const GrmObserver& observer) {
     } else {
         // SNP shards (+ one reduce) while the FP32 triangle fits comfortably per GPU, 2D output tiles from n >= 100 000
         const bool tile_mode = config_.partition == Partition::Tile || (config_.partition == Partition::Auto && rc.n_out >= 100000);
-        if (tile_mode && config_.gcta) throw ArgumentValidationException("--gcta is not available with the 2D-tile partition");
         run_multi_gpu(rc, tile_mode, &pass_ms, &syrk_ms);
     }
 

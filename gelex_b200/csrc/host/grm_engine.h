@@ -86,6 +86,9 @@ class GrmEngine {
         // GCTA binary format behind a flag (docs/source/data_formats.rst:188-208): instead of <out>.add.{bin,id} write
         // <out>.grm.bin (A_ij = G_ij / N_ij), <out>.grm.N.bin (N_ij = SNPs called in both samples) and <out>.grm.id.  Mode A, no LOCO.
         bool gcta = false;
+        // ... with GCTA's default diagonal in .grm.bin (its --make-grm-alg 0: A_jj = 1 + (1/N) sum (x^2 - (1 + 2p) x + 2p^2) / (2p(1 - p)))
+        // instead of sum z^2 / N.  Needs method StandardizeHWE, the one whose off-diagonal values are GCTA's.
+        bool gcta_diag = false;
     };
 
     explicit GrmEngine(Config config);
@@ -163,6 +166,9 @@ extern "C" int gelex_b200_grm_run(const char* bfile, const char* out_prefix, int
 // Config::gcta run (GCTA binary format out); see capi.cpp.
 extern "C" int gelex_b200_grm_run_gcta(const char* bfile, const char* out_prefix, int method, int chunk_size, int precision, int n_gpus,
                                        int writer_threads, char* err, int err_len);
+// _ex adds: gcta_diag (Config::gcta_diag) and partition (1 = SNP shards, 2 = 2D tiles; 0 = auto).
+extern "C" int gelex_b200_grm_run_gcta_ex(const char* bfile, const char* out_prefix, int method, int chunk_size, int precision, int n_gpus,
+                                          int writer_threads, int gcta_diag, int partition, char* err, int err_len);
 // strip_owners_for through C (CPU tests): out4 receives (rank, band, row_begin, row_end) per strip, up to cap strips; returns the strip count.
 extern "C" int gelex_b200_strip_owners(int64_t n, int world, const int64_t* band_row_end, int n_bands, int64_t* out4, int cap);
 // GrmEngine::gpus_worth_using through C (CPU tests).

@@ -33,7 +33,8 @@ __global__ void __launch_bounds__(256) pack_rows_kernel(const TAcc* __restrict__
                                                         const TAcc* __restrict__ D,  // entrywise divisor (GCTA N matrix) or nullptr
                                                         const int32_t* __restrict__ slot_of, int64_t row_begin,
                                                         int64_t row_count, double scale, TOut* __restrict__ out,
-                                                        double* __restrict__ trace) {
+                                                        double* __restrict__ trace,
+                                                        const double* __restrict__ gdiag = nullptr) {  // GCTA diagonal sums (with D): A_ii = 1 + gdiag[i] / D_ii
     const int64_t i = row_begin + blockIdx.x;
     if (blockIdx.x >= row_count) return;
     const int64_t base = i * (i + 1) / 2 - row_begin * (row_begin + 1) / 2;
@@ -50,7 +51,8 @@ __global__ void __launch_bounds__(256) pack_rows_kernel(const TAcc* __restrict__
             v *= scale;
             if (D != nullptr) {
                 const double d = static_cast<double>(D[off]);
-                v = d > 0.0 ? __ddiv_rn(v, d) : 0.0;
+                if (gdiag != nullptr && j == i) v = d > 0.0 ? 1.0 + __ddiv_rn(gdiag[i], d) : 0.0;
+                else v = d > 0.0 ? __ddiv_rn(v, d) : 0.0;
             }
         }
         out[base + j] = static_cast<TOut>(v);
@@ -70,7 +72,8 @@ template <typename TOut>
 __global__ void __launch_bounds__(256) pack_rows8_kernel(const float* __restrict__ A, const float* __restrict__ B,
                                                          const float* __restrict__ D, const int32_t* __restrict__ slot_of,
                                                          int64_t row_begin, int64_t row_count, double scale,
-                                                         TOut* __restrict__ out, double* __restrict__ trace) {
+                                                         TOut* __restrict__ out, double* __restrict__ trace,
+                                                         const double* __restrict__ gdiag = nullptr) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t local = static_cast<int64_t>(blockIdx.x) * 8 + warp;
     if (local >= row_count) return;
@@ -106,7 +109,8 @@ __global__ void __launch_bounds__(256) pack_rows8_kernel(const float* __restrict
                     v *= scale;
                     if (D != nullptr) {
                         const double dd = static_cast<double>(dv[e]);
-                        v = dd > 0.0 ? __ddiv_rn(v, dd) : 0.0;
+                        if (gdiag != nullptr && j0 + e == i) v = dd > 0.0 ? 1.0 + __ddiv_rn(gdiag[i], dd) : 0.0;
+                        else v = dd > 0.0 ? __ddiv_rn(v, dd) : 0.0;
                     }
                 }
                 o[e] = static_cast<TOut>(v);
@@ -132,10 +136,12 @@ __global__ void __launch_bounds__(256) pack_rows8_kernel(const float* __restrict
 // Rectangular read-out for the 2D-tile multi-GPU mode: rows [row_begin, +row_count) x columns [col_begin, +col_count) of
 // the lower triangle as a dense row-major [row_count][col_count] block (entries above the diagonal or in tiles this
 // handle does not own read as 0), so a rank can ship exactly the super-tiles it owns to their offsets in the .bin file.
+// D / gdiag: the GCTA ratio form of pack_rows_kernel (same FP64 arithmetic, so both partitions write the same bytes).
 template <typename TAcc, typename TOut>
 __global__ void __launch_bounds__(256) pack_block_kernel(const TAcc* __restrict__ A, const int32_t* __restrict__ slot_of,
                                                          int64_t row_begin, int64_t row_count, int64_t col_begin,
-                                                         int64_t col_count, TOut* __restrict__ out) {
+                                                         int64_t col_count, TOut* __restrict__ out,
+                                                         const TAcc* __restrict__ D = nullptr, const double* __restrict__ gdiag = nullptr) {
     if (blockIdx.x >= row_count) return;
     const int64_t i = row_begin + blockIdx.x;
     const int64_t I = i >> 8;
@@ -146,7 +152,18 @@ __global__ void __launch_bounds__(256) pack_block_kernel(const TAcc* __restrict_
         TOut v = TOut(0);
         if (j <= i) {
             const int32_t slot = slot_of[I * (I + 1) / 2 + (j >> 8)];
-            if (slot >= 0) v = static_cast<TOut>(A[static_cast<int64_t>(slot) * 65536 + tile_elem_offset<TAcc>(r, static_cast<int>(j & 255))]);
+            if (slot >= 0) {
+                const int64_t off = static_cast<int64_t>(slot) * 65536 + tile_elem_offset<TAcc>(r, static_cast<int>(j & 255));
+                if (D == nullptr) {
+                    v = static_cast<TOut>(A[off]);
+                } else {
+                    const double d = static_cast<double>(D[off]);
+                    double w = static_cast<double>(A[off]) * 1.0;
+                    if (gdiag != nullptr && j == i) w = d > 0.0 ? 1.0 + __ddiv_rn(gdiag[i], d) : 0.0;
+                    else w = d > 0.0 ? __ddiv_rn(w, d) : 0.0;
+                    v = static_cast<TOut>(w);
+                }
+            }
         }
         dst[jl] = v;
     }

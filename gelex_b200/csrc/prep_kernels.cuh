@@ -206,6 +206,7 @@ struct StatsOut {
     SnpTable* tab64[2];
     SnpMoments* moments[2];  // [kind]; only the genotype-export hook asks for them (with tab64 of the same kind)
     int second_nonmissing;   // kind 1 = the 0/1 non-missing indicator instead of the dominance policy (GGRM_SECOND_NONMISSING)
+    double4* gcta_w;         // [snp] GCTA diagonal terms by BED code {x = 2, missing, x = 1, x = 0}; nullptr unless GGRM_SECOND_NONMISSING_GCTA_DIAG
 };
 
 __global__ void __launch_bounds__(256) count_stats_kernel(const uint8_t* __restrict__ dense, int64_t bpv_pad,
@@ -279,6 +280,81 @@ __global__ void __launch_bounds__(256) count_stats_kernel(const uint8_t* __restr
             compute_snp_table(method, GGRM_KIND_ADD, n0, n1, n2, nmiss, all_missing_policy, &freq, &t);
         }
         if (out.freq != nullptr) out.freq[o] = freq;
+        if (out.gcta_w != nullptr) {
+            // GCTA's default diagonal term of one SNP: (x^2 - (1 + 2p) x + 2p^2) / (2p(1 - p)), x = A1 count, p = A1 frequency;
+            // 0 for a missing call and for a SNP without variation (which contributes 0 to the off-diagonal sums as well)
+            const int validi = n0 + n1 + n2;
+            const double p = validi > 0 ? static_cast<double>(n1 + 2 * n2) / (2.0 * static_cast<double>(validi)) : 0.0;
+            const double den = 2.0 * p * (1.0 - p);
+            double4 w = make_double4(0.0, 0.0, 0.0, 0.0);
+            if (den > 0.0) {
+                w.x = (4.0 - 2.0 * (1.0 + 2.0 * p) + 2.0 * p * p) / den;  // BED 00: x = 2
+                w.z = (1.0 - (1.0 + 2.0 * p) + 2.0 * p * p) / den;        // BED 10: x = 1
+                w.w = (2.0 * p * p) / den;                                // BED 11: x = 0
+            }
+            out.gcta_w[snp] = w;
+        }
+    }
+}
+
+// GCTA diagonal sums.  lanes[L][sample] = sum over the SNPs pushed so far whose global index is L mod 16 of
+// gcta_w[snp][code(sample, snp)], each lane added one SNP after the other in SNP order, and diag[sample] = lanes[0] + ... +
+// lanes[15] in that order: the result does not depend on how the SNPs were cut into chunks or pushes.  One block per 128
+// samples (32 bytes = one sector of every dense row): thread (x, y) owns half-word x of those bytes (8 samples, 8 FP64
+// accumulators in registers) for the SNPs u = y, y + 16, ... of the chunk.  The chunk is walked 256 SNPs at a time: their tables
+// go to shared memory (a term is then ONE indexed 8-byte load - entry [1], "missing", is 0), and a thread issues its 16 row
+// loads of the batch before it uses the first.  Reads the dense chunk once more (n/4 bytes per SNP) and the lanes twice.
+constexpr int kGctaLanes = 16;
+constexpr int kGctaSamplesPerBlock = 128;
+__global__ void __launch_bounds__(256) gcta_diag_kernel(const uint8_t* __restrict__ dense, int64_t bpv_pad, const double4* __restrict__ gcta_w,
+                                                        int64_t snp_count, int64_t first_snp, int64_t n_pad, double* __restrict__ lanes,
+                                                        double* __restrict__ diag) {
+    __shared__ __align__(32) double s_w[256 * 4];
+    const int x = threadIdx.x & 15, y = threadIdx.x >> 4;
+    const int64_t b0 = static_cast<int64_t>(blockIdx.x) * (kGctaSamplesPerBlock / 4);  // byte offset of the block's samples inside a dense row
+    const int64_t sample0 = b0 * 4 + x * 8;                                          // first of this thread's 8 samples
+    const int lane = static_cast<int>((first_snp + y) & (kGctaLanes - 1));
+    double* mine = lanes + static_cast<int64_t>(lane) * n_pad + sample0;
+    double acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = mine[k];
+    const uint16_t* col = reinterpret_cast<const uint16_t*>(dense + b0) + x;
+    const int64_t pitch = bpv_pad / 2;
+    for (int64_t s0 = 0; s0 < snp_count; s0 += 256) {
+        const int cnt = static_cast<int>(snp_count - s0 < 256 ? snp_count - s0 : 256);
+        __syncthreads();
+        {
+            double4 w = make_double4(0.0, 0.0, 0.0, 0.0);
+            if (static_cast<int>(threadIdx.x) < cnt) {
+                const double2* src = reinterpret_cast<const double2*>(gcta_w + s0 + threadIdx.x);
+                const double2 w01 = __ldg(src), w23 = __ldg(src + 1);
+                w = make_double4(w01.x, 0.0, w23.x, w23.y);
+            }
+            reinterpret_cast<double4*>(s_w)[threadIdx.x] = w;
+        }
+        uint32_t word[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {  // SNPs past the end of the chunk read as "missing everywhere"
+            const int ul = y + 16 * i;
+            word[i] = ul < cnt ? static_cast<uint32_t>(__ldg(col + (s0 + ul) * pitch)) : 0x5555u;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const double* t = s_w + (y + 16 * i) * 4;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] += t[(word[i] >> (2 * k)) & 3u];
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) mine[k] = acc[k];
+    __syncthreads();  // the block's lane sums are in global memory and visible to the block
+    if (threadIdx.x < kGctaSamplesPerBlock) {
+        const int64_t sample = b0 * 4 + threadIdx.x;
+        double total = 0.0;
+#pragma unroll
+        for (int l = 0; l < kGctaLanes; ++l) total += lanes[static_cast<int64_t>(l) * n_pad + sample];
+        diag[sample] = total;
     }
 }
 

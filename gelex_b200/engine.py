@@ -42,6 +42,7 @@ def load_host():
         h.gelex_b200_gpus_worth_using.argtypes = [C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int]
         h.gelex_b200_piece_owners.argtypes = [C.c_int64, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
         h.gelex_b200_grm_run_gcta.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]
+        h.gelex_b200_grm_run_gcta_ex.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]
         vp = C.c_void_p
         h.gelex_b200_genotype_export.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, C.c_int64,
                                                  C.c_char_p, C.c_int]
@@ -220,14 +221,16 @@ def read_snp_stats(path):
     return {"num_samples": n, "num_variants": m, "monomorphic_indices": mono, "mean": mean, "stddev": sd}
 
 
-def grm_run_gcta(bfile, out_prefix, method="SH", chunk_size=10000, precision=_lib.PREC_FP16, n_gpus=1, writer_threads=4):
+def grm_run_gcta(bfile, out_prefix, method="SH", chunk_size=10000, precision=_lib.PREC_FP16, n_gpus=1, writer_threads=4,
+                 gcta_diag=False, partition="snp"):
     """GrmEngine with Config::gcta (SURVEY 8f-3): writes <out>.grm.bin (A_ij = G_ij / N_ij), <out>.grm.N.bin (N_ij = SNPs called in both
-    samples) and <out>.grm.id - the GCTA binary format the reference's docs name (docs/source/data_formats.rst:188-208)."""
+    samples) and <out>.grm.id - the GCTA binary format the reference's docs name (docs/source/data_formats.rst:188-208).
+    gcta_diag: GCTA's default diagonal instead of sum z^2 / N (method SH only); partition: "snp" | "tile" | "auto" when n_gpus > 1."""
     h = load_host()
     m = _lib.METHODS[method] if isinstance(method, str) else int(method)
     err = C.create_string_buffer(2048)
-    st = h.gelex_b200_grm_run_gcta(str(bfile).encode(), str(out_prefix).encode(), m, int(chunk_size), int(precision), int(n_gpus),
-                                   int(writer_threads), err, len(err))
+    st = h.gelex_b200_grm_run_gcta_ex(str(bfile).encode(), str(out_prefix).encode(), m, int(chunk_size), int(precision), int(n_gpus),
+                                      int(writer_threads), int(bool(gcta_diag)), {"auto": 0, "snp": 1, "tile": 2}[partition], err, len(err))
     if st != 0:
         raise EngineError(int(st), err.value.decode())
 

@@ -64,7 +64,12 @@ enum { GGRM_ALLMISS_REFERENCE_NAN = 0, GGRM_ALLMISS_SKIP = 1 };
 /* What the second accumulator (the `want_dom` slot, kind 1) holds: the dominance matrix of `method`, or the number of SNPs
  * non-missing in BOTH samples, N = M M^T with M = the 0/1 non-missing indicator (exact: integers < 2^24 in FP32) - the
  * `.grm.N.bin` matrix of the GCTA format. */
-enum { GGRM_SECOND_DOMINANCE = 0, GGRM_SECOND_NONMISSING = 1 };
+enum { GGRM_SECOND_DOMINANCE = 0, GGRM_SECOND_NONMISSING = 1,
+       /* as GGRM_SECOND_NONMISSING, and ggrm_fetch_gcta(which = 0) returns GCTA's DEFAULT diagonal (--make-grm-alg 0),
+        *   A_jj = 1 + (1 / N_jj) sum_i (x_ij^2 - (1 + 2 p_i) x_ij + 2 p_i^2) / (2 p_i (1 - p_i))     over the SNPs called in sample j,
+        * instead of sum z^2 / N: one more per-sample FP64 sum per SNP chunk (x = A1 count, p = A1 frequency; monomorphic SNPs skipped).
+        * Needs method GGRM_STANDARDIZE_HWE, whose off-diagonal sum (x_ij - 2p)(x_ik - 2p) / 2pq is GCTA's. */
+       GGRM_SECOND_NONMISSING_GCTA_DIAG = 2 };
 
 typedef struct ggrm_handle ggrm_t;
 
@@ -144,6 +149,17 @@ int ggrm_fetch(ggrm_t* h, int kind, int group, int64_t row_begin, int64_t row_co
  * called in both samples; the diagonal uses the same sum, not GCTA's inbreeding-based variant); which = 1: rows of N_ij.
  * Same row-major packed lower-triangle float32 layout as ggrm_fetch = the byte order of .grm.bin / .grm.N.bin. */
 int ggrm_fetch_gcta(ggrm_t* h, int which, int group, int64_t row_begin, int64_t row_count, float* out_lower_rows);
+/* The same read-out as a rectangular block (layout and ownership rules of ggrm_fetch_block): what the 2D-tile writer stores
+ * for the GCTA files.  Every rank of a 2D-tile run streams all SNPs, so its diagonal sums are complete without an exchange. */
+int ggrm_fetch_block_gcta(ggrm_t* h, int which, int group, int64_t row_begin, int64_t row_count, int64_t col_begin,
+                          int64_t col_count, float* out, int64_t ld);
+/* SNP shards with GGRM_SECOND_NONMISSING_GCTA_DIAG: every handle holds the per-sample diagonal sums of ITS SNPs.
+ * ggrm_gcta_diag_address gives the device address of that vector (n_out doubles, stable for the handle's life, final once
+ * the handle's pass is - e.g. when any of its band flags is up); ggrm_gcta_diag_reduce_async adds the peers' vectors to this
+ * handle's OWN sums into a separate total (on the read-out stream, so peers may do the same at the same time), which the
+ * GCTA read-outs that follow use. */
+int ggrm_gcta_diag_address(ggrm_t* h, void** d_ptr);
+int ggrm_gcta_diag_reduce_async(ggrm_t* h, const void* const* peers, int n_peers);
 
 /* 2D-tile mode read-out: the dense block rows [row_begin, +row_count) x columns [col_begin, +col_count) of the lower
  * triangle as float32 into `out` (host, caller-owned, row-major with leading dimension `ld` >= col_count elements).

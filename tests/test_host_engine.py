@@ -682,6 +682,10 @@ def test_gcta_flag_validation_needs_no_gpu(golden_dir, tmp_path):
     r = subprocess.run([str(engine.CLI_PATH), "grm", "-b", str(golden_dir / "tiny"), "--loco", "--gcta", "-o", str(tmp_path / "x")],
                        capture_output=True, text=True)
     assert r.returncode == 1 and not list(tmp_path.glob("x.grm*"))
+    for extra in (["--gcta", "--gcta-diag", "--geno-method", "OSH"], ["--gcta-diag"]):   # GCTA's diagonal: with --gcta and StandardizeHWE only
+        r = subprocess.run([str(engine.CLI_PATH), "grm", "-b", str(golden_dir / "tiny"), "--add", *extra, "-o", str(tmp_path / "x")],
+                           capture_output=True, text=True)
+        assert r.returncode == 1 and "--gcta-diag is GCTA's diagonal" in (r.stdout + r.stderr)
 
 
 @pytest.mark.gpu
