@@ -511,6 +511,11 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
         GGRM_CUDA(cudaMemsetAsync(h->d_counts, 0, static_cast<size_t>(cfg->m_total) * sizeof(int4), h->s_comp));
         GGRM_CUDA(cudaMemsetAsync(h->d_freq, 0, static_cast<size_t>(cfg->m_total) * sizeof(double), h->s_comp));
     }
+    // one launch for K1-K3 when the whole pass is one slab of few samples (nothing to overlap the prep with; see prep_fused_kernel)
+    h->fused_prep = !h->fp64 && h->n_pad <= 4096 && round_up(cfg->m_total, 64) <= k_cap;
+    if (const char* e = std::getenv("GGRM_FUSED_PREP")) h->fused_prep = std::atoi(e) != 0 && !h->fp64 && h->n_pad <= 4096;
+    if (h->fused_prep)
+        GGRM_CUDA(cudaFuncSetAttribute(prep_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(prep_fused_smem_bytes(h->bpv_pad))));
     if (cfg->second_matrix == GGRM_SECOND_NONMISSING_GCTA_DIAG) {
         dev_alloc(*h, &h->d_gcta_w, static_cast<size_t>(k_cap) * sizeof(double4), "GCTA diagonal terms of a chunk");
         dev_alloc(*h, &h->d_gcta_lanes, static_cast<size_t>(kGctaLanes * h->n_pad) * sizeof(double), "GCTA diagonal lane sums");

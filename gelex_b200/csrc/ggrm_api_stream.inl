@@ -251,10 +251,6 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
     GGRM_CUDA(cudaStreamWaitEvent(sp, h.z_free[zb], 0));  // the SYRKs of two slabs ago have finished reading Z[.][zb]
     start_group(h, g, h.fp64);
 
-    size_t ti = phase_begin(h, sp, 1);
-    repack_kernel<<<repack_grid(c, h.bpv_pad), 256, 0, sp>>>(h.d_raw[b], h.bpv_raw, h.d_dense, h.bpv_pad, h.n_out, h.d_out_to_raw, c);
-    GGRM_CUDA(cudaGetLastError());
-    GGRM_CUDA(cudaEventRecord(h.raw_free[b], sp));
     StatsOut so{};
     so.counts = h.d_counts;
     so.freq = h.d_freq;
@@ -266,10 +262,26 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
         so.tab16_lo[kind] = h.op_split && h.d_tab16[kind] != nullptr ? h.d_tab16[kind] + h.k_cap : nullptr;
         so.tab64[kind] = h.d_tab64[kind];
     }
-    count_stats_kernel<<<static_cast<unsigned>((c + 7) / 8), 256, 0, sp>>>(
-        h.d_dense, h.bpv_pad, h.n_out, h.n_pad, c, h.cfg.method, h.cfg.all_missing_policy,
-        h.cfg.precision == GGRM_PREC_FP16 ? 1 : 0, so, h.cur_first_snp);
-    GGRM_CUDA(cudaGetLastError());
+    const int64_t z_pitch = h.op_split ? 2 * h.k_cap : h.k_cap;  // hi in columns [0, k_cap), lo in [k_cap, 2 k_cap)
+    size_t ti = phase_begin(h, sp, 1);
+    if (h.fused_prep) {
+        prep_fused_kernel<<<static_cast<unsigned>((c + 63) / 64), 256, prep_fused_smem_bytes(h.bpv_pad), sp>>>(
+            h.d_raw[b], h.bpv_raw, h.d_dense, h.bpv_pad, h.n_out, h.n_pad, h.d_out_to_raw, c, h.cfg.method, h.cfg.all_missing_policy,
+            h.cfg.precision == GGRM_PREC_FP16 ? 1 : 0, so, h.cur_first_snp, static_cast<uint16_t*>(h.d_Z[0][zb]), static_cast<uint16_t*>(h.d_Z[1][zb]), z_pitch,
+            h.op_split ? h.k_cap : 0);
+        GGRM_CUDA(cudaGetLastError());
+        GGRM_CUDA(cudaEventRecord(h.raw_free[b], sp));
+        ++h.kernel_launches;
+    } else {
+        repack_kernel<<<repack_grid(c, h.bpv_pad), 256, 0, sp>>>(h.d_raw[b], h.bpv_raw, h.d_dense, h.bpv_pad, h.n_out, h.d_out_to_raw, c);
+        GGRM_CUDA(cudaGetLastError());
+        GGRM_CUDA(cudaEventRecord(h.raw_free[b], sp));
+        count_stats_kernel<<<static_cast<unsigned>((c + 7) / 8), 256, 0, sp>>>(
+            h.d_dense, h.bpv_pad, h.n_out, h.n_pad, c, h.cfg.method, h.cfg.all_missing_policy,
+            h.cfg.precision == GGRM_PREC_FP16 ? 1 : 0, so, h.cur_first_snp);
+        GGRM_CUDA(cudaGetLastError());
+        h.kernel_launches += 2;
+    }
     if (h.d_gcta_w != nullptr) {  // GGRM_SECOND_NONMISSING_GCTA_DIAG: this chunk's share of the per-sample diagonal sums
         gcta_diag_kernel<<<static_cast<unsigned>(h.n_pad / kGctaSamplesPerBlock), 256, 0, sp>>>(h.d_dense, h.bpv_pad, h.d_gcta_w, c, h.cur_first_snp, h.n_pad, h.d_gcta_lanes,
                                                                                  h.d_gcta_diag);
@@ -277,16 +289,14 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
         ++h.kernel_launches;
     }
     phase_end(h, sp, ti);
-    h.kernel_launches += 2;
 
     const dim3 egrid(static_cast<unsigned>((c + 63) / 64), static_cast<unsigned>(h.bpv_pad / 64));
     ti = phase_begin(h, sp, 2);
-    for (int kind = 0; kind < 2; ++kind) {
+    for (int kind = 0; kind < 2 && !h.fused_prep; ++kind) {
         if (h.d_Z[kind][zb] == nullptr) continue;
         if (h.fp64)
             expand64_kernel<<<egrid, 256, 0, sp>>>(h.d_dense, h.bpv_pad, h.d_tab64[kind], c, static_cast<double*>(h.d_Z[kind][zb]), h.k_cap);
         else {
-            const int64_t z_pitch = h.op_split ? 2 * h.k_cap : h.k_cap;  // hi in columns [0, k_cap), lo in [k_cap, 2 k_cap)
             expand16_kernel<<<egrid, 256, 0, sp>>>(h.d_dense, h.bpv_pad, h.d_tab16[kind], c, static_cast<uint16_t*>(h.d_Z[kind][zb]), z_pitch);
             if (h.op_split) {
                 GGRM_CUDA(cudaGetLastError());

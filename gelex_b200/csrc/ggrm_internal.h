@@ -127,6 +127,7 @@ struct Handle {
     int64_t push_end_hint = -1;                                    // ggrm_set_push_end: no SNP >= this will be pushed (-1: the last group's end)
     int z_buf = 0;
     bool overlap_prep = true;                                      // GGRM_OVERLAP_PREP=0: run K1-K3 on s_comp (serial)
+    bool fused_prep = false;                                       // K1-K3 as one launch (prep_fused_kernel): single-slab passes of few samples; GGRM_FUSED_PREP=0/1
     // pinned staging ring (pageable callers)
     static constexpr int kRingSlots = 4;
     uint8_t* ring[kRingSlots] = {nullptr, nullptr, nullptr, nullptr};

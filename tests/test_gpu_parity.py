@@ -856,3 +856,48 @@ def test_fp16_overflow_is_reported_and_bf16_stays_finite():
             assert np.all(np.isfinite(got))
             ref = R[a, : r + 1]
             assert np.max(np.abs(got - ref)) <= 1e-4 * np.max(np.abs(ref)) + 1e-3, r
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("precision", [g.PREC_FP16, g.PREC_BF16])
+def test_fused_prep_launch_is_bit_identical_to_the_three_kernels(monkeypatch, precision):
+    # single-slab passes of few samples run K1-K3 as ONE launch (prep_fused_kernel); the separate kernels stay the path of every
+    # other shape.  Same device functions on the same bytes: operands, statistics and therefore the accumulators are bit-identical.
+    rng = np.random.default_rng(17)
+    cases = [
+        dict(n=515, m=900, kw=dict(method="OSH", want_add=True, want_dom=True)),                       # ragged n, two kinds
+        dict(n=2000, m=3000, kw=dict(method="SH", want_add=True, want_dom=True, second_matrix=2)),     # GCTA counts + diagonal terms
+        dict(n=3100, m=130, kw=dict(method="OC", want_add=False, want_dom=True), drop=200),            # projection with dropped samples, m % 64 != 0
+        dict(n=4096, m=257, kw=dict(method="S", want_add=True, want_dom=False)),                       # the largest sample count the launch takes
+    ]
+    for case in cases:
+        n, m, kw = case["n"], case["m"], dict(case["kw"])
+        bed = g.synth_bed_host(n, 0, m, 1234 + n, 0.03)
+        n_out = n
+        if "drop" in case:
+            r2o = rng.permutation(n).astype(np.int32)
+            n_out = n - case["drop"]
+            r2o[r2o >= n_out] = -1
+            kw.update(raw_to_out=r2o, n_out=n_out)
+        got = {}
+        for fused in ("0", "1"):
+            monkeypatch.setenv("GGRM_FUSED_PREP", fused)
+            with g.Accumulator(n, m, precision=precision, keep_stats=True, **kw) as acc:
+                acc.push(bed[: m // 3], 0)
+                acc.push(bed[m // 3:], m // 3)
+                acc.finish()
+                out = [acc.fetch(k, g.GROUP_WHOLE)[0] for k in (0, 1) if (kw.get("want_add", True), kw.get("want_dom", False))[k]]
+                out += list(acc.snp_stats(0, m))
+                if kw.get("second_matrix") == 2:
+                    out.append(acc.fetch_gcta(0))
+                launches = acc.timers()["kernel_launches"]
+            got[fused] = (out, launches)
+        assert got["1"][1] < got["0"][1], "the fused launch replaces at least two"
+        for a, b in zip(got["0"][0], got["1"][0]):
+            assert np.array_equal(a, b, equal_nan=True), (n, m)
+    monkeypatch.delenv("GGRM_FUSED_PREP")
+    # more samples than the launch holds in shared memory, or more than one slab: the separate kernels, whatever the environment says
+    with g.Accumulator(4100, 100, method="SH", precision=precision) as acc:
+        acc.push(g.synth_bed_host(4100, 0, 100, 5, 0.0), 0)
+        acc.finish()
+        assert acc.timers()["kernel_launches"] >= 4
