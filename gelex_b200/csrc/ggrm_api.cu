@@ -514,6 +514,7 @@ static void create_impl(const ggrm_config_t* cfg, Handle* h) {
     // one launch for K1-K3 when the whole pass is one slab of few samples (nothing to overlap the prep with; see prep_fused_kernel)
     h->fused_prep = !h->fp64 && h->n_pad <= 4096 && round_up(cfg->m_total, 64) <= k_cap;
     if (const char* e = std::getenv("GGRM_FUSED_PREP")) h->fused_prep = std::atoi(e) != 0 && !h->fp64 && h->n_pad <= 4096;
+    if (const char* e = std::getenv("GGRM_DIRECT_SRC")) h->direct_src_ok = std::atoi(e) != 0;
     if (h->fused_prep)
         GGRM_CUDA(cudaFuncSetAttribute(prep_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(prep_fused_smem_bytes(h->bpv_pad))));
     if (cfg->second_matrix == GGRM_SECOND_NONMISSING_GCTA_DIAG) {

@@ -132,6 +132,8 @@ extern "C" int ggrm_stage_slot(ggrm_stage_t* ss, int slot, const uint8_t** d_ptr
 extern "C" int ggrm_wait_copies(ggrm_t* hh) {
     Handle* h = reinterpret_cast<Handle*>(hh);
     GGRM_API_BEGIN(h)
+    materialize_direct_src(*h);  // a payload registered in place is copied now: the caller wants its memory back
     GGRM_CUDA(cudaStreamSynchronize(h->s_copy));
+    for (auto& ev : h->raw_free) GGRM_CUDA(cudaEventSynchronize(ev));  // ... and a fused prep launch that reads one in place has run
     GGRM_API_END(h)
 }

@@ -27,6 +27,17 @@ static void collect_timers(Handle& h) {
             prev = &t;
         }
         std::fprintf(stderr, "[ggrm] SYRK gaps: %d gaps, total %.3f ms\n", n, gap_sum);
+        if (h.pass_begin != nullptr && h.timers.size() <= 16) {  // short passes: every timed phase against the start of the pass
+            static const char* names[] = {"copy", "prep", "expand", "syrk", "fetch", "5", "6"};
+            for (auto& t : h.timers) {
+                float a = 0.f, b = 0.f;
+                if (cudaEventElapsedTime(&a, h.pass_begin, t.a) == cudaSuccess && cudaEventElapsedTime(&b, h.pass_begin, t.b) == cudaSuccess)
+                    std::fprintf(stderr, "[ggrm]   %-7s %8.1f .. %8.1f us\n", names[t.phase < 7 ? t.phase : 6], a * 1e3, b * 1e3);
+            }
+            float e = 0.f;
+            if (h.pass_end != nullptr && cudaEventElapsedTime(&e, h.pass_begin, h.pass_end) == cudaSuccess) std::fprintf(stderr, "[ggrm]   pass end %8.1f us\n", e * 1e3);
+            cudaGetLastError();
+        }
     }
     std::vector<Timer> pending;  // still running (ggrm_finish_async + partial read-out): collected by a later call
     for (auto& t : h.timers) {
@@ -238,14 +249,17 @@ static void accumulate_slabs(Handle& h, int g, bool banded) {
     h.deferred.clear();
 }
 
+// K1-K3 of a slab run on s_prep, beside the previous slab's SYRK (which owns s_comp); the serial mode (GGRM_OVERLAP_PREP=0) and
+// the fused single-slab launch - nothing to run beside, and one event hop less in front of the only SYRK launch - use s_comp
+static cudaStream_t prep_stream(const Handle& h) { return h.overlap_prep && !h.fused_prep ? h.s_prep : h.s_comp; }
+
 static void flush_chunk(Handle& h, bool final_flush = false) {
     if (h.cur_count == 0) return;
     const int b = h.cur_buf;
     const int zb = h.z_buf;
     const int64_t c = h.cur_count;
     const int g = h.cur_group;
-    // K1-K3 of this slab run on s_prep (beside the previous slab's SYRK, which owns s_comp); serial mode uses s_comp for both
-    cudaStream_t sp = h.overlap_prep ? h.s_prep : h.s_comp;
+    cudaStream_t sp = prep_stream(h);
     GGRM_CUDA(cudaEventRecord(h.h2d_done, h.s_copy));
     GGRM_CUDA(cudaStreamWaitEvent(sp, h.h2d_done, 0));
     GGRM_CUDA(cudaStreamWaitEvent(sp, h.z_free[zb], 0));  // the SYRKs of two slabs ago have finished reading Z[.][zb]
@@ -266,12 +280,13 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
     size_t ti = phase_begin(h, sp, 1);
     if (h.fused_prep) {
         prep_fused_kernel<<<static_cast<unsigned>((c + 63) / 64), 256, prep_fused_smem_bytes(h.bpv_pad), sp>>>(
-            h.d_raw[b], h.bpv_raw, h.d_dense, h.bpv_pad, h.n_out, h.n_pad, h.d_out_to_raw, c, h.cfg.method, h.cfg.all_missing_policy,
+            h.direct_src != nullptr ? h.direct_src : h.d_raw[b], h.bpv_raw, h.d_dense, h.bpv_pad, h.n_out, h.n_pad, h.d_out_to_raw, c, h.cfg.method, h.cfg.all_missing_policy,
             h.cfg.precision == GGRM_PREC_FP16 ? 1 : 0, so, h.cur_first_snp, static_cast<uint16_t*>(h.d_Z[0][zb]), static_cast<uint16_t*>(h.d_Z[1][zb]), z_pitch,
             h.op_split ? h.k_cap : 0);
         GGRM_CUDA(cudaGetLastError());
         GGRM_CUDA(cudaEventRecord(h.raw_free[b], sp));
         ++h.kernel_launches;
+        h.direct_src = nullptr;
     } else {
         repack_kernel<<<repack_grid(c, h.bpv_pad), 256, 0, sp>>>(h.d_raw[b], h.bpv_raw, h.d_dense, h.bpv_pad, h.n_out, h.d_out_to_raw, c);
         GGRM_CUDA(cudaGetLastError());
@@ -291,7 +306,7 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
     phase_end(h, sp, ti);
 
     const dim3 egrid(static_cast<unsigned>((c + 63) / 64), static_cast<unsigned>(h.bpv_pad / 64));
-    ti = phase_begin(h, sp, 2);
+    if (!h.fused_prep) ti = phase_begin(h, sp, 2);  // (the fused launch did K3 already: no empty phase, its two event records cost ~5 us of a 0.25 ms pass)
     for (int kind = 0; kind < 2 && !h.fused_prep; ++kind) {
         if (h.d_Z[kind][zb] == nullptr) continue;
         if (h.fp64)
@@ -308,7 +323,7 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
         GGRM_CUDA(cudaGetLastError());
         ++h.kernel_launches;
     }
-    phase_end(h, sp, ti);
+    if (!h.fused_prep) phase_end(h, sp, ti);
     GGRM_CUDA(cudaEventRecord(h.prep_done[zb], sp));
 
     // K4.  A slab among the last tail_slabs of the pass is only parked here (its operands stay resident in their ring buffer);
@@ -336,6 +351,24 @@ static void flush_chunk(Handle& h, bool final_flush = false) {
     h.cur_count = 0;
     h.cur_first_snp = -1;
     GGRM_CUDA(cudaStreamWaitEvent(h.s_copy, h.raw_free[h.cur_buf], 0));
+}
+
+// true when p is memory of this handle's own device (a peer's memory is copied: the copy engine does not need peer access)
+static bool device_pointer_is_local(const Handle& h, const uint8_t* p) {
+    cudaPointerAttributes attr{};
+    if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return attr.type == cudaMemoryTypeDevice && attr.device == h.cfg.device;
+}
+
+// The slab being filled was registered in place (Handle::direct_src) and something else wants the chunk buffer or the source
+// back: copy it now, as the ordinary path would have.
+static void materialize_direct_src(Handle& h) {
+    if (h.direct_src == nullptr) return;
+    GGRM_CUDA(cudaMemcpyAsync(h.d_raw[h.cur_buf], h.direct_src, static_cast<size_t>(h.cur_count * h.bpv_raw), cudaMemcpyDeviceToDevice, h.s_copy));
+    h.direct_src = nullptr;
 }
 
 static void copy_rows(Handle& h, const uint8_t* src, bool src_is_device, bool src_is_pinned, int64_t rows, uint8_t* dst) {
@@ -394,7 +427,7 @@ static void push_impl(Handle& h, const uint8_t* payload, bool is_device, int64_t
         GGRM_CUDA(cudaEventRecord(h.pass_begin, h.s_copy));
         h.pass_open = true;
     }
-    const size_t tcopy = phase_begin(h, h.s_copy, 0);
+    size_t tcopy = SIZE_MAX;  // the copy phase is timed from its first copy (a payload read in place enqueues none)
     const int64_t end = snp_begin + snp_count;
     int64_t s = snp_begin;
     while (s < end) {
@@ -438,12 +471,22 @@ static void push_impl(Handle& h, const uint8_t* payload, bool is_device, int64_t
                 h.cur_trailing = h.tail_slabs > 0 && g + 1 == static_cast<int>(h.groups.size()) && pieces <= tail;
             }
             const int64_t take = std::min(run_end - s, h.cur_cap - h.cur_count);
-            copy_rows(h, payload + (s - snp_begin) * h.bpv_raw, is_device, pinned, take, h.d_raw[h.cur_buf] + h.cur_count * h.bpv_raw);
+            const uint8_t* src = payload + (s - snp_begin) * h.bpv_raw;
+            // one device-resident push that is the whole single-slab pass: the fused prep launch reads it where it lies (no 2 x 25 MB
+            // copy in front of a 0.25 ms pass at C1); anything else is copied into the chunk buffer as before
+            if (is_device && h.fused_prep && h.direct_src_ok && h.cur_count == 0 && s == h.groups[g].begin && take == h.groups[g].end - s &&
+                device_pointer_is_local(h, src)) {
+                h.direct_src = src;
+            } else {
+                if (tcopy == SIZE_MAX) tcopy = phase_begin(h, h.s_copy, 0);
+                materialize_direct_src(h);
+                copy_rows(h, src, is_device, pinned, take, h.d_raw[h.cur_buf] + h.cur_count * h.bpv_raw);
+            }
             h.cur_count += take;
             s += take;
         }
     }
-    phase_end(h, h.s_copy, tcopy);
+    if (tcopy != SIZE_MAX) phase_end(h, h.s_copy, tcopy);
     h.last_snp_pushed = end - 1;
 }
 
@@ -531,11 +574,12 @@ static void reset_impl(Handle& h) {
             GGRM_CUDA(cudaMemsetAsync(h.whole[kind], 0, static_cast<size_t>(std::max<int64_t>(h.accum_elems, 4)) * h.elem_bytes, h.s_comp));
     }
     if (h.d_gcta_diag != nullptr) {  // the streams are idle (finish_sync); the next pass's first chunk adds to it on the prep stream
-        cudaStream_t sp = h.overlap_prep ? h.s_prep : h.s_comp;
+        cudaStream_t sp = prep_stream(h);
         GGRM_CUDA(cudaMemsetAsync(h.d_gcta_lanes, 0, static_cast<size_t>(kGctaLanes * h.n_pad) * sizeof(double), sp));
         GGRM_CUDA(cudaMemsetAsync(h.d_gcta_diag, 0, static_cast<size_t>(h.n_pad) * sizeof(double), sp));
         h.gcta_total_valid = false;
     }
+    h.direct_src = nullptr;
     h.cur_count = 0;
     h.cur_first_snp = -1;
     h.cur_group = -1;

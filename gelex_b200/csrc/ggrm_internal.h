@@ -127,6 +127,8 @@ struct Handle {
     int64_t push_end_hint = -1;                                    // ggrm_set_push_end: no SNP >= this will be pushed (-1: the last group's end)
     int z_buf = 0;
     bool overlap_prep = true;                                      // GGRM_OVERLAP_PREP=0: run K1-K3 on s_comp (serial)
+    const uint8_t* direct_src = nullptr;                           // fused prep: the slab being filled IS this device payload (one push = the whole pass): read in place
+    bool direct_src_ok = true;                                     // GGRM_DIRECT_SRC=0: always copy
     bool fused_prep = false;                                       // K1-K3 as one launch (prep_fused_kernel): single-slab passes of few samples; GGRM_FUSED_PREP=0/1
     // pinned staging ring (pageable callers)
     static constexpr int kRingSlots = 4;

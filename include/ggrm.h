@@ -109,7 +109,9 @@ const char* ggrm_last_error(const ggrm_t* h); /* h may be NULL: error of the las
  * pageable memory is staged through the library's pinned ring (may block while the ring is full); memory that is
  * already pinned (cudaHostRegister/cudaHostAlloc) is copied from directly and must stay valid until ggrm_finish. */
 int ggrm_push(ggrm_t* h, const uint8_t* bed_payload, int64_t snp_begin, int64_t snp_count, int64_t bytes_per_variant);
-/* Same, payload already resident in device memory of cfg.device (used by bench.py's HBM-resident leg). */
+/* Same, payload already resident in device memory of cfg.device (used by bench.py's HBM-resident leg).  The payload must stay
+ * valid until ggrm_wait_copies or ggrm_finish has returned: it is normally copied on the copy stream, and a pass that is ONE slab
+ * of few samples handed over in ONE call (the fused K1-K3 launch, n_pad <= 4096) reads it in place instead of copying it. */
 int ggrm_push_device(ggrm_t* h, const uint8_t* d_bed_payload, int64_t snp_begin, int64_t snp_count,
                      int64_t bytes_per_variant);
 /* Drain: every pushed SNP is accumulated, every group is complete.  Blocks until the device is idle. */

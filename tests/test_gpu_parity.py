@@ -901,3 +901,59 @@ def test_fused_prep_launch_is_bit_identical_to_the_three_kernels(monkeypatch, pr
         acc.push(g.synth_bed_host(4100, 0, 100, 5, 0.0), 0)
         acc.finish()
         assert acc.timers()["kernel_launches"] >= 4
+
+
+@pytest.mark.gpu
+def test_device_payload_read_in_place_matches_the_copied_one(monkeypatch):
+    # one ggrm_push_device call that is the whole single-slab pass is read where it lies by the fused prep launch (no copy into the
+    # chunk buffer); ggrm_wait_copies hands the memory back early by making the copy after all.  Same bits every way.
+    import torch
+
+    n, m = 1000, 4000
+    bed = g.synth_bed_host(n, 0, m, 99, 0.02)
+    d_bed = torch.from_numpy(bed).cuda()
+    torch.cuda.synchronize()
+
+    def run(mode):
+        with g.Accumulator(n, m, method="SH", precision=g.PREC_FP16, keep_stats=True) as acc:
+            if mode == "two pushes":        # not the whole pass in one call: copied
+                acc.push_device(d_bed.data_ptr(), 0, m // 2)
+                acc.push_device(d_bed.data_ptr() + (m // 2) * bed.shape[1], m // 2, m - m // 2)
+            elif mode == "wait_copies":     # registered in place, then claimed back before the pass runs
+                scratch = d_bed.clone()
+                torch.cuda.synchronize()
+                acc.push_device(scratch.data_ptr(), 0, m)
+                acc.wait_copies()
+                scratch.fill_(0x55)          # the caller's memory is its own again: all missing now
+                torch.cuda.synchronize()
+            else:
+                acc.push_device(d_bed.data_ptr(), 0, m)
+            acc.finish()
+            out = acc.fetch(0, g.GROUP_WHOLE)[0]
+            launches = acc.timers()["kernel_launches"]
+            # a second pass over the same handle
+            acc.reset()
+            acc.push_device(d_bed.data_ptr(), 0, m)
+            acc.finish()
+            again = acc.fetch(0, g.GROUP_WHOLE)[0]
+        assert np.array_equal(out, again)
+        return out, launches
+
+    monkeypatch.setenv("GGRM_DIRECT_SRC", "0")
+    copied, _ = run("one push")
+    monkeypatch.delenv("GGRM_DIRECT_SRC")
+    assert np.all(np.isfinite(copied)) and copied.any()
+    for mode in ("one push", "two pushes", "wait_copies"):
+        got, _ = run(mode)
+        assert np.array_equal(got, copied), mode
+    # LOCO groups inside one slab: every group's push range is registered and flushed on its own
+    groups = [(0, 1500), (1500, 4000)]
+    res = []
+    for direct in ("0", "1"):
+        monkeypatch.setenv("GGRM_DIRECT_SRC", direct)
+        with g.Accumulator(n, m, method="SH", precision=g.PREC_FP16, groups=groups, keep_whole=True) as acc:
+            acc.push_device(d_bed.data_ptr(), 0, m)
+            acc.finish()
+            res.append([acc.fetch(0, gi)[0] for gi in (0, 1, g.GROUP_WHOLE)])
+    for a, b in zip(*res):
+        assert np.array_equal(a, b)
