@@ -74,6 +74,50 @@ extern "C" int gelex_b200_grm_run_ex(const char* bfile, const char* out_prefix, 
     }
 }
 
+// gelex_b200_grm_run_ex with the observer's events recorded: events3 receives up to cap triples (type, a, b) in the order the observer
+// saw them - 0 GrmDataLoadedEvent (samples, snps), 1 GrmComputeStartedEvent (total_snps, 0), 2 GrmProgressEvent (current, total),
+// 3 GrmProgressEvent with done (current, total), 4 GrmFilesWrittenEvent (num_files, 0) - and *n_events their number.
+extern "C" int gelex_b200_grm_run_events(const char* bfile, const char* out_prefix, int method, int mode, int do_loco, int chunk_size,
+                                         int precision, int n_gpus, int64_t* events3, int64_t cap, int64_t* n_events, char* err, int err_len) {
+    try {
+        if (bfile == nullptr || out_prefix == nullptr || n_events == nullptr) throw ArgumentValidationException("null argument");
+        if (method < 1 || method > 8) throw InvalidInputException("Invalid genotype process method.");
+        GrmEngine::Config cfg;
+        cfg.bed_path = format_bed_path(bfile);
+        cfg.mode = mode == 2 ? GrmType::AD : (mode == 1 ? GrmType::D : GrmType::A);
+        cfg.method = static_cast<GenotypeProcessMethod>(method);
+        cfg.do_loco = do_loco != 0;
+        cfg.out_prefix = out_prefix;
+        cfg.chunk_size = chunk_size;
+        cfg.precision = precision;
+        cfg.gpus.clear();
+        const char* over = std::getenv("GELEX_B200_OVERSUBSCRIBE");
+        const int devs = ggrm_device_count();
+        for (int i = 0; i < (n_gpus > 0 ? n_gpus : 1); ++i) cfg.gpus.push_back(over != nullptr && over[0] == '1' && devs > 0 ? i % devs : i);
+        int64_t count = 0;
+        auto put = [&](int64_t type, size_t a, size_t b) {
+            if (events3 != nullptr && count < cap) {
+                events3[3 * count] = type;
+                events3[3 * count + 1] = static_cast<int64_t>(a);
+                events3[3 * count + 2] = static_cast<int64_t>(b);
+            }
+            ++count;
+        };
+        GrmEngine engine(cfg);
+        engine.compute([&](const GrmEvent& ev) {
+            if (const auto* e = std::get_if<GrmDataLoadedEvent>(&ev)) put(0, e->num_samples, e->num_snps);
+            else if (const auto* e = std::get_if<GrmComputeStartedEvent>(&ev)) put(1, e->total_snps, 0);
+            else if (const auto* e = std::get_if<GrmProgressEvent>(&ev)) put(e->done ? 3 : 2, e->current, e->total);
+            else if (const auto* e = std::get_if<GrmFilesWrittenEvent>(&ev)) put(4, e->num_files, 0);
+        });
+        *n_events = count;
+        set_err(err, err_len, "");
+        return 0;
+    } catch (...) {
+        return translate_exception(err, err_len);
+    }
+}
+
 // Metadata-only entry (no GPU needed): sample order, projection and chromosome runs as the engine will use them.
 // ids_out: n_out lines "FID\tIID\n" (the .id payload) written into buf (truncated to buf_len); returns n_out or < 0.
 extern "C" int64_t gelex_b200_plan(const char* bfile, int mode, int do_loco, int32_t* raw_to_out, int64_t raw_cap, int64_t* n_raw_out,

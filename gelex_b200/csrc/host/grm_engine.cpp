@@ -639,21 +639,39 @@ ggrm_t* create_handle(const RunContext& rc, int device, const std::vector<int>& 
     return h;
 }
 
+// Progress of a work item.  The reference runs the dominance item of a SNP range AFTER its additive item (grm_work_plan.cpp:94-103,
+// 139-149: per group, one item per task) and each item reports (current, total) chunk by chunk (grm.h:124-130).  One pass computes
+// both matrices here, so the additive item's events go out as the pass advances and the dominance item's - the same sequence once
+// more - are replayed when the pass over the range is complete: an observer sees the events of the reference in the reference's order.
+using ProgressReplay = std::vector<std::pair<size_t, size_t>>;
+
+void emit_progress_locked(const RunContext& rc, size_t current, size_t total, ProgressReplay& replay) {
+    (*rc.observer)(GrmProgressEvent{current, total, false});
+    const int kinds = (rc.want_add ? 1 : 0) + (rc.want_dom && !rc.gcta ? 1 : 0);
+    if (kinds < 2) return;
+    if (!replay.empty() && current <= replay.back().first) replay.clear();  // an item that was abandoned (exception) left its events behind
+    replay.emplace_back(current, total);
+    if (current == total) {
+        for (const auto& e : replay) (*rc.observer)(GrmProgressEvent{e.first, e.second, false});
+        replay.clear();
+    }
+}
+
 void emit_progress(const RunContext& rc, size_t current, size_t total) {
     if (rc.observer == nullptr || !*rc.observer) return;
+    thread_local ProgressReplay replay;  // a GPU thread works through its items one after the other
     std::lock_guard<std::mutex> lk(*rc.mu);
-    const int kinds = (rc.want_add ? 1 : 0) + (rc.want_dom && !rc.gcta ? 1 : 0);
-    for (int k = 0; k < kinds; ++k) (*rc.observer)(GrmProgressEvent{current, total, false});
+    emit_progress_locked(rc, current, total, replay);
 }
 
 // SNP shards of ONE work item on several GPUs: the observer was told the item has `total` SNPs (GrmComputeStartedEvent), so the
 // ranks report against one shared counter - (sum over ranks, total), monotone because the counter moves under the observer's lock.
-void emit_progress_shared(const RunContext& rc, int64_t* shared_done, int64_t step, size_t total) {
+void emit_progress_shared(const RunContext& rc, int64_t* shared_done, int64_t step, size_t total, ProgressReplay* replay) {
     std::lock_guard<std::mutex> lk(*rc.mu);
     *shared_done += step;
     if (rc.observer == nullptr || !*rc.observer) return;
-    const int kinds = (rc.want_add ? 1 : 0) + (rc.want_dom && !rc.gcta ? 1 : 0);
-    for (int k = 0; k < kinds; ++k) (*rc.observer)(GrmProgressEvent{static_cast<size_t>(*shared_done), total, false});
+    ProgressReplay none;
+    emit_progress_locked(rc, static_cast<size_t>(*shared_done), total, replay != nullptr ? *replay : none);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -795,7 +813,7 @@ class BedRelay {
 
 // Push SNPs [begin, end) in host chunks of cfg.chunk_size (the reference's load_chunk granularity); through the relay when there is one.
 void push_range(const RunContext& rc, ggrm_t* h, int64_t begin, int64_t end, int64_t item_total, int64_t* item_done, bool report = true,
-                BedRelay* relay = nullptr, int64_t* shared_done = nullptr) {
+                BedRelay* relay = nullptr, int64_t* shared_done = nullptr, ProgressReplay* shared_replay = nullptr) {
     for (int64_t s = begin; s < end; s += rc.cfg->chunk_size) {
         const int64_t c = std::min<int64_t>(rc.cfg->chunk_size, end - s);
         if (s < 0 || s + c > rc.m || c <= 0)  // validate_chunk_range, bed_pipe.cpp:38-52
@@ -808,7 +826,7 @@ void push_range(const RunContext& rc, ggrm_t* h, int64_t begin, int64_t end, int
             check(h, ggrm_push(h, p, s, c, rc.bpv));
         }
         *item_done += c;
-        if (report && shared_done != nullptr) emit_progress_shared(rc, shared_done, c, static_cast<size_t>(item_total));
+        if (report && shared_done != nullptr) emit_progress_shared(rc, shared_done, c, static_cast<size_t>(item_total), shared_replay);
         else if (report) emit_progress(rc, static_cast<size_t>(*item_done), static_cast<size_t>(item_total));
     }
 }
@@ -1170,6 +1188,7 @@ struct ShardPipe {
     int n_bands = 1;
     std::atomic<bool> failed{false};
     int64_t snps_done = 0;                        // over all ranks (progress events; guarded by the observer's mutex)
+    ProgressReplay replay;                        // ... and the second item's events of an A + D run (emit_progress_locked)
 };
 
 void run_pipelined_rank(const RunContext& rc, ShardPipe& sp, size_t r, double* pass_ms, double* syrk_ms) {
@@ -1182,7 +1201,7 @@ void run_pipelined_rank(const RunContext& rc, ShardPipe& sp, size_t r, double* p
     BinFile files[2];
     int64_t done = 0;
     const auto t_push = Clock::now();
-    push_range(rc, h, sp.snps[r].first, sp.snps[r].second, rc.m, &done, true, nullptr, &sp.snps_done);
+    push_range(rc, h, sp.snps[r].first, sp.snps[r].second, rc.m, &done, true, nullptr, &sp.snps_done, &sp.replay);
     check(h, ggrm_finish_async(h));
     const auto t0 = Clock::now();
     note_phase(rc, "push", t_push, t0);

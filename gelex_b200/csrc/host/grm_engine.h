@@ -163,6 +163,9 @@ extern "C" int gelex_b200_grm_run_ex(const char* bfile, const char* out_prefix, 
                                      int precision, int n_gpus, int write_whole, int partition, int writer_threads, char* err, int err_len);
 extern "C" int gelex_b200_grm_run(const char* bfile, const char* out_prefix, int method, int mode, int do_loco, int chunk_size,
                                   int precision, int n_gpus, int write_whole, char* err, int err_len);
+// gelex_b200_grm_run_ex (one partition rule: auto) with the observer's events recorded as (type, a, b) triples; see capi.cpp.
+extern "C" int gelex_b200_grm_run_events(const char* bfile, const char* out_prefix, int method, int mode, int do_loco, int chunk_size,
+                                         int precision, int n_gpus, int64_t* events3, int64_t cap, int64_t* n_events, char* err, int err_len);
 // Config::gcta run (GCTA binary format out); see capi.cpp.
 extern "C" int gelex_b200_grm_run_gcta(const char* bfile, const char* out_prefix, int method, int chunk_size, int precision, int n_gpus,
                                        int writer_threads, char* err, int err_len);

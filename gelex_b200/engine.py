@@ -41,6 +41,8 @@ def load_host():
         h.gelex_b200_strip_owners.argtypes = [C.c_int64, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
         h.gelex_b200_gpus_worth_using.argtypes = [C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int]
         h.gelex_b200_piece_owners.argtypes = [C.c_int64, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        h.gelex_b200_grm_run_events.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int64,
+                                                C.POINTER(C.c_int64), C.c_char_p, C.c_int]
         h.gelex_b200_grm_run_gcta.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]
         h.gelex_b200_grm_run_gcta_ex.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]
         vp = C.c_void_p
@@ -98,6 +100,24 @@ def grm_run(bfile, out_prefix, method="OSH", mode="A", loco=False, chunk_size=10
                                  int(n_gpus), int(write_whole), PARTITIONS[partition], int(writer_threads), err, len(err))
     if st != 0:
         raise EngineError(st, err.value.decode())
+
+
+EVENT_NAMES = {0: "data_loaded", 1: "compute_started", 2: "progress", 3: "progress_done", 4: "files_written"}
+
+
+def grm_run_events(bfile, out_prefix, method="OSH", mode="A", loco=False, chunk_size=10000, precision=_lib.PREC_FP16, n_gpus=1, max_events=1 << 16):
+    """grm_run with the observer's events recorded: [(name, a, b)] in the order the observer saw them (see gelex_b200_grm_run_events)."""
+    h = load_host()
+    m = _lib.METHODS[method] if isinstance(method, str) else int(method)
+    err = C.create_string_buffer(2048)
+    ev = np.zeros((max_events, 3), dtype=np.int64)
+    n = C.c_int64()
+    st = h.gelex_b200_grm_run_events(str(bfile).encode(), str(out_prefix).encode(), m, MODES[mode], int(loco), int(chunk_size), int(precision),
+                                     int(n_gpus), ev.ctypes.data_as(C.c_void_p), max_events, C.byref(n), err, len(err))
+    if st != 0:
+        raise EngineError(st, err.value.decode())
+    assert n.value <= max_events, "event buffer too small"
+    return [(EVENT_NAMES[int(t)], int(a), int(b)) for t, a, b in ev[: n.value]]
 
 
 def plan(bfile, mode="A", loco=False, max_samples=1 << 22, max_items=4096):

@@ -754,3 +754,34 @@ def test_engine_direct_dma_into_the_output_mapping_matches_the_staged_writer(tmp
             assert (shm / f"dma{suffix}").read_bytes() == (shm / f"staged{suffix}").read_bytes(), suffix
     finally:
         shutil.rmtree(shm, ignore_errors=True)
+
+
+@pytest.mark.gpu
+def test_observer_sees_the_events_of_the_reference_in_its_order(tmp_path, monkeypatch):
+    # The reference's observer gets, per work item in plan order (per chromosome group: add, then dom), one (current, total) event per
+    # chunk with `current` counted inside the item (grm.h:124-130, grm_engine.cpp:78-110), bracketed by the dataset / total-work events
+    # and the done + files-written events.  The engine computes add and dom of a range in ONE pass: the dom item's events are replayed
+    # when the pass over the range completes, so the sequence is the reference's.
+    n, m, chunk = 300, 1000, 128
+    bed = g.synth_bed_host(n, 0, m, 5, 0.01)
+    chroms = ["1"] * 400 + ["2"] * 250 + ["7"] * 350
+    plink_io.write_plink(tmp_path / "d", bed, [("F", f"s{i:04d}") for i in range(n)], chroms)
+    for mode in ("A", "D", "AD"):
+        for loco in (False, True):
+            p = engine.plan(tmp_path / "d", mode=mode, loco=loco)
+            total = sum(e - b for _, b, e in p["items"])
+            want = [("data_loaded", n, m), ("compute_started", total, 0)]
+            for _, b, e in p["items"]:   # plan order = the reference's item order
+                want += [("progress", min(s + chunk, e) - b, e - b) for s in range(b, e, chunk)]
+            want += [("progress_done", total, total), ("files_written", 2 * len(p["items"]), 0)]
+            got = engine.grm_run_events(tmp_path / "d", tmp_path / f"o_{mode}_{int(loco)}", method="SH", mode=mode, loco=loco, chunk_size=chunk)
+            assert got == want, (mode, loco)
+    # SNP shards on two GPUs: chunks are cut inside every shard, so `current` advances in other steps; the two items still come one
+    # after the other, each monotone and ending at (m, m)
+    monkeypatch.setenv("GELEX_B200_OVERSUBSCRIBE", "1")
+    got = engine.grm_run_events(tmp_path / "d", tmp_path / "o2", method="SH", mode="AD", loco=False, chunk_size=chunk, n_gpus=2)
+    prog = [(a, b) for name, a, b in got if name == "progress"]
+    half = len(prog) // 2
+    assert len(prog) % 2 == 0 and prog[:half] == prog[half:]
+    cur = [a for a, _ in prog[:half]]
+    assert cur == sorted(cur) and cur[-1] == m and all(b == m for _, b in prog)
